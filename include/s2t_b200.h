@@ -1,0 +1,229 @@
+/*
+ * s2t_b200 — C ABI of the B200-native S2T speech-encoder hot path.
+ *
+ * Drop-in boundary (last row): these are the entry points the reference's Python
+ * plugin layer binds instead of the torch / torchaudio library calls it makes today.  Every function
+ *   - takes raw DEVICE pointers (unless the name ends in `_host`), integer shapes and a CUDA stream
+ *     (passed as void* == cudaStream_t), never a torch type;
+ *   - never allocates, frees or keeps a pointer: the caller owns all buffers and workspaces;
+ *   - is asynchronous on `stream`;
+ *   - returns 0 on success, a negative status otherwise; s2t_last_error() gives the message
+ *     (thread-local).
+ *
+ * All kernels are compiled for sm_100a only; there is no CPU or other-arch fallback.
+ *
+ * Layout conventions: activations are row-major [rows = utterance-major b*T + t][channels];
+ * bf16 = __nv_bfloat16 storage, fp32 accumulate.  "ld*" = row stride in ELEMENTS.
+ */
+#ifndef S2T_B200_H_
+#define S2T_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define S2T_ABI_VERSION 1
+
+/* status / introspection ---------------------------------------------------------------------- */
+const char* s2t_last_error(void);
+int s2t_abi_version(void);
+/* compute capability of the current device as major*10+minor (100 on B200); negative on error */
+int s2t_device_arch(void);
+
+/* --------------------------------------------------------------------------------------------- */
+/* K4: tcgen05/TMEM GEMM family.                                                                  */
+/* Replaces torch.nn.Linear / torch.matmul / torch.bmm / nn.Conv1d on the reference path:         */
+/*   fairseq/modules/s2t_transformer_layer.py:49-50,59-65 (FFN), multihead_attention.py:246-265,  */
+/*   372-416 (q/k/v/out proj, QK^T, PV), espnet_multihead_attention.py:39-42,343-352,             */
+/*   modules/speech_to_text/subsampling.py:133-151 (Conv1d as implicit GEMM through an            */
+/*   overlapping-row tensor map), modules/speech_to_text/ctc.py:59 (vocabulary projection).       */
+/*                                                                                               */
+/*   out[z][m][n] = residual + out_scale * dropout( gate( act( alpha * sum_k A[z][m][k]*B[z][n][k] */
+/*                                                             + bias[n] ) ) )                    */
+/* --------------------------------------------------------------------------------------------- */
+enum { S2T_ACT_NONE = 0, S2T_ACT_RELU = 1, S2T_ACT_SWISH = 2 };
+enum {
+  S2T_GATE_NONE = 0,
+  S2T_GATE_POSITIVE = 1,   /* v = gate > 0 ? v : 0            (ReLU backward from saved output)   */
+  S2T_GATE_SWISH_GRAD = 2, /* v *= d swish(gate) / d gate     (Swish backward from saved input)   */
+  S2T_GATE_MUL = 3         /* v *= gate                                                           */
+};
+
+typedef struct s2t_gemm_args {
+  int M, N, K;
+  int nb1, nb2; /* two batch dims (0/1 = none); gridDim.z = nb1*nb2, z = z2*nb1 + z1              */
+  /* A: logical [M][K].  a_mn_major=0: memory [M][lda] (K contiguous).  =1: memory [K][lda] (M contiguous) */
+  const void* a;
+  int a_mn_major;
+  long long lda, a_bs1, a_bs2;
+  /* B: logical [N][K].  b_mn_major=0: memory [N][ldb] (K contiguous, the nn.Linear weight layout).
+   *                     =1: memory [K][ldb] (N contiguous)                                        */
+  const void* b;
+  int b_mn_major;
+  long long ldb, b_bs1, b_bs2;
+  /* output [M][ldc], bf16 or fp32 */
+  void* out;
+  int out_fp32;
+  long long ldc, c_bs1, c_bs2;
+  /* epilogue */
+  float alpha;      /* scales the accumulator                                                      */
+  const void* bias; /* bf16 [N] or NULL                                                            */
+  int act;          /* S2T_ACT_*                                                                   */
+  const void* gate; /* bf16 [M][ldg] or NULL                                                       */
+  int gate_mode;    /* S2T_GATE_*                                                                  */
+  long long ldg, g_bs1, g_bs2;
+  float dropout_p;  /* 0 = off; mask = Philox(seed, stream, element index), regenerable in backward */
+  unsigned long long dropout_seed;
+  unsigned int dropout_stream;
+  float out_scale;
+  const void* residual; /* bf16 [M][ldr] or NULL (ldr=0 -> ldc)                                    */
+  long long ldr, r_bs1, r_bs2;
+  int tile_n; /* 0 = auto, else 64/128/256                                                        */
+} s2t_gemm_args;
+
+int s2t_gemm_bf16(const s2t_gemm_args* args, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
+/* K1: Kaldi-compatible log-mel filterbank (+ utterance CMVN).                                    */
+/* Replaces fairseq/data/audio/audio_utils.py:59-79,82-103 (torchaudio.compliance.kaldi.fbank)    */
+/* and feature_transforms/utterance_cmvn.py:30-45.                                                */
+/* --------------------------------------------------------------------------------------------- */
+/* number of frames for n samples, snip_edges=True: 1 + (n - 400) / 160 (0 if n < 400)            */
+int s2t_fbank_num_frames(long long num_samples);
+/*
+ * wave      fp32 [B][wave_ld] samples in int16 scale (reference does not normalise, audio_utils.py:92)
+ * num_samples int32 [B] valid samples per utterance
+ * mel_w     fp32 [n_mels][257] mel filter weights computed on the host with torchaudio's fp32 formulas
+ *           (column 256 is zero) — shared with the oracle so both use the identical matrix
+ * mel_range int32 [n_mels][2] = [lo, hi) non-zero bin range of each filter (the matrix is sparse)
+ * window    fp32 [400] povey window
+ * out       [B] x out_bs + [max_frames][out_ld], fp32 or bf16; frames >= the utterance's own count
+ *           are zero filled (as the collater pads, speech_to_text_dataset.py:267-285)
+ * out_frames int32 [B] (written; may be NULL)
+ */
+int s2t_fbank_fwd(const float* wave, long long wave_ld, const int* num_samples, int batch,
+                  const float* mel_w, const int* mel_range, const float* window, int n_mels,
+                  void* out, int out_bf16, int max_frames, long long out_ld, long long out_bs,
+                  int* out_frames, void* stream);
+/* per-utterance, per-bin mean/variance normalisation over the valid frames (E[x^2]-E[x]^2 variance
+ * from pre-centring sums, floor 1e-10, utterance_cmvn.py:35-43).  feats fp32 [B] x in_bs +
+ * [max_frames][in_ld]; out fp32 or bf16 [B] x out_bs + [max_frames][out_ld] (may alias feats when
+ * fp32); frames >= num_frames[b] are written as zeros.                                            */
+int s2t_cmvn_utt(const float* feats, long long in_ld, long long in_bs, void* out, int out_bf16,
+                 long long out_ld, long long out_bs, const int* num_frames, int batch,
+                 int max_frames, int n_mels, int norm_means, int norm_vars, void* stream);
+/* (x - mean) / std with global statistics (feature_transforms/global_cmvn.py:26-29)              */
+int s2t_cmvn_global(const float* feats, long long in_ld, long long in_bs, void* out, int out_bf16,
+                    long long out_ld, long long out_bs, const int* num_frames, int batch,
+                    int max_frames, int n_mels, const float* mean, const float* std_, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
+/* K3: LayerNorm (fairseq/modules/layer_norm.py:30-35 -> nn.LayerNorm(C, eps=1e-5, affine)).      */
+/* x, y bf16 [rows][C]; gamma/beta bf16 [C]; stats fp32 [rows][2] = (mean, rstd) saved for bwd.   */
+/* --------------------------------------------------------------------------------------------- */
+int s2t_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* stats,
+                      int rows, int C, float eps, void* stream);
+/* dx = LN'(dy) (+ dx_residual if non-NULL).  dgamma/dbeta partials: fp32 [n_partials][2][C] in
+ * `partials` (n_partials from s2t_layernorm_bwd_partials), reduced by this call into bf16
+ * dgamma/dbeta (accumulate=1 adds to the existing values).                                        */
+int s2t_layernorm_bwd_partials(int rows, int C);
+int s2t_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* stats,
+                      const void* dx_residual, void* dx, float* partials, void* dgamma,
+                      void* dbeta, int accumulate, int rows, int C, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
+/* Elementwise / data-movement kernels of the path                                                */
+/* --------------------------------------------------------------------------------------------- */
+/* GLU over channel halves (subsampling.py:140-151: nn.GLU(dim=1) after each Conv1d):
+ * x bf16 [rows][2C] -> y[rows][ldy] = x[:, :C] * sigmoid(x[:, C:]).  With lengths != NULL the rows are
+ * utterance-major (row = b*T + t) and rows with t >= lengths[b] produce 0 (the padding mask the
+ * encoder applies after subsampling, s2t_transformer.py:1765); the backward zeroes their gradient. */
+int s2t_glu_fwd(const void* x, void* y, long long ldy, int rows, int C, const int* lengths, int T,
+                void* stream);
+int s2t_glu_bwd(const void* x, const void* dy, long long lddy, void* dx, int rows, int C,
+                const int* lengths, int T, void* stream);
+/* column sums: out[c] = sum_r x[r][c]  (bias gradients).  x bf16 [rows][ld]; out bf16 [C].        */
+int s2t_colsum(const void* x, long long ld, int rows, int C, void* out, int accumulate,
+               float* workspace, long long workspace_floats, void* stream);
+long long s2t_colsum_workspace_floats(int rows, int C);
+/* col2im for the strided Conv1d dgrad: dcol bf16 [B][T_out][k*C] -> dx bf16 [B][T_in][C],
+ * dx[b][t][c] = sum_{(t_out,j): stride*t_out + j - pad == t} dcol[b][t_out][j*C + c]            */
+int s2t_col2im1d(const void* dcol, void* dx, int batch, int t_in, int t_out, int C, int ksize,
+                 int stride, int pad, void* stream);
+/* embed block (s2t_transformer.py:1765-1794): y = dropout(scale * x * valid + pos_table[pos_idx])
+ * with pos_idx = t + 2 for valid frames (padding_idx 1 + cumsum, sinusoidal_positional_embedding
+ * via utils.make_positions) and the zero row for padded frames.  x,y bf16 [B][T][C];
+ * lengths int32 [B]; pos_table fp32 [n_pos][C] (NULL = no positional term).                       */
+int s2t_embed_fwd(const void* x, const int* lengths, const float* pos_table, int n_pos, void* y,
+                  int batch, int T, int C, float scale, float dropout_p,
+                  unsigned long long seed, unsigned int stream_id, void* stream);
+int s2t_embed_bwd(const void* dy, void* dx, int batch, int T, int C, float scale,
+                  float dropout_p, unsigned long long seed, unsigned int stream_id, void* stream);
+/* zero rows t >= lengths[b] of x bf16 [B][T][ld] in place (padding masks, s2t_transformer.py:1765,1828) */
+int s2t_mask_rows(void* x, const int* lengths, int batch, int T, int C, long long ld, void* stream);
+/* weight re-layout for the implicit-GEMM Conv1d: w bf16 [Cout][Cin][k] -> [Cout][k][Cin] (and back, summing nothing) */
+int s2t_permute_conv_weight(const void* w, void* out, int cout, int cin, int k, int inverse,
+                            void* stream);
+/* plain bf16 <-> fp32 casts and fills used by the host glue */
+int s2t_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
+int s2t_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
+/* Attention softmax (multihead_attention.py:383-400; espnet_multihead_attention.py:119-133).     */
+/* scores bf16 [nbh][Tq][ld] (q.k^T) -> probs = softmax_j( clamp(scale*(scores + bias)) ) over keys  */
+/* j < klen[b] in fp32, cast to bf16; keys >= klen[b] get probability 0.  b = z / heads.           */
+/* bias_mode: 0 none; 1 bias bf16 [nbh][Tq][ld_bias] added element-wise; 2 relative-position bias  */
+/* BD bf16 [nbh][T][ld_bias >= 2T-1] read through the rel_shift map BD[i][j - i + T - 1]           */
+/* (espnet_multihead_attention.py:292-311).  clamp <= 0 disables the clamp.                        */
+/* probs_drop (optional) = dropout(probs) with the regenerable Philox mask.                        */
+/* --------------------------------------------------------------------------------------------- */
+int s2t_attn_softmax_fwd(const void* scores, long long ld, const void* bias, long long ld_bias,
+                         int bias_mode, void* probs, void* probs_drop, const int* klen, int nbh,
+                         int heads, int Tq, int Tk, float scale, float clamp, float dropout_p,
+                         unsigned long long seed, unsigned int stream_id, void* stream);
+/* dscores = scale * probs * (dp - sum_k dp*probs), dp = dropout_mask * dprobs_drop / (1-p);
+ * dbias (optional, bias_mode 2 layout [nbh][T][ld_bias]) receives the same values un-shifted.     */
+int s2t_attn_softmax_bwd(const void* probs, const void* dprobs_drop, void* dscores, void* dbias,
+                         long long ld_bias, const int* klen, int nbh, int heads, int Tq, int Tk,
+                         long long ld, float scale, float dropout_p, unsigned long long seed,
+                         unsigned int stream_id, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
+/* K7/K8/K9: CTC head softmax, CTC loss forward/backward, greedy decode.                          */
+/* Replaces utils.log_softmax (fairseq/utils.py:477-481) + torch.nn.CTCLoss(blank, 'none',        */
+/* zero_infinity=True) (fairseq/criterions/ctc.py:243-245,435-474) and CTCDecoder greedy          */
+/* (fairseq/models/speech_to_text/s2t_ctc.py:312-347).                                            */
+/* logits bf16 or fp32, utterance-major [B][T][ldv] (V valid columns).                            */
+/* --------------------------------------------------------------------------------------------- */
+/* lse[b][t] = logsumexp_v logits[b][t][v] (fp32) */
+int s2t_row_lse(const void* logits, int is_bf16, long long ldv, int rows, int V, float* lse,
+                void* stream);
+long long s2t_ctc_workspace_bytes(int batch, int T, int max_target_len);
+/*
+ * targets int32 [B][tgt_ld] (already stripped of pad/eos, criterions/ctc.py:516-540),
+ * input_lengths / target_lengths int32 [B].
+ * Outputs: nll fp32 [B] (0 where infeasible: zero_infinity), and — when dlogits != NULL —
+ * dlogits[b][t][v] = grad_scale[b-independent] * (softmax(logits)[v] - occupancy[b][t][v]) for
+ * t < input_length, 0 elsewhere and 0 everywhere for infeasible utterances (the gradient of
+ * sum_b nll[b] through log_softmax, criterions/ctc.py:467-473).
+ */
+int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, const float* lse,
+                 const int* targets, long long tgt_ld, const int* input_lengths,
+                 const int* target_lengths, int batch, int T, int V, int max_target_len, int blank,
+                 float* nll, void* dlogits /*same dtype and layout as logits, or NULL*/,
+                 float grad_scale, void* workspace, long long workspace_bytes, void* stream);
+/*
+ * Greedy CTC: argmax over V (lowest index on ties), padded frames -> blank, collapse repeats,
+ * drop blank.  tokens int32 [B][T] (first out_lengths[b] valid, rest -1); frame_ids int32 [B][T]
+ * (required) receives the per-frame argmax after pad->blank.
+ */
+int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, const int* input_lengths,
+                   int batch, int T, int V, int blank, int* tokens, int* out_lengths,
+                   int* frame_ids, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* S2T_B200_H_ */

@@ -1,0 +1,527 @@
+// K7/K8/K9: CTC head log-softmax statistics, CTC loss forward/backward, greedy CTC decode.
+//
+// Replaces, on the reference path,
+//   utils.log_softmax(logits, dim=-1) in fp32                      (fairseq/utils.py:477-481)
+//   torch.nn.CTCLoss(blank=0, reduction="none", zero_infinity=True) (fairseq/criterions/ctc.py:243-245,
+//                                                                    435-474; ATen LossCTC alpha/beta)
+//   CTCDecoder greedy: argmax -> pad->blank -> unique_consecutive -> drop blank
+//                                                                   (fairseq/models/speech_to_text/s2t_ctc.py:312-347)
+//
+// The log-probabilities are never materialised: the loss works from the logits, one fp32 row-LSE
+// vector and the (2S+1)-state lattice; the gradient w.r.t. the LOGITS, softmax - occupancy, is written
+// once (algorithmic HBM traffic = read logits + write grad).
+//
+// Kernels:
+//   row_lse            one CTA per (b,t) row, online max/sum, 16-byte loads
+//   ctc_gather         lp_g[b][t][s] = logit[b][t][l'_s] - lse[b][t]  (parallel gather, so the serial
+//                      recursions below read contiguous, prefetchable fp32 rows)
+//   ctc_alpha_beta     grid (B, 2): y=0 forward (alpha, nll), y=1 backward (beta) recursion, lattice
+//                      row in shared memory, one __syncthreads per frame, lp rows prefetched 4 frames ahead
+//   ctc_dense_grad     dlogits = scale * softmax(logits) (0 for padded frames / infeasible utterances)
+//   ctc_occupancy      dlogits[b][t][l'_s] -= scale * gamma_t(s), duplicates of a label merged in smem
+//   argmax / collapse  greedy decode
+#include "common.cuh"
+
+#include <math.h>
+
+#include "../../include/s2t_b200.h"
+
+namespace s2t {
+
+constexpr float kNegInf = -INFINITY;
+
+__device__ __forceinline__ float load_logit(const void* p, int is_bf16, long long idx) {
+  return is_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[idx])
+                 : reinterpret_cast<const float*>(p)[idx];
+}
+
+__device__ __forceinline__ void online_merge(float& m, float& s, float m2, float s2) {
+  if (m2 == kNegInf) return;
+  if (m == kNegInf) {
+    m = m2;
+    s = s2;
+    return;
+  }
+  const float mm = fmaxf(m, m2);
+  s = s * __expf(m - mm) + s2 * __expf(m2 - mm);
+  m = mm;
+}
+
+// ---------------------------------------------------------------------------------------------
+// row LSE
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+row_lse_kernel(const void* __restrict__ logits, int is_bf16, long long ldv, int V,
+               float* __restrict__ lse) {
+  __shared__ float s_m[8], s_s[8];
+  const long long row = blockIdx.x;
+  float m = kNegInf, s = 0.f;
+  if (is_bf16) {
+    const __nv_bfloat16* x = reinterpret_cast<const __nv_bfloat16*>(logits) + row * ldv;
+    const int nv = V >> 3;
+    for (int i = threadIdx.x; i < nv; i += 256) {
+      const uint4 v = *reinterpret_cast<const uint4*>(x + i * 8);
+      const float f[8] = {bf16_lo(v.x), bf16_hi(v.x), bf16_lo(v.y), bf16_hi(v.y),
+                          bf16_lo(v.z), bf16_hi(v.z), bf16_lo(v.w), bf16_hi(v.w)};
+      float lm = f[0];
+#pragma unroll
+      for (int j = 1; j < 8; ++j) lm = fmaxf(lm, f[j]);
+      float ls = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ls += __expf(f[j] - lm);
+      online_merge(m, s, lm, ls);
+    }
+    for (int i = (nv << 3) + threadIdx.x; i < V; i += 256) online_merge(m, s, __bfloat162float(x[i]), 1.f);
+  } else {
+    const float* x = reinterpret_cast<const float*>(logits) + row * ldv;
+    const int nv = V >> 2;
+    for (int i = threadIdx.x; i < nv; i += 256) {
+      const float4 v = *reinterpret_cast<const float4*>(x + i * 4);
+      const float lm = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+      const float ls = __expf(v.x - lm) + __expf(v.y - lm) + __expf(v.z - lm) + __expf(v.w - lm);
+      online_merge(m, s, lm, ls);
+    }
+    for (int i = (nv << 2) + threadIdx.x; i < V; i += 256) online_merge(m, s, x[i], 1.f);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, m, o);
+    const float s2 = __shfl_xor_sync(0xffffffffu, s, o);
+    online_merge(m, s, m2, s2);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    s_m[warp] = m;
+    s_s[warp] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float M = s_m[0], S = s_s[0];
+    for (int w = 1; w < 8; ++w) online_merge(M, S, s_m[w], s_s[w]);
+    lse[row] = M + logf(S);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// workspace layout (all fp32 / int32, sizes in elements):
+//   lp_g  [B][T][Sp]   alpha [B][T][Sp]   beta [B][T][Sp]   leader int [B][Sp]   nll_raw [B]
+// ---------------------------------------------------------------------------------------------
+struct CtcWs {
+  float* lp_g;
+  float* alpha;
+  float* beta;
+  int* leader;
+  float* nll_raw;
+};
+
+__host__ __device__ inline long long ctc_ws_floats(int B, int T, int Sp) {
+  return 3ll * B * T * Sp + 1ll * B * Sp + B;
+}
+
+__device__ __forceinline__ int ext_label(const int* tgt, int s, int blank) {
+  return (s & 1) ? tgt[s >> 1] : blank;
+}
+
+__global__ void ctc_gather_kernel(const void* __restrict__ logits, int is_bf16, long long ldv,
+                                  const float* __restrict__ lse, const int* __restrict__ targets,
+                                  long long tgt_ld, const int* __restrict__ in_len,
+                                  const int* __restrict__ tgt_len, int T, int Sp, int V, int blank,
+                                  CtcWs ws) {
+  const int b = blockIdx.y;
+  const int Tb = min(in_len[b], T);
+  const int S = tgt_len[b];
+  const int Se = 2 * S + 1;
+  const int* tgt = targets + b * tgt_ld;
+  // leaders (first extended position carrying the same label); blank positions lead to 0
+  if (blockIdx.x == 0) {
+    for (int s = threadIdx.x; s < Sp; s += blockDim.x) {
+      int lead = s;
+      if (s < Se) {
+        if ((s & 1) == 0) lead = 0;
+        else {
+          const int l = tgt[s >> 1];
+          for (int k = 0; k < (s >> 1); ++k)
+            if (tgt[k] == l) {
+              lead = 2 * k + 1;
+              break;
+            }
+        }
+      }
+      ws.leader[b * Sp + s] = lead;
+    }
+  }
+  const long long n = static_cast<long long>(Tb) * Se;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int t = static_cast<int>(i / Se), s = static_cast<int>(i % Se);
+    int l = ext_label(tgt, s, blank);
+    l = min(max(l, 0), V - 1);
+    const long long row = static_cast<long long>(b) * T + t;
+    ws.lp_g[row * Sp + s] = load_logit(logits, is_bf16, row * ldv + l) - lse[row];
+  }
+}
+
+__device__ __forceinline__ float lse3(float a, float b, float c) {
+  const float m = fmaxf(fmaxf(a, b), c);
+  if (m == kNegInf) return kNegInf;
+  return m + logf(__expf(a - m) + __expf(b - m) + __expf(c - m));
+}
+
+constexpr int kCtcMaxPerThread = 4;  // Sp <= 4 * blockDim
+
+__global__ void ctc_alpha_beta_kernel(const int* __restrict__ targets, long long tgt_ld,
+                                      const int* __restrict__ in_len, const int* __restrict__ tgt_len,
+                                      int T, int Sp, int blank, CtcWs ws) {
+  extern __shared__ float s_lat[];  // [2][Sp + 4]
+  const int b = blockIdx.x;
+  const bool fwd = blockIdx.y == 0;
+  const int Tb = min(in_len[b], T);
+  const int S = tgt_len[b];
+  const int Se = 2 * S + 1;
+  const int* tgt = targets + b * tgt_ld;
+  const int stride = Sp + 4;
+  float* buf0 = s_lat + 2;           // two guard cells on each side hold -inf
+  float* buf1 = s_lat + stride + 2;
+  for (int i = threadIdx.x; i < 2 * stride; i += blockDim.x) s_lat[i] = kNegInf;
+
+  // can this state take the skip transition (from s-2 forward / to s+2 backward)?
+  bool skip[kCtcMaxPerThread];
+#pragma unroll
+  for (int k = 0; k < kCtcMaxPerThread; ++k) {
+    const int s = threadIdx.x + k * blockDim.x;
+    skip[k] = false;
+    if (s < Se && (s & 1)) {
+      if (fwd) skip[k] = s >= 3 && tgt[s >> 1] != tgt[(s >> 1) - 1];
+      else skip[k] = (s + 2 < Se) && tgt[s >> 1] != tgt[(s >> 1) + 1];
+    }
+  }
+  __syncthreads();
+  if (Tb <= 0) {
+    if (fwd && threadIdx.x == 0) ws.nll_raw[b] = (S == 0) ? 0.f : INFINITY;
+    return;
+  }
+  const float* lp = ws.lp_g + static_cast<long long>(b) * T * Sp;
+  float* lat = (fwd ? ws.alpha : ws.beta) + static_cast<long long>(b) * T * Sp;
+
+  float* prev = buf0;
+  float* cur = buf1;
+  // ---- boundary frame ----------------------------------------------------------------------------
+  {
+    const int t = fwd ? 0 : Tb - 1;
+#pragma unroll
+    for (int k = 0; k < kCtcMaxPerThread; ++k) {
+      const int s = threadIdx.x + k * blockDim.x;
+      if (s < Se) {
+        float v = kNegInf;
+        if (fwd) {
+          if (s <= 1) v = lp[static_cast<long long>(t) * Sp + s];
+        } else {
+          if (s >= Se - 2) v = lp[static_cast<long long>(t) * Sp + s];
+        }
+        prev[s] = v;
+        lat[static_cast<long long>(t) * Sp + s] = v;
+      }
+    }
+  }
+  __syncthreads();
+  // ---- recursion, lp rows prefetched kPf frames ahead ----------------------------------------------
+  constexpr int kPf = 4;
+  float pf[kPf][kCtcMaxPerThread];
+#pragma unroll
+  for (int d = 0; d < kPf; ++d) {
+    const int step = 1 + d;
+    const int t = fwd ? step : Tb - 1 - step;
+#pragma unroll
+    for (int k = 0; k < kCtcMaxPerThread; ++k) {
+      const int s = threadIdx.x + k * blockDim.x;
+      pf[d][k] = (step < Tb && s < Se) ? lp[static_cast<long long>(t) * Sp + s] : 0.f;
+    }
+  }
+  for (int step0 = 1; step0 < Tb; step0 += kPf) {
+#pragma unroll
+    for (int d = 0; d < kPf; ++d) {
+      const int step = step0 + d;
+      if (step < Tb) {  // block-uniform
+        const int t = fwd ? step : Tb - 1 - step;
+#pragma unroll
+        for (int k = 0; k < kCtcMaxPerThread; ++k) {
+          const int s = threadIdx.x + k * blockDim.x;
+          if (s < Se) {
+            float a, bb, c;
+            if (fwd) {
+              a = prev[s];
+              bb = prev[s - 1];
+              c = skip[k] ? prev[s - 2] : kNegInf;
+            } else {
+              a = prev[s];
+              bb = (s + 1 < Se) ? prev[s + 1] : kNegInf;
+              c = skip[k] ? prev[s + 2] : kNegInf;
+            }
+            const float v = lse3(a, bb, c) + pf[d][k];
+            cur[s] = v;
+            lat[static_cast<long long>(t) * Sp + s] = v;
+          }
+          // refill this prefetch slot with the row kPf frames further on
+          const int nstep = step + kPf;
+          const int nt = fwd ? nstep : Tb - 1 - nstep;
+          pf[d][k] = (nstep < Tb && s < Se) ? lp[static_cast<long long>(nt) * Sp + s] : 0.f;
+        }
+        __syncthreads();
+        float* tmp = prev;
+        prev = cur;
+        cur = tmp;
+      }
+    }
+  }
+  if (fwd && threadIdx.x == 0) {
+    const float a = prev[Se - 1];
+    const float c = Se >= 2 ? prev[Se - 2] : kNegInf;
+    const float m = fmaxf(a, c);
+    const float ll = (m == kNegInf) ? kNegInf : m + logf(__expf(a - m) + __expf(c - m));
+    ws.nll_raw[b] = -ll;
+  }
+}
+
+// dlogits = scale * softmax(logits) for valid frames of feasible utterances, 0 elsewhere; also
+// publishes nll with zero_infinity applied.
+__global__ void __launch_bounds__(256)
+ctc_dense_grad_kernel(const void* __restrict__ logits, int is_bf16, long long ldv,
+                      const float* __restrict__ lse, const int* __restrict__ in_len, int T, int V,
+                      const float* __restrict__ nll_raw, float* __restrict__ nll_out,
+                      void* __restrict__ dlogits, float scale) {
+  const long long row = blockIdx.x;
+  const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
+  const float nr = nll_raw[b];
+  const bool feasible = isfinite(nr);
+  if (t == 0 && threadIdx.x == 0 && nll_out != nullptr) nll_out[b] = feasible ? nr : 0.f;
+  if (dlogits == nullptr) return;
+  const bool live = feasible && t < in_len[b];
+  const float l = lse[row];
+  if (is_bf16) {
+    const __nv_bfloat16* x = reinterpret_cast<const __nv_bfloat16*>(logits) + row * ldv;
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(dlogits) + row * ldv;
+    const int nv = V >> 3;
+    for (int i = threadIdx.x; i < nv; i += 256) {
+      uint4 ov = make_uint4(0, 0, 0, 0);
+      if (live) {
+        const uint4 v = *reinterpret_cast<const uint4*>(x + i * 8);
+        ov.x = pack_bf16(scale * __expf(bf16_lo(v.x) - l), scale * __expf(bf16_hi(v.x) - l));
+        ov.y = pack_bf16(scale * __expf(bf16_lo(v.y) - l), scale * __expf(bf16_hi(v.y) - l));
+        ov.z = pack_bf16(scale * __expf(bf16_lo(v.z) - l), scale * __expf(bf16_hi(v.z) - l));
+        ov.w = pack_bf16(scale * __expf(bf16_lo(v.w) - l), scale * __expf(bf16_hi(v.w) - l));
+      }
+      *reinterpret_cast<uint4*>(o + i * 8) = ov;
+    }
+    for (int i = (nv << 3) + threadIdx.x; i < V; i += 256)
+      o[i] = __float2bfloat16(live ? scale * __expf(__bfloat162float(x[i]) - l) : 0.f);
+  } else {
+    const float* x = reinterpret_cast<const float*>(logits) + row * ldv;
+    float* o = reinterpret_cast<float*>(dlogits) + row * ldv;
+    for (int i = threadIdx.x; i < V; i += 256) o[i] = live ? scale * expf(x[i] - l) : 0.f;
+  }
+}
+
+// one CTA per (t, b): gamma_t(s) = exp(alpha + beta - lp + nll); merged per label; RMW on dlogits
+__global__ void ctc_occupancy_kernel(const int* __restrict__ targets, long long tgt_ld,
+                                     const int* __restrict__ in_len, const int* __restrict__ tgt_len,
+                                     int T, int Sp, int V, int blank, CtcWs ws, int is_bf16,
+                                     long long ldv, void* __restrict__ dlogits, float scale) {
+  extern __shared__ float s_occ[];  // [Sp]
+  const int t = blockIdx.x, b = blockIdx.y;
+  const float nr = ws.nll_raw[b];
+  if (!isfinite(nr) || t >= min(in_len[b], T)) return;
+  const int S = tgt_len[b];
+  const int Se = 2 * S + 1;
+  const int* tgt = targets + b * tgt_ld;
+  for (int s = threadIdx.x; s < Se; s += blockDim.x) s_occ[s] = 0.f;
+  __syncthreads();
+  const long long base = (static_cast<long long>(b) * T + t) * Sp;
+  for (int s = threadIdx.x; s < Se; s += blockDim.x) {
+    const float g = ws.alpha[base + s] + ws.beta[base + s] - ws.lp_g[base + s] + nr;
+    const float occ = (g == kNegInf || !(g == g)) ? 0.f : __expf(g);
+    if (occ != 0.f) atomicAdd(&s_occ[ws.leader[b * Sp + s]], occ);
+  }
+  __syncthreads();
+  const long long row = static_cast<long long>(b) * T + t;
+  for (int s = threadIdx.x; s < Se; s += blockDim.x) {
+    if (ws.leader[b * Sp + s] != s) continue;
+    const float occ = s_occ[s];
+    if (occ == 0.f) continue;
+    int l = ext_label(tgt, s, blank);
+    l = min(max(l, 0), V - 1);
+    const long long idx = row * ldv + l;
+    if (is_bf16) {
+      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(dlogits);
+      o[idx] = __float2bfloat16(__bfloat162float(o[idx]) - scale * occ);
+    } else {
+      float* o = reinterpret_cast<float*>(dlogits);
+      o[idx] -= scale * occ;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// greedy decode
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+ctc_argmax_kernel(const void* __restrict__ logits, int is_bf16, long long ldv,
+                  const int* __restrict__ in_len, int T, int V, int blank,
+                  int* __restrict__ frame_ids) {
+  __shared__ float s_v[8];
+  __shared__ int s_i[8];
+  const long long row = blockIdx.x;
+  const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
+  if (t >= in_len[b]) {  // padded frames decode to blank (s2t_ctc.py:329-338)
+    if (threadIdx.x == 0) frame_ids[row] = blank;
+    return;
+  }
+  float best = kNegInf;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < V; i += 256) {
+    const float v = load_logit(logits, is_bf16, row * ldv + i);
+    if (v > best || (v == best && i < bi)) {
+      best = v;
+      bi = i;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float v2 = __shfl_xor_sync(0xffffffffu, best, o);
+    const int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (v2 > best || (v2 == best && i2 < bi)) {
+      best = v2;
+      bi = i2;
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    s_v[warp] = best;
+    s_i[warp] = bi;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w)
+      if (s_v[w] > best || (s_v[w] == best && s_i[w] < bi)) {
+        best = s_v[w];
+        bi = s_i[w];
+      }
+    frame_ids[row] = (bi == 0x7fffffff) ? blank : bi;
+  }
+}
+
+// one warp per utterance: keep[t] = id != blank && (t == 0 || id != id[t-1]); ballot prefix compaction
+__global__ void ctc_collapse_kernel(const int* __restrict__ frame_ids, int T, int blank,
+                                    int* __restrict__ tokens, int* __restrict__ out_len) {
+  const int b = blockIdx.x;
+  const int lane = threadIdx.x;
+  const int* ids = frame_ids + static_cast<long long>(b) * T;
+  int* out = tokens + static_cast<long long>(b) * T;
+  int count = 0;
+  for (int t0 = 0; t0 < T; t0 += 32) {
+    const int t = t0 + lane;
+    int id = blank, prev = -1;
+    if (t < T) {
+      id = ids[t];
+      prev = t > 0 ? ids[t - 1] : -1;
+    }
+    const bool keep = (t < T) && id != blank && id != prev;
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (keep) out[count + __popc(m & ((1u << lane) - 1u))] = id;
+    count += __popc(m);
+  }
+  for (int t = count + lane; t < T; t += 32) out[t] = -1;
+  if (lane == 0) out_len[b] = count;
+}
+
+}  // namespace s2t
+
+using namespace s2t;
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" int s2t_row_lse(const void* logits, int is_bf16, long long ldv, int rows, int V, float* lse,
+                           void* stream) {
+  S2T_REQUIRE(logits && lse, "s2t_row_lse: null pointer");
+  S2T_REQUIRE(V > 0, "s2t_row_lse: V must be positive");
+  S2T_REQUIRE(ldv % (is_bf16 ? 8 : 4) == 0, "s2t_row_lse: ldv alignment");
+  if (rows <= 0) return 0;
+  row_lse_kernel<<<rows, 256, 0, ST(stream)>>>(logits, is_bf16, ldv, V, lse);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" long long s2t_ctc_workspace_bytes(int batch, int T, int max_target_len) {
+  const int Sp = 2 * max_target_len + 1;
+  return 4 * ctc_ws_floats(batch, T, Sp) + 256;
+}
+
+extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, const float* lse,
+                            const int* targets, long long tgt_ld, const int* input_lengths,
+                            const int* target_lengths, int batch, int T, int V, int max_target_len,
+                            int blank, float* nll, void* dlogits, float grad_scale, void* workspace,
+                            long long workspace_bytes, void* stream) {
+  S2T_REQUIRE(logits && lse && targets && input_lengths && target_lengths && workspace,
+              "s2t_ctc_loss: null pointer");
+  S2T_REQUIRE(nll != nullptr, "s2t_ctc_loss: nll output required");
+  S2T_REQUIRE(max_target_len >= 0 && tgt_ld >= max_target_len, "s2t_ctc_loss: bad target shape");
+  S2T_REQUIRE(blank >= 0 && blank < V, "s2t_ctc_loss: blank out of range");
+  S2T_REQUIRE(workspace_bytes >= s2t_ctc_workspace_bytes(batch, T, max_target_len),
+              "s2t_ctc_loss: workspace too small");
+  S2T_REQUIRE(ldv % (is_bf16 ? 8 : 4) == 0, "s2t_ctc_loss: ldv alignment");
+  if (batch <= 0 || T <= 0) return 0;
+  const int Sp = 2 * max_target_len + 1;
+  int threads = ((Sp + 31) / 32) * 32;
+  if (threads > 1024) threads = 1024;
+  if (threads < 64) threads = 64;
+  S2T_REQUIRE(Sp <= kCtcMaxPerThread * threads, "s2t_ctc_loss: target too long (2S+1=%d > %d)", Sp,
+              kCtcMaxPerThread * threads);
+  CtcWs ws;
+  float* base = reinterpret_cast<float*>(workspace);
+  const long long n = 1ll * batch * T * Sp;
+  ws.lp_g = base;
+  ws.alpha = base + n;
+  ws.beta = base + 2 * n;
+  ws.leader = reinterpret_cast<int*>(base + 3 * n);
+  ws.nll_raw = base + 3 * n + 1ll * batch * Sp;
+  cudaStream_t st = ST(stream);
+
+  {
+    int gx = static_cast<int>((1ll * T * Sp + 255) / 256);
+    if (gx > 64) gx = 64;
+    if (gx < 1) gx = 1;
+    ctc_gather_kernel<<<dim3(gx, batch), 256, 0, st>>>(logits, is_bf16, ldv, lse, targets, tgt_ld,
+                                                      input_lengths, target_lengths, T, Sp, V, blank, ws);
+    S2T_LAUNCH_CHECK();
+  }
+  {
+    const size_t smem = sizeof(float) * 2 * (Sp + 4);
+    ctc_alpha_beta_kernel<<<dim3(batch, 2), threads, smem, st>>>(targets, tgt_ld, input_lengths,
+                                                                target_lengths, T, Sp, blank, ws);
+    S2T_LAUNCH_CHECK();
+  }
+  ctc_dense_grad_kernel<<<batch * T, 256, 0, st>>>(logits, is_bf16, ldv, lse, input_lengths, T, V,
+                                                  ws.nll_raw, nll, dlogits, grad_scale);
+  S2T_LAUNCH_CHECK();
+  if (dlogits != nullptr) {
+    int othreads = ((Sp + 31) / 32) * 32;
+    if (othreads > 256) othreads = 256;
+    ctc_occupancy_kernel<<<dim3(T, batch), othreads, sizeof(float) * Sp, st>>>(
+        targets, tgt_ld, input_lengths, target_lengths, T, Sp, V, blank, ws, is_bf16, ldv, dlogits,
+        grad_scale);
+    S2T_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+extern "C" int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, const int* input_lengths,
+                              int batch, int T, int V, int blank, int* tokens, int* out_lengths,
+                              int* frame_ids, void* stream) {
+  S2T_REQUIRE(logits && input_lengths && tokens && out_lengths && frame_ids,
+              "s2t_ctc_greedy: null pointer (frame_ids is a required [B][T] scratch/output)");
+  if (batch <= 0 || T <= 0) return 0;
+  ctc_argmax_kernel<<<batch * T, 256, 0, ST(stream)>>>(logits, is_bf16, ldv, input_lengths, T, V, blank,
+                                                      frame_ids);
+  S2T_LAUNCH_CHECK();
+  ctc_collapse_kernel<<<batch, 32, 0, ST(stream)>>>(frame_ids, T, blank, tokens, out_lengths);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,256 @@
+// K1: Kaldi-compatible 80-dim log-mel filterbank + CMVN on sm_100a.
+//
+// Replaces torchaudio.compliance.kaldi.fbank as called by the reference at
+// fairseq/data/audio/audio_utils.py:59-79 (num_mel_bins=80, sample_frequency=16000, everything else
+// default: 25 ms povey window, 10 ms shift, snip_edges, remove_dc_offset, preemphasis 0.97, power
+// spectrum, log floor = fp32 eps, dither 0) and UtteranceCMVN / GlobalCMVN
+// (fairseq/data/audio/feature_transforms/utterance_cmvn.py:30-45, global_cmvn.py:26-29).
+//
+// One warp owns one frame: 400 samples -> DC removal -> pre-emphasis -> window -> 512-point radix-2
+// FFT in shared memory (warp-synchronous, no block barriers) -> |X|^2 -> sparse mel projection (each
+// filter only touches its [lo,hi) bins) -> log.  Loads are coalesced (lane-strided), the waveform is
+// read once from HBM (frame overlap is served by L1/L2) and features are written once.
+#include "common.cuh"
+
+#include "../../include/s2t_b200.h"
+
+namespace s2t {
+
+constexpr int kFrameLen = 400;
+constexpr int kFrameShift = 160;
+constexpr int kFft = 512;
+constexpr int kBins = kFft / 2 + 1;  // 257
+constexpr int kFbankWarps = 8;
+
+__device__ __forceinline__ int bitrev9(int i) { return __brev(static_cast<unsigned>(i)) >> 23; }
+
+__global__ void __launch_bounds__(kFbankWarps * 32)
+fbank_kernel(const float* __restrict__ wave, long long wave_ld, const int* __restrict__ num_samples,
+             const float* __restrict__ mel_w, const int* __restrict__ mel_range,
+             const float* __restrict__ window, int n_mels, void* __restrict__ out, int out_bf16,
+             int max_frames, long long out_ld, long long out_bs, int* __restrict__ out_frames) {
+  __shared__ float2 s_fft[kFbankWarps][kFft];
+  __shared__ float s_pow[kFbankWarps][kBins + 3];
+  __shared__ float2 s_tw[kFft / 2];  // exp(-2*pi*i*k/512)
+
+  const int b = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int frame = blockIdx.x * kFbankWarps + warp;
+  const int ns = num_samples[b];
+  const int nframes = ns >= kFrameLen ? 1 + (ns - kFrameLen) / kFrameShift : 0;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && out_frames != nullptr)
+    out_frames[b] = nframes < max_frames ? nframes : max_frames;
+
+  for (int k = threadIdx.x; k < kFft / 2; k += blockDim.x) {
+    float s, c;
+    sincospif(-2.0f * static_cast<float>(k) / static_cast<float>(kFft), &s, &c);
+    s_tw[k] = make_float2(c, s);
+  }
+  __syncthreads();
+  if (frame >= max_frames) return;
+
+  float* orow_f = reinterpret_cast<float*>(out) + b * out_bs + static_cast<long long>(frame) * out_ld;
+  __nv_bfloat16* orow_h =
+      reinterpret_cast<__nv_bfloat16*>(out) + b * out_bs + static_cast<long long>(frame) * out_ld;
+  if (frame >= nframes) {  // zero-fill padding frames (collater zero-pads, speech_to_text_dataset.py:267-285)
+    for (int f = lane; f < n_mels; f += 32) {
+      if (out_bf16) orow_h[f] = __float2bfloat16(0.f);
+      else orow_f[f] = 0.f;
+    }
+    return;
+  }
+
+  // ---- load the frame (coalesced), remove DC offset --------------------------------------------
+  const float* src = wave + b * wave_ld + static_cast<long long>(frame) * kFrameShift;
+  float x[13];  // 400 = 12*32 + 16
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < 13; ++i) {
+    const int idx = i * 32 + lane;
+    x[i] = idx < kFrameLen ? __ldg(src + idx) : 0.f;
+    sum += x[i];
+  }
+  const float mean = warp_sum(sum) / static_cast<float>(kFrameLen);
+  // ---- pre-emphasis (replicate-padded first sample), povey window, bit-reversed scatter ---------
+  float2* fft = s_fft[warp];
+#pragma unroll
+  for (int i = 0; i < 13; ++i) {
+    const int idx = i * 32 + lane;
+    const float cur = x[i] - mean;
+    // previous sample lives in lane-1 of the same i, or lane 31 of i-1
+    float prev = __shfl_up_sync(0xffffffffu, cur, 1);
+    const float prev_row = __shfl_sync(0xffffffffu, (i > 0 ? x[i > 0 ? i - 1 : 0] - mean : 0.f), 31);
+    if (lane == 0) prev = (i == 0) ? cur : prev_row;
+    float v = 0.f;
+    if (idx < kFrameLen) v = (cur - 0.97f * prev) * __ldg(window + idx);
+    fft[bitrev9(idx)] = make_float2(v, 0.f);
+  }
+  // zero padding 416..511 (indices 400..415 were written above as v = 0)
+  for (int idx = 13 * 32 + lane; idx < kFft; idx += 32) fft[bitrev9(idx)] = make_float2(0.f, 0.f);
+  __syncwarp();
+
+  // ---- 512-point radix-2 DIT FFT, 256 butterflies per stage, 8 per lane -------------------------
+#pragma unroll
+  for (int st = 0; st < 9; ++st) {
+    const int half = 1 << st;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int t = j * 32 + lane;               // butterfly id 0..255
+      const int pos = t & (half - 1);
+      const int i0 = ((t >> st) << (st + 1)) + pos;
+      const int i1 = i0 + half;
+      const float2 w = s_tw[pos << (8 - st)];
+      const float2 a = fft[i0], c = fft[i1];
+      const float tr = c.x * w.x - c.y * w.y;
+      const float ti = c.x * w.y + c.y * w.x;
+      fft[i0] = make_float2(a.x + tr, a.y + ti);
+      fft[i1] = make_float2(a.x - tr, a.y - ti);
+    }
+    __syncwarp();
+  }
+  // ---- power spectrum: torchaudio does rfft().abs().pow(2) ----------------------------------------
+  float* pw = s_pow[warp];
+  for (int k = lane; k < kBins; k += 32) {
+    const float2 v = fft[k];
+    const float a = sqrtf(v.x * v.x + v.y * v.y);
+    pw[k] = a * a;
+  }
+  __syncwarp();
+  // ---- mel projection + log ---------------------------------------------------------------------
+  for (int f = lane; f < n_mels; f += 32) {
+    const int lo = mel_range[2 * f], hi = mel_range[2 * f + 1];
+    const float* wrow = mel_w + static_cast<long long>(f) * kBins;
+    float acc = 0.f;
+    for (int k = lo; k < hi; ++k) acc = fmaf(pw[k], __ldg(wrow + k), acc);
+    const float v = logf(fmaxf(acc, 1.1920928955078125e-07f));
+    if (out_bf16) orow_h[f] = __float2bfloat16(v);
+    else orow_f[f] = v;
+  }
+}
+
+// Per-utterance CMVN.  block = (n_mels-rounded-up, slices); double accumulators keep the
+// E[x^2]-E[x]^2 cancellation (utterance_cmvn.py:35-43) well inside the parity tolerance.
+__global__ void cmvn_utt_kernel(const float* __restrict__ in, long long in_ld, long long in_bs,
+                                void* __restrict__ out, int out_bf16, long long out_ld,
+                                long long out_bs, const int* __restrict__ num_frames, int max_frames,
+                                int n_mels, int norm_means, int norm_vars) {
+  extern __shared__ double s_red[];  // [slices][2][n_mels]
+  const int b = blockIdx.x;
+  const int f = threadIdx.x, sl = threadIdx.y, nsl = blockDim.y;
+  int T = num_frames[b];
+  if (T > max_frames) T = max_frames;
+  const float* src = in + b * in_bs;
+  double s = 0.0, ss = 0.0;
+  if (f < n_mels) {
+    for (int t = sl; t < T; t += nsl) {
+      const double v = static_cast<double>(src[static_cast<long long>(t) * in_ld + f]);
+      s += v;
+      ss += v * v;
+    }
+    s_red[(sl * 2 + 0) * n_mels + f] = s;
+    s_red[(sl * 2 + 1) * n_mels + f] = ss;
+  }
+  __syncthreads();
+  float mean = 0.f, inv_std = 1.f;
+  if (f < n_mels) {
+    double ts = 0.0, tss = 0.0;
+    for (int i = 0; i < nsl; ++i) {
+      ts += s_red[(i * 2 + 0) * n_mels + f];
+      tss += s_red[(i * 2 + 1) * n_mels + f];
+    }
+    const int Tn = T > 0 ? T : 1;
+    // mirror the reference's fp32 arithmetic on the (accurately summed) moments
+    const float m = static_cast<float>(ts / Tn);
+    const float sq = static_cast<float>(tss);
+    if (norm_means) mean = m;
+    if (norm_vars) {
+      float var = sq / static_cast<float>(Tn) - m * m;
+      inv_std = 1.0f / sqrtf(fmaxf(var, 1e-10f));
+    }
+  }
+  if (f < n_mels) {
+    for (int t = sl; t < max_frames; t += nsl) {
+      float v = 0.f;
+      if (t < T) {
+        v = src[static_cast<long long>(t) * in_ld + f];
+        v = (v - mean);
+        if (norm_vars) v = v * inv_std;
+      }
+      const long long o = b * out_bs + static_cast<long long>(t) * out_ld + f;
+      if (out_bf16) reinterpret_cast<__nv_bfloat16*>(out)[o] = __float2bfloat16(v);
+      else reinterpret_cast<float*>(out)[o] = v;
+    }
+  }
+}
+
+__global__ void cmvn_global_kernel(const float* __restrict__ in, long long in_ld, long long in_bs,
+                                   void* __restrict__ out, int out_bf16, long long out_ld,
+                                   long long out_bs, const int* __restrict__ num_frames,
+                                   int max_frames, int n_mels, const float* __restrict__ mean,
+                                   const float* __restrict__ std_) {
+  const int b = blockIdx.y;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<long long>(max_frames) * n_mels) return;
+  const int t = static_cast<int>(i / n_mels), f = static_cast<int>(i % n_mels);
+  int T = num_frames[b];
+  float v = 0.f;
+  if (t < T) v = (in[b * in_bs + static_cast<long long>(t) * in_ld + f] - mean[f]) / std_[f];
+  const long long o = b * out_bs + static_cast<long long>(t) * out_ld + f;
+  if (out_bf16) reinterpret_cast<__nv_bfloat16*>(out)[o] = __float2bfloat16(v);
+  else reinterpret_cast<float*>(out)[o] = v;
+}
+
+}  // namespace s2t
+
+using namespace s2t;
+
+extern "C" int s2t_fbank_num_frames(long long n) {
+  return n >= kFrameLen ? static_cast<int>(1 + (n - kFrameLen) / kFrameShift) : 0;
+}
+
+extern "C" int s2t_fbank_fwd(const float* wave, long long wave_ld, const int* num_samples, int batch,
+                             const float* mel_w, const int* mel_range, const float* window,
+                             int n_mels, void* out, int out_bf16, int max_frames, long long out_ld,
+                             long long out_bs, int* out_frames, void* stream) {
+  S2T_REQUIRE(wave && num_samples && mel_w && mel_range && window && out, "s2t_fbank_fwd: null pointer");
+  S2T_REQUIRE(n_mels > 0 && n_mels <= 128, "s2t_fbank_fwd: n_mels=%d out of range", n_mels);
+  if (batch <= 0 || max_frames <= 0) return 0;
+  dim3 grid((max_frames + kFbankWarps - 1) / kFbankWarps, batch);
+  fbank_kernel<<<grid, kFbankWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      wave, wave_ld, num_samples, mel_w, mel_range, window, n_mels, out, out_bf16, max_frames, out_ld,
+      out_bs, out_frames);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int s2t_cmvn_utt(const float* feats, long long in_ld, long long in_bs, void* out,
+                            int out_bf16, long long out_ld, long long out_bs, const int* num_frames,
+                            int batch, int max_frames, int n_mels, int norm_means, int norm_vars,
+                            void* stream) {
+  S2T_REQUIRE(feats && out && num_frames, "s2t_cmvn_utt: null pointer");
+  S2T_REQUIRE(n_mels > 0 && n_mels <= 128, "s2t_cmvn_utt: n_mels=%d out of range", n_mels);
+  if (batch <= 0 || max_frames <= 0) return 0;
+  const int fx = ((n_mels + 31) / 32) * 32;
+  const int slices = 1024 / fx >= 8 ? 8 : 1024 / fx;
+  dim3 block(fx, slices);
+  const size_t smem = sizeof(double) * slices * 2 * n_mels;
+  cmvn_utt_kernel<<<batch, block, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
+      feats, in_ld, in_bs, out, out_bf16, out_ld, out_bs, num_frames, max_frames, n_mels, norm_means,
+      norm_vars);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int s2t_cmvn_global(const float* feats, long long in_ld, long long in_bs, void* out,
+                               int out_bf16, long long out_ld, long long out_bs,
+                               const int* num_frames, int batch, int max_frames, int n_mels,
+                               const float* mean, const float* std_, void* stream) {
+  S2T_REQUIRE(feats && out && num_frames && mean && std_, "s2t_cmvn_global: null pointer");
+  if (batch <= 0 || max_frames <= 0) return 0;
+  const long long n = static_cast<long long>(max_frames) * n_mels;
+  dim3 grid(static_cast<unsigned>((n + 255) / 256), batch);
+  cmvn_global_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      feats, in_ld, in_bs, out, out_bf16, out_ld, out_bs, num_frames, max_frames, n_mels, mean, std_);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}

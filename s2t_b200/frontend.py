@@ -1,0 +1,111 @@
+"""Host side of the fbank front end: constant tables + the drop-in ``get_fbank`` replacements.
+
+Mirrors the reference interface ``fairseq/data/audio/audio_utils.py``:
+  * ``_get_torchaudio_fbank(waveform, sample_rate, n_bins=80) -> np.ndarray`` (``:59-79``)
+  * ``get_fbank(path_or_fp, n_bins=80)`` (``:82-103``; file decoding stays with the reference's
+    ``get_waveform``, only the feature computation is replaced)
+and adds the batched device entry point used when raw waveforms are collated to the GPU (config C2).
+
+The mel filter matrix and the povey window are computed once on the host with the same fp32 torch
+formulas torchaudio uses (``torchaudio/compliance/kaldi.py:436-511`` get_mel_banks, ``:_feature_window_function``)
+— SURVEY.md §8(a1) measured that re-deriving them in another precision costs 2/3 of the error budget.
+"""
+from __future__ import annotations
+
+import math
+from functools import lru_cache
+from typing import Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import ops
+
+SAMPLE_RATE = 16000
+FRAME_LEN, FRAME_SHIFT, FFT_LEN = 400, 160, 512
+
+
+def _mel_scalar(f: float) -> float:
+    return 1127.0 * math.log(1.0 + f / 700.0)
+
+
+def mel_filterbank(n_mels: int = 80, low_freq: float = 20.0, high_freq: float = 0.0,
+                   sample_rate: float = SAMPLE_RATE) -> torch.Tensor:
+    """[n_mels, 257] fp32 triangular mel weights (Kaldi, no VTLN); last column is zero."""
+    nyquist = 0.5 * sample_rate
+    if high_freq <= 0.0:
+        high_freq += nyquist
+    bin_width = sample_rate / FFT_LEN
+    lo, hi = _mel_scalar(low_freq), _mel_scalar(high_freq)
+    delta = (hi - lo) / (n_mels + 1)
+    idx = torch.arange(n_mels).unsqueeze(1)
+    left, center, right = lo + idx * delta, lo + (idx + 1.0) * delta, lo + (idx + 2.0) * delta
+    mel = (1127.0 * (1.0 + (bin_width * torch.arange(FFT_LEN // 2)) / 700.0).log()).unsqueeze(0)
+    w = torch.max(torch.zeros(1), torch.min((mel - left) / (center - left), (right - mel) / (right - center)))
+    return torch.nn.functional.pad(w, (0, 1)).to(torch.float32).contiguous()
+
+
+def mel_ranges(mel_w: torch.Tensor) -> torch.Tensor:
+    """[n_mels, 2] int32 = [lo, hi) range of non-zero bins of every filter."""
+    nz = mel_w != 0
+    n_bins = mel_w.shape[1]
+    ar = torch.arange(n_bins).unsqueeze(0).expand_as(mel_w)
+    lo = torch.where(nz, ar, torch.full_like(ar, n_bins)).min(dim=1).values
+    hi = torch.where(nz, ar + 1, torch.zeros_like(ar)).max(dim=1).values
+    lo = torch.minimum(lo, hi)
+    return torch.stack([lo, hi], dim=1).to(torch.int32).contiguous()
+
+
+def povey_window() -> torch.Tensor:
+    return torch.hann_window(FRAME_LEN, periodic=False, dtype=torch.float32).pow(0.85).contiguous()
+
+
+@lru_cache(maxsize=8)
+def _tables(device_str: str, n_mels: int):
+    dev = torch.device(device_str)
+    w = mel_filterbank(n_mels)
+    return w.to(dev), mel_ranges(w).to(dev), povey_window().to(dev)
+
+
+def num_frames(num_samples: int) -> int:
+    return 0 if num_samples < FRAME_LEN else 1 + (num_samples - FRAME_LEN) // FRAME_SHIFT
+
+
+def fbank_batch(wave: torch.Tensor, num_samples: torch.Tensor, n_mels: int = 80, *,
+                cmvn: Optional[str] = None, out: Optional[torch.Tensor] = None,
+                out_dtype: torch.dtype = torch.float32, max_frames: Optional[int] = None,
+                global_stats: Optional[Tuple[torch.Tensor, torch.Tensor]] = None,
+                scratch: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Device entry point: wave fp32 [B, N] (int16 scale) on CUDA -> (features [B, T, n_mels], frames int32 [B]).
+
+    ``cmvn`` in {None, "utterance", "global"}; padded frames are zero (collater semantics).
+    """
+    if not wave.is_cuda:
+        raise RuntimeError("fbank_batch needs CUDA tensors (s2t_b200 has no CPU path)")
+    mel_w, rng, win = _tables(str(wave.device), n_mels)
+    if max_frames is None:
+        max_frames = num_frames(wave.shape[1])
+    if cmvn is None:
+        return ops.fbank(wave, num_samples, mel_w, rng, win, max_frames, out=out, out_dtype=out_dtype)
+    raw, frames = ops.fbank(wave, num_samples, mel_w, rng, win, max_frames, out=scratch)
+    if cmvn == "utterance":
+        if out is None:
+            out = torch.empty(raw.shape, device=raw.device, dtype=out_dtype)
+        ops.cmvn_utt(raw, frames, out=out)
+    elif cmvn == "global":
+        if out is None:
+            out = torch.empty(raw.shape, device=raw.device, dtype=out_dtype)
+        ops.cmvn_global(raw, frames, global_stats[0], global_stats[1], out=out)
+    else:
+        raise ValueError(f"unknown cmvn {cmvn!r}")
+    return out, frames
+
+
+def _get_torchaudio_fbank(waveform, sample_rate, n_bins: int = 80) -> Optional[np.ndarray]:
+    """Drop-in for audio_utils.py:59-79: (N,) or (1, N) samples in int16 scale -> (T, n_bins) fp32 numpy."""
+    if sample_rate != SAMPLE_RATE:
+        raise ValueError("s2t_b200 fbank supports 16 kHz input (the path's sample rate)")
+    w = torch.as_tensor(np.asarray(waveform), dtype=torch.float32).reshape(1, -1).cuda()
+    n = torch.tensor([w.shape[1]], dtype=torch.int32, device=w.device)
+    feats, _ = fbank_batch(w, n, n_bins)
+    return feats[0].cpu().numpy()

@@ -1,0 +1,100 @@
+"""ctypes binding of libs2t_b200.so — the only way the Python host code reaches the CUDA kernels.
+
+There is no CPU or library fallback: if the shared library is missing, or a call is made without a
+B200-class device, the call raises.  Signatures mirror ``include/s2t_b200.h`` one to one.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+LIB_PATH = Path(__file__).resolve().parent / "libs2t_b200.so"
+
+_vp, _i, _ll, _f, _ull, _u = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong, C.c_uint
+
+ACT_NONE, ACT_RELU, ACT_SWISH = 0, 1, 2
+GATE_NONE, GATE_POSITIVE, GATE_SWISH_GRAD, GATE_MUL = 0, 1, 2, 3
+
+
+class GemmArgs(C.Structure):
+    """struct s2t_gemm_args (include/s2t_b200.h)."""
+
+    _fields_ = [
+        ("M", _i), ("N", _i), ("K", _i), ("nb1", _i), ("nb2", _i),
+        ("a", _vp), ("a_mn_major", _i), ("lda", _ll), ("a_bs1", _ll), ("a_bs2", _ll),
+        ("b", _vp), ("b_mn_major", _i), ("ldb", _ll), ("b_bs1", _ll), ("b_bs2", _ll),
+        ("out", _vp), ("out_fp32", _i), ("ldc", _ll), ("c_bs1", _ll), ("c_bs2", _ll),
+        ("alpha", _f), ("bias", _vp), ("act", _i),
+        ("gate", _vp), ("gate_mode", _i), ("ldg", _ll), ("g_bs1", _ll), ("g_bs2", _ll),
+        ("dropout_p", _f), ("dropout_seed", _ull), ("dropout_stream", _u),
+        ("out_scale", _f),
+        ("residual", _vp), ("ldr", _ll), ("r_bs1", _ll), ("r_bs2", _ll),
+        ("tile_n", _i),
+    ]
+
+
+# name -> (restype, argtypes); every symbol declared in include/s2t_b200.h must appear here
+SIGNATURES = {
+    "s2t_last_error": (C.c_char_p, []),
+    "s2t_abi_version": (_i, []),
+    "s2t_device_arch": (_i, []),
+    "s2t_gemm_bf16": (_i, [C.POINTER(GemmArgs), _vp]),
+    "s2t_fbank_num_frames": (_i, [_ll]),
+    "s2t_fbank_fwd": (_i, [_vp, _ll, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _ll, _ll, _vp, _vp]),
+    "s2t_cmvn_utt": (_i, [_vp, _ll, _ll, _vp, _i, _ll, _ll, _vp, _i, _i, _i, _i, _i, _vp]),
+    "s2t_cmvn_global": (_i, [_vp, _ll, _ll, _vp, _i, _ll, _ll, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    "s2t_layernorm_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
+    "s2t_layernorm_bwd_partials": (_i, [_i, _i]),
+    "s2t_layernorm_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "s2t_glu_fwd": (_i, [_vp, _vp, _ll, _i, _i, _vp, _i, _vp]),
+    "s2t_glu_bwd": (_i, [_vp, _vp, _ll, _vp, _i, _i, _vp, _i, _vp]),
+    "s2t_colsum": (_i, [_vp, _ll, _i, _i, _vp, _i, _vp, _ll, _vp]),
+    "s2t_colsum_workspace_floats": (_ll, [_i, _i]),
+    "s2t_col2im1d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "s2t_embed_fwd": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _f, _f, _ull, _u, _vp]),
+    "s2t_embed_bwd": (_i, [_vp, _vp, _i, _i, _i, _f, _f, _ull, _u, _vp]),
+    "s2t_mask_rows": (_i, [_vp, _vp, _i, _i, _i, _ll, _vp]),
+    "s2t_permute_conv_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "s2t_cast_f32_to_bf16": (_i, [_vp, _vp, _ll, _vp]),
+    "s2t_cast_bf16_to_f32": (_i, [_vp, _vp, _ll, _vp]),
+    "s2t_attn_softmax_fwd": (_i, [_vp, _ll, _vp, _ll, _i, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _f, _ull, _u, _vp]),
+    "s2t_attn_softmax_bwd": (_i, [_vp, _vp, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _ll, _f, _f, _ull, _u, _vp]),
+    "s2t_row_lse": (_i, [_vp, _i, _ll, _i, _i, _vp, _vp]),
+    "s2t_ctc_workspace_bytes": (_ll, [_i, _i, _i]),
+    "s2t_ctc_loss": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _ll, _vp]),
+    "s2t_ctc_greedy": (_i, [_vp, _i, _ll, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+}
+
+
+class S2TLibraryError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the CUDA library (once).  Raises if it has not been built — never falls back."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise S2TLibraryError(
+            f"{LIB_PATH} is missing: build it with `python -m s2t_b200.build` "
+            "(or __graft_entry__.build()). s2t_b200 has no CPU fallback."
+        )
+    lib = C.CDLL(str(LIB_PATH))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    if lib.s2t_abi_version() != 1:
+        raise S2TLibraryError("libs2t_b200.so ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+def check(status: int) -> None:
+    if status != 0:
+        msg = load().s2t_last_error().decode(errors="replace")
+        raise S2TLibraryError(f"s2t_b200 call failed ({status}): {msg}")

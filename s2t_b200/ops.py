@@ -1,0 +1,375 @@
+"""Thin torch-tensor wrappers over the C ABI (``include/s2t_b200.h``).
+
+torch is used for device memory and streams only; every computation below is one of our own sm_100a
+kernels called through ctypes.  Nothing here falls back to torch ops: a missing library or a non-CUDA
+tensor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import lib as _lib
+from .lib import ACT_NONE, ACT_RELU, ACT_SWISH, GATE_MUL, GATE_NONE, GATE_POSITIVE, GATE_SWISH_GRAD  # noqa: F401
+
+BF16 = torch.bfloat16
+
+#: number of kernel launches issued through this module (bench.py reports it as ``gpu_launches``)
+launch_count = 0
+_LAUNCHES = {
+    "s2t_gemm_bf16": 1, "s2t_fbank_fwd": 1, "s2t_cmvn_utt": 1, "s2t_cmvn_global": 1,
+    "s2t_layernorm_fwd": 1, "s2t_layernorm_bwd": 2, "s2t_glu_fwd": 1, "s2t_glu_bwd": 1,
+    "s2t_colsum": 2, "s2t_col2im1d": 1, "s2t_embed_fwd": 1, "s2t_embed_bwd": 1, "s2t_mask_rows": 1,
+    "s2t_permute_conv_weight": 1, "s2t_cast_f32_to_bf16": 1, "s2t_cast_bf16_to_f32": 1,
+    "s2t_attn_softmax_fwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4,
+    "s2t_ctc_greedy": 2,
+}
+
+
+def _call(name: str, *args) -> None:
+    global launch_count
+    fn = getattr(_lib.load(), name)
+    _lib.check(fn(*args))
+    launch_count += _LAUNCHES.get(name, 1)
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise _lib.S2TLibraryError("s2t_b200 kernels need CUDA tensors (no CPU fallback)")
+    return t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+# --------------------------------------------------------------------------------------------------
+# GEMM
+# --------------------------------------------------------------------------------------------------
+def gemm_raw(
+    *, M: int, N: int, K: int,
+    a: torch.Tensor, lda: int, a_mn: bool = False, a_bs: Tuple[int, int] = (0, 0), a_off: int = 0,
+    b: torch.Tensor, ldb: int, b_mn: bool = False, b_bs: Tuple[int, int] = (0, 0), b_off: int = 0,
+    out: torch.Tensor, ldc: int, c_bs: Tuple[int, int] = (0, 0), c_off: int = 0,
+    batch: Tuple[int, int] = (1, 1), alpha: float = 1.0, bias: Optional[torch.Tensor] = None,
+    act: int = ACT_NONE, gate: Optional[torch.Tensor] = None, gate_mode: int = GATE_NONE, ldg: int = 0,
+    g_bs: Tuple[int, int] = (0, 0), dropout: Optional[Tuple[float, int, int]] = None,
+    out_scale: float = 1.0, residual: Optional[torch.Tensor] = None, ldr: int = 0,
+    r_bs: Tuple[int, int] = (0, 0), tile_n: int = 0,
+) -> None:
+    """out[z] = residual + out_scale*dropout(gate(act(alpha * A[z] @ B[z]^T + bias))) — see s2t_b200.h.
+
+    ``*_off`` are element offsets into the given tensors (views into fused buffers, heads, …).
+    """
+    for t in (a, b):
+        if t.dtype != BF16:
+            raise TypeError("GEMM operands must be bf16")
+    if out.dtype not in (BF16, torch.float32):
+        raise TypeError("GEMM output must be bf16 or fp32")
+    g = _lib.GemmArgs()
+    g.M, g.N, g.K = M, N, K
+    g.nb1, g.nb2 = batch
+    g.a, g.a_mn_major, g.lda = _p(a) + 2 * a_off, int(a_mn), lda
+    g.a_bs1, g.a_bs2 = a_bs
+    g.b, g.b_mn_major, g.ldb = _p(b) + 2 * b_off, int(b_mn), ldb
+    g.b_bs1, g.b_bs2 = b_bs
+    g.out_fp32 = int(out.dtype == torch.float32)
+    g.out = _p(out) + out.element_size() * c_off
+    g.ldc = ldc
+    g.c_bs1, g.c_bs2 = c_bs
+    g.alpha = alpha
+    g.bias = _p(bias)
+    g.act = act
+    g.gate, g.gate_mode, g.ldg = _p(gate), gate_mode, ldg
+    g.g_bs1, g.g_bs2 = g_bs
+    if dropout is not None and dropout[0] > 0.0:
+        g.dropout_p, g.dropout_seed, g.dropout_stream = dropout
+    g.out_scale = out_scale
+    g.residual, g.ldr = _p(residual), ldr
+    g.r_bs1, g.r_bs2 = r_bs
+    g.tile_n = tile_n
+    _call("s2t_gemm_bf16", C.byref(g), _stream())
+
+
+def linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
+           out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = BF16, **epi) -> torch.Tensor:
+    """y[R, N] = epilogue(x[R, K] @ w[N, K]^T) — the nn.Linear contraction."""
+    R, K = x.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty((R, N), device=x.device, dtype=out_dtype)
+    gemm_raw(M=R, N=N, K=K, a=x, lda=x.stride(0), b=w, ldb=w.stride(0), out=out, ldc=out.stride(0),
+             bias=bias, **epi)
+    return out
+
+
+def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, *, out: Optional[torch.Tensor] = None, **epi) -> torch.Tensor:
+    """dx[R, K] = dy[R, N] @ w[N, K]  (B operand read MN-major: no transposed weight copy)."""
+    R, N = dy.shape
+    K = w.shape[1]
+    if out is None:
+        out = torch.empty((R, K), device=dy.device, dtype=BF16)
+    gemm_raw(M=R, N=K, K=N, a=dy, lda=dy.stride(0), b=w, ldb=w.stride(0), b_mn=True, out=out,
+             ldc=out.stride(0), **epi)
+    return out
+
+
+def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out: Optional[torch.Tensor] = None,
+                 out_dtype: torch.dtype = BF16, **epi) -> torch.Tensor:
+    """dw[N, K] = dy[R, N]^T @ x[R, K]  (both operands read MN-major)."""
+    R, N = dy.shape
+    K = x.shape[1]
+    if out is None:
+        out = torch.empty((N, K), device=dy.device, dtype=out_dtype)
+    gemm_raw(M=N, N=K, K=R, a=dy, lda=dy.stride(0), a_mn=True, b=x, ldb=x.stride(0), b_mn=True,
+             out=out, ldc=out.stride(0), **epi)
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# fbank / CMVN
+# --------------------------------------------------------------------------------------------------
+def fbank_num_frames(n: int) -> int:
+    return _lib.load().s2t_fbank_num_frames(n)
+
+
+def fbank(wave: torch.Tensor, num_samples: torch.Tensor, mel_w: torch.Tensor, mel_range: torch.Tensor,
+          window: torch.Tensor, max_frames: int, out: Optional[torch.Tensor] = None,
+          out_dtype: torch.dtype = torch.float32) -> Tuple[torch.Tensor, torch.Tensor]:
+    """wave fp32 [B, N] (int16 scale) -> log-mel [B, max_frames, n_mels], frames int32 [B]."""
+    B = wave.shape[0]
+    n_mels = mel_w.shape[0]
+    if out is None:
+        out = torch.empty((B, max_frames, n_mels), device=wave.device, dtype=out_dtype)
+    frames = torch.empty((B,), device=wave.device, dtype=torch.int32)
+    _call("s2t_fbank_fwd", _p(wave), wave.stride(0), _p(num_samples), B, _p(mel_w), _p(mel_range),
+          _p(window), n_mels, _p(out), int(out.dtype == BF16), max_frames, out.stride(1), out.stride(0),
+          _p(frames), _stream())
+    return out, frames
+
+
+def cmvn_utt(feats: torch.Tensor, num_frames: torch.Tensor, out: Optional[torch.Tensor] = None,
+             norm_means: bool = True, norm_vars: bool = True) -> torch.Tensor:
+    B, T, F = feats.shape
+    if out is None:
+        out = torch.empty_like(feats)
+    _call("s2t_cmvn_utt", _p(feats), feats.stride(1), feats.stride(0), _p(out), int(out.dtype == BF16),
+          out.stride(1), out.stride(0), _p(num_frames), B, T, F, int(norm_means), int(norm_vars), _stream())
+    return out
+
+
+def cmvn_global(feats: torch.Tensor, num_frames: torch.Tensor, mean: torch.Tensor, std: torch.Tensor,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    B, T, F = feats.shape
+    if out is None:
+        out = torch.empty_like(feats)
+    _call("s2t_cmvn_global", _p(feats), feats.stride(1), feats.stride(0), _p(out), int(out.dtype == BF16),
+          out.stride(1), out.stride(0), _p(num_frames), B, T, F, _p(mean), _p(std), _stream())
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# LayerNorm
+# --------------------------------------------------------------------------------------------------
+def layernorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,
+                  out: Optional[torch.Tensor] = None, stats: Optional[torch.Tensor] = None):
+    rows, Cd = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    if stats is None:
+        stats = torch.empty((rows, 2), device=x.device, dtype=torch.float32)
+    _call("s2t_layernorm_fwd", _p(x), _p(gamma), _p(beta), _p(out), _p(stats), rows, Cd, eps, _stream())
+    return out, stats
+
+
+def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, stats: torch.Tensor,
+                  dgamma: torch.Tensor, dbeta: torch.Tensor, *, dx_residual: Optional[torch.Tensor] = None,
+                  out: Optional[torch.Tensor] = None, accumulate: bool = False,
+                  partials: Optional[torch.Tensor] = None) -> torch.Tensor:
+    rows, Cd = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    if partials is None:
+        n = _lib.load().s2t_layernorm_bwd_partials(rows, Cd)
+        partials = torch.empty((n, 2, Cd), device=x.device, dtype=torch.float32)
+    _call("s2t_layernorm_bwd", _p(dy), _p(x), _p(gamma), _p(stats), _p(dx_residual), _p(out), _p(partials),
+          _p(dgamma), _p(dbeta), int(accumulate), rows, Cd, _stream())
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# elementwise
+# --------------------------------------------------------------------------------------------------
+def glu_fwd(x: torch.Tensor, out: Optional[torch.Tensor] = None, lengths: Optional[torch.Tensor] = None,
+            T: int = 0) -> torch.Tensor:
+    rows, C2 = x.shape
+    if out is None:
+        out = torch.empty((rows, C2 // 2), device=x.device, dtype=BF16)
+    _call("s2t_glu_fwd", _p(x), _p(out), out.stride(0), rows, C2 // 2, _p(lengths), T, _stream())
+    return out
+
+
+def glu_bwd(x: torch.Tensor, dy: torch.Tensor, out: Optional[torch.Tensor] = None,
+            lengths: Optional[torch.Tensor] = None, T: int = 0) -> torch.Tensor:
+    rows, C2 = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    _call("s2t_glu_bwd", _p(x), _p(dy), dy.stride(0), _p(out), rows, C2 // 2, _p(lengths), T, _stream())
+    return out
+
+
+def colsum(x: torch.Tensor, out: torch.Tensor, accumulate: bool = False,
+           workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+    rows, Cd = x.shape
+    need = _lib.load().s2t_colsum_workspace_floats(rows, Cd)
+    if workspace is None or workspace.numel() < need:
+        workspace = torch.empty((need,), device=x.device, dtype=torch.float32)
+    _call("s2t_colsum", _p(x), x.stride(0), rows, Cd, _p(out), int(accumulate), _p(workspace),
+          workspace.numel(), _stream())
+    return out
+
+
+def col2im1d(dcol: torch.Tensor, batch: int, t_in: int, t_out: int, Cd: int, ksize: int, stride: int,
+             pad: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if out is None:
+        out = torch.empty((batch, t_in, Cd), device=dcol.device, dtype=BF16)
+    _call("s2t_col2im1d", _p(dcol), _p(out), batch, t_in, t_out, Cd, ksize, stride, pad, _stream())
+    return out
+
+
+def embed_fwd(x: torch.Tensor, lengths: torch.Tensor, pos_table: Optional[torch.Tensor], scale: float,
+              dropout: Tuple[float, int, int] = (0.0, 0, 0), out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    B, T, Cd = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    n_pos = pos_table.shape[0] if pos_table is not None else 0
+    _call("s2t_embed_fwd", _p(x), _p(lengths), _p(pos_table), n_pos, _p(out), B, T, Cd, scale,
+          dropout[0], dropout[1], dropout[2], _stream())
+    return out
+
+
+def embed_bwd(dy: torch.Tensor, scale: float, dropout: Tuple[float, int, int] = (0.0, 0, 0),
+              out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    B, T, Cd = dy.shape
+    if out is None:
+        out = torch.empty_like(dy)
+    _call("s2t_embed_bwd", _p(dy), _p(out), B, T, Cd, scale, dropout[0], dropout[1], dropout[2], _stream())
+    return out
+
+
+def mask_rows_(x: torch.Tensor, lengths: torch.Tensor) -> torch.Tensor:
+    B, T, Cd = x.shape
+    _call("s2t_mask_rows", _p(x), _p(lengths), B, T, Cd, x.stride(1), _stream())
+    return x
+
+
+def permute_conv_weight(w: torch.Tensor, inverse: bool = False, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[Cout, Cin, k] -> [Cout, k, Cin] (inverse=False) or back."""
+    if not inverse:
+        cout, cin, k = w.shape
+        shape = (cout, k, cin)
+    else:
+        cout, k, cin = w.shape
+        shape = (cout, cin, k)
+    if out is None:
+        out = torch.empty(shape, device=w.device, dtype=BF16)
+    _call("s2t_permute_conv_weight", _p(w), _p(out), cout, cin, k, int(inverse), _stream())
+    return out
+
+
+def cast_f32_to_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if out is None:
+        out = torch.empty(x.shape, device=x.device, dtype=BF16)
+    _call("s2t_cast_f32_to_bf16", _p(x), _p(out), x.numel(), _stream())
+    return out
+
+
+def cast_bf16_to_f32(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if out is None:
+        out = torch.empty(x.shape, device=x.device, dtype=torch.float32)
+    _call("s2t_cast_bf16_to_f32", _p(x), _p(out), x.numel(), _stream())
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# attention softmax
+# --------------------------------------------------------------------------------------------------
+def attn_softmax_fwd(scores: torch.Tensor, klen: Optional[torch.Tensor], heads: int, Tk: int, *,
+                     probs: Optional[torch.Tensor] = None, probs_drop: Optional[torch.Tensor] = None,
+                     bias: Optional[torch.Tensor] = None, bias_mode: int = 0, scale: float = 1.0,
+                     clamp: float = 0.0, dropout: Tuple[float, int, int] = (0.0, 0, 0)):
+    """scores bf16 [nbh, Tq, ld]; returns (probs, probs_drop or None)."""
+    nbh, Tq, ld = scores.shape
+    if probs is None:
+        probs = torch.empty_like(scores)
+    ld_bias = bias.stride(1) if bias is not None else 0
+    _call("s2t_attn_softmax_fwd", _p(scores), ld, _p(bias), ld_bias, bias_mode, _p(probs), _p(probs_drop),
+          _p(klen), nbh, heads, Tq, Tk, scale, clamp, dropout[0], dropout[1], dropout[2], _stream())
+    return probs, probs_drop
+
+
+def attn_softmax_bwd(probs: torch.Tensor, dprobs_drop: torch.Tensor, klen: Optional[torch.Tensor],
+                     heads: int, Tk: int, *, out: Optional[torch.Tensor] = None,
+                     dbias: Optional[torch.Tensor] = None, scale: float = 1.0,
+                     dropout: Tuple[float, int, int] = (0.0, 0, 0)) -> torch.Tensor:
+    nbh, Tq, ld = probs.shape
+    if out is None:
+        out = torch.empty_like(probs)
+    ld_bias = dbias.stride(1) if dbias is not None else 0
+    _call("s2t_attn_softmax_bwd", _p(probs), _p(dprobs_drop), _p(out), _p(dbias), ld_bias, _p(klen), nbh,
+          heads, Tq, Tk, ld, scale, dropout[0], dropout[1], dropout[2], _stream())
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# CTC
+# --------------------------------------------------------------------------------------------------
+def row_lse(logits: torch.Tensor, V: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """logits [rows, ldv] (bf16 or fp32) -> fp32 [rows] log-sum-exp over the first V columns."""
+    rows = logits.shape[0]
+    if out is None:
+        out = torch.empty((rows,), device=logits.device, dtype=torch.float32)
+    _call("s2t_row_lse", _p(logits), int(logits.dtype == BF16), logits.stride(0), rows, V, _p(out), _stream())
+    return out
+
+
+def ctc_workspace_bytes(B: int, T: int, max_target_len: int) -> int:
+    return _lib.load().s2t_ctc_workspace_bytes(B, T, max_target_len)
+
+
+def ctc_loss(logits: torch.Tensor, targets: torch.Tensor, input_lengths: torch.Tensor,
+             target_lengths: torch.Tensor, V: int, blank: int = 0, *, need_grad: bool = True,
+             grad_scale: float = 1.0, lse: Optional[torch.Tensor] = None,
+             dlogits: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None):
+    """logits [B, T, ldv] utterance-major; targets int32 [B, Smax].  Returns (nll fp32 [B], dlogits|None)."""
+    B, T, ldv = logits.shape
+    smax = targets.shape[1]
+    flat = logits.view(B * T, ldv)
+    if lse is None:
+        lse = row_lse(flat, V)
+    need = ctc_workspace_bytes(B, T, smax)
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty(((need + 3) // 4,), device=logits.device, dtype=torch.float32)
+    nll = torch.empty((B,), device=logits.device, dtype=torch.float32)
+    if need_grad and dlogits is None:
+        dlogits = torch.empty_like(logits)
+    _call("s2t_ctc_loss", _p(logits), int(logits.dtype == BF16), ldv, _p(lse), _p(targets),
+          targets.stride(0), _p(input_lengths), _p(target_lengths), B, T, V, smax, blank, _p(nll),
+          _p(dlogits) if need_grad else None, grad_scale, _p(workspace),
+          workspace.numel() * workspace.element_size(), _stream())
+    return nll, (dlogits if need_grad else None)
+
+
+def ctc_greedy(logits: torch.Tensor, input_lengths: torch.Tensor, V: int, blank: int = 0):
+    """logits [B, T, ldv] -> (tokens int32 [B, T] padded with -1, lengths int32 [B], frame_ids int32 [B, T])."""
+    B, T, ldv = logits.shape
+    tokens = torch.empty((B, T), device=logits.device, dtype=torch.int32)
+    lens = torch.empty((B,), device=logits.device, dtype=torch.int32)
+    frame_ids = torch.empty((B, T), device=logits.device, dtype=torch.int32)
+    _call("s2t_ctc_greedy", _p(logits), int(logits.dtype == BF16), ldv, _p(input_lengths), B, T, V, blank,
+          _p(tokens), _p(lens), _p(frame_ids), _stream())
+    return tokens, lens, frame_ids

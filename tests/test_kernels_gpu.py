@@ -1,0 +1,295 @@
+"""GPU parity of the HBM-bound kernels (fbank/CMVN, LayerNorm, GLU, colsum, col2im, embed, softmax, CTC,
+greedy) through the C ABI, against the CPU oracle (oracle/) or — for plain floating-point elementwise
+math — an fp32 torch reference.  Tolerances are written next to each assertion."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+BF16 = torch.bfloat16
+
+
+def _rand(shape, seed, scale=1.0, dtype=BF16):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype)
+
+
+# ------------------------------------------------------------------------------------------------ fbank
+@pytest.mark.parametrize("lens", [[160000] * 2, [16000, 12345, 400, 399, 801]])
+def test_fbank_matches_oracle(cuda_lib, lens):
+    """fbank fp32: max-abs 1e-3 on log-mel values (north_star tolerance)."""
+    from oracle import fbank as O
+    from s2t_b200 import frontend
+    B, N = len(lens), max(lens)
+    g = torch.Generator().manual_seed(0)
+    wave = torch.randn((B, N), generator=g) * 3000.0
+    t = torch.arange(N) / 16000.0
+    wave += 2000.0 * torch.sin(2 * np.pi * 440.0 * t)
+    for b, n in enumerate(lens):
+        wave[b, n:] = 0
+    feats, frames = frontend.fbank_batch(wave.cuda(), torch.tensor(lens, dtype=torch.int32).cuda())
+    feats, frames = feats.cpu().numpy(), frames.cpu().numpy()
+    for b, n in enumerate(lens):
+        ref = O.fbank(wave[b, :n].numpy())
+        assert frames[b] == ref.shape[0] == O.num_frames(n)
+        if ref.shape[0]:
+            assert np.abs(feats[b, :frames[b]] - ref).max() < 1e-3
+        assert np.all(feats[b, frames[b]:] == 0)
+
+
+def test_fbank_utterance_cmvn_matches_oracle(cuda_lib):
+    """CMVN'd features: max-abs 2e-3."""
+    from oracle import fbank as O
+    from s2t_b200 import frontend
+    lens = [48000, 40000, 33333]
+    g = torch.Generator().manual_seed(1)
+    wave = torch.randn((3, 48000), generator=g) * 3000.0
+    feats, frames = frontend.fbank_batch(wave.cuda(), torch.tensor(lens, dtype=torch.int32).cuda(),
+                                         cmvn="utterance")
+    feats, frames = feats.cpu().numpy(), frames.cpu().numpy()
+    for b, n in enumerate(lens):
+        ref = O.utterance_cmvn(O.fbank(wave[b, :n].numpy()))
+        assert np.abs(feats[b, :frames[b]] - ref).max() < 2e-3
+        assert np.all(feats[b, frames[b]:] == 0)
+    # global CMVN
+    mean = torch.linspace(10, 20, 80)
+    std = torch.linspace(1, 3, 80)
+    gfeats, _ = frontend.fbank_batch(wave.cuda(), torch.tensor(lens, dtype=torch.int32).cuda(),
+                                     cmvn="global", global_stats=(mean.cuda(), std.cuda()))
+    ref = O.global_cmvn(O.fbank(wave[0].numpy()), mean.numpy(), std.numpy())
+    assert np.abs(gfeats[0].cpu().numpy() - ref).max() < 1e-3
+
+
+# ------------------------------------------------------------------------------------------------ LayerNorm
+@pytest.mark.parametrize("rows,C", [(2000, 256), (37, 512), (5, 80), (1000, 1024), (64, 176)])
+def test_layernorm_fwd_bwd(cuda_lib, rows, C):
+    from s2t_b200 import ops
+    x, gm, bt, dy = _rand((rows, C), 1, 2.0), _rand((C,), 2), _rand((C,), 3), _rand((rows, C), 4)
+    res = _rand((rows, C), 5)
+    y, stats = ops.layernorm_fwd(x.cuda(), gm.cuda(), bt.cuda())
+    xf = x.float().requires_grad_(True)
+    gf, bf = gm.float().requires_grad_(True), bt.float().requires_grad_(True)
+    ref = torch.nn.functional.layer_norm(xf, (C,), gf, bf, 1e-5)
+    assert (y.float().cpu() - ref).abs().max() <= 2 ** -7 * ref.abs().max()  # one bf16 rounding
+    ref.backward(dy.float())
+    dg = torch.empty((C,), device="cuda", dtype=BF16)
+    db = torch.empty((C,), device="cuda", dtype=BF16)
+    dx = ops.layernorm_bwd(dy.cuda(), x.cuda(), gm.cuda(), stats, dg, db, dx_residual=res.cuda())
+    torch.cuda.synchronize()
+    want_dx = xf.grad + res.float()
+    assert (dx.float().cpu() - want_dx).abs().max() <= 2 ** -6 * want_dx.abs().max()
+    assert (dg.float().cpu() - gf.grad).abs().max() <= 2 ** -6 * gf.grad.abs().max() + 1e-2
+    assert (db.float().cpu() - bf.grad).abs().max() <= 2 ** -6 * bf.grad.abs().max() + 1e-2
+
+
+# ------------------------------------------------------------------------------------------------ elementwise
+def test_glu_fwd_bwd_with_padding_mask(cuda_lib):
+    from s2t_b200 import ops
+    B, T, C = 3, 50, 128
+    lens = torch.tensor([50, 31, 7], dtype=torch.int32)
+    x, dy = _rand((B * T, 2 * C), 1), _rand((B * T, C), 2)
+    y = ops.glu_fwd(x.cuda(), lengths=lens.cuda(), T=T)
+    xf = x.float().requires_grad_(True)
+    mask = (torch.arange(T)[None, :] < lens[:, None]).reshape(B * T, 1).float()
+    ref = torch.nn.functional.glu(xf, dim=1) * mask
+    assert (y.float().cpu() - ref).abs().max() < 2 ** -7 * ref.abs().max()
+    ref.backward(dy.float())
+    dx = ops.glu_bwd(x.cuda(), dy.cuda(), lengths=lens.cuda(), T=T)
+    assert (dx.float().cpu() - xf.grad).abs().max() < 2 ** -7 * xf.grad.abs().max()
+    y2 = ops.glu_fwd(x.cuda())
+    assert (y2.float().cpu() - torch.nn.functional.glu(x.float(), dim=1)).abs().max() < 2 ** -7 * 10
+
+
+@pytest.mark.parametrize("rows,C", [(2000, 256), (63, 2048), (1, 8), (1000, 10000)])
+def test_colsum(cuda_lib, rows, C):
+    from s2t_b200 import ops
+    x = _rand((rows, C), 3)
+    out = torch.zeros((C,), device="cuda", dtype=BF16)
+    ops.colsum(x.cuda(), out)
+    ref = x.float().sum(0)
+    assert (out.float().cpu() - ref).abs().max() <= 2 ** -7 * ref.abs().max() + 1e-3
+    ops.colsum(x.cuda(), out, accumulate=True)
+    assert (out.float().cpu() - 2 * ref).abs().max() <= 2 ** -6 * 2 * ref.abs().max() + 1e-3
+
+
+def test_col2im1d_is_conv1d_input_grad(cuda_lib):
+    from s2t_b200 import ops
+    B, T, C, k, s, p = 2, 37, 16, 5, 2, 2
+    T_out = (T + 2 * p - k) // s + 1
+    dcol = _rand((B, T_out, k * C), 4)
+    dx = ops.col2im1d(dcol.cuda(), B, T, T_out, C, k, s, p)
+    ref = torch.zeros((B, T, C))
+    for to in range(T_out):
+        for j in range(k):
+            t = s * to + j - p
+            if 0 <= t < T:
+                ref[:, t] += dcol[:, to, j * C:(j + 1) * C].float()
+    assert (dx.float().cpu() - ref).abs().max() <= 2 ** -7 * ref.abs().max()
+
+
+def test_embed_fwd_bwd(cuda_lib):
+    from s2t_b200 import ops
+    B, T, C = 3, 40, 64
+    lens = torch.tensor([40, 25, 3], dtype=torch.int32)
+    x, dy = _rand((B, T, C), 5), _rand((B, T, C), 6)
+    table = torch.randn((T + 2, C), generator=torch.Generator().manual_seed(7))
+    table[1] = 0
+    y = ops.embed_fwd(x.cuda(), lens.cuda(), table.cuda(), 2.0)
+    valid = (torch.arange(T)[None, :] < lens[:, None])
+    pos = torch.where(valid[..., None], table[torch.arange(T) + 2][None].expand(B, T, C), torch.zeros(()))
+    ref = 2.0 * x.float() + pos
+    assert (y.float().cpu() - ref).abs().max() <= 2 ** -7 * ref.abs().max()
+    # dropout: regenerable mask, backward applies the same mask and scale
+    drop = (0.25, 99, 3)
+    yd = ops.embed_fwd(x.cuda(), lens.cuda(), table.cuda(), 2.0, dropout=drop).float().cpu()
+    kept = yd != 0
+    assert abs((~kept).float().mean().item() - 0.25) < 0.03
+    assert torch.allclose(yd[kept], (ref / 0.75).to(BF16).float()[kept], rtol=2e-2, atol=1e-2)
+    dx = ops.embed_bwd(dy.cuda(), 2.0, dropout=drop).float().cpu()
+    want = torch.where(kept, 2.0 * dy.float() / 0.75, torch.zeros(()))
+    assert (dx - want).abs().max() <= 2 ** -6 * want.abs().max()
+    m = x.clone().cuda()
+    ops.mask_rows_(m, lens.cuda())
+    assert torch.equal(m.cpu(), torch.where(valid[..., None], x, torch.zeros((), dtype=BF16)))
+
+
+# ------------------------------------------------------------------------------------------------ softmax
+@pytest.mark.parametrize("T", [250, 33])
+def test_attn_softmax_fwd_bwd(cuda_lib, T):
+    from s2t_b200 import ops
+    B, H = 2, 4
+    ld = (T + 7) // 8 * 8
+    klen = torch.tensor([T, T - 13], dtype=torch.int32)
+    s = torch.zeros((B * H, T, ld), dtype=BF16)
+    s[..., :T] = _rand((B * H, T, T), 1, 3.0)
+    dp = torch.zeros((B * H, T, ld), dtype=BF16)
+    dp[..., :T] = _rand((B * H, T, T), 2)
+    probs, _ = ops.attn_softmax_fwd(s.cuda(), klen.cuda(), H, T)
+    sf = s.float()[..., :T].view(B, H, T, T).requires_grad_(True)
+    mask = torch.arange(T)[None, None, None, :] >= klen[:, None, None, None]
+    ref = torch.softmax(sf.masked_fill(mask, float("-inf")), -1)
+    got = probs.float().cpu().view(B, H, T, ld)
+    assert (got[..., :T] - ref).abs().max() < 2 ** -8
+    assert got[..., T:].abs().max() == 0
+    (ref * dp.float()[..., :T].view(B, H, T, T)).sum().backward()
+    # feed the kernel the exact bf16 probs it produced
+    ds = ops.attn_softmax_bwd(probs, dp.cuda(), klen.cuda(), H, T)
+    got_ds = ds.float().cpu().view(B, H, T, ld)[..., :T]
+    assert (got_ds - sf.grad).abs().max() < 2 ** -6 * sf.grad.abs().max()
+
+
+def test_attn_softmax_relshift_bias_and_dropout(cuda_lib):
+    from s2t_b200 import ops
+    B, H, T = 1, 2, 40
+    ld, ldb = 40, 80
+    klen = torch.tensor([T - 5], dtype=torch.int32)
+    ac = _rand((B * H, T, ld), 3)
+    bd = torch.zeros((B * H, T, ldb), dtype=BF16)
+    bd[..., :2 * T - 1] = _rand((B * H, T, 2 * T - 1), 4)
+    scale = 0.125
+    probs, pd = ops.attn_softmax_fwd(ac.cuda(), klen.cuda(), H, T, bias=bd.cuda(), bias_mode=2, scale=scale,
+                                     clamp=1e8, probs_drop=torch.empty((B * H, T, ld), device="cuda", dtype=BF16),
+                                     dropout=(0.2, 5, 1))
+    i = torch.arange(T)[:, None]
+    j = torch.arange(T)[None, :]
+    shifted = bd.float()[..., :2 * T - 1].gather(-1, (j - i + T - 1).expand(B * H, T, T))  # BD[i, j-i+T-1]
+    sc = (ac.float() + shifted) * scale
+    sc = sc.masked_fill(j[None] >= klen[0], float("-inf"))
+    ref = torch.softmax(sc, -1)
+    assert (probs.float().cpu() - ref).abs().max() < 2 ** -8
+    pdc = pd.float().cpu()
+    kept = pdc != 0
+    live = ref > 1e-3
+    assert abs(1 - kept[live].float().mean().item() - 0.2) < 0.05
+    # backward with un-shift of the bias gradient
+    dpd = _rand((B * H, T, ld), 5)
+    dbias = torch.full((B * H, T, ldb), 7.0, device="cuda", dtype=BF16)
+    ds = ops.attn_softmax_bwd(probs, dpd.cuda(), klen.cuda(), H, T, dbias=dbias, scale=scale,
+                              dropout=(0.2, 5, 1)).float().cpu()
+    p = probs.float().cpu()
+    dpr = torch.where(kept, dpd.float() / 0.8, torch.zeros(()))
+    dpr = torch.where(j[None] < klen[0], dpr, torch.zeros(()))
+    want = scale * p * (dpr - (dpr * p).sum(-1, keepdim=True))
+    assert (ds - want).abs().max() < 2 ** -6 * want.abs().max() + 1e-4
+    db = dbias.float().cpu()
+    want_db = torch.zeros((B * H, T, 2 * T - 1))
+    want_db.scatter_(-1, (j - i + T - 1).expand(B * H, T, T), ds)
+    assert torch.equal(db[..., :2 * T - 1], want_db)
+
+
+# ------------------------------------------------------------------------------------------------ CTC
+def _ctc_case(seed, B, T, V, tlens, ilens, dtype):
+    rng = np.random.default_rng(seed)
+    logits = torch.from_numpy(rng.standard_normal((B, T, V)).astype(np.float32) * 2.0).to(dtype)
+    smax = max(max(tlens), 1)
+    tg = np.full((B, smax), 1, dtype=np.int32)
+    tgts = []
+    for b, n in enumerate(tlens):
+        row = rng.integers(1, V, size=n)
+        if n >= 4:
+            row[2] = row[1]  # repeated label needs a blank in between
+        tg[b, :n] = row
+        tgts.append(row)
+    return logits, tg, tgts
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, BF16])
+def test_ctc_loss_and_grad_match_oracle(cuda_lib, dtype):
+    """CTC loss rel 1e-3 (north_star); logits-gradient max-abs 1e-4 (fp32) / 2^-8 (bf16 storage)."""
+    from oracle import ctc as O
+    from s2t_b200 import ops
+    B, T, V = 5, 60, 104
+    tlens, ilens = [12, 0, 29, 40, 7], [60, 50, 59, 30, 8]   # utt 3 infeasible (S > T) -> zero_infinity
+    logits, tg, tgts = _ctc_case(0, B, T, V, tlens, ilens, dtype)
+    nll, dl = ops.ctc_loss(logits.cuda(), torch.from_numpy(tg).cuda(),
+                           torch.tensor(ilens, dtype=torch.int32).cuda(),
+                           torch.tensor(tlens, dtype=torch.int32).cuda(), V)
+    ref_nll, ref_grad = O.ctc_loss(logits.float().numpy(), tgts, ilens)
+    nll = nll.cpu().numpy()
+    assert ref_nll[3] == 0 and nll[3] == 0
+    assert np.allclose(nll, ref_nll, rtol=1e-3, atol=1e-3), (nll, ref_nll)
+    tol = 1e-4 if dtype == torch.float32 else 2 ** -8
+    assert np.abs(dl.float().cpu().numpy() - ref_grad).max() < tol
+    assert np.all(dl.float().cpu().numpy()[3] == 0)
+
+
+def test_ctc_loss_c1_shape(cuda_lib):
+    """BASELINE config-1 shape: B=8, T'=250, V=10000, S=60 — loss rel 1e-3 vs oracle on bf16 logits."""
+    from oracle import ctc as O
+    from s2t_b200 import ops
+    B, T, V = 8, 250, 10000
+    tlens, ilens = [60] * 8, [250, 250, 240, 230, 200, 190, 180, 150]
+    logits, tg, tgts = _ctc_case(1, B, T, V, tlens, ilens, BF16)
+    nll, dl = ops.ctc_loss(logits.cuda(), torch.from_numpy(tg).cuda(),
+                           torch.tensor(ilens, dtype=torch.int32).cuda(),
+                           torch.tensor(tlens, dtype=torch.int32).cuda(), V, grad_scale=0.5)
+    ref_nll, ref_grad = O.ctc_loss(logits.float().numpy(), tgts, ilens)
+    assert np.allclose(nll.cpu().numpy(), ref_nll, rtol=1e-3)
+    assert np.abs(dl.float().cpu().numpy() - 0.5 * ref_grad).max() < 2 ** -8
+    # size-independent property: every live frame's gradient sums to ~0 (softmax - occupancy)
+    rowsum = dl.float().sum(-1).cpu().numpy()
+    assert np.abs(rowsum).max() < 0.05
+
+
+def test_ctc_greedy_bit_exact(cuda_lib):
+    from oracle import ctc as O
+    from s2t_b200 import ops
+    B, T, V = 6, 97, 1000
+    rng = np.random.default_rng(3)
+    logits = rng.standard_normal((B, T, V)).astype(np.float32)
+    # long runs, blanks and crafted exact ties
+    for b in range(B):
+        for t in range(T):
+            logits[b, t, [0, 5, 5, 9, 0, 700][(t // 3 + b) % 6]] += 6.0
+    logits[0, 10, :] = 0.0            # full tie -> index 0 (blank)
+    logits[1, 11, 17] = logits[1, 11, 400] = 50.0  # two-way tie -> 17
+    ilens = [97, 96, 50, 1, 33, 64]
+    for dtype in (torch.float32, BF16):
+        lg = torch.from_numpy(logits).to(dtype)
+        tokens, lens, frame_ids = ops.ctc_greedy(lg.cuda(), torch.tensor(ilens, dtype=torch.int32).cuda(), V)
+        ref = O.greedy_decode(lg.float().numpy(), ilens)
+        tokens, lens = tokens.cpu().numpy(), lens.cpu().numpy()
+        for b in range(B):
+            assert lens[b] == len(ref[b])
+            assert np.array_equal(tokens[b, :lens[b]], ref[b])
+            assert np.all(tokens[b, lens[b]:] == -1)
