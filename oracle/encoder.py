@@ -1,0 +1,379 @@
+"""CPU oracle for the encoder + CTC head (TEST INFRASTRUCTURE — see oracle/__init__.py).
+
+A plain-PyTorch fp32 restatement of the reference modules on the hot path.  Every class cites the
+reference file:line it follows and keeps the reference's parameter names, so a ``state_dict`` moves
+between the reference (through oracle/ref_shim.py), this oracle and the product unchanged.  Autograd
+provides the backward pass.  Pinned against the reference itself by oracle/make_golden.py (run in the
+build container) and by the committed fixtures tests/golden/enc_*.npz.
+
+Also the timed CPU baseline (``bench.py --impl reference`` / ``cpu_baseline``): the structure mirrors the
+reference op for op (separate q/k/v Linear, bmm, fp32 softmax, Dropout modules, nn.CTCLoss) so its cost
+on host cores is the reference's cost.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+@dataclass
+class OracleConfig:
+    """Subset of the reference's args Namespace that the hot path reads (s2t_transformer.py:2256-2405)."""
+    input_dim: int = 80
+    embed_dim: int = 256
+    ffn_dim: int = 2048
+    heads: int = 4
+    layers: int = 12
+    subsampling_layers: int = 2
+    subsampling_filter: int = 1024
+    subsampling_kernel: int = 5
+    subsampling_stride: int = 2
+    attn_type: str = "selfattn"          # selfattn | rel_pos
+    encoder_embed_norm: bool = True
+    no_scale_embedding: bool = True
+    macaron_style: bool = False
+    use_cnn_module: bool = False
+    cnn_module_kernel: int = 15
+    cnn_module_norm: str = "batch_norm"
+    encoder_activation_fn: str = "relu"  # FFN activation
+    activation_fn: str = "relu"          # conv-module activation in S2TTransformerEncoderLayer (quirk A3)
+    layer_padding_mask: bool = False
+    dropout: float = 0.1
+    max_source_positions: int = 6000
+    vocab: int = 10000                   # source dictionary size (CTC head); 0 = no CTC head
+    tgt_vocab: int = 0                   # XCTC head (target vocabulary); 0 = none
+    inter_ctc_layers: Tuple[int, ...] = ()
+    inter_xctc_layers: Tuple[int, ...] = ()
+    share_inter_ctc: bool = True
+    ctc_pae: str = "none"                # none | inter_league
+    pae_unnorm_input: bool = False
+
+
+def lengths_to_padding_mask(lens: torch.Tensor, max_len: Optional[int] = None) -> torch.Tensor:
+    """fairseq/data/data_utils.py:518-522 — (B, T) bool, True = padding."""
+    max_len = int(lens.max()) if max_len is None else max_len
+    return torch.arange(max_len, device=lens.device)[None, :] >= lens[:, None]
+
+
+def act_fn(name: str):
+    return {"relu": F.relu, "swish": lambda x: x * torch.sigmoid(x), "gelu": F.gelu}[name]
+
+
+class Conv1dSubsampling(nn.Module):
+    """fairseq/modules/speech_to_text/subsampling.py:106-159 (act = glu, norm = none)."""
+
+    def __init__(self, num_layers, in_dim, filters, kernel_size, stride=2):
+        super().__init__()
+        self.layers = nn.ModuleList()
+        for i in range(num_layers):
+            cin = in_dim if i == 0 else filters[i - 1] // 2
+            cout = filters[i] * 2 if i == num_layers - 1 else filters[i]
+            # Sequential(conv, norm=Identity, GLU) in the reference -> parameter name layers.{i}.0.*
+            self.layers.append(nn.Sequential(
+                nn.Conv1d(cin, cout, kernel_size, stride=stride, padding=(kernel_size - 1) // 2),
+                nn.Identity(), nn.GLU(dim=1)))
+
+    def forward(self, x, x_len):
+        x = x.permute(1, 2, 0)                                   # (T,B,D) -> (B,D,T)
+        for layer in self.layers:
+            x = layer(x)
+            x_len = torch.div(x_len - 1, 2, rounding_mode="floor") + 1   # :155
+        return x.permute(2, 0, 1), x_len
+
+
+def sinusoidal_table(num_embeddings: int, dim: int, padding_idx: int = 1) -> torch.Tensor:
+    """fairseq/modules/sinusoidal_positional_embedding.py:34-58 — [sin | cos] halves, pad row zeroed."""
+    half = dim // 2
+    emb = math.log(10000) / (half - 1)
+    emb = torch.exp(torch.arange(half, dtype=torch.float) * -emb)
+    emb = torch.arange(num_embeddings, dtype=torch.float).unsqueeze(1) * emb.unsqueeze(0)
+    emb = torch.cat([torch.sin(emb), torch.cos(emb)], dim=1).view(num_embeddings, -1)
+    if dim % 2 == 1:
+        emb = torch.cat([emb, torch.zeros(num_embeddings, 1)], dim=1)
+    emb[padding_idx, :] = 0
+    return emb
+
+
+def abs_positions(padding_mask: torch.Tensor, dim: int, padding_idx: int = 1) -> torch.Tensor:
+    """PositionalEmbedding called on the bool padding mask (s2t_transformer.py:1784; quirk A6):
+    positions = cumsum(non-pad) * non-pad + padding_idx  (fairseq/utils.py:286-298)."""
+    nonpad = padding_mask.ne(padding_idx).int()               # True(=1) == padding_idx -> pad
+    pos = (torch.cumsum(nonpad, dim=1) * nonpad).long() + padding_idx
+    table = sinusoidal_table(int(pos.max()) + 1 + padding_idx, dim, padding_idx)
+    return table.index_select(0, pos.view(-1)).view(*pos.shape, dim)   # (B, T, C)
+
+
+def rel_positional_encoding(T: int, dim: int) -> torch.Tensor:
+    """fairseq/modules/positional_encoding.py:104-166 — (2T-1, 1, C); row k <-> relative position T-1-k,
+    interleaved sin/cos."""
+    position = torch.arange(0, T, dtype=torch.float32).unsqueeze(1)
+    div = torch.exp(torch.arange(0, dim, 2, dtype=torch.float32) * -(math.log(10000.0) / dim))
+    pos = torch.zeros(T, dim)
+    neg = torch.zeros(T, dim)
+    pos[:, 0::2], pos[:, 1::2] = torch.sin(position * div), torch.cos(position * div)
+    neg[:, 0::2], neg[:, 1::2] = torch.sin(-position * div), torch.cos(-position * div)
+    pe = torch.cat([torch.flip(pos, [0]), neg[1:]], dim=0)     # (2T-1, C)
+    return pe.unsqueeze(1)
+
+
+class FeedForwardModule(nn.Module):
+    """fairseq/modules/s2t_transformer_layer.py:26-66."""
+
+    def __init__(self, d, hidden, p, activation):
+        super().__init__()
+        self.w_1, self.w_2 = nn.Linear(d, hidden), nn.Linear(hidden, d)
+        self.dropout1, self.dropout2 = nn.Dropout(p), nn.Dropout(p)
+        self.activation = act_fn(activation)
+
+    def forward(self, x):
+        return self.dropout2(self.w_2(self.dropout1(self.activation(self.w_1(x)))))
+
+
+class MultiheadAttention(nn.Module):
+    """fairseq/modules/multihead_attention.py:24-431, encoder self-attention path only
+    (q scaled by d_k^-0.5 BEFORE QK^T :265, key-padding -inf :383-395, fp32 softmax, dropout on probs)."""
+
+    def __init__(self, d, heads, p):
+        super().__init__()
+        self.h, self.dk = heads, d // heads
+        self.q_proj, self.k_proj, self.v_proj, self.out_proj = (nn.Linear(d, d) for _ in range(4))
+        self.dropout = nn.Dropout(p)
+
+    def forward(self, x, padding_mask):                       # x (T,B,C); mask (B,T) True = pad
+        T, B, C = x.shape
+        q = self.q_proj(x) * self.dk ** -0.5
+        k, v = self.k_proj(x), self.v_proj(x)
+        q = q.contiguous().view(T, B * self.h, self.dk).transpose(0, 1)
+        k = k.contiguous().view(T, B * self.h, self.dk).transpose(0, 1)
+        v = v.contiguous().view(T, B * self.h, self.dk).transpose(0, 1)
+        w = torch.bmm(q, k.transpose(1, 2)).view(B, self.h, T, T)
+        w = w.masked_fill(padding_mask[:, None, None, :], float("-inf")).view(B * self.h, T, T)
+        w = self.dropout(F.softmax(w, dim=-1, dtype=torch.float32).type_as(w))
+        a = torch.bmm(w, v).transpose(0, 1).contiguous().view(T, B, C)
+        return self.out_proj(a)
+
+
+class RelPositionMultiHeadedAttention(nn.Module):
+    """fairseq/modules/espnet_multihead_attention.py:23-175 + :269-356 (rel_shift :292-311, quirk A5)."""
+
+    def __init__(self, d, heads, p):
+        super().__init__()
+        self.h, self.dk = heads, d // heads
+        self.linear_q, self.linear_k, self.linear_v, self.linear_out = (nn.Linear(d, d) for _ in range(4))
+        self.linear_pos = nn.Linear(d, d, bias=False)
+        self.pos_bias_u = nn.Parameter(torch.empty(heads, self.dk))
+        self.pos_bias_v = nn.Parameter(torch.empty(heads, self.dk))
+        nn.init.xavier_uniform_(self.pos_bias_u)
+        nn.init.xavier_uniform_(self.pos_bias_v)
+        self.dropout = nn.Dropout(p)
+
+    @staticmethod
+    def rel_shift(x):
+        b, h, t, n = x.shape
+        xp = torch.cat([x.new_zeros(b, h, t, 1), x], dim=-1).view(b, h, n + 1, t)
+        return xp[:, :, 1:].view_as(x)[:, :, :, : n // 2 + 1]
+
+    def forward(self, x, pos_emb, padding_mask):              # x (T,B,C); pos_emb (2T-1,1,C)
+        x = x.transpose(0, 1)
+        B, T, C = x.shape
+        q = self.linear_q(x).view(B, T, self.h, self.dk)
+        k = self.linear_k(x).view(B, T, self.h, self.dk).transpose(1, 2)
+        v = self.linear_v(x).view(B, T, self.h, self.dk).transpose(1, 2)
+        p = self.linear_pos(pos_emb.transpose(0, 1)).view(1, -1, self.h, self.dk).transpose(1, 2)
+        ac = torch.matmul((q + self.pos_bias_u).transpose(1, 2), k.transpose(-2, -1))
+        bd = self.rel_shift(torch.matmul((q + self.pos_bias_v).transpose(1, 2), p.transpose(-2, -1)))
+        s = (ac + bd) / math.sqrt(self.dk)
+        s = s.masked_fill(padding_mask[:, None, None, :], float("-inf"))
+        lim = 1e8 if s.dtype == torch.float32 else 1e4
+        s = s.clamp(min=-lim, max=lim)
+        a = self.dropout(F.softmax(s, dim=-1, dtype=torch.float32).type_as(s))
+        o = torch.matmul(a, v).transpose(1, 2).contiguous().view(B, T, C)
+        return self.linear_out(o).transpose(0, 1)
+
+
+class ConvolutionModule(nn.Module):
+    """fairseq/modules/convolution.py:8-120 (bias-free convs; BatchNorm1d over B*T incl. padded frames, A10)."""
+
+    def __init__(self, d, kernel, p, activation, norm_type="batch_norm"):
+        super().__init__()
+        self.pointwise_conv1 = nn.Conv1d(d, 2 * d, 1, bias=False)
+        self.depthwise_conv = nn.Conv1d(d, d, kernel, padding=(kernel - 1) // 2, groups=d, bias=False)
+        self.norm_type = norm_type
+        self.norm = nn.BatchNorm1d(d) if norm_type == "batch_norm" else nn.LayerNorm(d)
+        self.activation = act_fn(activation)
+        self.pointwise_conv2 = nn.Conv1d(d, d, 1, bias=False)
+        self.dropout = nn.Dropout(p)
+
+    def forward(self, x, padding_mask):                       # x (B,T,C)
+        x = x.transpose(1, 2)
+        zero = padding_mask.unsqueeze(1)
+        x = x.masked_fill(zero, 0.0)
+        x = F.glu(self.pointwise_conv1(x), dim=1)
+        x = self.depthwise_conv(x)
+        if self.norm_type == "layer_norm":
+            x = self.norm(x.transpose(1, 2)).transpose(1, 2)
+        else:
+            x = self.norm(x)
+        x = self.pointwise_conv2(self.activation(x))
+        x = x.masked_fill(zero, 0.0)
+        return self.dropout(x.transpose(1, 2))
+
+
+class EncoderLayer(nn.Module):
+    """fairseq/modules/s2t_transformer_layer.py:69-322, encoder_normalize_before=True (pre-norm)."""
+
+    def __init__(self, cfg: OracleConfig):
+        super().__init__()
+        d, p = cfg.embed_dim, cfg.dropout
+        self.attn_type = cfg.attn_type
+        if cfg.attn_type == "rel_pos":
+            self.self_attn = RelPositionMultiHeadedAttention(d, cfg.heads, p)
+        else:
+            self.self_attn = MultiheadAttention(d, cfg.heads, p)
+        self.self_attn_layer_norm = nn.LayerNorm(d)
+        self.dropout_module = nn.Dropout(p)
+        self.ffn_scale = 0.5 if cfg.macaron_style else 1.0
+        if cfg.macaron_style:
+            self.macaron_ffn = FeedForwardModule(d, cfg.ffn_dim, p, cfg.encoder_activation_fn)
+            self.macaron_norm = nn.LayerNorm(d)
+        else:
+            self.macaron_ffn = self.macaron_norm = None
+        if cfg.use_cnn_module:
+            self.conv_norm = nn.LayerNorm(d)
+            self.conv_module = ConvolutionModule(d, cfg.cnn_module_kernel, p, cfg.activation_fn, cfg.cnn_module_norm)
+            self.final_norm = nn.LayerNorm(d)
+        else:
+            self.conv_norm = self.conv_module = self.final_norm = None
+        self.ffn = FeedForwardModule(d, cfg.ffn_dim, p, cfg.encoder_activation_fn)
+        self.ffn_norm = nn.LayerNorm(d)
+
+    def forward(self, x, padding_mask, pos_emb=None):
+        if self.macaron_norm is not None:
+            x = x + self.ffn_scale * self.macaron_ffn(self.macaron_norm(x))
+        h = self.self_attn_layer_norm(x)
+        h = self.self_attn(h, pos_emb, padding_mask) if self.attn_type == "rel_pos" else self.self_attn(h, padding_mask)
+        x = x + self.dropout_module(h)
+        if self.conv_module is not None:
+            h = self.conv_module(self.conv_norm(x.transpose(0, 1)), padding_mask).transpose(0, 1)
+            x = x + h
+        x = x + self.ffn_scale * self.ffn(self.ffn_norm(x))
+        if self.conv_module is not None:
+            x = self.final_norm(x)
+        return x
+
+
+class CTC(nn.Module):
+    """fairseq/modules/speech_to_text/ctc.py:17-66 — [LayerNorm] -> dropout -> Linear(C, V) (quirk A11)."""
+
+    def __init__(self, d, vocab, p, need_layernorm=False):
+        super().__init__()
+        self.ctc_projection = nn.Linear(d, vocab)
+        nn.init.normal_(self.ctc_projection.weight, mean=0, std=d ** -0.5)
+        nn.init.constant_(self.ctc_projection.bias, 0.0)
+        self.ctc_dropout_module = nn.Dropout(p)
+        self.need_layernorm = need_layernorm
+        if need_layernorm:
+            self.LayerNorm = nn.LayerNorm(d)
+
+    def forward(self, x):
+        if self.need_layernorm:
+            x = self.LayerNorm(x)
+        return self.ctc_projection(self.ctc_dropout_module(x))
+
+
+class S2TTransformerEncoder(nn.Module):
+    """fairseq/models/speech_to_text/s2t_transformer.py:883 (init :887-1244, forward :1714-2154), for the
+    options of configs C1/C2/C4: conv1d subsampler, embed norm, abs or rel positions, pre-norm layers
+    (optionally macaron + conv module), final LayerNorm, CTC / XCTC heads on the top layer."""
+
+    def __init__(self, cfg: OracleConfig):
+        super().__init__()
+        self.cfg = cfg
+        d = cfg.embed_dim
+        self.dropout_module = nn.Dropout(cfg.dropout)
+        self.embed_scale = 1.0 if cfg.no_scale_embedding else math.sqrt(d)
+        filters = [cfg.subsampling_filter] * (cfg.subsampling_layers - 1) + [d]      # subsampling.py:231-247
+        self.subsample = Conv1dSubsampling(cfg.subsampling_layers, cfg.input_dim, filters,
+                                           cfg.subsampling_kernel, cfg.subsampling_stride)
+        if cfg.encoder_embed_norm:
+            self.embed_ln = nn.LayerNorm(d)
+        self.layers = nn.ModuleList([EncoderLayer(cfg) for _ in range(cfg.layers)])
+        self.layer_norm = nn.LayerNorm(d)
+        if cfg.vocab > 0:
+            self.ctc = CTC(d, cfg.vocab, cfg.dropout)
+        if cfg.tgt_vocab > 0:
+            self.xctc = CTC(d, cfg.tgt_vocab, cfg.dropout)
+
+    def forward(self, src_tokens: torch.Tensor, src_lengths: torch.Tensor) -> Dict[str, list]:
+        cfg = self.cfg
+        x = src_tokens.transpose(0, 1)                                     # :1728
+        x, lens = self.subsample(x, src_lengths)                           # :1748
+        pad = lengths_to_padding_mask(lens)                                # :1751
+        if pad.size(1) < x.size(0):                                        # :1752-1762 (quirk A9)
+            miss = torch.zeros(pad.size(0), x.size(0) - pad.size(1), dtype=torch.bool)
+            pad = torch.cat([miss, pad], dim=1)
+        x = x * (1 - pad.transpose(0, 1).unsqueeze(-1).type_as(x))        # :1765
+        if cfg.encoder_embed_norm:
+            x = self.embed_ln(x)                                           # :1768
+        x = self.embed_scale * x                                           # :1773
+        positions = None
+        if cfg.attn_type == "rel_pos":
+            positions = rel_positional_encoding(x.size(0), cfg.embed_dim).to(x.dtype)   # :1777
+        else:
+            x = x + abs_positions(pad, cfg.embed_dim).transpose(0, 1).to(x.dtype)       # :1784-1786
+        x = self.dropout_module(x)                                         # :1794
+        for layer in self.layers:                                          # :1824
+            if cfg.layer_padding_mask and not bool(pad.all()):
+                x = x.transpose(0, 1).masked_fill(pad.unsqueeze(2), 0.0).transpose(0, 1)  # :1828-1836
+            x = layer(x, pad, pos_emb=positions)                           # :1846
+        x = self.layer_norm(x)                                             # :2112
+        out = {"encoder_out": [x], "ctc_logit": [], "xctc_logit": [], "inter_ctc_logits": [],
+               "inter_xctc_logits": [], "encoder_padding_mask": [pad], "mixup": None,
+               "encoder_embedding": [], "encoder_states": [], "src_tokens": [], "src_lengths": []}
+        if cfg.vocab > 0:
+            out["ctc_logit"] = [self.ctc(x)]                               # :2126
+        if cfg.tgt_vocab > 0:
+            out["xctc_logit"] = [self.xctc(x)]                             # :2130
+        return out
+
+
+def ctc_criterion_loss(logit_tbv: torch.Tensor, padding_mask: torch.Tensor, tokens: torch.Tensor,
+                       pad: int = 1, eos: int = 2, blank: int = 0) -> torch.Tensor:
+    """CtcCriterion arithmetic (fairseq/criterions/ctc.py): input_lengths :556, targets :516-540,
+    fp32 log_softmax (s2t_ctc.py:98-112) and nn.CTCLoss(blank, 'none', zero_infinity=True).sum() :435-474."""
+    input_lengths = (~padding_mask).long().sum(-1)
+    mask = (tokens != pad) & (tokens != eos)
+    targets_flat = tokens.masked_select(mask)
+    target_lengths = mask.sum(-1)
+    lprobs = F.log_softmax(logit_tbv, dim=-1, dtype=torch.float32)
+    with torch.backends.cudnn.flags(enabled=False):
+        loss = F.ctc_loss(lprobs, targets_flat, input_lengths, target_lengths, blank=blank,
+                          reduction="none", zero_infinity=True)
+    return loss.sum()
+
+
+def config_from_args(args) -> OracleConfig:
+    """Map a reference-style args Namespace (after the arch function ran) onto OracleConfig."""
+    g = lambda k, d=None: getattr(args, k, d)
+    split = lambda s: tuple(int(v) for v in str(s).split(",")) if s else ()
+    return OracleConfig(
+        input_dim=g("input_feat_per_channel", 80) * g("input_channels", 1), embed_dim=args.encoder_embed_dim,
+        ffn_dim=args.encoder_ffn_embed_dim, heads=args.encoder_attention_heads, layers=args.encoder_layers,
+        subsampling_layers=g("subsampling_layers", 2), subsampling_filter=g("subsampling_filter", 1024),
+        subsampling_kernel=g("subsampling_kernel", 5), subsampling_stride=g("subsampling_stride", 2),
+        attn_type=g("encoder_attention_type", "selfattn"), encoder_embed_norm=g("encoder_embed_norm", False),
+        no_scale_embedding=g("encoder_no_scale_embedding", False), macaron_style=g("macaron_style", False),
+        use_cnn_module=g("use_cnn_module", False), cnn_module_kernel=g("cnn_module_kernel", 31),
+        cnn_module_norm=g("cnn_module_norm", "batch_norm"), encoder_activation_fn=g("encoder_activation_fn", "relu"),
+        activation_fn=g("activation_fn", "relu"), layer_padding_mask=g("layer_padding_mask", False),
+        dropout=args.dropout, max_source_positions=g("max_source_positions", 6000),
+        vocab=g("_src_vocab", 0) if g("ctc_weight", 0) > 0 else 0,
+        tgt_vocab=g("_tgt_vocab", 0) if g("xctc_weight", 0) > 0 else 0,
+        inter_ctc_layers=split(g("inter_ctc_layers")), inter_xctc_layers=split(g("inter_xctc_layers")),
+        share_inter_ctc=g("share_inter_ctc", False), ctc_pae=g("ctc_pae", "none"),
+        pae_unnorm_input=g("pae_unnorm_input", False))

@@ -1,0 +1,209 @@
+"""Generate tests/golden/*.npz from the REFERENCE ITSELF (run only in the build container).
+
+    python -m oracle.make_golden            # needs /root/reference
+
+For each case the unmodified reference modules (loaded through oracle/ref_shim.py) are run on seeded
+synthetic inputs with seeded weights; the restatement in oracle/ is checked against them on the spot
+(the script fails if they disagree) and the reference's outputs are stored.  Weights are NOT stored:
+both sides regenerate them with ``seeded_state_dict`` (torch CPU generator, platform independent) and
+the fixture keeps a checksum so a mismatch is detected.
+
+Fixtures:
+  fbank_cmvn.npz  : waveform -> torchaudio fbank -> reference UtteranceCMVN / GlobalCMVN
+  enc_<case>.npz  : features -> reference S2TTransformerEncoder -> ctc criterion loss, selected grads
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import sys
+from argparse import Namespace
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+GOLDEN = ROOT / "tests" / "golden"
+
+# name -> overrides of the reference args (on top of s2t_transformer_s + base.yaml-style flags)
+ENC_CASES = {
+    # C1 in miniature: s2t_transformer_s structure (conv1d x2 + GLU, embed norm, abs pos, pre-norm, relu FFN)
+    "c1_small": dict(encoder_layers=2, encoder_embed_dim=256, encoder_ffn_embed_dim=512,
+                     encoder_attention_heads=4, subsampling_filter=256, vocab=200, B=3, T=83, S=7),
+    # C4 in miniature: conformer.yaml (macaron, conv module k15 BatchNorm, rel_pos, swish FFN, layer mask)
+    "c4_small": dict(encoder_layers=2, encoder_embed_dim=256, encoder_ffn_embed_dim=512,
+                     encoder_attention_heads=4, subsampling_filter=256, vocab=200, B=3, T=83, S=7,
+                     macaron_style=True, use_cnn_module=True, cnn_module_kernel=15,
+                     encoder_attention_type="rel_pos", encoder_activation_fn="swish",
+                     layer_padding_mask=True),
+}
+
+
+def reference_args(**over) -> Namespace:
+    """egs/mustc/asr/conf/base.yaml + ctc.yaml flags that reach the encoder."""
+    a = Namespace(input_feat_per_channel=80, input_channels=1, max_source_positions=6000,
+                  encoder_embed_norm=True, encoder_no_scale_embedding=True, ctc_weight=0.3,
+                  dropout=0.0, fp16=False, activation_fn="relu")
+    vocab = over.pop("vocab", 10000)
+    for k in ("B", "T", "S"):
+        over.pop(k, None)
+    for k, v in over.items():
+        setattr(a, k, v)
+    a._src_vocab = a._tgt_vocab = vocab
+    return a
+
+
+def seeded_state_dict(shapes: dict, seed: int) -> dict:
+    """Deterministic weights for a {name: shape} map: N(0, 0.05) matrices, LayerNorm-like vectors near 1/0,
+    rounded to bf16-representable values so the bf16 product sees exactly the oracle's weights."""
+    g = torch.Generator().manual_seed(seed)
+    out = {}
+    for name in sorted(shapes):
+        shp = tuple(shapes[name])
+        if name.endswith("num_batches_tracked"):
+            out[name] = torch.zeros(shp, dtype=torch.long)
+            continue
+        t = torch.randn(shp, generator=g)
+        if name.endswith("running_var"):
+            t = 1.0 + 0.1 * t.abs()
+        elif name.endswith("running_mean"):
+            t = 0.1 * t
+        elif len(shp) == 1 and name.endswith("weight"):
+            t = 1.0 + 0.1 * t
+        elif len(shp) == 1:
+            t = 0.1 * t
+        else:
+            fan_in = int(np.prod(shp[1:])) if len(shp) > 1 else shp[0]
+            t = t * (1.0 / np.sqrt(fan_in))
+        out[name] = t.to(torch.bfloat16).to(torch.float32)
+    return out
+
+
+def state_checksum(sd: dict) -> str:
+    h = hashlib.sha256()
+    for k in sorted(sd):
+        h.update(k.encode())
+        h.update(sd[k].detach().cpu().contiguous().numpy().tobytes())
+    return h.hexdigest()
+
+
+def synth_batch(B: int, T: int, S: int, vocab: int, seed: int):
+    """asr_test_base.get_dummy_input style (tests/speech_recognition/asr_test_base.py:70-101): randn
+    features, descending ragged lengths, targets with pad=1 / eos=2."""
+    g = torch.Generator().manual_seed(seed)
+    feats = torch.randn((B, T, 80), generator=g)
+    lens = torch.tensor(sorted([T] + [int(v) for v in torch.randint(T // 2, T, (B - 1,), generator=g)], reverse=True))
+    for b in range(B):
+        feats[b, lens[b]:] = 0
+    tokens = torch.full((B, S + 1), 1, dtype=torch.long)
+    for b in range(B):
+        n = S - b
+        tokens[b, :n] = torch.randint(4, vocab, (n,), generator=g)
+        tokens[b, n] = 2
+    return feats, lens, tokens
+
+
+GRAD_KEYS = ["subsample.layers.0.0.weight", "subsample.layers.1.0.bias", "embed_ln.weight",
+             "layers.0.ffn.w_1.weight", "layers.1.ffn.w_2.bias", "layers.0.self_attn_layer_norm.bias",
+             "layer_norm.weight", "ctc.ctc_projection.weight"]
+
+
+def run_reference_encoder(case: str, seed: int = 0):
+    from oracle import encoder as OE
+    from oracle import ref_shim
+    ref = ref_shim.load()
+    spec = dict(ENC_CASES[case])
+    B, T, S, vocab = spec["B"], spec["T"], spec["S"], spec["vocab"]
+    args = reference_args(**spec)
+    ref.s2t.s2t_transformer_s(args)                         # arch defaults, s2t_transformer.py:2408-2415
+    task = ref.FakeTask(vocab, vocab)
+    torch.manual_seed(seed)
+    enc = ref.s2t.S2TTransformerEncoder(args, task, None)
+    shapes = {k: v.shape for k, v in enc.state_dict().items() if not k.endswith("_float_tensor")}
+    sd = seeded_state_dict(shapes, seed)
+    missing = enc.load_state_dict(sd, strict=False)
+    assert not missing.unexpected_keys and all(k.endswith("_float_tensor") for k in missing.missing_keys), missing
+    enc.train()                                             # dropout = 0, BatchNorm uses batch statistics
+
+    feats, lens, tokens = synth_batch(B, T, S, vocab, seed + 1)
+    out = enc(feats, lens)
+    logit = out["ctc_logit"][0]
+    pad = out["encoder_padding_mask"][0]
+    loss = OE.ctc_criterion_loss(logit, pad, tokens)
+    loss.backward()
+    ref_grads = {k: p.grad.clone() for k, p in enc.named_parameters()}
+
+    # ---- validate the restatement against the reference on the spot --------------------------------
+    cfg = OE.config_from_args(args)
+    orc = OE.S2TTransformerEncoder(cfg)
+    o_keys, r_keys = set(orc.state_dict().keys()), set(shapes.keys())
+    assert o_keys == r_keys, (sorted(o_keys - r_keys)[:5], sorted(r_keys - o_keys)[:5])
+    orc.load_state_dict(sd)
+    orc.train()
+    o_out = orc(feats, lens)
+    o_loss = OE.ctc_criterion_loss(o_out["ctc_logit"][0], o_out["encoder_padding_mask"][0], tokens)
+    o_loss.backward()
+    err_x = (o_out["encoder_out"][0] - out["encoder_out"][0]).abs().max().item()
+    err_l = (o_out["ctc_logit"][0] - logit).abs().max().item()
+    assert err_x < 1e-4 and err_l < 1e-4, (err_x, err_l)
+    assert abs(o_loss.item() - loss.item()) < 1e-3 * abs(loss.item())
+    for k, p in orc.named_parameters():
+        den = ref_grads[k].norm().item() + 1e-8
+        rel = (p.grad - ref_grads[k]).norm().item() / den
+        assert rel < 1e-3, (k, rel)
+    print(f"[{case}] oracle == reference: |dx|={err_x:.2e} |dlogit|={err_l:.2e} loss={loss.item():.4f}")
+
+    fix = dict(
+        case=case, seed=seed, weights_sha256=state_checksum(sd),
+        param_names=np.array(sorted(shapes)), param_shapes=np.array([str(tuple(shapes[k])) for k in sorted(shapes)]),
+        feats=feats.numpy(), lens=lens.numpy(), tokens=tokens.numpy(),
+        encoder_out=out["encoder_out"][0].detach().numpy(), ctc_logit=logit.detach().numpy(),
+        padding_mask=pad.numpy(), loss=np.float64(loss.item()),
+        torch_version=torch.__version__,
+    )
+    for k in GRAD_KEYS:
+        if k in ref_grads:
+            fix["grad::" + k] = ref_grads[k].numpy()
+    fix["grad_norms"] = np.array([ref_grads[k].norm().item() for k in sorted(ref_grads)])
+    fix["grad_names"] = np.array(sorted(ref_grads))
+    return fix
+
+
+def run_reference_fbank(seed: int = 0):
+    import torchaudio
+    import torchaudio.compliance.kaldi as K
+    from oracle import fbank as OF
+    from oracle import ref_shim
+    ref = ref_shim.load()
+    g = torch.Generator().manual_seed(seed)
+    n = 16000 * 2 + 321
+    wave = torch.randn((1, n), generator=g) * 3000.0 + 1500.0 * torch.sin(2 * np.pi * 440.0 * torch.arange(n) / 16000.0)
+    feat = K.fbank(wave, num_mel_bins=80, sample_frequency=16000).numpy()          # audio_utils.py:74-76
+    ucmvn = ref.utterance_cmvn.UtteranceCMVN()(feat.copy())
+    mean = feat.mean(axis=0).astype(np.float32) + 0.25
+    std = feat.std(axis=0).astype(np.float32) + 0.5
+    gc = ref.global_cmvn.GlobalCMVN.__new__(ref.global_cmvn.GlobalCMVN)
+    gc.mean, gc.std = mean, std
+    gcmvn = gc(feat.copy())
+    # validate the restatement
+    o = OF.fbank(wave[0].numpy())
+    assert np.abs(o - feat).max() < 2e-4, np.abs(o - feat).max()
+    assert np.abs(OF.utterance_cmvn(feat) - ucmvn).max() == 0
+    assert np.abs(OF.global_cmvn(feat, mean, std) - gcmvn).max() == 0
+    print(f"[fbank] oracle == torchaudio {torchaudio.__version__}: max-abs {np.abs(o - feat).max():.2e}; CMVN bit-exact")
+    return dict(wave=wave[0].numpy(), fbank=feat, utt_cmvn=ucmvn, gmean=mean, gstd=std, global_cmvn=gcmvn,
+                torchaudio_version=torchaudio.__version__)
+
+
+def main():
+    GOLDEN.mkdir(parents=True, exist_ok=True)
+    np.savez_compressed(GOLDEN / "fbank_cmvn.npz", **run_reference_fbank())
+    for case in ENC_CASES:
+        np.savez_compressed(GOLDEN / f"enc_{case}.npz", **run_reference_encoder(case))
+    for f in sorted(GOLDEN.glob("*.npz")):
+        print(f.name, f.stat().st_size // 1024, "KiB")
+
+
+if __name__ == "__main__":
+    sys.exit(main())

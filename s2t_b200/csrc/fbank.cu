@@ -128,58 +128,65 @@ fbank_kernel(const float* __restrict__ wave, long long wave_ld, const int* __res
   }
 }
 
-// Per-utterance CMVN.  block = (n_mels-rounded-up, slices); double accumulators keep the
-// E[x^2]-E[x]^2 cancellation (utterance_cmvn.py:35-43) well inside the parity tolerance.
-__global__ void cmvn_utt_kernel(const float* __restrict__ in, long long in_ld, long long in_bs,
-                                void* __restrict__ out, int out_bf16, long long out_ld,
-                                long long out_bs, const int* __restrict__ num_frames, int max_frames,
-                                int n_mels, int norm_means, int norm_vars) {
-  extern __shared__ double s_red[];  // [slices][2][n_mels]
+// Per-utterance CMVN.  The reference (utterance_cmvn.py:35-43) computes E[x^2]-E[x]^2 in fp32 numpy:
+// an axis-0 reduction of a C-contiguous (T, 80) array accumulates row after row, i.e. per bin a strictly
+// SEQUENTIAL fp32 sum over frames, and the catastrophic cancellation of that formula is part of the
+// oracle.  So: frames are staged chunk-wise in shared memory by the whole CTA (coalesced),
+// and one thread per bin replays the exact sequential fp32 accumulation (no FMA contraction).
+constexpr int kCmvnChunk = 64;
+
+__global__ void __launch_bounds__(256)
+cmvn_utt_kernel(const float* __restrict__ in, long long in_ld, long long in_bs,
+                void* __restrict__ out, int out_bf16, long long out_ld, long long out_bs,
+                const int* __restrict__ num_frames, int max_frames, int n_mels, int norm_means,
+                int norm_vars) {
+  extern __shared__ float s_chunk[];  // [kCmvnChunk][n_mels] + [2][n_mels]
+  float* s_mean = s_chunk + kCmvnChunk * n_mels;
+  float* s_std = s_mean + n_mels;
   const int b = blockIdx.x;
-  const int f = threadIdx.x, sl = threadIdx.y, nsl = blockDim.y;
   int T = num_frames[b];
   if (T > max_frames) T = max_frames;
   const float* src = in + b * in_bs;
-  double s = 0.0, ss = 0.0;
-  if (f < n_mels) {
-    for (int t = sl; t < T; t += nsl) {
-      const double v = static_cast<double>(src[static_cast<long long>(t) * in_ld + f]);
-      s += v;
-      ss += v * v;
+  float sum = 0.f, sq = 0.f;
+  for (int t0 = 0; t0 < T; t0 += kCmvnChunk) {
+    const int nt = min(kCmvnChunk, T - t0);
+    for (int i = threadIdx.x; i < nt * n_mels; i += blockDim.x) {
+      const int t = i / n_mels, f = i - t * n_mels;
+      s_chunk[i] = src[static_cast<long long>(t0 + t) * in_ld + f];
     }
-    s_red[(sl * 2 + 0) * n_mels + f] = s;
-    s_red[(sl * 2 + 1) * n_mels + f] = ss;
+    __syncthreads();
+    if (threadIdx.x < n_mels) {
+      for (int t = 0; t < nt; ++t) {
+        const float v = s_chunk[t * n_mels + threadIdx.x];
+        sum = __fadd_rn(sum, v);
+        sq = __fadd_rn(sq, __fmul_rn(v, v));
+      }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x < n_mels) {
+    const float Tn = static_cast<float>(T > 0 ? T : 1);
+    const float m = __fdiv_rn(sum, Tn);
+    float sd = 1.f;
+    if (norm_vars) {
+      const float var = __fsub_rn(__fdiv_rn(sq, Tn), __fmul_rn(m, m));
+      sd = __fsqrt_rn(fmaxf(var, 1e-10f));
+    }
+    s_mean[threadIdx.x] = norm_means ? m : 0.f;
+    s_std[threadIdx.x] = sd;
   }
   __syncthreads();
-  float mean = 0.f, inv_std = 1.f;
-  if (f < n_mels) {
-    double ts = 0.0, tss = 0.0;
-    for (int i = 0; i < nsl; ++i) {
-      ts += s_red[(i * 2 + 0) * n_mels + f];
-      tss += s_red[(i * 2 + 1) * n_mels + f];
+  const long long total = static_cast<long long>(max_frames) * n_mels;
+  for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+    const int t = static_cast<int>(i / n_mels), f = static_cast<int>(i - static_cast<long long>(t) * n_mels);
+    float v = 0.f;
+    if (t < T) {
+      v = __fsub_rn(src[static_cast<long long>(t) * in_ld + f], s_mean[f]);
+      if (norm_vars) v = __fdiv_rn(v, s_std[f]);
     }
-    const int Tn = T > 0 ? T : 1;
-    // mirror the reference's fp32 arithmetic on the (accurately summed) moments
-    const float m = static_cast<float>(ts / Tn);
-    const float sq = static_cast<float>(tss);
-    if (norm_means) mean = m;
-    if (norm_vars) {
-      float var = sq / static_cast<float>(Tn) - m * m;
-      inv_std = 1.0f / sqrtf(fmaxf(var, 1e-10f));
-    }
-  }
-  if (f < n_mels) {
-    for (int t = sl; t < max_frames; t += nsl) {
-      float v = 0.f;
-      if (t < T) {
-        v = src[static_cast<long long>(t) * in_ld + f];
-        v = (v - mean);
-        if (norm_vars) v = v * inv_std;
-      }
-      const long long o = b * out_bs + static_cast<long long>(t) * out_ld + f;
-      if (out_bf16) reinterpret_cast<__nv_bfloat16*>(out)[o] = __float2bfloat16(v);
-      else reinterpret_cast<float*>(out)[o] = v;
-    }
+    const long long o = b * out_bs + static_cast<long long>(t) * out_ld + f;
+    if (out_bf16) reinterpret_cast<__nv_bfloat16*>(out)[o] = __float2bfloat16(v);
+    else reinterpret_cast<float*>(out)[o] = v;
   }
 }
 
@@ -230,11 +237,8 @@ extern "C" int s2t_cmvn_utt(const float* feats, long long in_ld, long long in_bs
   S2T_REQUIRE(feats && out && num_frames, "s2t_cmvn_utt: null pointer");
   S2T_REQUIRE(n_mels > 0 && n_mels <= 128, "s2t_cmvn_utt: n_mels=%d out of range", n_mels);
   if (batch <= 0 || max_frames <= 0) return 0;
-  const int fx = ((n_mels + 31) / 32) * 32;
-  const int slices = 1024 / fx >= 8 ? 8 : 1024 / fx;
-  dim3 block(fx, slices);
-  const size_t smem = sizeof(double) * slices * 2 * n_mels;
-  cmvn_utt_kernel<<<batch, block, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
+  const size_t smem = sizeof(float) * (kCmvnChunk + 2) * n_mels;
+  cmvn_utt_kernel<<<batch, 256, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
       feats, in_ld, in_bs, out, out_bf16, out_ld, out_bs, num_frames, max_frames, n_mels, norm_means,
       norm_vars);
   S2T_LAUNCH_CHECK();

@@ -31,6 +31,7 @@ constexpr int kGemmThreads = 192;
 struct GemmKernelParams {
   int M, N, K;
   int nb1;
+  int a_zm1, a_zm2, b_zm1, b_zm2;  // 0 = operand is broadcast along that batch dim (stride 0)
   void* out;
   int out_fp32;
   int vec_ok;  // ldc/ldr/ldg multiples of 8 and 16B-aligned bases -> 16-byte accesses allowed
@@ -116,18 +117,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint8_t* a_dst = smem + s * Cfg::kStageBytes;
         uint8_t* b_dst = a_dst + Cfg::kABytes;
         if (A_MN == 0) {
-          tma_load_4d(a_dst, &tmA, &full_bar[s], kb * kBK, m0, z1, z2);
+          tma_load_4d(a_dst, &tmA, &full_bar[s], kb * kBK, m0, z1 * p.a_zm1, z2 * p.a_zm2);
         } else {
 #pragma unroll
           for (int c = 0; c < kBM / 64; ++c)
-            tma_load_4d(a_dst + c * (kBK * 128), &tmA, &full_bar[s], m0 + c * 64, kb * kBK, z1, z2);
+            tma_load_4d(a_dst + c * (kBK * 128), &tmA, &full_bar[s], m0 + c * 64, kb * kBK, z1 * p.a_zm1,
+                        z2 * p.a_zm2);
         }
         if (B_MN == 0) {
-          tma_load_4d(b_dst, &tmB, &full_bar[s], kb * kBK, n0, z1, z2);
+          tma_load_4d(b_dst, &tmB, &full_bar[s], kb * kBK, n0, z1 * p.b_zm1, z2 * p.b_zm2);
         } else {
 #pragma unroll
           for (int c = 0; c < BN / 64; ++c)
-            tma_load_4d(b_dst + c * (kBK * 128), &tmB, &full_bar[s], n0 + c * 64, kb * kBK, z1, z2);
+            tma_load_4d(b_dst + c * (kBK * 128), &tmB, &full_bar[s], n0 + c * 64, kb * kBK, z1 * p.b_zm1,
+                        z2 * p.b_zm2);
         }
       }
     }
@@ -337,6 +340,8 @@ static int make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, u
   S2T_REQUIRE((ld * 2) % 16 == 0, "GEMM operand leading stride must be a multiple of 8 elements (got %llu)",
               (unsigned long long)ld);
   // Unit batch dims still need a legal (16B-multiple, non-zero) stride.
+  if (bs1 == 0) nb1 = 1;  // broadcast batch dims collapse; the kernel zeroes the coordinate
+  if (bs2 == 0) nb2 = 1;
   uint64_t s1 = (nb1 > 1 ? bs1 : ld * outer) * 2, s2 = (nb2 > 1 ? bs2 : ld * outer) * 2;
   if (s1 == 0) s1 = 16;
   if (s2 == 0) s2 = 16;
@@ -443,6 +448,8 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
   GemmKernelParams kp;
   memset(&kp, 0, sizeof(kp));
   kp.M = g->M; kp.N = g->N; kp.K = g->K; kp.nb1 = nb1;
+  kp.a_zm1 = g->a_bs1 != 0; kp.a_zm2 = g->a_bs2 != 0;
+  kp.b_zm1 = g->b_bs1 != 0; kp.b_zm2 = g->b_bs2 != 0;
   kp.out = g->out; kp.out_fp32 = g->out_fp32;
   kp.ldc = g->ldc; kp.c_bs1 = g->c_bs1; kp.c_bs2 = g->c_bs2;
   kp.residual = reinterpret_cast<const __nv_bfloat16*>(g->residual);
