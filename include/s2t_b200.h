@@ -81,6 +81,9 @@ typedef struct s2t_gemm_args {
   const void* residual; /* bf16 [M][ldr] or NULL (ldr=0 -> ldc)                                    */
   long long ldr, r_bs1, r_bs2;
   int tile_n; /* 0 = auto, else 64/128/256                                                        */
+  /* optional DEVICE counter added to dropout_seed when the kernel runs, so a captured CUDA graph    */
+  /* draws a fresh mask on every replay (the host bumps the counter between replays); NULL = none   */
+  const unsigned long long* dropout_seed_offset;
 } s2t_gemm_args;
 
 int s2t_gemm_bf16(const s2t_gemm_args* args, void* stream);
@@ -140,8 +143,10 @@ int s2t_layernorm_bwd(const void* dy, const void* x, const void* gamma, const fl
  * x bf16 [rows][2C] -> y[rows][ldy] = x[:, :C] * sigmoid(x[:, C:]).  With lengths != NULL the rows are
  * utterance-major (row = b*T + t) and rows with t >= lengths[b] produce 0 (the padding mask the
  * encoder applies after subsampling, s2t_transformer.py:1765); the backward zeroes their gradient. */
-int s2t_glu_fwd(const void* x, void* y, long long ldy, int rows, int C, const int* lengths, int T,
-                void* stream);
+/* y_bs != 0: row r = b*T + t is written at y + b*y_bs + t*ldy (output inside a per-utterance padded
+ * buffer, e.g. the zero-framed input of the next Conv1d); y_bs == 0: dense rows y + r*ldy.          */
+int s2t_glu_fwd(const void* x, void* y, long long ldy, long long y_bs, int rows, int C,
+                const int* lengths, int T, void* stream);
 int s2t_glu_bwd(const void* x, const void* dy, long long lddy, void* dx, int rows, int C,
                 const int* lengths, int T, void* stream);
 /* column sums: out[c] = sum_r x[r][c]  (bias gradients).  x bf16 [rows][ld]; out bf16 [C].        */
@@ -158,14 +163,33 @@ int s2t_col2im1d(const void* dcol, void* dx, int batch, int t_in, int t_out, int
  * lengths int32 [B]; pos_table fp32 [n_pos][C] (NULL = no positional term).                       */
 int s2t_embed_fwd(const void* x, const int* lengths, const float* pos_table, int n_pos, void* y,
                   int batch, int T, int C, float scale, float dropout_p,
-                  unsigned long long seed, unsigned int stream_id, void* stream);
+                  unsigned long long seed, unsigned int stream_id,
+                  const unsigned long long* seed_offset, void* stream);
 int s2t_embed_bwd(const void* dy, void* dx, int batch, int T, int C, float scale,
-                  float dropout_p, unsigned long long seed, unsigned int stream_id, void* stream);
+                  float dropout_p, unsigned long long seed, unsigned int stream_id,
+                  const unsigned long long* seed_offset, void* stream);
 /* zero rows t >= lengths[b] of x bf16 [B][T][ld] in place (padding masks, s2t_transformer.py:1765,1828) */
 int s2t_mask_rows(void* x, const int* lengths, int batch, int T, int C, long long ld, void* stream);
 /* weight re-layout for the implicit-GEMM Conv1d: w bf16 [Cout][Cin][k] -> [Cout][k][Cin] (and back, summing nothing) */
 int s2t_permute_conv_weight(const void* w, void* out, int cout, int cin, int k, int inverse,
                             void* stream);
+/* standalone regenerable dropout: y = out_scale * mask(seed, stream_id, i/8) * x / (1-p) (p = 0: plain
+ * scaling), x,y bf16 [n], n % 8 == 0.
+ * Same Philox numbering as the GEMM epilogue on a dense [rows][N%8==0] tensor, so this re-applies an
+ * epilogue-drawn mask in the backward pass; also CTC.forward's dropout (modules/speech_to_text/ctc.py:59) */
+int s2t_dropout(const void* x, void* y, long long n, float p, float out_scale,
+                unsigned long long seed, unsigned int stream_id,
+                const unsigned long long* seed_offset, void* stream);
+/* explicit im2col of a zero-framed channels-last Conv1d input (for the weight gradient):
+ * xcol[b*t_out + t][j*C + c] = xp[b*x_bs + (t*stride + j)*C + c]                                   */
+int s2t_im2col1d(const void* xp, long long x_bs, void* xcol, int batch, int t_out, int C, int ksize,
+                 int stride, void* stream);
+/* *counter += inc on the device (dropout seed counter of a captured step)                         */
+int s2t_counter_add(unsigned long long* counter, unsigned long long inc, void* stream);
+/* y += x, bf16 [n], n % 8 == 0                                                                    */
+int s2t_add_bf16(const void* x, void* y, long long n, void* stream);
+/* out[0] = scale * sum_i x[i]  (per-utterance NLL -> batch loss, criterions/ctc.py:473)            */
+int s2t_f32_sum(const float* x, int n, float scale, float* out, void* stream);
 /* plain bf16 <-> fp32 casts and fills used by the host glue */
 int s2t_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
 int s2t_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream);
@@ -182,13 +206,14 @@ int s2t_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream);
 int s2t_attn_softmax_fwd(const void* scores, long long ld, const void* bias, long long ld_bias,
                          int bias_mode, void* probs, void* probs_drop, const int* klen, int nbh,
                          int heads, int Tq, int Tk, float scale, float clamp, float dropout_p,
-                         unsigned long long seed, unsigned int stream_id, void* stream);
+                         unsigned long long seed, unsigned int stream_id,
+                         const unsigned long long* seed_offset, void* stream);
 /* dscores = scale * probs * (dp - sum_k dp*probs), dp = dropout_mask * dprobs_drop / (1-p);
  * dbias (optional, bias_mode 2 layout [nbh][T][ld_bias]) receives the same values un-shifted.     */
 int s2t_attn_softmax_bwd(const void* probs, const void* dprobs_drop, void* dscores, void* dbias,
                          long long ld_bias, const int* klen, int nbh, int heads, int Tq, int Tk,
                          long long ld, float scale, float dropout_p, unsigned long long seed,
-                         unsigned int stream_id, void* stream);
+                         unsigned int stream_id, const unsigned long long* seed_offset, void* stream);
 
 /* --------------------------------------------------------------------------------------------- */
 /* K7/K8/K9: CTC head softmax, CTC loss forward/backward, greedy decode.                          */

@@ -24,8 +24,8 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf
 // GLU: y = a * sigmoid(g), x = [a | g] along channels.  Optional padding mask by utterance length.
 // ---------------------------------------------------------------------------------------------
 __global__ void glu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
-                               long long ldy, long long rows, int C, const int* __restrict__ lengths,
-                               int T) {
+                               long long ldy, long long y_bs, long long rows, int C,
+                               const int* __restrict__ lengths, int T) {
   const int cv = C >> 3;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= rows * cv) return;
@@ -44,7 +44,8 @@ __global__ void glu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat1
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = 0.f;
   }
-  *reinterpret_cast<uint4*>(y + r * ldy + c) = pack8e(o);
+  const long long yoff = y_bs != 0 ? (r / T) * y_bs + (r % T) * ldy : r * ldy;
+  *reinterpret_cast<uint4*>(y + yoff + c) = pack8e(o);
 }
 
 __global__ void glu_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
@@ -162,7 +163,8 @@ __global__ void embed_fwd_kernel(const __nv_bfloat16* __restrict__ x, const int*
                                  const float* __restrict__ pos_table, int n_pos,
                                  __nv_bfloat16* __restrict__ y, int batch, int T, int C, float scale,
                                  uint32_t thresh16, float inv_keep, unsigned long long seed,
-                                 uint32_t stream_id) {
+                                 uint32_t stream_id, const unsigned long long* __restrict__ seed_off) {
+  if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const int cv = C >> 3;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<long long>(batch) * T * cv) return;
@@ -191,7 +193,9 @@ __global__ void embed_fwd_kernel(const __nv_bfloat16* __restrict__ x, const int*
 
 __global__ void embed_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx,
                                  long long n_vec, float scale, uint32_t thresh16, float inv_keep,
-                                 unsigned long long seed, uint32_t stream_id) {
+                                 unsigned long long seed, uint32_t stream_id,
+                                 const unsigned long long* __restrict__ seed_off) {
+  if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n_vec) return;
   float v[8];
@@ -271,14 +275,15 @@ using namespace s2t;
 #define BF(p) reinterpret_cast<__nv_bfloat16*>(p)
 #define CBF(p) reinterpret_cast<const __nv_bfloat16*>(p)
 
-extern "C" int s2t_glu_fwd(const void* x, void* y, long long ldy, int rows, int C,
+extern "C" int s2t_glu_fwd(const void* x, void* y, long long ldy, long long y_bs, int rows, int C,
                            const int* lengths, int T, void* stream) {
   S2T_REQUIRE(x && y, "s2t_glu_fwd: null pointer");
-  S2T_REQUIRE(C % 8 == 0 && ldy % 8 == 0, "s2t_glu_fwd: C and ldy must be multiples of 8");
+  S2T_REQUIRE(C % 8 == 0 && ldy % 8 == 0 && y_bs % 8 == 0, "s2t_glu_fwd: C, ldy, y_bs must be multiples of 8");
+  S2T_REQUIRE(y_bs == 0 || T > 0, "s2t_glu_fwd: y_bs needs T");
   if (rows <= 0) return 0;
   const long long n = static_cast<long long>(rows) * (C / 8);
-  glu_fwd_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), ldy, rows, C, lengths,
-                                                            T > 0 ? T : 1);
+  glu_fwd_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), ldy, y_bs, rows, C,
+                                                            lengths, T > 0 ? T : 1);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -331,7 +336,8 @@ static inline uint32_t thresh16(float p) { return static_cast<uint32_t>(p * 6553
 
 extern "C" int s2t_embed_fwd(const void* x, const int* lengths, const float* pos_table, int n_pos,
                              void* y, int batch, int T, int C, float scale, float dropout_p,
-                             unsigned long long seed, unsigned int stream_id, void* stream) {
+                             unsigned long long seed, unsigned int stream_id,
+                             const unsigned long long* seed_offset, void* stream) {
   S2T_REQUIRE(x && y && lengths, "s2t_embed_fwd: null pointer");
   S2T_REQUIRE(C % 8 == 0, "s2t_embed_fwd: C must be a multiple of 8");
   S2T_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "s2t_embed_fwd: bad dropout_p");
@@ -339,21 +345,21 @@ extern "C" int s2t_embed_fwd(const void* x, const int* lengths, const float* pos
   if (n <= 0) return 0;
   embed_fwd_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(
       CBF(x), lengths, pos_table, n_pos, BF(y), batch, T, C, scale,
-      dropout_p > 0.f ? thresh16(dropout_p) : 0u, 1.f / (1.f - dropout_p), seed, stream_id);
+      dropout_p > 0.f ? thresh16(dropout_p) : 0u, 1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int s2t_embed_bwd(const void* dy, void* dx, int batch, int T, int C, float scale,
                              float dropout_p, unsigned long long seed, unsigned int stream_id,
-                             void* stream) {
+                             const unsigned long long* seed_offset, void* stream) {
   S2T_REQUIRE(dy && dx, "s2t_embed_bwd: null pointer");
   S2T_REQUIRE(C % 8 == 0, "s2t_embed_bwd: C must be a multiple of 8");
   const long long n = static_cast<long long>(batch) * T * (C / 8);
   if (n <= 0) return 0;
   embed_bwd_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(
       CBF(dy), BF(dx), n, scale, dropout_p > 0.f ? thresh16(dropout_p) : 0u, 1.f / (1.f - dropout_p),
-      seed, stream_id);
+      seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }

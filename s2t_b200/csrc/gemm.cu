@@ -47,6 +47,7 @@ struct GemmKernelParams {
   uint32_t drop_thresh16;
   float drop_inv_keep;
   unsigned long long drop_seed;
+  const unsigned long long* drop_seed_off;  // optional device counter added to the seed (CUDA-graph replay)
   uint32_t drop_stream;
 };
 
@@ -171,6 +172,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // dropout counter: element (z, row, col) lives in Philox group (z*M+row)*ceil(N/8) + col/8, bit col%8
     const unsigned long long drop_row =
         (static_cast<unsigned long long>(z) * p.M + row) * static_cast<unsigned long long>((p.N + 7) >> 3);
+    const unsigned long long drop_seed =
+        p.drop_seed + ((p.drop_thresh16 != 0 && p.drop_seed_off != nullptr) ? *p.drop_seed_off : 0ull);
 
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
@@ -233,7 +236,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         if (p.drop_thresh16 != 0) {
           const uint32_t keep =
-              dropout_keep8(p.drop_seed, p.drop_stream, drop_row + (col >> 3), p.drop_thresh16);
+              dropout_keep8(drop_seed, p.drop_stream, drop_row + (col >> 3), p.drop_thresh16);
 #pragma unroll
           for (int j = 0; j < 8; ++j) v[j] = ((keep >> j) & 1u) ? v[j] * p.drop_inv_keep : 0.f;
         }
@@ -464,6 +467,7 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
     kp.drop_thresh16 = static_cast<uint32_t>(g->dropout_p * 65536.f + 0.5f);
     kp.drop_inv_keep = 1.f / (1.f - g->dropout_p);
     kp.drop_seed = g->dropout_seed;
+    kp.drop_seed_off = g->dropout_seed_offset;
     kp.drop_stream = g->dropout_stream;
   }
   const int esz = g->out_fp32 ? 4 : 2;

@@ -38,7 +38,9 @@ attn_softmax_fwd_kernel(const __nv_bfloat16* __restrict__ scores, long long ld,
                         __nv_bfloat16* __restrict__ probs, __nv_bfloat16* __restrict__ probs_drop,
                         const int* __restrict__ klen, long long nrows, int heads, int Tq, int Tk,
                         float scale, float clamp, uint32_t thresh16, float inv_keep,
-                        unsigned long long seed, uint32_t stream_id) {
+                        unsigned long long seed, uint32_t stream_id,
+                        const unsigned long long* __restrict__ seed_off) {
+  if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long row = static_cast<long long>(blockIdx.x) * kSmWarps + warp;
   if (row >= nrows) return;
@@ -96,7 +98,9 @@ attn_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ probs, const __nv_bflo
                         __nv_bfloat16* __restrict__ dscores, __nv_bfloat16* __restrict__ dbias,
                         long long ld_bias, const int* __restrict__ klen, long long nrows, int heads,
                         int Tq, int Tk, long long ld, float scale, uint32_t thresh16, float inv_keep,
-                        unsigned long long seed, uint32_t stream_id) {
+                        unsigned long long seed, uint32_t stream_id,
+                        const unsigned long long* __restrict__ seed_off) {
+  if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long row = static_cast<long long>(blockIdx.x) * kSmWarps + warp;
   if (row >= nrows) return;
@@ -180,7 +184,8 @@ extern "C" int s2t_attn_softmax_fwd(const void* scores, long long ld, const void
                                     long long ld_bias, int bias_mode, void* probs, void* probs_drop,
                                     const int* klen, int nbh, int heads, int Tq, int Tk, float scale,
                                     float clamp, float dropout_p, unsigned long long seed,
-                                    unsigned int stream_id, void* stream) {
+                                    unsigned int stream_id, const unsigned long long* seed_offset,
+                                    void* stream) {
   S2T_REQUIRE(scores && probs, "s2t_attn_softmax_fwd: null pointer");
   S2T_REQUIRE(ld % 8 == 0 && ld >= ((Tk + 7) & ~7), "s2t_attn_softmax_fwd: ld must be a multiple of 8 and >= round8(Tk)");
   S2T_REQUIRE(heads > 0 && nbh % heads == 0, "s2t_attn_softmax_fwd: nbh must be a multiple of heads");
@@ -194,7 +199,7 @@ extern "C" int s2t_attn_softmax_fwd(const void* scores, long long ld, const void
       ld_bias, bias_mode, reinterpret_cast<__nv_bfloat16*>(probs),
       reinterpret_cast<__nv_bfloat16*>(probs_drop), klen, nrows, heads, Tq, Tk, scale, clamp,
       dropout_p > 0.f ? static_cast<uint32_t>(dropout_p * 65536.f + 0.5f) : 0u,
-      1.f / (1.f - dropout_p), seed, stream_id);
+      1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -203,7 +208,7 @@ extern "C" int s2t_attn_softmax_bwd(const void* probs, const void* dprobs_drop, 
                                     void* dbias, long long ld_bias, const int* klen, int nbh,
                                     int heads, int Tq, int Tk, long long ld, float scale,
                                     float dropout_p, unsigned long long seed, unsigned int stream_id,
-                                    void* stream) {
+                                    const unsigned long long* seed_offset, void* stream) {
   S2T_REQUIRE(probs && dprobs_drop && dscores, "s2t_attn_softmax_bwd: null pointer");
   S2T_REQUIRE(ld % 8 == 0 && ld >= ((Tk + 7) & ~7), "s2t_attn_softmax_bwd: ld must be a multiple of 8 and >= round8(Tk)");
   S2T_REQUIRE(heads > 0 && nbh % heads == 0, "s2t_attn_softmax_bwd: nbh must be a multiple of heads");
@@ -216,7 +221,7 @@ extern "C" int s2t_attn_softmax_bwd(const void* probs, const void* dprobs_drop, 
       reinterpret_cast<__nv_bfloat16*>(dscores), reinterpret_cast<__nv_bfloat16*>(dbias), ld_bias, klen,
       nrows, heads, Tq, Tk, ld, scale,
       dropout_p > 0.f ? static_cast<uint32_t>(dropout_p * 65536.f + 0.5f) : 0u,
-      1.f / (1.f - dropout_p), seed, stream_id);
+      1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }

@@ -30,6 +30,7 @@ class GemmArgs(C.Structure):
         ("out_scale", _f),
         ("residual", _vp), ("ldr", _ll), ("r_bs1", _ll), ("r_bs2", _ll),
         ("tile_n", _i),
+        ("dropout_seed_offset", _vp),
     ]
 
 
@@ -46,19 +47,24 @@ SIGNATURES = {
     "s2t_layernorm_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
     "s2t_layernorm_bwd_partials": (_i, [_i, _i]),
     "s2t_layernorm_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
-    "s2t_glu_fwd": (_i, [_vp, _vp, _ll, _i, _i, _vp, _i, _vp]),
+    "s2t_glu_fwd": (_i, [_vp, _vp, _ll, _ll, _i, _i, _vp, _i, _vp]),
     "s2t_glu_bwd": (_i, [_vp, _vp, _ll, _vp, _i, _i, _vp, _i, _vp]),
     "s2t_colsum": (_i, [_vp, _ll, _i, _i, _vp, _i, _vp, _ll, _vp]),
     "s2t_colsum_workspace_floats": (_ll, [_i, _i]),
     "s2t_col2im1d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
-    "s2t_embed_fwd": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _f, _f, _ull, _u, _vp]),
-    "s2t_embed_bwd": (_i, [_vp, _vp, _i, _i, _i, _f, _f, _ull, _u, _vp]),
+    "s2t_embed_fwd": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_embed_bwd": (_i, [_vp, _vp, _i, _i, _i, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_dropout": (_i, [_vp, _vp, _ll, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_im2col1d": (_i, [_vp, _ll, _vp, _i, _i, _i, _i, _i, _vp]),
+    "s2t_counter_add": (_i, [_vp, _ull, _vp]),
+    "s2t_add_bf16": (_i, [_vp, _vp, _ll, _vp]),
+    "s2t_f32_sum": (_i, [_vp, _i, _f, _vp, _vp]),
     "s2t_mask_rows": (_i, [_vp, _vp, _i, _i, _i, _ll, _vp]),
     "s2t_permute_conv_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "s2t_cast_f32_to_bf16": (_i, [_vp, _vp, _ll, _vp]),
     "s2t_cast_bf16_to_f32": (_i, [_vp, _vp, _ll, _vp]),
-    "s2t_attn_softmax_fwd": (_i, [_vp, _ll, _vp, _ll, _i, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _f, _ull, _u, _vp]),
-    "s2t_attn_softmax_bwd": (_i, [_vp, _vp, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _ll, _f, _f, _ull, _u, _vp]),
+    "s2t_attn_softmax_fwd": (_i, [_vp, _ll, _vp, _ll, _i, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_attn_softmax_bwd": (_i, [_vp, _vp, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _ll, _f, _f, _ull, _u, _vp, _vp]),
     "s2t_row_lse": (_i, [_vp, _i, _ll, _i, _i, _vp, _vp]),
     "s2t_ctc_workspace_bytes": (_ll, [_i, _i, _i]),
     "s2t_ctc_loss": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _ll, _vp]),

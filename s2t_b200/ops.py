@@ -47,6 +47,14 @@ def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+def _drop(d):
+    """dropout spec (p, seed, stream_id[, seed_offset u64 device tensor]) -> 4 C arguments."""
+    if d is None or d[0] <= 0.0:
+        return 0.0, 0, 0, None
+    off = d[3] if len(d) > 3 else None
+    return float(d[0]), int(d[1]), int(d[2]), _p(off)
+
+
 # --------------------------------------------------------------------------------------------------
 # GEMM
 # --------------------------------------------------------------------------------------------------
@@ -86,8 +94,7 @@ def gemm_raw(
     g.act = act
     g.gate, g.gate_mode, g.ldg = _p(gate), gate_mode, ldg
     g.g_bs1, g.g_bs2 = g_bs
-    if dropout is not None and dropout[0] > 0.0:
-        g.dropout_p, g.dropout_seed, g.dropout_stream = dropout
+    g.dropout_p, g.dropout_seed, g.dropout_stream, g.dropout_seed_offset = _drop(dropout)
     g.out_scale = out_scale
     g.residual, g.ldr = _p(residual), ldr
     g.r_bs1, g.r_bs2 = r_bs
@@ -205,11 +212,15 @@ def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, stats:
 # elementwise
 # --------------------------------------------------------------------------------------------------
 def glu_fwd(x: torch.Tensor, out: Optional[torch.Tensor] = None, lengths: Optional[torch.Tensor] = None,
-            T: int = 0) -> torch.Tensor:
+            T: int = 0, *, ldy: Optional[int] = None, y_bs: int = 0, y_off: int = 0) -> torch.Tensor:
+    """x [rows, 2C] -> out = x[:, :C] * sigmoid(x[:, C:]).  With ``y_bs`` the row b*T+t lands at element
+    ``y_off + b*y_bs + t*ldy`` of ``out`` (a per-utterance framed buffer)."""
     rows, C2 = x.shape
     if out is None:
         out = torch.empty((rows, C2 // 2), device=x.device, dtype=BF16)
-    _call("s2t_glu_fwd", _p(x), _p(out), out.stride(0), rows, C2 // 2, _p(lengths), T, _stream())
+    if ldy is None:
+        ldy = out.stride(0)
+    _call("s2t_glu_fwd", _p(x), _p(out) + 2 * y_off, ldy, y_bs, rows, C2 // 2, _p(lengths), T, _stream())
     return out
 
 
@@ -248,7 +259,7 @@ def embed_fwd(x: torch.Tensor, lengths: torch.Tensor, pos_table: Optional[torch.
         out = torch.empty_like(x)
     n_pos = pos_table.shape[0] if pos_table is not None else 0
     _call("s2t_embed_fwd", _p(x), _p(lengths), _p(pos_table), n_pos, _p(out), B, T, Cd, scale,
-          dropout[0], dropout[1], dropout[2], _stream())
+          *_drop(dropout), _stream())
     return out
 
 
@@ -257,7 +268,7 @@ def embed_bwd(dy: torch.Tensor, scale: float, dropout: Tuple[float, int, int] = 
     B, T, Cd = dy.shape
     if out is None:
         out = torch.empty_like(dy)
-    _call("s2t_embed_bwd", _p(dy), _p(out), B, T, Cd, scale, dropout[0], dropout[1], dropout[2], _stream())
+    _call("s2t_embed_bwd", _p(dy), _p(out), B, T, Cd, scale, *_drop(dropout), _stream())
     return out
 
 
@@ -295,6 +306,38 @@ def cast_bf16_to_f32(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> tor
     return out
 
 
+def dropout(x: torch.Tensor, spec, out: Optional[torch.Tensor] = None, scale: float = 1.0) -> torch.Tensor:
+    """y = scale * dropout(x): standalone regenerable dropout (same Philox numbering as the GEMM epilogue
+    on a dense tensor); spec with p = 0 gives a plain scaled copy."""
+    if out is None:
+        out = torch.empty_like(x)
+    p, seed, sid, off = _drop(spec)
+    _call("s2t_dropout", _p(x), _p(out), x.numel(), p, scale, seed, sid, off, _stream())
+    return out
+
+
+def im2col1d(xp: torch.Tensor, x_bs: int, batch: int, t_out: int, Cd: int, ksize: int, stride: int,
+             out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if out is None:
+        out = torch.empty((batch * t_out, ksize * Cd), device=xp.device, dtype=BF16)
+    _call("s2t_im2col1d", _p(xp), x_bs, _p(out), batch, t_out, Cd, ksize, stride, _stream())
+    return out
+
+
+def counter_add(counter: torch.Tensor, inc: int = 1) -> None:
+    _call("s2t_counter_add", _p(counter), inc, _stream())
+
+
+def add_(y: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    _call("s2t_add_bf16", _p(x), _p(y), y.numel(), _stream())
+    return y
+
+
+def f32_sum(x: torch.Tensor, out: torch.Tensor, scale: float = 1.0) -> torch.Tensor:
+    _call("s2t_f32_sum", _p(x), x.numel(), scale, _p(out), _stream())
+    return out
+
+
 # --------------------------------------------------------------------------------------------------
 # attention softmax
 # --------------------------------------------------------------------------------------------------
@@ -308,7 +351,7 @@ def attn_softmax_fwd(scores: torch.Tensor, klen: Optional[torch.Tensor], heads: 
         probs = torch.empty_like(scores)
     ld_bias = bias.stride(1) if bias is not None else 0
     _call("s2t_attn_softmax_fwd", _p(scores), ld, _p(bias), ld_bias, bias_mode, _p(probs), _p(probs_drop),
-          _p(klen), nbh, heads, Tq, Tk, scale, clamp, dropout[0], dropout[1], dropout[2], _stream())
+          _p(klen), nbh, heads, Tq, Tk, scale, clamp, *_drop(dropout), _stream())
     return probs, probs_drop
 
 
@@ -321,7 +364,7 @@ def attn_softmax_bwd(probs: torch.Tensor, dprobs_drop: torch.Tensor, klen: Optio
         out = torch.empty_like(probs)
     ld_bias = dbias.stride(1) if dbias is not None else 0
     _call("s2t_attn_softmax_bwd", _p(probs), _p(dprobs_drop), _p(out), _p(dbias), ld_bias, _p(klen), nbh,
-          heads, Tq, Tk, ld, scale, dropout[0], dropout[1], dropout[2], _stream())
+          heads, Tq, Tk, ld, scale, *_drop(dropout), _stream())
     return out
 
 
@@ -344,7 +387,8 @@ def ctc_workspace_bytes(B: int, T: int, max_target_len: int) -> int:
 def ctc_loss(logits: torch.Tensor, targets: torch.Tensor, input_lengths: torch.Tensor,
              target_lengths: torch.Tensor, V: int, blank: int = 0, *, need_grad: bool = True,
              grad_scale: float = 1.0, lse: Optional[torch.Tensor] = None,
-             dlogits: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None):
+             dlogits: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None,
+             nll: Optional[torch.Tensor] = None):
     """logits [B, T, ldv] utterance-major; targets int32 [B, Smax].  Returns (nll fp32 [B], dlogits|None)."""
     B, T, ldv = logits.shape
     smax = targets.shape[1]
@@ -354,7 +398,8 @@ def ctc_loss(logits: torch.Tensor, targets: torch.Tensor, input_lengths: torch.T
     need = ctc_workspace_bytes(B, T, smax)
     if workspace is None or workspace.numel() * workspace.element_size() < need:
         workspace = torch.empty(((need + 3) // 4,), device=logits.device, dtype=torch.float32)
-    nll = torch.empty((B,), device=logits.device, dtype=torch.float32)
+    if nll is None:
+        nll = torch.empty((B,), device=logits.device, dtype=torch.float32)
     if need_grad and dlogits is None:
         dlogits = torch.empty_like(logits)
     _call("s2t_ctc_loss", _p(logits), int(logits.dtype == BF16), ldv, _p(lse), _p(targets),
