@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""bench.py — encoder+CTC fwd/bwd audio-seconds/second of the S2T speech-encoder hot path on B200.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (N>1: launched by torchrun, one rank per GPU)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path on this box's host cores
+
+Workload (BASELINE.json configs[1], SURVEY.md §8 "C2"): s2t_transformer_s (12 layers, d=256, ffn=2048, 4 heads,
+Conv1d x2 subsampler) + CTC head V=10000 + CTC loss, end to end from raw 16 kHz synthetic waveform (Kaldi fbank
++ utterance CMVN on the GPU), batch 8 x 10 s utterances per GPU, bf16 storage / fp32 accumulate, recipe dropout
+0.1, forward + backward (optimizer step excluded as in the metric; gradient all-reduce included for N >= 2).
+One "step" = one pass of the hot path over one batch.  Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "encoder+CTC fwd/bwd audio-sec/sec"
+UNIT = "audio-s/s"
+SAMPLE_RATE = 16000
+VOCAB = 10000
+TARGET_LEN = 60           # ~6 tokens / s
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=8, help="utterances per GPU per step")
+    ap.add_argument("--seconds", type=float, default=10.0, help="utterance duration")
+    ap.add_argument("--no-graph", action="store_true", help="eager launches instead of CUDA-graph replay")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-kernels", action="store_true", help="also print a per-kernel time table (stderr)")
+    return ap.parse_args()
+
+
+def workload_name(a) -> str:
+    return (f"C2: s2t_transformer_s enc+CTC(V={VOCAB}) from raw 16 kHz waveform, {a.batch} x {a.seconds:g} s per GPU, "
+            f"fbank+CMVN on device, dropout 0.1, fwd+bwd")
+
+
+def synth_batch(batch: int, seconds: float, seed: int):
+    """Synthetic int16-scale waveform: randn * 3000 + a 440 Hz tone; random targets."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    n = int(seconds * SAMPLE_RATE)
+    t = torch.arange(n, dtype=torch.float32) / SAMPLE_RATE
+    wave = torch.randn((batch, n), generator=g) * 3000.0 + 1500.0 * torch.sin(2 * 3.141592653589793 * 440.0 * t)
+    num = torch.full((batch,), n, dtype=torch.int32)
+    targets = torch.randint(4, VOCAB, (batch, TARGET_LEN), generator=g).to(torch.int32)
+    tlen = torch.full((batch,), TARGET_LEN, dtype=torch.int32)
+    return wave, num, targets, tlen
+
+
+# --------------------------------------------------------------------------------------------------
+# clocks sampler (B200_PROFILING.md "clocks DURING the timed region")
+# --------------------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the reference's own PyTorch path on the host cores
+# --------------------------------------------------------------------------------------------------
+def cpu_reference_run(batch: int, seconds: float, steps: int, warmup: int):
+    """The reference fairseq CPU path for this workload: torchaudio Kaldi fbank + UtteranceCMVN per
+    utterance, then S2TTransformerEncoder + fp32 log_softmax + nn.CTCLoss forward/backward in fp32 with recipe
+    dropout, on all host cores.  /root/reference cannot travel to the GPU box, so the module code is oracle/'s
+    op-for-op restatement (pinned bit-level against the reference by oracle/make_golden.py): kind = "port"."""
+    import numpy as np
+    import torch
+    from oracle import encoder as OE
+    from oracle import fbank as OF
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    try:
+        import torchaudio.compliance.kaldi as K
+        fb = lambda w: K.fbank(w.unsqueeze(0), num_mel_bins=80, sample_frequency=SAMPLE_RATE).numpy()
+    except Exception:  # torchaudio missing: the numpy restatement of the same algorithm
+        fb = lambda w: OF.fbank(w.numpy())
+    torch.manual_seed(0)
+    enc = OE.S2TTransformerEncoder(OE.OracleConfig(dropout=0.1, vocab=VOCAB))
+    enc.train()
+    wave, num, targets, tlen = synth_batch(batch, seconds, 0)
+    tokens = torch.cat([targets.long(), torch.full((batch, 1), 2, dtype=torch.long)], dim=1)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        feats = [torch.from_numpy(OF.utterance_cmvn(fb(wave[b, : int(num[b])]))) for b in range(batch)]
+        lens = torch.tensor([f.shape[0] for f in feats])
+        src = torch.zeros((batch, int(lens.max()), 80))
+        for b, f in enumerate(feats):
+            src[b, : f.shape[0]] = f
+        enc.zero_grad(set_to_none=True)
+        out = enc(src, lens)
+        loss = OE.ctc_criterion_loss(out["ctc_logit"][0], out["encoder_padding_mask"][0], tokens)
+        loss.backward()
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+            if sum(times) > 25.0:                      # bounded sample: ~10-30 s of CPU work
+                break
+    audio_s = float(num.sum()) / SAMPLE_RATE
+    total = sum(times)
+    return {"value": audio_s * len(times) / total, "ms_per_step": 1e3 * total / len(times), "cores": cores,
+            "sample": f"{len(times)} step(s) of the same {batch} x {seconds:g} s batch after {warmup} warm-up, fp32, dropout 0.1, "
+                      f"torch.set_num_threads({cores})", "loss": float(loss.item())}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warmup = max(1, min(a.steps, 5)), max(1, min(a.warmup, 1))
+    r = cpu_reference_run(a.batch, a.seconds, steps, warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "device": "host CPU"},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------------
+def gemm_roofline(torch, eng, P, peaks):
+    """Roofline of the dominant kernel, gemm_bf16_kernel (tcgen05/TMEM GEMM family — it carries every linear layer,
+    attention contraction and the vocabulary projection).  Timed live: every GEMM launch of one eager training step is
+    bracketed by CUDA events on the launching stream; achieved = algorithmic FLOPs (2*M*N*K*batches per launch, summed)
+    / summed launch durations."""
+    from s2t_b200 import ops
+    recs = []
+    orig = ops.gemm_raw
+
+    def timed(**kw):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        orig(**kw)
+        e1.record()
+        nb = kw.get("batch", (1, 1))
+        recs.append((e0, e1, 2.0 * kw["M"] * kw["N"] * kw["K"] * nb[0] * nb[1]))
+
+    best = None
+    for _ in range(3):
+        recs.clear()
+        ops.gemm_raw = timed
+        try:
+            e_all0, e_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e_all0.record()
+            eng.train_step(P)
+            e_all1.record()
+        finally:
+            ops.gemm_raw = orig
+        torch.cuda.synchronize()
+        ms = sum(a.elapsed_time(b) for a, b, _ in recs)
+        fl = sum(f for _, _, f in recs)
+        if best is None or ms < best[0]:
+            best = (ms, fl, len(recs), e_all0.elapsed_time(e_all1))
+    ms, fl, n, step_ms = best
+    peak = float(peaks.get("bf16_tflops_sustained") or 1400.0)
+    ach = fl / (ms * 1e-3) / 1e12
+    return {"bound": "tensor", "kernel": "gemm_bf16_kernel (all GEMM launches of one step)", "achieved": ach, "peak": peak,
+            "unit": "TFLOP/s", "frac": ach / peak, "traffic": None, "launches_per_step": n,
+            "avg_launch_us": 1e3 * ms / n, "gemm_ms_per_step": ms, "eager_step_ms": step_ms, "flop_per_step": fl,
+            "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained"}
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from s2t_b200 import ops
+    from s2t_b200.engine import EncoderConfig, S2TEncoderEngine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl b200) needs a CUDA device: s2t_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    peaks = {}
+    pk = ROOT / "MEASURED_PEAKS.json"
+    if pk.exists():
+        peaks = json.loads(pk.read_text())
+
+    cfg = EncoderConfig(vocab=VOCAB, dropout=0.1)              # s2t_transformer_s defaults (C1/C2)
+    eng = S2TEncoderEngine(cfg)
+    if world > 1:
+        dist.broadcast(eng.store.flat, src=0)                  # same weights on every rank (trainer.py:431)
+        eng.enable_data_parallel(n_buckets=4)
+    n_samp = int(a.seconds * SAMPLE_RATE)
+    from s2t_b200 import frontend
+    T = frontend.num_frames(n_samp)
+    P = eng.plan(a.batch, T, TARGET_LEN, wave_len=n_samp)
+    # a few different pinned host batches, rotated through the e2e loop
+    host = []
+    for i in range(4):
+        w, n, tg, tl = synth_batch(a.batch, a.seconds, 1000 * rank + i)
+        host.append(tuple(t.pin_memory() for t in (w, n, tg, tl)))
+    h2d = sum(t.numel() * t.element_size() for t in host[0])
+    loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+    audio_s_step = a.batch * n_samp / SAMPLE_RATE               # per rank
+
+    def load(i):
+        w, n, tg, tl = host[i % len(host)]
+        eng.set_inputs(P, wave=w, num_samples=n, targets=tg, target_lengths=tl)
+
+    load(0)
+    l0 = ops.launch_count
+    eng.train_step(P)                                           # eager warm-up (also counts launches per step)
+    torch.cuda.synchronize()
+    launches_per_step = ops.launch_count - l0
+    if not a.no_graph:
+        eng.capture(P)
+    kind = "train"
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident throughput ("value"): inputs already in HBM ---------------------------------------
+    for _ in range(max(a.warmup, 3)):
+        eng.run(P, kind)
+    barrier()
+    clocks = Clocks(local)
+    if rank == 0:
+        clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(a.steps):
+        eng.run(P, kind)
+    e1.record()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    clk = clocks.stop() if rank == 0 else None
+    loss_val = float(P.loss.item())
+
+    # ---- end to end through the public call with HOST buffers: H2D of the batch + step + D2H of the loss --------
+    for i in range(3):
+        load(i)
+        eng.run(P, kind)
+        loss_host.copy_(P.loss, non_blocking=True)
+        torch.cuda.synchronize()
+    barrier()
+    e0.record()
+    for i in range(a.steps):
+        load(i)
+        eng.run(P, kind)
+        loss_host.copy_(P.loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()               # the caller reads the loss every step
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+
+    roof = gemm_roofline(torch, eng, P, peaks) if rank == 0 else None
+    if a.profile_kernels and rank == 0:
+        kernel_table(torch, eng, P)
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        r = cpu_reference_run(a.batch, a.seconds, 3, 1)
+        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        act_mb = sum(t.numel() * t.element_size() for t in vars(P).values() if isinstance(t, torch.Tensor)) / 2 ** 20
+        line = {
+            "metric": METRIC, "value": world * audio_s_step * a.steps / (ms_total * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_total / a.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(a), "global_batch_utts": world * a.batch, "audio_s_per_step": world * audio_s_step,
+                       "frames": T, "vocab": VOCAB, "params": eng.num_params(), "parallelism": f"dp{world}",
+                       "cuda_graph": not a.no_graph,
+                       "l2": "no flush: per-step working set (activations+logits+grads, > 400 MB) exceeds the 126 MB L2"},
+            "e2e": {"value": world * audio_s_step * a.steps / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / a.steps,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+            "gpu_launches": launches_per_step * a.steps * 2,     # device-resident loop + e2e loop, per rank
+            "launches_per_step": launches_per_step, "loss": loss_val, "clocks": clk, "roofline": roof,
+            "cpu_baseline": cpu, "plan_tensor_mb_top_level": round(act_mb, 1),
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def kernel_table(torch, eng, P):
+    """Per-entry-point device time of one eager step (CUDA events around every C-ABI call) -> stderr."""
+    from s2t_b200 import ops
+    recs = []
+    orig = ops._call
+
+    def timed(name, *args):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        orig(name, *args)
+        e1.record()
+        recs.append((name, e0, e1))
+
+    ops._call = timed
+    try:
+        eng.train_step(P)
+    finally:
+        ops._call = orig
+    torch.cuda.synchronize()
+    agg = {}
+    for name, a, b in recs:
+        t, n = agg.get(name, (0.0, 0))
+        agg[name] = (t + a.elapsed_time(b), n + 1)
+    tot = sum(t for t, _ in agg.values())
+    for name, (t, n) in sorted(agg.items(), key=lambda kv: -kv[1][0]):
+        print(f"{name:28s} calls {n:4d}  total {t:8.3f} ms  avg {1e3 * t / n:8.1f} us  {100 * t / tot:5.1f} %", file=sys.stderr)
+    print(f"{'sum':28s} calls {len(recs):4d}  total {tot:8.3f} ms", file=sys.stderr)
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

@@ -231,7 +231,8 @@ class S2TEncoderEngine:
         self.step_counter = torch.zeros(1, device=self.device, dtype=torch.int64)
         self.plans: Dict[Tuple[int, int, int, int], Plan] = {}
         self.training = True
-        self.grad_ready_hook = None  # callable(lo, hi): grad range [lo, hi) of store.grad is final (dp.py)
+        self.grad_ready_hook = None  # callable(offset): store.grad[offset:] is final (dp.BucketedAllReduce.on_ready)
+        self.dp = None               # dp.BucketedAllReduce when data parallel
         self.init_parameters()
 
     # ------------------------------------------------------------------------------------------
@@ -618,9 +619,25 @@ class S2TEncoderEngine:
     def train_step(self, P: Plan) -> None:
         """One fwd+bwd pass: loss in P.loss, gradients in store.grad.  No host sync, no allocation."""
         ops.counter_add(self.step_counter, 1)
+        if self.dp is not None:
+            self.dp.reset()
         self._forward(P)
         self._loss(P, need_grad=True)
         self._backward(P)
+        if self.dp is not None:
+            self.dp.finish()
+
+    def enable_data_parallel(self, n_buckets: int = 4, group=None) -> None:
+        """Bucketed gradient all-reduce overlapped with backward (dp.py); cut points = the offsets at which the
+        backward pass reports progress (start of every layer / block in the flat gradient buffer)."""
+        from .dp import BucketedAllReduce
+        S = self.store
+        cuts = [S.offset(n) for n in S.names()
+                if n.endswith("self_attn_layer_norm.weight") or n in ("layer_norm.weight", "ctc.ctc_projection.weight",
+                                                                      "embed_ln.weight")
+                or (n.startswith("subsample.") and n.endswith("weight"))]
+        self.dp = BucketedAllReduce(S.grad, cuts, n_buckets, group)
+        self.grad_ready_hook = self.dp.on_ready
 
     def capture(self, P: Plan, kind: str = "train") -> None:
         """Capture train_step (or forward-only 'infer') of this plan into a CUDA graph."""
