@@ -1,0 +1,114 @@
+"""CPU tests (no GPU): the oracle against the committed golden vectors produced by the reference itself
+(tests/golden/*.npz, generator: oracle/make_golden.py) and against the third-party routines the reference
+calls (torchaudio kaldi.fbank, torch.nn.CTCLoss)."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+GOLDEN = Path(__file__).resolve().parent / "golden"
+
+
+def test_fbank_oracle_matches_golden_torchaudio_output():
+    from oracle import fbank as OF
+    fx = np.load(GOLDEN / "fbank_cmvn.npz")
+    got = OF.fbank(fx["wave"])
+    assert got.shape == fx["fbank"].shape == (OF.num_frames(len(fx["wave"])), 80)
+    assert np.abs(got - fx["fbank"]).max() < 1e-3          # fbank fp32 max-abs 1e-3
+    assert np.abs(OF.utterance_cmvn(fx["fbank"]) - fx["utt_cmvn"]).max() == 0.0     # reference UtteranceCMVN, bit-exact
+    assert np.abs(OF.global_cmvn(fx["fbank"], fx["gmean"], fx["gstd"]) - fx["global_cmvn"]).max() == 0.0
+
+
+def test_fbank_oracle_matches_live_torchaudio():
+    K = pytest.importorskip("torchaudio.compliance.kaldi")
+    from oracle import fbank as OF
+    g = torch.Generator().manual_seed(7)
+    for n in (400, 401, 1234, 16000):
+        w = torch.randn((1, n), generator=g) * 3000.0
+        ref = K.fbank(w, num_mel_bins=80, sample_frequency=16000).numpy()
+        got = OF.fbank(w[0].numpy())
+        assert got.shape == ref.shape
+        assert np.abs(got - ref).max() < 1e-3
+    assert OF.num_frames(399) == 0 and OF.num_frames(400) == 1 and OF.num_frames(160000) == 998
+
+
+def test_product_mel_tables_equal_oracle_tables():
+    """The product computes its mel matrix / window on the host with the same fp32 formulas (frontend.py)."""
+    from oracle import fbank as OF
+    from s2t_b200 import frontend
+    w = frontend.mel_filterbank(80).numpy()
+    assert w.shape == (80, 257) and np.all(w[:, 256] == 0)
+    assert np.abs(w[:, :256] - OF.mel_banks(80)[:, :256]).max() < 1e-6
+    assert np.abs(frontend.povey_window().numpy() - OF.povey_window()).max() < 1e-7
+    rng = frontend.mel_ranges(torch.from_numpy(w)).numpy()
+    for m in range(80):
+        nz = np.nonzero(w[m])[0]
+        assert rng[m, 0] == nz.min() and rng[m, 1] == nz.max() + 1
+
+
+@pytest.mark.parametrize("case", ["ragged", "repeats", "infeasible", "empty_target"])
+def test_ctc_oracle_matches_torch_ctcloss(case):
+    from oracle import ctc as OC
+    g = torch.Generator().manual_seed(11)
+    B, T, V = 3, 17, 9
+    logits = torch.randn((B, T, V), generator=g, dtype=torch.float64)
+    in_len = [17, 12, 9]
+    tg = {"ragged": [[3, 4, 5, 6], [2, 2, 7], [8]], "repeats": [[3, 3, 3], [4, 4], [5, 6, 6, 5]],
+          "infeasible": [[1, 2, 3], [4] * 13, [5]], "empty_target": [[], [3], [4, 4]]}[case]
+    nll, grad = OC.ctc_loss(logits.numpy(), [np.array(t, dtype=np.int64) for t in tg], in_len, blank=0)
+    x = logits.clone().requires_grad_(True)
+    lp = torch.log_softmax(x, -1).transpose(0, 1)
+    ref = torch.nn.functional.ctc_loss(lp, torch.tensor(sum(tg, []), dtype=torch.long), torch.tensor(in_len),
+                                       torch.tensor([len(t) for t in tg]), blank=0, reduction="none", zero_infinity=True)
+    ref.sum().backward()
+    assert np.allclose(nll, ref.detach().numpy(), rtol=1e-9, atol=1e-9)
+    assert np.allclose(grad, x.grad.numpy(), rtol=1e-7, atol=1e-9)
+
+
+def test_greedy_oracle_pad_to_blank_before_collapse():
+    from oracle import ctc as OC
+    V = 5
+    ids = np.array([[1, 1, 0, 1, 2, 2, 3, 3], [4, 4, 4, 0, 0, 2, 2, 2]])
+    logits = np.full((2, 8, V), -5.0)
+    for b in range(2):
+        for t in range(8):
+            logits[b, t, ids[b, t]] = 1.0
+    logits[0, 5, 1] = 1.0                                       # exact tie: lowest index wins (argmax of the fp32 log-probs)
+    out = OC.greedy_decode(logits, [8, 6], blank=0)
+    assert out[0].tolist() == [1, 1, 2, 1, 3] and out[1].tolist() == [4, 2]
+    toks = OC.targets_for_ctc_loss(np.array([[5, 6, 2, 1], [7, 2, 1, 1]]))
+    assert [t.tolist() for t in toks] == [[5, 6], [7]]
+
+
+@pytest.mark.parametrize("case", ["c1_small", "c4_small"])
+def test_encoder_oracle_matches_reference_golden(case):
+    """oracle/encoder.py reproduces the reference's S2TTransformerEncoder + ctc criterion outputs and gradients."""
+    from oracle import encoder as OE
+    from oracle.make_golden import ENC_CASES, reference_args, seeded_state_dict, state_checksum
+    fx = np.load(GOLDEN / f"enc_{case}.npz")
+    shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
+    sd = seeded_state_dict(shapes, int(fx["seed"]))
+    assert state_checksum(sd) == str(fx["weights_sha256"])
+    spec = dict(ENC_CASES[case])
+    args = reference_args(**spec)
+    for k, v in dict(encoder_embed_dim=256, encoder_ffn_embed_dim=2048, encoder_layers=12, encoder_attention_heads=4,
+                     subsampling_layers=2, subsampling_filter=1024, subsampling_kernel=5, subsampling_stride=2).items():
+        if not hasattr(args, k):
+            setattr(args, k, v)
+    orc = OE.S2TTransformerEncoder(OE.config_from_args(args))
+    orc.load_state_dict(sd)
+    orc.train()
+    feats, lens, tokens = (torch.from_numpy(fx[k]) for k in ("feats", "lens", "tokens"))
+    out = orc(feats, lens)
+    loss = OE.ctc_criterion_loss(out["ctc_logit"][0], out["encoder_padding_mask"][0], tokens)
+    loss.backward()
+    assert torch.equal(out["encoder_padding_mask"][0], torch.from_numpy(fx["padding_mask"]))
+    assert (out["encoder_out"][0].detach() - torch.from_numpy(fx["encoder_out"])).abs().max() < 1e-4
+    assert (out["ctc_logit"][0].detach() - torch.from_numpy(fx["ctc_logit"])).abs().max() < 1e-4
+    assert abs(loss.item() - float(fx["loss"])) < 1e-3 * abs(float(fx["loss"]))
+    params = dict(orc.named_parameters())
+    for key in fx.files:
+        if key.startswith("grad::"):
+            ref = torch.from_numpy(fx[key])
+            assert (params[key[6:]].grad - ref).norm() <= 1e-3 * ref.norm() + 1e-9, key
