@@ -84,6 +84,9 @@ typedef struct s2t_gemm_args {
   /* optional DEVICE counter added to dropout_seed when the kernel runs, so a captured CUDA graph    */
   /* draws a fresh mask on every replay (the host bumps the counter between replays); NULL = none   */
   const unsigned long long* dropout_seed_offset;
+  /* split-K over a thread-block cluster (partials reduced through distributed shared memory):           */
+  /* 0 = automatic, -1 = never, n > 1 = forced: the largest feasible factor <= n                          */
+  int split_k;
 } s2t_gemm_args;
 
 int s2t_gemm_bf16(const s2t_gemm_args* args, void* stream);

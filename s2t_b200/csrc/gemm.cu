@@ -26,16 +26,18 @@ namespace s2t {
 
 constexpr int kBM = 128;
 constexpr int kBK = 64;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;  // TMA warp, MMA warp, 8 epilogue warps
+constexpr int kEpiWarps = 8;
 
 struct GemmKernelParams {
   int M, N, K;
   int nb1;
   int a_zm1, a_zm2, b_zm1, b_zm2;  // 0 = operand is broadcast along that batch dim (stride 0)
-  void* out;
+  int nbatch;
+  int split_k;  // cluster size of the split-K kernel (1 = persistent kernel)
   int out_fp32;
-  int vec_ok;  // ldc/ldr/ldg multiples of 8 and 16B-aligned bases -> 16-byte accesses allowed
-  long long ldc, c_bs1, c_bs2;
+  int bias_vec;  // bias base 16B aligned -> 16-byte loads
+  int aux_vec;   // gate / residual strides multiples of 8 and 16B-aligned bases -> 16-byte loads
   const __nv_bfloat16* residual;
   long long ldr, r_bs1, r_bs2;
   const __nv_bfloat16* gate;
@@ -56,8 +58,11 @@ struct GemmCfg {
   static constexpr int kABytes = kBM * kBK * 2;
   static constexpr int kBBytes = BN * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BN >= 256) ? 2 : (BN >= 128 ? 3 : 4);  // <= 96 KB: two CTAs per SM
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kStages = (BN >= 256) ? 3 : (BN >= 128 ? 5 : 6);  // 144-160 KB operand ring
+  static constexpr int kStagingBytes = kEpiWarps * 2 /*double buffer*/ * 4096;
+  static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;            // two accumulator buffers
+  static constexpr int kSmemBytes =
+      kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {
@@ -66,37 +71,333 @@ __device__ __forceinline__ float apply_act(float v, int act) {
   return v;
 }
 
-template <int BN, int A_MN, int B_MN>
-__global__ void __launch_bounds__(kGemmThreads, 2)
+// Epilogue variants.  EPI >= 0 fixes the feature set at compile time (bits: 0-1 act, 2-3 gate mode, 4 dropout,
+// 5 residual/out_scale); EPI = -1 reads everything from the runtime parameters (any combination, slower code).
+constexpr int kEpiGeneric = -1;
+constexpr int epi_code(int act, int gate, int drop, int res) { return act | (gate << 2) | (drop << 4) | (res << 5); }
+
+template <int EPI>
+__device__ __forceinline__ void epilogue8(float (&v)[8], const GemmKernelParams& p, int col, int nvalid,
+                                          long long grow, long long rrow, unsigned long long drop_row,
+                                          unsigned long long drop_seed) {
+  const int act = EPI < 0 ? p.act : (EPI & 3);
+  const int gate_mode = EPI < 0 ? p.gate_mode : ((EPI >> 2) & 3);
+  const bool drop = EPI < 0 ? (p.drop_thresh16 != 0) : ((EPI >> 4) & 1);
+  const bool res = EPI < 0 ? true : ((EPI >> 5) & 1);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] *= p.alpha;
+  if (p.bias != nullptr) {
+    if (nvalid == 8 && p.bias_vec) {
+      const uint4 bv = *reinterpret_cast<const uint4*>(p.bias + col);
+      v[0] += bf16_lo(bv.x); v[1] += bf16_hi(bv.x); v[2] += bf16_lo(bv.y); v[3] += bf16_hi(bv.y);
+      v[4] += bf16_lo(bv.z); v[5] += bf16_hi(bv.z); v[6] += bf16_lo(bv.w); v[7] += bf16_hi(bv.w);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j < nvalid) v[j] += __bfloat162float(p.bias[col + j]);
+    }
+  }
+  if (act == S2T_ACT_RELU) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+  } else if (act == S2T_ACT_SWISH) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = v[j] * __frcp_rn(1.f + __expf(-v[j]));
+  }
+  if (gate_mode != S2T_GATE_NONE) {
+    float gt[8];
+    if (nvalid == 8 && p.aux_vec) {
+      const uint4 gv = *reinterpret_cast<const uint4*>(p.gate + grow + col);
+      gt[0] = bf16_lo(gv.x); gt[1] = bf16_hi(gv.x); gt[2] = bf16_lo(gv.y); gt[3] = bf16_hi(gv.y);
+      gt[4] = bf16_lo(gv.z); gt[5] = bf16_hi(gv.z); gt[6] = bf16_lo(gv.w); gt[7] = bf16_hi(gv.w);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) gt[j] = j < nvalid ? __bfloat162float(p.gate[grow + col + j]) : 0.f;
+    }
+    if (gate_mode == S2T_GATE_POSITIVE) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = gt[j] > 0.f ? v[j] : 0.f;
+    } else if (gate_mode == S2T_GATE_SWISH_GRAD) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float sg = __frcp_rn(1.f + __expf(-gt[j]));
+        v[j] *= sg * (1.f + gt[j] * (1.f - sg));
+      }
+    } else {  // S2T_GATE_MUL
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] *= gt[j];
+    }
+  }
+  if (drop) {
+    const uint32_t keep = dropout_keep8(drop_seed, p.drop_stream, drop_row + (col >> 3), p.drop_thresh16);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = ((keep >> j) & 1u) ? v[j] * p.drop_inv_keep : 0.f;
+  }
+  if (res) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] *= p.out_scale;
+    if (p.residual != nullptr) {
+      if (nvalid == 8 && p.aux_vec) {
+        const uint4 rv = *reinterpret_cast<const uint4*>(p.residual + rrow + col);
+        v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x); v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
+        v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z); v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j < nvalid) v[j] += __bfloat162float(p.residual[rrow + col + j]);
+      }
+    }
+  }
+}
+
+// Persistent, warp-specialised GEMM.  One CTA per SM walks tiles blockIdx.x, +gridDim.x, ...;
+//   warp 0    TMA producer  : operand ring (full/empty mbarriers) running continuously across tiles
+//   warp 1    MMA issuer    : tcgen05.mma into one of TWO TMEM accumulator buffers (tmem_full/tmem_empty)
+//   warps 2-5 epilogue      : tcgen05.ld -> fused epilogue -> swizzled smem staging -> TMA store (coalesced,
+//                             edge-clipped by the tensor map); overlaps the next tile's loads and MMAs
+template <int BN, int A_MN, int B_MN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const GemmKernelParams p) {
+                 const __grid_constant__ CUtensorMap tmC, const GemmKernelParams p) {
   using Cfg = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned (stage sizes are multiples of 1024)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
-  uint64_t* accum_bar = empty_bar + Cfg::kStages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;   // [2]
+  uint64_t* tempty_bar = tfull_bar + 2;             // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * kBM;
-  const int n0 = blockIdx.x * BN;
-  const int z = blockIdx.z;
-  const int z1 = z % p.nb1;
-  const int z2 = z / p.nb1;
   const int num_kb = (p.K + kBK - 1) / kBK;
+  const int tiles_m = (p.M + kBM - 1) / kBM;
+  const int tiles_n = (p.N + BN - 1) / BN;
+  const int tiles_per_z = tiles_m * tiles_n;
+  const int num_tiles = tiles_per_z * p.nbatch;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < Cfg::kStages; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    mbar_init(accum_bar, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], kEpiWarps);
+    }
     fence_mbar_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int z = tile / tiles_per_z;
+        const int r = tile - z * tiles_per_z;
+        const int m0 = (r % tiles_m) * kBM, n0 = (r / tiles_m) * BN;
+        const int z1 = z % p.nb1, z2 = z / p.nb1;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % Cfg::kStages;
+          const uint32_t ph = (it / Cfg::kStages) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          mbar_expect_tx(&full_bar[s], Cfg::kStageBytes);
+          uint8_t* a_dst = smem + s * Cfg::kStageBytes;
+          uint8_t* b_dst = a_dst + Cfg::kABytes;
+          if (A_MN == 0) {
+            tma_load_4d(a_dst, &tmA, &full_bar[s], kb * kBK, m0, z1 * p.a_zm1, z2 * p.a_zm2);
+          } else {
+#pragma unroll
+            for (int c = 0; c < kBM / 64; ++c)
+              tma_load_4d(a_dst + c * (kBK * 128), &tmA, &full_bar[s], m0 + c * 64, kb * kBK, z1 * p.a_zm1,
+                          z2 * p.a_zm2);
+          }
+          if (B_MN == 0) {
+            tma_load_4d(b_dst, &tmB, &full_bar[s], kb * kBK, n0, z1 * p.b_zm1, z2 * p.b_zm2);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c)
+              tma_load_4d(b_dst + c * (kBK * 128), &tmB, &full_bar[s], n0 + c * 64, kb * kBK, z1 * p.b_zm1,
+                          z2 * p.b_zm2);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer --------------------------------
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, A_MN, B_MN);
+      uint32_t it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+        const uint32_t buf = lt & 1;
+        mbar_wait(&tempty_bar[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % Cfg::kStages;
+          const uint32_t ph = (it / Cfg::kStages) & 1;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + s * Cfg::kStageBytes);
+          const uint32_t b_addr = a_addr + Cfg::kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t adesc = A_MN ? umma_smem_desc(a_addr + k * 2048, kBK * 128, 1024)
+                                        : umma_smem_desc(a_addr + k * 32, 16, 1024);
+            const uint64_t bdesc = B_MN ? umma_smem_desc(b_addr + k * 2048, kBK * 128, 1024)
+                                        : umma_smem_desc(b_addr + k * 32, 16, 1024);
+            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);  // frees this smem stage once the MMAs above retire
+        }
+        umma_commit(&tfull_bar[buf]);  // accumulator of this tile complete
+      }
+    }
+  } else {
+    // ------------------------------ epilogue ----------------------------------
+    // 8 warps: warp w may touch TMEM lanes 32*(w%4)..; the two warps of a lane quarter split the tile's
+    // 128-byte output units (64 bf16 / 32 fp32 columns) between them.
+    const int ew = warp - 2;
+    const int q = warp & 3;
+    const int half = ew >> 2;
+    uint8_t* stage_base = staging + ew * 8192;
+    const unsigned long long drop_seed =
+        p.drop_seed + ((p.drop_thresh16 != 0 && p.drop_seed_off != nullptr) ? *p.drop_seed_off : 0ull);
+    constexpr int kChunksPerUnitBf16 = 2;
+    const int cpu = p.out_fp32 ? 1 : kChunksPerUnitBf16;  // 32-column TMEM chunks per staged unit
+    const int units = (BN / 32) / cpu;
+    uint32_t lt = 0, sb = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      const int z = tile / tiles_per_z;
+      const int r = tile - z * tiles_per_z;
+      const int m0 = (r % tiles_m) * kBM, n0 = (r / tiles_m) * BN;
+      const int z1 = z % p.nb1, z2 = z / p.nb1;
+      const uint32_t buf = lt & 1;
+      const int row = m0 + q * 32 + lane;
+      const long long rrow = static_cast<long long>(row) * p.ldr + z1 * p.r_bs1 + z2 * p.r_bs2;
+      const long long grow = static_cast<long long>(row) * p.ldg + z1 * p.g_bs1 + z2 * p.g_bs2;
+      const unsigned long long drop_row =
+          (static_cast<unsigned long long>(z) * p.M + row) * static_cast<unsigned long long>((p.N + 7) >> 3);
+      const bool row_ok = row < p.M;
+      mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + buf * BN + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+      for (int u = half; u < units; u += 2) {
+        const int ucol0 = n0 + u * cpu * 32;
+        if (ucol0 >= p.N) break;  // warp-uniform
+        uint32_t rg[2][32];
+        tmem_ld_32x32(t_addr + u * cpu * 32, rg[0]);
+        if (cpu == 2) tmem_ld_32x32(t_addr + u * cpu * 32 + 32, rg[1]);
+        uint8_t* sbuf = stage_base + (sb & 1) * 4096;
+        // this staging buffer was handed to a TMA store two stores ago: wait until it has been read
+        if (lane == 0) tma_store_wait_read<1>();
+        tmem_ld_wait();
+        __syncwarp();
+        uint8_t* srow = sbuf + lane * 128;
+#pragma unroll
+        for (int sub = 0; sub < 2; ++sub) {
+          if (sub < cpu) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              const int col = ucol0 + sub * 32 + g * 8;
+              float v[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rg[sub][g * 8 + j]);
+              if (row_ok && col < p.N)
+                epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed);
+              if (p.out_fp32) {
+                *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
+              } else {
+                uint4 ov;
+                ov.x = pack_bf16(v[0], v[1]); ov.y = pack_bf16(v[2], v[3]);
+                ov.z = pack_bf16(v[4], v[5]); ov.w = pack_bf16(v[6], v[7]);
+                *reinterpret_cast<uint4*>(srow + (((sub * 4 + g) ^ (lane & 7)) << 4)) = ov;
+              }
+            }
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
+          tma_store_commit();
+        }
+        ++sb;
+      }
+      // accumulator drained: hand the TMEM buffer back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+    }
+    if (lane == 0) tma_store_wait_read<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+// Split-K GEMM for K-heavy problems with few output tiles (weight gradients: K = B*T rows; ffn.w_2; the
+// vocabulary dgrad).  A thread-block cluster of S CTAs shares one output tile: CTA r reduces k-blocks
+// [r*kb_per, (r+1)*kb_per) into its own TMEM accumulator, ranks > 0 park their fp32 partial tile in their
+// shared memory (the idle operand ring), the leader pulls them over DSMEM (ld.shared::cluster), adds them to its
+// own accumulator and runs the fused epilogue + TMA store.  No global workspace, one launch.
+template <int BN, int A_MN, int B_MN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                        const __grid_constant__ CUtensorMap tmC, const GemmKernelParams p) {
+  using Cfg = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
+  uint64_t* empty_bar = full_bar + Cfg::kStages;
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull_bar + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int S = p.split_k;
+  const int rank = static_cast<int>(cluster_ctarank());
+  const int tile = blockIdx.x / S;
+  const int num_kb = (p.K + kBK - 1) / kBK;
+  const int kb_per = (num_kb + S - 1) / S;
+  const int kb0 = rank * kb_per;
+  const int kb1 = min(num_kb, kb0 + kb_per);  // host guarantees kb0 < num_kb for every rank
+  const int tiles_m = (p.M + kBM - 1) / kBM;
+  const int tiles_n = (p.N + BN - 1) / BN;
+  const int tiles_per_z = tiles_m * tiles_n;
+  const int z = tile / tiles_per_z;
+  const int r = tile - z * tiles_per_z;
+  const int m0 = (r % tiles_m) * kBM, n0 = (r / tiles_m) * BN;
+  const int z1 = z % p.nb1, z2 = z / p.nb1;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < Cfg::kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(tfull_bar, 1);
+    fence_mbar_init();
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    if (rank == 0) tma_prefetch_desc(&tmC);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, BN < 32 ? 32 : BN);
@@ -108,11 +409,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ------------------------------ TMA producer ------------------------------
     if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % Cfg::kStages;
-        const uint32_t ph = (kb / Cfg::kStages) & 1;
+      for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+        const int s = it % Cfg::kStages;
+        const uint32_t ph = (it / Cfg::kStages) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
         mbar_expect_tx(&full_bar[s], Cfg::kStageBytes);
         uint8_t* a_dst = smem + s * Cfg::kStageBytes;
@@ -136,12 +436,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    // ------------------------------ MMA issuer --------------------------------
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, A_MN, B_MN);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % Cfg::kStages;
-        const uint32_t ph = (kb / Cfg::kStages) & 1;
+      for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+        const int s = it % Cfg::kStages;
+        const uint32_t ph = (it / Cfg::kStages) & 1;
         mbar_wait(&full_bar[s], ph);
         tc_fence_after();
         const uint32_t a_addr = smem_u32(smem + s * Cfg::kStageBytes);
@@ -152,134 +451,111 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                       : umma_smem_desc(a_addr + k * 32, 16, 1024);
           const uint64_t bdesc = B_MN ? umma_smem_desc(b_addr + k * 2048, kBK * 128, 1024)
                                       : umma_smem_desc(b_addr + k * 32, 16, 1024);
-          umma_bf16(tmem_base, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_bf16(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
         }
-        umma_commit(&empty_bar[s]);  // frees this smem stage once the MMAs above retire
+        umma_commit(&empty_bar[s]);
       }
-      umma_commit(accum_bar);  // accumulator complete
-    }
-  } else {
-    // ------------------------------ epilogue ----------------------------------
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
-    const int row = m0 + q * 32 + lane;
-    const bool row_ok = row < p.M;
-    mbar_wait(accum_bar, 0);
-    tc_fence_after();
-
-    const long long crow = static_cast<long long>(row) * p.ldc + z1 * p.c_bs1 + z2 * p.c_bs2;
-    const long long rrow = static_cast<long long>(row) * p.ldr + z1 * p.r_bs1 + z2 * p.r_bs2;
-    const long long grow = static_cast<long long>(row) * p.ldg + z1 * p.g_bs1 + z2 * p.g_bs2;
-    // dropout counter: element (z, row, col) lives in Philox group (z*M+row)*ceil(N/8) + col/8, bit col%8
-    const unsigned long long drop_row =
-        (static_cast<unsigned long long>(z) * p.M + row) * static_cast<unsigned long long>((p.N + 7) >> 3);
-    const unsigned long long drop_seed =
-        p.drop_seed + ((p.drop_thresh16 != 0 && p.drop_seed_off != nullptr) ? *p.drop_seed_off : 0ull);
-
-#pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      const int col0 = n0 + c * 32;
-      if (col0 >= p.N) break;  // warp-uniform
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, r);
-      tmem_ld_wait();
-      if (!row_ok) continue;
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {  // groups of 8 columns
-        const int col = col0 + g * 8;
-        if (col >= p.N) break;
-        const int nvalid = min(8, p.N - col);
-        const bool full8 = (nvalid == 8) && p.vec_ok;
-        float v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * p.alpha;
-        if (p.bias != nullptr) {
-          if (nvalid == 8 && (col & 7) == 0 &&
-              (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) {
-            const uint4 bv = *reinterpret_cast<const uint4*>(p.bias + col);
-            v[0] += bf16_lo(bv.x); v[1] += bf16_hi(bv.x);
-            v[2] += bf16_lo(bv.y); v[3] += bf16_hi(bv.y);
-            v[4] += bf16_lo(bv.z); v[5] += bf16_hi(bv.z);
-            v[6] += bf16_lo(bv.w); v[7] += bf16_hi(bv.w);
-          } else {
-            for (int j = 0; j < nvalid; ++j) v[j] += __bfloat162float(p.bias[col + j]);
-          }
-        }
-        if (p.act != S2T_ACT_NONE) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], p.act);
-        }
-        if (p.gate_mode != S2T_GATE_NONE) {
-          float gt[8];
-          if (full8) {
-            const uint4 gv = *reinterpret_cast<const uint4*>(p.gate + grow + col);
-            gt[0] = bf16_lo(gv.x); gt[1] = bf16_hi(gv.x);
-            gt[2] = bf16_lo(gv.y); gt[3] = bf16_hi(gv.y);
-            gt[4] = bf16_lo(gv.z); gt[5] = bf16_hi(gv.z);
-            gt[6] = bf16_lo(gv.w); gt[7] = bf16_hi(gv.w);
-          } else {
-            for (int j = 0; j < 8; ++j)
-              gt[j] = j < nvalid ? __bfloat162float(p.gate[grow + col + j]) : 0.f;
-          }
-          if (p.gate_mode == S2T_GATE_POSITIVE) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = gt[j] > 0.f ? v[j] : 0.f;
-          } else if (p.gate_mode == S2T_GATE_SWISH_GRAD) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float s = 1.f / (1.f + __expf(-gt[j]));
-              v[j] *= s * (1.f + gt[j] * (1.f - s));
-            }
-          } else {  // S2T_GATE_MUL
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] *= gt[j];
-          }
-        }
-        if (p.drop_thresh16 != 0) {
-          const uint32_t keep =
-              dropout_keep8(drop_seed, p.drop_stream, drop_row + (col >> 3), p.drop_thresh16);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = ((keep >> j) & 1u) ? v[j] * p.drop_inv_keep : 0.f;
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] *= p.out_scale;
-        if (p.residual != nullptr) {
-          if (full8) {
-            const uint4 rv = *reinterpret_cast<const uint4*>(p.residual + rrow + col);
-            v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x);
-            v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
-            v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z);
-            v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
-          } else {
-            for (int j = 0; j < nvalid; ++j) v[j] += __bfloat162float(p.residual[rrow + col + j]);
-          }
-        }
-        if (p.out_fp32) {
-          float* o = reinterpret_cast<float*>(p.out) + crow + col;
-          if (full8) {
-            *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
-            *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
-          } else {
-            for (int j = 0; j < nvalid; ++j) o[j] = v[j];
-          }
-        } else {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + crow + col;
-          if (full8) {
-            uint4 ov;
-            ov.x = pack_bf16(v[0], v[1]);
-            ov.y = pack_bf16(v[2], v[3]);
-            ov.z = pack_bf16(v[4], v[5]);
-            ov.w = pack_bf16(v[6], v[7]);
-            *reinterpret_cast<uint4*>(o) = ov;
-          } else {
-            for (int j = 0; j < nvalid; ++j) o[j] = __float2bfloat16(v[j]);
-          }
-        }
-      }
+      umma_commit(tfull_bar);
     }
   }
-
+  const int ew = warp - 2;
+  const int q = warp & 3;
+  const int half = ew >> 2;
+  const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+  // partial tile layout in the (now idle) operand ring: float4 index ((c*8 + g4)*128 + row): conflict-free
+  // for row-per-lane writers and readers alike
+  float4* part = reinterpret_cast<float4*>(smem);
+  const int prow = q * 32 + lane;
+  if (warp >= 2 && rank != 0) {
+    mbar_wait(tfull_bar, 0);  // all MMAs of this CTA retired: accumulator complete, ring no longer read
+    tc_fence_after();
+#pragma unroll 1
+    for (int c = half; c < BN / 32; c += 2) {
+      uint32_t rg[32];
+      tmem_ld_32x32(t_addr + c * 32, rg);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g4 = 0; g4 < 8; ++g4)
+        part[(c * 8 + g4) * 128 + prow] =
+            make_float4(__uint_as_float(rg[g4 * 4]), __uint_as_float(rg[g4 * 4 + 1]),
+                        __uint_as_float(rg[g4 * 4 + 2]), __uint_as_float(rg[g4 * 4 + 3]));
+    }
+  }
   tc_fence_before();
-  __syncthreads();
+  __syncwarp();
+  cluster_sync_all();  // partial tiles of ranks > 0 are visible cluster-wide
+  if (warp >= 2 && rank == 0) {
+    uint8_t* stage_base = staging + ew * 8192;
+    const unsigned long long drop_seed =
+        p.drop_seed + ((p.drop_thresh16 != 0 && p.drop_seed_off != nullptr) ? *p.drop_seed_off : 0ull);
+    const int cpu = p.out_fp32 ? 1 : 2;
+    const int units = (BN / 32) / cpu;
+    const int row = m0 + prow;
+    const long long rrow = static_cast<long long>(row) * p.ldr + z1 * p.r_bs1 + z2 * p.r_bs2;
+    const long long grow = static_cast<long long>(row) * p.ldg + z1 * p.g_bs1 + z2 * p.g_bs2;
+    const unsigned long long drop_row =
+        (static_cast<unsigned long long>(z) * p.M + row) * static_cast<unsigned long long>((p.N + 7) >> 3);
+    const bool row_ok = row < p.M;
+    const uint32_t part_local = smem_u32(part);
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    uint32_t sb = 0;
+#pragma unroll 1
+    for (int u = half; u < units; u += 2) {
+      const int ucol0 = n0 + u * cpu * 32;
+      if (ucol0 >= p.N) break;
+      uint8_t* sbuf = stage_base + (sb & 1) * 4096;
+      if (lane == 0) tma_store_wait_read<1>();
+      __syncwarp();
+      uint8_t* srow = sbuf + lane * 128;
+#pragma unroll 1
+      for (int sub = 0; sub < cpu; ++sub) {
+        const int c = u * cpu + sub;
+        uint32_t rg[32];
+        tmem_ld_32x32(t_addr + c * 32, rg);
+        tmem_ld_wait();
+        float acc[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc[j] = __uint_as_float(rg[j]);
+        for (int pr = 1; pr < S; ++pr) {
+          const uint32_t base = dsmem_addr(part_local, pr);
+#pragma unroll
+          for (int g4 = 0; g4 < 8; ++g4) {
+            const float4 t = dsmem_ld_f4(base + (((c * 8 + g4) * 128 + prow) << 4));
+            acc[g4 * 4] += t.x; acc[g4 * 4 + 1] += t.y; acc[g4 * 4 + 2] += t.z; acc[g4 * 4 + 3] += t.w;
+          }
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int col = ucol0 + sub * 32 + g * 8;
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j];
+          if (row_ok && col < p.N) epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed);
+          if (p.out_fp32) {
+            *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
+          } else {
+            uint4 ov;
+            ov.x = pack_bf16(v[0], v[1]); ov.y = pack_bf16(v[2], v[3]);
+            ov.z = pack_bf16(v[4], v[5]); ov.w = pack_bf16(v[6], v[7]);
+            *reinterpret_cast<uint4*>(srow + (((sub * 4 + g) ^ (lane & 7)) << 4)) = ov;
+          }
+        }
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
+        tma_store_commit();
+      }
+      ++sb;
+    }
+    if (lane == 0) tma_store_wait_read<0>();
+  }
+  tc_fence_before();
+  __syncwarp();
+  cluster_sync_all();  // ranks > 0 keep their shared memory alive until the leader has read it
   if (warp == 1) tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
 }
 
@@ -325,10 +601,11 @@ struct MapKeyHash {
 //   ld: stride of the outer dimension (elements), box_outer: rows per TMA box.
 static int make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, uint64_t outer,
                             uint64_t ld, uint64_t nb1, uint64_t bs1, uint64_t nb2, uint64_t bs2,
-                            uint32_t box_outer) {
+                            uint32_t box_outer, int fp32 = 0) {
+  const uint64_t es = fp32 ? 4 : 2;
   static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
   static std::mutex mu;
-  MapKey key{{reinterpret_cast<uint64_t>(ptr), inner, outer, ld, nb1, bs1, nb2, bs2, box_outer, 0}};
+  MapKey key{{reinterpret_cast<uint64_t>(ptr), inner, outer, ld, nb1, bs1, nb2, bs2, box_outer, (uint64_t)fp32}};
   {
     std::lock_guard<std::mutex> lk(mu);
     auto it = cache.find(key);
@@ -340,20 +617,21 @@ static int make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, u
   EncodeTiledFn enc = get_encode_fn();
   S2T_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
   S2T_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "GEMM operand base must be 16B aligned");
-  S2T_REQUIRE((ld * 2) % 16 == 0, "GEMM operand leading stride must be a multiple of 8 elements (got %llu)",
+  S2T_REQUIRE((ld * es) % 16 == 0, "GEMM operand/output leading stride must be a multiple of 16 bytes (got %llu elements)",
               (unsigned long long)ld);
   // Unit batch dims still need a legal (16B-multiple, non-zero) stride.
   if (bs1 == 0) nb1 = 1;  // broadcast batch dims collapse; the kernel zeroes the coordinate
   if (bs2 == 0) nb2 = 1;
-  uint64_t s1 = (nb1 > 1 ? bs1 : ld * outer) * 2, s2 = (nb2 > 1 ? bs2 : ld * outer) * 2;
+  uint64_t s1 = (nb1 > 1 ? bs1 : ld * outer) * es, s2 = (nb2 > 1 ? bs2 : ld * outer) * es;
   if (s1 == 0) s1 = 16;
   if (s2 == 0) s2 = 16;
-  S2T_REQUIRE(s1 % 16 == 0 && s2 % 16 == 0, "GEMM batch strides must be multiples of 8 elements");
+  S2T_REQUIRE(s1 % 16 == 0 && s2 % 16 == 0, "GEMM batch strides must be multiples of 16 bytes");
   cuuint64_t dims[4] = {inner, outer, nb1, nb2};
-  cuuint64_t strides[3] = {ld * 2, s1, s2};
-  cuuint32_t box[4] = {64, box_outer, 1, 1};
+  cuuint64_t strides[3] = {ld * es, s1, s2};
+  cuuint32_t box[4] = {fp32 ? 32u : 64u, box_outer, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides,
+  CUresult r = enc(out, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                   const_cast<void*>(ptr), dims, strides,
                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   S2T_REQUIRE(r == CUDA_SUCCESS,
@@ -369,32 +647,6 @@ static int make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, u
   return 0;
 }
 
-template <int BN, int A_MN, int B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmKernelParams& kp,
-                       int nbatch, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
-  static bool configured = false;
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
-  if (!configured) {
-    S2T_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        Cfg::kSmemBytes));
-    configured = true;
-  }
-  dim3 grid((kp.N + BN - 1) / BN, (kp.M + kBM - 1) / kBM, nbatch);
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, kp);
-  S2T_LAUNCH_CHECK();
-  return 0;
-}
-
-template <int BN>
-static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
-                          const GemmKernelParams& kp, int nbatch, cudaStream_t stream) {
-  if (!a_mn && !b_mn) return launch_gemm<BN, 0, 0>(ta, tb, kp, nbatch, stream);
-  if (!a_mn && b_mn) return launch_gemm<BN, 0, 1>(ta, tb, kp, nbatch, stream);
-  if (a_mn && !b_mn) return launch_gemm<BN, 1, 0>(ta, tb, kp, nbatch, stream);
-  return launch_gemm<BN, 1, 1>(ta, tb, kp, nbatch, stream);
-}
-
 static int sm_count() {
   static int n = 0;
   if (n == 0) {
@@ -404,6 +656,91 @@ static int sm_count() {
     if (n <= 0) n = 148;
   }
   return n;
+}
+
+template <int BN, int A_MN, int B_MN, int EPI>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
+                       const GemmKernelParams& kp, int nbatch, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  static bool configured = false;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI>;
+  if (!configured) {
+    S2T_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::kSmemBytes));
+    configured = true;
+  }
+  const long long tiles = 1ll * ((kp.N + BN - 1) / BN) * ((kp.M + kBM - 1) / kBM) * nbatch;
+  const int grid = static_cast<int>(tiles < sm_count() ? tiles : sm_count());
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, tc, kp);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int BN, int A_MN, int B_MN, int EPI>
+static int launch_gemm_splitk(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
+                              const GemmKernelParams& kp, int nbatch, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  static bool configured = false;
+  auto kern = gemm_bf16_splitk_kernel<BN, A_MN, B_MN, EPI>;
+  if (!configured) {
+    S2T_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::kSmemBytes));
+    configured = true;
+  }
+  const long long tiles = 1ll * ((kp.N + BN - 1) / BN) * ((kp.M + kBM - 1) / kBM) * nbatch;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(static_cast<unsigned>(tiles * kp.split_k), 1, 1);
+  cfg.blockDim = dim3(kGemmThreads, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kp.split_k;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  S2T_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, kp));
+  return 0;
+}
+
+template <int BN>
+static int dispatch_splitk(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
+                           const CUtensorMap& tc, const GemmKernelParams& kp, int nbatch,
+                           cudaStream_t stream) {
+  const bool plain = kp.act == S2T_ACT_NONE && kp.gate_mode == S2T_GATE_NONE && kp.drop_thresh16 == 0 &&
+                     kp.residual == nullptr && kp.out_scale == 1.f;
+#define S2T_SK_CASE(AM, BM_)                                                                        \
+  if (a_mn == AM && b_mn == BM_)                                                                    \
+    return plain ? launch_gemm_splitk<BN, AM, BM_, 0>(ta, tb, tc, kp, nbatch, stream)               \
+                 : launch_gemm_splitk<BN, AM, BM_, kEpiGeneric>(ta, tb, tc, kp, nbatch, stream);
+  S2T_SK_CASE(0, 0) S2T_SK_CASE(0, 1) S2T_SK_CASE(1, 0) S2T_SK_CASE(1, 1)
+#undef S2T_SK_CASE
+  return -1;
+}
+
+template <int BN>
+static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
+                          const CUtensorMap& tc, const GemmKernelParams& kp, int nbatch,
+                          cudaStream_t stream) {
+  // compile-time epilogue variants for the combinations the training step launches most; anything else
+  // runs the generic (runtime-parameter) epilogue
+  const int act = kp.act, gm = kp.gate_mode, dr = kp.drop_thresh16 != 0 ? 1 : 0;
+  const int rs = (kp.residual != nullptr || kp.out_scale != 1.f) ? 1 : 0;
+  const int code = epi_code(act, gm, dr, rs);
+#define S2T_GEMM_CASE(AM, BM_, CODE)                                         \
+  if (a_mn == AM && b_mn == BM_ && code == (CODE))                           \
+    return launch_gemm<BN, AM, BM_, (CODE)>(ta, tb, tc, kp, nbatch, stream);
+  S2T_GEMM_CASE(0, 0, 0) S2T_GEMM_CASE(0, 1, 0) S2T_GEMM_CASE(1, 0, 0) S2T_GEMM_CASE(1, 1, 0)
+  S2T_GEMM_CASE(0, 0, epi_code(0, 0, 0, 1)) S2T_GEMM_CASE(0, 0, epi_code(0, 0, 1, 1))
+  S2T_GEMM_CASE(0, 0, epi_code(S2T_ACT_RELU, 0, 0, 0)) S2T_GEMM_CASE(0, 0, epi_code(S2T_ACT_RELU, 0, 1, 0))
+  S2T_GEMM_CASE(0, 1, epi_code(0, S2T_GATE_POSITIVE, 0, 0)) S2T_GEMM_CASE(0, 1, epi_code(0, S2T_GATE_POSITIVE, 1, 0))
+#undef S2T_GEMM_CASE
+  if (!a_mn && !b_mn) return launch_gemm<BN, 0, 0, kEpiGeneric>(ta, tb, tc, kp, nbatch, stream);
+  if (!a_mn && b_mn) return launch_gemm<BN, 0, 1, kEpiGeneric>(ta, tb, tc, kp, nbatch, stream);
+  if (a_mn && !b_mn) return launch_gemm<BN, 1, 0, kEpiGeneric>(ta, tb, tc, kp, nbatch, stream);
+  return launch_gemm<BN, 1, 1, kEpiGeneric>(ta, tb, tc, kp, nbatch, stream);
 }
 
 }  // namespace s2t
@@ -419,23 +756,50 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
   S2T_REQUIRE(nb1 * nb2 <= 65535, "s2t_gemm_bf16: too many batches");
   S2T_REQUIRE(g->a && g->b && g->out, "s2t_gemm_bf16: null operand");
 
-  // tile width: widest BN that still gives every SM a CTA (small-M problems are latency bound)
-  int bn = g->tile_n;
-  if (bn != 64 && bn != 128 && bn != 256) {
+  // Tile width and split-K factor from a small cost model (cycles per SM, measured constants: ~44 B/clk of
+  // operand traffic per SM, ~13 clk per output column of a 128-row tile in the 8-warp epilogue).
+  const int num_kb = (g->K + kBK - 1) / kBK;
+  int bn = g->tile_n, split = 1;
+  {
     const long long mt = (g->M + kBM - 1) / kBM;
     const long long nbz = static_cast<long long>(nb1) * nb2;
-    bn = 64;
-    for (int cand : {256, 128}) {
-      if (g->N < cand / 2 + 1 && cand > 64) continue;  // mostly-empty tile
-      const long long ctas = mt * ((g->N + cand - 1) / cand) * nbz;
-      if (ctas >= sm_count()) {
+    double best = -1.0;
+    for (int cand : {64, 128, 256}) {
+      if (g->tile_n == 64 || g->tile_n == 128 || g->tile_n == 256) {
+        if (cand != g->tile_n) continue;
+      } else if (cand > 64 && g->N <= cand / 2) {
+        continue;  // mostly-empty tile
+      }
+      const long long tiles = mt * ((g->N + cand - 1) / cand) * nbz;
+      const double kb_cyc = (kBM + cand) * 128.0 / 44.0;
+      const double epi = cand * 13.0;
+      const long long waves = (tiles + sm_count() - 1) / sm_count();
+      const double main1 = num_kb * kb_cyc;
+      double cost = 2500.0 + (waves - 1) * (main1 > epi ? main1 : epi) + main1 + epi;
+      int s_here = 1;
+      if (g->split_k >= 0 && num_kb >= 12) {
+        // power-of-two clusters only (odd sizes pack badly into GPCs), one wave, >= 4 k-blocks per rank
+        for (int sk : {2, 4, 8}) {
+          if (g->split_k > 1 && sk > g->split_k) break;
+          if (tiles * sk > 128) break;
+          const int kb_per = (num_kb + sk - 1) / sk;
+          if (kb_per < 4 || (sk - 1) * kb_per >= num_kb) continue;
+          const double c2 = 4500.0 + kb_per * kb_cyc + epi * (1.0 + 0.6 * (sk - 1));
+          if (c2 < cost || (g->split_k > 1 && sk > s_here)) {  // split_k > 1 forces the largest feasible factor
+            cost = c2;
+            s_here = sk;
+          }
+        }
+      }
+      if (best < 0 || cost < best) {
+        best = cost;
         bn = cand;
-        break;
+        split = s_here;
       }
     }
   }
 
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tc;
   int rc;
   if (g->a_mn_major)
     rc = make_operand_map(&ta, g->a, g->M, g->K, g->lda, nb1, g->a_bs1, nb2, g->a_bs2, kBK);
@@ -447,20 +811,27 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
   else
     rc = make_operand_map(&tb, g->b, g->K, g->N, g->ldb, nb1, g->b_bs1, nb2, g->b_bs2, bn);
   if (rc) return rc;
+  // output: written by TMA stores of 32-row x 128-byte boxes (clipped at M / N by the map)
+  S2T_REQUIRE((nb1 == 1 || g->c_bs1 != 0) && (nb2 == 1 || g->c_bs2 != 0),
+              "s2t_gemm_bf16: batched output needs non-zero batch strides");
+  rc = make_operand_map(&tc, g->out, g->N, g->M, g->ldc, nb1, g->c_bs1, nb2, g->c_bs2, 32, g->out_fp32 ? 1 : 0);
+  if (rc) return rc;
 
   GemmKernelParams kp;
   memset(&kp, 0, sizeof(kp));
   kp.M = g->M; kp.N = g->N; kp.K = g->K; kp.nb1 = nb1;
+  kp.nbatch = nb1 * nb2;
+  kp.split_k = split;
   kp.a_zm1 = g->a_bs1 != 0; kp.a_zm2 = g->a_bs2 != 0;
   kp.b_zm1 = g->b_bs1 != 0; kp.b_zm2 = g->b_bs2 != 0;
-  kp.out = g->out; kp.out_fp32 = g->out_fp32;
-  kp.ldc = g->ldc; kp.c_bs1 = g->c_bs1; kp.c_bs2 = g->c_bs2;
+  kp.out_fp32 = g->out_fp32 ? 1 : 0;
   kp.residual = reinterpret_cast<const __nv_bfloat16*>(g->residual);
   kp.ldr = g->ldr ? g->ldr : g->ldc; kp.r_bs1 = g->r_bs1; kp.r_bs2 = g->r_bs2;
   kp.gate = reinterpret_cast<const __nv_bfloat16*>(g->gate);
   kp.ldg = g->ldg ? g->ldg : g->ldc; kp.g_bs1 = g->g_bs1; kp.g_bs2 = g->g_bs2;
   kp.bias = reinterpret_cast<const __nv_bfloat16*>(g->bias);
   kp.alpha = g->alpha; kp.out_scale = g->out_scale;
+  kp.drop_inv_keep = 1.f;
   kp.act = g->act; kp.gate_mode = g->gate ? g->gate_mode : S2T_GATE_NONE;
   if (g->dropout_p > 0.f) {
     S2T_REQUIRE(g->dropout_p < 1.f, "dropout_p must be < 1");
@@ -470,20 +841,26 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
     kp.drop_seed_off = g->dropout_seed_offset;
     kp.drop_stream = g->dropout_stream;
   }
-  const int esz = g->out_fp32 ? 4 : 2;
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-  bool vec = (kp.ldc % 8 == 0) && (kp.c_bs1 % 8 == 0) && (kp.c_bs2 % 8 == 0) && al16(g->out);
-  (void)esz;
+  kp.bias_vec = kp.bias && al16(kp.bias) ? 1 : 0;
+  bool vec = true;
   if (kp.residual)
     vec = vec && (kp.ldr % 8 == 0) && (kp.r_bs1 % 8 == 0) && (kp.r_bs2 % 8 == 0) && al16(kp.residual);
   if (kp.gate)
     vec = vec && (kp.ldg % 8 == 0) && (kp.g_bs1 % 8 == 0) && (kp.g_bs2 % 8 == 0) && al16(kp.gate);
-  kp.vec_ok = vec ? 1 : 0;
+  kp.aux_vec = vec ? 1 : 0;
 
   const int nbatch = nb1 * nb2;
+  if (split > 1) {
+    switch (bn) {
+      case 256: return dispatch_splitk<256>(g->a_mn_major, g->b_mn_major, ta, tb, tc, kp, nbatch, stream);
+      case 128: return dispatch_splitk<128>(g->a_mn_major, g->b_mn_major, ta, tb, tc, kp, nbatch, stream);
+      default: return dispatch_splitk<64>(g->a_mn_major, g->b_mn_major, ta, tb, tc, kp, nbatch, stream);
+    }
+  }
   switch (bn) {
-    case 256: return dispatch_major<256>(g->a_mn_major, g->b_mn_major, ta, tb, kp, nbatch, stream);
-    case 128: return dispatch_major<128>(g->a_mn_major, g->b_mn_major, ta, tb, kp, nbatch, stream);
-    default: return dispatch_major<64>(g->a_mn_major, g->b_mn_major, ta, tb, kp, nbatch, stream);
+    case 256: return dispatch_major<256>(g->a_mn_major, g->b_mn_major, ta, tb, tc, kp, nbatch, stream);
+    case 128: return dispatch_major<128>(g->a_mn_major, g->b_mn_major, ta, tb, tc, kp, nbatch, stream);
+    default: return dispatch_major<64>(g->a_mn_major, g->b_mn_major, ta, tb, tc, kp, nbatch, stream);
   }
 }

@@ -31,6 +31,7 @@ class GemmArgs(C.Structure):
         ("residual", _vp), ("ldr", _ll), ("r_bs1", _ll), ("r_bs2", _ll),
         ("tile_n", _i),
         ("dropout_seed_offset", _vp),
+        ("split_k", _i),
     ]
 
 

@@ -67,7 +67,7 @@ def gemm_raw(
     act: int = ACT_NONE, gate: Optional[torch.Tensor] = None, gate_mode: int = GATE_NONE, ldg: int = 0,
     g_bs: Tuple[int, int] = (0, 0), dropout: Optional[Tuple[float, int, int]] = None,
     out_scale: float = 1.0, residual: Optional[torch.Tensor] = None, ldr: int = 0,
-    r_bs: Tuple[int, int] = (0, 0), tile_n: int = 0,
+    r_bs: Tuple[int, int] = (0, 0), tile_n: int = 0, split_k: int = 0,
 ) -> None:
     """out[z] = residual + out_scale*dropout(gate(act(alpha * A[z] @ B[z]^T + bias))) — see s2t_b200.h.
 
@@ -99,6 +99,7 @@ def gemm_raw(
     g.residual, g.ldr = _p(residual), ldr
     g.r_bs1, g.r_bs2 = r_bs
     g.tile_n = tile_n
+    g.split_k = split_k
     _call("s2t_gemm_bf16", C.byref(g), _stream())
 
 

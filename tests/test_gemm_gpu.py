@@ -163,3 +163,28 @@ def test_conv1d_as_overlapping_row_gemm(cuda_lib):
     _check(out, ref.transpose(1, 2).reshape(B * T_out, Cout))
     back = ops.permute_conv_weight(wp, inverse=True)
     assert torch.equal(back.cpu(), w)
+
+
+@pytest.mark.parametrize("M,N,K,kind", [(256, 256, 2000, "wgrad"), (2000, 256, 2048, "lin"), (300, 200, 1000, "lin"),
+                                        (2000, 256, 10000, "dgrad"), (768, 256, 2000, "wgrad")])
+@pytest.mark.parametrize("split_k", [0, 2, 5, 8])
+@pytest.mark.parametrize("tile_n", [0, 64, 256])
+def test_split_k_cluster_reduction(cuda_lib, M, N, K, kind, split_k, tile_n):
+    """Split-K over a thread-block cluster (DSMEM reduction) equals the plain product, with and without an epilogue."""
+    from s2t_b200 import ops
+    if kind == "lin":
+        x, w = _rand((M, K), 31), _rand((N, K), 32, 0.05)
+        bias, res = _rand((N,), 33), _rand((M, N), 34)
+        out = ops.linear(x.cuda(), w.cuda(), bias.cuda(), residual=res.cuda(), ldr=N, out_scale=0.5, tile_n=tile_n,
+                         split_k=split_k)
+        ref = res.float() + 0.5 * (x.float() @ w.float().T + bias.float())
+    elif kind == "dgrad":
+        dy, w = _rand((M, K), 35), _rand((K, N), 36, 0.05)
+        out = ops.linear_dgrad(dy.cuda(), w.cuda(), tile_n=tile_n, split_k=split_k)
+        ref = dy.float() @ w.float()
+    else:
+        dy, x = _rand((K, M), 37, 0.1), _rand((K, N), 38)
+        out = ops.linear_wgrad(dy.cuda(), x.cuda(), out_dtype=torch.float32, tile_n=tile_n, split_k=split_k)
+        ref = dy.float().T @ x.float()
+    torch.cuda.synchronize()
+    _check(out, ref)

@@ -38,6 +38,8 @@ def main():
         ("ctc 2000x10000x256", 2000, 10000, 256, "lin"), ("ffn1 10000x2048x256", 10000, 2048, 256, "lin"),
         ("dgrad ffn2 2000x2048x256", 2000, 2048, 256, "dgrad"), ("wgrad ffn1 2048x256x2000", 2048, 256, 2000, "wgrad"),
         ("wgrad ctc 10000x256x2000", 10000, 256, 2000, "wgrad"), ("dgrad ctc 2000x256x10000", 2000, 256, 10000, "dgrad"),
+        ("wgrad ffn2 256x2048x2000", 256, 2048, 2000, "wgrad"), ("wgrad out 256x256x2000", 256, 256, 2000, "wgrad"),
+        ("wgrad qkv 768x256x2000", 768, 256, 2000, "wgrad"), ("dgrad qkv 2000x256x768", 2000, 256, 768, "dgrad"),
     ]
     for name, M, N, K, kind in shapes:
         if kind == "lin":
@@ -57,9 +59,9 @@ def main():
             ref = lambda: torch.matmul(dy.t(), x, out=out)
         fl = 2.0 * M * N * K
         row = [f"{name:28s}"]
-        for tn in (64, 128, 256):
+        for tn in (0,):
             us = timeit(mk(tn))
-            row.append(f"bn{tn}: {us:7.1f}us {fl / us / 1e6:7.1f}TF")
+            row.append(f"auto: {us:7.1f}us {fl / us / 1e6:7.1f}TF")
         us = timeit(ref)
         row.append(f"cublas: {us:7.1f}us {fl / us / 1e6:7.1f}TF")
         print("  ".join(row), flush=True)
