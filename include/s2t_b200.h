@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define S2T_ABI_VERSION 1
+#define S2T_ABI_VERSION 2
 
 /* status / introspection ---------------------------------------------------------------------- */
 const char* s2t_last_error(void);
@@ -187,6 +187,11 @@ int s2t_dropout(const void* x, void* y, long long n, float p, float out_scale,
  * xcol[b*t_out + t][j*C + c] = xp[b*x_bs + (t*stride + j)*C + c]                                   */
 int s2t_im2col1d(const void* xp, long long x_bs, void* xcol, int batch, int t_out, int C, int ksize,
                  int stride, void* stream);
+/* y[b][pad + t][:] = t < lengths[b] ? x[b][t][:] : 0 : x bf16 [B][T][C] into the zero-framed input
+ * y bf16 [B] x y_bs + [T + 2 pad][C] of the next Conv1d with the padding mask applied
+ * (Downsampling.forward, pdss2t_transformer.py:107-116); lengths may be NULL                       */
+int s2t_frame_rows(const void* x, const int* lengths, void* y, long long y_bs, int pad, int batch,
+                   int T, int C, void* stream);
 /* *counter += inc on the device (dropout seed counter of a captured step)                         */
 int s2t_counter_add(unsigned long long* counter, unsigned long long inc, void* stream);
 /* y += x, bf16 [n], n % 8 == 0                                                                    */
@@ -206,17 +211,64 @@ int s2t_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream);
 /* (espnet_multihead_attention.py:292-311).  clamp <= 0 disables the clamp.                        */
 /* probs_drop (optional) = dropout(probs) with the regenerable Philox mask.                        */
 /* --------------------------------------------------------------------------------------------- */
+/* bias_head_major != 0: the bias / dbias rows are ordered [head][batch][T] instead of the scores'    */
+/* [batch][head][T] (then every head's dBD is one dense [batch*T][ld_bias] matrix).                  */
 int s2t_attn_softmax_fwd(const void* scores, long long ld, const void* bias, long long ld_bias,
-                         int bias_mode, void* probs, void* probs_drop, const int* klen, int nbh,
+                         int bias_mode, int bias_head_major, void* probs, void* probs_drop,
+                         const int* klen, int nbh,
                          int heads, int Tq, int Tk, float scale, float clamp, float dropout_p,
                          unsigned long long seed, unsigned int stream_id,
                          const unsigned long long* seed_offset, void* stream);
 /* dscores = scale * probs * (dp - sum_k dp*probs), dp = dropout_mask * dprobs_drop / (1-p);
  * dbias (optional, bias_mode 2 layout [nbh][T][ld_bias]) receives the same values un-shifted.     */
 int s2t_attn_softmax_bwd(const void* probs, const void* dprobs_drop, void* dscores, void* dbias,
-                         long long ld_bias, const int* klen, int nbh, int heads, int Tq, int Tk,
+                         long long ld_bias, int bias_head_major, const int* klen, int nbh, int heads,
+                         int Tq, int Tk,
                          long long ld, float scale, float dropout_p, unsigned long long seed,
                          unsigned int stream_id, const unsigned long long* seed_offset, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
+/* K6: Conformer convolution module (fairseq/modules/convolution.py:8-120), channels-last.        */
+/* x, y bf16 [B][T][C]; depthwise weight bf16 [C][K] (the reference's (C,1,K) Conv1d weight);     */
+/* K odd, <= 31; zero padding (K-1)/2 at both ends of every utterance's T frames.                 */
+/* --------------------------------------------------------------------------------------------- */
+/* number of time tiles (= thread blocks = rows of the partial buffers below) for a [B][T] batch  */
+long long s2t_dwconv1d_tiles(int batch, int T);
+/* y = depthwise_conv(x).  bn_partials (optional) fp32 [tiles][2][C] receives per-tile sum(y),    */
+/* sum(y^2) per channel: the batch statistics s2t_batchnorm_fwd reduces (convolution.py:96-99).   */
+int s2t_dwconv1d_fwd(const void* x, const void* w, void* y, float* bn_partials, int batch, int T,
+                     int C, int K, void* stream);
+/* dx = conv_transpose(dy, w); dw[c][j] = sum_{b,t} dy[b][t][c] * x[b][t+j-pad][c].              */
+/* workspace fp32 [tiles][K][C].                                                                  */
+int s2t_dwconv1d_bwd(const void* x, const void* w, const void* dy, void* dx, void* dw,
+                     float* workspace, int batch, int T, int C, int K, void* stream);
+/* nn.BatchNorm1d(C) over `rows` = B*T rows (padded frames included, quirk A10) + activation      */
+/* (S2T_ACT_*).  training != 0: batch statistics from `partials` fp32 [nparts][2][C] (biased      */
+/* variance), running_mean/var fp32 [C] updated with `momentum` (unbiased variance) and           */
+/* *num_batches_tracked += 1 (all three optional).  training == 0: running statistics.            */
+/* save_stats fp32 [2][C] receives (mean, rstd) for the backward pass.                             */
+int s2t_batchnorm_fwd(const void* x, const float* partials, int nparts, const void* gamma,
+                      const void* beta, float* running_mean, float* running_var,
+                      long long* num_batches_tracked, float* save_stats, void* y, long long rows,
+                      int C, float eps, float momentum, int act, int training, void* stream);
+/* rows of the fp32 [n][2][C] scratch s2t_batchnorm_bwd needs                                      */
+int s2t_batchnorm_bwd_partials(long long rows);
+/* da = gradient w.r.t. the activation output; x = the BatchNorm input; dx, dgamma, dbeta bf16.    */
+int s2t_batchnorm_bwd(const void* da, const void* x, const float* save_stats, const void* gamma,
+                      const void* beta, float* partials, void* dx, void* dgamma, void* dbeta,
+                      long long rows, int C, int act, int training, void* stream);
+
+/* rel-pos attention query biases (espnet_multihead_attention.py:343-347): quv bf16 [rows][2C] =  */
+/* (q + pos_bias_u | q + pos_bias_v), q = C columns with row stride ldq; u, v bf16 [C] = (H, d_k). */
+int s2t_relpos_qbias_fwd(const void* q, long long ldq, const void* u, const void* v, void* quv,
+                         long long rows, int C, void* stream);
+/* dq (row stride lddq) = dquv[:, :C] + dquv[:, C:]  (d pos_bias_u/v = column sums of dquv)        */
+int s2t_relpos_qbias_bwd(const void* dquv, void* dq, long long lddq, long long rows, int C,
+                         void* stream);
+/* y = dropout(act(x)), dense bf16 [n], n % 8 == 0; Philox numbering of s2t_dropout (the mask is   */
+/* re-applied by a GEMM epilogue in the backward pass).  FFN with Swish: s2t_transformer_layer.py:59-65 */
+int s2t_act_dropout(const void* x, void* y, long long n, int act, float p, unsigned long long seed,
+                    unsigned int stream_id, const unsigned long long* seed_offset, void* stream);
 
 /* --------------------------------------------------------------------------------------------- */
 /* K7/K8/K9: CTC head softmax, CTC loss forward/backward, greedy decode.                          */

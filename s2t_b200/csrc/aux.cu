@@ -60,6 +60,24 @@ __global__ void im2col1d_kernel(const __nv_bfloat16* __restrict__ xp, long long 
   }
 }
 
+// y[b][pad + t][:] = t < lengths[b] ? x[b][t][:] : 0 — a stage output copied into the zero-framed input of the
+// next Conv1d with the padding mask applied (Downsampling.forward, pdss2t_transformer.py:107-116)
+__global__ void frame_rows_kernel(const __nv_bfloat16* __restrict__ x, const int* __restrict__ lengths,
+                                  __nv_bfloat16* __restrict__ y, long long y_bs, int pad, int batch, int T, int C) {
+  const int cv = C >> 3;
+  const long long n = static_cast<long long>(batch) * T * cv;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % cv) << 3;
+    const long long bt = i / cv;
+    const int t = static_cast<int>(bt % T);
+    const int b = static_cast<int>(bt / T);
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (lengths == nullptr || t < lengths[b]) v = *reinterpret_cast<const uint4*>(x + bt * C + c);
+    *reinterpret_cast<uint4*>(y + b * y_bs + static_cast<long long>(pad + t) * C + c) = v;
+  }
+}
+
 __global__ void counter_add_kernel(unsigned long long* c, unsigned long long inc) {
   if (threadIdx.x == 0 && blockIdx.x == 0) *c += inc;
 }
@@ -128,6 +146,18 @@ extern "C" int s2t_im2col1d(const void* xp, long long x_bs, void* xcol, int batc
   im2col1d_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(xp), x_bs, reinterpret_cast<__nv_bfloat16*>(xcol), batch,
       t_out, C, ksize, stride);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int s2t_frame_rows(const void* x, const int* lengths, void* y, long long y_bs, int pad, int batch,
+                              int T, int C, void* stream) {
+  S2T_REQUIRE(x && y, "s2t_frame_rows: null pointer");
+  S2T_REQUIRE(C % 8 == 0 && y_bs % 8 == 0 && pad >= 0, "s2t_frame_rows: bad shape");
+  const long long n = static_cast<long long>(batch) * T * (C / 8);
+  if (n <= 0) return 0;
+  frame_rows_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(reinterpret_cast<const __nv_bfloat16*>(x), lengths,
+                                                             reinterpret_cast<__nv_bfloat16*>(y), y_bs, pad, batch, T, C);
   S2T_LAUNCH_CHECK();
   return 0;
 }

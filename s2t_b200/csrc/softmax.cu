@@ -35,7 +35,7 @@ __device__ __forceinline__ float score_at(const RowCtx& c, int j) {
 __global__ void __launch_bounds__(kSmWarps * 32)
 attn_softmax_fwd_kernel(const __nv_bfloat16* __restrict__ scores, long long ld,
                         const __nv_bfloat16* __restrict__ bias, long long ld_bias, int bias_mode,
-                        __nv_bfloat16* __restrict__ probs, __nv_bfloat16* __restrict__ probs_drop,
+                        int bias_head_major, __nv_bfloat16* __restrict__ probs, __nv_bfloat16* __restrict__ probs_drop,
                         const int* __restrict__ klen, long long nrows, int heads, int Tq, int Tk,
                         float scale, float clamp, uint32_t thresh16, float inv_keep,
                         unsigned long long seed, uint32_t stream_id,
@@ -51,7 +51,11 @@ attn_softmax_fwd_kernel(const __nv_bfloat16* __restrict__ scores, long long ld,
   kl = kl < Tk ? kl : Tk;
   RowCtx c;
   c.srow = scores + row * ld;
-  c.brow = bias ? bias + row * ld_bias : nullptr;
+  // bias rows are ordered [batch][head][Tq] like the scores, or [head][batch][Tq] (bias_head_major: the
+  // layout that lets the linear_pos gradient contract over batch*time in one GEMM)
+  const long long brow_idx =
+      bias_head_major ? ((z % heads) * (nrows / Tq / heads) + b) * Tq + i : row;
+  c.brow = bias ? bias + brow_idx * ld_bias : nullptr;
   c.bias_mode = bias ? bias_mode : 0;
   c.shift = Tk - 1 - i;
   c.scale = scale;
@@ -96,7 +100,7 @@ attn_softmax_fwd_kernel(const __nv_bfloat16* __restrict__ scores, long long ld,
 __global__ void __launch_bounds__(kSmWarps * 32)
 attn_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ probs, const __nv_bfloat16* __restrict__ dpd,
                         __nv_bfloat16* __restrict__ dscores, __nv_bfloat16* __restrict__ dbias,
-                        long long ld_bias, const int* __restrict__ klen, long long nrows, int heads,
+                        long long ld_bias, int bias_head_major, const int* __restrict__ klen, long long nrows, int heads,
                         int Tq, int Tk, long long ld, float scale, uint32_t thresh16, float inv_keep,
                         unsigned long long seed, uint32_t stream_id,
                         const unsigned long long* __restrict__ seed_off) {
@@ -163,7 +167,9 @@ attn_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ probs, const __nv_bflo
   if (dbias != nullptr) {
     // un-shift: dBD[i][c] = dS[i][c + i - (Tk-1)] (zero outside), c in [0, 2Tk-1)
     __syncwarp();
-    __nv_bfloat16* brow = dbias + row * ld_bias;
+    const long long brow_idx =
+        bias_head_major ? ((z % heads) * (nrows / Tq / heads) + b) * Tq + i : row;
+    __nv_bfloat16* brow = dbias + brow_idx * ld_bias;
     const int shift = Tk - 1 - i;
     const int nb = 2 * Tk - 1;
     const int nb8 = (nb + 7) & ~7;
@@ -181,8 +187,8 @@ attn_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ probs, const __nv_bflo
 using namespace s2t;
 
 extern "C" int s2t_attn_softmax_fwd(const void* scores, long long ld, const void* bias,
-                                    long long ld_bias, int bias_mode, void* probs, void* probs_drop,
-                                    const int* klen, int nbh, int heads, int Tq, int Tk, float scale,
+                                    long long ld_bias, int bias_mode, int bias_head_major, void* probs,
+                                    void* probs_drop, const int* klen, int nbh, int heads, int Tq, int Tk, float scale,
                                     float clamp, float dropout_p, unsigned long long seed,
                                     unsigned int stream_id, const unsigned long long* seed_offset,
                                     void* stream) {
@@ -196,7 +202,7 @@ extern "C" int s2t_attn_softmax_fwd(const void* scores, long long ld, const void
   const unsigned grid = static_cast<unsigned>((nrows + kSmWarps - 1) / kSmWarps);
   attn_softmax_fwd_kernel<<<grid, kSmWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(scores), ld, reinterpret_cast<const __nv_bfloat16*>(bias),
-      ld_bias, bias_mode, reinterpret_cast<__nv_bfloat16*>(probs),
+      ld_bias, bias_mode, bias_head_major, reinterpret_cast<__nv_bfloat16*>(probs),
       reinterpret_cast<__nv_bfloat16*>(probs_drop), klen, nrows, heads, Tq, Tk, scale, clamp,
       dropout_p > 0.f ? static_cast<uint32_t>(dropout_p * 65536.f + 0.5f) : 0u,
       1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
@@ -205,7 +211,8 @@ extern "C" int s2t_attn_softmax_fwd(const void* scores, long long ld, const void
 }
 
 extern "C" int s2t_attn_softmax_bwd(const void* probs, const void* dprobs_drop, void* dscores,
-                                    void* dbias, long long ld_bias, const int* klen, int nbh,
+                                    void* dbias, long long ld_bias, int bias_head_major, const int* klen,
+                                    int nbh,
                                     int heads, int Tq, int Tk, long long ld, float scale,
                                     float dropout_p, unsigned long long seed, unsigned int stream_id,
                                     const unsigned long long* seed_offset, void* stream) {
@@ -218,7 +225,8 @@ extern "C" int s2t_attn_softmax_bwd(const void* probs, const void* dprobs_drop, 
   const unsigned grid = static_cast<unsigned>((nrows + kSmWarps - 1) / kSmWarps);
   attn_softmax_bwd_kernel<<<grid, kSmWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(probs), reinterpret_cast<const __nv_bfloat16*>(dprobs_drop),
-      reinterpret_cast<__nv_bfloat16*>(dscores), reinterpret_cast<__nv_bfloat16*>(dbias), ld_bias, klen,
+      reinterpret_cast<__nv_bfloat16*>(dscores), reinterpret_cast<__nv_bfloat16*>(dbias), ld_bias,
+      bias_head_major, klen,
       nrows, heads, Tq, Tk, ld, scale,
       dropout_p > 0.f ? static_cast<uint32_t>(dropout_p * 65536.f + 0.5f) : 0u,
       1.f / (1.f - dropout_p), seed, stream_id, seed_offset);

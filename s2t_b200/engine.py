@@ -11,28 +11,37 @@ One engine = one encoder (+ CTC head) resident on one GPU.  It owns
 
 Row layout: activations are [b*T + t][C] (utterance-major), bf16 storage, fp32 accumulation.
 
-Reference behaviour followed (file:line in the method docstrings): ``S2TTransformerEncoder.forward``
-(fairseq/models/speech_to_text/s2t_transformer.py:1714-2154), ``Conv1dSubsampling``
-(modules/speech_to_text/subsampling.py:106-159), ``S2TTransformerEncoderLayer``
-(modules/s2t_transformer_layer.py:229-322), ``MultiheadAttention`` (modules/multihead_attention.py),
-``CTC`` (modules/speech_to_text/ctc.py:17-66) and the ``ctc`` criterion arithmetic
-(criterions/ctc.py:435-474,516-540).
+Two encoder families share the layer code:
+  * ``encoder_type="s2t"`` — ``S2TTransformerEncoder`` (fairseq/models/speech_to_text/s2t_transformer.py:883,
+    forward :1714-2154): Conv1dSubsampling stem (modules/speech_to_text/subsampling.py:106-159), one stage of
+    Transformer / Conformer layers (modules/s2t_transformer_layer.py:229-322);
+  * ``encoder_type="pds"`` — ``PDSS2TTransformerEncoder`` (models/speech_to_text/pdss2t_transformer.py:1042-1281):
+    per stage a ``Downsampling`` Conv1d (+LayerNorm) stem (:53-144), positions, and ``PDSTransformerEncoderLayer``s
+    (modules/pds_layer.py:263-359).
+Attention is fairseq ``MultiheadAttention`` (modules/multihead_attention.py) or ESPnet
+``RelPositionMultiHeadedAttention`` (modules/espnet_multihead_attention.py:269-356); the conv module is
+modules/convolution.py:8-120; heads are ``CTC`` (modules/speech_to_text/ctc.py:17-66) with the ``ctc`` criterion
+arithmetic (criterions/ctc.py:435-474,516-540).
 """
 from __future__ import annotations
 
 import math
-from dataclasses import dataclass
-from typing import Dict, List, Optional, Tuple
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
 
 from . import frontend, ops
 from .params import BF16, ParamStore
 
+F32 = torch.float32
+
 
 @dataclass
 class EncoderConfig:
-    """The subset of the reference's args Namespace the path reads (s2t_transformer.py:2256-2405)."""
+    """The subset of the reference's args Namespace the path reads (s2t_transformer.py:2256-2405,
+    pdss2t_transformer.py:1361-1560)."""
+    encoder_type: str = "s2t"              # s2t | pds
     input_dim: int = 80
     embed_dim: int = 256
     ffn_dim: int = 2048
@@ -50,18 +59,29 @@ class EncoderConfig:
     cnn_module_kernel: int = 15
     cnn_module_norm: str = "batch_norm"
     encoder_activation_fn: str = "relu"    # FFN activation
-    activation_fn: str = "relu"            # conv-module activation (quirk A3)
+    activation_fn: str = "relu"            # conv-module activation of the S2T layer (quirk A3)
     layer_padding_mask: bool = False
     dropout: float = 0.1
     max_source_positions: int = 6000
     vocab: int = 10000                     # CTC head (source dictionary); 0 = none
     ctc_weight: float = 1.0
     blank: int = 0
+    # --- PDS (pdss2t_transformer.py:1361-1560; defaults = pdss2t_transformer_s_8) -------------------------
+    pds_layers: Tuple[int, ...] = (3, 3, 3, 3)
+    pds_ratios: Tuple[int, ...] = (2, 2, 1, 2)
+    pds_dims: Tuple[int, ...] = (256, 256, 256, 256)
+    pds_kernels: Tuple[int, ...] = (5, 5, 5, 5)
+    pds_ffn_ratios: Tuple[int, ...] = (8, 8, 8, 8)
+    pds_heads: Tuple[int, ...] = (4, 4, 4, 4)
+    pds_position_embed: Tuple[int, ...] = (1, 1, 1, 1)
+    pds_embed_norm: bool = True
+    pds_dropout: float = 0.0               # base_architecture default (pdss2t_transformer.py:1489)
 
     @staticmethod
-    def from_args(args, vocab: int) -> "EncoderConfig":
+    def from_args(args, vocab: int, family: str = "s2t") -> "EncoderConfig":
         g = lambda k, d=None: getattr(args, k, d)
-        return EncoderConfig(
+        ints = lambda s: tuple(int(v) for v in str(s).split("_"))
+        kw = dict(
             input_dim=g("input_feat_per_channel", 80) * g("input_channels", 1),
             embed_dim=args.encoder_embed_dim, ffn_dim=args.encoder_ffn_embed_dim,
             heads=args.encoder_attention_heads, layers=args.encoder_layers,
@@ -75,6 +95,14 @@ class EncoderConfig:
             layer_padding_mask=g("layer_padding_mask", False), dropout=args.dropout,
             max_source_positions=g("max_source_positions", 6000),
             vocab=vocab if g("ctc_weight", 0) > 0 else 0, ctc_weight=g("ctc_weight", 1.0) or 1.0)
+        if family == "pds":
+            n = int(args.pds_stages)
+            kw.update(encoder_type="pds", pds_layers=ints(args.pds_layers)[:n], pds_ratios=ints(args.pds_ratios)[:n],
+                      pds_dims=ints(args.pds_embed_dims)[:n], pds_kernels=ints(args.pds_kernel_sizes)[:n],
+                      pds_ffn_ratios=ints(args.pds_ffn_ratios)[:n], pds_heads=ints(args.pds_attn_heads)[:n],
+                      pds_position_embed=ints(g("pds_position_embed", "_".join(["1"] * n)))[:n],
+                      pds_embed_norm=g("pds_embed_norm", False), pds_dropout=g("pds_dropout", args.dropout))
+        return EncoderConfig(**kw)
 
 
 def sinusoidal_table(num_embeddings: int, dim: int, padding_idx: int = 1) -> torch.Tensor:
@@ -90,13 +118,91 @@ def sinusoidal_table(num_embeddings: int, dim: int, padding_idx: int = 1) -> tor
     return tab.contiguous()
 
 
+def rel_position_table(T: int, dim: int) -> torch.Tensor:
+    """RelPositionalEncoding (fairseq/modules/positional_encoding.py:104-166): the centre 2T-1 rows of the table,
+    row k <-> relative position T-1-k, interleaved sin/cos, div = exp(2i * -ln(1e4)/dim).  fp32 [2T-1, dim]."""
+    pos = torch.arange(0, T, dtype=torch.float32).unsqueeze(1)
+    div = torch.exp(torch.arange(0, dim, 2, dtype=torch.float32) * -(math.log(10000.0) / dim))
+    pe_pos, pe_neg = torch.zeros(T, dim), torch.zeros(T, dim)
+    pe_pos[:, 0::2], pe_pos[:, 1::2] = torch.sin(pos * div), torch.cos(pos * div)
+    pe_neg[:, 0::2], pe_neg[:, 1::2] = torch.sin(-pos * div), torch.cos(-pos * div)
+    return torch.cat([torch.flip(pe_pos, [0]), pe_neg[1:]], dim=0).contiguous()
+
+
 def _round8(n: int) -> int:
     return (n + 7) // 8 * 8
 
 
-class _LayerBufs:
-    """Saved activations of one encoder layer."""
-    __slots__ = ("ln1", "st1", "qkv", "probs", "probs_d", "ctx", "x1", "ln2", "st2", "f")
+_ACT = {"relu": ops.ACT_RELU, "swish": ops.ACT_SWISH}
+
+
+@dataclass
+class _LayerSpec:
+    """Static description of one encoder layer: parameter prefix, widths, owning stage, dropout-site base."""
+    prefix: str
+    stage: int
+    index: int          # position inside its stage
+    gidx: int           # global layer index
+    C: int
+    F: int
+    H: int
+    conv_act: int
+    p_drop: float
+    first: str = ""      # first parameter of the layer in the flat store
+
+    @property
+    def site(self) -> int:
+        return 64 * (self.gidx + 1)
+
+
+class _Bufs:
+    """Attribute bag for saved activations / scratch."""
+
+
+class _Stage(_Bufs):
+    """Buffers shared by the layers of one stage (same T, C): lengths, attention scratch, gradient scratch pool."""
+
+    def __init__(self, eng: "S2TEncoderEngine", B: int, T: int, C: int, F: int, H: int, n_layers: int, idx: int):
+        c, dev = eng.cfg, eng.device
+        z = lambda *s, dt=BF16: torch.zeros(s, device=dev, dtype=dt)
+        e = lambda *s, dt=BF16: torch.empty(s, device=dev, dtype=dt)
+        self.idx, self.B, self.T, self.C, self.F, self.H = idx, B, T, C, F, H
+        self.dk = C // H
+        R = self.R = B * T
+        self.ld = _round8(T)
+        self.lens = z(B, dt=torch.int32)
+        self.x = [e(R, C) for _ in range(n_layers + 1)]     # x[j] = input of layer j, x[-1] = stage output
+        self.scores = z(B * H, T, self.ld)
+        self.g_p, self.g_s = z(B * H, T, self.ld), z(B * H, T, self.ld)
+        self.pool = [e(R, C) for _ in range(6)]
+        self._pool_ids = {id(t) for t in self.pool}
+        self.g_f = e(R, F)
+        self.g_qkv = e(R, 3 * C)
+        lib = ops._lib.load()
+        cs = max(lib.s2t_colsum_workspace_floats(R, 3 * C), lib.s2t_colsum_workspace_floats(R, F))
+        self.colsum_ws = e(cs, dt=F32)
+        self.ln_part = e(lib.s2t_layernorm_bwd_partials(R, C), 2, C, dt=F32)
+        if c.attn_type == "rel_pos":
+            n_rel = 2 * T - 1
+            self.ldb = _round8(n_rel)
+            self.pos_emb = rel_position_table(T, C).to(dev).to(BF16)          # (2T-1, C), .to(x.dtype) in the reference
+            self.bd = z(H, B, T, self.ldb)                                      # head-major (see softmax.cu)
+            self.g_bd = z(H, B, T, self.ldb)
+            self.g_quv = e(R, 2 * C)
+            self.g_pp = e(n_rel, C)
+        if c.use_cnn_module:
+            self.g_2c = e(R, 2 * C)
+            self.bn_part = e(ops.dwconv1d_tiles(B, T), 2, C, dt=F32)
+            self.bn_bwd_part = e(ops.batchnorm_bwd_partials(R), 2, C, dt=F32)
+            self.dw_ws = e(ops.dwconv1d_tiles(B, T) * c.cnn_module_kernel * C, dt=F32)
+
+    def take(self) -> torch.Tensor:
+        return self.pool.pop()
+
+    def give(self, *bufs: torch.Tensor) -> None:
+        for t in bufs:
+            if t is not None and id(t) in self._pool_ids and all(t is not f for f in self.pool):
+                self.pool.append(t)
 
 
 class Plan:
@@ -107,75 +213,122 @@ class Plan:
         self.B, self.T, self.smax, self.wave_len = B, T, smax, wave_len
         z = lambda *s, dt=BF16: torch.zeros(s, device=dev, dtype=dt)
         e = lambda *s, dt=BF16: torch.empty(s, device=dev, dtype=dt)
-        k, st = c.subsampling_kernel, c.subsampling_stride
-        pad = (k - 1) // 2
-        self.pad = pad
         # --- static inputs --------------------------------------------------------------------
-        self.feats_in = z(B, T, c.input_dim, dt=torch.float32)
-        self.wave = z(B, wave_len, dt=torch.float32) if wave_len else None
+        self.feats_in = z(B, T, c.input_dim, dt=F32)
+        self.wave = z(B, wave_len, dt=F32) if wave_len else None
         self.num_samples = z(B, dt=torch.int32) if wave_len else None
-        self.fbank_raw = e(B, T, c.input_dim, dt=torch.float32) if wave_len else None
+        self.fbank_raw = e(B, T, c.input_dim, dt=F32) if wave_len else None
         self.src_len = z(B, dt=torch.int32)
         self.targets = z(B, max(smax, 1), dt=torch.int32)
         self.tgt_len = z(B, dt=torch.int32)
-        # --- subsampler: framed inputs (pad zero rows front/back), pre-GLU conv outputs --------------
-        self.t_sub = [T]
-        for _ in range(c.subsampling_layers):
-            self.t_sub.append((self.t_sub[-1] + 2 * pad - k) // st + 1)
-        chans = [c.input_dim] + [f // 2 for f in eng.sub_filters]
-        self.framed = [z(B, self.t_sub[i] + 2 * pad, chans[i]) for i in range(c.subsampling_layers)]
-        self.pre = [e(B * self.t_sub[i + 1], eng.sub_filters[i]) for i in range(c.subsampling_layers)]
-        self.sub_len = [z(B, dt=torch.int32) for _ in range(c.subsampling_layers)]
-        T2 = self.T2 = self.t_sub[-1]
-        R = self.R = B * T2
-        C, F, H = c.embed_dim, c.ffn_dim, c.heads
-        self.ld = _round8(T2)
-        self.x0 = e(R, C)
-        self.e_ln, self.e_st = e(R, C), e(R, 2, dt=torch.float32)
-        self.x = [e(R, C) for _ in range(c.layers + 1)]
-        self.layers: List[_LayerBufs] = []
         drop = c.dropout > 0
-        for _ in range(c.layers):
-            L = _LayerBufs()
-            L.ln1, L.st1 = e(R, C), e(R, 2, dt=torch.float32)
-            L.qkv = e(R, 3 * C)
-            L.probs = z(B * H, T2, self.ld)
-            L.probs_d = z(B * H, T2, self.ld) if drop else L.probs
-            L.ctx = e(R, C)
-            L.x1 = e(R, C)
-            L.ln2, L.st2 = e(R, C), e(R, 2, dt=torch.float32)
-            L.f = e(R, F)
+        self.stages: List[_Stage] = []
+        lib = ops._lib.load()
+        if c.encoder_type == "s2t":
+            k, st = c.subsampling_kernel, c.subsampling_stride
+            pad = self.pad = (k - 1) // 2
+            # Conv1dSubsampling stem: framed inputs (pad zero rows front/back), pre-GLU conv outputs
+            self.t_sub = [T]
+            for _ in range(c.subsampling_layers):
+                self.t_sub.append((self.t_sub[-1] + 2 * pad - k) // st + 1)
+            chans = [c.input_dim] + [f // 2 for f in eng.sub_filters]
+            n = c.subsampling_layers
+            self.framed = [z(B, self.t_sub[i] + 2 * pad, chans[i]) for i in range(n)]
+            self.pre = [e(B * self.t_sub[i + 1], eng.sub_filters[i]) for i in range(n)]
+            self.sub_len = [z(B, dt=torch.int32) for _ in range(n)]
+            self.g_pre = [e(B * self.t_sub[i + 1], eng.sub_filters[i]) for i in range(n)]
+            self.g_col = [e(B * self.t_sub[i + 1], k * chans[i]) for i in range(n)]
+            self.xcol = [e(B * self.t_sub[i + 1], k * chans[i]) for i in range(n)]
+            self.g_sub = [e(B, self.t_sub[i], chans[i]) for i in range(n)]
+            T2 = self.t_sub[-1]
+            St = _Stage(eng, B, T2, c.embed_dim, c.ffn_dim, c.heads, c.layers, 0)
+            St.lens = self.sub_len[-1]
+            self.stages.append(St)
+            self.x0 = e(St.R, c.embed_dim)
+            self.e_ln, self.e_st = e(St.R, c.embed_dim), e(St.R, 2, dt=F32)
+            cs = max(lib.s2t_colsum_workspace_floats(p.shape[0], p.shape[1]) for p in self.pre)
+            self.stem_colsum_ws = e(cs, dt=F32)
+        else:
+            # PDS: pad T to a multiple of prod(ratios) — a whole extra block when already a multiple (quirk A7)
+            mult = 1
+            for r in c.pds_ratios:
+                mult *= max(1, r)
+            self.T_pad = T + (mult - T % mult) if mult > 1 else T
+            t_in, cin = self.T_pad, c.input_dim
+            self.pds: List[_Bufs] = []
+            for i, (r, d, k) in enumerate(zip(c.pds_ratios, c.pds_dims, c.pds_kernels)):
+                pad = (k - 1) // 2
+                t_out = (t_in + 2 * pad - k) // r + 1
+                D = _Bufs()
+                D.t_in, D.t_out, D.cin, D.cout, D.k, D.stride, D.pad = t_in, t_out, cin, d, k, r, pad
+                D.framed = z(B, t_in + 2 * pad, cin)
+                D.conv = e(B * t_out, d)
+                D.ln, D.st = (e(B * t_out, d), e(B * t_out, 2, dt=F32)) if c.pds_embed_norm else (None, None)
+                D.in_len = z(B, dt=torch.int32)
+                D.xcol = e(B * t_out, k * cin)
+                D.g_col = e(B * t_out, k * cin)
+                D.colsum_ws = e(lib.s2t_colsum_workspace_floats(B * t_out, d), dt=F32)
+                self.pds.append(D)
+                self.stages.append(_Stage(eng, B, t_out, d, d * c.pds_ffn_ratios[i], c.pds_heads[i], c.pds_layers[i], i))
+                t_in, cin = t_out, d
+        last = self.stages[-1]
+        T2 = self.T2 = last.T
+        R = self.R = last.R
+        C = last.C
+        self.ld = last.ld
+        # --- per-layer saved activations ---------------------------------------------------------
+        self.layers: List[_Bufs] = []
+        for spec in eng.layer_specs:
+            St = self.stages[spec.stage]
+            Rs, Cs, Fs, Hs = St.R, St.C, St.F, St.H
+            L = _Bufs()
+            pdrop = spec.p_drop > 0
+            if c.macaron_style:
+                L.m_ln, L.m_st = e(Rs, Cs), e(Rs, 2, dt=F32)
+                L.m_f = e(Rs, Fs)
+                L.m_h = e(Rs, Fs) if c.encoder_activation_fn != "relu" else None
+                L.xa = e(Rs, Cs)
+            L.ln1, L.st1 = e(Rs, Cs), e(Rs, 2, dt=F32)
+            L.qkv = e(Rs, 3 * Cs)
+            L.probs = z(B * Hs, St.T, St.ld)
+            L.probs_d = z(B * Hs, St.T, St.ld) if pdrop else L.probs
+            L.ctx = e(Rs, Cs)
+            L.x1 = e(Rs, Cs)
+            if c.attn_type == "rel_pos":
+                L.quv = e(Rs, 2 * Cs)
+                L.pp = e(2 * St.T - 1, Cs)
+            if c.use_cnn_module:
+                L.c_ln, L.c_st = e(Rs, Cs), e(Rs, 2, dt=F32)
+                L.pw1 = e(Rs, 2 * Cs)
+                L.glu = e(Rs, Cs)
+                L.dw = e(Rs, Cs)
+                L.bn = e(Rs, Cs)
+                L.bn_save = e(2, Cs, dt=F32)
+                L.xc = e(Rs, Cs)
+                L.xd, L.f_st = e(Rs, Cs), e(Rs, 2, dt=F32)     # input / stats of final_norm
+            L.ln2, L.st2 = e(Rs, Cs), e(Rs, 2, dt=F32)
+            L.f = e(Rs, Fs)
+            L.h = e(Rs, Fs) if c.encoder_activation_fn != "relu" else None
             self.layers.append(L)
-        self.scores = z(B * H, T2, self.ld)
-        self.enc_out, self.enc_st = e(R, C), e(R, 2, dt=torch.float32)
+        self.enc_out, self.enc_st = e(R, C), e(R, 2, dt=F32)
         self.enc_drop = e(R, C) if drop else self.enc_out
         V = c.vocab
         self.ldv = _round8(max(V, 8))
         if V > 0:
             self.logits = z(R, self.ldv)
             self.dlogits = z(R, self.ldv)
-            self.lse = e(R, dt=torch.float32)
-            self.nll = z(B, dt=torch.float32)
-            self.loss = z(1, dt=torch.float32)
-            self.ctc_ws = e((ops.ctc_workspace_bytes(B, T2, max(smax, 1)) + 3) // 4, dt=torch.float32)
-        # --- backward scratch -----------------------------------------------------------------
-        self.g_a, self.g_b, self.g_c, self.g_d = e(R, C), e(R, C), e(R, C), e(R, C)
-        self.g_f = e(R, F)
-        self.g_qkv = e(R, 3 * C)
-        self.g_p = z(B * H, T2, self.ld)
-        self.g_s = z(B * H, T2, self.ld)
-        self.g_pre = [e(B * self.t_sub[i + 1], eng.sub_filters[i]) for i in range(c.subsampling_layers)]
-        self.g_col = [e(B * self.t_sub[i + 1], k * chans[i]) for i in range(c.subsampling_layers)]
-        self.xcol = [e(B * self.t_sub[i + 1], k * chans[i]) for i in range(c.subsampling_layers)]
-        self.g_sub = [e(B, self.t_sub[i], chans[i]) for i in range(c.subsampling_layers)]
-        lib = ops._lib.load()
-        cs = 0
-        for rows, cols in [(R, 3 * C), (R, F), (R, self.ldv)] + [(p.shape[0], p.shape[1]) for p in self.pre]:
-            cs = max(cs, lib.s2t_colsum_workspace_floats(rows, cols))
-        self.colsum_ws = e(cs, dt=torch.float32)
-        self.ln_part = e(lib.s2t_layernorm_bwd_partials(R, C), 2, C, dt=torch.float32)
+            self.lse = e(R, dt=F32)
+            self.nll = z(B, dt=F32)
+            self.loss = z(1, dt=F32)
+            self.ctc_ws = e((ops.ctc_workspace_bytes(B, T2, max(smax, 1)) + 3) // 4, dt=F32)
+            self.head_colsum_ws = e(lib.s2t_colsum_workspace_floats(R, self.ldv), dt=F32)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.graph_kind: Optional[str] = None
+
+    @property
+    def out_len(self) -> torch.Tensor:
+        """int32 [B] valid frames of the encoder output."""
+        return self.stages[-1].lens
 
 
 class S2TEncoderEngine:
@@ -185,49 +338,71 @@ class S2TEncoderEngine:
         if not torch.cuda.is_available():
             raise ops._lib.S2TLibraryError("S2TEncoderEngine needs a CUDA device (no CPU fallback)")
         ops._lib.load()
-        if cfg.attn_type != "selfattn" or cfg.macaron_style or cfg.use_cnn_module:
-            raise NotImplementedError("engine: rel_pos / macaron / conv-module blocks are not built yet")
-        if cfg.encoder_activation_fn != "relu":
-            raise NotImplementedError("engine: only the relu FFN is built")
+        if cfg.encoder_type not in ("s2t", "pds"):
+            raise NotImplementedError(f"engine: encoder_type {cfg.encoder_type!r}")
+        if cfg.attn_type not in ("selfattn", "rel_pos"):
+            raise NotImplementedError(f"engine: attention type {cfg.attn_type!r} is not built")
+        if cfg.encoder_activation_fn not in _ACT or cfg.activation_fn not in _ACT:
+            raise NotImplementedError("engine: activations are relu | swish")
+        if cfg.use_cnn_module and cfg.cnn_module_norm != "batch_norm":
+            raise NotImplementedError("engine: conv module norm is batch_norm")
         self.cfg = cfg
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         c = cfg
-        C = c.embed_dim
-        assert C % c.heads == 0 and (C // c.heads) % 8 == 0 and C % 8 == 0 and c.input_dim % 8 == 0
-        # Conv1dSubsampling filters: [filter]*(L-1) + [d], last one doubled for the GLU (subsampling.py:231-247,118-121)
-        filt = [c.subsampling_filter] * (c.subsampling_layers - 1) + [C]
-        self.sub_filters = [f if i < c.subsampling_layers - 1 else 2 * f for i, f in enumerate(filt)]
         S = self.store = ParamStore(self.device)
-        self.conv_names: List[str] = []
-        cin = c.input_dim
-        for i, cout in enumerate(self.sub_filters):
-            n = f"subsample.layers.{i}.0.weight"
-            S.declare(n, (cout, c.subsampling_kernel, cin))  # kernel layout [Cout][k][Cin]; reference is [Cout][Cin][k]
-            self.conv_names.append(n)
-            S.declare(f"subsample.layers.{i}.0.bias", (cout,))
-            cin = cout // 2
-        if c.encoder_embed_norm:
-            S.declare("embed_ln.weight", (C,)); S.declare("embed_ln.bias", (C,))
-        for l in range(c.layers):
-            p = f"layers.{l}."
-            S.declare(p + "self_attn_layer_norm.weight", (C,)); S.declare(p + "self_attn_layer_norm.bias", (C,))
-            S.declare(p + "self_attn.q_proj.weight", (C, C))
-            S.declare(p + "self_attn.k_proj.weight", (C, C), pack=True)
-            S.declare(p + "self_attn.v_proj.weight", (C, C), pack=True)
-            S.declare(p + "self_attn.q_proj.bias", (C,))
-            S.declare(p + "self_attn.k_proj.bias", (C,), pack=True)
-            S.declare(p + "self_attn.v_proj.bias", (C,), pack=True)
-            S.declare(p + "self_attn.out_proj.weight", (C, C)); S.declare(p + "self_attn.out_proj.bias", (C,))
-            S.declare(p + "ffn_norm.weight", (C,)); S.declare(p + "ffn_norm.bias", (C,))
-            S.declare(p + "ffn.w_1.weight", (c.ffn_dim, C)); S.declare(p + "ffn.w_1.bias", (c.ffn_dim,))
-            S.declare(p + "ffn.w_2.weight", (C, c.ffn_dim)); S.declare(p + "ffn.w_2.bias", (C,))
+        self.conv_names: List[str] = []          # Conv1d weights stored [Cout][k][Cin] (reference: [Cout][Cin][k])
+        self.ref_shapes: Dict[str, Tuple[int, ...]] = {}   # reference shape where it differs by a plain reshape
+        self.buffers: Dict[str, torch.Tensor] = {}         # BatchNorm running statistics (fp32 / int64)
+        self.layer_specs: List[_LayerSpec] = []
+        self.ffn_act = _ACT[c.encoder_activation_fn]
+        if c.encoder_type == "s2t":
+            C = c.embed_dim
+            assert C % c.heads == 0 and (C // c.heads) % 8 == 0 and C % 8 == 0 and c.input_dim % 8 == 0
+            # Conv1dSubsampling filters: [filter]*(L-1) + [d], last one doubled for the GLU (subsampling.py:231-247,118-121)
+            filt = [c.subsampling_filter] * (c.subsampling_layers - 1) + [C]
+            self.sub_filters = [f if i < c.subsampling_layers - 1 else 2 * f for i, f in enumerate(filt)]
+            cin = c.input_dim
+            for i, cout in enumerate(self.sub_filters):
+                n = f"subsample.layers.{i}.0.weight"
+                S.declare(n, (cout, c.subsampling_kernel, cin))
+                self.conv_names.append(n)
+                S.declare(f"subsample.layers.{i}.0.bias", (cout,))
+                cin = cout // 2
+            if c.encoder_embed_norm:
+                S.declare("embed_ln.weight", (C,)); S.declare("embed_ln.bias", (C,))
+            for l in range(c.layers):
+                # conv-module activation of S2TTransformerEncoderLayer = args.activation_fn (quirk A3)
+                spec = _LayerSpec(f"layers.{l}.", 0, l, l, C, c.ffn_dim, c.heads, _ACT[c.activation_fn], c.dropout)
+                self.layer_specs.append(spec)
+                self._declare_layer(spec)
+            self.out_dim = C
+        else:
+            cin, g = c.input_dim, 0
+            for i, (d, k) in enumerate(zip(c.pds_dims, c.pds_kernels)):
+                assert d % c.pds_heads[i] == 0 and (d // c.pds_heads[i]) % 8 == 0 and cin % 8 == 0
+                n = f"downsampling{i + 1}.conv.0.weight"
+                S.declare(n, (d, k, cin))
+                self.conv_names.append(n)
+                S.declare(f"downsampling{i + 1}.conv.0.bias", (d,))
+                if c.pds_embed_norm:
+                    S.declare(f"downsampling{i + 1}.norm.weight", (d,)); S.declare(f"downsampling{i + 1}.norm.bias", (d,))
+                for j in range(c.pds_layers[i]):
+                    # PDSTransformerEncoderLayer: conv-module activation = encoder_activation_fn (pds_layer.py:67,104)
+                    spec = _LayerSpec(f"stage{i + 1}.{j}.", i, j, g, d, d * c.pds_ffn_ratios[i], c.pds_heads[i],
+                                      _ACT[c.encoder_activation_fn], c.dropout)
+                    self.layer_specs.append(spec)
+                    self._declare_layer(spec)
+                    g += 1
+                cin = d
+            self.out_dim = c.pds_dims[-1]
+        C = self.out_dim
         S.declare("layer_norm.weight", (C,)); S.declare("layer_norm.bias", (C,))
         if c.vocab > 0:
             S.declare("ctc.ctc_projection.weight", (c.vocab, C))
             S.declare("ctc.ctc_projection.bias", (_round8(c.vocab),))  # padded to the logits' row stride
         S.finalize()
-        self.embed_scale = 1.0 if c.no_scale_embedding else math.sqrt(C)
-        self.pos_table = sinusoidal_table(c.max_source_positions + 2, C).to(self.device)
+        self.embed_scale = 1.0 if (c.no_scale_embedding or c.encoder_type == "pds") else math.sqrt(C)  # quirk A17
+        self.pos_tables: Dict[int, torch.Tensor] = {}
         self.step_counter = torch.zeros(1, device=self.device, dtype=torch.int64)
         self.plans: Dict[Tuple[int, int, int, int], Plan] = {}
         self.training = True
@@ -235,13 +410,64 @@ class S2TEncoderEngine:
         self.dp = None               # dp.BucketedAllReduce when data parallel
         self.init_parameters()
 
+    def _pos_table(self, dim: int) -> torch.Tensor:
+        if dim not in self.pos_tables:
+            self.pos_tables[dim] = sinusoidal_table(self.cfg.max_source_positions + 2, dim).to(self.device)
+        return self.pos_tables[dim]
+
+    @property
+    def pos_table(self) -> torch.Tensor:
+        return self._pos_table(self.out_dim)
+
+    def _declare_layer(self, sp: _LayerSpec) -> None:
+        """Parameters of one layer in forward order (names: SURVEY.md §8b)."""
+        c, S, p, C, F = self.cfg, self.store, sp.prefix, sp.C, sp.F
+        ln = lambda n: (S.declare(p + n + ".weight", (C,)), S.declare(p + n + ".bias", (C,)))
+        sp.first = p + ("macaron_norm" if c.macaron_style else "self_attn_layer_norm") + ".weight"
+        if c.macaron_style:
+            ln("macaron_norm")
+            S.declare(p + "macaron_ffn.w_1.weight", (F, C)); S.declare(p + "macaron_ffn.w_1.bias", (F,))
+            S.declare(p + "macaron_ffn.w_2.weight", (C, F)); S.declare(p + "macaron_ffn.w_2.bias", (C,))
+        ln("self_attn_layer_norm")
+        a = p + "self_attn."
+        q, k, v, o = ("linear_q", "linear_k", "linear_v", "linear_out") if c.attn_type == "rel_pos" else \
+                     ("q_proj", "k_proj", "v_proj", "out_proj")
+        S.declare(a + q + ".weight", (C, C))
+        S.declare(a + k + ".weight", (C, C), pack=True)
+        S.declare(a + v + ".weight", (C, C), pack=True)
+        S.declare(a + q + ".bias", (C,))
+        S.declare(a + k + ".bias", (C,), pack=True)
+        S.declare(a + v + ".bias", (C,), pack=True)
+        S.declare(a + o + ".weight", (C, C)); S.declare(a + o + ".bias", (C,))
+        if c.attn_type == "rel_pos":
+            S.declare(a + "linear_pos.weight", (C, C))
+            S.declare(a + "pos_bias_u", (C,)); S.declare(a + "pos_bias_v", (C,), pack=True)
+            self.ref_shapes[a + "pos_bias_u"] = self.ref_shapes[a + "pos_bias_v"] = (sp.H, C // sp.H)
+        if c.use_cnn_module:
+            K = c.cnn_module_kernel
+            ln("conv_norm")
+            m = p + "conv_module."
+            S.declare(m + "pointwise_conv1.weight", (2 * C, C)); self.ref_shapes[m + "pointwise_conv1.weight"] = (2 * C, C, 1)
+            S.declare(m + "depthwise_conv.weight", (C, K)); self.ref_shapes[m + "depthwise_conv.weight"] = (C, 1, K)
+            S.declare(m + "norm.weight", (C,)); S.declare(m + "norm.bias", (C,))
+            S.declare(m + "pointwise_conv2.weight", (C, C)); self.ref_shapes[m + "pointwise_conv2.weight"] = (C, C, 1)
+            self.buffers[m + "norm.running_mean"] = torch.zeros(C, device=self.device, dtype=F32)
+            self.buffers[m + "norm.running_var"] = torch.ones(C, device=self.device, dtype=F32)
+            self.buffers[m + "norm.num_batches_tracked"] = torch.zeros((), device=self.device, dtype=torch.int64)
+        ln("ffn_norm")
+        S.declare(p + "ffn.w_1.weight", (F, C)); S.declare(p + "ffn.w_1.bias", (F,))
+        S.declare(p + "ffn.w_2.weight", (C, F)); S.declare(p + "ffn.w_2.bias", (C,))
+        if c.use_cnn_module:
+            ln("final_norm")
+
     # ------------------------------------------------------------------------------------------
     # parameters
     # ------------------------------------------------------------------------------------------
     def init_parameters(self, seed: int = 0) -> None:
         """Reference initialisers: Conv1d / Linear default (kaiming-uniform a=sqrt(5) == U(+-1/sqrt(fan_in))),
-        xavier-uniform attention projections (multihead_attention.py:95-113, q/k/v gain 1/sqrt(2)), LayerNorm 1/0,
-        CTC projection N(0, C^-0.5) with zero bias (modules/speech_to_text/ctc.py:27-33)."""
+        xavier-uniform fairseq attention projections (multihead_attention.py:95-113, q/k/v gain 1/sqrt(2)) and
+        pos_bias_u/v (espnet_multihead_attention.py:284-288), LayerNorm / BatchNorm 1/0, CTC projection
+        N(0, C^-0.5) with zero bias (modules/speech_to_text/ctc.py:27-33)."""
         g = torch.Generator().manual_seed(seed)
         S = self.store
         for name in S.names():
@@ -251,7 +477,7 @@ class S2TEncoderEngine:
             elif name.endswith("norm.bias") or name == "embed_ln.bias":
                 t = torch.zeros(shape)
             elif name == "ctc.ctc_projection.weight":
-                t = torch.randn(shape, generator=g) * self.cfg.embed_dim ** -0.5
+                t = torch.randn(shape, generator=g) * shape[1] ** -0.5
             elif name == "ctc.ctc_projection.bias":
                 t = torch.zeros(shape)
             elif name.endswith("_proj.weight"):
@@ -260,6 +486,9 @@ class S2TEncoderEngine:
                 t = (torch.rand(shape, generator=g) * 2 - 1) * bound
             elif name.endswith("out_proj.bias"):
                 t = torch.zeros(shape)
+            elif name.endswith(("pos_bias_u", "pos_bias_v")):
+                h, dk = self.ref_shapes[name]
+                t = (torch.rand(shape, generator=g) * 2 - 1) * math.sqrt(6.0 / (h + dk))
             else:
                 if name.endswith("bias"):
                     w = S.shape(name[:-4] + "weight")
@@ -276,9 +505,13 @@ class S2TEncoderEngine:
         for name in S.names():
             if name not in sd:
                 raise KeyError(f"state_dict is missing {name}")
-            t = sd[name].detach().to(torch.float32)
+            t = sd[name].detach().to(F32)
             if name in self.conv_names:
                 t = t.permute(0, 2, 1).contiguous()               # [Cout][Cin][k] -> [Cout][k][Cin]
+            if name in self.ref_shapes:
+                if tuple(t.shape) != self.ref_shapes[name]:
+                    raise ValueError(f"{name}: shape {tuple(t.shape)} != {self.ref_shapes[name]}")
+                t = t.reshape(S.shape(name))
             if name == "ctc.ctc_projection.bias":
                 full = torch.zeros(S.shape(name))
                 full[: t.numel()] = t
@@ -286,6 +519,9 @@ class S2TEncoderEngine:
             if tuple(t.shape) != S.shape(name):
                 raise ValueError(f"{name}: shape {tuple(t.shape)} != {S.shape(name)}")
             S.p(name).copy_(t.to(BF16))
+        for name, buf in self.buffers.items():
+            if name in sd:
+                buf.copy_(sd[name].to(buf.dtype))
 
     def _export(self, grad: bool) -> Dict[str, torch.Tensor]:
         S = self.store
@@ -294,13 +530,18 @@ class S2TEncoderEngine:
             t = (S.g(name) if grad else S.p(name)).detach().float()
             if name in self.conv_names:
                 t = t.permute(0, 2, 1).contiguous()
+            if name in self.ref_shapes:
+                t = t.reshape(self.ref_shapes[name])
             if name == "ctc.ctc_projection.bias":
                 t = t[: self.cfg.vocab]
             out[name] = t
         return out
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
-        return self._export(False)
+        sd = self._export(False)
+        for name, buf in self.buffers.items():
+            sd[name] = buf.detach().clone()
+        return sd
 
     def grads(self) -> Dict[str, torch.Tensor]:
         """Gradients in the reference layout (fp32 copies)."""
@@ -325,22 +566,20 @@ class S2TEncoderEngine:
             self.plans[key] = Plan(self, B, T, smax, wave_len)
         return self.plans[key]
 
-    def _drop(self, site: int):
+    def _drop(self, site: int, p: Optional[float] = None):
         """Dropout spec of call site ``site`` (unique stream id per site; mask regenerable in backward)."""
-        p = self.cfg.dropout if self.training else 0.0
+        p = (self.cfg.dropout if p is None else p) if self.training else 0.0
         if p <= 0.0:
             return None
         return (p, self.SEED, site, self.step_counter)
 
     # ------------------------------------------------------------------------------------------
-    # forward
+    # forward: stems
     # ------------------------------------------------------------------------------------------
-    def _stage_inputs(self, P: Plan) -> None:
-        """Features (or waveform -> fbank -> utterance CMVN) into the zero-framed bf16 conv input, and the
-        length arithmetic of the subsampler (subsampling.py:155: len = (len - 1) // 2 + 1 per layer)."""
+    def _features(self, P: Plan, dst: torch.Tensor, pad: int) -> None:
+        """Features (or waveform -> fbank -> utterance CMVN) into a zero-framed bf16 conv input [B][T+2pad][D];
+        frames >= src_len zero filled (collater padding, speech_to_text_dataset.py:267-285)."""
         c = self.cfg
-        fr = P.framed[0]
-        dst_off = P.pad * c.input_dim
         if P.wave is not None:
             mel_w, rng, win = frontend._tables(str(self.device), c.input_dim)
             ops.fbank(P.wave, P.num_samples, mel_w, rng, win, P.T, out=P.fbank_raw)
@@ -348,23 +587,22 @@ class S2TEncoderEngine:
         else:
             src = P.feats_in
         cm = 1 if P.wave is not None else 0
-        # utterance CMVN (wave path) or a plain cast (feature path): fp32 -> bf16 into the framed buffer,
-        # frames >= src_len zero filled (collater padding, speech_to_text_dataset.py:267-285)
-        ops._call("s2t_cmvn_utt", ops._p(src), src.stride(1), src.stride(0), ops._p(fr) + 2 * dst_off, 1,
-                  fr.stride(1), fr.stride(0), ops._p(P.src_len), P.B, P.T, c.input_dim, cm, cm, ops._stream())
+        ops._call("s2t_cmvn_utt", ops._p(src), src.stride(1), src.stride(0), ops._p(dst) + 2 * pad * c.input_dim, 1,
+                  dst.stride(1), dst.stride(0), ops._p(P.src_len), P.B, P.T, c.input_dim, cm, cm, ops._stream())
+
+    def _stem_s2t_fwd(self, P: Plan) -> None:
+        """Conv1dSubsampling (subsampling.py:145-159): [Conv1d(k, stride, pad) -> GLU] per layer as an
+        implicit GEMM whose A rows overlap in the zero-framed channels-last input; lengths (len-1)//2+1 (:155);
+        the last GLU also applies the encoder's padding mask (s2t_transformer.py:1765).  Then the embed block:
+        embed_ln -> x * embed_scale (+ sinusoidal positions for abs attention) -> dropout (:1768-1794)."""
+        c, S = self.cfg, self.store
+        k, st, n = c.subsampling_kernel, c.subsampling_stride, c.subsampling_layers
+        self._features(P, P.framed[0], P.pad)
         ln = P.src_len
-        k, st = c.subsampling_kernel, c.subsampling_stride
-        for i in range(c.subsampling_layers):
+        for i in range(n):
             torch.div(ln + (2 * P.pad - k), st, rounding_mode="floor", out=P.sub_len[i])
             P.sub_len[i] += 1
             ln = P.sub_len[i]
-
-    def _subsample_fwd(self, P: Plan) -> None:
-        """Conv1dSubsampling (subsampling.py:145-159): [Conv1d(k, stride, pad) -> GLU] per layer as an
-        implicit GEMM whose A rows overlap in the zero-framed channels-last input; the last GLU also applies
-        the encoder's padding mask (s2t_transformer.py:1765)."""
-        c, S = self.cfg, self.store
-        k, st, n = c.subsampling_kernel, c.subsampling_stride, c.subsampling_layers
         for i in range(n):
             xin = P.framed[i]
             cin, cout, t_out = xin.shape[2], self.sub_filters[i], P.t_sub[i + 1]
@@ -377,58 +615,156 @@ class S2TEncoderEngine:
                 ops.glu_fwd(P.pre[i], out=nxt, T=t_out, ldy=cout // 2, y_bs=nxt.stride(0), y_off=P.pad * (cout // 2))
             else:
                 ops.glu_fwd(P.pre[i], out=P.x0, lengths=P.sub_len[i], T=t_out)
-
-    def _embed_fwd(self, P: Plan) -> None:
-        """embed_ln -> x * embed_scale + sinusoidal positions -> dropout (s2t_transformer.py:1768-1794)."""
-        c, S = self.cfg, self.store
+        St = P.stages[0]
         src = P.x0
         if c.encoder_embed_norm:
             ops.layernorm_fwd(P.x0, S.p("embed_ln.weight"), S.p("embed_ln.bias"), out=P.e_ln, stats=P.e_st)
             src = P.e_ln
         C = c.embed_dim
-        ops.embed_fwd(src.view(P.B, P.T2, C), P.sub_len[-1], self.pos_table, self.embed_scale,
-                      self._drop(1), out=P.x[0].view(P.B, P.T2, C))
+        table = self._pos_table(C) if c.attn_type == "selfattn" else None       # rel_pos: x is not modified (A5)
+        ops.embed_fwd(src.view(P.B, St.T, C), St.lens, table, self.embed_scale, self._drop(1),
+                      out=St.x[0].view(P.B, St.T, C))
 
-    def _layer_fwd(self, P: Plan, l: int) -> None:
-        """S2TTransformerEncoderLayer.forward, pre-norm (s2t_transformer_layer.py:267-317) with fairseq
-        MultiheadAttention (multihead_attention.py:246-265 projections, q * d_k^-0.5; :383-395 key padding;
-        fp32 softmax + dropout on the probabilities; :372-416 bmm + out_proj)."""
+    def _stem_pds_fwd(self, P: Plan, i: int) -> None:
+        """PDS stage stem (pdss2t_transformer.py:1088-1121): Downsampling = zero the padded input frames, Conv1d(k,
+        stride=ratio, pad) [+ LayerNorm], zero the padded output frames, lens = floor((len-1)/stride+1) (:53-144);
+        then += positions (abs) and dropout (stage 0: dropout, later stages: pds_dropout)."""
         c, S = self.cfg, self.store
-        L, x = P.layers[l], P.x[l]
-        B, T, C, H, F = P.B, P.T2, c.embed_dim, c.heads, c.ffn_dim
-        dk, ld = C // H, P.ld
-        p, site = f"layers.{l}.", 16 * (l + 1)
-        ops.layernorm_fwd(x, S.p(p + "self_attn_layer_norm.weight"), S.p(p + "self_attn_layer_norm.bias"),
+        D, St = P.pds[i], P.stages[i]
+        if i == 0:
+            self._features(P, D.framed, D.pad)
+            D.in_len.copy_(P.src_len)
+        else:
+            prev = P.stages[i - 1]
+            D.in_len.copy_(prev.lens)
+            ops.frame_rows(prev.x[-1].view(P.B, prev.T, prev.C), prev.lens, D.framed, D.pad)
+        torch.div(D.in_len - 1, D.stride, rounding_mode="floor", out=St.lens)
+        St.lens += 1
+        n = f"downsampling{i + 1}."
+        w = S.p(n + "conv.0.weight").view(D.cout, D.k * D.cin)
+        ops.gemm_raw(M=D.t_out, N=D.cout, K=D.k * D.cin, a=D.framed, lda=D.stride * D.cin,
+                     a_bs=(D.framed.stride(0), 0), b=w, ldb=D.k * D.cin, out=D.conv, ldc=D.cout,
+                     c_bs=(D.t_out * D.cout, 0), batch=(P.B, 1), bias=S.p(n + "conv.0.bias"))
+        src = D.conv
+        if c.pds_embed_norm:
+            ops.layernorm_fwd(D.conv, S.p(n + "norm.weight"), S.p(n + "norm.bias"), out=D.ln, stats=D.st)
+            src = D.ln
+        table = self._pos_table(D.cout) if (c.attn_type == "selfattn" and c.pds_position_embed[i]) else None
+        p = c.dropout if i == 0 else c.pds_dropout
+        ops.embed_fwd(src.view(P.B, St.T, St.C), St.lens, table, 1.0, self._drop(2 + i, p),
+                      out=St.x[0].view(P.B, St.T, St.C))
+
+    # ------------------------------------------------------------------------------------------
+    # forward: layer blocks
+    # ------------------------------------------------------------------------------------------
+    def _ffn_fwd(self, St: _Stage, x: torch.Tensor, out: torch.Tensor, ln: torch.Tensor, st: torch.Tensor,
+                 h: Optional[torch.Tensor], f: torch.Tensor, norm: str, ffn: str, scale: float, site: int) -> None:
+        """out = x + scale * dropout(w_2(dropout(act(w_1(LN(x))))))  (FeedForwardModule, s2t_transformer_layer.py:26-66;
+        scale 0.5 in macaron style, :270-276,303-309)."""
+        S = self.store
+        ops.layernorm_fwd(x, S.p(norm + ".weight"), S.p(norm + ".bias"), out=ln, stats=st)
+        if self.ffn_act == ops.ACT_RELU:
+            ops.linear(ln, S.p(ffn + ".w_1.weight"), S.p(ffn + ".w_1.bias"), out=f, act=ops.ACT_RELU,
+                       dropout=self._drop(site))
+        else:   # keep the pre-activation for the backward pass
+            ops.linear(ln, S.p(ffn + ".w_1.weight"), S.p(ffn + ".w_1.bias"), out=h)
+            ops.act_dropout(h, self.ffn_act, self._drop(site), out=f)
+        ops.linear(f, S.p(ffn + ".w_2.weight"), S.p(ffn + ".w_2.bias"), out=out, dropout=self._drop(site + 1),
+                   out_scale=scale, residual=x, ldr=St.C)
+
+    def _attn_fwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, x: torch.Tensor) -> None:
+        """x1 = x + dropout(attention(LN(x))).
+        selfattn: fairseq MultiheadAttention (multihead_attention.py:246-265 projections, q * d_k^-0.5; :383-395 key
+        padding; fp32 softmax + dropout on the probabilities; :372-416 bmm + out_proj).
+        rel_pos: RelPositionMultiHeadedAttention (espnet_multihead_attention.py:313-356): AC = (q+u) k^T,
+        BD = rel_shift((q+v) p^T), softmax((AC+BD)/sqrt(d_k)) with -inf key mask and the +-1e4 clamp (:119-129)."""
+        c, S = self.cfg, self.store
+        B, T, C, H, dk, ld = P.B, St.T, St.C, St.H, St.dk, St.ld
+        a = sp.prefix + "self_attn."
+        rel = c.attn_type == "rel_pos"
+        q, o = ("linear_q", "linear_out") if rel else ("q_proj", "out_proj")
+        ops.layernorm_fwd(x, S.p(sp.prefix + "self_attn_layer_norm.weight"), S.p(sp.prefix + "self_attn_layer_norm.bias"),
                           out=L.ln1, stats=L.st1)
-        ops.linear(L.ln1, S.fused(p + "self_attn.q_proj.weight", 3 * C, C), S.fused(p + "self_attn.q_proj.bias", 3 * C, 0),
-                   out=L.qkv)
-        # scores[b,h] = d_k^-0.5 * q k^T  (bf16, like the reference's bf16 bmm), softmax in fp32
-        ops.gemm_raw(M=T, N=T, K=dk, a=L.qkv, lda=3 * C, a_bs=(dk, T * 3 * C), b=L.qkv, ldb=3 * C, b_off=C,
-                     b_bs=(dk, T * 3 * C), out=P.scores, ldc=ld, c_bs=(T * ld, H * T * ld), batch=(H, B),
-                     alpha=dk ** -0.5)
-        dspec = self._drop(site + 0)
-        ops.attn_softmax_fwd(P.scores, P.sub_len[-1], H, T, probs=L.probs,
-                             probs_drop=L.probs_d if dspec else None, dropout=dspec)
+        ops.linear(L.ln1, S.fused(a + q + ".weight", 3 * C, C), S.fused(a + q + ".bias", 3 * C, 0), out=L.qkv)
+        bs_s = (T * ld, H * T * ld)
+        dspec = self._drop(sp.site + 0, sp.p_drop)
+        if not rel:
+            ops.gemm_raw(M=T, N=T, K=dk, a=L.qkv, lda=3 * C, a_bs=(dk, T * 3 * C), b=L.qkv, ldb=3 * C, b_off=C,
+                         b_bs=(dk, T * 3 * C), out=St.scores, ldc=ld, c_bs=bs_s, batch=(H, B), alpha=dk ** -0.5)
+            ops.attn_softmax_fwd(St.scores, St.lens, H, T, probs=L.probs, probs_drop=L.probs_d if dspec else None,
+                                 dropout=dspec)
+        else:
+            ops.relpos_qbias_fwd(L.qkv, S.p(a + "pos_bias_u"), S.p(a + "pos_bias_v"), C, out=L.quv)
+            ops.linear(St.pos_emb, S.p(a + "linear_pos.weight"), out=L.pp)
+            ops.gemm_raw(M=T, N=T, K=dk, a=L.quv, lda=2 * C, a_bs=(dk, T * 2 * C), b=L.qkv, ldb=3 * C, b_off=C,
+                         b_bs=(dk, T * 3 * C), out=St.scores, ldc=ld, c_bs=bs_s, batch=(H, B))
+            ops.gemm_raw(M=T, N=2 * T - 1, K=dk, a=L.quv, a_off=C, lda=2 * C, a_bs=(dk, T * 2 * C), b=L.pp, ldb=C,
+                         b_bs=(dk, 0), out=St.bd, ldc=St.ldb, c_bs=(B * T * St.ldb, T * St.ldb), batch=(H, B))
+            ops.attn_softmax_fwd(St.scores, St.lens, H, T, probs=L.probs, probs_drop=L.probs_d if dspec else None,
+                                 bias=St.bd.view(H * B, T, St.ldb), bias_mode=2, bias_head_major=True,
+                                 scale=dk ** -0.5, clamp=1e4, dropout=dspec)
         pd = L.probs_d if dspec else L.probs
-        ops.gemm_raw(M=T, N=dk, K=T, a=pd, lda=ld, a_bs=(T * ld, H * T * ld), b=L.qkv, ldb=3 * C, b_off=2 * C,
+        ops.gemm_raw(M=T, N=dk, K=T, a=pd, lda=ld, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=2 * C,
                      b_mn=True, b_bs=(dk, T * 3 * C), out=L.ctx, ldc=C, c_bs=(dk, T * C), batch=(H, B))
-        ops.linear(L.ctx, S.p(p + "self_attn.out_proj.weight"), S.p(p + "self_attn.out_proj.bias"), out=L.x1,
-                   dropout=self._drop(site + 1), residual=x, ldr=C)
-        ops.layernorm_fwd(L.x1, S.p(p + "ffn_norm.weight"), S.p(p + "ffn_norm.bias"), out=L.ln2, stats=L.st2)
-        ops.linear(L.ln2, S.p(p + "ffn.w_1.weight"), S.p(p + "ffn.w_1.bias"), out=L.f, act=ops.ACT_RELU,
-                   dropout=self._drop(site + 2))
-        ops.linear(L.f, S.p(p + "ffn.w_2.weight"), S.p(p + "ffn.w_2.bias"), out=P.x[l + 1],
-                   dropout=self._drop(site + 3), residual=L.x1, ldr=C)
+        ops.linear(L.ctx, S.p(a + o + ".weight"), S.p(a + o + ".bias"), out=L.x1,
+                   dropout=self._drop(sp.site + 1, sp.p_drop), residual=x, ldr=C)
+
+    def _conv_fwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, x: torch.Tensor, out: torch.Tensor) -> None:
+        """out = x + dropout(ConvolutionModule(LN(x)))  (convolution.py:76-120; s2t_transformer_layer.py:290-300):
+        zero padded frames, pointwise Conv1d(C,2C) + GLU, depthwise Conv1d(k), BatchNorm1d + activation,
+        pointwise Conv1d(C,C).  (Padded output rows are left unmasked: they only ever feed padded rows.)"""
+        S = self.store
+        p, m = sp.prefix, sp.prefix + "conv_module."
+        B, T, C = P.B, St.T, St.C
+        ops.layernorm_fwd(x, S.p(p + "conv_norm.weight"), S.p(p + "conv_norm.bias"), out=L.c_ln, stats=L.c_st)
+        ops.mask_rows_(L.c_ln.view(B, T, C), St.lens)
+        ops.linear(L.c_ln, S.p(m + "pointwise_conv1.weight"), out=L.pw1)
+        ops.glu_fwd(L.pw1, out=L.glu)
+        ops.dwconv1d_fwd(L.glu.view(B, T, C), S.p(m + "depthwise_conv.weight"), out=L.dw.view(B, T, C),
+                         bn_partials=St.bn_part if self.training else None)
+        bufs = self.buffers
+        ops.batchnorm_fwd(L.dw, S.p(m + "norm.weight"), S.p(m + "norm.bias"),
+                          partials=St.bn_part if self.training else None,
+                          running_mean=bufs[m + "norm.running_mean"], running_var=bufs[m + "norm.running_var"],
+                          num_batches_tracked=bufs[m + "norm.num_batches_tracked"], save_stats=L.bn_save, out=L.bn,
+                          act=sp.conv_act, training=self.training)
+        ops.linear(L.bn, S.p(m + "pointwise_conv2.weight"), out=out, dropout=self._drop(sp.site + 6, sp.p_drop),
+                   residual=x, ldr=C)
+
+    def _layer_fwd(self, P: Plan, g: int) -> None:
+        """S2TTransformerEncoderLayer.forward / PDSTransformerEncoderLayer.forward, pre-norm
+        (s2t_transformer_layer.py:267-317, pds_layer.py:263-359)."""
+        c = self.cfg
+        sp, L = self.layer_specs[g], P.layers[g]
+        St = P.stages[sp.stage]
+        x, y = St.x[sp.index], St.x[sp.index + 1]
+        p = sp.prefix
+        if c.layer_padding_mask and c.encoder_type == "s2t":
+            ops.mask_rows_(x.view(P.B, St.T, St.C), St.lens)                  # s2t_transformer.py:1828-1836
+        s = 0.5 if c.macaron_style else 1.0
+        if c.macaron_style:
+            self._ffn_fwd(St, x, L.xa, L.m_ln, L.m_st, L.m_h, L.m_f, p + "macaron_norm", p + "macaron_ffn", s, sp.site + 2)
+            x = L.xa
+        self._attn_fwd(P, St, sp, L, x)
+        x = L.x1
+        if c.use_cnn_module:
+            self._conv_fwd(P, St, sp, L, x, L.xc)
+            x = L.xc
+            self._ffn_fwd(St, x, L.xd, L.ln2, L.st2, L.h, L.f, p + "ffn_norm", p + "ffn", s, sp.site + 4)
+            S = self.store
+            ops.layernorm_fwd(L.xd, S.p(p + "final_norm.weight"), S.p(p + "final_norm.bias"), out=y, stats=L.f_st)
+        else:
+            self._ffn_fwd(St, x, y, L.ln2, L.st2, L.h, L.f, p + "ffn_norm", p + "ffn", s, sp.site + 4)
 
     def _head_fwd(self, P: Plan) -> None:
         """Final LayerNorm (s2t_transformer.py:2112) and the CTC head: dropout -> Linear(C, V)
         (modules/speech_to_text/ctc.py:55-66, quirk A11)."""
         c, S = self.cfg, self.store
-        ops.layernorm_fwd(P.x[c.layers], S.p("layer_norm.weight"), S.p("layer_norm.bias"), out=P.enc_out,
+        ops.layernorm_fwd(P.stages[-1].x[-1], S.p("layer_norm.weight"), S.p("layer_norm.bias"), out=P.enc_out,
                           stats=P.enc_st)
         if c.vocab <= 0:
             return
-        spec = self._drop(2)
+        spec = self._drop(60)
         src = P.enc_out
         if spec:
             ops.dropout(P.enc_out, spec, out=P.enc_drop)
@@ -436,11 +772,16 @@ class S2TEncoderEngine:
         ops.linear(src, S.p("ctc.ctc_projection.weight"), S.p("ctc.ctc_projection.bias"), out=P.logits)
 
     def _forward(self, P: Plan) -> None:
-        self._stage_inputs(P)
-        self._subsample_fwd(P)
-        self._embed_fwd(P)
-        for l in range(self.cfg.layers):
-            self._layer_fwd(P, l)
+        g = 0
+        for i, St in enumerate(P.stages):
+            if self.cfg.encoder_type == "s2t":
+                self._stem_s2t_fwd(P)
+            else:
+                self._stem_pds_fwd(P, i)
+            n = self.cfg.layers if self.cfg.encoder_type == "s2t" else self.cfg.pds_layers[i]
+            for _ in range(n):
+                self._layer_fwd(P, g)
+                g += 1
         self._head_fwd(P)
 
     def _loss(self, P: Plan, need_grad: bool) -> None:
@@ -449,7 +790,7 @@ class S2TEncoderEngine:
         c = self.cfg
         B, T, V = P.B, P.T2, c.vocab
         ops.row_lse(P.logits, V, out=P.lse)
-        ops.ctc_loss(P.logits.view(B, T, P.ldv), P.targets, P.sub_len[-1], P.tgt_len, V, c.blank,
+        ops.ctc_loss(P.logits.view(B, T, P.ldv), P.targets, P.out_len, P.tgt_len, V, c.blank,
                      need_grad=need_grad, grad_scale=c.ctc_weight, lse=P.lse,
                      dlogits=P.dlogits.view(B, T, P.ldv) if need_grad else None, workspace=P.ctc_ws, nll=P.nll)
         ops.f32_sum(P.nll, P.loss, c.ctc_weight)
@@ -470,90 +811,173 @@ class S2TEncoderEngine:
 
     def _head_bwd(self, P: Plan) -> torch.Tensor:
         c, S = self.cfg, self.store
-        src = P.enc_drop if self._drop(2) else P.enc_out
-        ops.colsum(P.dlogits, S.g("ctc.ctc_projection.bias"), workspace=P.colsum_ws)
+        St = P.stages[-1]
+        C = St.C
+        src = P.enc_drop if self._drop(60) else P.enc_out
+        ops.colsum(P.dlogits, S.g("ctc.ctc_projection.bias"), workspace=P.head_colsum_ws)
         ops.linear_wgrad(P.dlogits[:, : c.vocab] if c.vocab != P.ldv else P.dlogits, src,
                          out=S.g("ctc.ctc_projection.weight"))
-        ops.gemm_raw(M=P.R, N=c.embed_dim, K=c.vocab, a=P.dlogits, lda=P.ldv,
-                     b=S.p("ctc.ctc_projection.weight"), ldb=c.embed_dim, b_mn=True, out=P.g_a, ldc=c.embed_dim)
-        d = self._branch_grad(P.g_a, self._drop(2), 1.0, P.g_b)
+        t0, t1 = St.take(), St.take()
+        ops.gemm_raw(M=P.R, N=C, K=c.vocab, a=P.dlogits, lda=P.ldv,
+                     b=S.p("ctc.ctc_projection.weight"), ldb=C, b_mn=True, out=t0, ldc=C)
+        d = self._branch_grad(t0, self._drop(60), 1.0, t1)
         self._ready("ctc.ctc_projection.weight")
-        dx = P.g_c
-        ops.layernorm_bwd(d, P.x[c.layers], S.p("layer_norm.weight"), P.enc_st, S.g("layer_norm.weight"),
-                          S.g("layer_norm.bias"), out=dx, partials=P.ln_part)
+        dx = St.take()
+        ops.layernorm_bwd(d, St.x[-1], S.p("layer_norm.weight"), P.enc_st, S.g("layer_norm.weight"),
+                          S.g("layer_norm.bias"), out=dx, partials=St.ln_part)
+        St.give(t0, t1)
         self._ready("layer_norm.weight")
         return dx
 
-    def _layer_bwd(self, P: Plan, l: int, dy: torch.Tensor) -> torch.Tensor:
-        """Backward of _layer_fwd.  ``dy`` = dL/dx[l+1]; returns dL/dx[l] (in one of the g_* scratch buffers)."""
-        c, S = self.cfg, self.store
-        L, x = P.layers[l], P.x[l]
-        B, T, C, H, F = P.B, P.T2, c.embed_dim, c.heads, c.ffn_dim
-        dk, ld = C // H, P.ld
-        p, site = f"layers.{l}.", 16 * (l + 1)
-        free = [b for b in (P.g_a, P.g_b, P.g_c, P.g_d) if b is not dy]
-        t0, t1, t2 = free[0], free[1], free[2]
-        # ---- FFN: x2 = x1 + drop3(w_2 drop2(relu(w_1 LN(x1)))) ------------------------------------------
-        d2 = self._branch_grad(dy, self._drop(site + 3), 1.0, t0)
-        ops.colsum(d2, S.g(p + "ffn.w_2.bias"), workspace=P.colsum_ws)
-        ops.linear_wgrad(d2, L.f, out=S.g(p + "ffn.w_2.weight"))
-        ops.linear_dgrad(d2, S.p(p + "ffn.w_2.weight"), out=P.g_f, gate=L.f, gate_mode=ops.GATE_POSITIVE, ldg=F,
-                         dropout=self._drop(site + 2))
-        ops.colsum(P.g_f, S.g(p + "ffn.w_1.bias"), workspace=P.colsum_ws)
-        ops.linear_wgrad(P.g_f, L.ln2, out=S.g(p + "ffn.w_1.weight"))
-        ops.linear_dgrad(P.g_f, S.p(p + "ffn.w_1.weight"), out=t0)
-        dx1 = t1
-        ops.layernorm_bwd(t0, L.x1, S.p(p + "ffn_norm.weight"), L.st2, S.g(p + "ffn_norm.weight"),
-                          S.g(p + "ffn_norm.bias"), dx_residual=dy, out=dx1, partials=P.ln_part)
-        # ---- attention: x1 = x + drop1(out_proj(P_drop V)) ----------------------------------------------
-        do = self._branch_grad(dx1, self._drop(site + 1), 1.0, t0)
-        ops.colsum(do, S.g(p + "self_attn.out_proj.bias"), workspace=P.colsum_ws)
-        ops.linear_wgrad(do, L.ctx, out=S.g(p + "self_attn.out_proj.weight"))
-        dctx = t2
-        ops.linear_dgrad(do, S.p(p + "self_attn.out_proj.weight"), out=dctx)
-        dspec = self._drop(site + 0)
-        pd = L.probs_d if dspec else L.probs
-        bs_x, bs_qkv, bs_s = (dk, T * C), (dk, T * 3 * C), (T * ld, H * T * ld)
-        # dP_drop = dctx V^T
-        ops.gemm_raw(M=T, N=T, K=dk, a=dctx, lda=C, a_bs=bs_x, b=L.qkv, ldb=3 * C, b_off=2 * C, b_bs=bs_qkv,
-                     out=P.g_p, ldc=ld, c_bs=bs_s, batch=(H, B))
-        # dV = P_drop^T dctx
-        ops.gemm_raw(M=T, N=dk, K=T, a=pd, lda=ld, a_mn=True, a_bs=bs_s, b=dctx, ldb=C, b_mn=True, b_bs=bs_x,
-                     out=P.g_qkv, c_off=2 * C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B))
-        ops.attn_softmax_bwd(L.probs, P.g_p, P.sub_len[-1], H, T, out=P.g_s, dropout=dspec)
-        # dQ = s dS K ; dK = s dS^T Q
-        ops.gemm_raw(M=T, N=dk, K=T, a=P.g_s, lda=ld, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=C, b_mn=True,
-                     b_bs=bs_qkv, out=P.g_qkv, c_off=0, ldc=3 * C, c_bs=bs_qkv, batch=(H, B), alpha=dk ** -0.5)
-        ops.gemm_raw(M=T, N=dk, K=T, a=P.g_s, lda=ld, a_mn=True, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=0,
-                     b_mn=True, b_bs=bs_qkv, out=P.g_qkv, c_off=C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B),
-                     alpha=dk ** -0.5)
-        ops.colsum(P.g_qkv, S.fused(p + "self_attn.q_proj.bias", 3 * C, 0, grad=True), workspace=P.colsum_ws)
-        ops.linear_wgrad(P.g_qkv, L.ln1, out=S.fused(p + "self_attn.q_proj.weight", 3 * C, C, grad=True))
-        ops.linear_dgrad(P.g_qkv, S.fused(p + "self_attn.q_proj.weight", 3 * C, C), out=t0)
-        dx = t2
-        ops.layernorm_bwd(t0, x, S.p(p + "self_attn_layer_norm.weight"), L.st1,
-                          S.g(p + "self_attn_layer_norm.weight"), S.g(p + "self_attn_layer_norm.bias"),
-                          dx_residual=dx1, out=dx, partials=P.ln_part)
-        self._ready(p + "self_attn_layer_norm.weight")
+    def _ffn_bwd(self, St: _Stage, dy: torch.Tensor, x: torch.Tensor, ln: torch.Tensor, st: torch.Tensor,
+                 h: Optional[torch.Tensor], f: torch.Tensor, norm: str, ffn: str, scale: float, site: int) -> torch.Tensor:
+        """Backward of _ffn_fwd; consumes ``dy`` (gradient w.r.t. the block output), returns the gradient w.r.t. x."""
+        S = self.store
+        t0 = St.take()
+        d2 = self._branch_grad(dy, self._drop(site + 1), scale, t0)
+        ops.colsum(d2, S.g(ffn + ".w_2.bias"), workspace=St.colsum_ws)
+        ops.linear_wgrad(d2, f, out=S.g(ffn + ".w_2.weight"))
+        if self.ffn_act == ops.ACT_RELU:
+            ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=St.g_f, gate=f, gate_mode=ops.GATE_POSITIVE, ldg=St.F,
+                             dropout=self._drop(site))
+        else:
+            ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=St.g_f, gate=h, gate_mode=ops.GATE_SWISH_GRAD, ldg=St.F,
+                             dropout=self._drop(site))
+        ops.colsum(St.g_f, S.g(ffn + ".w_1.bias"), workspace=St.colsum_ws)
+        ops.linear_wgrad(St.g_f, ln, out=S.g(ffn + ".w_1.weight"))
+        ops.linear_dgrad(St.g_f, S.p(ffn + ".w_1.weight"), out=t0)
+        dx = St.take()
+        ops.layernorm_bwd(t0, x, S.p(norm + ".weight"), st, S.g(norm + ".weight"), S.g(norm + ".bias"),
+                          dx_residual=dy, out=dx, partials=St.ln_part)
+        St.give(t0, dy)
         return dx
 
-    def _embed_bwd(self, P: Plan, dy: torch.Tensor) -> torch.Tensor:
-        c, S = self.cfg, self.store
-        C = c.embed_dim
-        t = P.g_a if dy is not P.g_a else P.g_b
-        ops.embed_bwd(dy.view(P.B, P.T2, C), self.embed_scale, self._drop(1), out=t.view(P.B, P.T2, C))
-        if not c.encoder_embed_norm:
-            return t
-        o = P.g_c if dy is not P.g_c else P.g_d
-        ops.layernorm_bwd(t, P.x0, S.p("embed_ln.weight"), P.e_st, S.g("embed_ln.weight"), S.g("embed_ln.bias"),
-                          out=o, partials=P.ln_part)
-        self._ready("embed_ln.weight")
-        return o
+    def _conv_bwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+        S = self.store
+        p, m = sp.prefix, sp.prefix + "conv_module."
+        B, T, C = P.B, St.T, St.C
+        t0 = St.take()
+        d = self._branch_grad(dy, self._drop(sp.site + 6, sp.p_drop), 1.0, t0)
+        ops.linear_wgrad(d, L.bn, out=S.g(m + "pointwise_conv2.weight"))
+        t1 = St.take()
+        ops.linear_dgrad(d, S.p(m + "pointwise_conv2.weight"), out=t1)                     # d act(bn)
+        ops.batchnorm_bwd(t1, L.dw, L.bn_save, S.p(m + "norm.weight"), S.p(m + "norm.bias"), S.g(m + "norm.weight"),
+                          S.g(m + "norm.bias"), out=t0, partials=St.bn_bwd_part, act=sp.conv_act,
+                          training=self.training)                                            # d dw
+        ops.dwconv1d_bwd(L.glu.view(B, T, C), S.p(m + "depthwise_conv.weight"), t0.view(B, T, C),
+                         S.g(m + "depthwise_conv.weight"), out=t1.view(B, T, C), workspace=St.dw_ws)   # d glu
+        ops.glu_bwd(L.pw1, t1, out=St.g_2c)
+        ops.linear_wgrad(St.g_2c, L.c_ln, out=S.g(m + "pointwise_conv1.weight"))
+        ops.linear_dgrad(St.g_2c, S.p(m + "pointwise_conv1.weight"), out=t0)
+        ops.mask_rows_(t0.view(B, T, C), St.lens)
+        dx = t1
+        ops.layernorm_bwd(t0, x, S.p(p + "conv_norm.weight"), L.c_st, S.g(p + "conv_norm.weight"),
+                          S.g(p + "conv_norm.bias"), dx_residual=dy, out=dx, partials=St.ln_part)
+        St.give(t0, dy)
+        return dx
 
-    def _subsample_bwd(self, P: Plan, dy: torch.Tensor) -> None:
-        """Backward of Conv1dSubsampling: GLU', bias = column sums, weight = dY^T im2col(X), input = col2im(dY W)."""
+    def _attn_bwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
         c, S = self.cfg, self.store
+        B, T, C, H, dk, ld = P.B, St.T, St.C, St.H, St.dk, St.ld
+        a = sp.prefix + "self_attn."
+        rel = c.attn_type == "rel_pos"
+        q, o = ("linear_q", "linear_out") if rel else ("q_proj", "out_proj")
+        t0 = St.take()
+        do = self._branch_grad(dy, self._drop(sp.site + 1, sp.p_drop), 1.0, t0)
+        ops.colsum(do, S.g(a + o + ".bias"), workspace=St.colsum_ws)
+        ops.linear_wgrad(do, L.ctx, out=S.g(a + o + ".weight"))
+        dctx = St.take()
+        ops.linear_dgrad(do, S.p(a + o + ".weight"), out=dctx)
+        dspec = self._drop(sp.site + 0, sp.p_drop)
+        pd = L.probs_d if dspec else L.probs
+        bs_x, bs_qkv, bs_s = (dk, T * C), (dk, T * 3 * C), (T * ld, H * T * ld)
+        g_qkv = St.g_qkv
+        # dP_drop = dctx V^T ; dV = P_drop^T dctx
+        ops.gemm_raw(M=T, N=T, K=dk, a=dctx, lda=C, a_bs=bs_x, b=L.qkv, ldb=3 * C, b_off=2 * C, b_bs=bs_qkv,
+                     out=St.g_p, ldc=ld, c_bs=bs_s, batch=(H, B))
+        ops.gemm_raw(M=T, N=dk, K=T, a=pd, lda=ld, a_mn=True, a_bs=bs_s, b=dctx, ldb=C, b_mn=True, b_bs=bs_x,
+                     out=g_qkv, c_off=2 * C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B))
+        if not rel:
+            ops.attn_softmax_bwd(L.probs, St.g_p, St.lens, H, T, out=St.g_s, dropout=dspec)
+            # dQ = s dS K ; dK = s dS^T Q
+            ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=C, b_mn=True,
+                         b_bs=bs_qkv, out=g_qkv, c_off=0, ldc=3 * C, c_bs=bs_qkv, batch=(H, B), alpha=dk ** -0.5)
+            ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_mn=True, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=0,
+                         b_mn=True, b_bs=bs_qkv, out=g_qkv, c_off=C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B),
+                         alpha=dk ** -0.5)
+        else:
+            ldb, nrel = St.ldb, 2 * T - 1
+            bs_quv, bs_bd = (dk, T * 2 * C), (B * T * ldb, T * ldb)
+            ops.attn_softmax_bwd(L.probs, St.g_p, St.lens, H, T, out=St.g_s, dbias=St.g_bd.view(H * B, T, ldb),
+                                 bias_head_major=True, scale=dk ** -0.5, dropout=dspec)
+            # d(q+u) = dS K ; dK = dS^T (q+u)
+            ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=C, b_mn=True,
+                         b_bs=bs_qkv, out=St.g_quv, c_off=0, ldc=2 * C, c_bs=bs_quv, batch=(H, B))
+            ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_mn=True, a_bs=bs_s, b=L.quv, ldb=2 * C, b_off=0,
+                         b_mn=True, b_bs=bs_quv, out=g_qkv, c_off=C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B))
+            # d(q+v) = dBD p ; dp[h] = sum_b dBD[h,b]^T (q+v)[b,h]  (one GEMM per head over K = B*T: head-major dBD)
+            ops.gemm_raw(M=T, N=dk, K=nrel, a=St.g_bd, lda=ldb, a_bs=bs_bd, b=L.pp, ldb=C, b_mn=True, b_bs=(dk, 0),
+                         out=St.g_quv, c_off=C, ldc=2 * C, c_bs=bs_quv, batch=(H, B))
+            ops.gemm_raw(M=nrel, N=dk, K=B * T, a=St.g_bd, lda=ldb, a_mn=True, a_bs=(B * T * ldb, 0), b=L.quv,
+                         ldb=2 * C, b_off=C, b_mn=True, b_bs=(dk, 0), out=St.g_pp, ldc=C, c_bs=(dk, 0), batch=(H, 1))
+            ops.colsum(St.g_quv, S.fused(a + "pos_bias_u", 2 * C, 0, grad=True), workspace=St.colsum_ws)
+            ops.relpos_qbias_bwd(St.g_quv, g_qkv, C)
+            ops.linear_wgrad(St.g_pp, St.pos_emb, out=S.g(a + "linear_pos.weight"))
+        ops.colsum(g_qkv, S.fused(a + q + ".bias", 3 * C, 0, grad=True), workspace=St.colsum_ws)
+        ops.linear_wgrad(g_qkv, L.ln1, out=S.fused(a + q + ".weight", 3 * C, C, grad=True))
+        ops.linear_dgrad(g_qkv, S.fused(a + q + ".weight", 3 * C, C), out=t0)
+        dx = dctx
+        n = sp.prefix + "self_attn_layer_norm"
+        ops.layernorm_bwd(t0, x, S.p(n + ".weight"), L.st1, S.g(n + ".weight"), S.g(n + ".bias"),
+                          dx_residual=dy, out=dx, partials=St.ln_part)
+        St.give(t0, dy)
+        return dx
+
+    def _layer_bwd(self, P: Plan, g: int, dy: torch.Tensor) -> torch.Tensor:
+        """Backward of _layer_fwd.  ``dy`` = dL/d(layer output) in a pool buffer of the stage; returns dL/d(input)."""
+        c, S = self.cfg, self.store
+        sp, L = self.layer_specs[g], P.layers[g]
+        St = P.stages[sp.stage]
+        x_in = St.x[sp.index]
+        p = sp.prefix
+        s = 0.5 if c.macaron_style else 1.0
+        x_attn = L.xa if c.macaron_style else x_in
+        if c.use_cnn_module:
+            d = St.take()
+            ops.layernorm_bwd(dy, L.xd, S.p(p + "final_norm.weight"), L.f_st, S.g(p + "final_norm.weight"),
+                              S.g(p + "final_norm.bias"), out=d, partials=St.ln_part)
+            St.give(dy)
+            d = self._ffn_bwd(St, d, L.xc, L.ln2, L.st2, L.h, L.f, p + "ffn_norm", p + "ffn", s, sp.site + 4)
+            d = self._conv_bwd(P, St, sp, L, d, L.x1)
+        else:
+            d = self._ffn_bwd(St, dy, L.x1, L.ln2, L.st2, L.h, L.f, p + "ffn_norm", p + "ffn", s, sp.site + 4)
+        d = self._attn_bwd(P, St, sp, L, d, x_attn)
+        if c.macaron_style:
+            d = self._ffn_bwd(St, d, x_in, L.m_ln, L.m_st, L.m_h, L.m_f, p + "macaron_norm", p + "macaron_ffn", s,
+                              sp.site + 2)
+        if c.layer_padding_mask and c.encoder_type == "s2t":
+            ops.mask_rows_(d.view(P.B, St.T, St.C), St.lens)
+        self._ready(sp.first)
+        return d
+
+    def _stem_s2t_bwd(self, P: Plan, dy: torch.Tensor) -> None:
+        """Backward of the embed block and Conv1dSubsampling: GLU', bias = column sums, weight = dY^T im2col(X),
+        input = col2im(dY W)."""
+        c, S = self.cfg, self.store
+        St = P.stages[0]
+        C = c.embed_dim
+        t = St.take()
+        ops.embed_bwd(dy.view(P.B, St.T, C), self.embed_scale, self._drop(1), out=t.view(P.B, St.T, C))
+        St.give(dy)
+        if c.encoder_embed_norm:
+            o = St.take()
+            ops.layernorm_bwd(t, P.x0, S.p("embed_ln.weight"), P.e_st, S.g("embed_ln.weight"), S.g("embed_ln.bias"),
+                              out=o, partials=St.ln_part)
+            St.give(t)
+            self._ready("embed_ln.weight")
+            t = o
         k, st, n = c.subsampling_kernel, c.subsampling_stride, c.subsampling_layers
+        dy = t
         for i in reversed(range(n)):
             xin = P.framed[i]
             cin, cout, t_out = xin.shape[2], self.sub_filters[i], P.t_sub[i + 1]
@@ -561,7 +985,7 @@ class S2TEncoderEngine:
                 ops.glu_bwd(P.pre[i], dy, out=P.g_pre[i], lengths=P.sub_len[i], T=t_out)
             else:
                 ops.glu_bwd(P.pre[i], dy, out=P.g_pre[i])
-            ops.colsum(P.g_pre[i], S.g(f"subsample.layers.{i}.0.bias"), workspace=P.colsum_ws)
+            ops.colsum(P.g_pre[i], S.g(f"subsample.layers.{i}.0.bias"), workspace=P.stem_colsum_ws)
             ops.im2col1d(xin, xin.stride(0), P.B, t_out, cin, k, st, out=P.xcol[i])
             ops.linear_wgrad(P.g_pre[i], P.xcol[i], out=S.g(f"subsample.layers.{i}.0.weight").view(cout, k * cin))
             if i > 0:
@@ -569,13 +993,53 @@ class S2TEncoderEngine:
                 ops.col2im1d(P.g_col[i], P.B, P.t_sub[i], t_out, cin, k, st, P.pad, out=P.g_sub[i])
                 dy = P.g_sub[i].view(P.B * P.t_sub[i], cin)
             self._ready(f"subsample.layers.{i}.0.weight")
+        St.give(t)
+
+    def _stem_pds_bwd(self, P: Plan, i: int, dy: torch.Tensor) -> Optional[torch.Tensor]:
+        """Backward of _stem_pds_fwd; returns the gradient w.r.t. the previous stage's output (None for stage 0)."""
+        c, S = self.cfg, self.store
+        D, St = P.pds[i], P.stages[i]
+        n = f"downsampling{i + 1}."
+        t = St.take()
+        p = c.dropout if i == 0 else c.pds_dropout
+        ops.embed_bwd(dy.view(P.B, St.T, St.C), 1.0, self._drop(2 + i, p), out=t.view(P.B, St.T, St.C))
+        ops.mask_rows_(t.view(P.B, St.T, St.C), St.lens)           # the stem zeroes padded output frames (:136-142)
+        St.give(dy)
+        if c.pds_embed_norm:
+            o = St.take()
+            ops.layernorm_bwd(t, D.conv, S.p(n + "norm.weight"), D.st, S.g(n + "norm.weight"), S.g(n + "norm.bias"),
+                              out=o, partials=St.ln_part)
+            St.give(t)
+            t = o
+        ops.colsum(t, S.g(n + "conv.0.bias"), workspace=D.colsum_ws)
+        ops.im2col1d(D.framed, D.framed.stride(0), P.B, D.t_out, D.cin, D.k, D.stride, out=D.xcol)
+        w = S.p(n + "conv.0.weight").view(D.cout, D.k * D.cin)
+        ops.linear_wgrad(t, D.xcol, out=S.g(n + "conv.0.weight").view(D.cout, D.k * D.cin))
+        out = None
+        if i > 0:
+            prev = P.stages[i - 1]
+            ops.linear_dgrad(t, w, out=D.g_col)
+            out = prev.take()
+            g_in = out.view(P.B, D.t_in, D.cin)
+            ops.col2im1d(D.g_col, P.B, D.t_in, D.t_out, D.cin, D.k, D.stride, D.pad, out=g_in)
+            ops.mask_rows_(g_in, prev.lens)                         # the stem zeroes padded input frames (:107-116)
+        St.give(t)
+        self._ready(n + "conv.0.weight")
+        return out
 
     def _backward(self, P: Plan) -> None:
+        c = self.cfg
         d = self._head_bwd(P)
-        for l in reversed(range(self.cfg.layers)):
-            d = self._layer_bwd(P, l, d)
-        d = self._embed_bwd(P, d)
-        self._subsample_bwd(P, d)
+        g = len(self.layer_specs)
+        for i in reversed(range(len(P.stages))):
+            n = c.layers if c.encoder_type == "s2t" else c.pds_layers[i]
+            for _ in range(n):
+                g -= 1
+                d = self._layer_bwd(P, g, d)
+            if c.encoder_type == "s2t":
+                self._stem_s2t_bwd(P, d)
+            else:
+                d = self._stem_pds_bwd(P, i, d)
 
     # ------------------------------------------------------------------------------------------
     # public API
@@ -613,7 +1077,7 @@ class S2TEncoderEngine:
             P.tgt_len.copy_(target_lengths, non_blocking=nb)
 
     def forward(self, P: Plan) -> None:
-        """Encoder forward on the plan's inputs; results in P.enc_out [B*T', C], P.logits [B*T', ldv], P.sub_len[-1]."""
+        """Encoder forward on the plan's inputs; results in P.enc_out [B*T', C], P.logits [B*T', ldv], P.out_len."""
         self._forward(P)
 
     def train_step(self, P: Plan) -> None:
@@ -632,10 +1096,10 @@ class S2TEncoderEngine:
         backward pass reports progress (start of every layer / block in the flat gradient buffer)."""
         from .dp import BucketedAllReduce
         S = self.store
+        firsts = {sp.first for sp in self.layer_specs}
         cuts = [S.offset(n) for n in S.names()
-                if n.endswith("self_attn_layer_norm.weight") or n in ("layer_norm.weight", "ctc.ctc_projection.weight",
-                                                                      "embed_ln.weight")
-                or (n.startswith("subsample.") and n.endswith("weight"))]
+                if n in firsts or n in ("layer_norm.weight", "ctc.ctc_projection.weight", "embed_ln.weight")
+                or (n.startswith("subsample.") and n.endswith("weight")) or n.endswith("conv.0.weight")]
         self.dp = BucketedAllReduce(S.grad, cuts, n_buckets, group)
         self.grad_ready_hook = self.dp.on_ready
 
@@ -664,4 +1128,4 @@ class S2TEncoderEngine:
     def greedy_decode(self, P: Plan):
         """CTCDecoder greedy (s2t_ctc.py:312-347) on the plan's logits: int32 tokens [B, T'] (-1 padded), lengths."""
         c = self.cfg
-        return ops.ctc_greedy(P.logits.view(P.B, P.T2, P.ldv), P.sub_len[-1], c.vocab, c.blank)
+        return ops.ctc_greedy(P.logits.view(P.B, P.T2, P.ldv), P.out_len, c.vocab, c.blank)

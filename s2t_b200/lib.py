@@ -12,6 +12,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libs2t_b200.so"
 
 _vp, _i, _ll, _f, _ull, _u = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong, C.c_uint
 
+ABI_VERSION = 2
 ACT_NONE, ACT_RELU, ACT_SWISH = 0, 1, 2
 GATE_NONE, GATE_POSITIVE, GATE_SWISH_GRAD, GATE_MUL = 0, 1, 2, 3
 
@@ -57,6 +58,7 @@ SIGNATURES = {
     "s2t_embed_bwd": (_i, [_vp, _vp, _i, _i, _i, _f, _f, _ull, _u, _vp, _vp]),
     "s2t_dropout": (_i, [_vp, _vp, _ll, _f, _f, _ull, _u, _vp, _vp]),
     "s2t_im2col1d": (_i, [_vp, _ll, _vp, _i, _i, _i, _i, _i, _vp]),
+    "s2t_frame_rows": (_i, [_vp, _vp, _vp, _ll, _i, _i, _i, _i, _vp]),
     "s2t_counter_add": (_i, [_vp, _ull, _vp]),
     "s2t_add_bf16": (_i, [_vp, _vp, _ll, _vp]),
     "s2t_f32_sum": (_i, [_vp, _i, _f, _vp, _vp]),
@@ -64,8 +66,17 @@ SIGNATURES = {
     "s2t_permute_conv_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "s2t_cast_f32_to_bf16": (_i, [_vp, _vp, _ll, _vp]),
     "s2t_cast_bf16_to_f32": (_i, [_vp, _vp, _ll, _vp]),
-    "s2t_attn_softmax_fwd": (_i, [_vp, _ll, _vp, _ll, _i, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _f, _ull, _u, _vp, _vp]),
-    "s2t_attn_softmax_bwd": (_i, [_vp, _vp, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _ll, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_attn_softmax_fwd": (_i, [_vp, _ll, _vp, _ll, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_attn_softmax_bwd": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _vp, _i, _i, _i, _i, _ll, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_dwconv1d_tiles": (_ll, [_i, _i]),
+    "s2t_dwconv1d_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "s2t_dwconv1d_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "s2t_batchnorm_fwd": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _f, _i, _i, _vp]),
+    "s2t_batchnorm_bwd_partials": (_i, [_ll]),
+    "s2t_batchnorm_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _i, _vp]),
+    "s2t_relpos_qbias_fwd": (_i, [_vp, _ll, _vp, _vp, _vp, _ll, _i, _vp]),
+    "s2t_relpos_qbias_bwd": (_i, [_vp, _vp, _ll, _ll, _i, _vp]),
+    "s2t_act_dropout": (_i, [_vp, _vp, _ll, _i, _f, _ull, _u, _vp, _vp]),
     "s2t_row_lse": (_i, [_vp, _i, _ll, _i, _i, _vp, _vp]),
     "s2t_ctc_workspace_bytes": (_ll, [_i, _i, _i]),
     "s2t_ctc_loss": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _ll, _vp]),
@@ -95,7 +106,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.s2t_abi_version() != 1:
+    if lib.s2t_abi_version() != ABI_VERSION:
         raise S2TLibraryError("libs2t_b200.so ABI version mismatch")
     _lib = lib
     return lib

@@ -24,7 +24,8 @@ _LAUNCHES = {
     "s2t_colsum": 2, "s2t_col2im1d": 1, "s2t_embed_fwd": 1, "s2t_embed_bwd": 1, "s2t_mask_rows": 1,
     "s2t_permute_conv_weight": 1, "s2t_cast_f32_to_bf16": 1, "s2t_cast_bf16_to_f32": 1,
     "s2t_attn_softmax_fwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4,
-    "s2t_ctc_greedy": 2,
+    "s2t_ctc_greedy": 2, "s2t_dwconv1d_fwd": 1, "s2t_dwconv1d_bwd": 3, "s2t_batchnorm_fwd": 1,
+    "s2t_batchnorm_bwd": 2, "s2t_relpos_qbias_fwd": 1, "s2t_relpos_qbias_bwd": 1, "s2t_act_dropout": 1,
 }
 
 
@@ -325,6 +326,13 @@ def im2col1d(xp: torch.Tensor, x_bs: int, batch: int, t_out: int, Cd: int, ksize
     return out
 
 
+def frame_rows(x: torch.Tensor, lengths: Optional[torch.Tensor], framed: torch.Tensor, pad: int) -> torch.Tensor:
+    """x bf16 [B, T, C] -> framed [B, T + 2 pad, C] rows [pad, pad + T), frames >= lengths[b] zeroed."""
+    B, T, Cd = x.shape
+    _call("s2t_frame_rows", _p(x), _p(lengths), _p(framed), framed.stride(0), pad, B, T, Cd, _stream())
+    return framed
+
+
 def counter_add(counter: torch.Tensor, inc: int = 1) -> None:
     _call("s2t_counter_add", _p(counter), inc, _stream())
 
@@ -345,13 +353,15 @@ def f32_sum(x: torch.Tensor, out: torch.Tensor, scale: float = 1.0) -> torch.Ten
 def attn_softmax_fwd(scores: torch.Tensor, klen: Optional[torch.Tensor], heads: int, Tk: int, *,
                      probs: Optional[torch.Tensor] = None, probs_drop: Optional[torch.Tensor] = None,
                      bias: Optional[torch.Tensor] = None, bias_mode: int = 0, scale: float = 1.0,
-                     clamp: float = 0.0, dropout: Tuple[float, int, int] = (0.0, 0, 0)):
+                     clamp: float = 0.0, dropout: Tuple[float, int, int] = (0.0, 0, 0),
+                     bias_head_major: bool = False):
     """scores bf16 [nbh, Tq, ld]; returns (probs, probs_drop or None)."""
     nbh, Tq, ld = scores.shape
     if probs is None:
         probs = torch.empty_like(scores)
     ld_bias = bias.stride(1) if bias is not None else 0
-    _call("s2t_attn_softmax_fwd", _p(scores), ld, _p(bias), ld_bias, bias_mode, _p(probs), _p(probs_drop),
+    _call("s2t_attn_softmax_fwd", _p(scores), ld, _p(bias), ld_bias, bias_mode, int(bias_head_major), _p(probs),
+          _p(probs_drop),
           _p(klen), nbh, heads, Tq, Tk, scale, clamp, *_drop(dropout), _stream())
     return probs, probs_drop
 
@@ -359,13 +369,101 @@ def attn_softmax_fwd(scores: torch.Tensor, klen: Optional[torch.Tensor], heads: 
 def attn_softmax_bwd(probs: torch.Tensor, dprobs_drop: torch.Tensor, klen: Optional[torch.Tensor],
                      heads: int, Tk: int, *, out: Optional[torch.Tensor] = None,
                      dbias: Optional[torch.Tensor] = None, scale: float = 1.0,
-                     dropout: Tuple[float, int, int] = (0.0, 0, 0)) -> torch.Tensor:
+                     dropout: Tuple[float, int, int] = (0.0, 0, 0), bias_head_major: bool = False) -> torch.Tensor:
     nbh, Tq, ld = probs.shape
     if out is None:
         out = torch.empty_like(probs)
     ld_bias = dbias.stride(1) if dbias is not None else 0
-    _call("s2t_attn_softmax_bwd", _p(probs), _p(dprobs_drop), _p(out), _p(dbias), ld_bias, _p(klen), nbh,
+    _call("s2t_attn_softmax_bwd", _p(probs), _p(dprobs_drop), _p(out), _p(dbias), ld_bias, int(bias_head_major),
+          _p(klen), nbh,
           heads, Tq, Tk, ld, scale, *_drop(dropout), _stream())
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# Conformer convolution module, rel-pos query biases
+# --------------------------------------------------------------------------------------------------
+def dwconv1d_tiles(B: int, T: int) -> int:
+    return int(_lib.load().s2t_dwconv1d_tiles(B, T))
+
+
+def dwconv1d_fwd(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None,
+                 bn_partials: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x bf16 [B, T, C], w bf16 [C, K] -> depthwise conv along T (zero padded); bn_partials fp32 [tiles, 2, C]."""
+    B, T, Cd = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    _call("s2t_dwconv1d_fwd", _p(x), _p(w), _p(out), _p(bn_partials), B, T, Cd, w.shape[-1], _stream())
+    return out
+
+
+def dwconv1d_bwd(x: torch.Tensor, w: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor,
+                 out: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+    B, T, Cd = x.shape
+    K = w.shape[-1]
+    if out is None:
+        out = torch.empty_like(x)
+    need = dwconv1d_tiles(B, T) * K * Cd
+    if workspace is None or workspace.numel() < need:
+        workspace = torch.empty((need,), device=x.device, dtype=torch.float32)
+    _call("s2t_dwconv1d_bwd", _p(x), _p(w), _p(dy), _p(out), _p(dw), _p(workspace), B, T, Cd, K, _stream())
+    return out
+
+
+def batchnorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, *, partials: Optional[torch.Tensor],
+                  running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
+                  num_batches_tracked: Optional[torch.Tensor], save_stats: torch.Tensor,
+                  out: Optional[torch.Tensor] = None, eps: float = 1e-5, momentum: float = 0.1,
+                  act: int = ACT_NONE, training: bool = True) -> torch.Tensor:
+    """x bf16 [rows, C] -> act(BatchNorm1d(x)); partials fp32 [n, 2, C] from dwconv1d_fwd (training)."""
+    rows, Cd = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    _call("s2t_batchnorm_fwd", _p(x), _p(partials), partials.shape[0] if partials is not None else 0, _p(gamma),
+          _p(beta), _p(running_mean), _p(running_var), _p(num_batches_tracked), _p(save_stats), _p(out), rows, Cd,
+          eps, momentum, act, int(training), _stream())
+    return out
+
+
+def batchnorm_bwd_partials(rows: int) -> int:
+    return _lib.load().s2t_batchnorm_bwd_partials(rows)
+
+
+def batchnorm_bwd(da: torch.Tensor, x: torch.Tensor, save_stats: torch.Tensor, gamma: torch.Tensor,
+                  beta: torch.Tensor, dgamma: torch.Tensor, dbeta: torch.Tensor, *,
+                  out: Optional[torch.Tensor] = None, partials: Optional[torch.Tensor] = None,
+                  act: int = ACT_NONE, training: bool = True) -> torch.Tensor:
+    rows, Cd = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    need = batchnorm_bwd_partials(rows) * 2 * Cd
+    if partials is None or partials.numel() < need:
+        partials = torch.empty((need,), device=x.device, dtype=torch.float32)
+    _call("s2t_batchnorm_bwd", _p(da), _p(x), _p(save_stats), _p(gamma), _p(beta), _p(partials), _p(out),
+          _p(dgamma), _p(dbeta), rows, Cd, act, int(training), _stream())
+    return out
+
+
+def relpos_qbias_fwd(q: torch.Tensor, u: torch.Tensor, v: torch.Tensor, C: int,
+                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q = first C columns of a [rows, ld] tensor -> [rows, 2C] = (q + u | q + v)."""
+    rows = q.shape[0]
+    if out is None:
+        out = torch.empty((rows, 2 * C), device=q.device, dtype=BF16)
+    _call("s2t_relpos_qbias_fwd", _p(q), q.stride(0), _p(u), _p(v), _p(out), rows, C, _stream())
+    return out
+
+
+def relpos_qbias_bwd(dquv: torch.Tensor, dq: torch.Tensor, C: int) -> torch.Tensor:
+    _call("s2t_relpos_qbias_bwd", _p(dquv), _p(dq), dq.stride(0), dquv.shape[0], C, _stream())
+    return dq
+
+
+def act_dropout(x: torch.Tensor, act: int, spec, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if out is None:
+        out = torch.empty_like(x)
+    p, seed, sid, off = _drop(spec)
+    _call("s2t_act_dropout", _p(x), _p(out), x.numel(), act, p, seed, sid, off, _stream())
     return out
 
 
