@@ -52,6 +52,16 @@ class OracleConfig:
     share_inter_ctc: bool = True
     ctc_pae: str = "none"                # none | inter_league
     pae_unnorm_input: bool = False
+    # PDS (pdss2t_transformer.py:1361-1560)
+    pds_layers: Tuple[int, ...] = (3, 3, 3, 3)
+    pds_ratios: Tuple[int, ...] = (2, 2, 1, 2)
+    pds_dims: Tuple[int, ...] = (256, 256, 256, 256)
+    pds_kernels: Tuple[int, ...] = (5, 5, 5, 5)
+    pds_ffn_ratios: Tuple[int, ...] = (8, 8, 8, 8)
+    pds_heads: Tuple[int, ...] = (4, 4, 4, 4)
+    pds_position_embed: Tuple[int, ...] = (1, 1, 1, 1)
+    pds_embed_norm: bool = True
+    pds_dropout: float = 0.0
 
 
 def lengths_to_padding_mask(lens: torch.Tensor, max_len: Optional[int] = None) -> torch.Tensor:
@@ -342,6 +352,82 @@ class S2TTransformerEncoder(nn.Module):
         return out
 
 
+class Downsampling(nn.Module):
+    """fairseq/models/speech_to_text/pdss2t_transformer.py:53-144, reduced_way = "conv"."""
+
+    def __init__(self, embed_norm, cin, cout, kernel, stride):
+        super().__init__()
+        self.stride = stride
+        self.conv = nn.Sequential(nn.Conv1d(cin, cout, kernel, stride=stride, padding=(kernel - 1) // 2))
+        self.embed_norm = embed_norm
+        if embed_norm:
+            self.norm = nn.LayerNorm(cout)
+
+    def forward(self, x, lengths):                              # x (T,B,C)
+        T = x.size(0)
+        assert T % self.stride == 0
+        x = x.masked_fill(lengths_to_padding_mask(lengths, T).transpose(0, 1).unsqueeze(2), 0.0)       # :107-116
+        lengths = ((lengths.float() - 1) / self.stride + 1).floor().long()                             # :121
+        x = self.conv(x.permute(1, 2, 0)).permute(2, 0, 1)
+        if self.embed_norm:
+            x = self.norm(x)
+        x = x.masked_fill(lengths_to_padding_mask(lengths, x.size(0)).transpose(0, 1).unsqueeze(2), 0.0)  # :136-142 (A8)
+        return x, lengths
+
+
+class PDSS2TTransformerEncoder(nn.Module):
+    """fairseq/models/speech_to_text/pdss2t_transformer.py:226 (forward :1042-1281) for the options of config C3:
+    conv down-sampling per stage, absolute or relative positions per stage, pre-norm layers, no fusion, final
+    LayerNorm, CTC head on top.  embed_scale is computed but never applied (quirk A17)."""
+
+    def __init__(self, cfg: OracleConfig):
+        super().__init__()
+        self.cfg = cfg
+        self.n = len(cfg.pds_dims)
+        cin = cfg.input_dim
+        for i in range(self.n):
+            d = cfg.pds_dims[i]
+            setattr(self, f"downsampling{i + 1}", Downsampling(cfg.pds_embed_norm, cin, d, cfg.pds_kernels[i], cfg.pds_ratios[i]))
+            from dataclasses import replace
+            lcfg = replace(cfg, embed_dim=d, ffn_dim=d * cfg.pds_ffn_ratios[i], heads=cfg.pds_heads[i],
+                           activation_fn=cfg.encoder_activation_fn)           # pds_layer.py:67,104 (quirk A3)
+            setattr(self, f"stage{i + 1}", nn.ModuleList([EncoderLayer(lcfg) for _ in range(cfg.pds_layers[i])]))
+            cin = d
+        self.layer_norm = nn.LayerNorm(cfg.pds_dims[-1])
+        if cfg.vocab > 0:
+            self.ctc = CTC(cfg.pds_dims[-1], cfg.vocab, cfg.dropout)
+
+    def forward(self, src_tokens, src_lengths):
+        cfg = self.cfg
+        x = src_tokens.transpose(0, 1)
+        lens = src_lengths
+        mult = 1
+        for r in cfg.pds_ratios:
+            mult *= max(1, r)
+        pad_to = mult - x.size(0) % mult                                      # :1050-1055 (quirk A7)
+        if mult > 1 and pad_to > 0:
+            x = torch.cat([x, x.new_zeros((pad_to, x.size(1), x.size(2)))], dim=0)
+        for i in range(self.n):
+            x, lens = getattr(self, f"downsampling{i + 1}")(x, lens)
+            pad = lengths_to_padding_mask(lens, x.size(0))
+            positions = None
+            if cfg.pds_position_embed[i]:
+                if cfg.attn_type == "rel_pos":
+                    positions = rel_positional_encoding(x.size(0), cfg.pds_dims[i]).to(x.dtype)
+                else:
+                    x = x + abs_positions(pad, cfg.pds_dims[i]).transpose(0, 1).to(x.dtype)
+            x = F.dropout(x, cfg.dropout if i == 0 else cfg.pds_dropout, self.training)          # :1118-1121
+            for layer in getattr(self, f"stage{i + 1}"):
+                x = layer(x, pad, pos_emb=positions)
+        x = self.layer_norm(x)
+        out = {"encoder_out": [x], "ctc_logit": [], "xctc_logit": [], "inter_ctc_logits": [],
+               "inter_xctc_logits": [], "encoder_padding_mask": [pad], "mixup": None,
+               "encoder_embedding": [], "encoder_states": [], "src_tokens": [], "src_lengths": []}
+        if cfg.vocab > 0:
+            out["ctc_logit"] = [self.ctc(x)]
+        return out
+
+
 def ctc_criterion_loss(logit_tbv: torch.Tensor, padding_mask: torch.Tensor, tokens: torch.Tensor,
                        pad: int = 1, eos: int = 2, blank: int = 0) -> torch.Tensor:
     """CtcCriterion arithmetic (fairseq/criterions/ctc.py): input_lengths :556, targets :516-540,
@@ -363,7 +449,7 @@ def config_from_args(args) -> OracleConfig:
     split = lambda s: tuple(int(v) for v in str(s).split(",")) if s else ()
     return OracleConfig(
         input_dim=g("input_feat_per_channel", 80) * g("input_channels", 1), embed_dim=args.encoder_embed_dim,
-        ffn_dim=args.encoder_ffn_embed_dim, heads=args.encoder_attention_heads, layers=args.encoder_layers,
+        ffn_dim=args.encoder_ffn_embed_dim, heads=args.encoder_attention_heads, layers=g("encoder_layers", 12),
         subsampling_layers=g("subsampling_layers", 2), subsampling_filter=g("subsampling_filter", 1024),
         subsampling_kernel=g("subsampling_kernel", 5), subsampling_stride=g("subsampling_stride", 2),
         attn_type=g("encoder_attention_type", "selfattn"), encoder_embed_norm=g("encoder_embed_norm", False),
@@ -376,4 +462,16 @@ def config_from_args(args) -> OracleConfig:
         tgt_vocab=g("_tgt_vocab", 0) if g("xctc_weight", 0) > 0 else 0,
         inter_ctc_layers=split(g("inter_ctc_layers")), inter_xctc_layers=split(g("inter_xctc_layers")),
         share_inter_ctc=g("share_inter_ctc", False), ctc_pae=g("ctc_pae", "none"),
-        pae_unnorm_input=g("pae_unnorm_input", False))
+        pae_unnorm_input=g("pae_unnorm_input", False), **_pds_from_args(args))
+
+
+def _pds_from_args(args) -> dict:
+    if getattr(args, "pds_stages", None) is None:
+        return {}
+    n = int(args.pds_stages)
+    ints = lambda k, d=None: tuple(int(v) for v in str(getattr(args, k, d)).split("_"))[:n]
+    return dict(pds_layers=ints("pds_layers"), pds_ratios=ints("pds_ratios"), pds_dims=ints("pds_embed_dims"),
+                pds_kernels=ints("pds_kernel_sizes"), pds_ffn_ratios=ints("pds_ffn_ratios"),
+                pds_heads=ints("pds_attn_heads"), pds_position_embed=ints("pds_position_embed", "_".join(["1"] * n)),
+                pds_embed_norm=getattr(args, "pds_embed_norm", False),
+                pds_dropout=getattr(args, "pds_dropout", args.dropout))

@@ -37,6 +37,12 @@ ENC_CASES = {
                      macaron_style=True, use_cnn_module=True, cnn_module_kernel=15,
                      encoder_attention_type="rel_pos", encoder_activation_fn="swish",
                      layer_padding_mask=True),
+    # C3 in miniature: pdss2t_transformer_s_8 structure (4 stages, ratios 2_2_1_2, conv down-sampling + LayerNorm,
+    # abs positions per stage, relu FFN), one layer per stage
+    "c3_small": dict(family="pds", pds_stages=4, pds_layers="1_1_1_1", pds_ratios="2_2_1_2", pds_fusion=False,
+                     pds_embed_dims="256_256_256_256", pds_kernel_sizes="5_5_5_5", pds_ffn_ratios="2_2_2_2",
+                     pds_attn_heads="4_4_4_4", pds_position_embed="1_1_1_1", pds_embed_norm=True,
+                     pds_ds_method="conv", pds_attn_ds_ratios="1_1_1_1", vocab=200, B=3, T=83, S=5),
 }
 
 
@@ -46,7 +52,7 @@ def reference_args(**over) -> Namespace:
                   encoder_embed_norm=True, encoder_no_scale_embedding=True, ctc_weight=0.3,
                   dropout=0.0, fp16=False, activation_fn="relu")
     vocab = over.pop("vocab", 10000)
-    for k in ("B", "T", "S"):
+    for k in ("B", "T", "S", "family"):
         over.pop(k, None)
     for k, v in over.items():
         setattr(a, k, v)
@@ -104,7 +110,9 @@ def synth_batch(B: int, T: int, S: int, vocab: int, seed: int):
     return feats, lens, tokens
 
 
-GRAD_KEYS = ["subsample.layers.0.0.weight", "subsample.layers.1.0.bias", "embed_ln.weight",
+GRAD_KEYS = ["downsampling1.conv.0.weight", "downsampling3.conv.0.bias", "downsampling2.norm.weight",
+             "stage1.0.ffn.w_1.weight", "stage4.0.self_attn.q_proj.weight", "stage2.0.self_attn_layer_norm.bias",
+             "subsample.layers.0.0.weight", "subsample.layers.1.0.bias", "embed_ln.weight",
              "layers.0.ffn.w_1.weight", "layers.1.ffn.w_2.bias", "layers.0.self_attn_layer_norm.bias",
              "layer_norm.weight", "ctc.ctc_projection.weight"]
 
@@ -115,11 +123,16 @@ def run_reference_encoder(case: str, seed: int = 0):
     ref = ref_shim.load()
     spec = dict(ENC_CASES[case])
     B, T, S, vocab = spec["B"], spec["T"], spec["S"], spec["vocab"]
+    family = spec.get("family", "s2t")
     args = reference_args(**spec)
-    ref.s2t.s2t_transformer_s(args)                         # arch defaults, s2t_transformer.py:2408-2415
     task = ref.FakeTask(vocab, vocab)
     torch.manual_seed(seed)
-    enc = ref.s2t.S2TTransformerEncoder(args, task, None)
+    if family == "pds":
+        ref.pds.pdss2t_transformer_s_8(args)                # arch defaults, pdss2t_transformer.py:1562
+        enc = ref.pds.PDSS2TTransformerEncoder(args, task, None)
+    else:
+        ref.s2t.s2t_transformer_s(args)                     # arch defaults, s2t_transformer.py:2408-2415
+        enc = ref.s2t.S2TTransformerEncoder(args, task, None)
     shapes = {k: v.shape for k, v in enc.state_dict().items() if not k.endswith("_float_tensor")}
     sd = seeded_state_dict(shapes, seed)
     missing = enc.load_state_dict(sd, strict=False)
@@ -136,7 +149,7 @@ def run_reference_encoder(case: str, seed: int = 0):
 
     # ---- validate the restatement against the reference on the spot --------------------------------
     cfg = OE.config_from_args(args)
-    orc = OE.S2TTransformerEncoder(cfg)
+    orc = OE.PDSS2TTransformerEncoder(cfg) if family == "pds" else OE.S2TTransformerEncoder(cfg)
     o_keys, r_keys = set(orc.state_dict().keys()), set(shapes.keys())
     assert o_keys == r_keys, (sorted(o_keys - r_keys)[:5], sorted(r_keys - o_keys)[:5])
     orc.load_state_dict(sd)

@@ -81,7 +81,7 @@ def test_greedy_oracle_pad_to_blank_before_collapse():
     assert [t.tolist() for t in toks] == [[5, 6], [7]]
 
 
-@pytest.mark.parametrize("case", ["c1_small", "c4_small"])
+@pytest.mark.parametrize("case", ["c1_small", "c4_small", "c3_small"])
 def test_encoder_oracle_matches_reference_golden(case):
     """oracle/encoder.py reproduces the reference's S2TTransformerEncoder + ctc criterion outputs and gradients."""
     from oracle import encoder as OE
@@ -96,7 +96,8 @@ def test_encoder_oracle_matches_reference_golden(case):
                      subsampling_layers=2, subsampling_filter=1024, subsampling_kernel=5, subsampling_stride=2).items():
         if not hasattr(args, k):
             setattr(args, k, v)
-    orc = OE.S2TTransformerEncoder(OE.config_from_args(args))
+    cls = OE.PDSS2TTransformerEncoder if spec.get("family") == "pds" else OE.S2TTransformerEncoder
+    orc = cls(OE.config_from_args(args))
     orc.load_state_dict(sd)
     orc.train()
     feats, lens, tokens = (torch.from_numpy(fx[k]) for k in ("feats", "lens", "tokens"))
