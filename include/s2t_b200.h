@@ -198,6 +198,9 @@ int s2t_counter_add(unsigned long long* counter, unsigned long long inc, void* s
 int s2t_add_bf16(const void* x, void* y, long long n, void* stream);
 /* out[0] = scale * sum_i x[i]  (per-utterance NLL -> batch loss, criterions/ctc.py:473)            */
 int s2t_f32_sum(const float* x, int n, float scale, float* out, void* stream);
+/* out[0] = sum_r w[r] * sum_c x[r][c]: the weighted sum of the per-utterance NLLs of every loss term
+ * (ctc_w*ctc + xctc_w*xctc + inter_ctc_w*mean(inter) + ..., criterions/ctc.py:1004-1015)           */
+int s2t_f32_weighted_sum(const float* x, const float* w, int rows, int cols, float* out, void* stream);
 /* plain bf16 <-> fp32 casts and fills used by the host glue */
 int s2t_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
 int s2t_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream);
@@ -269,6 +272,18 @@ int s2t_relpos_qbias_bwd(const void* dquv, void* dq, long long lddq, long long r
 /* re-applied by a GEMM epilogue in the backward pass).  FFN with Swish: s2t_transformer_layer.py:59-65 */
 int s2t_act_dropout(const void* x, void* y, long long n, int act, float p, unsigned long long seed,
                     unsigned int stream_id, const unsigned long long* seed_offset, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
+/* Prediction-aware encoding: inter-CTC + Adapter "inter_league" (s2t_transformer.py:1881-1946,   */
+/* 2043-2103; modules/speech_to_text/adapter.py:189-217,264-266,296-297).                         */
+/* probs[r][v] = exp(logits[r][v] - lse[r]) for v < V, 0 for V <= v < ldp; bf16 in / out.         */
+/* --------------------------------------------------------------------------------------------- */
+int s2t_softmax_rows_fwd(const void* logits, long long ldv, const float* lse, void* probs,
+                         long long ldp, int rows, int V, void* stream);
+/* dlogits[r][v] (+)= probs * (dprobs - sum_v dprobs * probs); accumulate != 0 adds to dlogits     */
+/* (the CTC-loss gradient of the same logits written by s2t_ctc_loss).                             */
+int s2t_softmax_rows_bwd(const void* probs, const void* dprobs, long long ldp, void* dlogits,
+                         long long ldv, int rows, int V, int accumulate, void* stream);
 
 /* --------------------------------------------------------------------------------------------- */
 /* K7/K8/K9: CTC head softmax, CTC loss forward/backward, greedy decode.                          */

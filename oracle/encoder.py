@@ -51,6 +51,7 @@ class OracleConfig:
     inter_xctc_layers: Tuple[int, ...] = ()
     share_inter_ctc: bool = True
     ctc_pae: str = "none"                # none | inter_league
+    xctc_pae: str = "none"
     pae_unnorm_input: bool = False
     # PDS (pdss2t_transformer.py:1361-1560)
     pds_layers: Tuple[int, ...] = (3, 3, 3, 3)
@@ -296,6 +297,22 @@ class CTC(nn.Module):
         return self.ctc_projection(self.ctc_dropout_module(x))
 
 
+class Adapter(nn.Module):
+    """fairseq/modules/speech_to_text/adapter.py:76-299, adapter_type = "inter_league": out = representation +
+    softmax(logit) @ embed_adapter.weight; the softmax runs in the logits' dtype (:215-217, quirk A13)."""
+
+    def __init__(self, d, vocab):
+        super().__init__()
+        self.embed_adapter = nn.Linear(d, vocab, bias=False)              # used transposed as a (V, C) matrix
+        nn.init.normal_(self.embed_adapter.weight, mean=0, std=d ** -0.5)
+
+    def forward(self, representation, logit):
+        T, B, _ = representation.shape
+        dist = F.softmax(logit, dim=-1)
+        soft = torch.mm(dist.contiguous().view(-1, logit.size(-1)), self.embed_adapter.weight).view(T, B, -1)
+        return representation + soft
+
+
 class S2TTransformerEncoder(nn.Module):
     """fairseq/models/speech_to_text/s2t_transformer.py:883 (init :887-1244, forward :1714-2154), for the
     options of configs C1/C2/C4: conv1d subsampler, embed norm, abs or rel positions, pre-norm layers
@@ -318,6 +335,16 @@ class S2TTransformerEncoder(nn.Module):
             self.ctc = CTC(d, cfg.vocab, cfg.dropout)
         if cfg.tgt_vocab > 0:
             self.xctc = CTC(d, cfg.tgt_vocab, cfg.dropout)
+        # inter-CTC / inter-XCTC with shared heads (s2t_transformer.py:1001-1100, 1135-1244)
+        assert cfg.share_inter_ctc or not cfg.inter_ctc_layers, "oracle: only share_inter_ctc is restated"
+        for l in cfg.inter_ctc_layers:
+            setattr(self, f"ctc_norm{l}", nn.LayerNorm(d))
+        for l in cfg.inter_xctc_layers:
+            setattr(self, f"xctc_norm{l}", nn.LayerNorm(d))
+        if cfg.inter_ctc_layers and cfg.ctc_pae != "none":
+            self.pae = Adapter(d, cfg.vocab)
+        if cfg.inter_xctc_layers and cfg.xctc_pae != "none":
+            self.xctc_pae = Adapter(d, cfg.tgt_vocab)
 
     def forward(self, src_tokens: torch.Tensor, src_lengths: torch.Tensor) -> Dict[str, list]:
         cfg = self.cfg
@@ -337,13 +364,26 @@ class S2TTransformerEncoder(nn.Module):
         else:
             x = x + abs_positions(pad, cfg.embed_dim).transpose(0, 1).to(x.dtype)       # :1784-1786
         x = self.dropout_module(x)                                         # :1794
-        for layer in self.layers:                                          # :1824
+        inter_ctc, inter_xctc = [], []
+        for idx, layer in enumerate(self.layers, start=1):                 # :1824
             if cfg.layer_padding_mask and not bool(pad.all()):
                 x = x.transpose(0, 1).masked_fill(pad.unsqueeze(2), 0.0).transpose(0, 1)  # :1828-1836
             x = layer(x, pad, pos_emb=positions)                           # :1846
+            if idx in cfg.inter_ctc_layers:                                # :1881-1946
+                norm_x = getattr(self, f"ctc_norm{idx}")(x)
+                logit = self.ctc(norm_x)
+                if cfg.ctc_pae != "none":
+                    x = self.pae(x if cfg.pae_unnorm_input else norm_x, logit)
+                inter_ctc.append([logit, pad])
+            if idx in cfg.inter_xctc_layers:                               # :2043-2103
+                norm_x = getattr(self, f"xctc_norm{idx}")(x)
+                logit = self.xctc(norm_x)
+                if cfg.xctc_pae != "none":
+                    x = self.xctc_pae(x if cfg.pae_unnorm_input else norm_x, logit)
+                inter_xctc.append(logit)
         x = self.layer_norm(x)                                             # :2112
-        out = {"encoder_out": [x], "ctc_logit": [], "xctc_logit": [], "inter_ctc_logits": [],
-               "inter_xctc_logits": [], "encoder_padding_mask": [pad], "mixup": None,
+        out = {"encoder_out": [x], "ctc_logit": [], "xctc_logit": [], "inter_ctc_logits": inter_ctc,
+               "inter_xctc_logits": inter_xctc, "encoder_padding_mask": [pad], "mixup": None,
                "encoder_embedding": [], "encoder_states": [], "src_tokens": [], "src_lengths": []}
         if cfg.vocab > 0:
             out["ctc_logit"] = [self.ctc(x)]                               # :2126
@@ -443,6 +483,28 @@ def ctc_criterion_loss(logit_tbv: torch.Tensor, padding_mask: torch.Tensor, toke
     return loss.sum()
 
 
+def ctc_criterion_total(out: Dict[str, list], src_tokens: torch.Tensor, tgt_tokens: Optional[torch.Tensor], *,
+                        ctc_weight: float, xctc_weight: float = 0.0, inter_ctc_weight: float = 0.0,
+                        inter_xctc_weight: float = 0.0) -> torch.Tensor:
+    """CtcCriterion.compute_ctc_loss weighting (fairseq/criterions/ctc.py:542-682, 759-833, 1004-1015):
+    ctc_w * ctc + xctc_w * xctc + inter_ctc_w * mean_l(inter) + inter_xctc_w * mean_l(inter_x); source-side losses use
+    the transcript tokens, target-side (XCTC) losses the target tokens."""
+    pad = out["encoder_padding_mask"][0]
+    loss = src_tokens.new_zeros((), dtype=torch.float32)
+    if inter_ctc_weight > 0 and out["inter_ctc_logits"]:
+        it = [ctc_criterion_loss(lg[0], lg[1] if lg[1] is not None else pad, src_tokens) for lg in out["inter_ctc_logits"]]
+        loss = loss + inter_ctc_weight * sum(it) / len(it)
+    if ctc_weight > 0 and out["ctc_logit"]:
+        loss = loss + ctc_weight * ctc_criterion_loss(out["ctc_logit"][0], pad, src_tokens)
+    if tgt_tokens is not None:
+        if inter_xctc_weight > 0 and out["inter_xctc_logits"]:
+            it = [ctc_criterion_loss(lg, pad, tgt_tokens) for lg in out["inter_xctc_logits"]]
+            loss = loss + inter_xctc_weight * sum(it) / len(it)
+        if xctc_weight > 0 and out["xctc_logit"]:
+            loss = loss + xctc_weight * ctc_criterion_loss(out["xctc_logit"][0], pad, tgt_tokens)
+    return loss
+
+
 def config_from_args(args) -> OracleConfig:
     """Map a reference-style args Namespace (after the arch function ran) onto OracleConfig."""
     g = lambda k, d=None: getattr(args, k, d)
@@ -462,6 +524,7 @@ def config_from_args(args) -> OracleConfig:
         tgt_vocab=g("_tgt_vocab", 0) if g("xctc_weight", 0) > 0 else 0,
         inter_ctc_layers=split(g("inter_ctc_layers")), inter_xctc_layers=split(g("inter_xctc_layers")),
         share_inter_ctc=g("share_inter_ctc", False), ctc_pae=g("ctc_pae", "none"),
+        xctc_pae=g("xctc_pae", g("ctc_pae", "none")),
         pae_unnorm_input=g("pae_unnorm_input", False), **_pds_from_args(args))
 
 

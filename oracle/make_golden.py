@@ -37,6 +37,14 @@ ENC_CASES = {
                      macaron_style=True, use_cnn_module=True, cnn_module_kernel=15,
                      encoder_attention_type="rel_pos", encoder_activation_fn="swish",
                      layer_padding_mask=True),
+    # C5 in miniature: BiL-CTC synchronous (reproduction_bil_ctc_synchronous.yaml): conformer + CTC (source vocab) +
+    # XCTC (target vocab) + shared inter-CTC / inter-XCTC at layers 2,3 + inter_league adapters on un-normalised input
+    "c5_small": dict(encoder_layers=4, encoder_embed_dim=256, encoder_ffn_embed_dim=512, encoder_attention_heads=4,
+                     subsampling_filter=256, vocab=200, B=3, T=83, S=7, macaron_style=True, use_cnn_module=True,
+                     cnn_module_kernel=15, encoder_attention_type="rel_pos", encoder_activation_fn="swish",
+                     ctc_weight=0.2, xctc_weight=0.1, inter_ctc_weight=0.1, inter_ctc_layers="2,3",
+                     share_inter_ctc=True, inter_xctc_weight=0.05, inter_xctc_layers="2,3",
+                     ctc_pae="inter_league", xctc_pae="inter_league", pae_unnorm_input=True),
     # C3 in miniature: pdss2t_transformer_s_8 structure (4 stages, ratios 2_2_1_2, conv down-sampling + LayerNorm,
     # abs positions per stage, relu FFN), one layer per stage
     "c3_small": dict(family="pds", pds_stages=4, pds_layers="1_1_1_1", pds_ratios="2_2_1_2", pds_fusion=False,
@@ -110,7 +118,9 @@ def synth_batch(B: int, T: int, S: int, vocab: int, seed: int):
     return feats, lens, tokens
 
 
-GRAD_KEYS = ["downsampling1.conv.0.weight", "downsampling3.conv.0.bias", "downsampling2.norm.weight",
+GRAD_KEYS = ["pae.embed_adapter.weight", "xctc_pae.embed_adapter.weight", "xctc.ctc_projection.weight", "ctc_norm2.weight",
+             "xctc_norm3.bias", "layers.2.conv_module.depthwise_conv.weight", "layers.1.self_attn.linear_pos.weight",
+             "downsampling1.conv.0.weight", "downsampling3.conv.0.bias", "downsampling2.norm.weight",
              "stage1.0.ffn.w_1.weight", "stage4.0.self_attn.q_proj.weight", "stage2.0.self_attn_layer_norm.bias",
              "subsample.layers.0.0.weight", "subsample.layers.1.0.bias", "embed_ln.weight",
              "layers.0.ffn.w_1.weight", "layers.1.ffn.w_2.bias", "layers.0.self_attn_layer_norm.bias",
@@ -140,10 +150,17 @@ def run_reference_encoder(case: str, seed: int = 0):
     enc.train()                                             # dropout = 0, BatchNorm uses batch statistics
 
     feats, lens, tokens = synth_batch(B, T, S, vocab, seed + 1)
+    multi = getattr(args, "xctc_weight", 0) > 0 or bool(getattr(args, "inter_ctc_layers", None))
+    tgt_tokens = synth_batch(B, T, S + 2, vocab, seed + 2)[2] if multi else None
+    wkw = dict(ctc_weight=args.ctc_weight, xctc_weight=getattr(args, "xctc_weight", 0.0),
+               inter_ctc_weight=getattr(args, "inter_ctc_weight", 0.0),
+               inter_xctc_weight=getattr(args, "inter_xctc_weight", 0.0))
+    crit = (lambda o: OE.ctc_criterion_total(o, tokens, tgt_tokens, **wkw)) if multi else \
+           (lambda o: OE.ctc_criterion_loss(o["ctc_logit"][0], o["encoder_padding_mask"][0], tokens))
     out = enc(feats, lens)
     logit = out["ctc_logit"][0]
     pad = out["encoder_padding_mask"][0]
-    loss = OE.ctc_criterion_loss(logit, pad, tokens)
+    loss = crit(out)
     loss.backward()
     ref_grads = {k: p.grad.clone() for k, p in enc.named_parameters()}
 
@@ -155,8 +172,13 @@ def run_reference_encoder(case: str, seed: int = 0):
     orc.load_state_dict(sd)
     orc.train()
     o_out = orc(feats, lens)
-    o_loss = OE.ctc_criterion_loss(o_out["ctc_logit"][0], o_out["encoder_padding_mask"][0], tokens)
+    o_loss = crit(o_out)
     o_loss.backward()
+    for key in ("inter_ctc_logits", "inter_xctc_logits", "xctc_logit"):
+        assert len(o_out[key]) == len(out[key]), key
+        for a, b in zip(o_out[key], out[key]):
+            a, b = (a[0] if isinstance(a, list) else a), (b[0] if isinstance(b, list) else b)
+            assert (a - b).abs().max().item() < 1e-4, key
     err_x = (o_out["encoder_out"][0] - out["encoder_out"][0]).abs().max().item()
     err_l = (o_out["ctc_logit"][0] - logit).abs().max().item()
     assert err_x < 1e-4 and err_l < 1e-4, (err_x, err_l)
@@ -175,6 +197,13 @@ def run_reference_encoder(case: str, seed: int = 0):
         padding_mask=pad.numpy(), loss=np.float64(loss.item()),
         torch_version=torch.__version__,
     )
+    if multi:
+        fix["tgt_tokens"] = tgt_tokens.numpy()
+        fix["xctc_logit"] = out["xctc_logit"][0].detach().numpy()
+        fix["inter_ctc_logit_last"] = out["inter_ctc_logits"][-1][0].detach().numpy()
+        fix["inter_xctc_logit_last"] = out["inter_xctc_logits"][-1].detach().numpy()
+        fix["loss_weights"] = np.array([wkw["ctc_weight"], wkw["xctc_weight"], wkw["inter_ctc_weight"],
+                                        wkw["inter_xctc_weight"]])
     for k in GRAD_KEYS:
         if k in ref_grads:
             fix["grad::" + k] = ref_grads[k].numpy()

@@ -109,6 +109,22 @@ __global__ void f32_sum_kernel(const float* __restrict__ x, int n, float scale, 
   }
 }
 
+// out[0] = sum_r w[r] * sum_c x[r][c]
+__global__ void f32_weighted_sum_kernel(const float* __restrict__ x, const float* __restrict__ w, int rows, int cols,
+                                        float* __restrict__ out) {
+  __shared__ float s[32];
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < rows * cols; i += blockDim.x) acc += w[i / cols] * x[i];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? s[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) *out = v;
+  }
+}
+
 static inline unsigned grid_for(long long n, int threads) {
   long long g = (n + threads - 1) / threads;
   if (g > 148ll * 16) g = 148ll * 16;
@@ -175,6 +191,14 @@ extern "C" int s2t_add_bf16(const void* x, void* y, long long n, void* stream) {
   if (n <= 0) return 0;
   add_bf16_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), n / 8);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int s2t_f32_weighted_sum(const float* x, const float* w, int rows, int cols, float* out, void* stream) {
+  S2T_REQUIRE(x && w && out, "s2t_f32_weighted_sum: null pointer");
+  S2T_REQUIRE(rows > 0 && cols > 0, "s2t_f32_weighted_sum: empty input");
+  f32_weighted_sum_kernel<<<1, 256, 0, ST(stream)>>>(x, w, rows, cols, out);
   S2T_LAUNCH_CHECK();
   return 0;
 }

@@ -26,6 +26,7 @@ arithmetic (criterions/ctc.py:435-474,516-540).
 from __future__ import annotations
 
 import math
+import re
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -66,6 +67,17 @@ class EncoderConfig:
     vocab: int = 10000                     # CTC head (source dictionary); 0 = none
     ctc_weight: float = 1.0
     blank: int = 0
+    # --- dual heads / inter-CTC / prediction-aware encoding (s2t_transformer.py:951-1244; C5) -------------
+    tgt_vocab: int = 0                     # XCTC head (target dictionary); 0 = none
+    xctc_weight: float = 0.0
+    inter_ctc_layers: Tuple[int, ...] = ()     # 1-based layer indices (inter-ctc-layers: 6,9,12,15)
+    inter_ctc_weight: float = 0.0
+    inter_xctc_layers: Tuple[int, ...] = ()
+    inter_xctc_weight: float = 0.0
+    share_inter_ctc: bool = True
+    ctc_pae: str = "none"                  # none | inter_league
+    xctc_pae: str = "none"
+    pae_unnorm_input: bool = False
     # --- PDS (pdss2t_transformer.py:1361-1560; defaults = pdss2t_transformer_s_8) -------------------------
     pds_layers: Tuple[int, ...] = (3, 3, 3, 3)
     pds_ratios: Tuple[int, ...] = (2, 2, 1, 2)
@@ -81,6 +93,7 @@ class EncoderConfig:
     def from_args(args, vocab: int, family: str = "s2t") -> "EncoderConfig":
         g = lambda k, d=None: getattr(args, k, d)
         ints = lambda s: tuple(int(v) for v in str(s).split("_"))
+        csv = lambda s: tuple(int(v) for v in str(s).split(",")) if s else ()
         kw = dict(
             input_dim=g("input_feat_per_channel", 80) * g("input_channels", 1),
             embed_dim=args.encoder_embed_dim, ffn_dim=args.encoder_ffn_embed_dim,
@@ -94,7 +107,12 @@ class EncoderConfig:
             encoder_activation_fn=g("encoder_activation_fn", "relu"), activation_fn=g("activation_fn", "relu"),
             layer_padding_mask=g("layer_padding_mask", False), dropout=args.dropout,
             max_source_positions=g("max_source_positions", 6000),
-            vocab=vocab if g("ctc_weight", 0) > 0 else 0, ctc_weight=g("ctc_weight", 1.0) or 1.0)
+            vocab=vocab if g("ctc_weight", 0) > 0 else 0, ctc_weight=g("ctc_weight", 1.0) or 1.0,
+            tgt_vocab=g("_tgt_vocab", vocab) if g("xctc_weight", 0) > 0 else 0, xctc_weight=g("xctc_weight", 0.0),
+            inter_ctc_layers=csv(g("inter_ctc_layers")), inter_ctc_weight=g("inter_ctc_weight", 0.0),
+            inter_xctc_layers=csv(g("inter_xctc_layers")), inter_xctc_weight=g("inter_xctc_weight", 0.0),
+            share_inter_ctc=g("share_inter_ctc", False), ctc_pae=g("ctc_pae", "none"),
+            xctc_pae=g("xctc_pae", g("ctc_pae", "none")), pae_unnorm_input=g("pae_unnorm_input", False))
         if family == "pds":
             n = int(args.pds_stages)
             kw.update(encoder_type="pds", pds_layers=ints(args.pds_layers)[:n], pds_ratios=ints(args.pds_ratios)[:n],
@@ -134,6 +152,8 @@ def _round8(n: int) -> int:
 
 
 _ACT = {"relu": ops.ACT_RELU, "swish": ops.ACT_SWISH}
+_NORM_W = re.compile(r"(norm\d*|embed_ln)\.weight$")
+_NORM_B = re.compile(r"(norm\d*|embed_ln)\.bias$")
 
 
 @dataclass
@@ -153,6 +173,24 @@ class _LayerSpec:
     @property
     def site(self) -> int:
         return 64 * (self.gidx + 1)
+
+
+@dataclass
+class _HeadSpec:
+    """One CTC head (modules/speech_to_text/ctc.py:17-66) and its inter-CTC uses (s2t_transformer.py:1881-1946,2043-2103)."""
+    name: str                      # parameter prefix: "ctc" (source vocabulary) | "xctc" (target vocabulary)
+    V: int
+    weight: float                  # weight of the top loss
+    inter_layers: Tuple[int, ...]  # 1-based layer indices carrying an inter loss with this (shared) head
+    inter_weight: float
+    norm: str                      # "ctc_norm" | "xctc_norm" (+ layer index)
+    pae: Optional[str]             # adapter parameter prefix ("pae" | "xctc_pae") or None
+    tgt: int                       # target set: 0 = transcript (source text), 1 = target text
+    site: int                      # dropout site base
+
+    @property
+    def ldv(self) -> int:
+        return _round8(max(self.V, 8))
 
 
 class _Bufs:
@@ -311,17 +349,61 @@ class Plan:
             L.h = e(Rs, Fs) if c.encoder_activation_fn != "relu" else None
             self.layers.append(L)
         self.enc_out, self.enc_st = e(R, C), e(R, 2, dt=F32)
-        self.enc_drop = e(R, C) if drop else self.enc_out
-        V = c.vocab
-        self.ldv = _round8(max(V, 8))
-        if V > 0:
-            self.logits = z(R, self.ldv)
-            self.dlogits = z(R, self.ldv)
-            self.lse = e(R, dt=F32)
-            self.nll = z(B, dt=F32)
+        # --- CTC heads: top logits per head, inter-CTC blocks, one nll row per loss term ------------------------
+        self.tg = [self.targets, z(B, max(smax, 1), dt=torch.int32)]
+        self.tl = [self.tgt_len, z(B, dt=torch.int32)]
+        self.heads: List[_Bufs] = []
+        self.inter: Dict[Tuple[int, int], _Bufs] = {}
+        weights: List[float] = []
+        for k, hs in enumerate(eng.heads):
+            Hd = _Bufs()
+            Hd.logits, Hd.dlogits = z(R, hs.ldv), z(R, hs.ldv)
+            Hd.lse = e(R, dt=F32)
+            Hd.drop = e(R, C) if drop else self.enc_out
+            Hd.colsum_ws = e(lib.s2t_colsum_workspace_floats(R, hs.ldv), dt=F32)
+            Hd.loss_idx = len(weights)
+            weights.append(hs.weight)
+            if hs.inter_layers:
+                Hd.ddist = e(R, hs.ldv)                                  # scratch shared by the head's inter blocks
+            self.heads.append(Hd)
+            for l in hs.inter_layers:
+                I = _Bufs()
+                I.nx, I.st = e(R, C), e(R, 2, dt=F32)
+                I.nxd = e(R, C) if drop else I.nx
+                I.logits, I.dlogits = z(R, hs.ldv), z(R, hs.ldv)
+                I.lse = e(R, dt=F32)
+                if hs.pae:
+                    I.dist = z(R, hs.ldv)
+                I.loss_idx = len(weights)
+                weights.append(hs.inter_weight / len(hs.inter_layers))
+                self.inter[(l, k)] = I
+        if eng.heads:
+            self.nll_all = z(len(weights), B, dt=F32)
+            self.loss_w = torch.tensor(weights, dtype=F32, device=dev)
+            self.loss_weights = weights
             self.loss = z(1, dt=F32)
             self.ctc_ws = e((ops.ctc_workspace_bytes(B, T2, max(smax, 1)) + 3) // 4, dt=F32)
-            self.head_colsum_ws = e(lib.s2t_colsum_workspace_floats(R, self.ldv), dt=F32)
+            # single-head conveniences (C1-C4 callers): the first head's buffers
+            h0 = self.heads[0]
+            self.logits, self.dlogits, self.lse, self.ldv = h0.logits, h0.dlogits, h0.lse, eng.heads[0].ldv
+            self.nll = self.nll_all[0]
+        # x chain: y[j] = buffer layer j writes; the inter blocks after it map y[j] -> ... -> x[j+1] (next layer's input)
+        St0 = self.stages[0]
+        St0.y = list(St0.x[1:])
+        for j in range(len(St0.y)):
+            blocks = eng.inter_after.get(j + 1, [])
+            pae_blocks = [k for k in blocks if eng.heads[k].pae]
+            cur = St0.x[j + 1]
+            if pae_blocks:
+                cur = St0.y[j] = e(R, C)
+            for k in blocks:
+                I = self.inter[(j + 1, k)]
+                I.xin = cur
+                if eng.heads[k].pae:
+                    I.xout = St0.x[j + 1] if k == pae_blocks[-1] else e(R, C)
+                    cur = I.xout
+                else:
+                    I.xout = cur
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.graph_kind: Optional[str] = None
 
@@ -355,6 +437,25 @@ class S2TEncoderEngine:
         self.buffers: Dict[str, torch.Tensor] = {}         # BatchNorm running statistics (fp32 / int64)
         self.layer_specs: List[_LayerSpec] = []
         self.ffn_act = _ACT[c.encoder_activation_fn]
+        self.heads: List[_HeadSpec] = []
+        if c.vocab > 0:
+            self.heads.append(_HeadSpec("ctc", c.vocab, c.ctc_weight, tuple(c.inter_ctc_layers), c.inter_ctc_weight,
+                                        "ctc_norm", "pae" if c.ctc_pae != "none" else None, 0, 40))
+        if c.tgt_vocab > 0:
+            self.heads.append(_HeadSpec("xctc", c.tgt_vocab, c.xctc_weight, tuple(c.inter_xctc_layers),
+                                        c.inter_xctc_weight, "xctc_norm", "xctc_pae" if c.xctc_pae != "none" else None,
+                                        1, 50))
+        for hs in self.heads:
+            if hs.inter_layers and (c.encoder_type != "s2t" or not c.share_inter_ctc):
+                raise NotImplementedError("engine: inter-CTC is built for the S2T encoder with share_inter_ctc")
+            if hs.pae and (c.ctc_pae if hs.name == "ctc" else c.xctc_pae) != "inter_league":
+                raise NotImplementedError("engine: the prediction-aware adapter is inter_league")
+        # inter_after[l] = head indices with an inter block after (1-based) layer l, CTC before XCTC (forward order)
+        self.inter_after: Dict[int, List[int]] = {}
+        for k, hs in enumerate(self.heads):
+            for l in hs.inter_layers:
+                self.inter_after.setdefault(l, []).append(k)
+        first_inter = min(self.inter_after) if self.inter_after else None
         if c.encoder_type == "s2t":
             C = c.embed_dim
             assert C % c.heads == 0 and (C // c.heads) % 8 == 0 and C % 8 == 0 and c.input_dim % 8 == 0
@@ -375,6 +476,13 @@ class S2TEncoderEngine:
                 spec = _LayerSpec(f"layers.{l}.", 0, l, l, C, c.ffn_dim, c.heads, _ACT[c.activation_fn], c.dropout)
                 self.layer_specs.append(spec)
                 self._declare_layer(spec)
+                # inter-CTC norms sit after their layer; the shared heads after the first inter layer, so the backward
+                # pass completes them (and reports the range final) as early as possible
+                for k in self.inter_after.get(l + 1, []):
+                    n = f"{self.heads[k].norm}{l + 1}"
+                    S.declare(n + ".weight", (C,)); S.declare(n + ".bias", (C,))
+                if first_inter == l + 1:
+                    self._declare_heads(C)
             self.out_dim = C
         else:
             cin, g = c.input_dim, 0
@@ -397,9 +505,8 @@ class S2TEncoderEngine:
             self.out_dim = c.pds_dims[-1]
         C = self.out_dim
         S.declare("layer_norm.weight", (C,)); S.declare("layer_norm.bias", (C,))
-        if c.vocab > 0:
-            S.declare("ctc.ctc_projection.weight", (c.vocab, C))
-            S.declare("ctc.ctc_projection.bias", (_round8(c.vocab),))  # padded to the logits' row stride
+        if first_inter is None:
+            self._declare_heads(C)
         S.finalize()
         self.embed_scale = 1.0 if (c.no_scale_embedding or c.encoder_type == "pds") else math.sqrt(C)  # quirk A17
         self.pos_tables: Dict[int, torch.Tensor] = {}
@@ -418,6 +525,17 @@ class S2TEncoderEngine:
     @property
     def pos_table(self) -> torch.Tensor:
         return self._pos_table(self.out_dim)
+
+    def _declare_heads(self, C: int) -> None:
+        """CTC / XCTC projections (bias padded to the logits' row stride) and the adapters' (V, C) embedding matrices."""
+        S = self.store
+        self.padded_bias: Dict[str, int] = {}
+        for hs in self.heads:
+            S.declare(hs.name + ".ctc_projection.weight", (hs.V, C))
+            S.declare(hs.name + ".ctc_projection.bias", (hs.ldv,))
+            self.padded_bias[hs.name + ".ctc_projection.bias"] = hs.V
+            if hs.pae and hs.inter_layers:
+                S.declare(hs.pae + ".embed_adapter.weight", (hs.V, C))
 
     def _declare_layer(self, sp: _LayerSpec) -> None:
         """Parameters of one layer in forward order (names: SURVEY.md §8b)."""
@@ -472,13 +590,13 @@ class S2TEncoderEngine:
         S = self.store
         for name in S.names():
             shape = S.shape(name)
-            if name.endswith("norm.weight") or name == "embed_ln.weight":
+            if _NORM_W.search(name):
                 t = torch.ones(shape)
-            elif name.endswith("norm.bias") or name == "embed_ln.bias":
+            elif _NORM_B.search(name):
                 t = torch.zeros(shape)
-            elif name == "ctc.ctc_projection.weight":
+            elif name.endswith(("ctc_projection.weight", "embed_adapter.weight")):
                 t = torch.randn(shape, generator=g) * shape[1] ** -0.5
-            elif name == "ctc.ctc_projection.bias":
+            elif name.endswith("ctc_projection.bias"):
                 t = torch.zeros(shape)
             elif name.endswith("_proj.weight"):
                 gain = 1.0 if "out_proj" in name else 2 ** -0.5
@@ -512,7 +630,7 @@ class S2TEncoderEngine:
                 if tuple(t.shape) != self.ref_shapes[name]:
                     raise ValueError(f"{name}: shape {tuple(t.shape)} != {self.ref_shapes[name]}")
                 t = t.reshape(S.shape(name))
-            if name == "ctc.ctc_projection.bias":
+            if name in self.padded_bias:
                 full = torch.zeros(S.shape(name))
                 full[: t.numel()] = t
                 t = full
@@ -532,8 +650,8 @@ class S2TEncoderEngine:
                 t = t.permute(0, 2, 1).contiguous()
             if name in self.ref_shapes:
                 t = t.reshape(self.ref_shapes[name])
-            if name == "ctc.ctc_projection.bias":
-                t = t[: self.cfg.vocab]
+            if name in self.padded_bias:
+                t = t[: self.padded_bias[name]]
             out[name] = t
         return out
 
@@ -548,7 +666,7 @@ class S2TEncoderEngine:
         return self._export(True)
 
     def num_params(self) -> int:
-        return self.store.num_params() - (_round8(self.cfg.vocab) - self.cfg.vocab if self.cfg.vocab else 0)
+        return self.store.num_params() - sum(hs.ldv - hs.V for hs in self.heads)
 
     def train(self, mode: bool = True):
         self.training = mode
@@ -737,7 +855,7 @@ class S2TEncoderEngine:
         c = self.cfg
         sp, L = self.layer_specs[g], P.layers[g]
         St = P.stages[sp.stage]
-        x, y = St.x[sp.index], St.x[sp.index + 1]
+        x, y = St.x[sp.index], (St.y[sp.index] if sp.stage == 0 else St.x[sp.index + 1])
         p = sp.prefix
         if c.layer_padding_mask and c.encoder_type == "s2t":
             ops.mask_rows_(x.view(P.B, St.T, St.C), St.lens)                  # s2t_transformer.py:1828-1836
@@ -756,20 +874,41 @@ class S2TEncoderEngine:
         else:
             self._ffn_fwd(St, x, y, L.ln2, L.st2, L.h, L.f, p + "ffn_norm", p + "ffn", s, sp.site + 4)
 
+    def _ctc_proj_fwd(self, hs: _HeadSpec, x: torch.Tensor, xd: torch.Tensor, logits: torch.Tensor, site: int) -> None:
+        """CTC.forward (modules/speech_to_text/ctc.py:55-66, quirk A11): dropout -> Linear(C, V)."""
+        S = self.store
+        spec = self._drop(site)
+        src = x
+        if spec:
+            ops.dropout(x, spec, out=xd)
+            src = xd
+        ops.linear(src, S.p(hs.name + ".ctc_projection.weight"), S.p(hs.name + ".ctc_projection.bias"), out=logits)
+
     def _head_fwd(self, P: Plan) -> None:
-        """Final LayerNorm (s2t_transformer.py:2112) and the CTC head: dropout -> Linear(C, V)
-        (modules/speech_to_text/ctc.py:55-66, quirk A11)."""
-        c, S = self.cfg, self.store
+        """Final LayerNorm (s2t_transformer.py:2112) and the top CTC / XCTC heads (:2124-2133)."""
+        S = self.store
         ops.layernorm_fwd(P.stages[-1].x[-1], S.p("layer_norm.weight"), S.p("layer_norm.bias"), out=P.enc_out,
                           stats=P.enc_st)
-        if c.vocab <= 0:
-            return
-        spec = self._drop(60)
-        src = P.enc_out
-        if spec:
-            ops.dropout(P.enc_out, spec, out=P.enc_drop)
-            src = P.enc_drop
-        ops.linear(src, S.p("ctc.ctc_projection.weight"), S.p("ctc.ctc_projection.bias"), out=P.logits)
+        for hs, Hd in zip(self.heads, P.heads):
+            self._ctc_proj_fwd(hs, P.enc_out, Hd.drop, Hd.logits, hs.site)
+
+    def _inter_fwd(self, P: Plan, l: int, k: int) -> None:
+        """Inter-CTC block after layer l with head k (s2t_transformer.py:1881-1946 / 2043-2103): norm_x = LN_l(x);
+        logit = CTC(norm_x); with a prediction-aware adapter (adapter.py:189-217,264-266,296-297, inter_league):
+        x <- (x | norm_x) + softmax(logit) @ embed_adapter.weight."""
+        c, S = self.cfg, self.store
+        hs, I = self.heads[k], P.inter[(l, k)]
+        n = f"{hs.norm}{l}"
+        ops.layernorm_fwd(I.xin, S.p(n + ".weight"), S.p(n + ".bias"), out=I.nx, stats=I.st)
+        self._ctc_proj_fwd(hs, I.nx, I.nxd, I.logits, hs.site + 1 + hs.inter_layers.index(l))
+        ops.row_lse(I.logits, hs.V, out=I.lse)
+        if hs.pae:
+            ops.softmax_rows_fwd(I.logits, I.lse, hs.V, out=I.dist)
+            E = S.p(hs.pae + ".embed_adapter.weight")
+            C = E.shape[1]
+            res = I.xin if c.pae_unnorm_input else I.nx
+            ops.gemm_raw(M=P.R, N=C, K=hs.V, a=I.dist, lda=hs.ldv, b=E, ldb=C, b_mn=True, out=I.xout, ldc=C,
+                         residual=res, ldr=C)
 
     def _forward(self, P: Plan) -> None:
         g = 0
@@ -782,18 +921,30 @@ class S2TEncoderEngine:
             for _ in range(n):
                 self._layer_fwd(P, g)
                 g += 1
+                if i == 0:
+                    for k in self.inter_after.get(g, []):
+                        self._inter_fwd(P, g, k)
         self._head_fwd(P)
 
     def _loss(self, P: Plan, need_grad: bool) -> None:
-        """fp32 log-softmax + CTCLoss(blank, 'none', zero_infinity=True).sum() and its gradient w.r.t. the
-        logits (criterions/ctc.py:435-474); loss = ctc_weight * sum_b nll_b (:1004)."""
+        """fp32 log-softmax + CTCLoss(blank, 'none', zero_infinity=True).sum() per loss term and its gradient w.r.t. the
+        logits (criterions/ctc.py:435-474); loss = ctc_w ctc + xctc_w xctc + inter_ctc_w mean_l(inter) +
+        inter_xctc_w mean_l(inter_x) (:1004-1015) — every term's weight is folded into its gradient."""
         c = self.cfg
-        B, T, V = P.B, P.T2, c.vocab
-        ops.row_lse(P.logits, V, out=P.lse)
-        ops.ctc_loss(P.logits.view(B, T, P.ldv), P.targets, P.out_len, P.tgt_len, V, c.blank,
-                     need_grad=need_grad, grad_scale=c.ctc_weight, lse=P.lse,
-                     dlogits=P.dlogits.view(B, T, P.ldv) if need_grad else None, workspace=P.ctc_ws, nll=P.nll)
-        ops.f32_sum(P.nll, P.loss, c.ctc_weight)
+        B, T = P.B, P.T2
+        for k, (hs, Hd) in enumerate(zip(self.heads, P.heads)):
+            terms = [(Hd.logits, Hd.dlogits, Hd.lse, Hd.loss_idx, True)]
+            terms += [(P.inter[(l, k)].logits, P.inter[(l, k)].dlogits, P.inter[(l, k)].lse, P.inter[(l, k)].loss_idx, False)
+                      for l in hs.inter_layers]
+            for logits, dlogits, lse, idx, need_lse in terms:
+                if need_lse:
+                    ops.row_lse(logits, hs.V, out=lse)
+                w = P.loss_weights[idx]
+                ops.ctc_loss(logits.view(B, T, hs.ldv), P.tg[hs.tgt], P.out_len, P.tl[hs.tgt], hs.V, c.blank,
+                             need_grad=need_grad, grad_scale=w, lse=lse,
+                             dlogits=dlogits.view(B, T, hs.ldv) if need_grad else None, workspace=P.ctc_ws,
+                             nll=P.nll_all[idx])
+        ops.weighted_sum(P.nll_all, P.loss_w, P.loss)
 
     # ------------------------------------------------------------------------------------------
     # backward
@@ -809,24 +960,94 @@ class S2TEncoderEngine:
             return dy
         return ops.dropout(dy, spec, out=out, scale=scale)
 
+    def _acc(self, name: str) -> bool:
+        """True if the gradient of ``name`` was already written in this backward pass (shared heads accumulate)."""
+        seen = name in self._touched
+        self._touched.add(name)
+        return seen
+
+    def _ctc_proj_bwd(self, P: Plan, hs: _HeadSpec, dlogits: torch.Tensor, src: torch.Tensor, ws: torch.Tensor,
+                      out: torch.Tensor, residual: Optional[torch.Tensor]) -> None:
+        """Backward of Linear(C, V): bias / weight gradients (accumulated across the uses of a shared head) and
+        out = dlogits @ W (+ residual)."""
+        S = self.store
+        wn, bn = hs.name + ".ctc_projection.weight", hs.name + ".ctc_projection.bias"
+        C = out.shape[1]
+        ops.colsum(dlogits, S.g(bn), accumulate=self._acc(bn), workspace=ws)
+        gw = S.g(wn)
+        dl = dlogits[:, : hs.V] if hs.V != hs.ldv else dlogits
+        if self._acc(wn):
+            ops.linear_wgrad(dl, src, out=gw, residual=gw, ldr=C)
+        else:
+            ops.linear_wgrad(dl, src, out=gw)
+        ops.gemm_raw(M=P.R, N=C, K=hs.V, a=dlogits, lda=hs.ldv, b=S.p(wn), ldb=C, b_mn=True, out=out, ldc=C,
+                     residual=residual, ldr=C if residual is not None else 0)
+
     def _head_bwd(self, P: Plan) -> torch.Tensor:
-        c, S = self.cfg, self.store
+        S = self.store
         St = P.stages[-1]
-        C = St.C
-        src = P.enc_drop if self._drop(60) else P.enc_out
-        ops.colsum(P.dlogits, S.g("ctc.ctc_projection.bias"), workspace=P.head_colsum_ws)
-        ops.linear_wgrad(P.dlogits[:, : c.vocab] if c.vocab != P.ldv else P.dlogits, src,
-                         out=S.g("ctc.ctc_projection.weight"))
-        t0, t1 = St.take(), St.take()
-        ops.gemm_raw(M=P.R, N=C, K=c.vocab, a=P.dlogits, lda=P.ldv,
-                     b=S.p("ctc.ctc_projection.weight"), ldb=C, b_mn=True, out=t0, ldc=C)
-        d = self._branch_grad(t0, self._drop(60), 1.0, t1)
-        self._ready("ctc.ctc_projection.weight")
+        self._touched = set()
+        d = None
+        for hs, Hd in zip(self.heads, P.heads):
+            spec = self._drop(hs.site)
+            t0 = St.take()
+            self._ctc_proj_bwd(P, hs, Hd.dlogits, Hd.drop if spec else P.enc_out, Hd.colsum_ws, t0, None)
+            if spec:
+                t1 = St.take()
+                ops.dropout(t0, spec, out=t1)
+                St.give(t0)
+                t0 = t1
+            if d is None:
+                d = t0
+            else:
+                ops.add_(d, t0)
+                St.give(t0)
+        if not self.inter_after:
+            self._ready(self.heads[0].name + ".ctc_projection.weight")
         dx = St.take()
         ops.layernorm_bwd(d, St.x[-1], S.p("layer_norm.weight"), P.enc_st, S.g("layer_norm.weight"),
                           S.g("layer_norm.bias"), out=dx, partials=St.ln_part)
-        St.give(t0, t1)
+        St.give(d)
         self._ready("layer_norm.weight")
+        return dx
+
+    def _inter_bwd(self, P: Plan, l: int, k: int, dy: torch.Tensor) -> torch.Tensor:
+        """Backward of _inter_fwd: ``dy`` = gradient w.r.t. the block output (== input when the head has no adapter);
+        adds the block's own CTC-loss gradient (already in I.dlogits) and returns the gradient w.r.t. the block input."""
+        c, S = self.cfg, self.store
+        hs, Hd, I = self.heads[k], P.heads[k], P.inter[(l, k)]
+        St = P.stages[0]
+        C = St.C
+        if hs.pae:
+            en = hs.pae + ".embed_adapter.weight"
+            E, gE = S.p(en), S.g(en)
+            # d dist = dy E^T ; dE (+)= dist^T dy ; dlogits += softmax'(d dist)
+            ops.gemm_raw(M=P.R, N=hs.V, K=C, a=dy, lda=C, b=E, ldb=C, out=Hd.ddist, ldc=hs.ldv)
+            dist = I.dist[:, : hs.V] if hs.V != hs.ldv else I.dist
+            if self._acc(en):
+                ops.linear_wgrad(dist, dy, out=gE, residual=gE, ldr=C)
+            else:
+                ops.linear_wgrad(dist, dy, out=gE)
+            ops.softmax_rows_bwd(I.dist, Hd.ddist, I.dlogits, hs.V, accumulate=True)
+        spec = self._drop(hs.site + 1 + hs.inter_layers.index(l))
+        t0 = St.take()
+        # d norm_x = dropout'(dlogits W) (+ dy when the adapter adds to the normalised input)
+        to_norm = dy if (hs.pae and not c.pae_unnorm_input) else None
+        self._ctc_proj_bwd(P, hs, I.dlogits, I.nxd if spec else I.nx, Hd.colsum_ws, t0, None if spec else to_norm)
+        if spec:
+            t1 = St.take()
+            ops.dropout(t0, spec, out=t1)
+            St.give(t0)
+            t0 = t1
+            if to_norm is not None:
+                ops.add_(t0, to_norm)
+        # gradient that bypasses the norm: dy flows to x unless the adapter consumed norm_x instead of x
+        skip = None if to_norm is not None else dy
+        n = f"{hs.norm}{l}"
+        dx = St.take()
+        ops.layernorm_bwd(t0, I.xin, S.p(n + ".weight"), I.st, S.g(n + ".weight"), S.g(n + ".bias"),
+                          dx_residual=skip, out=dx, partials=St.ln_part)
+        St.give(t0, dy)
         return dx
 
     def _ffn_bwd(self, St: _Stage, dy: torch.Tensor, x: torch.Tensor, ln: torch.Tensor, st: torch.Tensor,
@@ -1034,6 +1255,11 @@ class S2TEncoderEngine:
         for i in reversed(range(len(P.stages))):
             n = c.layers if c.encoder_type == "s2t" else c.pds_layers[i]
             for _ in range(n):
+                if i == 0 and (g in self.inter_after):
+                    for k in reversed(self.inter_after[g]):
+                        d = self._inter_bwd(P, g, k, d)
+                    first = f"{self.heads[self.inter_after[g][0]].norm}{g}.weight"
+                    self._ready(first)
                 g -= 1
                 d = self._layer_bwd(P, g, d)
             if c.encoder_type == "s2t":
@@ -1058,7 +1284,8 @@ class S2TEncoderEngine:
 
     def set_inputs(self, P: Plan, *, feats: Optional[torch.Tensor] = None, src_lengths: Optional[torch.Tensor] = None,
                    wave: Optional[torch.Tensor] = None, num_samples: Optional[torch.Tensor] = None,
-                   targets: Optional[torch.Tensor] = None, target_lengths: Optional[torch.Tensor] = None) -> None:
+                   targets: Optional[torch.Tensor] = None, target_lengths: Optional[torch.Tensor] = None,
+                   xtargets: Optional[torch.Tensor] = None, xtarget_lengths: Optional[torch.Tensor] = None) -> None:
         """Copy one batch into the plan's static input buffers (async on the current stream; host tensors
         should be pinned).  feats fp32 [B, T, D] + src_lengths, or wave fp32 [B, N] (int16 scale) + num_samples."""
         nb = True
@@ -1075,6 +1302,9 @@ class S2TEncoderEngine:
         if targets is not None:
             P.targets[:, : targets.shape[1]].copy_(targets, non_blocking=nb)
             P.tgt_len.copy_(target_lengths, non_blocking=nb)
+        if xtargets is not None:        # target-text tokens for the XCTC losses (criterions/ctc.py:763-767)
+            P.tg[1][:, : xtargets.shape[1]].copy_(xtargets, non_blocking=nb)
+            P.tl[1].copy_(xtarget_lengths, non_blocking=nb)
 
     def forward(self, P: Plan) -> None:
         """Encoder forward on the plan's inputs; results in P.enc_out [B*T', C], P.logits [B*T', ldv], P.out_len."""
@@ -1097,6 +1327,7 @@ class S2TEncoderEngine:
         from .dp import BucketedAllReduce
         S = self.store
         firsts = {sp.first for sp in self.layer_specs}
+        firsts |= {f"{self.heads[ks[0]].norm}{l}.weight" for l, ks in self.inter_after.items()}
         cuts = [S.offset(n) for n in S.names()
                 if n in firsts or n in ("layer_norm.weight", "ctc.ctc_projection.weight", "embed_ln.weight")
                 or (n.startswith("subsample.") and n.endswith("weight")) or n.endswith("conv.0.weight")]
@@ -1125,7 +1356,8 @@ class S2TEncoderEngine:
         else:
             self.forward(P)
 
-    def greedy_decode(self, P: Plan):
-        """CTCDecoder greedy (s2t_ctc.py:312-347) on the plan's logits: int32 tokens [B, T'] (-1 padded), lengths."""
-        c = self.cfg
-        return ops.ctc_greedy(P.logits.view(P.B, P.T2, P.ldv), P.out_len, c.vocab, c.blank)
+    def greedy_decode(self, P: Plan, head: int = 0):
+        """CTCDecoder greedy (s2t_ctc.py:312-347) on the logits of head ``head`` (0 = CTC, 1 = XCTC): int32 tokens
+        [B, T'] (-1 padded), lengths, per-frame ids."""
+        hs = self.heads[head]
+        return ops.ctc_greedy(P.heads[head].logits.view(P.B, P.T2, hs.ldv), P.out_len, hs.V, self.cfg.blank)

@@ -62,6 +62,7 @@ SIGNATURES = {
     "s2t_counter_add": (_i, [_vp, _ull, _vp]),
     "s2t_add_bf16": (_i, [_vp, _vp, _ll, _vp]),
     "s2t_f32_sum": (_i, [_vp, _i, _f, _vp, _vp]),
+    "s2t_f32_weighted_sum": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "s2t_mask_rows": (_i, [_vp, _vp, _i, _i, _i, _ll, _vp]),
     "s2t_permute_conv_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "s2t_cast_f32_to_bf16": (_i, [_vp, _vp, _ll, _vp]),
@@ -77,6 +78,8 @@ SIGNATURES = {
     "s2t_relpos_qbias_fwd": (_i, [_vp, _ll, _vp, _vp, _vp, _ll, _i, _vp]),
     "s2t_relpos_qbias_bwd": (_i, [_vp, _vp, _ll, _ll, _i, _vp]),
     "s2t_act_dropout": (_i, [_vp, _vp, _ll, _i, _f, _ull, _u, _vp, _vp]),
+    "s2t_softmax_rows_fwd": (_i, [_vp, _ll, _vp, _vp, _ll, _i, _i, _vp]),
+    "s2t_softmax_rows_bwd": (_i, [_vp, _vp, _ll, _vp, _ll, _i, _i, _i, _vp]),
     "s2t_row_lse": (_i, [_vp, _i, _ll, _i, _i, _vp, _vp]),
     "s2t_ctc_workspace_bytes": (_ll, [_i, _i, _i]),
     "s2t_ctc_loss": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _ll, _vp]),

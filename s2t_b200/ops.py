@@ -347,6 +347,12 @@ def f32_sum(x: torch.Tensor, out: torch.Tensor, scale: float = 1.0) -> torch.Ten
     return out
 
 
+def weighted_sum(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """out[0] = sum_r w[r] * sum_c x[r, c]  (fp32)."""
+    _call("s2t_f32_weighted_sum", _p(x), _p(w), x.shape[0], x.shape[1], _p(out), _stream())
+    return out
+
+
 # --------------------------------------------------------------------------------------------------
 # attention softmax
 # --------------------------------------------------------------------------------------------------
@@ -477,6 +483,22 @@ def row_lse(logits: torch.Tensor, V: int, out: Optional[torch.Tensor] = None) ->
         out = torch.empty((rows,), device=logits.device, dtype=torch.float32)
     _call("s2t_row_lse", _p(logits), int(logits.dtype == BF16), logits.stride(0), rows, V, _p(out), _stream())
     return out
+
+
+def softmax_rows_fwd(logits: torch.Tensor, lse: torch.Tensor, V: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """probs = exp(logits - lse) over the first V columns (bf16 [rows, ld]); padding columns zeroed."""
+    rows = logits.shape[0]
+    if out is None:
+        out = torch.empty_like(logits)
+    _call("s2t_softmax_rows_fwd", _p(logits), logits.stride(0), _p(lse), _p(out), out.stride(0), rows, V, _stream())
+    return out
+
+
+def softmax_rows_bwd(probs: torch.Tensor, dprobs: torch.Tensor, dlogits: torch.Tensor, V: int,
+                     accumulate: bool = False) -> torch.Tensor:
+    _call("s2t_softmax_rows_bwd", _p(probs), _p(dprobs), probs.stride(0), _p(dlogits), dlogits.stride(0),
+          probs.shape[0], V, int(accumulate), _stream())
+    return dlogits
 
 
 def ctc_workspace_bytes(B: int, T: int, max_target_len: int) -> int:

@@ -138,3 +138,33 @@ def test_softmax_head_major_bias_matches_batch_major(cuda_lib):
     d1 = ops.attn_softmax_bwd(p0, dp.cuda(), klen, H, T, dbias=db1, scale=0.3, bias_head_major=True)
     assert torch.equal(d0, d1)
     assert torch.equal(db0.view(B, H, T, ldb).transpose(0, 1).contiguous().view(H * B, T, ldb), db1)
+
+
+@pytest.mark.parametrize("rows,V", [(37, 200), (250, 10000), (5, 1001)])
+def test_softmax_rows_fwd_bwd(cuda_lib, rows, V):
+    """Adapter distribution (adapter.py:215-217) from the CTC row log-sum-exp, and its backward accumulated onto an
+    existing gradient.  bf16 probabilities: 1 % of the row maximum."""
+    from s2t_b200 import ops
+    ld = (V + 7) // 8 * 8
+    logits = torch.zeros((rows, ld), dtype=BF16)
+    logits[:, :V] = _rand((rows, V), 1, 3.0)
+    lg = logits.cuda()
+    lse = ops.row_lse(lg, V)
+    p = ops.softmax_rows_fwd(lg, lse, V)
+    x = logits[:, :V].float().requires_grad_(True)
+    ref = torch.softmax(x, -1)
+    _close(p[:, :V], ref.detach(), msg="probs")
+    assert torch.count_nonzero(p[:, V:]) == 0
+    dp = torch.zeros((rows, ld), dtype=BF16)
+    dp[:, :V] = _rand((rows, V), 2)
+    ref.backward(dp[:, :V].float())
+    base = torch.zeros((rows, ld), dtype=BF16)
+    base[:, :V] = _rand((rows, V), 3, 0.01)
+    out = base.clone().cuda()
+    pr = torch.zeros((rows, ld), dtype=BF16)
+    pr[:, :V] = ref.detach().to(BF16)
+    ops.softmax_rows_bwd(pr.cuda(), dp.cuda(), out, V, accumulate=True)
+    _close(out[:, :V], x.grad + base[:, :V].float(), rel=2e-2, msg="dlogits")
+    out2 = torch.full((rows, ld), 7.0, dtype=BF16, device="cuda")
+    ops.softmax_rows_bwd(pr.cuda(), dp.cuda(), out2, V, accumulate=False)
+    _close(out2[:, :V], x.grad, rel=2e-2, msg="dlogits (overwrite)")

@@ -22,7 +22,7 @@ def rel_l2(a: torch.Tensor, b: torch.Tensor) -> float:
     return float((a - b).norm() / (b.norm() + 1e-12))
 
 
-def _reference_bf16_noise(pds, cfg_kw, sd, feats, lens, tokens):
+def _reference_bf16_noise(pds, cfg_kw, sd, feats, lens, tokens, tgt_tokens=None):
     """Per-parameter gradient rel-L2 of the REFERENCE'S OWN low-precision mode — the whole model cast with
     ``.to(torch.bfloat16)`` (trainer.py:85-90), here the oracle restatement on CPU — against its fp32
     run on the same inputs and weights.  It measures how far bf16 round-off alone moves each gradient (ReLU/GLU gates
@@ -39,7 +39,12 @@ def _reference_bf16_noise(pds, cfg_kw, sd, feats, lens, tokens):
         m.train()
         m = m.to(dt)
         o = m(feats.to(dt), lens)
-        OE.ctc_criterion_loss(o["ctc_logit"][0], o["encoder_padding_mask"][0], tokens).backward()
+        if tgt_tokens is None:
+            OE.ctc_criterion_loss(o["ctc_logit"][0], o["encoder_padding_mask"][0], tokens).backward()
+        else:
+            OE.ctc_criterion_total(o, tokens, tgt_tokens, ctc_weight=cfg_kw["ctc_weight"], xctc_weight=cfg_kw["xctc_weight"],
+                                   inter_ctc_weight=cfg_kw["inter_ctc_weight"],
+                                   inter_xctc_weight=cfg_kw["inter_xctc_weight"]).backward()
         out.append({k: p.grad.double() for k, p in m.named_parameters()})
     return {k: float((out[1][k] - out[0][k]).norm() / (out[0][k].norm() + 1e-12)) for k in out[0]}
 
@@ -57,17 +62,19 @@ def _engine_for(cfg_kw, sd):
     return eng
 
 
-def _run(eng, feats, lens, tokens):
+def _run(eng, feats, lens, tokens, tgt_tokens=None):
     B, T, _ = feats.shape
     tg, tl = eng.strip_targets(tokens)
-    P = eng.plan(B, T, tg.shape[1])
-    eng.set_inputs(P, feats=feats, src_lengths=lens.to(torch.int32), targets=tg, target_lengths=tl)
+    xt, xl = eng.strip_targets(tgt_tokens) if tgt_tokens is not None else (None, None)
+    P = eng.plan(B, T, max(tg.shape[1], xt.shape[1] if xt is not None else 0))
+    eng.set_inputs(P, feats=feats, src_lengths=lens.to(torch.int32), targets=tg, target_lengths=tl,
+                   xtargets=xt, xtarget_lengths=xl)
     eng.train_step(P)
     torch.cuda.synchronize()
     return P
 
 
-@pytest.mark.parametrize("case", ["c1_small", "c4_small", "c3_small"])
+@pytest.mark.parametrize("case", ["c1_small", "c4_small", "c3_small", "c5_small"])
 def test_engine_matches_reference_golden(cuda_lib, case):
     from oracle.make_golden import ENC_CASES, seeded_state_dict, state_checksum
     fx = np.load(GOLDEN / f"enc_{case}.npz")
@@ -86,13 +93,20 @@ def test_engine_matches_reference_golden(cuda_lib, case):
                    attn_type=spec.get("encoder_attention_type", "selfattn"),
                    encoder_activation_fn=spec.get("encoder_activation_fn", "relu"),
                    layer_padding_mask=spec.get("layer_padding_mask", False))
+        if "xctc_weight" in spec:
+            csv = lambda k: tuple(int(v) for v in spec[k].split(","))
+            cfg.update(tgt_vocab=spec["vocab"], ctc_weight=spec["ctc_weight"], xctc_weight=spec["xctc_weight"],
+                       inter_ctc_layers=csv("inter_ctc_layers"), inter_ctc_weight=spec["inter_ctc_weight"],
+                       inter_xctc_layers=csv("inter_xctc_layers"), inter_xctc_weight=spec["inter_xctc_weight"],
+                       ctc_pae=spec["ctc_pae"], xctc_pae=spec["xctc_pae"], pae_unnorm_input=spec["pae_unnorm_input"])
     shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
     sd = seeded_state_dict(shapes, int(fx["seed"]))
     assert state_checksum(sd) == str(fx["weights_sha256"]), "weight generator drifted from the fixture"
     eng = _engine_for(cfg, sd)
     assert sorted(eng.state_dict().keys()) == sorted(shapes), "parameter names differ from the reference state_dict"
     feats, lens, tokens = (torch.from_numpy(fx[k]) for k in ("feats", "lens", "tokens"))
-    P = _run(eng, feats, lens, tokens)
+    tgt_tokens = torch.from_numpy(fx["tgt_tokens"]) if "tgt_tokens" in fx.files else None
+    P = _run(eng, feats, lens, tokens, tgt_tokens)
     B, T2, C, V = P.B, P.T2, eng.cfg.embed_dim, eng.cfg.vocab
     enc = P.enc_out.float().view(B, T2, C).transpose(0, 1).cpu()
     logit = P.logits.float().view(B, T2, P.ldv)[..., :V].transpose(0, 1).cpu()
@@ -104,7 +118,14 @@ def test_engine_matches_reference_golden(cuda_lib, case):
     loss, ref_loss = float(P.loss.item()), float(fx["loss"])
     assert abs(loss - ref_loss) <= 1e-2 * abs(ref_loss), (loss, ref_loss)
     grads = eng.grads()
-    noise = _reference_bf16_noise(spec.get("family") == "pds", cfg, sd, feats, lens, tokens)
+    noise = _reference_bf16_noise(spec.get("family") == "pds", cfg, sd, feats, lens, tokens, tgt_tokens)
+    if tgt_tokens is not None:        # the other logits of the dual-head / inter-CTC encoder (valid frames)
+        Tv = fx["ctc_logit"].shape[0]
+        pairs = [(P.heads[1].logits, "xctc_logit"), (P.inter[(3, 0)].logits, "inter_ctc_logit_last"),
+                 (P.inter[(3, 1)].logits, "inter_xctc_logit_last")]
+        for mine, key in pairs:
+            got = mine.float().view(B, T2, -1)[..., :V].transpose(0, 1).cpu()
+            assert rel_l2(got[valid], torch.from_numpy(fx[key])[valid]) <= 3e-2, key
     for key in fx.files:
         if key.startswith("grad::"):
             name = key[6:]

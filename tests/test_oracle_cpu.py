@@ -81,7 +81,7 @@ def test_greedy_oracle_pad_to_blank_before_collapse():
     assert [t.tolist() for t in toks] == [[5, 6], [7]]
 
 
-@pytest.mark.parametrize("case", ["c1_small", "c4_small", "c3_small"])
+@pytest.mark.parametrize("case", ["c1_small", "c4_small", "c3_small", "c5_small"])
 def test_encoder_oracle_matches_reference_golden(case):
     """oracle/encoder.py reproduces the reference's S2TTransformerEncoder + ctc criterion outputs and gradients."""
     from oracle import encoder as OE
@@ -102,7 +102,15 @@ def test_encoder_oracle_matches_reference_golden(case):
     orc.train()
     feats, lens, tokens = (torch.from_numpy(fx[k]) for k in ("feats", "lens", "tokens"))
     out = orc(feats, lens)
-    loss = OE.ctc_criterion_loss(out["ctc_logit"][0], out["encoder_padding_mask"][0], tokens)
+    if "tgt_tokens" in fx.files:
+        w = [float(v) for v in fx["loss_weights"]]
+        loss = OE.ctc_criterion_total(out, tokens, torch.from_numpy(fx["tgt_tokens"]), ctc_weight=w[0], xctc_weight=w[1],
+                                      inter_ctc_weight=w[2], inter_xctc_weight=w[3])
+        assert (out["xctc_logit"][0].detach() - torch.from_numpy(fx["xctc_logit"])).abs().max() < 1e-4
+        assert (out["inter_ctc_logits"][-1][0].detach() - torch.from_numpy(fx["inter_ctc_logit_last"])).abs().max() < 1e-4
+        assert (out["inter_xctc_logits"][-1].detach() - torch.from_numpy(fx["inter_xctc_logit_last"])).abs().max() < 1e-4
+    else:
+        loss = OE.ctc_criterion_loss(out["ctc_logit"][0], out["encoder_padding_mask"][0], tokens)
     loss.backward()
     assert torch.equal(out["encoder_padding_mask"][0], torch.from_numpy(fx["padding_mask"]))
     assert (out["encoder_out"][0].detach() - torch.from_numpy(fx["encoder_out"])).abs().max() < 1e-4
