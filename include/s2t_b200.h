@@ -312,11 +312,13 @@ int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, const float* ls
 /*
  * Greedy CTC: argmax over V (lowest index on ties), padded frames -> blank, collapse repeats,
  * drop blank.  tokens int32 [B][T] (first out_lengths[b] valid, rest -1); frame_ids int32 [B][T]
- * (required) receives the per-frame argmax after pad->blank.
+ * (required) receives the per-frame argmax after pad->blank.  scores fp32 [B] (optional, with the
+ * fp32 [B][T] scratch frame_lp) = -sum_t [argmax_t != blank] max_v log_softmax(logits[b][t])[v] over
+ * ALL T frames: the hypothesis score of CTCDecoder.generate (s2t_ctc.py:325-332, quirk A14).
  */
 int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, const int* input_lengths,
                    int batch, int T, int V, int blank, int* tokens, int* out_lengths,
-                   int* frame_ids, void* stream);
+                   int* frame_ids, float* scores, float* frame_lp, void* stream);
 
 #ifdef __cplusplus
 }

@@ -117,3 +117,14 @@ def greedy_decode(logits: np.ndarray, input_lengths, blank: int = 0) -> List[np.
         row = row[keep]
         out.append(row[row != blank].astype(np.int64))
     return out
+
+
+def greedy_scores(logits: np.ndarray, blank: int = 0) -> np.ndarray:
+    """Hypothesis score of CTCDecoder.generate (s2t_ctc.py:322-332, quirk A14): topk(1) of the fp32 log-softmax over
+    ALL frames (the padding mask is applied to the indices only), blank positions filled with the VALUE ``blank``
+    (0), score = -sum_t.  float64 here."""
+    lp = log_softmax(np.asarray(logits, dtype=np.float64))
+    top = lp.max(axis=-1)
+    idx = lp.argmax(axis=-1)
+    real = np.where(idx == blank, float(blank), top)
+    return -real.sum(axis=-1)

@@ -17,6 +17,7 @@ PKG_DIR = Path(__file__).resolve().parent
 CSRC = PKG_DIR / "csrc"
 BUILD_DIR = PKG_DIR / "build"
 LIB_PATH = PKG_DIR / "libs2t_b200.so"
+STAMP_PATH = PKG_DIR / "libs2t_b200.stamp"     # digest of the sources the .so was built from (travels with it)
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -42,9 +43,24 @@ def _digest(paths) -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
+def _inputs():
     sources = sorted(CSRC.glob("*.cu"))
     headers = sorted(CSRC.glob("*.cuh")) + [PKG_DIR.parent / "include" / "s2t_b200.h"]
+    return sources, headers
+
+
+def source_digest() -> str:
+    sources, headers = _inputs()
+    return _digest(headers) + _digest(sources)
+
+
+def is_stale() -> bool:
+    """True when libs2t_b200.so is missing or was built from other sources than the ones in the tree."""
+    return not (LIB_PATH.exists() and STAMP_PATH.exists() and STAMP_PATH.read_text() == source_digest())
+
+
+def build(force: bool = False, verbose: bool = False) -> Path:
+    sources, headers = _inputs()
     BUILD_DIR.mkdir(exist_ok=True)
     stamp = BUILD_DIR / "stamp.txt"
     hdr_digest = _digest(headers)
@@ -81,6 +97,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         if res.returncode != 0:
             raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
         stamp.write_text(hdr_digest)
+    STAMP_PATH.write_text(source_digest())
     return LIB_PATH
 
 

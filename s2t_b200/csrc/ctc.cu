@@ -363,35 +363,52 @@ __global__ void ctc_occupancy_kernel(const int* __restrict__ targets, long long 
 // ---------------------------------------------------------------------------------------------
 // greedy decode
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void argmax_take(float v, int i, float& best, int& bi) {
+  if (v > best || (v == best && i < bi)) {
+    best = v;
+    bi = i;
+  }
+}
+
+// One CTA per (b,t) row: argmax over V (lowest index on ties; 16-byte loads for bf16).  Padded frames decode to
+// blank (s2t_ctc.py:329-338).  With frame_lp != NULL every row (padded ones too, as the reference's topk runs before
+// the padding mask, s2t_ctc.py:325-331) also gets frame_lp = argmax != blank ? max_logit - logsumexp : 0.
 __global__ void __launch_bounds__(256)
 ctc_argmax_kernel(const void* __restrict__ logits, int is_bf16, long long ldv,
                   const int* __restrict__ in_len, int T, int V, int blank,
-                  int* __restrict__ frame_ids) {
+                  int* __restrict__ frame_ids, float* __restrict__ frame_lp) {
   __shared__ float s_v[8];
   __shared__ int s_i[8];
+  __shared__ float s_best;
   const long long row = blockIdx.x;
   const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
-  if (t >= in_len[b]) {  // padded frames decode to blank (s2t_ctc.py:329-338)
+  const bool padded = t >= in_len[b];
+  if (padded && frame_lp == nullptr) {
     if (threadIdx.x == 0) frame_ids[row] = blank;
     return;
   }
   float best = kNegInf;
   int bi = 0x7fffffff;
-  for (int i = threadIdx.x; i < V; i += 256) {
-    const float v = load_logit(logits, is_bf16, row * ldv + i);
-    if (v > best || (v == best && i < bi)) {
-      best = v;
-      bi = i;
+  if (is_bf16) {
+    const __nv_bfloat16* x = reinterpret_cast<const __nv_bfloat16*>(logits) + row * ldv;
+    const int nv = V >> 3;
+    for (int i = threadIdx.x; i < nv; i += 256) {
+      const uint4 v = *reinterpret_cast<const uint4*>(x + i * 8);
+      const float f[8] = {bf16_lo(v.x), bf16_hi(v.x), bf16_lo(v.y), bf16_hi(v.y),
+                          bf16_lo(v.z), bf16_hi(v.z), bf16_lo(v.w), bf16_hi(v.w)};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) argmax_take(f[j], i * 8 + j, best, bi);
     }
+    for (int i = (nv << 3) + threadIdx.x; i < V; i += 256) argmax_take(__bfloat162float(x[i]), i, best, bi);
+  } else {
+    const float* x = reinterpret_cast<const float*>(logits) + row * ldv;
+    for (int i = threadIdx.x; i < V; i += 256) argmax_take(x[i], i, best, bi);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float v2 = __shfl_xor_sync(0xffffffffu, best, o);
     const int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
-    if (v2 > best || (v2 == best && i2 < bi)) {
-      best = v2;
-      bi = i2;
-    }
+    argmax_take(v2, i2, best, bi);
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (lane == 0) {
@@ -400,18 +417,33 @@ ctc_argmax_kernel(const void* __restrict__ logits, int is_bf16, long long ldv,
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    for (int w = 1; w < 8; ++w)
-      if (s_v[w] > best || (s_v[w] == best && s_i[w] < bi)) {
-        best = s_v[w];
-        bi = s_i[w];
-      }
-    frame_ids[row] = (bi == 0x7fffffff) ? blank : bi;
+    for (int w = 1; w < 8; ++w) argmax_take(s_v[w], s_i[w], best, bi);
+    if (bi == 0x7fffffff) bi = blank;
+    frame_ids[row] = padded ? blank : bi;
+    s_best = best;
+    s_i[0] = bi;
+  }
+  if (frame_lp == nullptr) return;
+  __syncthreads();
+  best = s_best;
+  bi = s_i[0];
+  float sum = 0.f;
+  for (int i = threadIdx.x; i < V; i += 256) sum += __expf(load_logit(logits, is_bf16, row * ldv + i) - best);
+  sum = warp_sum(sum);
+  __syncthreads();
+  if (lane == 0) s_v[warp] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float tot = 0.f;
+    for (int w = 0; w < 8; ++w) tot += s_v[w];
+    frame_lp[row] = (bi != blank) ? -logf(tot) : 0.f;   // max_logit - lse = -log(sum exp(x - max))
   }
 }
 
 // one warp per utterance: keep[t] = id != blank && (t == 0 || id != id[t-1]); ballot prefix compaction
 __global__ void ctc_collapse_kernel(const int* __restrict__ frame_ids, int T, int blank,
-                                    int* __restrict__ tokens, int* __restrict__ out_len) {
+                                    int* __restrict__ tokens, int* __restrict__ out_len,
+                                    const float* __restrict__ frame_lp, float* __restrict__ scores) {
   const int b = blockIdx.x;
   const int lane = threadIdx.x;
   const int* ids = frame_ids + static_cast<long long>(b) * T;
@@ -431,6 +463,12 @@ __global__ void ctc_collapse_kernel(const int* __restrict__ frame_ids, int T, in
   }
   for (int t = count + lane; t < T; t += 32) out[t] = -1;
   if (lane == 0) out_len[b] = count;
+  if (scores != nullptr) {  // score = -sum_t [argmax_t != blank] max log-prob (s2t_ctc.py:330-332, quirk A14)
+    float acc = 0.f;
+    for (int t = lane; t < T; t += 32) acc += frame_lp[static_cast<long long>(b) * T + t];
+    acc = warp_sum(acc);
+    if (lane == 0) scores[b] = -acc;
+  }
 }
 
 }  // namespace s2t
@@ -514,14 +552,17 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
 
 extern "C" int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, const int* input_lengths,
                               int batch, int T, int V, int blank, int* tokens, int* out_lengths,
-                              int* frame_ids, void* stream) {
+                              int* frame_ids, float* scores, float* frame_lp, void* stream) {
   S2T_REQUIRE(logits && input_lengths && tokens && out_lengths && frame_ids,
               "s2t_ctc_greedy: null pointer (frame_ids is a required [B][T] scratch/output)");
+  S2T_REQUIRE((scores == nullptr) == (frame_lp == nullptr),
+              "s2t_ctc_greedy: scores [B] and frame_lp [B][T] go together");
+  S2T_REQUIRE(ldv % (is_bf16 ? 8 : 1) == 0, "s2t_ctc_greedy: bf16 rows must be 16-byte aligned (ldv % 8 == 0)");
   if (batch <= 0 || T <= 0) return 0;
   ctc_argmax_kernel<<<batch * T, 256, 0, ST(stream)>>>(logits, is_bf16, ldv, input_lengths, T, V, blank,
-                                                      frame_ids);
+                                                      frame_ids, frame_lp);
   S2T_LAUNCH_CHECK();
-  ctc_collapse_kernel<<<batch, 32, 0, ST(stream)>>>(frame_ids, T, blank, tokens, out_lengths);
+  ctc_collapse_kernel<<<batch, 32, 0, ST(stream)>>>(frame_ids, T, blank, tokens, out_lengths, frame_lp, scores);
   S2T_LAUNCH_CHECK();
   return 0;
 }

@@ -1356,8 +1356,9 @@ class S2TEncoderEngine:
         else:
             self.forward(P)
 
-    def greedy_decode(self, P: Plan, head: int = 0):
+    def greedy_decode(self, P: Plan, head: int = 0, with_scores: bool = False):
         """CTCDecoder greedy (s2t_ctc.py:312-347) on the logits of head ``head`` (0 = CTC, 1 = XCTC): int32 tokens
         [B, T'] (-1 padded), lengths, per-frame ids."""
         hs = self.heads[head]
-        return ops.ctc_greedy(P.heads[head].logits.view(P.B, P.T2, hs.ldv), P.out_len, hs.V, self.cfg.blank)
+        return ops.ctc_greedy(P.heads[head].logits.view(P.B, P.T2, hs.ldv), P.out_len, hs.V, self.cfg.blank,
+                              with_scores=with_scores)

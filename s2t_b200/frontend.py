@@ -109,3 +109,61 @@ def _get_torchaudio_fbank(waveform, sample_rate, n_bins: int = 80) -> Optional[n
     n = torch.tensor([w.shape[1]], dtype=torch.int32, device=w.device)
     feats, _ = fbank_batch(w, n, n_bins)
     return feats[0].cpu().numpy()
+
+
+def get_fbank(path_or_fp, n_bins: int = 80, offset=None, size=None, get_waveform=None) -> np.ndarray:
+    """Drop-in for ``get_fbank`` (audio_utils.py:82-103): decode with the reference's ``get_waveform(...,
+    normalization=False)`` (int16 scale, quirk A1) — passed in, or imported from fairseq when available — and compute
+    the features on the GPU.  Returns (T, n_bins) float32 numpy like the reference."""
+    if get_waveform is None:
+        try:
+            from fairseq.data.audio.audio_utils import get_waveform  # type: ignore
+        except Exception as e:  # pragma: no cover
+            raise ImportError("get_fbank needs the reference's get_waveform (soundfile decoding stays with fairseq); "
+                              "pass get_waveform=") from e
+    sound, sample_rate = get_waveform(path_or_fp, normalization=False, offset=offset, size=size)
+    sound = np.asarray(sound)
+    if sound.ndim == 2:                      # (channels, N): the reference merges channels to mono (:70-72)
+        sound = sound.mean(axis=0)
+    return _get_torchaudio_fbank(sound, sample_rate, n_bins)
+
+
+class UtteranceCMVNB200:
+    """``UtteranceCMVN`` (feature_transforms/utterance_cmvn.py:8-45) on the device: (T, F) float32 numpy in / out."""
+
+    def __init__(self, norm_means: bool = True, norm_vars: bool = True):
+        self.norm_means, self.norm_vars = norm_means, norm_vars
+
+    def __call__(self, x: np.ndarray) -> np.ndarray:
+        t = torch.as_tensor(np.ascontiguousarray(x), dtype=torch.float32).unsqueeze(0).cuda()
+        n = torch.tensor([t.shape[1]], dtype=torch.int32, device=t.device)
+        return ops.cmvn_utt(t, n, norm_means=self.norm_means, norm_vars=self.norm_vars)[0].cpu().numpy()
+
+
+class GlobalCMVNB200:
+    """``GlobalCMVN`` (feature_transforms/global_cmvn.py:8-29): (x - mean) / std with ``.npz`` statistics."""
+
+    def __init__(self, stats_npz_path: Optional[str] = None, mean=None, std=None):
+        if stats_npz_path is not None:
+            stats = np.load(stats_npz_path)
+            mean, std = stats["mean"], stats["std"]
+        self.mean = torch.as_tensor(np.asarray(mean), dtype=torch.float32).cuda()
+        self.std = torch.as_tensor(np.asarray(std), dtype=torch.float32).cuda()
+
+    def __call__(self, x: np.ndarray) -> np.ndarray:
+        t = torch.as_tensor(np.ascontiguousarray(x), dtype=torch.float32).unsqueeze(0).cuda()
+        n = torch.tensor([t.shape[1]], dtype=torch.int32, device=t.device)
+        return ops.cmvn_global(t, n, self.mean, self.std)[0].cpu().numpy()
+
+
+def patch_audio_utils() -> bool:
+    """Replace the reference's fbank implementation in place (what the ``--user-dir`` module does for the data path):
+    ``fairseq.data.audio.audio_utils._get_kaldi_fbank`` -> None (skip PyKaldi) and ``_get_torchaudio_fbank`` -> ours, so
+    ``get_fbank`` and every caller (speech_to_text_dataset.py:204-226, data_utils.py:86-88) use the CUDA kernel."""
+    try:
+        from fairseq.data.audio import audio_utils  # type: ignore
+    except Exception:
+        return False
+    audio_utils._get_kaldi_fbank = lambda *a, **k: None
+    audio_utils._get_torchaudio_fbank = _get_torchaudio_fbank
+    return True

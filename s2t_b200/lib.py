@@ -83,7 +83,7 @@ SIGNATURES = {
     "s2t_row_lse": (_i, [_vp, _i, _ll, _i, _i, _vp, _vp]),
     "s2t_ctc_workspace_bytes": (_ll, [_i, _i, _i]),
     "s2t_ctc_loss": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _ll, _vp]),
-    "s2t_ctc_greedy": (_i, [_vp, _i, _ll, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "s2t_ctc_greedy": (_i, [_vp, _i, _ll, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 
 
@@ -99,11 +99,15 @@ def load() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if not LIB_PATH.exists():
-        raise S2TLibraryError(
-            f"{LIB_PATH} is missing: build it with `python -m s2t_b200.build` "
-            "(or __graft_entry__.build()). s2t_b200 has no CPU fallback."
-        )
+    from . import build as _build
+    if _build.is_stale():
+        # a library built from other sources than the tree's (or none): rebuild in place, never run a stale ABI
+        try:
+            _build.build()
+        except Exception as e:
+            raise S2TLibraryError(
+                f"{LIB_PATH} is missing or stale and could not be rebuilt ({e}); build it with "
+                "`python -m s2t_b200.build` (or __graft_entry__.build()). s2t_b200 has no CPU fallback.") from e
     lib = C.CDLL(str(LIB_PATH))
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported

@@ -530,12 +530,17 @@ def ctc_loss(logits: torch.Tensor, targets: torch.Tensor, input_lengths: torch.T
     return nll, (dlogits if need_grad else None)
 
 
-def ctc_greedy(logits: torch.Tensor, input_lengths: torch.Tensor, V: int, blank: int = 0):
-    """logits [B, T, ldv] -> (tokens int32 [B, T] padded with -1, lengths int32 [B], frame_ids int32 [B, T])."""
+def ctc_greedy(logits: torch.Tensor, input_lengths: torch.Tensor, V: int, blank: int = 0, with_scores: bool = False):
+    """logits [B, T, ldv] -> (tokens int32 [B, T] padded with -1, lengths int32 [B], frame_ids int32 [B, T]) and, with
+    ``with_scores``, the hypothesis scores fp32 [B] of CTCDecoder.generate (s2t_ctc.py:325-332)."""
     B, T, ldv = logits.shape
     tokens = torch.empty((B, T), device=logits.device, dtype=torch.int32)
     lens = torch.empty((B,), device=logits.device, dtype=torch.int32)
     frame_ids = torch.empty((B, T), device=logits.device, dtype=torch.int32)
+    scores = torch.empty((B,), device=logits.device, dtype=torch.float32) if with_scores else None
+    frame_lp = torch.empty((B, T), device=logits.device, dtype=torch.float32) if with_scores else None
     _call("s2t_ctc_greedy", _p(logits), int(logits.dtype == BF16), ldv, _p(input_lengths), B, T, V, blank,
-          _p(tokens), _p(lens), _p(frame_ids), _stream())
+          _p(tokens), _p(lens), _p(frame_ids), _p(scores), _p(frame_lp), _stream())
+    if with_scores:
+        return tokens, lens, frame_ids, scores
     return tokens, lens, frame_ids

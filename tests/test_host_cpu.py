@@ -129,3 +129,41 @@ def test_bucketed_allreduce_world2_gloo():
     for rank, ok, launched in res:
         assert ok, f"rank {rank}: averaged gradients differ"
         assert launched[0][1] == 1000 and launched[-1][0] == 0 and len(launched) <= 3
+
+
+def test_plugin_host_logic_and_registration(monkeypatch):
+    """plugin.register() patches the reference's registries (a fake fairseq package stands in: fairseq itself is not
+    importable here); host-side helpers of the decode / criterion path."""
+    import sys
+    import types
+    from s2t_b200 import decode, lib, plugin
+    assert plugin.register() == {"models": [], "criterions": []}            # no fairseq: nothing to patch
+    assert plugin._bucket(0) == 32 and plugin._bucket(33) == 64
+    assert decode.edit_distance([1, 2, 3], [1, 3]) == 1 and decode.edit_distance([], [4, 5]) == 2
+    assert decode.post_process("▁he llo ▁wor ld", "sentencepiece") == "hello world"
+    if not torch.cuda.is_available():
+        from argparse import Namespace
+        with pytest.raises(lib.S2TLibraryError):
+            plugin.S2TTransformerEncoderB200(Namespace(encoder_embed_dim=256, encoder_ffn_embed_dim=2048,
+                                                       encoder_attention_heads=4, encoder_layers=2, dropout=0.1), None)
+    # fake registries
+    fs, models, crits = types.ModuleType("fairseq"), types.ModuleType("fairseq.models"), types.ModuleType("fairseq.criterions")
+
+    class M:   # a registered model class with the reference's build_encoder hook
+        @classmethod
+        def build_encoder(cls, args, task=None, embed_tokens=None):
+            return "reference encoder"
+
+    models.ARCH_MODEL_REGISTRY = {"s2t_transformer_s": M, "pdss2t_transformer_s_8": type("P", (M,), {}),
+                                  "s2t_ctc": type("C", (M,), {}),
+                                  "transformer": type("T", (), {"build_encoder": classmethod(lambda cls, a: "reference encoder")})}
+    crits.CRITERION_REGISTRY = {"ctc": object, "cross_entropy": object}
+    fs.models, fs.criterions = models, crits
+    monkeypatch.setitem(sys.modules, "fairseq", fs)
+    monkeypatch.setitem(sys.modules, "fairseq.models", models)
+    monkeypatch.setitem(sys.modules, "fairseq.criterions", crits)
+    monkeypatch.setattr(plugin, "_HAVE_FAIRSEQ", True)
+    done = plugin.register()
+    assert sorted(done["models"]) == ["pdss2t_transformer_s_8", "s2t_ctc", "s2t_transformer_s"] and done["criterions"] == ["ctc"]
+    assert crits.CRITERION_REGISTRY["ctc"] is plugin.CtcCriterionB200 and crits.CRITERION_REGISTRY["cross_entropy"] is object
+    assert models.ARCH_MODEL_REGISTRY["transformer"].build_encoder(None) == "reference encoder"   # untouched

@@ -1,0 +1,145 @@
+"""The reference's plugin surface on the B200 engine: FairseqEncoder dict contract, the ctc criterion
+triple with autograd hand-off of the flat gradient, greedy CTCDecoder.  Checked against the reference golden fixtures
+and the CPU oracle."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+GOLDEN = Path(__file__).resolve().parent / "golden"
+
+REF_KEYS = {"encoder_out", "ctc_logit", "inter_ctc_logits", "xctc_logit", "inter_xctc_logits", "encoder_padding_mask",
+            "mixup", "encoder_embedding", "encoder_states", "src_tokens", "src_lengths"}      # s2t_transformer.py:2142-2154
+
+
+def _args(case):
+    from oracle.make_golden import ENC_CASES, reference_args
+    spec = dict(ENC_CASES[case])
+    args = reference_args(**spec)
+    for k, v in dict(encoder_embed_dim=256, encoder_ffn_embed_dim=2048, encoder_layers=12, encoder_attention_heads=4,
+                     subsampling_layers=2, subsampling_filter=1024, subsampling_kernel=5, subsampling_stride=2).items():
+        if not hasattr(args, k):
+            setattr(args, k, v)
+    return args, spec
+
+
+def _model(case):
+    from oracle.make_golden import seeded_state_dict
+    from s2t_b200 import plugin
+    fx = np.load(GOLDEN / f"enc_{case}.npz")
+    args, spec = _args(case)
+    if spec.get("family") == "pds":
+        args.encoder_type = "pds"
+    args.b200_cuda_graph = False
+    model = plugin.S2TCTCModelB200.build_model(args, None)
+    shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
+    model.encoder.load_state_dict(seeded_state_dict(shapes, int(fx["seed"])))
+    return model, fx
+
+
+def _sample(fx):
+    s = {"net_input": {"src_tokens": torch.from_numpy(fx["feats"]).cuda(), "src_lengths": torch.from_numpy(fx["lens"]).cuda(),
+                       "prev_output_tokens": None},
+         "transcript": {"tokens": torch.from_numpy(fx["tokens"])}, "target": torch.from_numpy(fx["tokens"])}
+    if "tgt_tokens" in fx.files:
+        s["target"] = torch.from_numpy(fx["tgt_tokens"])
+    return s
+
+
+@pytest.mark.parametrize("case", ["c1_small", "c3_small", "c5_small"])
+def test_encoder_forward_contract(cuda_lib, case):
+    model, fx = _model(case)
+    model.eval()
+    s = _sample(fx)
+    out = model(**s["net_input"])
+    assert set(out) == REF_KEYS
+    ref_enc, ref_logit = torch.from_numpy(fx["encoder_out"]), torch.from_numpy(fx["ctc_logit"])
+    enc, logit, pad = out["encoder_out"][0], out["ctc_logit"][0], out["encoder_padding_mask"][0]
+    assert tuple(enc.shape) == tuple(ref_enc.shape) and tuple(logit.shape) == tuple(ref_logit.shape)   # T' x B x C / V
+    assert pad.dtype == torch.bool and torch.equal(pad.cpu(), torch.from_numpy(fx["padding_mask"]))
+    valid = ~torch.from_numpy(fx["padding_mask"]).T
+    rel = lambda a, b: float((a.float().cpu()[valid] - b[valid]).norm() / b[valid].norm())
+    tol = 3e-2 if case == "c5_small" else 2e-2   # eval-mode BatchNorm (running stats 0/1) differs from the train-mode fixture
+    if case != "c5_small":
+        assert rel(enc, ref_enc) <= tol and rel(logit, ref_logit) <= 3e-2
+    else:
+        assert len(out["inter_ctc_logits"]) == 2 and isinstance(out["inter_ctc_logits"][0], list)
+        assert len(out["inter_xctc_logits"]) == 2 and torch.is_tensor(out["inter_xctc_logits"][0])
+        assert tuple(out["xctc_logit"][0].shape) == tuple(ref_logit.shape)
+    lp = model.get_normalized_probs(out, log_probs=True)
+    assert lp.dtype == torch.float32 and torch.allclose(lp.exp().sum(-1), torch.ones_like(lp[..., 0]), atol=1e-3)
+    # reorder_encoder_out (s2t_transformer.py:2156-2208)
+    order = torch.tensor([2, 0], device="cuda")
+    ro = model.encoder.reorder_encoder_out(out, order)
+    assert torch.equal(ro["encoder_out"][0], enc.index_select(1, order))
+    assert torch.equal(ro["encoder_padding_mask"][0], pad.index_select(0, order))
+
+
+@pytest.mark.parametrize("case", ["c1_small", "c5_small"])
+def test_criterion_forward_backward(cuda_lib, case):
+    from s2t_b200 import plugin
+    model, fx = _model(case)
+    crit = plugin.CtcCriterionB200(None, None)
+    model.train()
+    loss, sample_size, log = crit(model, _sample(fx))
+    # the fixture's c1 loss is the bare CTC loss; the criterion applies ctc_weight (criterions/ctc.py:1004), which the
+    # c5 fixture's total already contains
+    ref = float(fx["loss"]) * (_args(case)[0].ctc_weight if case == "c1_small" else 1.0)
+    assert loss.dim() == 0 and loss.requires_grad
+    assert abs(loss.item() - ref) <= 1e-2 * abs(ref), (loss.item(), ref)
+    assert sample_size == log["sample_size"] == log["ntokens"] and log["nsentences"] == fx["feats"].shape[0]
+    assert {"loss", "ntokens", "nsentences", "sample_size", "ctc_loss"} <= set(log)
+    (loss * 4.0).backward()                               # fairseq's loss scaling reaches the flat gradient
+    enc = model.encoder
+    g = enc.flat.grad
+    assert g is not None and g.shape == enc.flat.shape
+    assert torch.allclose(g.float(), enc.engine.store.grad.float() * 4.0, rtol=1e-2, atol=1e-6)
+    name = "ctc.ctc_projection.weight"
+    mine = enc.engine.grads()[name].cpu()
+    want = torch.from_numpy(fx["grad::" + name]) * (_args(case)[0].ctc_weight if case == "c1_small" else 1.0)
+    assert float((mine - want).norm() / want.norm()) <= 5e-2
+    # eval: no graph, no gradient, validation error counts present
+    model.eval()
+    with torch.no_grad():
+        l2, _, log2 = crit(model, _sample(fx))
+    assert not l2.requires_grad and np.isfinite(l2.item())
+    assert log2["c_total"] == int(((fx["tokens"] != 1) & (fx["tokens"] != 2)).sum()) and log2["c_errors"] >= 0
+
+
+def test_criterion_cuda_graph_path(cuda_lib):
+    """With b200_cuda_graph the criterion captures the fused step once per batch shape and replays it."""
+    from s2t_b200 import plugin
+    model, fx = _model("c1_small")
+    model.encoder.use_graph = True
+    crit = plugin.CtcCriterionB200(None, None)
+    model.train()
+    l1, _, _ = crit(model, _sample(fx))
+    l1.backward()
+    g1 = model.encoder.flat.grad.clone()
+    model.encoder.flat.grad = None
+    l2, _, _ = crit(model, _sample(fx))
+    l2.backward()
+    assert model.encoder._last_plan.graph is not None
+    assert torch.equal(l1, l2) and torch.equal(g1, model.encoder.flat.grad)      # dropout 0: replays are bit-identical
+
+
+def test_ctc_decoder_generate_bit_exact(cuda_lib):
+    from oracle import ctc as OC
+    from s2t_b200 import decode
+    model, fx = _model("c5_small")
+    gen = decode.CTCDecoderB200([model], None, None, blank_idx=0)
+    s = _sample(fx)
+    hyps = gen.generate([model], s)
+    P, eng = model.encoder._last_plan, model.encoder.engine
+    hs = eng.heads[-1]                                                     # target-side head decodes (s2t_ctc.py:265-271)
+    lg = P.heads[-1].logits.float().view(P.B, P.T2, hs.ldv)[..., : hs.V].cpu().numpy()
+    want = OC.greedy_decode(lg, P.out_len.cpu().numpy(), blank=0)
+    scores = OC.greedy_scores(lg, blank=0)
+    assert len(hyps) == P.B
+    for b, h in enumerate(hyps):
+        assert set(h[0]) == {"tokens", "score", "attention", "alignment", "positional_scores"}
+        assert h[0]["tokens"].dtype == torch.int64 and h[0]["tokens"].tolist() == [int(v) for v in want[b]]
+        assert abs(float(h[0]["score"]) - scores[b]) <= 1e-3 * abs(scores[b]) + 1e-3
+        assert len(h[0]["positional_scores"]) == len(want[b])
