@@ -116,10 +116,13 @@ int s2t_fbank_fwd(const float* wave, long long wave_ld, const int* num_samples, 
 /* per-utterance, per-bin mean/variance normalisation over the valid frames (E[x^2]-E[x]^2 variance
  * from pre-centring sums, floor 1e-10, utterance_cmvn.py:35-43).  feats fp32 [B] x in_bs +
  * [max_frames][in_ld]; out fp32 or bf16 [B] x out_bs + [max_frames][out_ld] (may alias feats when
- * fp32); frames >= num_frames[b] are written as zeros.                                            */
+ * fp32); frames >= num_frames[b] are written as zeros.  stats: fp32 [batch][2][n_mels] workspace that
+ * receives (mean, std) per utterance and bin; may be NULL when norm_means == norm_vars == 0 (the call
+ * is then a cast / copy with zero fill).                                                            */
 int s2t_cmvn_utt(const float* feats, long long in_ld, long long in_bs, void* out, int out_bf16,
                  long long out_ld, long long out_bs, const int* num_frames, int batch,
-                 int max_frames, int n_mels, int norm_means, int norm_vars, void* stream);
+                 int max_frames, int n_mels, int norm_means, int norm_vars, float* stats,
+                 void* stream);
 /* (x - mean) / std with global statistics (feature_transforms/global_cmvn.py:26-29)              */
 int s2t_cmvn_global(const float* feats, long long in_ld, long long in_bs, void* out, int out_bf16,
                     long long out_ld, long long out_bs, const int* num_frames, int batch,
@@ -131,13 +134,21 @@ int s2t_cmvn_global(const float* feats, long long in_ld, long long in_bs, void* 
 /* --------------------------------------------------------------------------------------------- */
 int s2t_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* stats,
                       int rows, int C, float eps, void* stream);
-/* dx = LN'(dy) (+ dx_residual if non-NULL).  dgamma/dbeta partials: fp32 [n_partials][2][C] in
- * `partials` (n_partials from s2t_layernorm_bwd_partials), reduced by this call into bf16
- * dgamma/dbeta (accumulate=1 adds to the existing values).                                        */
+/* dx = LN'(dy) (+ dx_residual if non-NULL); the per-CTA dgamma/dbeta partial sums go to `partials`,
+ * fp32 [n_partials][2][C] (n_partials from s2t_layernorm_bwd_partials).  Optional second output
+ * dx_drop = drop_scale * dropout(dx) with the regenerable Philox mask of (seed, stream_id): the
+ * gradient entering the next residual branch x + drop_scale * dropout(branch), so that branch's
+ * backward needs no separate dropout pass.                                                          */
 int s2t_layernorm_bwd_partials(int rows, int C);
 int s2t_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* stats,
-                      const void* dx_residual, void* dx, float* partials, void* dgamma,
-                      void* dbeta, int accumulate, int rows, int C, void* stream);
+                      const void* dx_residual, void* dx, float* partials, int rows, int C,
+                      void* dx_drop, float drop_p, float drop_scale, unsigned long long seed,
+                      unsigned int stream_id, const unsigned long long* seed_offset, void* stream);
+/* dgamma / dbeta (bf16 [C], either may be NULL) = sums of the partials written by s2t_layernorm_bwd
+ * for the same (rows, C); accumulate != 0 adds to the existing values.  A separate call so the
+ * caller can run it beside the dgrad chain.                                                         */
+int s2t_layernorm_bwd_reduce(const float* partials, int rows, int C, void* dgamma, void* dbeta,
+                             int accumulate, void* stream);
 
 /* --------------------------------------------------------------------------------------------- */
 /* Elementwise / data-movement kernels of the path                                                */

@@ -282,6 +282,119 @@ __global__ void ctc_alpha_beta_kernel(const int* __restrict__ targets, long long
   }
 }
 
+// Warp-resident lattice: one warp per (utterance, direction), lane l owns the NS consecutive states
+// [l*NS, (l+1)*NS) in registers, neighbours' edge states arrive by two warp shuffles per frame — no shared
+// memory and no block barrier on the T-step critical path (the recursion is latency-bound: T dependent steps).
+template <int NS>
+__global__ void __launch_bounds__(32)
+ctc_alpha_beta_warp_kernel(const int* __restrict__ targets, long long tgt_ld, const int* __restrict__ in_len,
+                           const int* __restrict__ tgt_len, int T, int Sp, int blank, CtcWs ws) {
+  __shared__ float s_fin[32 * NS];
+  const int b = blockIdx.x, lane = threadIdx.x;
+  const bool fwd = blockIdx.y == 0;
+  const int Tb = min(in_len[b], T);
+  const int S = tgt_len[b];
+  const int Se = 2 * S + 1;
+  const int* tgt = targets + b * tgt_ld;
+  if (Tb <= 0) {
+    if (fwd && lane == 0) ws.nll_raw[b] = (S == 0) ? 0.f : INFINITY;
+    return;
+  }
+  const float* lp = ws.lp_g + static_cast<long long>(b) * T * Sp;
+  float* lat = (fwd ? ws.alpha : ws.beta) + static_cast<long long>(b) * T * Sp;
+  const int s0 = lane * NS;
+  bool skip[NS];
+  float prev[NS];
+#pragma unroll
+  for (int k = 0; k < NS; ++k) {
+    const int s = s0 + k;
+    skip[k] = false;
+    if (s < Se && (s & 1)) {
+      if (fwd) skip[k] = s >= 3 && tgt[s >> 1] != tgt[(s >> 1) - 1];
+      else skip[k] = (s + 2 < Se) && tgt[s >> 1] != tgt[(s >> 1) + 1];
+    }
+  }
+  {
+    const int t = fwd ? 0 : Tb - 1;
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+      const int s = s0 + k;
+      float v = kNegInf;
+      if (s < Se && (fwd ? (s <= 1) : (s >= Se - 2))) v = lp[static_cast<long long>(t) * Sp + s];
+      prev[k] = v;
+      if (s < Se) lat[static_cast<long long>(t) * Sp + s] = v;
+    }
+  }
+  constexpr int kPf = 4;
+  float pf[kPf][NS];
+#pragma unroll
+  for (int d = 0; d < kPf; ++d) {
+    const int step = 1 + d;
+    const int t = fwd ? step : Tb - 1 - step;
+#pragma unroll
+    for (int k = 0; k < NS; ++k)
+      pf[d][k] = (step < Tb && s0 + k < Se) ? lp[static_cast<long long>(t) * Sp + s0 + k] : 0.f;
+  }
+  for (int step0 = 1; step0 < Tb; step0 += kPf) {
+#pragma unroll
+    for (int d = 0; d < kPf; ++d) {
+      const int step = step0 + d;
+      if (step < Tb) {  // warp-uniform
+        const int t = fwd ? step : Tb - 1 - step;
+        // n1 / n2: the states one and two positions outside this lane's range (towards s-1 fwd, s+1 bwd)
+        float n1, n2;
+        if (fwd) {
+          n1 = __shfl_up_sync(0xffffffffu, prev[NS - 1], 1);
+          n2 = NS >= 2 ? __shfl_up_sync(0xffffffffu, prev[NS >= 2 ? NS - 2 : 0], 1)
+                       : __shfl_up_sync(0xffffffffu, prev[0], 2);
+          if (lane == 0) n1 = n2 = kNegInf;
+          if (NS == 1 && lane == 1) n2 = kNegInf;
+        } else {
+          n1 = __shfl_down_sync(0xffffffffu, prev[0], 1);
+          n2 = NS >= 2 ? __shfl_down_sync(0xffffffffu, prev[NS >= 2 ? 1 : 0], 1)
+                       : __shfl_down_sync(0xffffffffu, prev[0], 2);
+          if (lane == 31) n1 = n2 = kNegInf;
+          if (NS == 1 && lane == 30) n2 = kNegInf;
+        }
+        float cur[NS];
+#pragma unroll
+        for (int k = 0; k < NS; ++k) {
+          const int s = s0 + k;
+          float bb, c;
+          if (fwd) {
+            bb = k >= 1 ? prev[k >= 1 ? k - 1 : 0] : n1;
+            c = k >= 2 ? prev[k >= 2 ? k - 2 : 0] : (k == 1 ? n1 : n2);
+          } else {
+            bb = k + 1 < NS ? prev[k + 1 < NS ? k + 1 : 0] : n1;
+            c = k + 2 < NS ? prev[k + 2 < NS ? k + 2 : 0] : (k + 2 == NS ? n1 : n2);
+          }
+          if (!skip[k]) c = kNegInf;
+          const float v = (s < Se) ? lse3(prev[k], bb, c) + pf[d][k] : kNegInf;   // states >= Se stay -inf
+          cur[k] = v;
+          if (s < Se) lat[static_cast<long long>(t) * Sp + s] = v;
+          const int nstep = step + kPf;
+          const int nt = fwd ? nstep : Tb - 1 - nstep;
+          pf[d][k] = (nstep < Tb && s < Se) ? lp[static_cast<long long>(nt) * Sp + s] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < NS; ++k) prev[k] = cur[k];
+      }
+    }
+  }
+  if (fwd) {
+#pragma unroll
+    for (int k = 0; k < NS; ++k) s_fin[s0 + k] = prev[k];
+    __syncwarp();
+    if (lane == 0) {
+      const float a = s_fin[Se - 1];
+      const float c = Se >= 2 ? s_fin[Se - 2] : kNegInf;
+      const float m = fmaxf(a, c);
+      const float ll = (m == kNegInf) ? kNegInf : m + logf(__expf(a - m) + __expf(c - m));
+      ws.nll_raw[b] = -ll;
+    }
+  }
+}
+
 // dlogits = scale * softmax(logits) for valid frames of feasible utterances, 0 elsewhere; also
 // publishes nll with zero_infinity applied.
 __global__ void __launch_bounds__(256)
@@ -532,8 +645,17 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
   }
   {
     const size_t smem = sizeof(float) * 2 * (Sp + 4);
-    ctc_alpha_beta_kernel<<<dim3(batch, 2), threads, smem, st>>>(targets, tgt_ld, input_lengths,
-                                                                target_lengths, T, Sp, blank, ws);
+    const dim3 g(batch, 2);
+    if (Sp <= 32)
+      ctc_alpha_beta_warp_kernel<1><<<g, 32, 0, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+    else if (Sp <= 64)
+      ctc_alpha_beta_warp_kernel<2><<<g, 32, 0, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+    else if (Sp <= 128)
+      ctc_alpha_beta_warp_kernel<4><<<g, 32, 0, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+    else if (Sp <= 256)
+      ctc_alpha_beta_warp_kernel<8><<<g, 32, 0, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+    else
+      ctc_alpha_beta_kernel<<<g, threads, smem, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
     S2T_LAUNCH_CHECK();
   }
   ctc_dense_grad_kernel<<<batch * T, 256, 0, st>>>(logits, is_bf16, ldv, lse, input_lengths, T, V,

@@ -135,34 +135,61 @@ fbank_kernel(const float* __restrict__ wave, long long wave_ld, const int* __res
 // and one thread per bin replays the exact sequential fp32 accumulation (no FMA contraction).
 constexpr int kCmvnChunk = 64;
 
+// stats[b][0][f] = mean (0 when !norm_means), stats[b][1][f] = std (1 when !norm_vars).  One CTA per utterance; the
+// next chunk is prefetched into registers while the current one is accumulated from shared memory.
 __global__ void __launch_bounds__(256)
-cmvn_utt_kernel(const float* __restrict__ in, long long in_ld, long long in_bs,
-                void* __restrict__ out, int out_bf16, long long out_ld, long long out_bs,
-                const int* __restrict__ num_frames, int max_frames, int n_mels, int norm_means,
-                int norm_vars) {
-  extern __shared__ float s_chunk[];  // [kCmvnChunk][n_mels] + [2][n_mels]
-  float* s_mean = s_chunk + kCmvnChunk * n_mels;
-  float* s_std = s_mean + n_mels;
+cmvn_utt_stats_kernel(const float* __restrict__ in, long long in_ld, long long in_bs,
+                      const int* __restrict__ num_frames, int max_frames, int n_mels, int norm_means,
+                      int norm_vars, float* __restrict__ stats) {
+  extern __shared__ float s_chunk[];  // [2][kCmvnChunk][n_mels]
+  constexpr int kPer = (kCmvnChunk * 128 + 255) / 256;  // n_mels <= 128
   const int b = blockIdx.x;
   int T = num_frames[b];
   if (T > max_frames) T = max_frames;
   const float* src = in + b * in_bs;
+  const int per = (kCmvnChunk * n_mels + 255) / 256;
+  float reg[kPer];
+  auto fetch = [&](int t0) {
+    const int nt = min(kCmvnChunk, T - t0);
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int i = threadIdx.x + k * 256;
+      if (k < per && i < nt * n_mels) {
+        const int t = i / n_mels, f = i - t * n_mels;
+        reg[k] = src[static_cast<long long>(t0 + t) * in_ld + f];
+      }
+    }
+  };
+  auto stash = [&](float* buf, int t0) {
+    const int nt = min(kCmvnChunk, T - t0);
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int i = threadIdx.x + k * 256;
+      if (k < per && i < nt * n_mels) buf[i] = reg[k];
+    }
+  };
   float sum = 0.f, sq = 0.f;
+  if (T > 0) {
+    fetch(0);
+    stash(s_chunk, 0);
+  }
+  __syncthreads();
+  int cur = 0;
   for (int t0 = 0; t0 < T; t0 += kCmvnChunk) {
     const int nt = min(kCmvnChunk, T - t0);
-    for (int i = threadIdx.x; i < nt * n_mels; i += blockDim.x) {
-      const int t = i / n_mels, f = i - t * n_mels;
-      s_chunk[i] = src[static_cast<long long>(t0 + t) * in_ld + f];
-    }
-    __syncthreads();
+    const bool more = t0 + kCmvnChunk < T;
+    if (more) fetch(t0 + kCmvnChunk);
+    const float* buf = s_chunk + cur * kCmvnChunk * n_mels;
     if (threadIdx.x < n_mels) {
       for (int t = 0; t < nt; ++t) {
-        const float v = s_chunk[t * n_mels + threadIdx.x];
+        const float v = buf[t * n_mels + threadIdx.x];
         sum = __fadd_rn(sum, v);
         sq = __fadd_rn(sq, __fmul_rn(v, v));
       }
     }
+    if (more) stash(s_chunk + (cur ^ 1) * kCmvnChunk * n_mels, t0 + kCmvnChunk);
     __syncthreads();
+    cur ^= 1;
   }
   if (threadIdx.x < n_mels) {
     const float Tn = static_cast<float>(T > 0 ? T : 1);
@@ -172,17 +199,34 @@ cmvn_utt_kernel(const float* __restrict__ in, long long in_ld, long long in_bs,
       const float var = __fsub_rn(__fdiv_rn(sq, Tn), __fmul_rn(m, m));
       sd = __fsqrt_rn(fmaxf(var, 1e-10f));
     }
-    s_mean[threadIdx.x] = norm_means ? m : 0.f;
-    s_std[threadIdx.x] = sd;
+    stats[(static_cast<long long>(b) * 2 + 0) * n_mels + threadIdx.x] = norm_means ? m : 0.f;
+    stats[(static_cast<long long>(b) * 2 + 1) * n_mels + threadIdx.x] = sd;
   }
-  __syncthreads();
+}
+
+// out[b][t][f] = t < T_b ? (in - mean) / std : 0 over the whole [max_frames][n_mels] plane (grid.y = utterance);
+// stats == NULL: plain cast / copy with zero fill.
+__global__ void __launch_bounds__(256)
+cmvn_apply_kernel(const float* __restrict__ in, long long in_ld, long long in_bs, void* __restrict__ out,
+                  int out_bf16, long long out_ld, long long out_bs, const int* __restrict__ num_frames,
+                  int max_frames, int n_mels, int norm_vars, const float* __restrict__ stats) {
+  const int b = blockIdx.y;
+  int T = num_frames[b];
+  if (T > max_frames) T = max_frames;
   const long long total = static_cast<long long>(max_frames) * n_mels;
-  for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+  const float* src = in + b * in_bs;
+  const float* mean = stats ? stats + static_cast<long long>(b) * 2 * n_mels : nullptr;
+  const float* sd = stats ? mean + n_mels : nullptr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int t = static_cast<int>(i / n_mels), f = static_cast<int>(i - static_cast<long long>(t) * n_mels);
     float v = 0.f;
     if (t < T) {
-      v = __fsub_rn(src[static_cast<long long>(t) * in_ld + f], s_mean[f]);
-      if (norm_vars) v = __fdiv_rn(v, s_std[f]);
+      v = src[static_cast<long long>(t) * in_ld + f];
+      if (stats != nullptr) {
+        v = __fsub_rn(v, mean[f]);
+        if (norm_vars) v = __fdiv_rn(v, sd[f]);
+      }
     }
     const long long o = b * out_bs + static_cast<long long>(t) * out_ld + f;
     if (out_bf16) reinterpret_cast<__nv_bfloat16*>(out)[o] = __float2bfloat16(v);
@@ -233,14 +277,26 @@ extern "C" int s2t_fbank_fwd(const float* wave, long long wave_ld, const int* nu
 extern "C" int s2t_cmvn_utt(const float* feats, long long in_ld, long long in_bs, void* out,
                             int out_bf16, long long out_ld, long long out_bs, const int* num_frames,
                             int batch, int max_frames, int n_mels, int norm_means, int norm_vars,
-                            void* stream) {
+                            float* stats, void* stream) {
   S2T_REQUIRE(feats && out && num_frames, "s2t_cmvn_utt: null pointer");
   S2T_REQUIRE(n_mels > 0 && n_mels <= 128, "s2t_cmvn_utt: n_mels=%d out of range", n_mels);
+  const bool norm = norm_means || norm_vars;
+  S2T_REQUIRE(!norm || stats, "s2t_cmvn_utt: stats workspace (fp32 [batch][2][n_mels]) is required when normalising");
   if (batch <= 0 || max_frames <= 0) return 0;
-  const size_t smem = sizeof(float) * (kCmvnChunk + 2) * n_mels;
-  cmvn_utt_kernel<<<batch, 256, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
-      feats, in_ld, in_bs, out, out_bf16, out_ld, out_bs, num_frames, max_frames, n_mels, norm_means,
-      norm_vars);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (norm) {
+    const size_t smem = sizeof(float) * 2 * kCmvnChunk * n_mels;
+    S2T_CHECK_CUDA(cudaFuncSetAttribute(cmvn_utt_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+    cmvn_utt_stats_kernel<<<batch, 256, smem, st>>>(feats, in_ld, in_bs, num_frames, max_frames, n_mels, norm_means,
+                                                   norm_vars, stats);
+    S2T_LAUNCH_CHECK();
+  }
+  const long long total = static_cast<long long>(max_frames) * n_mels;
+  long long gx = (total + 256 * 4 - 1) / (256 * 4);
+  if (gx > 1024) gx = 1024;
+  cmvn_apply_kernel<<<dim3(static_cast<unsigned>(gx), batch), 256, 0, st>>>(
+      feats, in_ld, in_bs, out, out_bf16, out_ld, out_bs, num_frames, max_frames, n_mels, norm_vars,
+      norm ? stats : nullptr);
   S2T_LAUNCH_CHECK();
   return 0;
 }

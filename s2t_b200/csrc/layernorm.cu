@@ -81,8 +81,12 @@ __global__ void __launch_bounds__(kLnWarps * 32)
 layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ stats,
                      const __nv_bfloat16* __restrict__ dx_res, __nv_bfloat16* __restrict__ dx,
-                     float* __restrict__ partials, int rows, int C, int rows_per_cta) {
+                     float* __restrict__ partials, int rows, int C, int rows_per_cta,
+                     __nv_bfloat16* __restrict__ dx_drop, uint32_t thresh16, float drop_scale,
+                     unsigned long long seed, uint32_t stream_id,
+                     const unsigned long long* __restrict__ seed_off) {
   extern __shared__ float s_part[];  // [kLnWarps][2][C]
+  if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nvec = C >> 3;
   float dg[NV][8], db[NV][8];
@@ -143,6 +147,13 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
           for (int j = 0; j < 8; ++j) o[j] += r[j];
         }
         dxr[vi] = pack8(o);
+        if (dx_drop != nullptr) {  // second output: drop_scale * dropout(dx) for the next residual branch's backward
+          const uint32_t keep = thresh16 != 0
+              ? dropout_keep8(seed, stream_id, static_cast<unsigned long long>(row) * nvec + vi, thresh16) : 0xffu;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = ((keep >> j) & 1u) ? o[j] * drop_scale : 0.f;
+          reinterpret_cast<uint4*>(dx_drop + static_cast<long long>(row) * C)[vi] = pack8(o);
+        }
       }
     }
   }
@@ -168,22 +179,33 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   }
 }
 
-__global__ void layernorm_bwd_reduce_kernel(const float* __restrict__ partials, int n_partials,
-                                            int C, __nv_bfloat16* __restrict__ dgamma,
-                                            __nv_bfloat16* __restrict__ dbeta, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= 2 * C) return;
-  const int which = c / C, col = c % C;
+// dgamma / dbeta = column sums of the per-CTA partials.  Block = 32 columns x 8 partial slices, so the serial depth is
+// n_partials / 8 coalesced loads (the reduce runs beside the dgrad chain on a side stream, but finishes in ~2 us).
+__global__ void __launch_bounds__(256)
+layernorm_bwd_reduce_kernel(const float* __restrict__ partials, int n_partials, int C,
+                            __nv_bfloat16* __restrict__ dgamma, __nv_bfloat16* __restrict__ dbeta, int accumulate) {
+  __shared__ float s_acc[8][33];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;  // column of the [2][C] row
   float acc = 0.f;
-  for (int p = 0; p < n_partials; ++p) acc += partials[(static_cast<long long>(p) * 2 + which) * C + col];
-  __nv_bfloat16* dst = which == 0 ? dgamma : dbeta;
-  if (dst == nullptr) return;
-  if (accumulate) acc += __bfloat162float(dst[col]);
-  dst[col] = __float2bfloat16(acc);
+  if (c < 2 * C)
+    for (int p = slice; p < n_partials; p += 8) acc += partials[static_cast<long long>(p) * 2 * C + c];
+  s_acc[slice][lane] = acc;
+  __syncthreads();
+  if (slice == 0 && c < 2 * C) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) acc += s_acc[k][lane];
+    const int which = c / C, col = c % C;
+    __nv_bfloat16* dst = which == 0 ? dgamma : dbeta;
+    if (dst != nullptr) {
+      if (accumulate) acc += __bfloat162float(dst[col]);
+      dst[col] = __float2bfloat16(acc);
+    }
+  }
 }
 
 static int ln_partials(int rows) {
-  int n = (rows + kLnWarps * 4 - 1) / (kLnWarps * 4);  // >= 4 rows per warp
+  int n = (rows + kLnWarps - 1) / kLnWarps;            // one row per warp while the grid fits in one wave
   if (n > 296) n = 296;                                // 2 CTAs per SM on 148 SMs
   if (n < 1) n = 1;
   return n;
@@ -221,10 +243,12 @@ extern "C" int s2t_layernorm_bwd_partials(int rows, int C) {
 
 extern "C" int s2t_layernorm_bwd(const void* dy, const void* x, const void* gamma,
                                  const float* stats, const void* dx_residual, void* dx,
-                                 float* partials, void* dgamma, void* dbeta, int accumulate,
-                                 int rows, int C, void* stream) {
+                                 float* partials, int rows, int C, void* dx_drop, float drop_p,
+                                 float drop_scale, unsigned long long seed, unsigned int stream_id,
+                                 const unsigned long long* seed_offset, void* stream) {
   S2T_REQUIRE(dy && x && gamma && stats && dx && partials, "s2t_layernorm_bwd: null pointer");
   S2T_REQUIRE(C % 8 == 0 && C >= 8 && C <= 1024, "s2t_layernorm_bwd: C=%d must be a multiple of 8 in [8,1024]", C);
+  S2T_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "s2t_layernorm_bwd: drop_p must be in [0,1)");
   if (rows <= 0) return 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int np = ln_partials(rows);
@@ -235,19 +259,33 @@ extern "C" int s2t_layernorm_bwd(const void* dy, const void* x, const void* gamm
   auto gp = reinterpret_cast<const __nv_bfloat16*>(gamma);
   auto rp = reinterpret_cast<const __nv_bfloat16*>(dx_residual);
   auto dxp = reinterpret_cast<__nv_bfloat16*>(dx);
+  auto ddp = reinterpret_cast<__nv_bfloat16*>(dx_drop);
+  const uint32_t th = drop_p > 0.f ? static_cast<uint32_t>(drop_p * 65536.f + 0.5f) : 0u;
+  const float sc = drop_scale / (1.f - drop_p);
   const int nv = (C / 8 + 31) / 32;
   if (smem > 48 * 1024) {
     S2T_CHECK_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<kLnMaxVec>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
+#define S2T_LN_BWD(NV)                                                                                         \
+  layernorm_bwd_kernel<NV><<<np, kLnWarps * 32, smem, st>>>(dyp, xp, gp, stats, rp, dxp, partials, rows, C,      \
+                                                            rows_per_cta, ddp, th, sc, seed, stream_id, seed_offset)
   switch (nv) {
-    case 1: layernorm_bwd_kernel<1><<<np, kLnWarps * 32, smem, st>>>(dyp, xp, gp, stats, rp, dxp, partials, rows, C, rows_per_cta); break;
-    case 2: layernorm_bwd_kernel<2><<<np, kLnWarps * 32, smem, st>>>(dyp, xp, gp, stats, rp, dxp, partials, rows, C, rows_per_cta); break;
-    default: layernorm_bwd_kernel<kLnMaxVec><<<np, kLnWarps * 32, smem, st>>>(dyp, xp, gp, stats, rp, dxp, partials, rows, C, rows_per_cta); break;
+    case 1: S2T_LN_BWD(1); break;
+    case 2: S2T_LN_BWD(2); break;
+    default: S2T_LN_BWD(kLnMaxVec); break;
   }
+#undef S2T_LN_BWD
   S2T_LAUNCH_CHECK();
-  layernorm_bwd_reduce_kernel<<<(2 * C + 127) / 128, 128, 0, st>>>(
-      partials, np, C, reinterpret_cast<__nv_bfloat16*>(dgamma),
+  return 0;
+}
+
+extern "C" int s2t_layernorm_bwd_reduce(const float* partials, int rows, int C, void* dgamma, void* dbeta,
+                                        int accumulate, void* stream) {
+  S2T_REQUIRE(partials, "s2t_layernorm_bwd_reduce: null pointer");
+  if (rows <= 0) return 0;
+  layernorm_bwd_reduce_kernel<<<(2 * C + 31) / 32, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      partials, ln_partials(rows), C, reinterpret_cast<__nv_bfloat16*>(dgamma),
       reinterpret_cast<__nv_bfloat16*>(dbeta), accumulate);
   S2T_LAUNCH_CHECK();
   return 0;

@@ -25,6 +25,7 @@ arithmetic (criterions/ctc.py:435-474,516-540).
 """
 from __future__ import annotations
 
+import contextlib
 import math
 import re
 from dataclasses import dataclass, field
@@ -212,14 +213,16 @@ class _Stage(_Bufs):
         self.x = [e(R, C) for _ in range(n_layers + 1)]     # x[j] = input of layer j, x[-1] = stage output
         self.scores = z(B * H, T, self.ld)
         self.g_p, self.g_s = z(B * H, T, self.ld), z(B * H, T, self.ld)
-        self.pool = [e(R, C) for _ in range(6)]
+        self.pool = [e(R, C) for _ in range(10)]
         self._pool_ids = {id(t) for t in self.pool}
         self.g_f = e(R, F)
         self.g_qkv = e(R, 3 * C)
         lib = ops._lib.load()
         cs = max(lib.s2t_colsum_workspace_floats(R, 3 * C), lib.s2t_colsum_workspace_floats(R, F))
-        self.colsum_ws = e(cs, dt=F32)
+        self.colsum_ws, self.colsum_ws2 = e(cs, dt=F32), e(cs, dt=F32)   # two: consecutive colsums overlap on a side stream
         self.ln_part = e(lib.s2t_layernorm_bwd_partials(R, C), 2, C, dt=F32)
+        self._ln_parts = [self.ln_part] + [e(lib.s2t_layernorm_bwd_partials(R, C), 2, C, dt=F32) for _ in range(3)]
+        self._ln_i = 0
         if c.attn_type == "rel_pos":
             n_rel = 2 * T - 1
             self.ldb = _round8(n_rel)
@@ -236,6 +239,12 @@ class _Stage(_Bufs):
 
     def take(self) -> torch.Tensor:
         return self.pool.pop()
+
+    def next_ln_part(self) -> torch.Tensor:
+        """Rotating LayerNorm-backward partial buffers (the dgamma/dbeta reduce of one LN runs on a side stream while
+        the next LN backward already writes its own partials)."""
+        self._ln_i = (self._ln_i + 1) % len(self._ln_parts)
+        return self._ln_parts[self._ln_i]
 
     def give(self, *bufs: torch.Tensor) -> None:
         for t in bufs:
@@ -256,6 +265,7 @@ class Plan:
         self.wave = z(B, wave_len, dt=F32) if wave_len else None
         self.num_samples = z(B, dt=torch.int32) if wave_len else None
         self.fbank_raw = e(B, T, c.input_dim, dt=F32) if wave_len else None
+        self.cmvn_stats = e(B, 2, c.input_dim, dt=F32) if wave_len else None
         self.src_len = z(B, dt=torch.int32)
         self.targets = z(B, max(smax, 1), dt=torch.int32)
         self.tgt_len = z(B, dt=torch.int32)
@@ -514,6 +524,11 @@ class S2TEncoderEngine:
         self.plans: Dict[Tuple[int, int, int, int], Plan] = {}
         self.training = True
         self.grad_ready_hook = None  # callable(offset): store.grad[offset:] is final (dp.BucketedAllReduce.on_ready)
+        # fork/join streams: leaf work of the backward pass (weight / bias gradients) and independent attention
+        # branches run beside the critical dgrad chain; captured into the CUDA graph as parallel branches
+        self.multi_stream = True
+        self._side = [torch.cuda.Stream(device=self.device) for _ in range(3)]
+        self._forked: set = set()
         self.dp = None               # dp.BucketedAllReduce when data parallel
         self.init_parameters()
 
@@ -706,7 +721,8 @@ class S2TEncoderEngine:
             src = P.feats_in
         cm = 1 if P.wave is not None else 0
         ops._call("s2t_cmvn_utt", ops._p(src), src.stride(1), src.stride(0), ops._p(dst) + 2 * pad * c.input_dim, 1,
-                  dst.stride(1), dst.stride(0), ops._p(P.src_len), P.B, P.T, c.input_dim, cm, cm, ops._stream())
+                  dst.stride(1), dst.stride(0), ops._p(P.src_len), P.B, P.T, c.input_dim, cm, cm,
+                  ops._p(P.cmvn_stats), ops._stream())
 
     def _stem_s2t_fwd(self, P: Plan) -> None:
         """Conv1dSubsampling (subsampling.py:145-159): [Conv1d(k, stride, pad) -> GLU] per layer as an
@@ -801,6 +817,9 @@ class S2TEncoderEngine:
         a = sp.prefix + "self_attn."
         rel = c.attn_type == "rel_pos"
         q, o = ("linear_q", "linear_out") if rel else ("q_proj", "out_proj")
+        if rel:   # the position projection does not depend on x: beside LayerNorm + QKV
+            with self._fork(2):
+                ops.linear(St.pos_emb, S.p(a + "linear_pos.weight"), out=L.pp)
         ops.layernorm_fwd(x, S.p(sp.prefix + "self_attn_layer_norm.weight"), S.p(sp.prefix + "self_attn_layer_norm.bias"),
                           out=L.ln1, stats=L.st1)
         ops.linear(L.ln1, S.fused(a + q + ".weight", 3 * C, C), S.fused(a + q + ".bias", 3 * C, 0), out=L.qkv)
@@ -813,11 +832,13 @@ class S2TEncoderEngine:
                                  dropout=dspec)
         else:
             ops.relpos_qbias_fwd(L.qkv, S.p(a + "pos_bias_u"), S.p(a + "pos_bias_v"), C, out=L.quv)
-            ops.linear(St.pos_emb, S.p(a + "linear_pos.weight"), out=L.pp)
+            self._join()                                                  # L.pp
+            with self._fork(2):                                           # BD beside AC
+                ops.gemm_raw(M=T, N=2 * T - 1, K=dk, a=L.quv, a_off=C, lda=2 * C, a_bs=(dk, T * 2 * C), b=L.pp, ldb=C,
+                             b_bs=(dk, 0), out=St.bd, ldc=St.ldb, c_bs=(B * T * St.ldb, T * St.ldb), batch=(H, B))
             ops.gemm_raw(M=T, N=T, K=dk, a=L.quv, lda=2 * C, a_bs=(dk, T * 2 * C), b=L.qkv, ldb=3 * C, b_off=C,
                          b_bs=(dk, T * 3 * C), out=St.scores, ldc=ld, c_bs=bs_s, batch=(H, B))
-            ops.gemm_raw(M=T, N=2 * T - 1, K=dk, a=L.quv, a_off=C, lda=2 * C, a_bs=(dk, T * 2 * C), b=L.pp, ldb=C,
-                         b_bs=(dk, 0), out=St.bd, ldc=St.ldb, c_bs=(B * T * St.ldb, T * St.ldb), batch=(H, B))
+            self._join()
             ops.attn_softmax_fwd(St.scores, St.lens, H, T, probs=L.probs, probs_drop=L.probs_d if dspec else None,
                                  bias=St.bd.view(H * B, T, St.ldb), bias_mode=2, bias_head_major=True,
                                  scale=dk ** -0.5, clamp=1e4, dropout=dspec)
@@ -949,10 +970,44 @@ class S2TEncoderEngine:
     # ------------------------------------------------------------------------------------------
     # backward
     # ------------------------------------------------------------------------------------------
+    def _fork(self, i: int = 0):
+        """Context: the enclosed launches run on side stream ``i`` after everything issued so far on the main stream.
+        Buffers they read must not be overwritten by the main stream before the next ``_join``."""
+        if not self.multi_stream:
+            return contextlib.nullcontext()
+        side = self._side[i]
+        side.wait_stream(torch.cuda.current_stream())
+        self._forked.add(i)
+        return torch.cuda.stream(side)
+
+    def _join(self) -> None:
+        """The main stream waits for all side-stream work forked since the last join."""
+        main = torch.cuda.current_stream()
+        for i in sorted(self._forked):
+            main.wait_stream(self._side[i])
+        self._forked.clear()
+
     def _ready(self, first_name: str) -> None:
         """Everything at or after ``first_name`` in the flat gradient buffer is final."""
+        self._join()
         if self.grad_ready_hook is not None:
             self.grad_ready_hook(self.store.offset(first_name))
+
+    def _ln_bwd(self, St: _Stage, dy: torch.Tensor, x: torch.Tensor, norm: str, stats: torch.Tensor, *,
+                dx_residual: Optional[torch.Tensor] = None, nxt=None):
+        """LayerNorm backward on the main stream, its dgamma/dbeta reduction on a side stream.  ``nxt`` = (dropout spec,
+        scale) of the residual branch whose backward consumes the result next: the kernel then also emits
+        scale * dropout(dx) (second return value), so that branch needs no separate dropout pass."""
+        S = self.store
+        part = St.next_ln_part()
+        dx, dd, spec, scale = St.take(), None, None, 1.0
+        if nxt is not None and (nxt[0] is not None or nxt[1] != 1.0):
+            dd, (spec, scale) = St.take(), nxt
+        ops.layernorm_bwd(dy, x, S.p(norm + ".weight"), stats, None, None, dx_residual=dx_residual, out=dx,
+                          partials=part, out_drop=dd, drop=spec, drop_scale=scale, reduce=False)
+        with self._fork(1):
+            ops.layernorm_bwd_reduce(part, x.shape[0], x.shape[1], S.g(norm + ".weight"), S.g(norm + ".bias"))
+        return dx, dd
 
     def _branch_grad(self, dy: torch.Tensor, spec, scale: float, out: torch.Tensor) -> torch.Tensor:
         """Gradient entering a residual branch y = x + scale * dropout(branch): scale * mask * dy / (1-p)."""
@@ -973,17 +1028,19 @@ class S2TEncoderEngine:
         S = self.store
         wn, bn = hs.name + ".ctc_projection.weight", hs.name + ".ctc_projection.bias"
         C = out.shape[1]
-        ops.colsum(dlogits, S.g(bn), accumulate=self._acc(bn), workspace=ws)
+        with self._fork(1):
+            ops.colsum(dlogits, S.g(bn), accumulate=self._acc(bn), workspace=ws)
         gw = S.g(wn)
         dl = dlogits[:, : hs.V] if hs.V != hs.ldv else dlogits
-        if self._acc(wn):
-            ops.linear_wgrad(dl, src, out=gw, residual=gw, ldr=C)
-        else:
-            ops.linear_wgrad(dl, src, out=gw)
+        with self._fork(0):
+            if self._acc(wn):
+                ops.linear_wgrad(dl, src, out=gw, residual=gw, ldr=C)
+            else:
+                ops.linear_wgrad(dl, src, out=gw)
         ops.gemm_raw(M=P.R, N=C, K=hs.V, a=dlogits, lda=hs.ldv, b=S.p(wn), ldb=C, b_mn=True, out=out, ldc=C,
                      residual=residual, ldr=C if residual is not None else 0)
 
-    def _head_bwd(self, P: Plan) -> torch.Tensor:
+    def _head_bwd(self, P: Plan):
         S = self.store
         St = P.stages[-1]
         self._touched = set()
@@ -1002,16 +1059,12 @@ class S2TEncoderEngine:
             else:
                 ops.add_(d, t0)
                 St.give(t0)
-        if not self.inter_after:
-            self._ready(self.heads[0].name + ".ctc_projection.weight")
-        dx = St.take()
-        ops.layernorm_bwd(d, St.x[-1], S.p("layer_norm.weight"), P.enc_st, S.g("layer_norm.weight"),
-                          S.g("layer_norm.bias"), out=dx, partials=St.ln_part)
-        St.give(d)
+        dx, dd = self._ln_bwd(St, d, St.x[-1], "layer_norm", P.enc_st, nxt=self._next_branch(len(self.layer_specs)))
         self._ready("layer_norm.weight")
-        return dx
+        St.give(d)
+        return dx, dd
 
-    def _inter_bwd(self, P: Plan, l: int, k: int, dy: torch.Tensor) -> torch.Tensor:
+    def _inter_bwd(self, P: Plan, l: int, k: int, dy: torch.Tensor, nxt=None):
         """Backward of _inter_fwd: ``dy`` = gradient w.r.t. the block output (== input when the head has no adapter);
         adds the block's own CTC-loss gradient (already in I.dlogits) and returns the gradient w.r.t. the block input."""
         c, S = self.cfg, self.store
@@ -1024,10 +1077,11 @@ class S2TEncoderEngine:
             # d dist = dy E^T ; dE (+)= dist^T dy ; dlogits += softmax'(d dist)
             ops.gemm_raw(M=P.R, N=hs.V, K=C, a=dy, lda=C, b=E, ldb=C, out=Hd.ddist, ldc=hs.ldv)
             dist = I.dist[:, : hs.V] if hs.V != hs.ldv else I.dist
-            if self._acc(en):
-                ops.linear_wgrad(dist, dy, out=gE, residual=gE, ldr=C)
-            else:
-                ops.linear_wgrad(dist, dy, out=gE)
+            with self._fork(2):
+                if self._acc(en):
+                    ops.linear_wgrad(dist, dy, out=gE, residual=gE, ldr=C)
+                else:
+                    ops.linear_wgrad(dist, dy, out=gE)
             ops.softmax_rows_bwd(I.dist, Hd.ddist, I.dlogits, hs.V, accumulate=True)
         spec = self._drop(hs.site + 1 + hs.inter_layers.index(l))
         t0 = St.take()
@@ -1043,119 +1097,153 @@ class S2TEncoderEngine:
                 ops.add_(t0, to_norm)
         # gradient that bypasses the norm: dy flows to x unless the adapter consumed norm_x instead of x
         skip = None if to_norm is not None else dy
-        n = f"{hs.norm}{l}"
-        dx = St.take()
-        ops.layernorm_bwd(t0, I.xin, S.p(n + ".weight"), I.st, S.g(n + ".weight"), S.g(n + ".bias"),
-                          dx_residual=skip, out=dx, partials=St.ln_part)
+        dx, dd = self._ln_bwd(St, t0, I.xin, f"{hs.norm}{l}", I.st, dx_residual=skip, nxt=nxt)
+        self._join()
         St.give(t0, dy)
-        return dx
+        return dx, dd
 
-    def _ffn_bwd(self, St: _Stage, dy: torch.Tensor, x: torch.Tensor, ln: torch.Tensor, st: torch.Tensor,
-                 h: Optional[torch.Tensor], f: torch.Tensor, norm: str, ffn: str, scale: float, site: int) -> torch.Tensor:
-        """Backward of _ffn_fwd; consumes ``dy`` (gradient w.r.t. the block output), returns the gradient w.r.t. x."""
+    def _ffn_bwd(self, St: _Stage, dy: torch.Tensor, dyd: Optional[torch.Tensor], x: torch.Tensor, ln: torch.Tensor,
+                 st: torch.Tensor, h: Optional[torch.Tensor], f: torch.Tensor, norm: str, ffn: str, scale: float,
+                 site: int, nxt=None):
+        """Backward of _ffn_fwd; consumes ``dy`` (gradient w.r.t. the block output), returns the gradient w.r.t. x.
+        Critical chain: dropout' -> dgrad w_2 -> dgrad w_1 -> LayerNorm'; weight / bias gradients on side streams."""
         S = self.store
-        t0 = St.take()
-        d2 = self._branch_grad(dy, self._drop(site + 1), scale, t0)
-        ops.colsum(d2, S.g(ffn + ".w_2.bias"), workspace=St.colsum_ws)
-        ops.linear_wgrad(d2, f, out=S.g(ffn + ".w_2.weight"))
+        t0, t1 = St.take(), St.take()
+        d2 = dyd if dyd is not None else self._branch_grad(dy, self._drop(site + 1), scale, t0)
+        with self._fork(0):
+            ops.linear_wgrad(d2, f, out=S.g(ffn + ".w_2.weight"))
+        with self._fork(1):
+            ops.colsum(d2, S.g(ffn + ".w_2.bias"), workspace=St.colsum_ws)
         if self.ffn_act == ops.ACT_RELU:
             ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=St.g_f, gate=f, gate_mode=ops.GATE_POSITIVE, ldg=St.F,
                              dropout=self._drop(site))
         else:
             ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=St.g_f, gate=h, gate_mode=ops.GATE_SWISH_GRAD, ldg=St.F,
                              dropout=self._drop(site))
-        ops.colsum(St.g_f, S.g(ffn + ".w_1.bias"), workspace=St.colsum_ws)
-        ops.linear_wgrad(St.g_f, ln, out=S.g(ffn + ".w_1.weight"))
-        ops.linear_dgrad(St.g_f, S.p(ffn + ".w_1.weight"), out=t0)
-        dx = St.take()
-        ops.layernorm_bwd(t0, x, S.p(norm + ".weight"), st, S.g(norm + ".weight"), S.g(norm + ".bias"),
-                          dx_residual=dy, out=dx, partials=St.ln_part)
-        St.give(t0, dy)
-        return dx
+        with self._fork(0):
+            ops.linear_wgrad(St.g_f, ln, out=S.g(ffn + ".w_1.weight"))
+        with self._fork(1):
+            ops.colsum(St.g_f, S.g(ffn + ".w_1.bias"), workspace=St.colsum_ws2)
+        ops.linear_dgrad(St.g_f, S.p(ffn + ".w_1.weight"), out=t1)
+        dx, dd = self._ln_bwd(St, t1, x, norm, st, dx_residual=dy, nxt=nxt)
+        self._join()
+        St.give(t0, t1, dy, dyd)
+        return dx, dd
 
-    def _conv_bwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    def _conv_bwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, dy: torch.Tensor, dyd: Optional[torch.Tensor],
+                  x: torch.Tensor, nxt=None):
         S = self.store
         p, m = sp.prefix, sp.prefix + "conv_module."
         B, T, C = P.B, St.T, St.C
-        t0 = St.take()
-        d = self._branch_grad(dy, self._drop(sp.site + 6, sp.p_drop), 1.0, t0)
-        ops.linear_wgrad(d, L.bn, out=S.g(m + "pointwise_conv2.weight"))
-        t1 = St.take()
+        t0, t1, t2 = St.take(), St.take(), St.take()
+        d = dyd if dyd is not None else self._branch_grad(dy, self._drop(sp.site + 6, sp.p_drop), 1.0, t0)
+        with self._fork(0):
+            ops.linear_wgrad(d, L.bn, out=S.g(m + "pointwise_conv2.weight"))
         ops.linear_dgrad(d, S.p(m + "pointwise_conv2.weight"), out=t1)                     # d act(bn)
         ops.batchnorm_bwd(t1, L.dw, L.bn_save, S.p(m + "norm.weight"), S.p(m + "norm.bias"), S.g(m + "norm.weight"),
-                          S.g(m + "norm.bias"), out=t0, partials=St.bn_bwd_part, act=sp.conv_act,
+                          S.g(m + "norm.bias"), out=t2, partials=St.bn_bwd_part, act=sp.conv_act,
                           training=self.training)                                            # d dw
-        ops.dwconv1d_bwd(L.glu.view(B, T, C), S.p(m + "depthwise_conv.weight"), t0.view(B, T, C),
+        ops.dwconv1d_bwd(L.glu.view(B, T, C), S.p(m + "depthwise_conv.weight"), t2.view(B, T, C),
                          S.g(m + "depthwise_conv.weight"), out=t1.view(B, T, C), workspace=St.dw_ws)   # d glu
         ops.glu_bwd(L.pw1, t1, out=St.g_2c)
-        ops.linear_wgrad(St.g_2c, L.c_ln, out=S.g(m + "pointwise_conv1.weight"))
-        ops.linear_dgrad(St.g_2c, S.p(m + "pointwise_conv1.weight"), out=t0)
-        ops.mask_rows_(t0.view(B, T, C), St.lens)
-        dx = t1
-        ops.layernorm_bwd(t0, x, S.p(p + "conv_norm.weight"), L.c_st, S.g(p + "conv_norm.weight"),
-                          S.g(p + "conv_norm.bias"), dx_residual=dy, out=dx, partials=St.ln_part)
-        St.give(t0, dy)
-        return dx
+        with self._fork(0):
+            ops.linear_wgrad(St.g_2c, L.c_ln, out=S.g(m + "pointwise_conv1.weight"))
+        ops.linear_dgrad(St.g_2c, S.p(m + "pointwise_conv1.weight"), out=t2)
+        ops.mask_rows_(t2.view(B, T, C), St.lens)
+        dx, dd = self._ln_bwd(St, t2, x, p + "conv_norm", L.c_st, dx_residual=dy, nxt=nxt)
+        self._join()
+        St.give(t0, t1, t2, dy, dyd)
+        return dx, dd
 
-    def _attn_bwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    def _attn_bwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, dy: torch.Tensor, dyd: Optional[torch.Tensor],
+                  x: torch.Tensor, nxt=None):
+        """Backward of _attn_fwd.  Critical chain: dropout' -> dgrad out -> dP -> softmax' -> dQ -> dgrad qkv -> LayerNorm';
+        dV, dK, the position branch and all weight / bias gradients run on side streams."""
         c, S = self.cfg, self.store
         B, T, C, H, dk, ld = P.B, St.T, St.C, St.H, St.dk, St.ld
         a = sp.prefix + "self_attn."
         rel = c.attn_type == "rel_pos"
         q, o = ("linear_q", "linear_out") if rel else ("q_proj", "out_proj")
-        t0 = St.take()
-        do = self._branch_grad(dy, self._drop(sp.site + 1, sp.p_drop), 1.0, t0)
-        ops.colsum(do, S.g(a + o + ".bias"), workspace=St.colsum_ws)
-        ops.linear_wgrad(do, L.ctx, out=S.g(a + o + ".weight"))
-        dctx = St.take()
+        t0, t1, dctx = St.take(), St.take(), St.take()
+        do = dyd if dyd is not None else self._branch_grad(dy, self._drop(sp.site + 1, sp.p_drop), 1.0, t0)
+        with self._fork(0):
+            ops.linear_wgrad(do, L.ctx, out=S.g(a + o + ".weight"))
+        with self._fork(1):
+            ops.colsum(do, S.g(a + o + ".bias"), workspace=St.colsum_ws)
         ops.linear_dgrad(do, S.p(a + o + ".weight"), out=dctx)
         dspec = self._drop(sp.site + 0, sp.p_drop)
         pd = L.probs_d if dspec else L.probs
         bs_x, bs_qkv, bs_s = (dk, T * C), (dk, T * 3 * C), (T * ld, H * T * ld)
         g_qkv = St.g_qkv
-        # dP_drop = dctx V^T ; dV = P_drop^T dctx
+        # dV = P_drop^T dctx (side) ; dP_drop = dctx V^T (main)
+        with self._fork(2):
+            ops.gemm_raw(M=T, N=dk, K=T, a=pd, lda=ld, a_mn=True, a_bs=bs_s, b=dctx, ldb=C, b_mn=True, b_bs=bs_x,
+                         out=g_qkv, c_off=2 * C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B))
         ops.gemm_raw(M=T, N=T, K=dk, a=dctx, lda=C, a_bs=bs_x, b=L.qkv, ldb=3 * C, b_off=2 * C, b_bs=bs_qkv,
                      out=St.g_p, ldc=ld, c_bs=bs_s, batch=(H, B))
-        ops.gemm_raw(M=T, N=dk, K=T, a=pd, lda=ld, a_mn=True, a_bs=bs_s, b=dctx, ldb=C, b_mn=True, b_bs=bs_x,
-                     out=g_qkv, c_off=2 * C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B))
         if not rel:
             ops.attn_softmax_bwd(L.probs, St.g_p, St.lens, H, T, out=St.g_s, dropout=dspec)
-            # dQ = s dS K ; dK = s dS^T Q
+            # dK = s dS^T Q (side) ; dQ = s dS K (main)
+            with self._fork(2):
+                ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_mn=True, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=0,
+                             b_mn=True, b_bs=bs_qkv, out=g_qkv, c_off=C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B),
+                             alpha=dk ** -0.5)
             ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=C, b_mn=True,
                          b_bs=bs_qkv, out=g_qkv, c_off=0, ldc=3 * C, c_bs=bs_qkv, batch=(H, B), alpha=dk ** -0.5)
-            ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_mn=True, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=0,
-                         b_mn=True, b_bs=bs_qkv, out=g_qkv, c_off=C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B),
-                         alpha=dk ** -0.5)
         else:
             ldb, nrel = St.ldb, 2 * T - 1
             bs_quv, bs_bd = (dk, T * 2 * C), (B * T * ldb, T * ldb)
             ops.attn_softmax_bwd(L.probs, St.g_p, St.lens, H, T, out=St.g_s, dbias=St.g_bd.view(H * B, T, ldb),
                                  bias_head_major=True, scale=dk ** -0.5, dropout=dspec)
-            # d(q+u) = dS K ; dK = dS^T (q+u)
+            # side 2: dK = dS^T (q+u) ; dp[h] = sum_b dBD[h,b]^T (q+v)[b,h] (one GEMM per head over K = B*T: head-major
+            # dBD) and the linear_pos weight gradient
+            with self._fork(2):
+                ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_mn=True, a_bs=bs_s, b=L.quv, ldb=2 * C, b_off=0,
+                             b_mn=True, b_bs=bs_quv, out=g_qkv, c_off=C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B))
+                ops.gemm_raw(M=nrel, N=dk, K=B * T, a=St.g_bd, lda=ldb, a_mn=True, a_bs=(B * T * ldb, 0), b=L.quv,
+                             ldb=2 * C, b_off=C, b_mn=True, b_bs=(dk, 0), out=St.g_pp, ldc=C, c_bs=(dk, 0), batch=(H, 1))
+                ops.linear_wgrad(St.g_pp, St.pos_emb, out=S.g(a + "linear_pos.weight"))
+            # main: d(q+u) = dS K ; d(q+v) = dBD p ; dq = d(q+u) + d(q+v)
             ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_bs=bs_s, b=L.qkv, ldb=3 * C, b_off=C, b_mn=True,
                          b_bs=bs_qkv, out=St.g_quv, c_off=0, ldc=2 * C, c_bs=bs_quv, batch=(H, B))
-            ops.gemm_raw(M=T, N=dk, K=T, a=St.g_s, lda=ld, a_mn=True, a_bs=bs_s, b=L.quv, ldb=2 * C, b_off=0,
-                         b_mn=True, b_bs=bs_quv, out=g_qkv, c_off=C, ldc=3 * C, c_bs=bs_qkv, batch=(H, B))
-            # d(q+v) = dBD p ; dp[h] = sum_b dBD[h,b]^T (q+v)[b,h]  (one GEMM per head over K = B*T: head-major dBD)
             ops.gemm_raw(M=T, N=dk, K=nrel, a=St.g_bd, lda=ldb, a_bs=bs_bd, b=L.pp, ldb=C, b_mn=True, b_bs=(dk, 0),
                          out=St.g_quv, c_off=C, ldc=2 * C, c_bs=bs_quv, batch=(H, B))
-            ops.gemm_raw(M=nrel, N=dk, K=B * T, a=St.g_bd, lda=ldb, a_mn=True, a_bs=(B * T * ldb, 0), b=L.quv,
-                         ldb=2 * C, b_off=C, b_mn=True, b_bs=(dk, 0), out=St.g_pp, ldc=C, c_bs=(dk, 0), batch=(H, 1))
-            ops.colsum(St.g_quv, S.fused(a + "pos_bias_u", 2 * C, 0, grad=True), workspace=St.colsum_ws)
+            with self._fork(1):
+                ops.colsum(St.g_quv, S.fused(a + "pos_bias_u", 2 * C, 0, grad=True), workspace=St.colsum_ws)
             ops.relpos_qbias_bwd(St.g_quv, g_qkv, C)
-            ops.linear_wgrad(St.g_pp, St.pos_emb, out=S.g(a + "linear_pos.weight"))
-        ops.colsum(g_qkv, S.fused(a + q + ".bias", 3 * C, 0, grad=True), workspace=St.colsum_ws)
-        ops.linear_wgrad(g_qkv, L.ln1, out=S.fused(a + q + ".weight", 3 * C, C, grad=True))
-        ops.linear_dgrad(g_qkv, S.fused(a + q + ".weight", 3 * C, C), out=t0)
-        dx = dctx
-        n = sp.prefix + "self_attn_layer_norm"
-        ops.layernorm_bwd(t0, x, S.p(n + ".weight"), L.st1, S.g(n + ".weight"), S.g(n + ".bias"),
-                          dx_residual=dy, out=dx, partials=St.ln_part)
-        St.give(t0, dy)
-        return dx
+        self._join()                                      # g_qkv is complete (dV / dK came from side streams)
+        with self._fork(0):
+            ops.linear_wgrad(g_qkv, L.ln1, out=S.fused(a + q + ".weight", 3 * C, C, grad=True))
+        with self._fork(1):
+            ops.colsum(g_qkv, S.fused(a + q + ".bias", 3 * C, 0, grad=True), workspace=St.colsum_ws)
+        ops.linear_dgrad(g_qkv, S.fused(a + q + ".weight", 3 * C, C), out=t1)
+        dx, dd = self._ln_bwd(St, t1, x, sp.prefix + "self_attn_layer_norm", L.st1, dx_residual=dy, nxt=nxt)
+        self._join()
+        St.give(t0, t1, dctx, dy, dyd)
+        return dx, dd
 
-    def _layer_bwd(self, P: Plan, g: int, dy: torch.Tensor) -> torch.Tensor:
-        """Backward of _layer_fwd.  ``dy`` = dL/d(layer output) in a pool buffer of the stage; returns dL/d(input)."""
+    def _branch_spec(self, g: int, block: str):
+        """(dropout spec, scale) of the residual branch ``block`` of layer g: y = x + scale * dropout(branch(x))."""
+        c, sp = self.cfg, self.layer_specs[g]
+        s = 0.5 if c.macaron_style else 1.0
+        return {"ffn": (self._drop(sp.site + 5), s), "conv": (self._drop(sp.site + 6, sp.p_drop), 1.0),
+                "attn": (self._drop(sp.site + 1, sp.p_drop), 1.0), "macaron": (self._drop(sp.site + 3), s)}[block]
+
+    def _next_branch(self, n_done: int):
+        """Branch spec of the first block the backward pass meets below layer index ``n_done`` (= the LAST forward block
+        of layer n_done - 1), or None when something else sits in between (inter-CTC block, final_norm, stage stem,
+        layer padding mask)."""
+        c = self.cfg
+        g = n_done - 1
+        if g < 0 or n_done in self.inter_after or c.use_cnn_module:
+            return None
+        if n_done < len(self.layer_specs) and self.layer_specs[n_done].stage != self.layer_specs[g].stage:
+            return None
+        return self._branch_spec(g, "ffn")
+
+    def _layer_bwd(self, P: Plan, g: int, dy: torch.Tensor, dyd: Optional[torch.Tensor] = None):
+        """Backward of _layer_fwd.  ``dy`` = dL/d(layer output) in a pool buffer of the stage (``dyd``: its pre-masked
+        copy for the FFN branch, when the producer emitted one); returns (dL/d(input), pre-masked copy or None)."""
         c, S = self.cfg, self.store
         sp, L = self.layer_specs[g], P.layers[g]
         St = P.stages[sp.stage]
@@ -1163,23 +1251,27 @@ class S2TEncoderEngine:
         p = sp.prefix
         s = 0.5 if c.macaron_style else 1.0
         x_attn = L.xa if c.macaron_style else x_in
+        mask_out = c.layer_padding_mask and c.encoder_type == "s2t"
+        # what consumes this layer's input gradient: the previous layer's FFN branch, unless something sits in between
+        below = None if (mask_out or sp.index == 0) else self._next_branch(g)
+        after_attn = self._branch_spec(g, "macaron") if c.macaron_style else below
         if c.use_cnn_module:
-            d = St.take()
-            ops.layernorm_bwd(dy, L.xd, S.p(p + "final_norm.weight"), L.f_st, S.g(p + "final_norm.weight"),
-                              S.g(p + "final_norm.bias"), out=d, partials=St.ln_part)
-            St.give(dy)
-            d = self._ffn_bwd(St, d, L.xc, L.ln2, L.st2, L.h, L.f, p + "ffn_norm", p + "ffn", s, sp.site + 4)
-            d = self._conv_bwd(P, St, sp, L, d, L.x1)
+            d, dd = self._ln_bwd(St, dy, L.xd, p + "final_norm", L.f_st, nxt=self._branch_spec(g, "ffn"))
+            St.give(dy, dyd)
+            d, dd = self._ffn_bwd(St, d, dd, L.xc, L.ln2, L.st2, L.h, L.f, p + "ffn_norm", p + "ffn", s, sp.site + 4,
+                                  nxt=self._branch_spec(g, "conv"))
+            d, dd = self._conv_bwd(P, St, sp, L, d, dd, L.x1, nxt=self._branch_spec(g, "attn"))
         else:
-            d = self._ffn_bwd(St, dy, L.x1, L.ln2, L.st2, L.h, L.f, p + "ffn_norm", p + "ffn", s, sp.site + 4)
-        d = self._attn_bwd(P, St, sp, L, d, x_attn)
+            d, dd = self._ffn_bwd(St, dy, dyd, L.x1, L.ln2, L.st2, L.h, L.f, p + "ffn_norm", p + "ffn", s, sp.site + 4,
+                                  nxt=self._branch_spec(g, "attn"))
+        d, dd = self._attn_bwd(P, St, sp, L, d, dd, x_attn, nxt=after_attn)
         if c.macaron_style:
-            d = self._ffn_bwd(St, d, x_in, L.m_ln, L.m_st, L.m_h, L.m_f, p + "macaron_norm", p + "macaron_ffn", s,
-                              sp.site + 2)
-        if c.layer_padding_mask and c.encoder_type == "s2t":
+            d, dd = self._ffn_bwd(St, d, dd, x_in, L.m_ln, L.m_st, L.m_h, L.m_f, p + "macaron_norm", p + "macaron_ffn", s,
+                                  sp.site + 2, nxt=below)
+        if mask_out:
             ops.mask_rows_(d.view(P.B, St.T, St.C), St.lens)
         self._ready(sp.first)
-        return d
+        return d, dd
 
     def _stem_s2t_bwd(self, P: Plan, dy: torch.Tensor) -> None:
         """Backward of the embed block and Conv1dSubsampling: GLU', bias = column sums, weight = dY^T im2col(X),
@@ -1206,9 +1298,11 @@ class S2TEncoderEngine:
                 ops.glu_bwd(P.pre[i], dy, out=P.g_pre[i], lengths=P.sub_len[i], T=t_out)
             else:
                 ops.glu_bwd(P.pre[i], dy, out=P.g_pre[i])
-            ops.colsum(P.g_pre[i], S.g(f"subsample.layers.{i}.0.bias"), workspace=P.stem_colsum_ws)
-            ops.im2col1d(xin, xin.stride(0), P.B, t_out, cin, k, st, out=P.xcol[i])
-            ops.linear_wgrad(P.g_pre[i], P.xcol[i], out=S.g(f"subsample.layers.{i}.0.weight").view(cout, k * cin))
+            with self._fork(1):
+                ops.colsum(P.g_pre[i], S.g(f"subsample.layers.{i}.0.bias"), workspace=P.stem_colsum_ws)
+            with self._fork(0):
+                ops.im2col1d(xin, xin.stride(0), P.B, t_out, cin, k, st, out=P.xcol[i])
+                ops.linear_wgrad(P.g_pre[i], P.xcol[i], out=S.g(f"subsample.layers.{i}.0.weight").view(cout, k * cin))
             if i > 0:
                 ops.linear_dgrad(P.g_pre[i], S.p(f"subsample.layers.{i}.0.weight").view(cout, k * cin), out=P.g_col[i])
                 ops.col2im1d(P.g_col[i], P.B, P.t_sub[i], t_out, cin, k, st, P.pad, out=P.g_sub[i])
@@ -1232,10 +1326,12 @@ class S2TEncoderEngine:
                               out=o, partials=St.ln_part)
             St.give(t)
             t = o
-        ops.colsum(t, S.g(n + "conv.0.bias"), workspace=D.colsum_ws)
-        ops.im2col1d(D.framed, D.framed.stride(0), P.B, D.t_out, D.cin, D.k, D.stride, out=D.xcol)
+        with self._fork(1):
+            ops.colsum(t, S.g(n + "conv.0.bias"), workspace=D.colsum_ws)
         w = S.p(n + "conv.0.weight").view(D.cout, D.k * D.cin)
-        ops.linear_wgrad(t, D.xcol, out=S.g(n + "conv.0.weight").view(D.cout, D.k * D.cin))
+        with self._fork(0):
+            ops.im2col1d(D.framed, D.framed.stride(0), P.B, D.t_out, D.cin, D.k, D.stride, out=D.xcol)
+            ops.linear_wgrad(t, D.xcol, out=S.g(n + "conv.0.weight").view(D.cout, D.k * D.cin))
         out = None
         if i > 0:
             prev = P.stages[i - 1]
@@ -1244,24 +1340,29 @@ class S2TEncoderEngine:
             g_in = out.view(P.B, D.t_in, D.cin)
             ops.col2im1d(D.g_col, P.B, D.t_in, D.t_out, D.cin, D.k, D.stride, D.pad, out=g_in)
             ops.mask_rows_(g_in, prev.lens)                         # the stem zeroes padded input frames (:107-116)
-        St.give(t)
         self._ready(n + "conv.0.weight")
+        St.give(t)
         return out
 
     def _backward(self, P: Plan) -> None:
         c = self.cfg
-        d = self._head_bwd(P)
+        d, dd = self._head_bwd(P)
         g = len(self.layer_specs)
         for i in reversed(range(len(P.stages))):
             n = c.layers if c.encoder_type == "s2t" else c.pds_layers[i]
             for _ in range(n):
                 if i == 0 and (g in self.inter_after):
-                    for k in reversed(self.inter_after[g]):
-                        d = self._inter_bwd(P, g, k, d)
-                    first = f"{self.heads[self.inter_after[g][0]].norm}{g}.weight"
-                    self._ready(first)
+                    blocks = self.inter_after[g]
+                    for j, k in enumerate(reversed(blocks)):
+                        last = j == len(blocks) - 1
+                        nxt = None if (not last or c.use_cnn_module) else self._branch_spec(g - 1, "ffn")
+                        P.stages[0].give(dd)
+                        d, dd = self._inter_bwd(P, g, k, d, nxt=nxt)
+                    self._ready(f"{self.heads[blocks[0]].norm}{g}.weight")
                 g -= 1
-                d = self._layer_bwd(P, g, d)
+                d, dd = self._layer_bwd(P, g, d, dd)
+            P.stages[i].give(dd)
+            dd = None
             if c.encoder_type == "s2t":
                 self._stem_s2t_bwd(P, d)
             else:

@@ -44,11 +44,12 @@ SIGNATURES = {
     "s2t_gemm_bf16": (_i, [C.POINTER(GemmArgs), _vp]),
     "s2t_fbank_num_frames": (_i, [_ll]),
     "s2t_fbank_fwd": (_i, [_vp, _ll, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _ll, _ll, _vp, _vp]),
-    "s2t_cmvn_utt": (_i, [_vp, _ll, _ll, _vp, _i, _ll, _ll, _vp, _i, _i, _i, _i, _i, _vp]),
+    "s2t_cmvn_utt": (_i, [_vp, _ll, _ll, _vp, _i, _ll, _ll, _vp, _i, _i, _i, _i, _i, _vp, _vp]),
     "s2t_cmvn_global": (_i, [_vp, _ll, _ll, _vp, _i, _ll, _ll, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "s2t_layernorm_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
     "s2t_layernorm_bwd_partials": (_i, [_i, _i]),
-    "s2t_layernorm_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "s2t_layernorm_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_layernorm_bwd_reduce": (_i, [_vp, _i, _i, _vp, _vp, _i, _vp]),
     "s2t_glu_fwd": (_i, [_vp, _vp, _ll, _ll, _i, _i, _vp, _i, _vp]),
     "s2t_glu_bwd": (_i, [_vp, _vp, _ll, _vp, _i, _i, _vp, _i, _vp]),
     "s2t_colsum": (_i, [_vp, _ll, _i, _i, _vp, _i, _vp, _ll, _vp]),

@@ -19,8 +19,8 @@ BF16 = torch.bfloat16
 #: number of kernel launches issued through this module (bench.py reports it as ``gpu_launches``)
 launch_count = 0
 _LAUNCHES = {
-    "s2t_gemm_bf16": 1, "s2t_fbank_fwd": 1, "s2t_cmvn_utt": 1, "s2t_cmvn_global": 1,
-    "s2t_layernorm_fwd": 1, "s2t_layernorm_bwd": 2, "s2t_glu_fwd": 1, "s2t_glu_bwd": 1,
+    "s2t_gemm_bf16": 1, "s2t_fbank_fwd": 1, "s2t_cmvn_utt": 2, "s2t_cmvn_global": 1,
+    "s2t_layernorm_fwd": 1, "s2t_layernorm_bwd": 1, "s2t_layernorm_bwd_reduce": 1, "s2t_glu_fwd": 1, "s2t_glu_bwd": 1,
     "s2t_colsum": 2, "s2t_col2im1d": 1, "s2t_embed_fwd": 1, "s2t_embed_bwd": 1, "s2t_mask_rows": 1,
     "s2t_permute_conv_weight": 1, "s2t_cast_f32_to_bf16": 1, "s2t_cast_bf16_to_f32": 1,
     "s2t_attn_softmax_fwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4,
@@ -162,12 +162,15 @@ def fbank(wave: torch.Tensor, num_samples: torch.Tensor, mel_w: torch.Tensor, me
 
 
 def cmvn_utt(feats: torch.Tensor, num_frames: torch.Tensor, out: Optional[torch.Tensor] = None,
-             norm_means: bool = True, norm_vars: bool = True) -> torch.Tensor:
+             norm_means: bool = True, norm_vars: bool = True, stats: Optional[torch.Tensor] = None) -> torch.Tensor:
     B, T, F = feats.shape
     if out is None:
         out = torch.empty_like(feats)
+    if stats is None and (norm_means or norm_vars):
+        stats = torch.empty((B, 2, F), device=feats.device, dtype=torch.float32)
     _call("s2t_cmvn_utt", _p(feats), feats.stride(1), feats.stride(0), _p(out), int(out.dtype == BF16),
-          out.stride(1), out.stride(0), _p(num_frames), B, T, F, int(norm_means), int(norm_vars), _stream())
+          out.stride(1), out.stride(0), _p(num_frames), B, T, F, int(norm_means), int(norm_vars), _p(stats),
+          _stream())
     return out
 
 
@@ -196,18 +199,31 @@ def layernorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps:
 
 
 def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, stats: torch.Tensor,
-                  dgamma: torch.Tensor, dbeta: torch.Tensor, *, dx_residual: Optional[torch.Tensor] = None,
-                  out: Optional[torch.Tensor] = None, accumulate: bool = False,
-                  partials: Optional[torch.Tensor] = None) -> torch.Tensor:
+                  dgamma: Optional[torch.Tensor], dbeta: Optional[torch.Tensor], *,
+                  dx_residual: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                  accumulate: bool = False, partials: Optional[torch.Tensor] = None,
+                  out_drop: Optional[torch.Tensor] = None, drop=None, drop_scale: float = 1.0,
+                  reduce: bool = True) -> torch.Tensor:
+    """dx = LN'(dy) (+ dx_residual); ``out_drop`` (optional) = drop_scale * dropout(dx) for the next branch.  With
+    ``reduce=False`` only the partial dgamma/dbeta sums are written (call :func:`layernorm_bwd_reduce` later, e.g. on a
+    side stream)."""
     rows, Cd = x.shape
     if out is None:
         out = torch.empty_like(x)
     if partials is None:
         n = _lib.load().s2t_layernorm_bwd_partials(rows, Cd)
         partials = torch.empty((n, 2, Cd), device=x.device, dtype=torch.float32)
-    _call("s2t_layernorm_bwd", _p(dy), _p(x), _p(gamma), _p(stats), _p(dx_residual), _p(out), _p(partials),
-          _p(dgamma), _p(dbeta), int(accumulate), rows, Cd, _stream())
+    p, seed, sid, off = _drop(drop)
+    _call("s2t_layernorm_bwd", _p(dy), _p(x), _p(gamma), _p(stats), _p(dx_residual), _p(out), _p(partials), rows, Cd,
+          _p(out_drop), p, drop_scale, seed, sid, off, _stream())
+    if reduce:
+        layernorm_bwd_reduce(partials, rows, Cd, dgamma, dbeta, accumulate)
     return out
+
+
+def layernorm_bwd_reduce(partials: torch.Tensor, rows: int, Cd: int, dgamma: Optional[torch.Tensor],
+                         dbeta: Optional[torch.Tensor], accumulate: bool = False) -> None:
+    _call("s2t_layernorm_bwd_reduce", _p(partials), rows, Cd, _p(dgamma), _p(dbeta), int(accumulate), _stream())
 
 
 # --------------------------------------------------------------------------------------------------

@@ -82,6 +82,28 @@ def test_layernorm_fwd_bwd(cuda_lib, rows, C):
     assert (db.float().cpu() - bf.grad).abs().max() <= 2 ** -6 * bf.grad.abs().max() + 1e-2
 
 
+def test_layernorm_bwd_dropped_second_output(cuda_lib):
+    """out_drop = drop_scale * dropout(dx) with exactly the mask s2t_dropout draws for the same (seed, stream) — the
+    pre-masked gradient handed to the next residual branch; the split reduce gives the same dgamma/dbeta."""
+    from s2t_b200 import ops
+    rows, C = 2000, 256
+    x, gm, dy = _rand((rows, C), 1, 2.0), _rand((C,), 2), _rand((rows, C), 4)
+    _, stats = ops.layernorm_fwd(x.cuda(), gm.cuda(), gm.cuda())
+    dg, db = (torch.empty((C,), device="cuda", dtype=BF16) for _ in range(2))
+    dx = ops.layernorm_bwd(dy.cuda(), x.cuda(), gm.cuda(), stats, dg, db)
+    spec = (0.1, 99, 21)
+    dd = torch.empty_like(dx)
+    part = torch.empty((ops._lib.load().s2t_layernorm_bwd_partials(rows, C), 2, C), device="cuda")
+    dx2 = ops.layernorm_bwd(dy.cuda(), x.cuda(), gm.cuda(), stats, None, None, out_drop=dd, drop=spec, drop_scale=0.5,
+                            partials=part, reduce=False)
+    dg2, db2 = (torch.empty((C,), device="cuda", dtype=BF16) for _ in range(2))
+    ops.layernorm_bwd_reduce(part, rows, C, dg2, db2)
+    assert torch.equal(dx, dx2) and torch.equal(dg, dg2) and torch.equal(db, db2)
+    want = ops.dropout(dx, spec, scale=0.5)
+    assert (dd.float() - want.float()).abs().max() <= 2 ** -7 * want.float().abs().max()   # one extra bf16 rounding
+    assert torch.equal(dd == 0, want == 0)
+
+
 # ------------------------------------------------------------------------------------------------ elementwise
 def test_glu_fwd_bwd_with_padding_mask(cuda_lib):
     from s2t_b200 import ops
@@ -251,6 +273,29 @@ def test_ctc_loss_and_grad_match_oracle(cuda_lib, dtype):
     tol = 1e-4 if dtype == torch.float32 else 2 ** -8
     assert np.abs(dl.float().cpu().numpy() - ref_grad).max() < tol
     assert np.all(dl.float().cpu().numpy()[3] == 0)
+
+
+@pytest.mark.parametrize("smax", [1, 14, 31, 63, 100, 127, 150])
+def test_ctc_lattice_sizes(cuda_lib, smax):
+    """Every lattice width class (warp-resident 1/2/4/8 states per lane, block fallback above 256 extended states),
+    with empty / single-label / repeated-label targets, against the float64 oracle."""
+    from oracle import ctc as O
+    from s2t_b200 import ops
+    B, V = 4, 56
+    T = 2 * smax + 9
+    tlens = [smax, max(smax - 1, 0), 0, max(smax // 2, 1)]
+    ilens = [T, T - 1, 5, max(T // 2, 3)]
+    logits, tg, tgts = _ctc_case(smax, B, T, V, tlens, ilens, torch.float32)
+    if smax >= 3:
+        tg[0, : smax] = 7                        # all-repeats target: needs a blank between every pair
+        tgts[0] = tg[0, : smax].copy()
+    nll, dl = ops.ctc_loss(logits.cuda(), torch.from_numpy(tg).cuda(), torch.tensor(ilens, dtype=torch.int32).cuda(),
+                           torch.tensor(tlens, dtype=torch.int32).cuda(), V)
+    ref_nll, ref_grad = O.ctc_loss(logits.float().numpy(), tgts, ilens)
+    assert np.allclose(nll.cpu().numpy(), ref_nll, rtol=1e-3, atol=1e-3), (nll.cpu().numpy(), ref_nll)
+    # fp32 log-domain lattice over up to 309 frames: |log alpha| reaches ~1e3, whose fp32 ulp is 6e-5, so occupancies
+    # (values in [0, 1]) carry ~1e-3 absolute round-off against the float64 oracle (torch's fp32 CTC is the same)
+    assert np.abs(dl.float().cpu().numpy() - ref_grad).max() < 3e-3
 
 
 def test_ctc_loss_c1_shape(cuda_lib):
