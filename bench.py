@@ -169,45 +169,63 @@ def run_reference(a):
 # --------------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------------
-def gemm_roofline(torch, eng, P, peaks):
-    """Roofline of the dominant kernel, gemm_bf16_kernel (tcgen05/TMEM GEMM family — it carries every linear layer,
-    attention contraction and the vocabulary projection).  Timed live: every GEMM launch of one eager training step is
-    bracketed by CUDA events on the launching stream; achieved = algorithmic FLOPs (2*M*N*K*batches per launch, summed)
-    / summed launch durations."""
+def gemm_roofline(torch, eng, P, peaks, replays: int = 20):
+    """Roofline of the dominant kernel family, gemm_bf16_kernel / gemm_bf16_splitk_kernel (tcgen05/TMEM GEMMs: every
+    linear layer, attention contraction, conv-as-GEMM and the vocabulary projection).  Timed live on the device: the
+    arguments of every GEMM launch of one training step are recorded, then exactly those launches (same operands, same
+    shapes, same epilogues) are captured back to back into one CUDA graph on one stream and replayed ``replays`` times
+    between two CUDA events on that stream.  achieved = algorithmic FLOPs (2*M*N*K*batches per launch, summed over the
+    step's launches) / (event time / replays); avg launch duration = event time / (replays * launches).  The operands
+    of one step (> 126 MB of activations, weights and gradients) exceed L2, as in the real step."""
     from s2t_b200 import ops
-    recs = []
+    calls = []
     orig = ops.gemm_raw
 
-    def timed(**kw):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
+    def rec(**kw):
+        calls.append(kw)
         orig(**kw)
-        e1.record()
-        nb = kw.get("batch", (1, 1))
-        recs.append((e0, e1, 2.0 * kw["M"] * kw["N"] * kw["K"] * nb[0] * nb[1]))
 
-    best = None
-    for _ in range(3):
-        recs.clear()
-        ops.gemm_raw = timed
-        try:
-            e_all0, e_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e_all0.record()
-            eng.train_step(P)
-            e_all1.record()
-        finally:
-            ops.gemm_raw = orig
+    ops.gemm_raw = rec
+    dp, hook = eng.dp, eng.grad_ready_hook
+    eng.dp, eng.grad_ready_hook = None, None     # rank 0 alone runs this step: no collective may be issued from it
+    try:
+        e_all0, e_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e_all0.record()
+        eng.train_step(P)
+        e_all1.record()
+    finally:
+        ops.gemm_raw = orig
+        eng.dp, eng.grad_ready_hook = dp, hook
+    torch.cuda.synchronize()
+    step_ms = e_all0.elapsed_time(e_all1)
+    fl = sum(2.0 * kw["M"] * kw["N"] * kw["K"] * kw.get("batch", (1, 1))[0] * kw.get("batch", (1, 1))[1] for kw in calls)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        for kw in calls:
+            orig(**kw)
         torch.cuda.synchronize()
-        ms = sum(a.elapsed_time(b) for a, b, _ in recs)
-        fl = sum(f for _, _, f in recs)
-        if best is None or ms < best[0]:
-            best = (ms, fl, len(recs), e_all0.elapsed_time(e_all1))
-    ms, fl, n, step_ms = best
+        with torch.cuda.graph(g, stream=side):
+            for kw in calls:
+                orig(**kw)
+        for _ in range(3):
+            g.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(side)
+        for _ in range(replays):
+            g.replay()
+        e1.record(side)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / replays
+    n = len(calls)
     peak = float(peaks.get("bf16_tflops_sustained") or 1400.0)
     ach = fl / (ms * 1e-3) / 1e12
-    return {"bound": "tensor", "kernel": "gemm_bf16_kernel (all GEMM launches of one step)", "achieved": ach, "peak": peak,
-            "unit": "TFLOP/s", "frac": ach / peak, "traffic": None, "launches_per_step": n,
-            "avg_launch_us": 1e3 * ms / n, "gemm_ms_per_step": ms, "eager_step_ms": step_ms, "flop_per_step": fl,
+    return {"bound": "tensor", "kernel": "gemm_bf16_kernel + gemm_bf16_splitk_kernel (all GEMM launches of one step)",
+            "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+            "launches_per_step": n, "avg_launch_us": 1e3 * ms / n, "gemm_ms_per_step": ms, "eager_step_ms": step_ms,
+            "flop_per_step": fl,
+            "how": f"the step's {n} GEMM launches captured alone into one CUDA graph, {replays} replays between CUDA events",
             "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained"}
 
 
@@ -220,6 +238,9 @@ def run_b200(a):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    import faulthandler
+    # a wedged collective must not hang the box: dump every thread's stack and exit instead
+    faulthandler.dump_traceback_later(float(os.environ.get("S2T_BENCH_WATCHDOG_S", "900")), exit=True)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py (impl b200) needs a CUDA device: s2t_b200 has no CPU fallback")
     torch.cuda.set_device(local)
@@ -353,10 +374,13 @@ def kernel_table(torch, eng, P):
         recs.append((name, e0, e1))
 
     ops._call = timed
+    dp, hook = eng.dp, eng.grad_ready_hook
+    eng.dp, eng.grad_ready_hook = None, None     # rank-0-only step: no collectives
     try:
         eng.train_step(P)
     finally:
         ops._call = orig
+        eng.dp, eng.grad_ready_hook = dp, hook
     torch.cuda.synchronize()
     agg = {}
     for name, a, b in recs:

@@ -31,6 +31,9 @@ const char* s2t_last_error(void);
 int s2t_abi_version(void);
 /* compute capability of the current device as major*10+minor (100 on B200); negative on error */
 int s2t_device_arch(void);
+/* Programmatic dependent launch between consecutive kernels of a stream (default on; S2T_PDL=0 in the environment
+ * turns it off).  Returns the previous setting.  Affects launches made after the call. */
+int s2t_set_pdl(int on);
 
 /* --------------------------------------------------------------------------------------------- */
 /* K4: tcgen05/TMEM GEMM family.                                                                  */

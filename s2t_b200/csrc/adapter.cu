@@ -25,6 +25,7 @@ __device__ __forceinline__ uint4 pack8v(const float (&f)[8]) {
 __global__ void __launch_bounds__(256)
 softmax_rows_fwd_kernel(const __nv_bfloat16* __restrict__ logits, long long ldv, const float* __restrict__ lse,
                         __nv_bfloat16* __restrict__ probs, long long ldp, int V) {
+  pdl_entry();
   const long long row = blockIdx.x;
   const float l = lse[row];
   const __nv_bfloat16* x = logits + row * ldv;
@@ -42,6 +43,7 @@ softmax_rows_fwd_kernel(const __nv_bfloat16* __restrict__ logits, long long ldv,
 __global__ void __launch_bounds__(256)
 softmax_rows_bwd_kernel(const __nv_bfloat16* __restrict__ probs, const __nv_bfloat16* __restrict__ dprobs,
                         long long ldp, __nv_bfloat16* __restrict__ dlogits, long long ldv, int V, int accumulate) {
+  pdl_entry();
   __shared__ float s_part[8];
   __shared__ float s_dot;
   const long long row = blockIdx.x;
@@ -91,8 +93,7 @@ extern "C" int s2t_softmax_rows_fwd(const void* logits, long long ldv, const flo
   S2T_REQUIRE(V > 0 && ldv % 8 == 0 && ldp % 8 == 0 && ldp >= V && ldv >= ldp,
               "s2t_softmax_rows_fwd: need V <= ldp <= ldv, both multiples of 8");
   if (rows <= 0) return 0;
-  softmax_rows_fwd_kernel<<<rows, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(logits), ldv, lse, reinterpret_cast<__nv_bfloat16*>(probs), ldp, V);
+  S2T_LAUNCH(softmax_rows_fwd_kernel, rows, 256, 0, reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<const __nv_bfloat16*>(logits), ldv, lse, reinterpret_cast<__nv_bfloat16*>(probs), ldp, V);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -103,9 +104,7 @@ extern "C" int s2t_softmax_rows_bwd(const void* probs, const void* dprobs, long 
   S2T_REQUIRE(V > 0 && ldv % 8 == 0 && ldp % 8 == 0 && ldp >= ((V + 7) & ~7) && ldv >= ((V + 7) & ~7),
               "s2t_softmax_rows_bwd: row strides must be multiples of 8 and cover round8(V)");
   if (rows <= 0) return 0;
-  softmax_rows_bwd_kernel<<<rows, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(probs), reinterpret_cast<const __nv_bfloat16*>(dprobs), ldp,
-      reinterpret_cast<__nv_bfloat16*>(dlogits), ldv, V, accumulate);
+  S2T_LAUNCH(softmax_rows_bwd_kernel, rows, 256, 0, reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<const __nv_bfloat16*>(probs), reinterpret_cast<const __nv_bfloat16*>(dprobs), ldp, reinterpret_cast<__nv_bfloat16*>(dlogits), ldv, V, accumulate);
   S2T_LAUNCH_CHECK();
   return 0;
 }

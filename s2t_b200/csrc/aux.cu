@@ -29,6 +29,7 @@ __global__ void dropout_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat1
                                long long n_vec, uint32_t thresh16, float scale,
                                unsigned long long seed, uint32_t stream_id,
                                const unsigned long long* __restrict__ seed_off) {
+  pdl_entry();
   if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_vec;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -47,6 +48,7 @@ __global__ void dropout_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat1
 __global__ void im2col1d_kernel(const __nv_bfloat16* __restrict__ xp, long long x_bs,
                                 __nv_bfloat16* __restrict__ xcol, int batch, int t_out, int C,
                                 int ksize, int stride) {
+  pdl_entry();
   const int rv = (ksize * C) >> 3;
   const long long n = static_cast<long long>(batch) * t_out * rv;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
@@ -64,6 +66,7 @@ __global__ void im2col1d_kernel(const __nv_bfloat16* __restrict__ xp, long long 
 // next Conv1d with the padding mask applied (Downsampling.forward, pdss2t_transformer.py:107-116)
 __global__ void frame_rows_kernel(const __nv_bfloat16* __restrict__ x, const int* __restrict__ lengths,
                                   __nv_bfloat16* __restrict__ y, long long y_bs, int pad, int batch, int T, int C) {
+  pdl_entry();
   const int cv = C >> 3;
   const long long n = static_cast<long long>(batch) * T * cv;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
@@ -79,11 +82,13 @@ __global__ void frame_rows_kernel(const __nv_bfloat16* __restrict__ x, const int
 }
 
 __global__ void counter_add_kernel(unsigned long long* c, unsigned long long inc) {
+  pdl_entry();
   if (threadIdx.x == 0 && blockIdx.x == 0) *c += inc;
 }
 
 __global__ void add_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                 long long n_vec) {
+  pdl_entry();
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_vec;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     float a[8], b[8];
@@ -96,6 +101,7 @@ __global__ void add_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
 }
 
 __global__ void f32_sum_kernel(const float* __restrict__ x, int n, float scale, float* __restrict__ out) {
+  pdl_entry();
   __shared__ float s[32];
   float acc = 0.f;
   for (int i = threadIdx.x; i < n; i += blockDim.x) acc += x[i];
@@ -112,6 +118,7 @@ __global__ void f32_sum_kernel(const float* __restrict__ x, int n, float scale, 
 // out[0] = sum_r w[r] * sum_c x[r][c]
 __global__ void f32_weighted_sum_kernel(const float* __restrict__ x, const float* __restrict__ w, int rows, int cols,
                                         float* __restrict__ out) {
+  pdl_entry();
   __shared__ float s[32];
   float acc = 0.f;
   for (int i = threadIdx.x; i < rows * cols; i += blockDim.x) acc += w[i / cols] * x[i];
@@ -145,10 +152,7 @@ extern "C" int s2t_dropout(const void* x, void* y, long long n, float p, float o
   S2T_REQUIRE(p >= 0.f && p < 1.f, "s2t_dropout: p must be in [0,1)");
   if (n <= 0) return 0;
   const long long nv = n / 8;
-  dropout_kernel<<<grid_for(nv, 256), 256, 0, ST(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), nv,
-      p > 0.f ? static_cast<uint32_t>(p * 65536.f + 0.5f) : 0u, out_scale / (1.f - p), seed, stream_id,
-      seed_offset);
+  S2T_LAUNCH(dropout_kernel, grid_for(nv, 256), 256, 0, ST(stream), reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), nv, p > 0.f ? static_cast<uint32_t>(p * 65536.f + 0.5f) : 0u, out_scale / (1.f - p), seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -159,9 +163,7 @@ extern "C" int s2t_im2col1d(const void* xp, long long x_bs, void* xcol, int batc
   S2T_REQUIRE(C % 8 == 0 && x_bs % 8 == 0 && ksize > 0 && stride > 0, "s2t_im2col1d: bad shape");
   const long long n = static_cast<long long>(batch) * t_out * (ksize * C / 8);
   if (n <= 0) return 0;
-  im2col1d_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(xp), x_bs, reinterpret_cast<__nv_bfloat16*>(xcol), batch,
-      t_out, C, ksize, stride);
+  S2T_LAUNCH(im2col1d_kernel, grid_for(n, 256), 256, 0, ST(stream), reinterpret_cast<const __nv_bfloat16*>(xp), x_bs, reinterpret_cast<__nv_bfloat16*>(xcol), batch, t_out, C, ksize, stride);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -172,15 +174,14 @@ extern "C" int s2t_frame_rows(const void* x, const int* lengths, void* y, long l
   S2T_REQUIRE(C % 8 == 0 && y_bs % 8 == 0 && pad >= 0, "s2t_frame_rows: bad shape");
   const long long n = static_cast<long long>(batch) * T * (C / 8);
   if (n <= 0) return 0;
-  frame_rows_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(reinterpret_cast<const __nv_bfloat16*>(x), lengths,
-                                                             reinterpret_cast<__nv_bfloat16*>(y), y_bs, pad, batch, T, C);
+  S2T_LAUNCH(frame_rows_kernel, grid_for(n, 256), 256, 0, ST(stream), reinterpret_cast<const __nv_bfloat16*>(x), lengths, reinterpret_cast<__nv_bfloat16*>(y), y_bs, pad, batch, T, C);
   S2T_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int s2t_counter_add(unsigned long long* counter, unsigned long long inc, void* stream) {
   S2T_REQUIRE(counter, "s2t_counter_add: null pointer");
-  counter_add_kernel<<<1, 32, 0, ST(stream)>>>(counter, inc);
+  S2T_LAUNCH(counter_add_kernel, 1, 32, 0, ST(stream), counter, inc);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -189,8 +190,7 @@ extern "C" int s2t_add_bf16(const void* x, void* y, long long n, void* stream) {
   S2T_REQUIRE(x && y, "s2t_add_bf16: null pointer");
   S2T_REQUIRE(n % 8 == 0, "s2t_add_bf16: n must be a multiple of 8");
   if (n <= 0) return 0;
-  add_bf16_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), n / 8);
+  S2T_LAUNCH(add_bf16_kernel, grid_for(n / 8, 256), 256, 0, ST(stream), reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), n / 8);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -198,14 +198,14 @@ extern "C" int s2t_add_bf16(const void* x, void* y, long long n, void* stream) {
 extern "C" int s2t_f32_weighted_sum(const float* x, const float* w, int rows, int cols, float* out, void* stream) {
   S2T_REQUIRE(x && w && out, "s2t_f32_weighted_sum: null pointer");
   S2T_REQUIRE(rows > 0 && cols > 0, "s2t_f32_weighted_sum: empty input");
-  f32_weighted_sum_kernel<<<1, 256, 0, ST(stream)>>>(x, w, rows, cols, out);
+  S2T_LAUNCH(f32_weighted_sum_kernel, 1, 256, 0, ST(stream), x, w, rows, cols, out);
   S2T_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int s2t_f32_sum(const float* x, int n, float scale, float* out, void* stream) {
   S2T_REQUIRE(x && out, "s2t_f32_sum: null pointer");
-  f32_sum_kernel<<<1, 256, 0, ST(stream)>>>(x, n, scale, out);
+  S2T_LAUNCH(f32_sum_kernel, 1, 256, 0, ST(stream), x, n, scale, out);
   S2T_LAUNCH_CHECK();
   return 0;
 }

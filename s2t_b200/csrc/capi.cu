@@ -3,6 +3,7 @@
 
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/s2t_b200.h"
 
@@ -15,7 +16,22 @@ void set_last_error(const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+
+static int g_pdl = -1;   // -1: read S2T_PDL on first use
+bool pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("S2T_PDL");
+    g_pdl = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return g_pdl != 0;
+}
 }  // namespace s2t
+
+extern "C" int s2t_set_pdl(int on) {
+  const int prev = s2t::pdl_enabled() ? 1 : 0;
+  s2t::g_pdl = on ? 1 : 0;
+  return prev;
+}
 
 extern "C" const char* s2t_last_error(void) { return s2t::g_err; }
 

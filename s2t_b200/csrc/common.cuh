@@ -6,6 +6,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string.h>
 
 namespace s2t {
 
@@ -33,6 +34,49 @@ void set_last_error(const char* fmt, ...);
   } while (0)
 
 #define S2T_LAUNCH_CHECK() S2T_CHECK_CUDA(cudaGetLastError())
+
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch (PDL).  The training step is a chain of several hundred kernels of a few
+// microseconds each, so launch latency and per-kernel set-up (barrier init, TMEM allocation, tensor-map prefetch,
+// index arithmetic) are a large share of the step.  Every kernel therefore
+//   * calls pdl_launch_dependents() first: the NEXT kernel in the stream may be scheduled as soon as all CTAs of
+//     this one are resident, and runs its own set-up while this kernel is still computing;
+//   * calls pdl_wait() before its first access to global memory: blocks until every prerequisite grid has completed
+//     and its writes are visible (transitively: a grid only completes after its own pdl_wait returned).
+// Launches go through launch_pdl(), which sets cudaLaunchAttributeProgrammaticStreamSerialization (captured as a
+// programmatic edge in CUDA graphs).  S2T_PDL=0 in the environment turns the attribute off (plain serialisation;
+// the device-side instructions are then no-ops).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// the common case: nothing worth overlapping before the first global access
+__device__ __forceinline__ void pdl_entry() {
+  pdl_launch_dependents();
+  pdl_wait();
+}
+
+bool pdl_enabled();   // capi.cu
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(static_cast<Args&&>(args))...);
+}
+// S2T_LAUNCH(kernel, grid, block, smem_bytes, stream, args...) — the kernel must call pdl_wait() (or pdl_entry())
+// before touching global memory.
+#define S2T_LAUNCH(kern, grid, block, smem, st, ...)                                      \
+  S2T_CHECK_CUDA(::s2t::launch_pdl(kern, dim3(grid), dim3(block), smem, st, __VA_ARGS__))
 
 // ---------------------------------------------------------------------------------------------
 // small device helpers
@@ -144,6 +188,14 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m
       " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(smem_dst)),
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
+}
+
+// 1-D bulk async copy global -> shared (TMA engine), completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_copy_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
 }
 
 // TMA store: shared (generic-proxy writes made visible by fence_proxy_async) -> global, bulk-group completion

@@ -55,6 +55,7 @@ __device__ __forceinline__ void stage_tile(const __nv_bfloat16* __restrict__ x, 
 __global__ void __launch_bounds__(kDwThreads)
 dwconv1d_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w,
                 __nv_bfloat16* __restrict__ y, float* __restrict__ stats, int T, int C, int K, int flip) {
+  pdl_entry();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int pad = (K - 1) >> 1;
   const int tiles = (T + kDwTile - 1) / kDwTile;
@@ -112,6 +113,7 @@ dwconv1d_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
 __global__ void __launch_bounds__(kDwThreads)
 dwconv1d_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                       float* __restrict__ dwp, int T, int C, int K) {
+  pdl_entry();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int pad = (K - 1) >> 1;
   const int tiles = (T + kDwTile - 1) / kDwTile;
@@ -149,6 +151,7 @@ dwconv1d_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
 // dw[c][j] (bf16, the reference's (C,1,k) layout) = sum_blocks dwp[block][j][c]
 __global__ void dwconv1d_wgrad_reduce_kernel(const float* __restrict__ dwp, int nblk, int C, int K,
                                              __nv_bfloat16* __restrict__ dw) {
+  pdl_entry();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;  // i = j*C + c
   if (i >= K * C) return;
   float a = 0.f;
@@ -205,6 +208,7 @@ batchnorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restric
                      float* __restrict__ rmean, float* __restrict__ rvar, long long* __restrict__ nbt,
                      float* __restrict__ save, __nv_bfloat16* __restrict__ y, long long rows, int C, float eps,
                      float momentum, int act, int training) {
+  pdl_entry();
   const int pairs = C >> 1;
   const int G = row_groups(pairs, kBnRows);
   const int rpg = kBnRows / G;
@@ -246,6 +250,7 @@ batchnorm_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfl
                             const float* __restrict__ save, const __nv_bfloat16* __restrict__ gamma,
                             const __nv_bfloat16* __restrict__ beta, float* __restrict__ partials,
                             long long rows, int C, int act) {
+  pdl_entry();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float* sst = reinterpret_cast<float*>(smem_raw);  // [G][2][C]
   const int pairs = C >> 1;
@@ -283,6 +288,7 @@ batchnorm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bflo
                            const __nv_bfloat16* __restrict__ beta, const float* __restrict__ partials, int nparts,
                            __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dgamma,
                            __nv_bfloat16* __restrict__ dbeta, long long rows, int C, int act, int training) {
+  pdl_entry();
   const int pairs = C >> 1;
   const int G = row_groups(pairs, kBnRows);
   const int rpg = kBnRows / G;
@@ -322,6 +328,7 @@ batchnorm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bflo
 __global__ void relpos_qbias_fwd_kernel(const __nv_bfloat16* __restrict__ q, long long ldq,
                                         const __nv_bfloat16* __restrict__ u, const __nv_bfloat16* __restrict__ v,
                                         __nv_bfloat16* __restrict__ quv, long long rows, int C) {
+  pdl_entry();
   const int cv = C >> 3;
   const long long n = rows * cv;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
@@ -348,6 +355,7 @@ __global__ void relpos_qbias_fwd_kernel(const __nv_bfloat16* __restrict__ q, lon
 // dq[r] (row stride lddq) = dquv[r][0:C] + dquv[r][C:2C]
 __global__ void relpos_qbias_bwd_kernel(const __nv_bfloat16* __restrict__ dquv, __nv_bfloat16* __restrict__ dq,
                                         long long lddq, long long rows, int C) {
+  pdl_entry();
   const int cv = C >> 3;
   const long long n = rows * cv;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
@@ -371,6 +379,7 @@ __global__ void act_dropout_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
                                    long long n_vec, int act, uint32_t thresh16, float inv_keep,
                                    unsigned long long seed, uint32_t stream_id,
                                    const unsigned long long* __restrict__ seed_off) {
+  pdl_entry();
   if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_vec;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -423,8 +432,7 @@ extern "C" int s2t_dwconv1d_fwd(const void* x, const void* w, void* y, float* bn
   const size_t smem = static_cast<size_t>(kDwTile + K - 1) * C * 2 + static_cast<size_t>(kDwTile) * 2 * C * 4;
   S2T_REQUIRE(smem <= 200 * 1024, "s2t_dwconv1d_fwd: C too large for the shared-memory tile");
   S2T_CHECK_CUDA(cudaFuncSetAttribute(dwconv1d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  dwconv1d_kernel<<<static_cast<unsigned>(s2t_dwconv1d_tiles(batch, T)), kDwThreads, smem, ST(stream)>>>(
-      BF(x), BF(w), BFM(y), bn_partials, T, C, K, 0);
+  S2T_LAUNCH(dwconv1d_kernel, static_cast<unsigned>(s2t_dwconv1d_tiles(batch, T)), kDwThreads, smem, ST(stream), BF(x), BF(w), BFM(y), bn_partials, T, C, K, 0);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -438,13 +446,12 @@ extern "C" int s2t_dwconv1d_bwd(const void* x, const void* w, const void* dy, vo
   S2T_REQUIRE(smem <= 200 * 1024, "s2t_dwconv1d_bwd: C too large for the shared-memory tile");
   S2T_CHECK_CUDA(cudaFuncSetAttribute(dwconv1d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   S2T_CHECK_CUDA(cudaFuncSetAttribute(dwconv1d_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  dwconv1d_kernel<<<tiles, kDwThreads, smem, ST(stream)>>>(BF(dy), BF(w), BFM(dx), nullptr, T, C, K, 1);
+  S2T_LAUNCH(dwconv1d_kernel, tiles, kDwThreads, smem, ST(stream), BF(dy), BF(w), BFM(dx), nullptr, T, C, K, 1);
   S2T_LAUNCH_CHECK();
   const size_t smem_w = static_cast<size_t>(2 * kDwTile + K - 1) * C * 2;
-  dwconv1d_wgrad_kernel<<<tiles, kDwThreads, smem_w, ST(stream)>>>(BF(x), BF(dy), workspace, T, C, K);
+  S2T_LAUNCH(dwconv1d_wgrad_kernel, tiles, kDwThreads, smem_w, ST(stream), BF(x), BF(dy), workspace, T, C, K);
   S2T_LAUNCH_CHECK();
-  dwconv1d_wgrad_reduce_kernel<<<(K * C + 255) / 256, 256, 0, ST(stream)>>>(workspace, static_cast<int>(tiles), C, K,
-                                                                          BFM(dw));
+  S2T_LAUNCH(dwconv1d_wgrad_reduce_kernel, (K * C + 255) / 256, 256, 0, ST(stream), workspace, static_cast<int>(tiles), C, K, BFM(dw));
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -461,9 +468,7 @@ extern "C" int s2t_batchnorm_fwd(const void* x, const float* partials, int npart
   S2T_REQUIRE(C > 0 && C % 8 == 0 && rows > 0, "s2t_batchnorm_fwd: bad shape");
   S2T_REQUIRE(training ? (partials != nullptr && nparts > 0) : (running_mean && running_var),
               "s2t_batchnorm_fwd: training needs the channel-sum partials, eval needs the running statistics");
-  batchnorm_fwd_kernel<<<static_cast<unsigned>((rows + kBnRows - 1) / kBnRows), kBnThreads, 0, ST(stream)>>>(
-      BF(x), partials, nparts, BF(gamma), BF(beta), running_mean, running_var, num_batches_tracked, save_stats,
-      BFM(y), rows, C, eps, momentum, act, training);
+  S2T_LAUNCH(batchnorm_fwd_kernel, static_cast<unsigned>((rows + kBnRows - 1) / kBnRows), kBnThreads, 0, ST(stream), BF(x), partials, nparts, BF(gamma), BF(beta), running_mean, running_var, num_batches_tracked, save_stats, BFM(y), rows, C, eps, momentum, act, training);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -478,12 +483,9 @@ extern "C" int s2t_batchnorm_bwd(const void* da, const void* x, const float* sav
   const size_t smem = static_cast<size_t>(kBnRows) * 2 * C * 4;
   S2T_REQUIRE(smem <= 200 * 1024, "s2t_batchnorm_bwd: C too large");
   S2T_CHECK_CUDA(cudaFuncSetAttribute(batchnorm_bwd_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  batchnorm_bwd_reduce_kernel<<<nblk, kBnThreads, smem, ST(stream)>>>(BF(da), BF(x), save_stats, BF(gamma), BF(beta),
-                                                                      partials, rows, C, act);
+  S2T_LAUNCH(batchnorm_bwd_reduce_kernel, nblk, kBnThreads, smem, ST(stream), BF(da), BF(x), save_stats, BF(gamma), BF(beta), partials, rows, C, act);
   S2T_LAUNCH_CHECK();
-  batchnorm_bwd_apply_kernel<<<nblk, kBnThreads, 0, ST(stream)>>>(BF(da), BF(x), save_stats, BF(gamma), BF(beta),
-                                                                 partials, static_cast<int>(nblk), BFM(dx),
-                                                                 BFM(dgamma), BFM(dbeta), rows, C, act, training);
+  S2T_LAUNCH(batchnorm_bwd_apply_kernel, nblk, kBnThreads, 0, ST(stream), BF(da), BF(x), save_stats, BF(gamma), BF(beta), partials, static_cast<int>(nblk), BFM(dx), BFM(dgamma), BFM(dbeta), rows, C, act, training);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -493,8 +495,7 @@ extern "C" int s2t_relpos_qbias_fwd(const void* q, long long ldq, const void* u,
   S2T_REQUIRE(q && u && v && quv, "s2t_relpos_qbias_fwd: null pointer");
   S2T_REQUIRE(C % 8 == 0 && ldq % 8 == 0, "s2t_relpos_qbias_fwd: C and ldq must be multiples of 8");
   if (rows <= 0) return 0;
-  relpos_qbias_fwd_kernel<<<cm_grid(rows * (C / 8), 256), 256, 0, ST(stream)>>>(BF(q), ldq, BF(u), BF(v), BFM(quv),
-                                                                               rows, C);
+  S2T_LAUNCH(relpos_qbias_fwd_kernel, cm_grid(rows * (C / 8), 256), 256, 0, ST(stream), BF(q), ldq, BF(u), BF(v), BFM(quv), rows, C);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -504,7 +505,7 @@ extern "C" int s2t_relpos_qbias_bwd(const void* dquv, void* dq, long long lddq, 
   S2T_REQUIRE(dquv && dq, "s2t_relpos_qbias_bwd: null pointer");
   S2T_REQUIRE(C % 8 == 0 && lddq % 8 == 0, "s2t_relpos_qbias_bwd: C and lddq must be multiples of 8");
   if (rows <= 0) return 0;
-  relpos_qbias_bwd_kernel<<<cm_grid(rows * (C / 8), 256), 256, 0, ST(stream)>>>(BF(dquv), BFM(dq), lddq, rows, C);
+  S2T_LAUNCH(relpos_qbias_bwd_kernel, cm_grid(rows * (C / 8), 256), 256, 0, ST(stream), BF(dquv), BFM(dq), lddq, rows, C);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -515,9 +516,7 @@ extern "C" int s2t_act_dropout(const void* x, void* y, long long n, int act, flo
   S2T_REQUIRE(n % 8 == 0, "s2t_act_dropout: n must be a multiple of 8");
   S2T_REQUIRE(p >= 0.f && p < 1.f, "s2t_act_dropout: p must be in [0,1)");
   if (n <= 0) return 0;
-  act_dropout_kernel<<<cm_grid(n / 8, 256), 256, 0, ST(stream)>>>(
-      BF(x), BFM(y), n / 8, act, p > 0.f ? static_cast<uint32_t>(p * 65536.f + 0.5f) : 0u, 1.f / (1.f - p), seed,
-      stream_id, seed_offset);
+  S2T_LAUNCH(act_dropout_kernel, cm_grid(n / 8, 256), 256, 0, ST(stream), BF(x), BFM(y), n / 8, act, p > 0.f ? static_cast<uint32_t>(p * 65536.f + 0.5f) : 0u, 1.f / (1.f - p), seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }

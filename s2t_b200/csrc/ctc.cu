@@ -21,6 +21,7 @@
 //   ctc_occupancy      dlogits[b][t][l'_s] -= scale * gamma_t(s), duplicates of a label merged in smem
 //   argmax / collapse  greedy decode
 #include "common.cuh"
+#include <stdlib.h>
 
 #include <math.h>
 
@@ -53,6 +54,7 @@ __device__ __forceinline__ void online_merge(float& m, float& s, float m2, float
 __global__ void __launch_bounds__(256)
 row_lse_kernel(const void* __restrict__ logits, int is_bf16, long long ldv, int V,
                float* __restrict__ lse) {
+  pdl_entry();
   __shared__ float s_m[8], s_s[8];
   const long long row = blockIdx.x;
   float m = kNegInf, s = 0.f;
@@ -127,6 +129,7 @@ __global__ void ctc_gather_kernel(const void* __restrict__ logits, int is_bf16, 
                                   long long tgt_ld, const int* __restrict__ in_len,
                                   const int* __restrict__ tgt_len, int T, int Sp, int V, int blank,
                                   CtcWs ws) {
+  pdl_entry();
   const int b = blockIdx.y;
   const int Tb = min(in_len[b], T);
   const int S = tgt_len[b];
@@ -167,11 +170,49 @@ __device__ __forceinline__ float lse3(float a, float b, float c) {
   return m + logf(__expf(a - m) + __expf(b - m) + __expf(c - m));
 }
 
+// branch-free log(e^a + e^b + e^c) on the SFU (ex2.approx / lg2.approx): the sum lies in [1, 3], where lg2.approx is
+// accurate to ~2^-21 absolute; an all -inf triple gives log(0) = -inf.
+__device__ __forceinline__ float lse3_fast(float a, float b, float c) {
+  const float m = fmaxf(fmaxf(a, b), c);
+  const float ms = (m == kNegInf) ? 0.f : m;
+  return ms + __logf(__expf(a - ms) + __expf(b - ms) + __expf(c - ms));
+}
+
+template <int N>
+__device__ __forceinline__ void vec_load(const float* __restrict__ p, float (&v)[N]) {
+  if constexpr (N == 1) {
+    v[0] = *p;
+  } else if constexpr (N == 2) {
+    const float2 t = *reinterpret_cast<const float2*>(p);
+    v[0] = t.x; v[1] = t.y;
+  } else {
+#pragma unroll
+    for (int i = 0; i < N; i += 4) {
+      const float4 t = *reinterpret_cast<const float4*>(p + i);
+      v[i] = t.x; v[i + 1] = t.y; v[i + 2] = t.z; v[i + 3] = t.w;
+    }
+  }
+}
+
+template <int N>
+__device__ __forceinline__ void vec_store(float* __restrict__ p, const float (&v)[N]) {
+  if constexpr (N == 1) {
+    *p = v[0];
+  } else if constexpr (N == 2) {
+    *reinterpret_cast<float2*>(p) = make_float2(v[0], v[1]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < N; i += 4)
+      *reinterpret_cast<float4*>(p + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+  }
+}
+
 constexpr int kCtcMaxPerThread = 4;  // Sp <= 4 * blockDim
 
 __global__ void ctc_alpha_beta_kernel(const int* __restrict__ targets, long long tgt_ld,
                                       const int* __restrict__ in_len, const int* __restrict__ tgt_len,
                                       int T, int Sp, int blank, CtcWs ws) {
+  pdl_entry();
   extern __shared__ float s_lat[];  // [2][Sp + 4]
   const int b = blockIdx.x;
   const bool fwd = blockIdx.y == 0;
@@ -285,13 +326,32 @@ __global__ void ctc_alpha_beta_kernel(const int* __restrict__ targets, long long
 // Warp-resident lattice: one warp per (utterance, direction), lane l owns the NS consecutive states
 // [l*NS, (l+1)*NS) in registers, neighbours' edge states arrive by two warp shuffles per frame — no shared
 // memory and no block barrier on the T-step critical path (the recursion is latency-bound: T dependent steps).
-template <int NS>
-__global__ void __launch_bounds__(32)
-ctc_alpha_beta_warp_kernel(const int* __restrict__ targets, long long tgt_ld, const int* __restrict__ in_len,
-                           const int* __restrict__ tgt_len, int T, int Sp, int blank, CtcWs ws) {
-  __shared__ float s_fin[32 * NS];
+// log(e^a + e^b) with one ex2 and one lg2; (-inf, -inf) -> -inf
+__device__ __forceinline__ float lse2_fast(float a, float b) {
+  const float m = fmaxf(a, b), n = fminf(a, b);
+  const float r = m + __logf(1.f + __expf(n - m));
+  return m == kNegInf ? kNegInf : r;
+}
+// log(e^a + e^b + e^c) with two ex2 and one lg2 (the largest term is exactly 1); all -inf -> -inf
+__device__ __forceinline__ float lse3_sorted(float a, float b, float c) {
+  const float hi = fmaxf(a, b), lo = fminf(a, b);
+  const float m = fmaxf(hi, c), mid = fmaxf(lo, fminf(hi, c)), mn = fminf(lo, c);
+  const float r = m + __logf(1.f + __expf(mid - m) + __expf(mn - m));
+  return m == kNegInf ? kNegInf : r;
+}
+
+// One warp walks one (utterance, direction) lattice.  The gathered emission log-probs lp_g[b] (T x Sp fp32) are staged
+// in shared memory by bulk async copies (whole utterance at once when it fits, else two alternating time chunks), so
+// the T-step dependent chain only ever waits on shared-memory loads, warp shuffles and the SFU: global-load latency
+// (and the scoreboard slots in-flight global loads would share with the shuffles) is off the critical path.
+// Blank states have no skip transition: log-sum-exp of two terms (1 ex2 + 1 lg2); label states: three terms sorted so
+// that the largest contributes exactly 1 (2 ex2 + 1 lg2).
+template <int NS, bool fwd>
+__device__ __forceinline__ void ctc_lattice_warp(const int* __restrict__ targets, long long tgt_ld,
+                                                 const int* __restrict__ in_len, const int* __restrict__ tgt_len,
+                                                 int T, int Sp, int Tc, const CtcWs& ws, float* s_fin, float* s_lp,
+                                                 uint64_t* bars) {
   const int b = blockIdx.x, lane = threadIdx.x;
-  const bool fwd = blockIdx.y == 0;
   const int Tb = min(in_len[b], T);
   const int S = tgt_len[b];
   const int Se = 2 * S + 1;
@@ -302,82 +362,116 @@ ctc_alpha_beta_warp_kernel(const int* __restrict__ targets, long long tgt_ld, co
   }
   const float* lp = ws.lp_g + static_cast<long long>(b) * T * Sp;
   float* lat = (fwd ? ws.alpha : ws.beta) + static_cast<long long>(b) * T * Sp;
+  const int n_chunks = (Tb + Tc - 1) / Tc;
+  // chunk c = steps [c*Tc, min(Tb, (c+1)*Tc)); step -> frame t = step (fwd) or Tb-1-step (bwd): a contiguous row range
+  auto issue = [&](int c) {
+    const int st0 = c * Tc, st1 = min(Tb, st0 + Tc);
+    const int t_lo = fwd ? st0 : Tb - st1;
+    const uint32_t bytes = static_cast<uint32_t>(st1 - st0) * Sp * 4u;
+    mbar_expect_tx(&bars[c & 1], bytes);
+    bulk_copy_g2s(s_lp + static_cast<size_t>(c & 1) * Tc * Sp, lp + static_cast<long long>(t_lo) * Sp, bytes,
+                  &bars[c & 1]);
+  };
+  if (lane == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    fence_mbar_init();
+    issue(0);
+    if (n_chunks > 1) issue(1);
+  }
+  __syncwarp();
   const int s0 = lane * NS;
-  bool skip[NS];
+  // Sp is a multiple of 8 (s2t_ctc_loss), so this lane's NS states are one aligned vector inside the row or all outside
+  const bool in_row = s0 < Sp;
+  bool skip[NS], live[NS];
   float prev[NS];
 #pragma unroll
   for (int k = 0; k < NS; ++k) {
     const int s = s0 + k;
     skip[k] = false;
+    live[k] = s < Se;
     if (s < Se && (s & 1)) {
       if (fwd) skip[k] = s >= 3 && tgt[s >> 1] != tgt[(s >> 1) - 1];
       else skip[k] = (s + 2 < Se) && tgt[s >> 1] != tgt[(s >> 1) + 1];
     }
   }
-  {
-    const int t = fwd ? 0 : Tb - 1;
+  const long long row_step = fwd ? Sp : -static_cast<long long>(Sp);
+  float* lat_row = lat + (fwd ? 0ll : static_cast<long long>(Tb - 1) * Sp) + s0;
+  for (int c = 0; c < n_chunks; ++c) {
+    const int st0 = c * Tc, st1 = min(Tb, st0 + Tc);
+    mbar_wait(&bars[c & 1], (c >> 1) & 1);
+    // row of `step` inside the chunk buffer: step - st0 (fwd) / st1 - 1 - step (bwd)
+    const float* buf = s_lp + static_cast<size_t>(c & 1) * Tc * Sp + s0;
+    const float* row = buf + (fwd ? 0 : (st1 - 1 - st0)) * Sp;
+    const int rstep = fwd ? Sp : -Sp;
+    int step = st0;
+    if (c == 0) {
+      float v0[NS] = {};
+      if (in_row) vec_load<NS>(row, v0);
 #pragma unroll
-    for (int k = 0; k < NS; ++k) {
-      const int s = s0 + k;
-      float v = kNegInf;
-      if (s < Se && (fwd ? (s <= 1) : (s >= Se - 2))) v = lp[static_cast<long long>(t) * Sp + s];
-      prev[k] = v;
-      if (s < Se) lat[static_cast<long long>(t) * Sp + s] = v;
+      for (int k = 0; k < NS; ++k) {
+        const int s = s0 + k;
+        prev[k] = (live[k] && (fwd ? (s <= 1) : (s >= Se - 2))) ? v0[k] : kNegInf;
+      }
+      if (in_row) vec_store<NS>(lat_row, prev);
+      lat_row += row_step;
+      row += rstep;
+      step = 1;
     }
-  }
-  constexpr int kPf = 4;
-  float pf[kPf][NS];
+    float nxt[NS] = {};
+    if (step < st1 && in_row) vec_load<NS>(row, nxt);
+#pragma unroll 4
+    for (; step < st1; ++step) {
+      float e[NS];
 #pragma unroll
-  for (int d = 0; d < kPf; ++d) {
-    const int step = 1 + d;
-    const int t = fwd ? step : Tb - 1 - step;
+      for (int k = 0; k < NS; ++k) e[k] = nxt[k];
+      row += rstep;
+      if (step + 1 < st1 && in_row) vec_load<NS>(row, nxt);
+      // n1 / n2: the states one and two positions outside this lane's range (towards s-1 fwd, s+1 bwd)
+      float n1, n2;
+      if (fwd) {
+        n1 = __shfl_up_sync(0xffffffffu, prev[NS - 1], 1);
+        n2 = NS >= 2 ? __shfl_up_sync(0xffffffffu, prev[NS >= 2 ? NS - 2 : 0], 1)
+                     : __shfl_up_sync(0xffffffffu, prev[0], 2);
+        if (lane == 0) n1 = n2 = kNegInf;
+        if (NS == 1 && lane == 1) n2 = kNegInf;
+      } else {
+        n1 = __shfl_down_sync(0xffffffffu, prev[0], 1);
+        n2 = NS >= 2 ? __shfl_down_sync(0xffffffffu, prev[NS >= 2 ? 1 : 0], 1)
+                     : __shfl_down_sync(0xffffffffu, prev[0], 2);
+        if (lane == 31) n1 = n2 = kNegInf;
+        if (NS == 1 && lane == 30) n2 = kNegInf;
+      }
+      float cur[NS];
 #pragma unroll
-    for (int k = 0; k < NS; ++k)
-      pf[d][k] = (step < Tb && s0 + k < Se) ? lp[static_cast<long long>(t) * Sp + s0 + k] : 0.f;
-  }
-  for (int step0 = 1; step0 < Tb; step0 += kPf) {
-#pragma unroll
-    for (int d = 0; d < kPf; ++d) {
-      const int step = step0 + d;
-      if (step < Tb) {  // warp-uniform
-        const int t = fwd ? step : Tb - 1 - step;
-        // n1 / n2: the states one and two positions outside this lane's range (towards s-1 fwd, s+1 bwd)
-        float n1, n2;
+      for (int k = 0; k < NS; ++k) {
+        float bb, cc;
         if (fwd) {
-          n1 = __shfl_up_sync(0xffffffffu, prev[NS - 1], 1);
-          n2 = NS >= 2 ? __shfl_up_sync(0xffffffffu, prev[NS >= 2 ? NS - 2 : 0], 1)
-                       : __shfl_up_sync(0xffffffffu, prev[0], 2);
-          if (lane == 0) n1 = n2 = kNegInf;
-          if (NS == 1 && lane == 1) n2 = kNegInf;
+          bb = k >= 1 ? prev[k >= 1 ? k - 1 : 0] : n1;
+          cc = k >= 2 ? prev[k >= 2 ? k - 2 : 0] : (k == 1 ? n1 : n2);
         } else {
-          n1 = __shfl_down_sync(0xffffffffu, prev[0], 1);
-          n2 = NS >= 2 ? __shfl_down_sync(0xffffffffu, prev[NS >= 2 ? 1 : 0], 1)
-                       : __shfl_down_sync(0xffffffffu, prev[0], 2);
-          if (lane == 31) n1 = n2 = kNegInf;
-          if (NS == 1 && lane == 30) n2 = kNegInf;
+          bb = k + 1 < NS ? prev[k + 1 < NS ? k + 1 : 0] : n1;
+          cc = k + 2 < NS ? prev[k + 2 < NS ? k + 2 : 0] : (k + 2 == NS ? n1 : n2);
         }
-        float cur[NS];
-#pragma unroll
-        for (int k = 0; k < NS; ++k) {
-          const int s = s0 + k;
-          float bb, c;
-          if (fwd) {
-            bb = k >= 1 ? prev[k >= 1 ? k - 1 : 0] : n1;
-            c = k >= 2 ? prev[k >= 2 ? k - 2 : 0] : (k == 1 ? n1 : n2);
-          } else {
-            bb = k + 1 < NS ? prev[k + 1 < NS ? k + 1 : 0] : n1;
-            c = k + 2 < NS ? prev[k + 2 < NS ? k + 2 : 0] : (k + 2 == NS ? n1 : n2);
-          }
-          if (!skip[k]) c = kNegInf;
-          const float v = (s < Se) ? lse3(prev[k], bb, c) + pf[d][k] : kNegInf;   // states >= Se stay -inf
-          cur[k] = v;
-          if (s < Se) lat[static_cast<long long>(t) * Sp + s] = v;
-          const int nstep = step + kPf;
-          const int nt = fwd ? nstep : Tb - 1 - nstep;
-          pf[d][k] = (nstep < Tb && s < Se) ? lp[static_cast<long long>(nt) * Sp + s] : 0.f;
+        float v;
+        if (NS >= 2 && (k & 1) == 0) {          // blank state (s0 is even): no skip transition
+          v = lse2_fast(prev[k], bb);
+        } else {
+          if (!skip[k]) cc = kNegInf;
+          v = lse3_sorted(prev[k], bb, cc);
         }
+        cur[k] = live[k] ? v + e[k] : kNegInf;   // states >= Se stay -inf
+      }
+      if (in_row) vec_store<NS>(lat_row, cur);
+      lat_row += row_step;
 #pragma unroll
-        for (int k = 0; k < NS; ++k) prev[k] = cur[k];
+      for (int k = 0; k < NS; ++k) prev[k] = cur[k];
+    }
+    if (c + 2 < n_chunks) {   // this buffer is free again: refill it with the chunk after next
+      __syncwarp();
+      if (lane == 0) {
+        fence_proxy_async();
+        issue(c + 2);
       }
     }
   }
@@ -395,6 +489,19 @@ ctc_alpha_beta_warp_kernel(const int* __restrict__ targets, long long tgt_ld, co
   }
 }
 
+template <int NS>
+__global__ void __launch_bounds__(32)
+ctc_alpha_beta_warp_kernel(const int* __restrict__ targets, long long tgt_ld, const int* __restrict__ in_len,
+                           const int* __restrict__ tgt_len, int T, int Sp, int Tc, CtcWs ws) {
+  pdl_entry();
+  extern __shared__ __align__(128) uint8_t s_dyn[];   // [1 or 2][Tc][Sp] fp32 emission rows
+  __shared__ float s_fin[32 * NS];
+  __shared__ __align__(8) uint64_t s_bars[2];
+  float* s_lp = reinterpret_cast<float*>(s_dyn);
+  if (blockIdx.y == 0) ctc_lattice_warp<NS, true>(targets, tgt_ld, in_len, tgt_len, T, Sp, Tc, ws, s_fin, s_lp, s_bars);
+  else ctc_lattice_warp<NS, false>(targets, tgt_ld, in_len, tgt_len, T, Sp, Tc, ws, s_fin, s_lp, s_bars);
+}
+
 // dlogits = scale * softmax(logits) for valid frames of feasible utterances, 0 elsewhere; also
 // publishes nll with zero_infinity applied.
 __global__ void __launch_bounds__(256)
@@ -402,6 +509,7 @@ ctc_dense_grad_kernel(const void* __restrict__ logits, int is_bf16, long long ld
                       const float* __restrict__ lse, const int* __restrict__ in_len, int T, int V,
                       const float* __restrict__ nll_raw, float* __restrict__ nll_out,
                       void* __restrict__ dlogits, float scale) {
+  pdl_entry();
   const long long row = blockIdx.x;
   const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
   const float nr = nll_raw[b];
@@ -439,6 +547,7 @@ __global__ void ctc_occupancy_kernel(const int* __restrict__ targets, long long 
                                      const int* __restrict__ in_len, const int* __restrict__ tgt_len,
                                      int T, int Sp, int V, int blank, CtcWs ws, int is_bf16,
                                      long long ldv, void* __restrict__ dlogits, float scale) {
+  pdl_entry();
   extern __shared__ float s_occ[];  // [Sp]
   const int t = blockIdx.x, b = blockIdx.y;
   const float nr = ws.nll_raw[b];
@@ -490,6 +599,7 @@ __global__ void __launch_bounds__(256)
 ctc_argmax_kernel(const void* __restrict__ logits, int is_bf16, long long ldv,
                   const int* __restrict__ in_len, int T, int V, int blank,
                   int* __restrict__ frame_ids, float* __restrict__ frame_lp) {
+  pdl_entry();
   __shared__ float s_v[8];
   __shared__ int s_i[8];
   __shared__ float s_best;
@@ -557,6 +667,7 @@ ctc_argmax_kernel(const void* __restrict__ logits, int is_bf16, long long ldv,
 __global__ void ctc_collapse_kernel(const int* __restrict__ frame_ids, int T, int blank,
                                     int* __restrict__ tokens, int* __restrict__ out_len,
                                     const float* __restrict__ frame_lp, float* __restrict__ scores) {
+  pdl_entry();
   const int b = blockIdx.x;
   const int lane = threadIdx.x;
   const int* ids = frame_ids + static_cast<long long>(b) * T;
@@ -595,13 +706,13 @@ extern "C" int s2t_row_lse(const void* logits, int is_bf16, long long ldv, int r
   S2T_REQUIRE(V > 0, "s2t_row_lse: V must be positive");
   S2T_REQUIRE(ldv % (is_bf16 ? 8 : 4) == 0, "s2t_row_lse: ldv alignment");
   if (rows <= 0) return 0;
-  row_lse_kernel<<<rows, 256, 0, ST(stream)>>>(logits, is_bf16, ldv, V, lse);
+  S2T_LAUNCH(row_lse_kernel, rows, 256, 0, ST(stream), logits, is_bf16, ldv, V, lse);
   S2T_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" long long s2t_ctc_workspace_bytes(int batch, int T, int max_target_len) {
-  const int Sp = 2 * max_target_len + 1;
+  const int Sp = (2 * max_target_len + 1 + 7) & ~7;   // rows are whole 16-byte vectors
   return 4 * ctc_ws_floats(batch, T, Sp) + 256;
 }
 
@@ -619,12 +730,13 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
               "s2t_ctc_loss: workspace too small");
   S2T_REQUIRE(ldv % (is_bf16 ? 8 : 4) == 0, "s2t_ctc_loss: ldv alignment");
   if (batch <= 0 || T <= 0) return 0;
-  const int Sp = 2 * max_target_len + 1;
+  const int Sp = (2 * max_target_len + 1 + 7) & ~7;   // rows are whole 16-byte vectors
   int threads = ((Sp + 31) / 32) * 32;
   if (threads > 1024) threads = 1024;
   if (threads < 64) threads = 64;
   S2T_REQUIRE(Sp <= kCtcMaxPerThread * threads, "s2t_ctc_loss: target too long (2S+1=%d > %d)", Sp,
               kCtcMaxPerThread * threads);
+  S2T_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "s2t_ctc_loss: workspace must be 16-byte aligned");
   CtcWs ws;
   float* base = reinterpret_cast<float*>(workspace);
   const long long n = 1ll * batch * T * Sp;
@@ -639,34 +751,46 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
     int gx = static_cast<int>((1ll * T * Sp + 255) / 256);
     if (gx > 64) gx = 64;
     if (gx < 1) gx = 1;
-    ctc_gather_kernel<<<dim3(gx, batch), 256, 0, st>>>(logits, is_bf16, ldv, lse, targets, tgt_ld,
-                                                      input_lengths, target_lengths, T, Sp, V, blank, ws);
+    S2T_LAUNCH(ctc_gather_kernel, dim3(gx, batch), 256, 0, st, logits, is_bf16, ldv, lse, targets, tgt_ld, input_lengths, target_lengths, T, Sp, V, blank, ws);
     S2T_LAUNCH_CHECK();
   }
   {
     const size_t smem = sizeof(float) * 2 * (Sp + 4);
     const dim3 g(batch, 2);
+    // shared-memory staging of the emission rows: whole utterance when T*Sp*4 <= 200 KB, else two 100 KB time chunks
+    const size_t row_bytes = static_cast<size_t>(Sp) * 4;
+    int Tc = T;
+    size_t lat_smem = static_cast<size_t>(T) * row_bytes;
+    if (lat_smem > 200 * 1024) {
+      Tc = static_cast<int>((100 * 1024) / row_bytes);
+      lat_smem = 2 * static_cast<size_t>(Tc) * row_bytes;
+    }
+#define S2T_CTC_WARP(NS)                                                                                          \
+  do {                                                                                                            \
+    S2T_CHECK_CUDA(cudaFuncSetAttribute(ctc_alpha_beta_warp_kernel<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                        210 * 1024));                                                             \
+    S2T_LAUNCH(ctc_alpha_beta_warp_kernel<NS>, g, 32, lat_smem, st, targets, tgt_ld, input_lengths, target_lengths, T, \
+               Sp, Tc, ws);                                                                                       \
+  } while (0)
     if (Sp <= 32)
-      ctc_alpha_beta_warp_kernel<1><<<g, 32, 0, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+      S2T_CTC_WARP(1);
     else if (Sp <= 64)
-      ctc_alpha_beta_warp_kernel<2><<<g, 32, 0, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+      S2T_CTC_WARP(2);
     else if (Sp <= 128)
-      ctc_alpha_beta_warp_kernel<4><<<g, 32, 0, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+      S2T_CTC_WARP(4);
     else if (Sp <= 256)
-      ctc_alpha_beta_warp_kernel<8><<<g, 32, 0, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+      S2T_CTC_WARP(8);
+#undef S2T_CTC_WARP
     else
-      ctc_alpha_beta_kernel<<<g, threads, smem, st>>>(targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+      S2T_LAUNCH(ctc_alpha_beta_kernel, g, threads, smem, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
     S2T_LAUNCH_CHECK();
   }
-  ctc_dense_grad_kernel<<<batch * T, 256, 0, st>>>(logits, is_bf16, ldv, lse, input_lengths, T, V,
-                                                  ws.nll_raw, nll, dlogits, grad_scale);
+  S2T_LAUNCH(ctc_dense_grad_kernel, batch * T, 256, 0, st, logits, is_bf16, ldv, lse, input_lengths, T, V, ws.nll_raw, nll, dlogits, grad_scale);
   S2T_LAUNCH_CHECK();
   if (dlogits != nullptr) {
     int othreads = ((Sp + 31) / 32) * 32;
     if (othreads > 256) othreads = 256;
-    ctc_occupancy_kernel<<<dim3(T, batch), othreads, sizeof(float) * Sp, st>>>(
-        targets, tgt_ld, input_lengths, target_lengths, T, Sp, V, blank, ws, is_bf16, ldv, dlogits,
-        grad_scale);
+    S2T_LAUNCH(ctc_occupancy_kernel, dim3(T, batch), othreads, sizeof(float) * Sp, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, V, blank, ws, is_bf16, ldv, dlogits, grad_scale);
     S2T_LAUNCH_CHECK();
   }
   return 0;
@@ -681,10 +805,9 @@ extern "C" int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, co
               "s2t_ctc_greedy: scores [B] and frame_lp [B][T] go together");
   S2T_REQUIRE(ldv % (is_bf16 ? 8 : 1) == 0, "s2t_ctc_greedy: bf16 rows must be 16-byte aligned (ldv % 8 == 0)");
   if (batch <= 0 || T <= 0) return 0;
-  ctc_argmax_kernel<<<batch * T, 256, 0, ST(stream)>>>(logits, is_bf16, ldv, input_lengths, T, V, blank,
-                                                      frame_ids, frame_lp);
+  S2T_LAUNCH(ctc_argmax_kernel, batch * T, 256, 0, ST(stream), logits, is_bf16, ldv, input_lengths, T, V, blank, frame_ids, frame_lp);
   S2T_LAUNCH_CHECK();
-  ctc_collapse_kernel<<<batch, 32, 0, ST(stream)>>>(frame_ids, T, blank, tokens, out_lengths, frame_lp, scores);
+  S2T_LAUNCH(ctc_collapse_kernel, batch, 32, 0, ST(stream), frame_ids, T, blank, tokens, out_lengths, frame_lp, scores);
   S2T_LAUNCH_CHECK();
   return 0;
 }

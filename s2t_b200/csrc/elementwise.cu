@@ -26,6 +26,7 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf
 __global__ void glu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                long long ldy, long long y_bs, long long rows, int C,
                                const int* __restrict__ lengths, int T) {
+  pdl_entry();
   const int cv = C >> 3;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= rows * cv) return;
@@ -51,6 +52,7 @@ __global__ void glu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat1
 __global__ void glu_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                                long long lddy, __nv_bfloat16* __restrict__ dx, long long rows, int C,
                                const int* __restrict__ lengths, int T) {
+  pdl_entry();
   const int cv = C >> 3;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= rows * cv) return;
@@ -81,20 +83,41 @@ __global__ void glu_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_b
 // ---------------------------------------------------------------------------------------------
 // column sums (bias gradients): two stages, fp32 partials [slabs][C]
 // ---------------------------------------------------------------------------------------------
-constexpr int kColsumRowsPerSlab = 64;
+constexpr int kColsumRowsPerSlab = 64;   // legacy workspace sizing (s2t_colsum_workspace_floats); no longer written
+constexpr int kColsumCluster = 8;        // CTAs of one cluster split the rows of a 64-column strip
 
-__global__ void colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int rows,
-                                      int C, float* __restrict__ partials) {
-  // block (32, 8): 32 lanes x 8-wide vectors = 256 columns per blockIdx.x; 8 row slices
-  __shared__ float s_acc[8][256];
-  const int col = (blockIdx.x * 32 + threadIdx.x) * 8;
-  const int r0 = blockIdx.y * kColsumRowsPerSlab;
-  const int r1 = min(rows, r0 + kColsumRowsPerSlab);
+// One launch: a cluster of 8 CTAs owns a 64-column strip; CTA r sums rows r, r+8, ... (thread (x, y): 8 columns
+// 8x..8x+7 of rows r + 8*(y + 32*i)), reduces its 32 row slices through shared memory, and the cluster leader
+// gathers the 8 per-CTA strips over DSMEM and writes the bf16 result (optionally accumulating into it).
+__global__ void __cluster_dims__(1, kColsumCluster, 1) __launch_bounds__(256)
+colsum_cluster_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int rows, int C,
+                      __nv_bfloat16* __restrict__ out, int accumulate) {
+  pdl_entry();
+  __shared__ float s_acc[32][65];
+  __shared__ __align__(16) float s_strip[64];
+  const int lx = threadIdx.x & 7, ly = threadIdx.x >> 3;      // 8 column groups x 32 row slices
+  const int col = blockIdx.x * 64 + lx * 8;
+  const int rank = static_cast<int>(cluster_ctarank());
   float acc[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
   if (col < C) {
-    for (int r = r0 + threadIdx.y; r < r1; r += 8) {
+    const int stride = kColsumCluster * 32;
+    int r = rank + kColsumCluster * ly;
+    for (; r + 3 * stride < rows; r += 4 * stride) {            // four independent 16-byte loads in flight
+      uint4 q[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        q[u] = *reinterpret_cast<const uint4*>(x + static_cast<long long>(r + u * stride) * ld + col);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float v[8];
+        unpack8e(q[u], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += v[j];
+      }
+    }
+    for (; r < rows; r += stride) {
       float v[8];
       unpack8e(*reinterpret_cast<const uint4*>(x + static_cast<long long>(r) * ld + col), v);
 #pragma unroll
@@ -102,26 +125,31 @@ __global__ void colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long 
     }
   }
 #pragma unroll
-  for (int j = 0; j < 8; ++j) s_acc[threadIdx.y][threadIdx.x * 8 + j] = acc[j];
+  for (int j = 0; j < 8; ++j) s_acc[ly][lx * 8 + j] = acc[j];
   __syncthreads();
-  const int t = threadIdx.y * 32 + threadIdx.x;  // 0..255
-  const int c = blockIdx.x * 256 + t;
-  if (c < C) {
-    float s = 0.f;
+  if (threadIdx.x < 64) {
+    float t = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) s += s_acc[k][t];
-    partials[static_cast<long long>(blockIdx.y) * C + c] = s;
+    for (int k = 0; k < 32; ++k) t += s_acc[k][threadIdx.x];
+    s_strip[threadIdx.x] = t;
   }
-}
-
-__global__ void colsum_final_kernel(const float* __restrict__ partials, int slabs, int C,
-                                    __nv_bfloat16* __restrict__ out, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  float s = 0.f;
-  for (int k = 0; k < slabs; ++k) s += partials[static_cast<long long>(k) * C + c];
-  if (accumulate) s += __bfloat162float(out[c]);
-  out[c] = __float2bfloat16(s);
+  cluster_sync_all();
+  if (rank == 0 && threadIdx.x < 64) {
+    const int c = blockIdx.x * 64 + threadIdx.x;
+    const uint32_t local = smem_u32(&s_strip[threadIdx.x]);
+    float t = 0.f;
+#pragma unroll
+    for (int pr = 0; pr < kColsumCluster; ++pr) {
+      float v;
+      asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(dsmem_addr(local, pr)) : "memory");
+      t += v;
+    }
+    if (c < C) {
+      if (accumulate) t += __bfloat162float(out[c]);
+      out[c] = __float2bfloat16(t);
+    }
+  }
+  cluster_sync_all();   // the strips of ranks > 0 stay alive until the leader has read them
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -129,6 +157,7 @@ __global__ void colsum_final_kernel(const float* __restrict__ partials, int slab
 // ---------------------------------------------------------------------------------------------
 __global__ void col2im1d_kernel(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx,
                                 int batch, int t_in, int t_out, int C, int ksize, int stride, int pad) {
+  pdl_entry();
   const int cv = C >> 3;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<long long>(batch) * t_in * cv) return;
@@ -164,6 +193,7 @@ __global__ void embed_fwd_kernel(const __nv_bfloat16* __restrict__ x, const int*
                                  __nv_bfloat16* __restrict__ y, int batch, int T, int C, float scale,
                                  uint32_t thresh16, float inv_keep, unsigned long long seed,
                                  uint32_t stream_id, const unsigned long long* __restrict__ seed_off) {
+  pdl_entry();
   if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const int cv = C >> 3;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -195,6 +225,7 @@ __global__ void embed_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bflo
                                  long long n_vec, float scale, uint32_t thresh16, float inv_keep,
                                  unsigned long long seed, uint32_t stream_id,
                                  const unsigned long long* __restrict__ seed_off) {
+  pdl_entry();
   if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n_vec) return;
@@ -212,6 +243,7 @@ __global__ void embed_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bflo
 
 __global__ void mask_rows_kernel(__nv_bfloat16* __restrict__ x, const int* __restrict__ lengths,
                                  int batch, int T, int C, long long ld) {
+  pdl_entry();
   const int cv = C >> 3;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<long long>(batch) * T * cv) return;
@@ -225,6 +257,7 @@ __global__ void mask_rows_kernel(__nv_bfloat16* __restrict__ x, const int* __res
 __global__ void permute_conv_weight_kernel(const __nv_bfloat16* __restrict__ w,
                                            __nv_bfloat16* __restrict__ out, int cout, int cin, int k,
                                            int inverse) {
+  pdl_entry();
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long n = static_cast<long long>(cout) * cin * k;
   if (i >= n) return;
@@ -242,6 +275,7 @@ __global__ void permute_conv_weight_kernel(const __nv_bfloat16* __restrict__ w,
 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                      long long n) {
+  pdl_entry();
   const long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
   if (i + 3 < n) {
     const float4 v = *reinterpret_cast<const float4*>(x + i);
@@ -255,6 +289,7 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16*
 }
 __global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y,
                                      long long n) {
+  pdl_entry();
   const long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
   if (i + 3 < n) {
     const uint2 v = *reinterpret_cast<const uint2*>(x + i);
@@ -282,8 +317,7 @@ extern "C" int s2t_glu_fwd(const void* x, void* y, long long ldy, long long y_bs
   S2T_REQUIRE(y_bs == 0 || T > 0, "s2t_glu_fwd: y_bs needs T");
   if (rows <= 0) return 0;
   const long long n = static_cast<long long>(rows) * (C / 8);
-  glu_fwd_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), ldy, y_bs, rows, C,
-                                                            lengths, T > 0 ? T : 1);
+  S2T_LAUNCH(glu_fwd_kernel, blocks_for(n, 256), 256, 0, ST(stream), CBF(x), BF(y), ldy, y_bs, rows, C, lengths, T > 0 ? T : 1);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -294,8 +328,7 @@ extern "C" int s2t_glu_bwd(const void* x, const void* dy, long long lddy, void* 
   S2T_REQUIRE(C % 8 == 0 && lddy % 8 == 0, "s2t_glu_bwd: C and lddy must be multiples of 8");
   if (rows <= 0) return 0;
   const long long n = static_cast<long long>(rows) * (C / 8);
-  glu_bwd_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), CBF(dy), lddy, BF(dx), rows, C,
-                                                            lengths, T > 0 ? T : 1);
+  S2T_LAUNCH(glu_bwd_kernel, blocks_for(n, 256), 256, 0, ST(stream), CBF(x), CBF(dy), lddy, BF(dx), rows, C, lengths, T > 0 ? T : 1);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -311,11 +344,8 @@ extern "C" int s2t_colsum(const void* x, long long ld, int rows, int C, void* ou
   S2T_REQUIRE(C % 8 == 0 && ld % 8 == 0, "s2t_colsum: C and ld must be multiples of 8");
   S2T_REQUIRE(workspace_floats >= s2t_colsum_workspace_floats(rows, C), "s2t_colsum: workspace too small");
   if (rows <= 0) return 0;
-  const int slabs = (rows + kColsumRowsPerSlab - 1) / kColsumRowsPerSlab;
-  dim3 grid((C + 255) / 256, slabs), block(32, 8);
-  colsum_partial_kernel<<<grid, block, 0, ST(stream)>>>(CBF(x), ld, rows, C, workspace);
-  S2T_LAUNCH_CHECK();
-  colsum_final_kernel<<<(C + 127) / 128, 128, 0, ST(stream)>>>(workspace, slabs, C, BF(out), accumulate);
+  (void)workspace_floats;
+  S2T_LAUNCH(colsum_cluster_kernel, dim3((C + 63) / 64, kColsumCluster), 256, 0, ST(stream), CBF(x), ld, rows, C, BF(out), accumulate);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -326,8 +356,7 @@ extern "C" int s2t_col2im1d(const void* dcol, void* dx, int batch, int t_in, int
   S2T_REQUIRE(C % 8 == 0 && stride > 0 && ksize > 0, "s2t_col2im1d: bad shape");
   const long long n = static_cast<long long>(batch) * t_in * (C / 8);
   if (n <= 0) return 0;
-  col2im1d_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(CBF(dcol), BF(dx), batch, t_in, t_out, C,
-                                                             ksize, stride, pad);
+  S2T_LAUNCH(col2im1d_kernel, blocks_for(n, 256), 256, 0, ST(stream), CBF(dcol), BF(dx), batch, t_in, t_out, C, ksize, stride, pad);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -343,9 +372,7 @@ extern "C" int s2t_embed_fwd(const void* x, const int* lengths, const float* pos
   S2T_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "s2t_embed_fwd: bad dropout_p");
   const long long n = static_cast<long long>(batch) * T * (C / 8);
   if (n <= 0) return 0;
-  embed_fwd_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(
-      CBF(x), lengths, pos_table, n_pos, BF(y), batch, T, C, scale,
-      dropout_p > 0.f ? thresh16(dropout_p) : 0u, 1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
+  S2T_LAUNCH(embed_fwd_kernel, blocks_for(n, 256), 256, 0, ST(stream), CBF(x), lengths, pos_table, n_pos, BF(y), batch, T, C, scale, dropout_p > 0.f ? thresh16(dropout_p) : 0u, 1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -357,9 +384,7 @@ extern "C" int s2t_embed_bwd(const void* dy, void* dx, int batch, int T, int C, 
   S2T_REQUIRE(C % 8 == 0, "s2t_embed_bwd: C must be a multiple of 8");
   const long long n = static_cast<long long>(batch) * T * (C / 8);
   if (n <= 0) return 0;
-  embed_bwd_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(
-      CBF(dy), BF(dx), n, scale, dropout_p > 0.f ? thresh16(dropout_p) : 0u, 1.f / (1.f - dropout_p),
-      seed, stream_id, seed_offset);
+  S2T_LAUNCH(embed_bwd_kernel, blocks_for(n, 256), 256, 0, ST(stream), CBF(dy), BF(dx), n, scale, dropout_p > 0.f ? thresh16(dropout_p) : 0u, 1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -370,7 +395,7 @@ extern "C" int s2t_mask_rows(void* x, const int* lengths, int batch, int T, int 
   S2T_REQUIRE(C % 8 == 0 && ld % 8 == 0, "s2t_mask_rows: C and ld must be multiples of 8");
   const long long n = static_cast<long long>(batch) * T * (C / 8);
   if (n <= 0) return 0;
-  mask_rows_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(BF(x), lengths, batch, T, C, ld);
+  S2T_LAUNCH(mask_rows_kernel, blocks_for(n, 256), 256, 0, ST(stream), BF(x), lengths, batch, T, C, ld);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -380,8 +405,7 @@ extern "C" int s2t_permute_conv_weight(const void* w, void* out, int cout, int c
   S2T_REQUIRE(w && out, "s2t_permute_conv_weight: null pointer");
   const long long n = static_cast<long long>(cout) * cin * k;
   if (n <= 0) return 0;
-  permute_conv_weight_kernel<<<blocks_for(n, 256), 256, 0, ST(stream)>>>(CBF(w), BF(out), cout, cin, k,
-                                                                        inverse);
+  S2T_LAUNCH(permute_conv_weight_kernel, blocks_for(n, 256), 256, 0, ST(stream), CBF(w), BF(out), cout, cin, k, inverse);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -389,14 +413,14 @@ extern "C" int s2t_permute_conv_weight(const void* w, void* out, int cout, int c
 extern "C" int s2t_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream) {
   S2T_REQUIRE(x && y, "s2t_cast_f32_to_bf16: null pointer");
   if (n <= 0) return 0;
-  cast_f32_bf16_kernel<<<blocks_for((n + 3) / 4, 256), 256, 0, ST(stream)>>>(x, BF(y), n);
+  S2T_LAUNCH(cast_f32_bf16_kernel, blocks_for((n + 3) / 4, 256), 256, 0, ST(stream), x, BF(y), n);
   S2T_LAUNCH_CHECK();
   return 0;
 }
 extern "C" int s2t_cast_bf16_to_f32(const void* x, float* y, long long n, void* stream) {
   S2T_REQUIRE(x && y, "s2t_cast_bf16_to_f32: null pointer");
   if (n <= 0) return 0;
-  cast_bf16_f32_kernel<<<blocks_for((n + 3) / 4, 256), 256, 0, ST(stream)>>>(CBF(x), y, n);
+  S2T_LAUNCH(cast_bf16_f32_kernel, blocks_for((n + 3) / 4, 256), 256, 0, ST(stream), CBF(x), y, n);
   S2T_LAUNCH_CHECK();
   return 0;
 }

@@ -29,6 +29,7 @@ fbank_kernel(const float* __restrict__ wave, long long wave_ld, const int* __res
              const float* __restrict__ mel_w, const int* __restrict__ mel_range,
              const float* __restrict__ window, int n_mels, void* __restrict__ out, int out_bf16,
              int max_frames, long long out_ld, long long out_bs, int* __restrict__ out_frames) {
+  pdl_entry();
   __shared__ float2 s_fft[kFbankWarps][kFft];
   __shared__ float s_pow[kFbankWarps][kBins + 3];
   __shared__ float2 s_tw[kFft / 2];  // exp(-2*pi*i*k/512)
@@ -133,15 +134,20 @@ fbank_kernel(const float* __restrict__ wave, long long wave_ld, const int* __res
 // SEQUENTIAL fp32 sum over frames, and the catastrophic cancellation of that formula is part of the
 // oracle.  So: frames are staged chunk-wise in shared memory by the whole CTA (coalesced),
 // and one thread per bin replays the exact sequential fp32 accumulation (no FMA contraction).
-constexpr int kCmvnChunk = 64;
+constexpr int kCmvnChunk = 128;
 
 // stats[b][0][f] = mean (0 when !norm_means), stats[b][1][f] = std (1 when !norm_vars).  One CTA per utterance; the
-// next chunk is prefetched into registers while the current one is accumulated from shared memory.
+// next chunk is prefetched into registers while the current one is accumulated from shared memory.  Threads 0..127
+// carry the per-bin sum chain, threads 128..255 the per-bin sum-of-squares chain (each one dependent fp32 add per
+// frame, in frame order: numpy's axis-0 reduction order, so the result is bit-exact); shared loads are issued eight
+// frames ahead of the adds.
 __global__ void __launch_bounds__(256)
 cmvn_utt_stats_kernel(const float* __restrict__ in, long long in_ld, long long in_bs,
                       const int* __restrict__ num_frames, int max_frames, int n_mels, int norm_means,
                       int norm_vars, float* __restrict__ stats) {
+  pdl_entry();
   extern __shared__ float s_chunk[];  // [2][kCmvnChunk][n_mels]
+  __shared__ float s_sq[128];
   constexpr int kPer = (kCmvnChunk * 128 + 255) / 256;  // n_mels <= 128
   const int b = blockIdx.x;
   int T = num_frames[b];
@@ -168,8 +174,30 @@ cmvn_utt_stats_kernel(const float* __restrict__ in, long long in_ld, long long i
       if (k < per && i < nt * n_mels) buf[i] = reg[k];
     }
   };
-  float sum = 0.f, sq = 0.f;
-  if (T > 0) {
+  const int f = threadIdx.x & 127;
+  const bool squares = threadIdx.x >= 128;
+  float acc = 0.f;
+  // contiguous, 16-byte aligned rows: chunks arrive by bulk async copy (one instruction per chunk, completion on an
+  // mbarrier), so the accumulation loop waits on shared memory only; otherwise they are staged through registers.
+  __shared__ __align__(8) uint64_t s_bar[2];
+  const bool bulk = in_ld == n_mels && (n_mels & 3) == 0 && (in_bs & 3) == 0 &&
+                    (reinterpret_cast<uintptr_t>(in) & 15) == 0;
+  auto issue = [&](int chunk) {   // thread 0
+    const int t0 = chunk * kCmvnChunk;
+    const uint32_t bytes = static_cast<uint32_t>(min(kCmvnChunk, T - t0)) * n_mels * 4u;
+    mbar_expect_tx(&s_bar[chunk & 1], bytes);
+    bulk_copy_g2s(s_chunk + (chunk & 1) * kCmvnChunk * n_mels, src + static_cast<long long>(t0) * in_ld, bytes,
+                  &s_bar[chunk & 1]);
+  };
+  if (bulk) {
+    if (threadIdx.x == 0) {
+      mbar_init(&s_bar[0], 1);
+      mbar_init(&s_bar[1], 1);
+      fence_mbar_init();
+      if (T > 0) issue(0);
+      if (T > kCmvnChunk) issue(1);
+    }
+  } else if (T > 0) {
     fetch(0);
     stash(s_chunk, 0);
   }
@@ -177,21 +205,42 @@ cmvn_utt_stats_kernel(const float* __restrict__ in, long long in_ld, long long i
   int cur = 0;
   for (int t0 = 0; t0 < T; t0 += kCmvnChunk) {
     const int nt = min(kCmvnChunk, T - t0);
+    const int chunk = t0 / kCmvnChunk;
     const bool more = t0 + kCmvnChunk < T;
-    if (more) fetch(t0 + kCmvnChunk);
-    const float* buf = s_chunk + cur * kCmvnChunk * n_mels;
-    if (threadIdx.x < n_mels) {
-      for (int t = 0; t < nt; ++t) {
-        const float v = buf[t * n_mels + threadIdx.x];
-        sum = __fadd_rn(sum, v);
-        sq = __fadd_rn(sq, __fmul_rn(v, v));
+    if (bulk) mbar_wait(&s_bar[chunk & 1], (chunk >> 1) & 1);
+    else if (more) fetch(t0 + kCmvnChunk);
+    const float* col = s_chunk + cur * kCmvnChunk * n_mels + f;
+    if (f < n_mels) {
+      int t = 0;
+      for (; t + 8 <= nt; t += 8) {
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = col[(t + j) * n_mels];
+        if (squares) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc = __fadd_rn(acc, __fmul_rn(v[j], v[j]));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc = __fadd_rn(acc, v[j]);
+        }
+      }
+      for (; t < nt; ++t) {
+        const float v = col[t * n_mels];
+        acc = squares ? __fadd_rn(acc, __fmul_rn(v, v)) : __fadd_rn(acc, v);
       }
     }
-    if (more) stash(s_chunk + (cur ^ 1) * kCmvnChunk * n_mels, t0 + kCmvnChunk);
+    if (!bulk && more) stash(s_chunk + (cur ^ 1) * kCmvnChunk * n_mels, t0 + kCmvnChunk);
     __syncthreads();
+    if (bulk && threadIdx.x == 0 && t0 + 2 * kCmvnChunk < T) {   // buffer `cur` has been consumed by every thread
+      fence_proxy_async();
+      issue(chunk + 2);
+    }
     cur ^= 1;
   }
+  if (squares) s_sq[f] = acc;
+  __syncthreads();
   if (threadIdx.x < n_mels) {
+    const float sum = acc, sq = s_sq[f];
     const float Tn = static_cast<float>(T > 0 ? T : 1);
     const float m = __fdiv_rn(sum, Tn);
     float sd = 1.f;
@@ -210,6 +259,7 @@ __global__ void __launch_bounds__(256)
 cmvn_apply_kernel(const float* __restrict__ in, long long in_ld, long long in_bs, void* __restrict__ out,
                   int out_bf16, long long out_ld, long long out_bs, const int* __restrict__ num_frames,
                   int max_frames, int n_mels, int norm_vars, const float* __restrict__ stats) {
+  pdl_entry();
   const int b = blockIdx.y;
   int T = num_frames[b];
   if (T > max_frames) T = max_frames;
@@ -239,6 +289,7 @@ __global__ void cmvn_global_kernel(const float* __restrict__ in, long long in_ld
                                    long long out_bs, const int* __restrict__ num_frames,
                                    int max_frames, int n_mels, const float* __restrict__ mean,
                                    const float* __restrict__ std_) {
+  pdl_entry();
   const int b = blockIdx.y;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<long long>(max_frames) * n_mels) return;
@@ -267,9 +318,7 @@ extern "C" int s2t_fbank_fwd(const float* wave, long long wave_ld, const int* nu
   S2T_REQUIRE(n_mels > 0 && n_mels <= 128, "s2t_fbank_fwd: n_mels=%d out of range", n_mels);
   if (batch <= 0 || max_frames <= 0) return 0;
   dim3 grid((max_frames + kFbankWarps - 1) / kFbankWarps, batch);
-  fbank_kernel<<<grid, kFbankWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      wave, wave_ld, num_samples, mel_w, mel_range, window, n_mels, out, out_bf16, max_frames, out_ld,
-      out_bs, out_frames);
+  S2T_LAUNCH(fbank_kernel, grid, kFbankWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream), wave, wave_ld, num_samples, mel_w, mel_range, window, n_mels, out, out_bf16, max_frames, out_ld, out_bs, out_frames);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -287,16 +336,13 @@ extern "C" int s2t_cmvn_utt(const float* feats, long long in_ld, long long in_bs
   if (norm) {
     const size_t smem = sizeof(float) * 2 * kCmvnChunk * n_mels;
     S2T_CHECK_CUDA(cudaFuncSetAttribute(cmvn_utt_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
-    cmvn_utt_stats_kernel<<<batch, 256, smem, st>>>(feats, in_ld, in_bs, num_frames, max_frames, n_mels, norm_means,
-                                                   norm_vars, stats);
+    S2T_LAUNCH(cmvn_utt_stats_kernel, batch, 256, smem, st, feats, in_ld, in_bs, num_frames, max_frames, n_mels, norm_means, norm_vars, stats);
     S2T_LAUNCH_CHECK();
   }
   const long long total = static_cast<long long>(max_frames) * n_mels;
   long long gx = (total + 256 * 4 - 1) / (256 * 4);
   if (gx > 1024) gx = 1024;
-  cmvn_apply_kernel<<<dim3(static_cast<unsigned>(gx), batch), 256, 0, st>>>(
-      feats, in_ld, in_bs, out, out_bf16, out_ld, out_bs, num_frames, max_frames, n_mels, norm_vars,
-      norm ? stats : nullptr);
+  S2T_LAUNCH(cmvn_apply_kernel, dim3(static_cast<unsigned>(gx), batch), 256, 0, st, feats, in_ld, in_bs, out, out_bf16, out_ld, out_bs, num_frames, max_frames, n_mels, norm_vars, norm ? stats : nullptr);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -309,8 +355,7 @@ extern "C" int s2t_cmvn_global(const float* feats, long long in_ld, long long in
   if (batch <= 0 || max_frames <= 0) return 0;
   const long long n = static_cast<long long>(max_frames) * n_mels;
   dim3 grid(static_cast<unsigned>((n + 255) / 256), batch);
-  cmvn_global_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      feats, in_ld, in_bs, out, out_bf16, out_ld, out_bs, num_frames, max_frames, n_mels, mean, std_);
+  S2T_LAUNCH(cmvn_global_kernel, grid, 256, 0, reinterpret_cast<cudaStream_t>(stream), feats, in_ld, in_bs, out, out_bf16, out_ld, out_bs, num_frames, max_frames, n_mels, mean, std_);
   S2T_LAUNCH_CHECK();
   return 0;
 }

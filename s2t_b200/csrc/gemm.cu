@@ -76,10 +76,34 @@ __device__ __forceinline__ float apply_act(float v, int act) {
 constexpr int kEpiGeneric = -1;
 constexpr int epi_code(int act, int gate, int drop, int res) { return act | (gate << 2) | (drop << 4) | (res << 5); }
 
+// Gate / residual operands of one staged output unit (up to 8 groups of 8 columns of this thread's row), fetched
+// BEFORE the accumulator is waited for so that their L2/HBM latency hides behind the MMA main loop instead of being
+// paid once per 8-column group on the epilogue's critical path.
+struct AuxUnit {
+  uint4 g[8];
+  uint4 r[8];
+};
+
+template <int EPI>
+__device__ __forceinline__ void aux_prefetch(AuxUnit& ax, const GemmKernelParams& p, int ucol0, int ngroups,
+                                             bool row_ok, long long grow, long long rrow) {
+  const bool need_g = EPI < 0 ? (p.gate_mode != S2T_GATE_NONE) : (((EPI >> 2) & 3) != 0);
+  const bool need_r = (EPI < 0 ? true : ((EPI >> 5) & 1)) && p.residual != nullptr;
+  if (!p.aux_vec || !row_ok || !(need_g || need_r)) return;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int col = ucol0 + i * 8;
+    if (i < ngroups && col + 8 <= p.N) {
+      if (need_g) ax.g[i] = __ldg(reinterpret_cast<const uint4*>(p.gate + grow + col));
+      if (need_r) ax.r[i] = __ldg(reinterpret_cast<const uint4*>(p.residual + rrow + col));
+    }
+  }
+}
+
 template <int EPI>
 __device__ __forceinline__ void epilogue8(float (&v)[8], const GemmKernelParams& p, int col, int nvalid,
                                           long long grow, long long rrow, unsigned long long drop_row,
-                                          unsigned long long drop_seed) {
+                                          unsigned long long drop_seed, const uint4& gpre, const uint4& rpre) {
   const int act = EPI < 0 ? p.act : (EPI & 3);
   const int gate_mode = EPI < 0 ? p.gate_mode : ((EPI >> 2) & 3);
   const bool drop = EPI < 0 ? (p.drop_thresh16 != 0) : ((EPI >> 4) & 1);
@@ -107,7 +131,7 @@ __device__ __forceinline__ void epilogue8(float (&v)[8], const GemmKernelParams&
   if (gate_mode != S2T_GATE_NONE) {
     float gt[8];
     if (nvalid == 8 && p.aux_vec) {
-      const uint4 gv = *reinterpret_cast<const uint4*>(p.gate + grow + col);
+      const uint4 gv = gpre;
       gt[0] = bf16_lo(gv.x); gt[1] = bf16_hi(gv.x); gt[2] = bf16_lo(gv.y); gt[3] = bf16_hi(gv.y);
       gt[4] = bf16_lo(gv.z); gt[5] = bf16_hi(gv.z); gt[6] = bf16_lo(gv.w); gt[7] = bf16_hi(gv.w);
     } else {
@@ -138,7 +162,7 @@ __device__ __forceinline__ void epilogue8(float (&v)[8], const GemmKernelParams&
     for (int j = 0; j < 8; ++j) v[j] *= p.out_scale;
     if (p.residual != nullptr) {
       if (nvalid == 8 && p.aux_vec) {
-        const uint4 rv = *reinterpret_cast<const uint4*>(p.residual + rrow + col);
+        const uint4 rv = rpre;
         v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x); v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
         v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z); v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
       } else {
@@ -160,6 +184,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const GemmKernelParams p) {
   using Cfg = GemmCfg<BN>;
+  pdl_launch_dependents();   // the next kernel's set-up may overlap this one (common.cuh, PDL)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -200,6 +225,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // barriers, TMEM and tensor maps are set up: from here on global memory written by earlier kernels is touched
+  pdl_wait();
 
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
@@ -292,6 +319,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const unsigned long long drop_row =
           (static_cast<unsigned long long>(z) * p.M + row) * static_cast<unsigned long long>((p.N + 7) >> 3);
       const bool row_ok = row < p.M;
+      AuxUnit ax;
+      if (half < units && n0 + half * cpu * 32 < p.N)
+        aux_prefetch<EPI>(ax, p, n0 + half * cpu * 32, cpu * 4, row_ok, grow, rrow);
       mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + buf * BN + (static_cast<uint32_t>(q * 32) << 16);
@@ -318,7 +348,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
               for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rg[sub][g * 8 + j]);
               if (row_ok && col < p.N)
-                epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed);
+                epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[sub * 4 + g],
+                               ax.r[sub * 4 + g]);
               if (p.out_fp32) {
                 *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
                 *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
@@ -338,6 +369,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tma_store_commit();
         }
         ++sb;
+        if (u + 2 < units && ucol0 + 2 * cpu * 32 < p.N)
+          aux_prefetch<EPI>(ax, p, ucol0 + 2 * cpu * 32, cpu * 4, row_ok, grow, rrow);
       }
       // accumulator drained: hand the TMEM buffer back to the MMA warp
       tc_fence_before();
@@ -362,6 +395,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                         const __grid_constant__ CUtensorMap tmC, const GemmKernelParams p) {
   using Cfg = GemmCfg<BN>;
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -407,6 +441,7 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -481,6 +516,16 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
                         __uint_as_float(rg[g4 * 4 + 2]), __uint_as_float(rg[g4 * 4 + 3]));
     }
   }
+  const int cpu = p.out_fp32 ? 1 : 2;
+  const int units = (BN / 32) / cpu;
+  const int row = m0 + prow;
+  const long long rrow = static_cast<long long>(row) * p.ldr + z1 * p.r_bs1 + z2 * p.r_bs2;
+  const long long grow = static_cast<long long>(row) * p.ldg + z1 * p.g_bs1 + z2 * p.g_bs2;
+  const bool row_ok = row < p.M;
+  AuxUnit ax;
+  // leader: gate / residual of the first unit travel while the other ranks finish their partial tiles
+  if (warp >= 2 && rank == 0 && half < units && n0 + half * cpu * 32 < p.N)
+    aux_prefetch<EPI>(ax, p, n0 + half * cpu * 32, cpu * 4, row_ok, grow, rrow);
   tc_fence_before();
   __syncwarp();
   cluster_sync_all();  // partial tiles of ranks > 0 are visible cluster-wide
@@ -488,14 +533,8 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
     uint8_t* stage_base = staging + ew * 8192;
     const unsigned long long drop_seed =
         p.drop_seed + ((p.drop_thresh16 != 0 && p.drop_seed_off != nullptr) ? *p.drop_seed_off : 0ull);
-    const int cpu = p.out_fp32 ? 1 : 2;
-    const int units = (BN / 32) / cpu;
-    const int row = m0 + prow;
-    const long long rrow = static_cast<long long>(row) * p.ldr + z1 * p.r_bs1 + z2 * p.r_bs2;
-    const long long grow = static_cast<long long>(row) * p.ldg + z1 * p.g_bs1 + z2 * p.g_bs2;
     const unsigned long long drop_row =
         (static_cast<unsigned long long>(z) * p.M + row) * static_cast<unsigned long long>((p.N + 7) >> 3);
-    const bool row_ok = row < p.M;
     const uint32_t part_local = smem_u32(part);
     mbar_wait(tfull_bar, 0);
     tc_fence_after();
@@ -508,8 +547,9 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
       if (lane == 0) tma_store_wait_read<1>();
       __syncwarp();
       uint8_t* srow = sbuf + lane * 128;
-#pragma unroll 1
-      for (int sub = 0; sub < cpu; ++sub) {
+#pragma unroll
+      for (int sub = 0; sub < 2; ++sub) {
+        if (sub >= cpu) break;
         const int c = u * cpu + sub;
         uint32_t rg[32];
         tmem_ld_32x32(t_addr + c * 32, rg);
@@ -531,7 +571,9 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
           float v[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j];
-          if (row_ok && col < p.N) epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed);
+          if (row_ok && col < p.N)
+            epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[sub * 4 + g],
+                           ax.r[sub * 4 + g]);
           if (p.out_fp32) {
             *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
             *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
@@ -550,6 +592,8 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         tma_store_commit();
       }
       ++sb;
+      if (u + 2 < units && ucol0 + 2 * cpu * 32 < p.N)
+        aux_prefetch<EPI>(ax, p, ucol0 + 2 * cpu * 32, cpu * 4, row_ok, grow, rrow);
     }
     if (lane == 0) tma_store_wait_read<0>();
   }
@@ -671,8 +715,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   }
   const long long tiles = 1ll * ((kp.N + BN - 1) / BN) * ((kp.M + kBM - 1) / kBM) * nbatch;
   const int grid = static_cast<int>(tiles < sm_count() ? tiles : sm_count());
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, tc, kp);
-  S2T_LAUNCH_CHECK();
+  S2T_LAUNCH(kern, grid, kGemmThreads, Cfg::kSmemBytes, stream, ta, tb, tc, kp);
   return 0;
 }
 
@@ -694,13 +737,15 @@ static int launch_gemm_splitk(const CUtensorMap& ta, const CUtensorMap& tb, cons
   cfg.blockDim = dim3(kGemmThreads, 1, 1);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = kp.split_k;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   S2T_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, kp));
   return 0;
 }

@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(kLnWarps * 32)
 layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ gamma,
                      const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                      float* __restrict__ stats, int rows, int C, float eps) {
+  pdl_entry();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * kLnWarps + warp;
   if (row >= rows) return;
@@ -85,6 +86,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                      __nv_bfloat16* __restrict__ dx_drop, uint32_t thresh16, float drop_scale,
                      unsigned long long seed, uint32_t stream_id,
                      const unsigned long long* __restrict__ seed_off) {
+  pdl_entry();
   extern __shared__ float s_part[];  // [kLnWarps][2][C]
   if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -184,6 +186,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 __global__ void __launch_bounds__(256)
 layernorm_bwd_reduce_kernel(const float* __restrict__ partials, int n_partials, int C,
                             __nv_bfloat16* __restrict__ dgamma, __nv_bfloat16* __restrict__ dbeta, int accumulate) {
+  pdl_entry();
   __shared__ float s_acc[8][33];
   const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;  // column of the [2][C] row
@@ -228,9 +231,9 @@ extern "C" int s2t_layernorm_fwd(const void* x, const void* gamma, const void* b
   auto yp = reinterpret_cast<__nv_bfloat16*>(y);
   const int nv = (C / 8 + 31) / 32;
   switch (nv) {
-    case 1: layernorm_fwd_kernel<1><<<grid, kLnWarps * 32, 0, st>>>(xp, gp, bp, yp, stats, rows, C, eps); break;
-    case 2: layernorm_fwd_kernel<2><<<grid, kLnWarps * 32, 0, st>>>(xp, gp, bp, yp, stats, rows, C, eps); break;
-    default: layernorm_fwd_kernel<kLnMaxVec><<<grid, kLnWarps * 32, 0, st>>>(xp, gp, bp, yp, stats, rows, C, eps); break;
+    case 1: S2T_LAUNCH(layernorm_fwd_kernel<1>, grid, kLnWarps * 32, 0, st, xp, gp, bp, yp, stats, rows, C, eps); break;
+    case 2: S2T_LAUNCH(layernorm_fwd_kernel<2>, grid, kLnWarps * 32, 0, st, xp, gp, bp, yp, stats, rows, C, eps); break;
+    default: S2T_LAUNCH(layernorm_fwd_kernel<kLnMaxVec>, grid, kLnWarps * 32, 0, st, xp, gp, bp, yp, stats, rows, C, eps); break;
   }
   S2T_LAUNCH_CHECK();
   return 0;
@@ -268,8 +271,7 @@ extern "C" int s2t_layernorm_bwd(const void* dy, const void* x, const void* gamm
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
 #define S2T_LN_BWD(NV)                                                                                         \
-  layernorm_bwd_kernel<NV><<<np, kLnWarps * 32, smem, st>>>(dyp, xp, gp, stats, rp, dxp, partials, rows, C,      \
-                                                            rows_per_cta, ddp, th, sc, seed, stream_id, seed_offset)
+  S2T_LAUNCH(layernorm_bwd_kernel<NV>, np, kLnWarps * 32, smem, st, dyp, xp, gp, stats, rp, dxp, partials, rows, C, rows_per_cta, ddp, th, sc, seed, stream_id, seed_offset)
   switch (nv) {
     case 1: S2T_LN_BWD(1); break;
     case 2: S2T_LN_BWD(2); break;
@@ -284,9 +286,7 @@ extern "C" int s2t_layernorm_bwd_reduce(const float* partials, int rows, int C, 
                                         int accumulate, void* stream) {
   S2T_REQUIRE(partials, "s2t_layernorm_bwd_reduce: null pointer");
   if (rows <= 0) return 0;
-  layernorm_bwd_reduce_kernel<<<(2 * C + 31) / 32, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      partials, ln_partials(rows), C, reinterpret_cast<__nv_bfloat16*>(dgamma),
-      reinterpret_cast<__nv_bfloat16*>(dbeta), accumulate);
+  S2T_LAUNCH(layernorm_bwd_reduce_kernel, (2 * C + 31) / 32, 256, 0, reinterpret_cast<cudaStream_t>(stream), partials, ln_partials(rows), C, reinterpret_cast<__nv_bfloat16*>(dgamma), reinterpret_cast<__nv_bfloat16*>(dbeta), accumulate);
   S2T_LAUNCH_CHECK();
   return 0;
 }

@@ -40,6 +40,7 @@ attn_softmax_fwd_kernel(const __nv_bfloat16* __restrict__ scores, long long ld,
                         float scale, float clamp, uint32_t thresh16, float inv_keep,
                         unsigned long long seed, uint32_t stream_id,
                         const unsigned long long* __restrict__ seed_off) {
+  pdl_entry();
   if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long row = static_cast<long long>(blockIdx.x) * kSmWarps + warp;
@@ -104,6 +105,7 @@ attn_softmax_bwd_kernel(const __nv_bfloat16* __restrict__ probs, const __nv_bflo
                         int Tq, int Tk, long long ld, float scale, uint32_t thresh16, float inv_keep,
                         unsigned long long seed, uint32_t stream_id,
                         const unsigned long long* __restrict__ seed_off) {
+  pdl_entry();
   if (thresh16 != 0 && seed_off != nullptr) seed += *seed_off;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long row = static_cast<long long>(blockIdx.x) * kSmWarps + warp;
@@ -200,12 +202,7 @@ extern "C" int s2t_attn_softmax_fwd(const void* scores, long long ld, const void
   const long long nrows = static_cast<long long>(nbh) * Tq;
   if (nrows <= 0) return 0;
   const unsigned grid = static_cast<unsigned>((nrows + kSmWarps - 1) / kSmWarps);
-  attn_softmax_fwd_kernel<<<grid, kSmWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(scores), ld, reinterpret_cast<const __nv_bfloat16*>(bias),
-      ld_bias, bias_mode, bias_head_major, reinterpret_cast<__nv_bfloat16*>(probs),
-      reinterpret_cast<__nv_bfloat16*>(probs_drop), klen, nrows, heads, Tq, Tk, scale, clamp,
-      dropout_p > 0.f ? static_cast<uint32_t>(dropout_p * 65536.f + 0.5f) : 0u,
-      1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
+  S2T_LAUNCH(attn_softmax_fwd_kernel, grid, kSmWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<const __nv_bfloat16*>(scores), ld, reinterpret_cast<const __nv_bfloat16*>(bias), ld_bias, bias_mode, bias_head_major, reinterpret_cast<__nv_bfloat16*>(probs), reinterpret_cast<__nv_bfloat16*>(probs_drop), klen, nrows, heads, Tq, Tk, scale, clamp, dropout_p > 0.f ? static_cast<uint32_t>(dropout_p * 65536.f + 0.5f) : 0u, 1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }
@@ -223,13 +220,7 @@ extern "C" int s2t_attn_softmax_bwd(const void* probs, const void* dprobs_drop, 
   const long long nrows = static_cast<long long>(nbh) * Tq;
   if (nrows <= 0) return 0;
   const unsigned grid = static_cast<unsigned>((nrows + kSmWarps - 1) / kSmWarps);
-  attn_softmax_bwd_kernel<<<grid, kSmWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(probs), reinterpret_cast<const __nv_bfloat16*>(dprobs_drop),
-      reinterpret_cast<__nv_bfloat16*>(dscores), reinterpret_cast<__nv_bfloat16*>(dbias), ld_bias,
-      bias_head_major, klen,
-      nrows, heads, Tq, Tk, ld, scale,
-      dropout_p > 0.f ? static_cast<uint32_t>(dropout_p * 65536.f + 0.5f) : 0u,
-      1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
+  S2T_LAUNCH(attn_softmax_bwd_kernel, grid, kSmWarps * 32, 0, reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<const __nv_bfloat16*>(probs), reinterpret_cast<const __nv_bfloat16*>(dprobs_drop), reinterpret_cast<__nv_bfloat16*>(dscores), reinterpret_cast<__nv_bfloat16*>(dbias), ld_bias, bias_head_major, klen, nrows, heads, Tq, Tk, ld, scale, dropout_p > 0.f ? static_cast<uint32_t>(dropout_p * 65536.f + 0.5f) : 0u, 1.f / (1.f - dropout_p), seed, stream_id, seed_offset);
   S2T_LAUNCH_CHECK();
   return 0;
 }

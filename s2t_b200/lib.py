@@ -41,6 +41,7 @@ SIGNATURES = {
     "s2t_last_error": (C.c_char_p, []),
     "s2t_abi_version": (_i, []),
     "s2t_device_arch": (_i, []),
+    "s2t_set_pdl": (_i, [_i]),
     "s2t_gemm_bf16": (_i, [C.POINTER(GemmArgs), _vp]),
     "s2t_fbank_num_frames": (_i, [_ll]),
     "s2t_fbank_fwd": (_i, [_vp, _ll, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _ll, _ll, _vp, _vp]),
