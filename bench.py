@@ -357,7 +357,17 @@ def run_b200(a):
         }
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # The captured step graph holds NCCL kernels of the process group's communicator; tearing the communicator down
+        # under it (destroy_process_group) can block forever.  Drain, meet at a barrier, drop the graphs and leave
+        # without running the communicator's destructor.
+        torch.cuda.synchronize()
+        dist.barrier()
+        for plan in list(eng.plans.values()):
+            plan.graph = None
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def kernel_table(torch, eng, P):

@@ -221,6 +221,10 @@ __device__ __forceinline__ void fence_proxy_async() {
 // ---------------------------------------------------------------------------------------------
 // thread-block clusters / distributed shared memory
 // ---------------------------------------------------------------------------------------------
+// named barrier `id` (1..15; 0 is __syncthreads) over `nthreads` threads (a multiple of 32)
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));

@@ -303,9 +303,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint8_t* stage_base = staging + ew * 8192;
     const unsigned long long drop_seed =
         p.drop_seed + ((p.drop_thresh16 != 0 && p.drop_seed_off != nullptr) ? *p.drop_seed_off : 0ull);
-    constexpr int kChunksPerUnitBf16 = 2;
-    const int cpu = p.out_fp32 ? 1 : kChunksPerUnitBf16;  // 32-column TMEM chunks per staged unit
-    const int units = (BN / 32) / cpu;
+    const int units = BN / 32;   // fp32 output: one 32-column TMEM chunk (128-byte rows) per staged unit
     uint32_t lt = 0, sb = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
       const int z = tile / tiles_per_z;
@@ -319,58 +317,87 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const unsigned long long drop_row =
           (static_cast<unsigned long long>(z) * p.M + row) * static_cast<unsigned long long>((p.N + 7) >> 3);
       const bool row_ok = row < p.M;
-      AuxUnit ax;
-      if (half < units && n0 + half * cpu * 32 < p.N)
-        aux_prefetch<EPI>(ax, p, n0 + half * cpu * 32, cpu * 4, row_ok, grow, rrow);
-      mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
-      tc_fence_after();
       const uint32_t t_addr = tmem_base + buf * BN + (static_cast<uint32_t>(q * 32) << 16);
+      if (!p.out_fp32) {
+        // bf16 output: a staged unit is 64 columns (128-byte rows).  BOTH warps of the lane quarter work on every unit,
+        // warp `half` converting its 32-column half; they meet at a named barrier, then one lane hands the unit to the
+        // TMA store.  Four staging buffers per quarter: the store of unit k-3 has been read before unit k+1 is written.
+        constexpr int kUnits = BN / 64;
+        uint8_t* stage_q = staging + q * 16384;
+        AuxUnit ax;
+        if (n0 + half * 32 < p.N) aux_prefetch<EPI>(ax, p, n0 + half * 32, 4, row_ok, grow, rrow);
+        mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
+        tc_fence_after();
 #pragma unroll 1
-      for (int u = half; u < units; u += 2) {
-        const int ucol0 = n0 + u * cpu * 32;
-        if (ucol0 >= p.N) break;  // warp-uniform
-        uint32_t rg[2][32];
-        tmem_ld_32x32(t_addr + u * cpu * 32, rg[0]);
-        if (cpu == 2) tmem_ld_32x32(t_addr + u * cpu * 32 + 32, rg[1]);
-        uint8_t* sbuf = stage_base + (sb & 1) * 4096;
-        // this staging buffer was handed to a TMA store two stores ago: wait until it has been read
-        if (lane == 0) tma_store_wait_read<1>();
-        tmem_ld_wait();
-        __syncwarp();
-        uint8_t* srow = sbuf + lane * 128;
+        for (int u = 0; u < kUnits; ++u) {
+          const int ucol0 = n0 + u * 64;
+          if (ucol0 >= p.N) break;  // warp-uniform
+          uint32_t rg[32];
+          tmem_ld_32x32(t_addr + u * 64 + half * 32, rg);
+          uint8_t* sbuf = stage_q + (sb & 3) * 4096;
+          uint8_t* srow = sbuf + lane * 128;
+          tmem_ld_wait();
 #pragma unroll
-        for (int sub = 0; sub < 2; ++sub) {
-          if (sub < cpu) {
+          for (int g = 0; g < 4; ++g) {
+            const int col = ucol0 + half * 32 + g * 8;
+            float v[8];
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              const int col = ucol0 + sub * 32 + g * 8;
-              float v[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rg[sub][g * 8 + j]);
-              if (row_ok && col < p.N)
-                epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[sub * 4 + g],
-                               ax.r[sub * 4 + g]);
-              if (p.out_fp32) {
-                *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
-                *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
-              } else {
-                uint4 ov;
-                ov.x = pack_bf16(v[0], v[1]); ov.y = pack_bf16(v[2], v[3]);
-                ov.z = pack_bf16(v[4], v[5]); ov.w = pack_bf16(v[6], v[7]);
-                *reinterpret_cast<uint4*>(srow + (((sub * 4 + g) ^ (lane & 7)) << 4)) = ov;
-              }
-            }
+            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rg[g * 8 + j]);
+            if (row_ok && col < p.N)
+              epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[g], ax.r[g]);
+            uint4 ov;
+            ov.x = pack_bf16(v[0], v[1]); ov.y = pack_bf16(v[2], v[3]);
+            ov.z = pack_bf16(v[4], v[5]); ov.w = pack_bf16(v[6], v[7]);
+            *reinterpret_cast<uint4*>(srow + (((half * 4 + g) ^ (lane & 7)) << 4)) = ov;
           }
+          fence_proxy_async();
+          named_bar_sync(1 + q, 64);
+          if (half == 0 && lane == 0) {
+            tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
+            tma_store_commit();
+            tma_store_wait_read<2>();
+          }
+          ++sb;
+          if (u + 1 < kUnits && ucol0 + 64 + half * 32 < p.N)
+            aux_prefetch<EPI>(ax, p, ucol0 + 64 + half * 32, 4, row_ok, grow, rrow);
         }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-          tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
-          tma_store_commit();
+      } else {
+        AuxUnit ax;
+        if (half < units && n0 + half * 32 < p.N) aux_prefetch<EPI>(ax, p, n0 + half * 32, 4, row_ok, grow, rrow);
+        mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int u = half; u < units; u += 2) {
+          const int ucol0 = n0 + u * 32;
+          if (ucol0 >= p.N) break;  // warp-uniform
+          uint32_t rg[32];
+          tmem_ld_32x32(t_addr + u * 32, rg);
+          uint8_t* sbuf = stage_base + (sb & 1) * 4096;
+          // this staging buffer was handed to a TMA store two stores ago: wait until it has been read
+          if (lane == 0) tma_store_wait_read<1>();
+          tmem_ld_wait();
+          __syncwarp();
+          uint8_t* srow = sbuf + lane * 128;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const int col = ucol0 + g * 8;
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rg[g * 8 + j]);
+            if (row_ok && col < p.N)
+              epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[g], ax.r[g]);
+            *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
+            tma_store_commit();
+          }
+          ++sb;
+          if (u + 2 < units && ucol0 + 64 < p.N) aux_prefetch<EPI>(ax, p, ucol0 + 64, 4, row_ok, grow, rrow);
         }
-        ++sb;
-        if (u + 2 < units && ucol0 + 2 * cpu * 32 < p.N)
-          aux_prefetch<EPI>(ax, p, ucol0 + 2 * cpu * 32, cpu * 4, row_ok, grow, rrow);
       }
       // accumulator drained: hand the TMEM buffer back to the MMA warp
       tc_fence_before();
@@ -516,21 +543,21 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
                         __uint_as_float(rg[g4 * 4 + 2]), __uint_as_float(rg[g4 * 4 + 3]));
     }
   }
-  const int cpu = p.out_fp32 ? 1 : 2;
-  const int units = (BN / 32) / cpu;
+  // Leader epilogue.  Work split: 32-column TMEM chunk c belongs to warp half (c & 1) of its lane quarter, so all
+  // eight epilogue warps are busy for every BN.  bf16 output: the two warps of a quarter fill one 64-column staged
+  // unit together (named barrier, one TMA store); fp32 output: every chunk is its own 128-byte unit.
   const int row = m0 + prow;
   const long long rrow = static_cast<long long>(row) * p.ldr + z1 * p.r_bs1 + z2 * p.r_bs2;
   const long long grow = static_cast<long long>(row) * p.ldg + z1 * p.g_bs1 + z2 * p.g_bs2;
   const bool row_ok = row < p.M;
+  constexpr int kChunks = BN / 32;
   AuxUnit ax;
-  // leader: gate / residual of the first unit travel while the other ranks finish their partial tiles
-  if (warp >= 2 && rank == 0 && half < units && n0 + half * cpu * 32 < p.N)
-    aux_prefetch<EPI>(ax, p, n0 + half * cpu * 32, cpu * 4, row_ok, grow, rrow);
+  // gate / residual of the first chunk travel while the other ranks finish their partial tiles
+  if (warp >= 2 && rank == 0 && n0 + half * 32 < p.N) aux_prefetch<EPI>(ax, p, n0 + half * 32, 4, row_ok, grow, rrow);
   tc_fence_before();
   __syncwarp();
   cluster_sync_all();  // partial tiles of ranks > 0 are visible cluster-wide
   if (warp >= 2 && rank == 0) {
-    uint8_t* stage_base = staging + ew * 8192;
     const unsigned long long drop_seed =
         p.drop_seed + ((p.drop_thresh16 != 0 && p.drop_seed_off != nullptr) ? *p.drop_seed_off : 0ull);
     const unsigned long long drop_row =
@@ -538,62 +565,71 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
     const uint32_t part_local = smem_u32(part);
     mbar_wait(tfull_bar, 0);
     tc_fence_after();
+    uint8_t* stage_q = staging + q * 16384;      // bf16: 4 unit buffers shared by the quarter's two warps
+    uint8_t* stage_w = staging + ew * 8192;      // fp32: 2 unit buffers per warp
     uint32_t sb = 0;
 #pragma unroll 1
-    for (int u = half; u < units; u += 2) {
-      const int ucol0 = n0 + u * cpu * 32;
-      if (ucol0 >= p.N) break;
-      uint8_t* sbuf = stage_base + (sb & 1) * 4096;
-      if (lane == 0) tma_store_wait_read<1>();
-      __syncwarp();
+    for (int c = half; c < kChunks; c += 2) {
+      const int ccol0 = n0 + c * 32;
+      const int ucol0 = p.out_fp32 ? ccol0 : n0 + (c >> 1) * 64;
+      if (ucol0 >= p.N) break;   // uniform over the quarter's two warps
+      uint8_t* sbuf = p.out_fp32 ? stage_w + (sb & 1) * 4096 : stage_q + (sb & 3) * 4096;
       uint8_t* srow = sbuf + lane * 128;
+      uint32_t rg[32];
+      tmem_ld_32x32(t_addr + c * 32, rg);
+      if (p.out_fp32) {
+        if (lane == 0) tma_store_wait_read<1>();
+        __syncwarp();
+      }
+      tmem_ld_wait();
+      float acc[32];
 #pragma unroll
-      for (int sub = 0; sub < 2; ++sub) {
-        if (sub >= cpu) break;
-        const int c = u * cpu + sub;
-        uint32_t rg[32];
-        tmem_ld_32x32(t_addr + c * 32, rg);
-        tmem_ld_wait();
-        float acc[32];
+      for (int j = 0; j < 32; ++j) acc[j] = __uint_as_float(rg[j]);
+      for (int pr = 1; pr < S; ++pr) {
+        const uint32_t base = dsmem_addr(part_local, pr);
+        float4 t[8];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) acc[j] = __uint_as_float(rg[j]);
-        for (int pr = 1; pr < S; ++pr) {
-          const uint32_t base = dsmem_addr(part_local, pr);
+        for (int g4 = 0; g4 < 8; ++g4) t[g4] = dsmem_ld_f4(base + (((c * 8 + g4) * 128 + prow) << 4));
 #pragma unroll
-          for (int g4 = 0; g4 < 8; ++g4) {
-            const float4 t = dsmem_ld_f4(base + (((c * 8 + g4) * 128 + prow) << 4));
-            acc[g4 * 4] += t.x; acc[g4 * 4 + 1] += t.y; acc[g4 * 4 + 2] += t.z; acc[g4 * 4 + 3] += t.w;
-          }
+        for (int g4 = 0; g4 < 8; ++g4) {
+          acc[g4 * 4] += t[g4].x; acc[g4 * 4 + 1] += t[g4].y; acc[g4 * 4 + 2] += t[g4].z; acc[g4 * 4 + 3] += t[g4].w;
         }
+      }
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int col = ucol0 + sub * 32 + g * 8;
-          float v[8];
+      for (int g = 0; g < 4; ++g) {
+        const int col = ccol0 + g * 8;
+        float v[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j];
-          if (row_ok && col < p.N)
-            epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[sub * 4 + g],
-                           ax.r[sub * 4 + g]);
-          if (p.out_fp32) {
-            *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
-            *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
-          } else {
-            uint4 ov;
-            ov.x = pack_bf16(v[0], v[1]); ov.y = pack_bf16(v[2], v[3]);
-            ov.z = pack_bf16(v[4], v[5]); ov.w = pack_bf16(v[6], v[7]);
-            *reinterpret_cast<uint4*>(srow + (((sub * 4 + g) ^ (lane & 7)) << 4)) = ov;
-          }
+        for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j];
+        if (row_ok && col < p.N)
+          epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[g], ax.r[g]);
+        if (p.out_fp32) {
+          *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
+          *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
+        } else {
+          uint4 ov;
+          ov.x = pack_bf16(v[0], v[1]); ov.y = pack_bf16(v[2], v[3]);
+          ov.z = pack_bf16(v[4], v[5]); ov.w = pack_bf16(v[6], v[7]);
+          *reinterpret_cast<uint4*>(srow + (((half * 4 + g) ^ (lane & 7)) << 4)) = ov;
         }
       }
       fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) {
-        tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
-        tma_store_commit();
+      if (p.out_fp32) {
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
+          tma_store_commit();
+        }
+      } else {
+        named_bar_sync(1 + q, 64);
+        if (half == 0 && lane == 0) {
+          tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
+          tma_store_commit();
+          tma_store_wait_read<2>();
+        }
       }
       ++sb;
-      if (u + 2 < units && ucol0 + 2 * cpu * 32 < p.N)
-        aux_prefetch<EPI>(ax, p, ucol0 + 2 * cpu * 32, cpu * 4, row_ok, grow, rrow);
+      if (c + 2 < kChunks && ccol0 + 64 < p.N) aux_prefetch<EPI>(ax, p, ccol0 + 64, 4, row_ok, grow, rrow);
     }
     if (lane == 0) tma_store_wait_read<0>();
   }
