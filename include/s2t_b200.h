@@ -34,6 +34,9 @@ int s2t_device_arch(void);
 /* Programmatic dependent launch between consecutive kernels of a stream (default on; S2T_PDL=0 in the environment
  * turns it off).  Returns the previous setting.  Affects launches made after the call. */
 int s2t_set_pdl(int on);
+/* Debug: with S2T_GEMM_TRACE=1 in the environment CTA 0 of every persistent GEMM launch records 16 %globaltimer
+ * stamps of its phases; this copies the stamps of the last launch to host_out16.  Negative when tracing is off. */
+int s2t_gemm_trace_read(unsigned long long* host_out16);
 
 /* --------------------------------------------------------------------------------------------- */
 /* K4: tcgen05/TMEM GEMM family.                                                                  */

@@ -15,6 +15,7 @@
 //     output scale, residual add, bf16 or fp32 output,
 //   * two batch dimensions (e.g. batch x heads) map to gridDim.z through 4-D tensor maps.
 #include "common.cuh"
+#include <stdlib.h>
 
 #include <mutex>
 #include <string.h>
@@ -51,6 +52,10 @@ struct GemmKernelParams {
   unsigned long long drop_seed;
   const unsigned long long* drop_seed_off;  // optional device counter added to the seed (CUDA-graph replay)
   uint32_t drop_stream;
+  void* out;            // split-K kernel stores its slice directly (the persistent kernel uses the TMA map)
+  long long ldc, c_bs1, c_bs2;
+  int out_vec;          // out base 16B aligned, ldc and batch strides multiples of 8 (bf16) / 4 (fp32)
+  unsigned long long* trace;  // debug: globaltimer stamps of CTA 0's phases (S2T_GEMM_TRACE=1), else nullptr
 };
 
 template <int BN>
@@ -64,6 +69,14 @@ struct GemmCfg {
   static constexpr int kSmemBytes =
       kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
+
+__device__ __forceinline__ void trace_stamp(const GemmKernelParams& p, int slot) {
+  if (p.trace != nullptr && blockIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[slot] = t;
+  }
+}
 
 __device__ __forceinline__ float apply_act(float v, int act) {
   if (act == S2T_ACT_RELU) return fmaxf(v, 0.f);
@@ -80,20 +93,23 @@ constexpr int epi_code(int act, int gate, int drop, int res) { return act | (gat
 // BEFORE the accumulator is waited for so that their L2/HBM latency hides behind the MMA main loop instead of being
 // paid once per 8-column group on the epilogue's critical path.
 struct AuxUnit {
-  uint4 g[8];
-  uint4 r[8];
+  uint4 g[4];
+  uint4 r[4];
+  uint4 b[4];   // bias (per column, the same for every row) — also a dependent global load per 8 columns otherwise
 };
 
 template <int EPI>
 __device__ __forceinline__ void aux_prefetch(AuxUnit& ax, const GemmKernelParams& p, int ucol0, int ngroups,
                                              bool row_ok, long long grow, long long rrow) {
-  const bool need_g = EPI < 0 ? (p.gate_mode != S2T_GATE_NONE) : (((EPI >> 2) & 3) != 0);
-  const bool need_r = (EPI < 0 ? true : ((EPI >> 5) & 1)) && p.residual != nullptr;
-  if (!p.aux_vec || !row_ok || !(need_g || need_r)) return;
+  const bool need_g = (EPI < 0 ? (p.gate_mode != S2T_GATE_NONE) : (((EPI >> 2) & 3) != 0)) && p.aux_vec;
+  const bool need_r = (EPI < 0 ? true : ((EPI >> 5) & 1)) && p.residual != nullptr && p.aux_vec;
+  const bool need_b = p.bias != nullptr && p.bias_vec;
+  if (!row_ok || !(need_g || need_r || need_b)) return;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
+  for (int i = 0; i < 4; ++i) {
     const int col = ucol0 + i * 8;
     if (i < ngroups && col + 8 <= p.N) {
+      if (need_b) ax.b[i] = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
       if (need_g) ax.g[i] = __ldg(reinterpret_cast<const uint4*>(p.gate + grow + col));
       if (need_r) ax.r[i] = __ldg(reinterpret_cast<const uint4*>(p.residual + rrow + col));
     }
@@ -103,7 +119,8 @@ __device__ __forceinline__ void aux_prefetch(AuxUnit& ax, const GemmKernelParams
 template <int EPI>
 __device__ __forceinline__ void epilogue8(float (&v)[8], const GemmKernelParams& p, int col, int nvalid,
                                           long long grow, long long rrow, unsigned long long drop_row,
-                                          unsigned long long drop_seed, const uint4& gpre, const uint4& rpre) {
+                                          unsigned long long drop_seed, const uint4& gpre, const uint4& rpre,
+                                          const uint4& bpre) {
   const int act = EPI < 0 ? p.act : (EPI & 3);
   const int gate_mode = EPI < 0 ? p.gate_mode : ((EPI >> 2) & 3);
   const bool drop = EPI < 0 ? (p.drop_thresh16 != 0) : ((EPI >> 4) & 1);
@@ -112,7 +129,7 @@ __device__ __forceinline__ void epilogue8(float (&v)[8], const GemmKernelParams&
   for (int j = 0; j < 8; ++j) v[j] *= p.alpha;
   if (p.bias != nullptr) {
     if (nvalid == 8 && p.bias_vec) {
-      const uint4 bv = *reinterpret_cast<const uint4*>(p.bias + col);
+      const uint4 bv = bpre;
       v[0] += bf16_lo(bv.x); v[1] += bf16_hi(bv.x); v[2] += bf16_lo(bv.y); v[3] += bf16_hi(bv.y);
       v[4] += bf16_lo(bv.z); v[5] += bf16_hi(bv.z); v[6] += bf16_lo(bv.w); v[7] += bf16_hi(bv.w);
     } else {
@@ -185,6 +202,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const __grid_constant__ CUtensorMap tmC, const GemmKernelParams p) {
   using Cfg = GemmCfg<BN>;
   pdl_launch_dependents();   // the next kernel's set-up may overlap this one (common.cuh, PDL)
+  if (threadIdx.x == 0) trace_stamp(p, 0);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -226,7 +244,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   // barriers, TMEM and tensor maps are set up: from here on global memory written by earlier kernels is touched
+  if (threadIdx.x == 0) trace_stamp(p, 1);
   pdl_wait();
+  if (threadIdx.x == 0) trace_stamp(p, 2);
 
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
@@ -261,6 +281,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                           z2 * p.b_zm2);
           }
         }
+        if (tile == static_cast<int>(blockIdx.x)) trace_stamp(p, 3);
       }
     }
   } else if (warp == 1) {
@@ -277,6 +298,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int s = it % Cfg::kStages;
           const uint32_t ph = (it / Cfg::kStages) & 1;
           mbar_wait(&full_bar[s], ph);
+          if (it == 0) trace_stamp(p, 4);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + s * Cfg::kStageBytes);
           const uint32_t b_addr = a_addr + Cfg::kABytes;
@@ -291,6 +313,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           umma_commit(&empty_bar[s]);  // frees this smem stage once the MMAs above retire
         }
         umma_commit(&tfull_bar[buf]);  // accumulator of this tile complete
+        if (lt == 0) trace_stamp(p, 5);
       }
     }
   } else {
@@ -327,6 +350,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         AuxUnit ax;
         if (n0 + half * 32 < p.N) aux_prefetch<EPI>(ax, p, n0 + half * 32, 4, row_ok, grow, rrow);
         mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
+        if (ew == 0 && lane == 0 && lt < 2) trace_stamp(p, 6 + 2 * lt);
         tc_fence_after();
 #pragma unroll 1
         for (int u = 0; u < kUnits; ++u) {
@@ -344,7 +368,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rg[g * 8 + j]);
             if (row_ok && col < p.N)
-              epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[g], ax.r[g]);
+              epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[g], ax.r[g], ax.b[g]);
             uint4 ov;
             ov.x = pack_bf16(v[0], v[1]); ov.y = pack_bf16(v[2], v[3]);
             ov.z = pack_bf16(v[4], v[5]); ov.w = pack_bf16(v[6], v[7]);
@@ -385,7 +409,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rg[g * 8 + j]);
             if (row_ok && col < p.N)
-              epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[g], ax.r[g]);
+              epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[g], ax.r[g], ax.b[g]);
             *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
             *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
           }
@@ -399,17 +423,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (u + 2 < units && ucol0 + 64 < p.N) aux_prefetch<EPI>(ax, p, ucol0 + 64, 4, row_ok, grow, rrow);
         }
       }
+      if (ew == 0 && lane == 0 && lt < 2) trace_stamp(p, 7 + 2 * lt);
       // accumulator drained: hand the TMEM buffer back to the MMA warp
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[buf]);
     }
     if (lane == 0) tma_store_wait_read<0>();
+    if (ew == 0 && lane == 0) trace_stamp(p, 10);
   }
 
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  if (threadIdx.x == 0) trace_stamp(p, 11);
 }
 
 // Split-K GEMM for K-heavy problems with few output tiles (weight gradients: K = B*T rows; ffn.w_2; the
@@ -423,6 +450,7 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
                         const __grid_constant__ CUtensorMap tmC, const GemmKernelParams p) {
   using Cfg = GemmCfg<BN>;
   pdl_launch_dependents();
+  if (threadIdx.x == 0) trace_stamp(p, 0);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -458,7 +486,6 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
     fence_mbar_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if (rank == 0) tma_prefetch_desc(&tmC);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, BN < 32 ? 32 : BN);
@@ -468,7 +495,9 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) trace_stamp(p, 1);
   pdl_wait();
+  if (threadIdx.x == 0) trace_stamp(p, 2);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -504,6 +533,7 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         const int s = it % Cfg::kStages;
         const uint32_t ph = (it / Cfg::kStages) & 1;
         mbar_wait(&full_bar[s], ph);
+        if (it == 0) trace_stamp(p, 4);
         tc_fence_after();
         const uint32_t a_addr = smem_u32(smem + s * Cfg::kStageBytes);
         const uint32_t b_addr = a_addr + Cfg::kABytes;
@@ -518,125 +548,141 @@ gemm_bf16_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_co
         umma_commit(&empty_bar[s]);
       }
       umma_commit(tfull_bar);
+      trace_stamp(p, 5);
     }
   }
   const int ew = warp - 2;
   const int q = warp & 3;
   const int half = ew >> 2;
   const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-  // partial tile layout in the (now idle) operand ring: float4 index ((c*8 + g4)*128 + row): conflict-free
-  // for row-per-lane writers and readers alike
-  float4* part = reinterpret_cast<float4*>(smem);
   const int prow = q * 32 + lane;
-  if (warp >= 2 && rank != 0) {
-    mbar_wait(tfull_bar, 0);  // all MMAs of this CTA retired: accumulator complete, ring no longer read
+  // Reduce-scatter over the cluster, push style: rank r owns the tile's columns [r*w, (r+1)*w), w = BN / S.  Every rank
+  // scatters its fp32 accumulator straight from TMEM registers into the owners' shared memory (remote stores are
+  // fire-and-forget: no DSMEM round trip on anybody's critical path); after one cluster barrier each owner sums the S
+  // slices from its LOCAL shared memory, runs the fused epilogue and stores its slice to global memory.
+  // Receive buffer = the epilogue staging area (not part of the operand ring, so a fast peer may write into it while
+  // this CTA's MMAs are still reading operands); layout: float4 index ((src*w/4 + j)*128 + row).
+  const int w = BN / S;
+  float4* recv = reinterpret_cast<float4*>(BN <= 128 ? staging : smem);
+  if (BN > 128) {           // 128 KB of partials only fit in the operand ring: wait until every rank's MMAs have retired
+    if (warp >= 2) {
+      mbar_wait(tfull_bar, 0);
+      tc_fence_after();
+    }
+    tc_fence_before();
+    __syncwarp();
+    cluster_sync_all();
+  }
+  if (warp >= 2) {
+    mbar_wait(tfull_bar, 0);  // all MMAs of this CTA retired: accumulator complete
     tc_fence_after();
+    const uint32_t recv_local = smem_u32(recv);
+    const int w4 = w >> 2;
 #pragma unroll 1
     for (int c = half; c < BN / 32; c += 2) {
       uint32_t rg[32];
       tmem_ld_32x32(t_addr + c * 32, rg);
       tmem_ld_wait();
 #pragma unroll
-      for (int g4 = 0; g4 < 8; ++g4)
-        part[(c * 8 + g4) * 128 + prow] =
-            make_float4(__uint_as_float(rg[g4 * 4]), __uint_as_float(rg[g4 * 4 + 1]),
-                        __uint_as_float(rg[g4 * 4 + 2]), __uint_as_float(rg[g4 * 4 + 3]));
+      for (int g4 = 0; g4 < 8; ++g4) {
+        const int j4 = c * 8 + g4;            // float4 column of the tile
+        const int owner = j4 / w4;
+        const uint32_t off = static_cast<uint32_t>(((rank * w4 + (j4 - owner * w4)) * 128 + prow) << 4);
+        dsmem_st_f4(dsmem_addr(recv_local, owner) + off,
+                    make_float4(__uint_as_float(rg[g4 * 4]), __uint_as_float(rg[g4 * 4 + 1]),
+                                __uint_as_float(rg[g4 * 4 + 2]), __uint_as_float(rg[g4 * 4 + 3])));
+      }
     }
   }
-  // Leader epilogue.  Work split: 32-column TMEM chunk c belongs to warp half (c & 1) of its lane quarter, so all
-  // eight epilogue warps are busy for every BN.  bf16 output: the two warps of a quarter fill one 64-column staged
-  // unit together (named barrier, one TMA store); fp32 output: every chunk is its own 128-byte unit.
+  // Owner side.  Thread = one row; the two warp halves of a lane quarter split the slice's 8-column groups.
+  const int ngroups = w >> 3;
+  const int ngh = (ngroups + 1) >> 1;
+  const int g_lo = half * ngh;
+  const int g_hi = min(ngroups, g_lo + ngh);
+  const int tcol0 = rank * w;
   const int row = m0 + prow;
   const long long rrow = static_cast<long long>(row) * p.ldr + z1 * p.r_bs1 + z2 * p.r_bs2;
   const long long grow = static_cast<long long>(row) * p.ldg + z1 * p.g_bs1 + z2 * p.g_bs2;
   const bool row_ok = row < p.M;
-  constexpr int kChunks = BN / 32;
   AuxUnit ax;
-  // gate / residual of the first chunk travel while the other ranks finish their partial tiles
-  if (warp >= 2 && rank == 0 && n0 + half * 32 < p.N) aux_prefetch<EPI>(ax, p, n0 + half * 32, 4, row_ok, grow, rrow);
+  // bias / gate / residual of the first groups travel while the other ranks finish their partial tiles
+  if (warp >= 2 && g_lo < g_hi && n0 + tcol0 + g_lo * 8 < p.N)
+    aux_prefetch<EPI>(ax, p, n0 + tcol0 + g_lo * 8, min(4, g_hi - g_lo), row_ok, grow, rrow);
   tc_fence_before();
   __syncwarp();
-  cluster_sync_all();  // partial tiles of ranks > 0 are visible cluster-wide
-  if (warp >= 2 && rank == 0) {
+  cluster_sync_all();  // all partial tiles are visible cluster-wide
+  if (warp >= 2) {
+    if (ew == 0 && lane == 0) trace_stamp(p, 6);
     const unsigned long long drop_seed =
         p.drop_seed + ((p.drop_thresh16 != 0 && p.drop_seed_off != nullptr) ? *p.drop_seed_off : 0ull);
     const unsigned long long drop_row =
         (static_cast<unsigned long long>(z) * p.M + row) * static_cast<unsigned long long>((p.N + 7) >> 3);
-    const uint32_t part_local = smem_u32(part);
-    mbar_wait(tfull_bar, 0);
-    tc_fence_after();
-    uint8_t* stage_q = staging + q * 16384;      // bf16: 4 unit buffers shared by the quarter's two warps
-    uint8_t* stage_w = staging + ew * 8192;      // fp32: 2 unit buffers per warp
-    uint32_t sb = 0;
+    const long long orow = static_cast<long long>(row) * p.ldc + z1 * p.c_bs1 + z2 * p.c_bs2;
 #pragma unroll 1
-    for (int c = half; c < kChunks; c += 2) {
-      const int ccol0 = n0 + c * 32;
-      const int ucol0 = p.out_fp32 ? ccol0 : n0 + (c >> 1) * 64;
-      if (ucol0 >= p.N) break;   // uniform over the quarter's two warps
-      uint8_t* sbuf = p.out_fp32 ? stage_w + (sb & 1) * 4096 : stage_q + (sb & 3) * 4096;
-      uint8_t* srow = sbuf + lane * 128;
-      uint32_t rg[32];
-      tmem_ld_32x32(t_addr + c * 32, rg);
-      if (p.out_fp32) {
-        if (lane == 0) tma_store_wait_read<1>();
-        __syncwarp();
-      }
-      tmem_ld_wait();
-      float acc[32];
+    for (int gb = g_lo; gb < g_hi; gb += 4) {
+      if (gb != g_lo && n0 + tcol0 + gb * 8 < p.N)
+        aux_prefetch<EPI>(ax, p, n0 + tcol0 + gb * 8, min(4, g_hi - gb), row_ok, grow, rrow);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) acc[j] = __uint_as_float(rg[j]);
-      for (int pr = 1; pr < S; ++pr) {
-        const uint32_t base = dsmem_addr(part_local, pr);
-        float4 t[8];
+      for (int i = 0; i < 4; ++i) {
+        const int g = gb + i;
+        const int tcol = tcol0 + g * 8;
+        const int col = n0 + tcol;
+        if (g < g_hi && col < p.N) {   // warp-uniform
+          float4 t[16];
 #pragma unroll
-        for (int g4 = 0; g4 < 8; ++g4) t[g4] = dsmem_ld_f4(base + (((c * 8 + g4) * 128 + prow) << 4));
+          for (int pr = 0; pr < 8; ++pr) {
+            if (pr < S) {
+              const float4* src = recv + (pr * (w >> 2) + g * 2) * 128 + prow;
+              t[2 * pr] = src[0];
+              t[2 * pr + 1] = src[128];
+            }
+          }
+          float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int g4 = 0; g4 < 8; ++g4) {
-          acc[g4 * 4] += t[g4].x; acc[g4 * 4 + 1] += t[g4].y; acc[g4 * 4 + 2] += t[g4].z; acc[g4 * 4 + 3] += t[g4].w;
+          for (int pr = 0; pr < 8; ++pr) {
+            if (pr < S) {
+              v[0] += t[2 * pr].x; v[1] += t[2 * pr].y; v[2] += t[2 * pr].z; v[3] += t[2 * pr].w;
+              v[4] += t[2 * pr + 1].x; v[5] += t[2 * pr + 1].y; v[6] += t[2 * pr + 1].z; v[7] += t[2 * pr + 1].w;
+            }
+          }
+          if (p.trace != nullptr && ew == 0 && lane == 0 && g == g_lo && v[0] != 12345.678f) trace_stamp(p, 7);
+          if (row_ok) {
+            const int nvalid = min(8, p.N - col);
+            epilogue8<EPI>(v, p, col, nvalid, grow, rrow, drop_row, drop_seed, ax.g[i], ax.r[i], ax.b[i]);
+            if (p.out_fp32) {
+              float* o = reinterpret_cast<float*>(p.out) + orow + col;
+              if (nvalid == 8 && p.out_vec) {
+                *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (j < nvalid) o[j] = v[j];
+              }
+            } else {
+              __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + orow + col;
+              if (nvalid == 8 && p.out_vec) {
+                uint4 ov;
+                ov.x = pack_bf16(v[0], v[1]); ov.y = pack_bf16(v[2], v[3]);
+                ov.z = pack_bf16(v[4], v[5]); ov.w = pack_bf16(v[6], v[7]);
+                *reinterpret_cast<uint4*>(o) = ov;
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (j < nvalid) o[j] = __float2bfloat16(v[j]);
+              }
+            }
+          }
         }
       }
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const int col = ccol0 + g * 8;
-        float v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j];
-        if (row_ok && col < p.N)
-          epilogue8<EPI>(v, p, col, min(8, p.N - col), grow, rrow, drop_row, drop_seed, ax.g[g], ax.r[g]);
-        if (p.out_fp32) {
-          *reinterpret_cast<float4*>(srow + (((2 * g) ^ (lane & 7)) << 4)) = make_float4(v[0], v[1], v[2], v[3]);
-          *reinterpret_cast<float4*>(srow + (((2 * g + 1) ^ (lane & 7)) << 4)) = make_float4(v[4], v[5], v[6], v[7]);
-        } else {
-          uint4 ov;
-          ov.x = pack_bf16(v[0], v[1]); ov.y = pack_bf16(v[2], v[3]);
-          ov.z = pack_bf16(v[4], v[5]); ov.w = pack_bf16(v[6], v[7]);
-          *reinterpret_cast<uint4*>(srow + (((half * 4 + g) ^ (lane & 7)) << 4)) = ov;
-        }
-      }
-      fence_proxy_async();
-      if (p.out_fp32) {
-        __syncwarp();
-        if (lane == 0) {
-          tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
-          tma_store_commit();
-        }
-      } else {
-        named_bar_sync(1 + q, 64);
-        if (half == 0 && lane == 0) {
-          tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
-          tma_store_commit();
-          tma_store_wait_read<2>();
-        }
-      }
-      ++sb;
-      if (c + 2 < kChunks && ccol0 + 64 < p.N) aux_prefetch<EPI>(ax, p, ccol0 + 64, 4, row_ok, grow, rrow);
     }
-    if (lane == 0) tma_store_wait_read<0>();
+    if (ew == 0 && lane == 0) trace_stamp(p, 9);
   }
   tc_fence_before();
   __syncwarp();
-  cluster_sync_all();  // ranks > 0 keep their shared memory alive until the leader has read it
+  cluster_sync_all();  // every rank keeps its shared memory alive until all peers have read it
   if (warp == 1) tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
+  if (threadIdx.x == 0) trace_stamp(p, 11);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -828,6 +874,28 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUten
 
 using namespace s2t;
 
+// Debug phase trace (S2T_GEMM_TRACE=1): 16 globaltimer stamps written by CTA 0 of the last persistent-kernel launch.
+static unsigned long long* gemm_trace_buffer() {
+  static unsigned long long* buf = nullptr;
+  static int init = 0;
+  if (!init) {
+    init = 1;
+    const char* e = getenv("S2T_GEMM_TRACE");
+    if (e != nullptr && e[0] == '1') {
+      if (cudaMalloc(&buf, 16 * sizeof(unsigned long long)) != cudaSuccess) buf = nullptr;
+      else cudaMemset(buf, 0, 16 * sizeof(unsigned long long));
+    }
+  }
+  return buf;
+}
+
+extern "C" int s2t_gemm_trace_read(unsigned long long* host_out16) {
+  unsigned long long* buf = gemm_trace_buffer();
+  S2T_REQUIRE(buf != nullptr && host_out16 != nullptr, "s2t_gemm_trace_read: tracing is off (set S2T_GEMM_TRACE=1)");
+  S2T_CHECK_CUDA(cudaMemcpy(host_out16, buf, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
 extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   S2T_REQUIRE(g != nullptr, "s2t_gemm_bf16: null args");
@@ -865,7 +933,9 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
           if (tiles * sk > 128) break;
           const int kb_per = (num_kb + sk - 1) / sk;
           if (kb_per < 4 || (sk - 1) * kb_per >= num_kb) continue;
-          const double c2 = 4500.0 + kb_per * kb_cyc + epi * (1.0 + 0.6 * (sk - 1));
+          // reduce-scatter tail: park the partial tile (~600 clk), receive (sk-1)/sk of one fp32 tile over DSMEM at
+          // ~21 B/clk, run the epilogue on 1/sk of the tile
+          const double c2 = 4500.0 + kb_per * kb_cyc + 600.0 + epi / sk + cand * 512.0 * (sk - 1) / sk / 21.0;
           if (c2 < cost || (g->split_k > 1 && sk > s_here)) {  // split_k > 1 forces the largest feasible factor
             cost = c2;
             s_here = sk;
@@ -930,6 +1000,14 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
   if (kp.gate)
     vec = vec && (kp.ldg % 8 == 0) && (kp.g_bs1 % 8 == 0) && (kp.g_bs2 % 8 == 0) && al16(kp.gate);
   kp.aux_vec = vec ? 1 : 0;
+  kp.trace = gemm_trace_buffer();
+  kp.out = g->out;
+  kp.ldc = g->ldc; kp.c_bs1 = nb1 > 1 ? g->c_bs1 : 0; kp.c_bs2 = nb2 > 1 ? g->c_bs2 : 0;
+  {
+    const long long m = g->out_fp32 ? 4 : 8;
+    kp.out_vec = ((reinterpret_cast<uintptr_t>(g->out) & 15) == 0 && g->ldc % m == 0 && kp.c_bs1 % m == 0 &&
+                  kp.c_bs2 % m == 0) ? 1 : 0;
+  }
 
   const int nbatch = nb1 * nb2;
   if (split > 1) {

@@ -42,6 +42,7 @@ SIGNATURES = {
     "s2t_abi_version": (_i, []),
     "s2t_device_arch": (_i, []),
     "s2t_set_pdl": (_i, [_i]),
+    "s2t_gemm_trace_read": (_i, [_vp]),
     "s2t_gemm_bf16": (_i, [C.POINTER(GemmArgs), _vp]),
     "s2t_fbank_num_frames": (_i, [_ll]),
     "s2t_fbank_fwd": (_i, [_vp, _ll, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _ll, _ll, _vp, _vp]),
