@@ -30,6 +30,7 @@ UNIT = "audio-s/s"
 SAMPLE_RATE = 16000
 VOCAB = 10000
 TARGET_LEN = 60           # ~6 tokens / s
+MICRO_DEFAULT = 1          # utterance groups run side by side (s2t_b200/microbatch.py)
 
 
 def parse():
@@ -41,6 +42,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=8, help="utterances per GPU per step")
     ap.add_argument("--seconds", type=float, default=10.0, help="utterance duration")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of CUDA-graph replay")
+    ap.add_argument("--micro", type=int, default=MICRO_DEFAULT,
+                    help="utterance groups of the batch run side by side on parallel streams (1 = one chain)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-kernels", action="store_true", help="also print a per-kernel time table (stderr)")
     return ap.parse_args()
@@ -253,7 +256,11 @@ def run_b200(a):
         peaks = json.loads(pk.read_text())
 
     cfg = EncoderConfig(vocab=VOCAB, dropout=0.1)              # s2t_transformer_s defaults (C1/C2)
-    eng = S2TEncoderEngine(cfg)
+    if a.micro > 1:
+        from s2t_b200.microbatch import MicroBatchEngine
+        eng = MicroBatchEngine(cfg, n_micro=a.micro)
+    else:
+        eng = S2TEncoderEngine(cfg)
     if world > 1:
         dist.broadcast(eng.store.flat, src=0)                  # same weights on every rank (trainer.py:431)
         eng.enable_data_parallel(n_buckets=4)
@@ -347,7 +354,7 @@ def run_b200(a):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload_name(a), "global_batch_utts": world * a.batch, "audio_s_per_step": world * audio_s_step,
                        "frames": T, "vocab": VOCAB, "params": eng.num_params(), "parallelism": f"dp{world}",
-                       "cuda_graph": not a.no_graph,
+                       "cuda_graph": not a.no_graph, "micro_batches": a.micro,
                        "l2": "no flush: per-step working set (activations+logits+grads, > 400 MB) exceeds the 126 MB L2"},
             "e2e": {"value": world * audio_s_step * a.steps / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / a.steps,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
