@@ -209,6 +209,19 @@ int s2t_im2col1d(const void* xp, long long x_bs, void* xcol, int batch, int t_ou
  * (Downsampling.forward, pdss2t_transformer.py:107-116); lengths may be NULL                       */
 int s2t_frame_rows(const void* x, const int* lengths, void* y, long long y_bs, int pad, int batch,
                    int T, int C, void* stream);
+/* Conv2dSubsampling (fairseq/modules/speech_to_text/subsampling.py:162-228): nn.Conv2d(k, stride, no padding) over a
+ * channels-last activation x bf16 [B][T][D][Cin] as a GEMM over the patch matrix
+ *   col[(b*T2 + t2)*D2 + d2][(j*k + i)*Cin + c] = x[b][stride*t2 + j][stride*d2 + i][c],  zero columns up to Kpad,
+ * T2 = (T-k)/stride + 1, D2 = (D-k)/stride + 1; Kpad % 8 == 0.                                      */
+int s2t_im2col2d(const void* x, void* col, int batch, int T, int D, int Cin, int k, int stride, int Kpad,
+                 void* stream);
+/* transpose of s2t_im2col2d (input gradient): dx[b][t][d][c] = sum of the dcol entries that read it; Cin % 8 == 0 */
+int s2t_col2im2d(const void* dcol, void* dx, int batch, int T, int D, int Cin, int k, int stride, int Kpad,
+                 void* stream);
+/* per-channel sum / sum of squares of x bf16 [rows][C] as fp32 partials [s2t_colstats_parts(rows)][2][C] — the
+ * batch statistics s2t_batchnorm_fwd consumes (BatchNorm2d over (B, D', T') == BatchNorm1d over the rows)   */
+int s2t_colstats_parts(long long rows);
+int s2t_colstats(const void* x, float* partials, long long rows, int C, void* stream);
 /* *counter += inc on the device (dropout seed counter of a captured step)                         */
 int s2t_counter_add(unsigned long long* counter, unsigned long long inc, void* stream);
 /* y += x, bf16 [n], n % 8 == 0                                                                    */

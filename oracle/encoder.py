@@ -33,6 +33,9 @@ class OracleConfig:
     subsampling_filter: int = 1024
     subsampling_kernel: int = 5
     subsampling_stride: int = 2
+    subsampling_type: str = "conv1d"      # conv1d | conv2d
+    subsampling_norm: str = "none"        # conv2d: none | batch2d
+    subsampling_activation: str = "glu"   # conv2d: swish | relu | none
     attn_type: str = "selfattn"          # selfattn | rel_pos
     encoder_embed_norm: bool = True
     no_scale_embedding: bool = True
@@ -95,6 +98,38 @@ class Conv1dSubsampling(nn.Module):
             x = layer(x)
             x_len = torch.div(x_len - 1, 2, rounding_mode="floor") + 1   # :155
         return x.permute(2, 0, 1), x_len
+
+
+class Conv2dSubsampling(nn.Module):
+    """fairseq/modules/speech_to_text/subsampling.py:162-228 (norm = batch2d | none, act = swish | relu | none)."""
+
+    class _Swish(nn.Module):
+        def forward(self, x):
+            return x * torch.sigmoid(x)
+
+    def __init__(self, num_layers, in_dim, filters, kernel_size, stride=2, norm="none", act="swish"):
+        super().__init__()
+        acts = {"swish": Conv2dSubsampling._Swish, "relu": nn.ReLU, "none": nn.Identity}
+        self.layers = nn.ModuleList()
+        for i in range(num_layers):
+            cin = 1 if i == 0 else filters[i - 1]
+            # Sequential(conv, norm = Sequential(Identity, BatchNorm2d, Identity) | Identity, act): names layers.{i}.0.*, .1.1.*
+            nrm = nn.Sequential(nn.Identity(), nn.BatchNorm2d(filters[i]), nn.Identity()) if norm == "batch2d" else nn.Identity()
+            self.layers.append(nn.Sequential(nn.Conv2d(cin, filters[i], kernel_size, stride=stride), nrm, acts[act]()))
+        dim = in_dim
+        for _ in range(num_layers):
+            dim = (dim - 1) // 2                                  # :202-204
+        self.linear = nn.Linear(dim * filters[-1], filters[-1])
+
+    def forward(self, x, x_len):
+        x = x.permute(1, 2, 0).unsqueeze(1)                      # (T,B,D) -> (B,1,D,T)
+        for layer in self.layers:
+            x = layer(x)
+            x_len = torch.div(x_len - 1, 2, rounding_mode="floor")   # :218 (quirk A9)
+        b, ch, d, t = x.size()
+        assert t == int(x_len.max()), (t, int(x_len.max()))       # :222
+        x = x.reshape(b, ch * d, t).permute(2, 0, 1)
+        return self.linear(x), x_len
 
 
 def sinusoidal_table(num_embeddings: int, dim: int, padding_idx: int = 1) -> torch.Tensor:
@@ -325,8 +360,12 @@ class S2TTransformerEncoder(nn.Module):
         self.dropout_module = nn.Dropout(cfg.dropout)
         self.embed_scale = 1.0 if cfg.no_scale_embedding else math.sqrt(d)
         filters = [cfg.subsampling_filter] * (cfg.subsampling_layers - 1) + [d]      # subsampling.py:231-247
-        self.subsample = Conv1dSubsampling(cfg.subsampling_layers, cfg.input_dim, filters,
-                                           cfg.subsampling_kernel, cfg.subsampling_stride)
+        if cfg.subsampling_type == "conv2d":
+            self.subsample = Conv2dSubsampling(cfg.subsampling_layers, cfg.input_dim, filters, cfg.subsampling_kernel,
+                                               cfg.subsampling_stride, cfg.subsampling_norm, cfg.subsampling_activation)
+        else:
+            self.subsample = Conv1dSubsampling(cfg.subsampling_layers, cfg.input_dim, filters,
+                                               cfg.subsampling_kernel, cfg.subsampling_stride)
         if cfg.encoder_embed_norm:
             self.embed_ln = nn.LayerNorm(d)
         self.layers = nn.ModuleList([EncoderLayer(cfg) for _ in range(cfg.layers)])
@@ -514,6 +553,8 @@ def config_from_args(args) -> OracleConfig:
         ffn_dim=args.encoder_ffn_embed_dim, heads=args.encoder_attention_heads, layers=g("encoder_layers", 12),
         subsampling_layers=g("subsampling_layers", 2), subsampling_filter=g("subsampling_filter", 1024),
         subsampling_kernel=g("subsampling_kernel", 5), subsampling_stride=g("subsampling_stride", 2),
+        subsampling_type=g("subsampling_type", "conv1d"), subsampling_norm=g("subsampling_norm", "none"),
+        subsampling_activation=g("subsampling_activation", "glu"),
         attn_type=g("encoder_attention_type", "selfattn"), encoder_embed_norm=g("encoder_embed_norm", False),
         no_scale_embedding=g("encoder_no_scale_embedding", False), macaron_style=g("macaron_style", False),
         use_cnn_module=g("use_cnn_module", False), cnn_module_kernel=g("cnn_module_kernel", 31),

@@ -45,6 +45,12 @@ ENC_CASES = {
                      ctc_weight=0.2, xctc_weight=0.1, inter_ctc_weight=0.1, inter_ctc_layers="2,3",
                      share_inter_ctc=True, inter_xctc_weight=0.05, inter_xctc_layers="2,3",
                      ctc_pae="inter_league", xctc_pae="inter_league", pae_unnorm_input=True),
+    # Conv2dSubsampling stem (egs/librispeech/asr/conf/ConformerCTCSmall.yaml:16-22: conv2d, kernel 3, stride 2,
+    # batch2d norm, swish) in front of the plain C1 layers
+    "conv2d_small": dict(encoder_layers=2, encoder_embed_dim=256, encoder_ffn_embed_dim=512, encoder_attention_heads=4,
+                         subsampling_type="conv2d", subsampling_layers=2, subsampling_filter=64, subsampling_kernel=3,
+                         subsampling_stride=2, subsampling_norm="batch2d", subsampling_activation="swish",
+                         vocab=200, B=3, T=83, S=5),
     # C3 in miniature: pdss2t_transformer_s_8 structure (4 stages, ratios 2_2_1_2, conv down-sampling + LayerNorm,
     # abs positions per stage, relu FFN), one layer per stage
     "c3_small": dict(family="pds", pds_stages=4, pds_layers="1_1_1_1", pds_ratios="2_2_1_2", pds_fusion=False,
@@ -122,7 +128,8 @@ GRAD_KEYS = ["pae.embed_adapter.weight", "xctc_pae.embed_adapter.weight", "xctc.
              "xctc_norm3.bias", "layers.2.conv_module.depthwise_conv.weight", "layers.1.self_attn.linear_pos.weight",
              "downsampling1.conv.0.weight", "downsampling3.conv.0.bias", "downsampling2.norm.weight",
              "stage1.0.ffn.w_1.weight", "stage4.0.self_attn.q_proj.weight", "stage2.0.self_attn_layer_norm.bias",
-             "subsample.layers.0.0.weight", "subsample.layers.1.0.bias", "embed_ln.weight",
+             "subsample.layers.0.0.weight", "subsample.layers.1.0.bias", "embed_ln.weight", "subsample.layers.1.0.weight",
+             "subsample.layers.0.1.1.weight", "subsample.layers.1.1.1.bias", "subsample.linear.bias",
              "layers.0.ffn.w_1.weight", "layers.1.ffn.w_2.bias", "layers.0.self_attn_layer_norm.bias",
              "layer_norm.weight", "ctc.ctc_projection.weight"]
 

@@ -53,6 +53,9 @@ class EncoderConfig:
     subsampling_filter: int = 1024
     subsampling_kernel: int = 5
     subsampling_stride: int = 2
+    subsampling_type: str = "conv1d"       # conv1d (Conv1d + GLU stack) | conv2d (Conv2dSubsampling, subsampling.py:162-228)
+    subsampling_norm: str = "none"         # conv2d: none | batch2d
+    subsampling_activation: str = "glu"    # conv1d: glu; conv2d: swish | relu | none
     attn_type: str = "selfattn"            # selfattn | rel_pos
     encoder_embed_norm: bool = True
     no_scale_embedding: bool = True
@@ -101,6 +104,8 @@ class EncoderConfig:
             heads=args.encoder_attention_heads, layers=args.encoder_layers,
             subsampling_layers=g("subsampling_layers", 2), subsampling_filter=g("subsampling_filter", 1024),
             subsampling_kernel=g("subsampling_kernel", 5), subsampling_stride=g("subsampling_stride", 2),
+            subsampling_type=g("subsampling_type", "conv1d"), subsampling_norm=g("subsampling_norm", "none"),
+            subsampling_activation=g("subsampling_activation", "glu"),
             attn_type=g("encoder_attention_type", "selfattn"), encoder_embed_norm=g("encoder_embed_norm", False),
             no_scale_embedding=g("encoder_no_scale_embedding", False), macaron_style=g("macaron_style", False),
             use_cnn_module=g("use_cnn_module", False), cnn_module_kernel=g("cnn_module_kernel", 31),
@@ -272,7 +277,37 @@ class Plan:
         drop = c.dropout > 0
         self.stages: List[_Stage] = []
         lib = ops._lib.load()
-        if c.encoder_type == "s2t":
+        if c.encoder_type == "s2t" and c.subsampling_type == "conv2d":
+            # Conv2dSubsampling stem: channels-last activations [B][T][D][C], explicit patch matrices
+            k, st = c.subsampling_kernel, c.subsampling_stride
+            self.x_in = z(B, T, c.input_dim)
+            self.c2: List[_Bufs] = []
+            Ti, Di = T, c.input_dim
+            for i, (cin, cout, Kpad) in enumerate(eng.sub2d):
+                L = _Bufs()
+                L.Tin, L.Din, L.cin, L.cout, L.Kpad = Ti, Di, cin, cout, Kpad
+                L.Tout, L.Dout = (Ti - k) // st + 1, (Di - k) // st + 1
+                assert L.Tout > 0 and L.Dout > 0, "input shorter than the Conv2d subsampling receptive field"
+                L.rows = B * L.Tout * L.Dout
+                L.col = e(L.rows, Kpad)
+                L.pre, L.y = e(L.rows, cout), e(L.rows, cout)
+                L.g_y, L.g_pre = e(L.rows, cout), e(L.rows, cout)
+                L.g_col = e(L.rows, Kpad) if i > 0 else None
+                L.bn_part = e(ops.colstats_parts(L.rows), 2, cout, dt=F32)
+                L.bn_save = e(2, cout, dt=F32)
+                L.bn_bwd_part = e(ops.batchnorm_bwd_partials(L.rows) * 2 * cout, dt=F32)
+                L.colsum_ws = e(lib.s2t_colsum_workspace_floats(L.rows, cout), dt=F32)
+                self.c2.append(L)
+                Ti, Di = L.Tout, L.Dout
+            assert Di == eng.sub2d_dim
+            self.sub_len = [z(B, dt=torch.int32) for _ in eng.sub2d]
+            St = _Stage(eng, B, Ti, c.embed_dim, c.ffn_dim, c.heads, c.layers, 0)
+            St.lens = self.sub_len[-1]
+            self.stages.append(St)
+            self.x0 = e(St.R, c.embed_dim)
+            self.e_ln, self.e_st = e(St.R, c.embed_dim), e(St.R, 2, dt=F32)
+            self.stem_colsum_ws = e(lib.s2t_colsum_workspace_floats(St.R, c.embed_dim), dt=F32)
+        elif c.encoder_type == "s2t":
             k, st = c.subsampling_kernel, c.subsampling_stride
             pad = self.pad = (k - 1) // 2
             # Conv1dSubsampling stem: framed inputs (pad zero rows front/back), pre-GLU conv outputs
@@ -444,6 +479,8 @@ class S2TEncoderEngine:
         S = self.store = ParamStore(self.device)
         self.conv_names: List[str] = []          # Conv1d weights stored [Cout][k][Cin] (reference: [Cout][Cin][k])
         self.ref_shapes: Dict[str, Tuple[int, ...]] = {}   # reference shape where it differs by a plain reshape
+        self.conv2d_names: Dict[str, Tuple[int, int, int, int]] = {}   # Conv2d weights [Cout][Kpad]: (cout, cin, k, Kpad)
+        self.lin_perm: Dict[str, Tuple[int, int, int]] = {}            # Conv2dSubsampling.linear: (C, channels, D')
         self.buffers: Dict[str, torch.Tensor] = {}         # BatchNorm running statistics (fp32 / int64)
         self.layer_specs: List[_LayerSpec] = []
         self.ffn_act = _ACT[c.encoder_activation_fn]
@@ -471,14 +508,17 @@ class S2TEncoderEngine:
             assert C % c.heads == 0 and (C // c.heads) % 8 == 0 and C % 8 == 0 and c.input_dim % 8 == 0
             # Conv1dSubsampling filters: [filter]*(L-1) + [d], last one doubled for the GLU (subsampling.py:231-247,118-121)
             filt = [c.subsampling_filter] * (c.subsampling_layers - 1) + [C]
-            self.sub_filters = [f if i < c.subsampling_layers - 1 else 2 * f for i, f in enumerate(filt)]
-            cin = c.input_dim
-            for i, cout in enumerate(self.sub_filters):
-                n = f"subsample.layers.{i}.0.weight"
-                S.declare(n, (cout, c.subsampling_kernel, cin))
-                self.conv_names.append(n)
-                S.declare(f"subsample.layers.{i}.0.bias", (cout,))
-                cin = cout // 2
+            if c.subsampling_type == "conv2d":
+                self._declare_conv2d_stem(filt)
+            else:
+                self.sub_filters = [f if i < c.subsampling_layers - 1 else 2 * f for i, f in enumerate(filt)]
+                cin = c.input_dim
+                for i, cout in enumerate(self.sub_filters):
+                    n = f"subsample.layers.{i}.0.weight"
+                    S.declare(n, (cout, c.subsampling_kernel, cin))
+                    self.conv_names.append(n)
+                    S.declare(f"subsample.layers.{i}.0.bias", (cout,))
+                    cin = cout // 2
             if c.encoder_embed_norm:
                 S.declare("embed_ln.weight", (C,)); S.declare("embed_ln.bias", (C,))
             for l in range(c.layers):
@@ -593,6 +633,64 @@ class S2TEncoderEngine:
         if c.use_cnn_module:
             ln("final_norm")
 
+    def _declare_conv2d_stem(self, filt: List[int]) -> None:
+        """Conv2dSubsampling parameters (subsampling.py:178-205): per layer Conv2d(k, stride) [+ BatchNorm2d]; then
+        Linear(D' * C_last, C_last).  Conv weights are kept as GEMM operands [Cout][Kpad], column (j*k + i)*Cin + c for
+        time tap j, feature tap i (reference layout [Cout][Cin][i][j]); the Linear's input index is d*C + c (channels-last
+        activations) instead of the reference's c*D' + d."""
+        c, S = self.cfg, self.store
+        if c.subsampling_norm not in ("none", "batch2d") or c.subsampling_activation not in ("swish", "relu", "none"):
+            raise NotImplementedError("engine: conv2d subsampling supports norm none|batch2d and activation swish|relu|none")
+        if c.subsampling_norm == "none" and c.subsampling_activation != "none":
+            raise NotImplementedError("engine: conv2d subsampling activation without batch2d norm")
+        k = c.subsampling_kernel
+        cin, D = 1, c.input_dim
+        self.sub2d = []
+        for i, cout in enumerate(filt):
+            assert cout % 8 == 0
+            K = k * k * cin
+            Kpad = max(16, (K + 7) // 8 * 8)
+            n = f"subsample.layers.{i}.0.weight"
+            S.declare(n, (cout, Kpad))
+            self.conv2d_names[n] = (cout, cin, k, Kpad)
+            S.declare(f"subsample.layers.{i}.0.bias", (cout,))
+            if c.subsampling_norm == "batch2d":
+                b = f"subsample.layers.{i}.1.1."
+                S.declare(b + "weight", (cout,)); S.declare(b + "bias", (cout,))
+                self.buffers[b + "running_mean"] = torch.zeros(cout, device=self.device, dtype=F32)
+                self.buffers[b + "running_var"] = torch.ones(cout, device=self.device, dtype=F32)
+                self.buffers[b + "num_batches_tracked"] = torch.zeros((), device=self.device, dtype=torch.int64)
+            self.sub2d.append((cin, cout, Kpad))
+            cin = cout
+            D = (D - 1) // 2 if (k, c.subsampling_stride) == (3, 2) else (D - k) // c.subsampling_stride + 1
+        self.sub2d_dim = D
+        C = filt[-1]
+        S.declare("subsample.linear.weight", (C, D * C))
+        self.lin_perm["subsample.linear.weight"] = (C, C, D)
+        S.declare("subsample.linear.bias", (C,))
+
+    def _to_internal(self, name: str, t: torch.Tensor) -> torch.Tensor:
+        if name in self.conv2d_names:
+            cout, cin, k, Kpad = self.conv2d_names[name]
+            if tuple(t.shape) != (cout, cin, k, k):
+                raise ValueError(f"{name}: shape {tuple(t.shape)} != {(cout, cin, k, k)}")
+            full = torch.zeros((cout, Kpad), dtype=t.dtype)
+            full[:, : k * k * cin] = t.permute(0, 3, 2, 1).reshape(cout, k * k * cin)     # [Cout][j][i][Cin]
+            return full
+        if name in self.lin_perm:
+            C, ch, D = self.lin_perm[name]
+            return t.reshape(C, ch, D).permute(0, 2, 1).reshape(C, D * ch)
+        return t
+
+    def _to_reference(self, name: str, t: torch.Tensor) -> torch.Tensor:
+        if name in self.conv2d_names:
+            cout, cin, k, Kpad = self.conv2d_names[name]
+            return t[:, : k * k * cin].reshape(cout, k, k, cin).permute(0, 3, 2, 1).contiguous()
+        if name in self.lin_perm:
+            C, ch, D = self.lin_perm[name]
+            return t.reshape(C, D, ch).permute(0, 2, 1).reshape(C, ch * D)
+        return t
+
     # ------------------------------------------------------------------------------------------
     # parameters
     # ------------------------------------------------------------------------------------------
@@ -605,10 +703,17 @@ class S2TEncoderEngine:
         S = self.store
         for name in S.names():
             shape = S.shape(name)
-            if _NORM_W.search(name):
+            if _NORM_W.search(name) or (name.startswith("subsample.layers.") and name.endswith(".1.1.weight")):
                 t = torch.ones(shape)
-            elif _NORM_B.search(name):
+            elif _NORM_B.search(name) or (name.startswith("subsample.layers.") and name.endswith(".1.1.bias")):
                 t = torch.zeros(shape)
+            elif name in self.conv2d_names or name[:-4] + "weight" in self.conv2d_names:
+                cout, cin, k, Kpad = self.conv2d_names[name if name in self.conv2d_names else name[:-4] + "weight"]
+                bound = 1.0 / math.sqrt(cin * k * k)
+                if name.endswith("bias"):
+                    t = (torch.rand(shape, generator=g) * 2 - 1) * bound
+                else:
+                    t = self._to_internal(name, (torch.rand((cout, cin, k, k), generator=g) * 2 - 1) * bound)
             elif name.endswith(("ctc_projection.weight", "embed_adapter.weight")):
                 t = torch.randn(shape, generator=g) * shape[1] ** -0.5
             elif name.endswith("ctc_projection.bias"):
@@ -638,7 +743,7 @@ class S2TEncoderEngine:
         for name in S.names():
             if name not in sd:
                 raise KeyError(f"state_dict is missing {name}")
-            t = sd[name].detach().to(F32)
+            t = self._to_internal(name, sd[name].detach().to(F32).cpu())
             if name in self.conv_names:
                 t = t.permute(0, 2, 1).contiguous()               # [Cout][Cin][k] -> [Cout][k][Cin]
             if name in self.ref_shapes:
@@ -667,7 +772,7 @@ class S2TEncoderEngine:
                 t = t.reshape(self.ref_shapes[name])
             if name in self.padded_bias:
                 t = t[: self.padded_bias[name]]
-            out[name] = t
+            out[name] = self._to_reference(name, t)
         return out
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
@@ -724,6 +829,104 @@ class S2TEncoderEngine:
                   dst.stride(1), dst.stride(0), ops._p(P.src_len), P.B, P.T, c.input_dim, cm, cm,
                   ops._p(P.cmvn_stats), ops._stream())
 
+    def _embed_block_fwd(self, P: Plan) -> None:
+        """embed_ln -> x * embed_scale (+ sinusoidal positions for abs attention) -> dropout (s2t_transformer.py:1768-1794)."""
+        c, S = self.cfg, self.store
+        St = P.stages[0]
+        src = P.x0
+        if c.encoder_embed_norm:
+            ops.layernorm_fwd(P.x0, S.p("embed_ln.weight"), S.p("embed_ln.bias"), out=P.e_ln, stats=P.e_st)
+            src = P.e_ln
+        C = c.embed_dim
+        table = self._pos_table(C) if c.attn_type == "selfattn" else None       # rel_pos: x is not modified (A5)
+        ops.embed_fwd(src.view(P.B, St.T, C), St.lens, table, self.embed_scale, self._drop(1),
+                      out=St.x[0].view(P.B, St.T, C))
+
+    def _stem_conv2d_fwd(self, P: Plan) -> None:
+        """Conv2dSubsampling (subsampling.py:207-228): per layer Conv2d(k, stride, no padding) [+ BatchNorm2d over
+        (B, D', T') in training mode: batch statistics include the zero-padded frames] + activation; lengths (len-1)//2
+        per layer (:218, quirk A9); (B, C, D', T') -> (T', B, C*D') -> Linear.  The reference's host-side assert
+        T' == max(lengths) (:222, quirk A16) is not evaluated.  Then the encoder zeroes padded frames (:1765)."""
+        c, S = self.cfg, self.store
+        k, st = c.subsampling_kernel, c.subsampling_stride
+        self._features(P, P.x_in, 0)
+        ln = P.src_len
+        for i in range(len(P.c2)):
+            torch.div(ln - 1, 2, rounding_mode="floor", out=P.sub_len[i])
+            ln = P.sub_len[i]
+        x = P.x_in.view(P.B, P.T, c.input_dim, 1)
+        act = _ACT.get(c.subsampling_activation, ops.ACT_NONE)
+        for i, L in enumerate(P.c2):
+            n = f"subsample.layers.{i}."
+            ops.im2col2d(x, k, st, L.Kpad, out=L.col)
+            ops.linear(L.col, S.p(n + "0.weight"), S.p(n + "0.bias"), out=L.pre)
+            if c.subsampling_norm == "batch2d":
+                b, bufs = n + "1.1.", self.buffers
+                if self.training:
+                    ops.colstats(L.pre, out=L.bn_part)
+                ops.batchnorm_fwd(L.pre, S.p(b + "weight"), S.p(b + "bias"), partials=L.bn_part if self.training else None,
+                                  running_mean=bufs[b + "running_mean"], running_var=bufs[b + "running_var"],
+                                  num_batches_tracked=bufs[b + "num_batches_tracked"], save_stats=L.bn_save, out=L.y,
+                                  act=act, training=self.training)
+                y = L.y
+            else:
+                y = L.pre
+            x = y.view(P.B, L.Tout, L.Dout, L.cout)
+        St = P.stages[0]
+        L = P.c2[-1]
+        ops.linear(y.view(P.B * L.Tout, L.Dout * L.cout), S.p("subsample.linear.weight"), S.p("subsample.linear.bias"),
+                   out=P.x0)
+        ops.mask_rows_(P.x0.view(P.B, St.T, c.embed_dim), St.lens)
+        self._embed_block_fwd(P)
+
+    def _stem_conv2d_bwd(self, P: Plan, dy: torch.Tensor) -> None:
+        """Backward of the embed block and Conv2dSubsampling: Linear, then per layer BatchNorm2d + activation,
+        bias = column sums, weight = dY^T patches, input = col2im(dY W)."""
+        c, S = self.cfg, self.store
+        St = P.stages[0]
+        C = c.embed_dim
+        k, st = c.subsampling_kernel, c.subsampling_stride
+        t = St.take()
+        ops.embed_bwd(dy.view(P.B, St.T, C), self.embed_scale, self._drop(1), out=t.view(P.B, St.T, C))
+        St.give(dy)
+        if c.encoder_embed_norm:
+            o = St.take()
+            ops.layernorm_bwd(t, P.x0, S.p("embed_ln.weight"), P.e_st, S.g("embed_ln.weight"), S.g("embed_ln.bias"),
+                              out=o, partials=St.ln_part)
+            St.give(t)
+            self._ready("embed_ln.weight")
+            t = o
+        ops.mask_rows_(t.view(P.B, St.T, C), St.lens)                   # padded frames were zeroed in forward
+        L = P.c2[-1]
+        y_last = (L.y if c.subsampling_norm == "batch2d" else L.pre).view(P.B * L.Tout, L.Dout * L.cout)
+        with self._fork(1):
+            ops.colsum(t, S.g("subsample.linear.bias"), workspace=P.stem_colsum_ws)
+        with self._fork(0):
+            ops.linear_wgrad(t, y_last, out=S.g("subsample.linear.weight"))
+        ops.linear_dgrad(t, S.p("subsample.linear.weight"), out=L.g_y.view(P.B * L.Tout, L.Dout * L.cout))
+        self._ready("subsample.linear.weight")
+        St.give(t)
+        act = _ACT.get(c.subsampling_activation, ops.ACT_NONE)
+        for i in reversed(range(len(P.c2))):
+            L = P.c2[i]
+            n = f"subsample.layers.{i}."
+            if c.subsampling_norm == "batch2d":
+                b = n + "1.1."
+                ops.batchnorm_bwd(L.g_y, L.pre, L.bn_save, S.p(b + "weight"), S.p(b + "bias"), S.g(b + "weight"),
+                                  S.g(b + "bias"), out=L.g_pre, partials=L.bn_bwd_part, act=act, training=self.training)
+                g = L.g_pre
+            else:
+                g = L.g_y
+            with self._fork(1):
+                ops.colsum(g, S.g(n + "0.bias"), workspace=L.colsum_ws)
+            with self._fork(0):
+                ops.linear_wgrad(g, L.col, out=S.g(n + "0.weight"))
+            if i > 0:
+                ops.linear_dgrad(g, S.p(n + "0.weight"), out=L.g_col)
+                prev = P.c2[i - 1]
+                ops.col2im2d(L.g_col, P.B, L.Tin, L.Din, L.cin, k, st, out=prev.g_y.view(P.B, L.Tin, L.Din, L.cin))
+            self._ready(n + "0.weight")
+
     def _stem_s2t_fwd(self, P: Plan) -> None:
         """Conv1dSubsampling (subsampling.py:145-159): [Conv1d(k, stride, pad) -> GLU] per layer as an
         implicit GEMM whose A rows overlap in the zero-framed channels-last input; lengths (len-1)//2+1 (:155);
@@ -749,15 +952,7 @@ class S2TEncoderEngine:
                 ops.glu_fwd(P.pre[i], out=nxt, T=t_out, ldy=cout // 2, y_bs=nxt.stride(0), y_off=P.pad * (cout // 2))
             else:
                 ops.glu_fwd(P.pre[i], out=P.x0, lengths=P.sub_len[i], T=t_out)
-        St = P.stages[0]
-        src = P.x0
-        if c.encoder_embed_norm:
-            ops.layernorm_fwd(P.x0, S.p("embed_ln.weight"), S.p("embed_ln.bias"), out=P.e_ln, stats=P.e_st)
-            src = P.e_ln
-        C = c.embed_dim
-        table = self._pos_table(C) if c.attn_type == "selfattn" else None       # rel_pos: x is not modified (A5)
-        ops.embed_fwd(src.view(P.B, St.T, C), St.lens, table, self.embed_scale, self._drop(1),
-                      out=St.x[0].view(P.B, St.T, C))
+        self._embed_block_fwd(P)
 
     def _stem_pds_fwd(self, P: Plan, i: int) -> None:
         """PDS stage stem (pdss2t_transformer.py:1088-1121): Downsampling = zero the padded input frames, Conv1d(k,
@@ -934,7 +1129,9 @@ class S2TEncoderEngine:
     def _forward(self, P: Plan) -> None:
         g = 0
         for i, St in enumerate(P.stages):
-            if self.cfg.encoder_type == "s2t":
+            if self.cfg.encoder_type == "s2t" and self.cfg.subsampling_type == "conv2d":
+                self._stem_conv2d_fwd(P)
+            elif self.cfg.encoder_type == "s2t":
                 self._stem_s2t_fwd(P)
             else:
                 self._stem_pds_fwd(P, i)
@@ -1363,7 +1560,9 @@ class S2TEncoderEngine:
                 d, dd = self._layer_bwd(P, g, d, dd)
             P.stages[i].give(dd)
             dd = None
-            if c.encoder_type == "s2t":
+            if c.encoder_type == "s2t" and c.subsampling_type == "conv2d":
+                self._stem_conv2d_bwd(P, d)
+            elif c.encoder_type == "s2t":
                 self._stem_s2t_bwd(P, d)
             else:
                 d = self._stem_pds_bwd(P, i, d)

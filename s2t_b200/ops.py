@@ -21,11 +21,11 @@ launch_count = 0
 _LAUNCHES = {
     "s2t_gemm_bf16": 1, "s2t_fbank_fwd": 1, "s2t_cmvn_utt": 2, "s2t_cmvn_global": 1,
     "s2t_layernorm_fwd": 1, "s2t_layernorm_bwd": 1, "s2t_layernorm_bwd_reduce": 1, "s2t_glu_fwd": 1, "s2t_glu_bwd": 1,
-    "s2t_colsum": 2, "s2t_col2im1d": 1, "s2t_embed_fwd": 1, "s2t_embed_bwd": 1, "s2t_mask_rows": 1,
+    "s2t_colsum": 1, "s2t_col2im1d": 1, "s2t_embed_fwd": 1, "s2t_embed_bwd": 1, "s2t_mask_rows": 1,
     "s2t_permute_conv_weight": 1, "s2t_cast_f32_to_bf16": 1, "s2t_cast_bf16_to_f32": 1,
     "s2t_attn_softmax_fwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4,
     "s2t_ctc_greedy": 2, "s2t_dwconv1d_fwd": 1, "s2t_dwconv1d_bwd": 3, "s2t_batchnorm_fwd": 1,
-    "s2t_batchnorm_bwd": 2, "s2t_relpos_qbias_fwd": 1, "s2t_relpos_qbias_bwd": 1, "s2t_act_dropout": 1,
+    "s2t_batchnorm_bwd": 2, "s2t_im2col2d": 1, "s2t_col2im2d": 1, "s2t_colstats": 1, "s2t_relpos_qbias_fwd": 1, "s2t_relpos_qbias_bwd": 1, "s2t_act_dropout": 1,
 }
 
 
@@ -347,6 +347,37 @@ def frame_rows(x: torch.Tensor, lengths: Optional[torch.Tensor], framed: torch.T
     B, T, Cd = x.shape
     _call("s2t_frame_rows", _p(x), _p(lengths), _p(framed), framed.stride(0), pad, B, T, Cd, _stream())
     return framed
+
+
+def im2col2d(x: torch.Tensor, k: int, stride: int, Kpad: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x bf16 [B, T, D, Cin] -> patch matrix [B*T2*D2, Kpad] of Conv2d(k, stride, no padding); column (j*k+i)*Cin+c."""
+    B, T, D, Cin = x.shape
+    T2, D2 = (T - k) // stride + 1, (D - k) // stride + 1
+    if out is None:
+        out = torch.empty((B * T2 * D2, Kpad), device=x.device, dtype=BF16)
+    _call("s2t_im2col2d", _p(x), _p(out), B, T, D, Cin, k, stride, Kpad, _stream())
+    return out
+
+
+def col2im2d(dcol: torch.Tensor, B: int, T: int, D: int, Cin: int, k: int, stride: int,
+             out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if out is None:
+        out = torch.empty((B, T, D, Cin), device=dcol.device, dtype=BF16)
+    _call("s2t_col2im2d", _p(dcol), _p(out), B, T, D, Cin, k, stride, dcol.shape[1], _stream())
+    return out
+
+
+def colstats_parts(rows: int) -> int:
+    return _lib.load().s2t_colstats_parts(rows)
+
+
+def colstats(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x bf16 [rows, C] -> fp32 partials [parts, 2, C] (per-channel sum, sum of squares) for batchnorm_fwd."""
+    rows, Cd = x.shape
+    if out is None:
+        out = torch.empty((colstats_parts(rows), 2, Cd), device=x.device, dtype=torch.float32)
+    _call("s2t_colstats", _p(x), _p(out), rows, Cd, _stream())
+    return out
 
 
 def counter_add(counter: torch.Tensor, inc: int = 1) -> None:

@@ -74,7 +74,7 @@ def _run(eng, feats, lens, tokens, tgt_tokens=None):
     return P
 
 
-@pytest.mark.parametrize("case", ["c1_small", "c4_small", "c3_small", "c5_small"])
+@pytest.mark.parametrize("case", ["c1_small", "c4_small", "c3_small", "c5_small", "conv2d_small"])
 def test_engine_matches_reference_golden(cuda_lib, case):
     from oracle.make_golden import ENC_CASES, seeded_state_dict, state_checksum
     fx = np.load(GOLDEN / f"enc_{case}.npz")
@@ -93,6 +93,10 @@ def test_engine_matches_reference_golden(cuda_lib, case):
                    attn_type=spec.get("encoder_attention_type", "selfattn"),
                    encoder_activation_fn=spec.get("encoder_activation_fn", "relu"),
                    layer_padding_mask=spec.get("layer_padding_mask", False))
+        for k in ("subsampling_type", "subsampling_layers", "subsampling_kernel", "subsampling_stride", "subsampling_norm",
+                  "subsampling_activation"):
+            if k in spec:
+                cfg[k] = spec[k]
         if "xctc_weight" in spec:
             csv = lambda k: tuple(int(v) for v in spec[k].split(","))
             cfg.update(tgt_vocab=spec["vocab"], ctc_weight=spec["ctc_weight"], xctc_weight=spec["xctc_weight"],

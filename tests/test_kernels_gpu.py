@@ -338,3 +338,50 @@ def test_ctc_greedy_bit_exact(cuda_lib):
             assert lens[b] == len(ref[b])
             assert np.array_equal(tokens[b, :lens[b]], ref[b])
             assert np.all(tokens[b, lens[b]:] == -1)
+
+
+# --------------------------------------------------------------------------------------------------
+# Conv2dSubsampling support kernels (bit-exact data movement; fp32 partial sums)
+# --------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("cin,kpad", [(1, 16), (8, 72), (24, 216)])
+def test_im2col2d_and_col2im2d(cuda_lib, cin, kpad):
+    """Patch matrix of Conv2d(k=3, stride=2, no padding) over channels-last x[B][T][D][C] against torch unfold
+    (bit-exact copies), and col2im2d as its exact transpose (<col, im2col(x)> == <col2im(col), x>)."""
+    from s2t_b200 import ops
+    g = torch.Generator().manual_seed(cin)
+    B, T, D, k, st = 2, 21, 14, 3, 2
+    x = torch.randn((B, T, D, cin), generator=g).to(BF16)
+    col = ops.im2col2d(x.cuda(), k, st, kpad).cpu()
+    T2, D2 = (T - k) // st + 1, (D - k) // st + 1
+    # reference: unfold over (T, D) with channels first -> [B, C*k*k, T2*D2], kernel index order (c, j, i)
+    u = torch.nn.functional.unfold(x.float().permute(0, 3, 1, 2), kernel_size=k, stride=st)
+    u = u.view(B, cin, k, k, T2, D2).permute(0, 4, 5, 2, 3, 1).reshape(B * T2 * D2, k * k * cin)   # (j, i, c) columns
+    assert torch.equal(col[:, : k * k * cin].float(), u)
+    assert torch.all(col[:, k * k * cin:] == 0)
+    if cin % 8 == 0:
+        dcol = torch.randn((B * T2 * D2, kpad), generator=g).to(BF16)
+        dx = ops.col2im2d(dcol.cuda(), B, T, D, cin, k, st).float().cpu()
+        lhs = (dcol.float()[:, : k * k * cin] * u).sum()
+        rhs = (dx * x.float()).sum()
+        assert abs(float(lhs - rhs)) <= 2e-2 * abs(float(lhs)) + 1e-2
+
+
+def test_colstats_feed_batchnorm(cuda_lib):
+    """colstats partials -> batchnorm_fwd == BatchNorm over the rows (training mode, batch statistics)."""
+    from s2t_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    rows, C = 5000, 176
+    x = (torch.randn((rows, C), generator=g) * 2 + 0.5).to(BF16)
+    gamma, beta = torch.rand(C, generator=g).to(BF16), torch.randn(C, generator=g).to(BF16)
+    part = ops.colstats(x.cuda())
+    s = part.sum(0).cpu()
+    assert torch.allclose(s[0], x.float().sum(0), rtol=1e-4, atol=1e-2)
+    assert torch.allclose(s[1], (x.float() ** 2).sum(0), rtol=1e-4, atol=1e-2)
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    nbt = torch.zeros((), device="cuda", dtype=torch.int64)
+    save = torch.empty((2, C), device="cuda")
+    y = ops.batchnorm_fwd(x.cuda(), gamma.cuda(), beta.cuda(), partials=part, running_mean=rm, running_var=rv,
+                          num_batches_tracked=nbt, save_stats=save, act=ops.ACT_SWISH, training=True)
+    bn = torch.nn.functional.batch_norm(x.float(), None, None, gamma.float(), beta.float(), training=True)
+    ref = bn * torch.sigmoid(bn)
+    assert (y.float().cpu() - ref).abs().max() <= 3e-2
