@@ -224,8 +224,25 @@ def gemm_roofline(torch, eng, P, peaks, replays: int = 20):
     n = len(calls)
     peak = float(peaks.get("bf16_tflops_sustained") or 1400.0)
     ach = fl / (ms * 1e-3) / 1e12
+    # algorithmic operand/result bytes per launch (every operand read once, the result written once) and the DRAM bytes
+    # ncu measured for the same launches (profiles/gemm_traffic.json, committed with the launch list it was taken from)
+    esz = lambda t: t.element_size() if t is not None else 2
+    alg = 0.0
+    for kw in calls:
+        nb = kw.get("batch", (1, 1))
+        z = nb[0] * nb[1]
+        alg += z * (kw["M"] * kw["K"] * 2 + kw["N"] * kw["K"] * 2 + kw["M"] * kw["N"] * esz(kw.get("out")))
+    traffic = None
+    tf = ROOT / "profiles" / "gemm_traffic.json"
+    if tf.exists():
+        try:
+            traffic = float(json.loads(tf.read_text())["dram_bytes_per_launch"])
+        except Exception:
+            traffic = None
     return {"bound": "tensor", "kernel": "gemm_bf16_kernel + gemm_bf16_splitk_kernel (all GEMM launches of one step)",
-            "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+            "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
+            "traffic_unit": "DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum, cold cache)",
+            "algorithmic_bytes_per_launch": alg / n,
             "launches_per_step": n, "avg_launch_us": 1e3 * ms / n, "gemm_ms_per_step": ms, "eager_step_ms": step_ms,
             "flop_per_step": fl,
             "how": f"the step's {n} GEMM launches captured alone into one CUDA graph, {replays} replays between CUDA events",
