@@ -209,6 +209,15 @@ int s2t_im2col1d(const void* xp, long long x_bs, void* xcol, int batch, int t_ou
  * (Downsampling.forward, pdss2t_transformer.py:107-116); lengths may be NULL                       */
 int s2t_frame_rows(const void* x, const int* lengths, void* y, long long y_bs, int pad, int batch,
                    int T, int C, void* stream);
+/* Fused self-attention forward (fairseq MultiheadAttention, modules/multihead_attention.py:246-265,372-416) for
+ * d_k == 64 and T <= 256: per (utterance, head, 128-query tile) S = scale * Q K^T on tcgen05 into TMEM, key-padding mask,
+ * fp32 softmax from TMEM, dropout, P V on tcgen05.  qkv bf16 [B*T][ldqkv] with q | k | v at columns 0 | C | 2C, head h at
+ * h*64; outputs: probs / probs_drop bf16 [B*H][T][ld] (kept for the backward pass; probs_drop may be NULL when
+ * dropout_p == 0), ctx bf16 [B*T][ldctx].  Same Philox numbering as s2t_attn_softmax_fwd.                    */
+int s2t_attn_fused_fwd(const void* qkv, long long ldqkv, int C, void* probs, void* probs_drop, long long ld,
+                       void* ctx, long long ldctx, const int* klen, int batch, int heads, int T, int dk,
+                       float scale, float dropout_p, unsigned long long seed, unsigned int stream_id,
+                       const unsigned long long* seed_offset, void* stream);
 /* Conv2dSubsampling (fairseq/modules/speech_to_text/subsampling.py:162-228): nn.Conv2d(k, stride, no padding) over a
  * channels-last activation x bf16 [B][T][D][Cin] as a GEMM over the patch matrix
  *   col[(b*T2 + t2)*D2 + d2][(j*k + i)*Cin + c] = x[b][stride*t2 + j][stride*d2 + i][c],  zero columns up to Kpad,

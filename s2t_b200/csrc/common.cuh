@@ -57,6 +57,11 @@ __device__ __forceinline__ void pdl_entry() {
 
 bool pdl_enabled();   // capi.cu
 
+// Build (or fetch from the cache) the 4-D SWIZZLE_128B tensor map of one bf16 (or fp32) matrix operand: `inner` contiguous
+// elements x `outer` rows of stride `ld`, two batch dimensions; TMA box = 64 (32 for fp32) x box_outer.  gemm.cu
+int make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint64_t nb1,
+                     uint64_t bs1, uint64_t nb2, uint64_t bs2, uint32_t box_outer, int fp32 = 0);
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
                               Args&&... args) {

@@ -725,9 +725,9 @@ struct MapKeyHash {
 // Build (or fetch) the 4-D bf16 tensor map of one operand.
 //   inner/outer: extents of the contiguous and the strided matrix dimension,
 //   ld: stride of the outer dimension (elements), box_outer: rows per TMA box.
-static int make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, uint64_t outer,
+int make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, uint64_t outer,
                             uint64_t ld, uint64_t nb1, uint64_t bs1, uint64_t nb2, uint64_t bs2,
-                            uint32_t box_outer, int fp32 = 0) {
+                            uint32_t box_outer, int fp32) {
   const uint64_t es = fp32 ? 4 : 2;
   static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
   static std::mutex mu;

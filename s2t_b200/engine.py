@@ -27,6 +27,7 @@ from __future__ import annotations
 
 import contextlib
 import math
+import os
 import re
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
@@ -567,6 +568,7 @@ class S2TEncoderEngine:
         # fork/join streams: leaf work of the backward pass (weight / bias gradients) and independent attention
         # branches run beside the critical dgrad chain; captured into the CUDA graph as parallel branches
         self.multi_stream = True
+        self.fused_attention = os.environ.get("S2T_FUSED_ATTN", "0") == "1"   # attn.cu (selfattn, d_k 64, T' <= 256): parity with the 3-launch form at C2 (2.25 vs 2.23 ms/step), off by default
         self._side = [torch.cuda.Stream(device=self.device) for _ in range(3)]
         self._forked: set = set()
         self.dp = None               # dp.BucketedAllReduce when data parallel
@@ -1020,6 +1022,13 @@ class S2TEncoderEngine:
         ops.linear(L.ln1, S.fused(a + q + ".weight", 3 * C, C), S.fused(a + q + ".bias", 3 * C, 0), out=L.qkv)
         bs_s = (T * ld, H * T * ld)
         dspec = self._drop(sp.site + 0, sp.p_drop)
+        if not rel and self.fused_attention and dk == 64 and T <= 256:
+            # one launch: S = q k^T (TMEM) -> masked fp32 softmax -> dropout -> P v  (attn.cu)
+            ops.attn_fused_fwd(L.qkv, C, St.lens, B, H, T, dk, probs=L.probs, probs_drop=L.probs_d if dspec else None,
+                               ctx=L.ctx, scale=dk ** -0.5, dropout=dspec)
+            ops.linear(L.ctx, S.p(a + o + ".weight"), S.p(a + o + ".bias"), out=L.x1,
+                       dropout=self._drop(sp.site + 1, sp.p_drop), residual=x, ldr=C)
+            return
         if not rel:
             ops.gemm_raw(M=T, N=T, K=dk, a=L.qkv, lda=3 * C, a_bs=(dk, T * 3 * C), b=L.qkv, ldb=3 * C, b_off=C,
                          b_bs=(dk, T * 3 * C), out=St.scores, ldc=ld, c_bs=bs_s, batch=(H, B), alpha=dk ** -0.5)
@@ -1312,8 +1321,11 @@ class S2TEncoderEngine:
         with self._fork(1):
             ops.colsum(d2, S.g(ffn + ".w_2.bias"), workspace=St.colsum_ws)
         if self.ffn_act == ops.ACT_RELU:
+            # f = dropout(relu(h)) is positive exactly where h > 0 AND the element was kept, so the gate on f covers the
+            # dropout mask too: no Philox regeneration in this epilogue, only the 1/(1-p) scale (folded into alpha)
+            spec = self._drop(site)
             ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=St.g_f, gate=f, gate_mode=ops.GATE_POSITIVE, ldg=St.F,
-                             dropout=self._drop(site))
+                             alpha=1.0 / (1.0 - spec[0]) if spec else 1.0)
         else:
             ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=St.g_f, gate=h, gate_mode=ops.GATE_SWISH_GRAD, ldg=St.F,
                              dropout=self._drop(site))

@@ -62,6 +62,7 @@ SIGNATURES = {
     "s2t_dropout": (_i, [_vp, _vp, _ll, _f, _f, _ull, _u, _vp, _vp]),
     "s2t_im2col1d": (_i, [_vp, _ll, _vp, _i, _i, _i, _i, _i, _vp]),
     "s2t_frame_rows": (_i, [_vp, _vp, _vp, _ll, _i, _i, _i, _i, _vp]),
+    "s2t_attn_fused_fwd": (_i, [_vp, _ll, _i, _vp, _vp, _ll, _vp, _ll, _vp, _i, _i, _i, _i, _f, _f, _ull, _u, _vp, _vp]),
     "s2t_im2col2d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2t_col2im2d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2t_colstats_parts": (_i, [_ll]),

@@ -23,7 +23,7 @@ _LAUNCHES = {
     "s2t_layernorm_fwd": 1, "s2t_layernorm_bwd": 1, "s2t_layernorm_bwd_reduce": 1, "s2t_glu_fwd": 1, "s2t_glu_bwd": 1,
     "s2t_colsum": 1, "s2t_col2im1d": 1, "s2t_embed_fwd": 1, "s2t_embed_bwd": 1, "s2t_mask_rows": 1,
     "s2t_permute_conv_weight": 1, "s2t_cast_f32_to_bf16": 1, "s2t_cast_bf16_to_f32": 1,
-    "s2t_attn_softmax_fwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4,
+    "s2t_attn_softmax_fwd": 1, "s2t_attn_fused_fwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4,
     "s2t_ctc_greedy": 2, "s2t_dwconv1d_fwd": 1, "s2t_dwconv1d_bwd": 3, "s2t_batchnorm_fwd": 1,
     "s2t_batchnorm_bwd": 2, "s2t_im2col2d": 1, "s2t_col2im2d": 1, "s2t_colstats": 1, "s2t_relpos_qbias_fwd": 1, "s2t_relpos_qbias_bwd": 1, "s2t_act_dropout": 1,
 }
@@ -417,6 +417,15 @@ def attn_softmax_fwd(scores: torch.Tensor, klen: Optional[torch.Tensor], heads: 
           _p(probs_drop),
           _p(klen), nbh, heads, Tq, Tk, scale, clamp, *_drop(dropout), _stream())
     return probs, probs_drop
+
+
+def attn_fused_fwd(qkv: torch.Tensor, C: int, klen: Optional[torch.Tensor], B: int, H: int, T: int, dk: int, *,
+                   probs: torch.Tensor, probs_drop: Optional[torch.Tensor], ctx: torch.Tensor, scale: float,
+                   dropout=None) -> None:
+    """Fused self-attention forward (d_k == 64, T <= 256): qkv bf16 [B*T, >=3C] -> probs (+ probs_drop) [B*H, T, ld] and
+    ctx [B*T, C]."""
+    _call("s2t_attn_fused_fwd", _p(qkv), qkv.stride(0), C, _p(probs), _p(probs_drop), probs.stride(1), _p(ctx),
+          ctx.stride(0), _p(klen), B, H, T, dk, scale, *_drop(dropout), _stream())
 
 
 def attn_softmax_bwd(probs: torch.Tensor, dprobs_drop: torch.Tensor, klen: Optional[torch.Tensor],

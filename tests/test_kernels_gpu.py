@@ -9,6 +9,11 @@ pytestmark = pytest.mark.gpu
 BF16 = torch.bfloat16
 
 
+def rel_l2(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
 def _rand(shape, seed, scale=1.0, dtype=BF16):
     g = torch.Generator().manual_seed(seed)
     return (torch.randn(shape, generator=g) * scale).to(dtype)
@@ -385,3 +390,50 @@ def test_colstats_feed_batchnorm(cuda_lib):
     bn = torch.nn.functional.batch_norm(x.float(), None, None, gamma.float(), beta.float(), training=True)
     ref = bn * torch.sigmoid(bn)
     assert (y.float().cpu() - ref).abs().max() <= 3e-2
+
+
+# --------------------------------------------------------------------------------------------------
+# fused self-attention forward (attn.cu) against the three-launch form it replaces
+# --------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("T,p", [(250, 0.0), (250, 0.1), (77, 0.1), (256, 0.0)])
+def test_attn_fused_fwd_matches_unfused(cuda_lib, T, p):
+    """S = q k^T / sqrt(d_k) -> key-padding mask -> fp32 softmax -> dropout -> P v.  Same Philox numbering as the
+    softmax kernel: the dropped positions must coincide exactly; values within bf16 rounding of the unfused path
+    (which rounds the scores to bf16 before the softmax) and of a float reference."""
+    from s2t_b200 import ops
+    g = torch.Generator().manual_seed(T)
+    B, H, dk = 3, 4, 64
+    C = H * dk
+    qkv = (torch.randn((B * T, 3 * C), generator=g) * 0.7).to(BF16).cuda()
+    klen = torch.tensor([T, max(T - 40, 1), max(T // 2, 1)], dtype=torch.int32).cuda()
+    ld = (T + 7) // 8 * 8
+    spec = (p, 1234, 5, None) if p > 0 else None
+    probs = torch.zeros((B * H, T, ld), dtype=BF16, device="cuda")
+    probs_d = torch.zeros_like(probs) if p > 0 else None
+    ctx = torch.zeros((B * T, C), dtype=BF16, device="cuda")
+    ops.attn_fused_fwd(qkv, C, klen, B, H, T, dk, probs=probs, probs_drop=probs_d, ctx=ctx, scale=dk ** -0.5, dropout=spec)
+    # unfused: scores GEMM -> softmax kernel -> PV GEMM (the engine's selfattn path)
+    scores = torch.zeros_like(probs)
+    bs = (T * ld, H * T * ld)
+    ops.gemm_raw(M=T, N=T, K=dk, a=qkv, lda=3 * C, a_bs=(dk, T * 3 * C), b=qkv, ldb=3 * C, b_off=C, b_bs=(dk, T * 3 * C),
+                 out=scores, ldc=ld, c_bs=bs, batch=(H, B), alpha=dk ** -0.5)
+    r_probs = torch.zeros_like(probs)
+    r_probs_d = torch.zeros_like(probs) if p > 0 else None
+    ops.attn_softmax_fwd(scores, klen, H, T, probs=r_probs, probs_drop=r_probs_d, dropout=spec)
+    r_ctx = torch.zeros_like(ctx)
+    pd = r_probs_d if p > 0 else r_probs
+    ops.gemm_raw(M=T, N=dk, K=T, a=pd, lda=ld, a_bs=bs, b=qkv, ldb=3 * C, b_off=2 * C, b_mn=True, b_bs=(dk, T * 3 * C),
+                 out=r_ctx, ldc=C, c_bs=(dk, T * C), batch=(H, B))
+    torch.cuda.synchronize()
+    assert (probs.float() - r_probs.float()).abs().max() <= 2e-2
+    if p > 0:
+        assert torch.equal(probs_d == 0, r_probs_d == 0) or \
+            ((probs_d == 0) != (r_probs_d == 0)).float().mean() < 1e-4      # identical masks (up to p == 0 underflow)
+        assert (probs_d.float() - r_probs_d.float()).abs().max() <= 3e-2
+    assert rel_l2(ctx, r_ctx) <= 2e-2
+    # float reference (no dropout): softmax rows sum to one over the valid keys, zero elsewhere
+    row_sums = probs.float().view(B, H, T, ld).sum(-1)
+    assert (row_sums - 1).abs().max() <= 2e-2
+    for b in range(B):
+        tail = probs.float().view(B, H, T, ld)[b, :, :, int(klen[b]):]
+        assert tail.numel() == 0 or float(tail.abs().max()) == 0.0
