@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define S2T_ABI_VERSION 2
+#define S2T_ABI_VERSION 3
 
 /* status / introspection ---------------------------------------------------------------------- */
 const char* s2t_last_error(void);
@@ -93,6 +93,10 @@ typedef struct s2t_gemm_args {
   /* split-K over a thread-block cluster (partials reduced through distributed shared memory):           */
   /* 0 = automatic, -1 = never, n > 1 = forced: the largest feasible factor <= n                          */
   int split_k;
+  /* upper bound on the CTAs (= SMs, one CTA per SM) the launch may occupy; 0 = the whole GPU.  A GEMM that runs on a  */
+  /* side stream beside a latency-critical chain of kernels is given a small share so that the chain's CTAs always      */
+  /* find free SMs; with a bound the split-K factor is also limited so that tiles * split_k <= max_ctas                 */
+  int max_ctas;
 } s2t_gemm_args;
 
 int s2t_gemm_bf16(const s2t_gemm_args* args, void* stream);

@@ -36,6 +36,7 @@ struct GemmKernelParams {
   int a_zm1, a_zm2, b_zm1, b_zm2;  // 0 = operand is broadcast along that batch dim (stride 0)
   int nbatch;
   int split_k;  // cluster size of the split-K kernel (1 = persistent kernel)
+  int max_ctas; // grid bound of the persistent kernel (0 = one CTA per SM)
   int out_fp32;
   int bias_vec;  // bias base 16B aligned -> 16-byte loads
   int aux_vec;   // gate / residual strides multiples of 8 and 16B-aligned bases -> 16-byte loads
@@ -796,7 +797,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     configured = true;
   }
   const long long tiles = 1ll * ((kp.N + BN - 1) / BN) * ((kp.M + kBM - 1) / kBM) * nbatch;
-  const int grid = static_cast<int>(tiles < sm_count() ? tiles : sm_count());
+  const int cap = (kp.max_ctas > 0 && kp.max_ctas < sm_count()) ? kp.max_ctas : sm_count();
+  const int grid = static_cast<int>(tiles < cap ? tiles : cap);
   S2T_LAUNCH(kern, grid, kGemmThreads, Cfg::kSmemBytes, stream, ta, tb, tc, kp);
   return 0;
 }
@@ -913,6 +915,8 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
     const long long mt = (g->M + kBM - 1) / kBM;
     const long long nbz = static_cast<long long>(nb1) * nb2;
     double best = -1.0;
+    const int cta_cap = (g->max_ctas > 0 && g->max_ctas < sm_count()) ? g->max_ctas : sm_count();
+    const int sk_cap = cta_cap < 128 ? cta_cap : 128;
     for (int cand : {64, 128, 256}) {
       if (g->tile_n == 64 || g->tile_n == 128 || g->tile_n == 256) {
         if (cand != g->tile_n) continue;
@@ -922,7 +926,7 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
       const long long tiles = mt * ((g->N + cand - 1) / cand) * nbz;
       const double kb_cyc = (kBM + cand) * 128.0 / 44.0;
       const double epi = cand * 13.0;
-      const long long waves = (tiles + sm_count() - 1) / sm_count();
+      const long long waves = (tiles + cta_cap - 1) / cta_cap;
       const double main1 = num_kb * kb_cyc;
       double cost = 2500.0 + (waves - 1) * (main1 > epi ? main1 : epi) + main1 + epi;
       int s_here = 1;
@@ -930,7 +934,7 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
         // power-of-two clusters only (odd sizes pack badly into GPCs), one wave, >= 4 k-blocks per rank
         for (int sk : {2, 4, 8}) {
           if (g->split_k > 1 && sk > g->split_k) break;
-          if (tiles * sk > 128) break;
+          if (tiles * sk > sk_cap) break;
           const int kb_per = (num_kb + sk - 1) / sk;
           if (kb_per < 4 || (sk - 1) * kb_per >= num_kb) continue;
           // reduce-scatter tail: park the partial tile (~600 clk), receive (sk-1)/sk of one fp32 tile over DSMEM at
@@ -973,6 +977,7 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
   kp.M = g->M; kp.N = g->N; kp.K = g->K; kp.nb1 = nb1;
   kp.nbatch = nb1 * nb2;
   kp.split_k = split;
+  kp.max_ctas = g->max_ctas;
   kp.a_zm1 = g->a_bs1 != 0; kp.a_zm2 = g->a_bs2 != 0;
   kp.b_zm1 = g->b_bs1 != 0; kp.b_zm2 = g->b_bs2 != 0;
   kp.out_fp32 = g->out_fp32 ? 1 : 0;

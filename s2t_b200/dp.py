@@ -79,6 +79,10 @@ class BucketedAllReduce:
             self._launch(*self.buckets[self.next])
             self.next += 1
 
+    def would_ship(self, offset: int) -> bool:
+        """True when ``on_ready(offset)`` would hand at least one bucket to the collective."""
+        return self.next < len(self.buckets) and self.buckets[self.next][0] >= offset
+
     def finish(self) -> None:
         self.on_ready(0)
         for w, view in self.works:

@@ -229,6 +229,7 @@ class _Stage(_Bufs):
         self.ln_part = e(lib.s2t_layernorm_bwd_partials(R, C), 2, C, dt=F32)
         self._ln_parts = [self.ln_part] + [e(lib.s2t_layernorm_bwd_partials(R, C), 2, C, dt=F32) for _ in range(3)]
         self._ln_i = 0
+        self._ln_ev: List[Optional[torch.cuda.Event]] = [None] * len(self._ln_parts)
         if c.attn_type == "rel_pos":
             n_rel = 2 * T - 1
             self.ldb = _round8(n_rel)
@@ -570,6 +571,11 @@ class S2TEncoderEngine:
         self.multi_stream = True
         self.fused_attention = os.environ.get("S2T_FUSED_ATTN", "0") == "1"   # attn.cu (selfattn, d_k 64, T' <= 256): parity with the 3-launch form at C2 (2.25 vs 2.23 ms/step), off by default
         self._side = [torch.cuda.Stream(device=self.device) for _ in range(3)]
+        # SM partition of the backward pass: (chain GEMM CTAs, weight-gradient GEMM CTAs, weight-gradient split-K policy);
+        # measured on B200 (148 SMs): 100 + 48 without split-K, 2.14 -> 1.94 ms/step (ops.set_sm_shares)
+        self.sm_shares = tuple(int(v) for v in os.environ.get("S2T_SM_SHARES", "100,48,-1").split(","))
+        self._ln_stream = torch.cuda.Stream(device=self.device)   # LayerNorm dgamma/dbeta reductions (_ln_bwd)
+        self._ln_pending = False
         self._forked: set = set()
         self.dp = None               # dp.BucketedAllReduce when data parallel
         self.init_parameters()
@@ -1196,8 +1202,18 @@ class S2TEncoderEngine:
     def _ready(self, first_name: str) -> None:
         """Everything at or after ``first_name`` in the flat gradient buffer is final."""
         self._join()
-        if self.grad_ready_hook is not None:
-            self.grad_ready_hook(self.store.offset(first_name))
+        if self.grad_ready_hook is None:
+            return                       # single GPU: the LayerNorm reductions are collected at the end of backward
+        off = self.store.offset(first_name)
+        if self.dp is not None and self.grad_ready_hook == self.dp.on_ready and not self.dp.would_ship(off):
+            return                       # no bucket completes here: nothing has to be final yet
+        self._join_ln()
+        self.grad_ready_hook(off)
+
+    def _join_ln(self) -> None:
+        if self._ln_pending:
+            torch.cuda.current_stream().wait_stream(self._ln_stream)
+            self._ln_pending = False
 
     def _ln_bwd(self, St: _Stage, dy: torch.Tensor, x: torch.Tensor, norm: str, stats: torch.Tensor, *,
                 dx_residual: Optional[torch.Tensor] = None, nxt=None):
@@ -1209,9 +1225,24 @@ class S2TEncoderEngine:
         dx, dd, spec, scale = St.take(), None, None, 1.0
         if nxt is not None and (nxt[0] is not None or nxt[1] != 1.0):
             dd, (spec, scale) = St.take(), nxt
+        idx = St._ln_i
+        main = torch.cuda.current_stream()
+        if self.multi_stream and St._ln_ev[idx] is not None:
+            main.wait_event(St._ln_ev[idx])          # the reduce that last read this partial buffer has finished
         ops.layernorm_bwd(dy, x, S.p(norm + ".weight"), stats, None, None, dx_residual=dx_residual, out=dx,
                           partials=part, out_drop=dd, drop=spec, drop_scale=scale, reduce=False)
-        with self._fork(1):
+        if self.multi_stream:
+            # dgamma / dbeta reduction on its own stream, joined only where gradients are declared final (_ready):
+            # the ordinary _join() after every block must not put these 5 us on the dgrad chain
+            ln = self._ln_stream
+            ln.wait_stream(main)
+            with torch.cuda.stream(ln):
+                ops.layernorm_bwd_reduce(part, x.shape[0], x.shape[1], S.g(norm + ".weight"), S.g(norm + ".bias"))
+                ev = torch.cuda.Event()
+                ev.record(ln)
+            St._ln_ev[idx] = ev
+            self._ln_pending = True
+        else:
             ops.layernorm_bwd_reduce(part, x.shape[0], x.shape[1], S.g(norm + ".weight"), S.g(norm + ".bias"))
         return dx, dd
 
@@ -1555,6 +1586,16 @@ class S2TEncoderEngine:
 
     def _backward(self, P: Plan) -> None:
         c = self.cfg
+        for St in P.stages:
+            St._ln_ev = [None] * len(St._ln_parts)      # events never cross a step (or a graph-capture) boundary
+        prev = ops.set_sm_shares(*(self.sm_shares if self.multi_stream else (0, 0, 0)))
+        try:
+            self._backward_body(P)
+        finally:
+            ops.set_sm_shares(*prev)
+
+    def _backward_body(self, P: Plan) -> None:
+        c = self.cfg
         d, dd = self._head_bwd(P)
         g = len(self.layer_specs)
         for i in reversed(range(len(P.stages))):
@@ -1578,6 +1619,8 @@ class S2TEncoderEngine:
                 self._stem_s2t_bwd(P, d)
             else:
                 d = self._stem_pds_bwd(P, i, d)
+        self._join()
+        self._join_ln()
 
     # ------------------------------------------------------------------------------------------
     # public API
@@ -1656,7 +1699,11 @@ class S2TEncoderEngine:
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        # the dgrad chain is captured on a high-priority stream: when a chain GEMM and a side-stream weight-gradient
+        # GEMM become ready together (both 1 CTA/SM), the chain's CTAs are placed first
+        prio = -1 if os.environ.get("S2T_CHAIN_PRIORITY", "1") == "1" else 0
+        cs = torch.cuda.Stream(device=self.device, priority=prio)
+        with torch.cuda.graph(g, stream=cs):
             fn(P)
         P.graph, P.graph_kind = g, kind
 

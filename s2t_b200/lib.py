@@ -12,7 +12,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libs2t_b200.so"
 
 _vp, _i, _ll, _f, _ull, _u = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong, C.c_uint
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 ACT_NONE, ACT_RELU, ACT_SWISH = 0, 1, 2
 GATE_NONE, GATE_POSITIVE, GATE_SWISH_GRAD, GATE_MUL = 0, 1, 2, 3
 
@@ -33,6 +33,7 @@ class GemmArgs(C.Structure):
         ("tile_n", _i),
         ("dropout_seed_offset", _vp),
         ("split_k", _i),
+        ("max_ctas", _i),
     ]
 
 

@@ -7,6 +7,7 @@ tensor raises.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Sequence, Tuple
 
 import torch
@@ -59,6 +60,22 @@ def _drop(d):
 # --------------------------------------------------------------------------------------------------
 # GEMM
 # --------------------------------------------------------------------------------------------------
+# SM shares for the duration of the engine's multi-stream backward pass (0 = the whole GPU): GEMMs of the dgrad chain are
+# bounded to ``chain`` CTAs and weight-gradient GEMMs (side streams) to ``wgrad`` CTAs without split-K, chain + wgrad =
+# the SM count, so that neither ever waits for an SM held by the other (every GEMM CTA needs a whole SM's shared memory).
+_default_max_ctas = 0
+_wgrad_max_ctas = 0
+_wgrad_split_k = 0
+
+
+def set_sm_shares(chain: int = 0, wgrad: int = 0, wgrad_split_k: int = 0) -> Tuple[int, int, int]:
+    """Returns the previous (chain, wgrad, wgrad_split_k)."""
+    global _default_max_ctas, _wgrad_max_ctas, _wgrad_split_k
+    old = (_default_max_ctas, _wgrad_max_ctas, _wgrad_split_k)
+    _default_max_ctas, _wgrad_max_ctas, _wgrad_split_k = int(chain), int(wgrad), int(wgrad_split_k)
+    return old
+
+
 def gemm_raw(
     *, M: int, N: int, K: int,
     a: torch.Tensor, lda: int, a_mn: bool = False, a_bs: Tuple[int, int] = (0, 0), a_off: int = 0,
@@ -68,7 +85,7 @@ def gemm_raw(
     act: int = ACT_NONE, gate: Optional[torch.Tensor] = None, gate_mode: int = GATE_NONE, ldg: int = 0,
     g_bs: Tuple[int, int] = (0, 0), dropout: Optional[Tuple[float, int, int]] = None,
     out_scale: float = 1.0, residual: Optional[torch.Tensor] = None, ldr: int = 0,
-    r_bs: Tuple[int, int] = (0, 0), tile_n: int = 0, split_k: int = 0,
+    r_bs: Tuple[int, int] = (0, 0), tile_n: int = 0, split_k: int = 0, max_ctas: int = 0,
 ) -> None:
     """out[z] = residual + out_scale*dropout(gate(act(alpha * A[z] @ B[z]^T + bias))) — see s2t_b200.h.
 
@@ -101,6 +118,7 @@ def gemm_raw(
     g.r_bs1, g.r_bs2 = r_bs
     g.tile_n = tile_n
     g.split_k = split_k
+    g.max_ctas = max_ctas if max_ctas else _default_max_ctas
     _call("s2t_gemm_bf16", C.byref(g), _stream())
 
 
@@ -134,6 +152,8 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out: Optional[torch.Tenso
     K = x.shape[1]
     if out is None:
         out = torch.empty((N, K), device=dy.device, dtype=out_dtype)
+    epi.setdefault("split_k", _wgrad_split_k)
+    epi.setdefault("max_ctas", _wgrad_max_ctas)
     gemm_raw(M=N, N=K, K=R, a=dy, lda=dy.stride(0), a_mn=True, b=x, ldb=x.stride(0), b_mn=True,
              out=out, ldc=out.stride(0), **epi)
     return out

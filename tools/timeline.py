@@ -26,18 +26,26 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     torch.cuda.synchronize()
 evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA and "memcpy" not in e.name.lower()]
 evs.sort(key=lambda e: e.time_range.start)
+def _sid(e):
+    try:
+        return e.device_resource_id if hasattr(e, "device_resource_id") else -1
+    except Exception:
+        return -1
 # split replays at counter_add
 marks = [i for i, e in enumerate(evs) if "counter_add" in e.name]
 step = evs[marks[1]:marks[2]] if len(marks) >= 3 else evs
 t0 = step[0].time_range.start
-rows = [((e.time_range.start - t0), (e.time_range.end - e.time_range.start), e.name.split("(")[0].replace("void ", "")[:60]) for e in step]
+sids = {}
+for e in step:
+    sids.setdefault(_sid(e), len(sids))
+rows = [((e.time_range.start - t0), (e.time_range.end - e.time_range.start), e.name.split("(")[0].replace("void ", "").replace(", ", ";")[:60], sids[_sid(e)]) for e in step]
 with open(out, "w") as f:
-    f.write("start_us,dur_us,name\n")
+    f.write("start_us,dur_us,name,stream\n")
     for r in rows:
-        f.write(f"{r[0]:.2f},{r[1]:.2f},{r[2]}\n")
+        f.write(f"{r[0]:.2f},{r[1]:.2f},{r[2]},{r[3]}\n")
 end = max(r[0] + r[1] for r in rows)
 busy, cur_s, cur_e = 0.0, None, None
-for s_, d, _ in rows:
+for s_, d, _, _ in rows:
     e_ = s_ + d
     if cur_e is None or s_ > cur_e:
         if cur_e is not None:
@@ -49,7 +57,7 @@ busy += cur_e - cur_s
 print(f"kernels {len(rows)}  span {end:.1f} us  device busy (union) {busy:.1f} us  idle {end - busy:.1f} us  sum of durations {sum(r[1] for r in rows):.1f} us")
 import collections
 agg = collections.defaultdict(lambda: [0, 0.0])
-for _, d, nme in rows:
+for _, d, nme, _ in rows:
     agg[nme][0] += 1; agg[nme][1] += d
 for k, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:25]:
     print(f"{k:62s} {c:4d} {t:9.1f} us  avg {t / c:6.1f}")
