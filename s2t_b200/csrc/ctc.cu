@@ -512,7 +512,9 @@ ctc_dense_grad_kernel(const void* __restrict__ logits, int is_bf16, long long ld
   pdl_entry();
   const long long row = blockIdx.x;
   const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
-  const float nr = nll_raw[b];
+  // nll_raw == nullptr: launched beside the lattice kernel (s2t_ctc_loss); the occupancy kernel then publishes nll and
+  // clears the rows of infeasible utterances
+  const float nr = nll_raw != nullptr ? nll_raw[b] : 0.f;
   const bool feasible = isfinite(nr);
   if (t == 0 && threadIdx.x == 0 && nll_out != nullptr) nll_out[b] = feasible ? nr : 0.f;
   if (dlogits == nullptr) return;
@@ -546,11 +548,26 @@ ctc_dense_grad_kernel(const void* __restrict__ logits, int is_bf16, long long ld
 __global__ void ctc_occupancy_kernel(const int* __restrict__ targets, long long tgt_ld,
                                      const int* __restrict__ in_len, const int* __restrict__ tgt_len,
                                      int T, int Sp, int V, int blank, CtcWs ws, int is_bf16,
-                                     long long ldv, void* __restrict__ dlogits, float scale) {
+                                     long long ldv, void* __restrict__ dlogits, float scale,
+                                     float* __restrict__ nll_out) {
   pdl_entry();
   extern __shared__ float s_occ[];  // [Sp]
   const int t = blockIdx.x, b = blockIdx.y;
   const float nr = ws.nll_raw[b];
+  if (nll_out != nullptr) {
+    // the dense part ran without knowing which utterances are feasible (zero_infinity): settle that here
+    if (t == 0 && threadIdx.x == 0) nll_out[b] = isfinite(nr) ? nr : 0.f;
+    if (!isfinite(nr) && t < min(in_len[b], T)) {
+      const long long r0 = (static_cast<long long>(b) * T + t) * ldv;
+      if (is_bf16) {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(dlogits) + r0;
+        for (int i = threadIdx.x; i < V; i += blockDim.x) o[i] = __float2bfloat16(0.f);
+      } else {
+        float* o = reinterpret_cast<float*>(dlogits) + r0;
+        for (int i = threadIdx.x; i < V; i += blockDim.x) o[i] = 0.f;
+      }
+    }
+  }
   if (!isfinite(nr) || t >= min(in_len[b], T)) return;
   const int S = tgt_len[b];
   const int Se = 2 * S + 1;
@@ -747,6 +764,26 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
   ws.nll_raw = base + 3 * n + 1ll * batch * Sp;
   cudaStream_t st = ST(stream);
 
+  // With a gradient wanted, scale * softmax (one pass over the [B*T, V] logits, every SM) runs on an internal side
+  // stream beside gather + lattice (a handful of warps, ~T dependent steps); the occupancy pass joins the two.
+  // Event fork / join: also legal while `st` is being captured into a CUDA graph.
+  static cudaStream_t side = nullptr;
+  static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  const bool overlap = dlogits != nullptr;
+  if (overlap) {
+    if (side == nullptr) {
+      S2T_CHECK_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+      S2T_CHECK_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+      S2T_CHECK_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+    }
+    S2T_CHECK_CUDA(cudaEventRecord(ev_fork, st));
+    S2T_CHECK_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+    S2T_LAUNCH(ctc_dense_grad_kernel, batch * T, 256, 0, side, logits, is_bf16, ldv, lse, input_lengths, T, V,
+               static_cast<const float*>(nullptr), static_cast<float*>(nullptr), dlogits, grad_scale);
+    S2T_LAUNCH_CHECK();
+    S2T_CHECK_CUDA(cudaEventRecord(ev_join, side));
+  }
+
   {
     int gx = static_cast<int>((1ll * T * Sp + 255) / 256);
     if (gx > 64) gx = 64;
@@ -785,12 +822,14 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
       S2T_LAUNCH(ctc_alpha_beta_kernel, g, threads, smem, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
     S2T_LAUNCH_CHECK();
   }
-  S2T_LAUNCH(ctc_dense_grad_kernel, batch * T, 256, 0, st, logits, is_bf16, ldv, lse, input_lengths, T, V, ws.nll_raw, nll, dlogits, grad_scale);
-  S2T_LAUNCH_CHECK();
-  if (dlogits != nullptr) {
+  if (!overlap) {   // loss only: publish nll (zero_infinity applied)
+    S2T_LAUNCH(ctc_dense_grad_kernel, batch * T, 256, 0, st, logits, is_bf16, ldv, lse, input_lengths, T, V, ws.nll_raw, nll, dlogits, grad_scale);
+    S2T_LAUNCH_CHECK();
+  } else {
+    S2T_CHECK_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
     int othreads = ((Sp + 31) / 32) * 32;
     if (othreads > 256) othreads = 256;
-    S2T_LAUNCH(ctc_occupancy_kernel, dim3(T, batch), othreads, sizeof(float) * Sp, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, V, blank, ws, is_bf16, ldv, dlogits, grad_scale);
+    S2T_LAUNCH(ctc_occupancy_kernel, dim3(T, batch), othreads, sizeof(float) * Sp, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, V, blank, ws, is_bf16, ldv, dlogits, grad_scale, nll);
     S2T_LAUNCH_CHECK();
   }
   return 0;

@@ -37,6 +37,7 @@ struct GemmKernelParams {
   int nbatch;
   int split_k;  // cluster size of the split-K kernel (1 = persistent kernel)
   int max_ctas; // grid bound of the persistent kernel (0 = one CTA per SM)
+  int gate_tma; // persistent kernel, compile-time gate epilogue: gate tiles arrive by TMA (tmG) instead of per-row loads
   int out_fp32;
   int bias_vec;  // bias base 16B aligned -> 16-byte loads
   int aux_vec;   // gate / residual strides multiples of 8 and 16B-aligned bases -> 16-byte loads
@@ -59,17 +60,23 @@ struct GemmKernelParams {
   unsigned long long* trace;  // debug: globaltimer stamps of CTA 0's phases (S2T_GEMM_TRACE=1), else nullptr
 };
 
-template <int BN>
+// GATE = 1: the persistent kernel stages the epilogue's gate operand through shared memory by TMA (32 KB: 4 lane
+// quarters x 2 buffers x [32 rows][128 B]); one operand stage less to make room.
+template <int BN, int GATE = 0>
 struct GemmCfg {
   static constexpr int kABytes = kBM * kBK * 2;
   static constexpr int kBBytes = BN * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BN >= 256) ? 3 : (BN >= 128 ? 5 : 6);  // 144-160 KB operand ring
+  static constexpr int kStages = ((BN >= 256) ? 3 : (BN >= 128 ? 5 : 6)) - GATE;  // 144-160 KB operand ring
   static constexpr int kStagingBytes = kEpiWarps * 2 /*double buffer*/ * 4096;
+  static constexpr int kGateBytes = GATE ? 4 * 2 * 4096 : 0;
   static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;            // two accumulator buffers
   static constexpr int kSmemBytes =
-      kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+      kStages * kStageBytes + kStagingBytes + kGateBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
+
+// compile-time epilogue code with a gate operand -> the TMA-staged gate path of the persistent kernel
+constexpr int epi_gate_tma(int epi) { return (epi >= 0 && ((epi >> 2) & 3) != 0) ? 1 : 0; }
 
 __device__ __forceinline__ void trace_stamp(const GemmKernelParams& p, int slot) {
   if (p.trace != nullptr && blockIdx.x == 0) {
@@ -102,7 +109,7 @@ struct AuxUnit {
 template <int EPI>
 __device__ __forceinline__ void aux_prefetch(AuxUnit& ax, const GemmKernelParams& p, int ucol0, int ngroups,
                                              bool row_ok, long long grow, long long rrow) {
-  const bool need_g = (EPI < 0 ? (p.gate_mode != S2T_GATE_NONE) : (((EPI >> 2) & 3) != 0)) && p.aux_vec;
+  const bool need_g = (EPI < 0 ? (p.gate_mode != S2T_GATE_NONE) : (((EPI >> 2) & 3) != 0)) && p.aux_vec && !p.gate_tma;
   const bool need_r = (EPI < 0 ? true : ((EPI >> 5) & 1)) && p.residual != nullptr && p.aux_vec;
   const bool need_b = p.bias != nullptr && p.bias_vec;
   if (!row_ok || !(need_g || need_r || need_b)) return;
@@ -200,19 +207,23 @@ __device__ __forceinline__ void epilogue8(float (&v)[8], const GemmKernelParams&
 template <int BN, int A_MN, int B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmC, const GemmKernelParams p) {
-  using Cfg = GemmCfg<BN>;
+                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmG,
+                 const GemmKernelParams p) {
+  constexpr int kGateTma = epi_gate_tma(EPI);
+  using Cfg = GemmCfg<BN, kGateTma>;
   pdl_launch_dependents();   // the next kernel's set-up may overlap this one (common.cuh, PDL)
   if (threadIdx.x == 0) trace_stamp(p, 0);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned (stage sizes are multiples of 1024)
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
+  uint8_t* gate_stage = staging + Cfg::kStagingBytes;         // [4 quarters][2][4096] (GATE variants only)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(gate_stage + Cfg::kGateBytes);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;   // [2]
   uint64_t* tempty_bar = tfull_bar + 2;             // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* gate_bar = tempty_bar + 2;              // [4 quarters][2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gate_bar + 8);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -231,10 +242,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], kEpiWarps);
     }
+    for (int i = 0; i < 8; ++i) mbar_init(&gate_bar[i], 1);
     fence_mbar_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC);
+    if (kGateTma) tma_prefetch_desc(&tmG);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, Cfg::kTmemCols);
@@ -328,7 +341,33 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const unsigned long long drop_seed =
         p.drop_seed + ((p.drop_thresh16 != 0 && p.drop_seed_off != nullptr) ? *p.drop_seed_off : 0ull);
     const int units = BN / 32;   // fp32 output: one 32-column TMEM chunk (128-byte rows) per staged unit
-    uint32_t lt = 0, sb = 0;
+    uint32_t lt = 0, sb = 0, gcount = 0;
+    // gate operand (bf16 output, compile-time gate epilogue): one TMA box [32 rows][64 columns] per staged unit into a
+    // swizzled buffer of this lane quarter (read back conflict-free, one 16-byte chunk per thread and column group).
+    // The issuing lane walks the quarter's unit sequence two units ahead of the consumers, across tile boundaries.
+    const bool gtma = kGateTma && p.gate_tma;
+    int ptile = blockIdx.x, pu = 0;
+    uint32_t pcount = 0;
+    auto gate_issue_next = [&]() {
+      if (ptile >= num_tiles) return;
+      const int pz = ptile / tiles_per_z;
+      const int pr = ptile - pz * tiles_per_z;
+      const int pm0 = (pr % tiles_m) * kBM, pn0 = (pr / tiles_m) * BN;
+      uint64_t* gbar = &gate_bar[q * 2 + (pcount & 1)];
+      mbar_expect_tx(gbar, 4096);
+      tma_load_4d(gate_stage + q * 8192 + (pcount & 1) * 4096, &tmG, gbar, pn0 + pu * 64, pm0 + q * 32,
+                  p.g_bs1 != 0 ? pz % p.nb1 : 0, p.g_bs2 != 0 ? pz / p.nb1 : 0);
+      ++pcount;
+      ++pu;
+      if (pu == BN / 64 || pn0 + pu * 64 >= p.N) {
+        pu = 0;
+        ptile += gridDim.x;
+      }
+    };
+    if (gtma && half == 0 && lane == 0) {
+      gate_issue_next();
+      gate_issue_next();
+    }
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
       const int z = tile / tiles_per_z;
       const int r = tile - z * tiles_per_z;
@@ -361,6 +400,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tmem_ld_32x32(t_addr + u * 64 + half * 32, rg);
           uint8_t* sbuf = stage_q + (sb & 3) * 4096;
           uint8_t* srow = sbuf + lane * 128;
+          if (gtma) {
+            mbar_wait(&gate_bar[q * 2 + (gcount & 1)], (gcount >> 1) & 1);
+            const uint8_t* grow_s = gate_stage + q * 8192 + (gcount & 1) * 4096 + lane * 128;
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+              ax.g[g] = *reinterpret_cast<const uint4*>(grow_s + (((half * 4 + g) ^ (lane & 7)) << 4));
+          }
           tmem_ld_wait();
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
@@ -381,8 +427,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tma_store_4d(&tmC, sbuf, ucol0, m0 + q * 32, z1, z2);
             tma_store_commit();
             tma_store_wait_read<2>();
+            // both warps have read this unit's gate buffer (barrier above): refill it for the unit after next
+            if (gtma) gate_issue_next();
           }
           ++sb;
+          ++gcount;
           if (u + 1 < kUnits && ucol0 + 64 + half * 32 < p.N)
             aux_prefetch<EPI>(ax, p, ucol0 + 64 + half * 32, 4, row_ok, grow, rrow);
         }
@@ -787,8 +836,16 @@ static int sm_count() {
 
 template <int BN, int A_MN, int B_MN, int EPI>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
-                       const GemmKernelParams& kp, int nbatch, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
+                       const GemmKernelParams& kp_in, int nbatch, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN, epi_gate_tma(EPI)>;
+  GemmKernelParams kp = kp_in;
+  CUtensorMap tg = tc;     // placeholder when the variant has no TMA-staged gate
+  kp.gate_tma = 0;
+  if (epi_gate_tma(EPI) && kp.gate != nullptr && kp.aux_vec && !kp.out_fp32) {
+    const int rc = make_operand_map(&tg, kp.gate, kp.N, kp.M, kp.ldg, kp.nb1, kp.g_bs1, kp.nbatch / kp.nb1, kp.g_bs2, 32);
+    if (rc) return rc;
+    kp.gate_tma = 1;
+  }
   static bool configured = false;
   auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI>;
   if (!configured) {
@@ -799,7 +856,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   const long long tiles = 1ll * ((kp.N + BN - 1) / BN) * ((kp.M + kBM - 1) / kBM) * nbatch;
   const int cap = (kp.max_ctas > 0 && kp.max_ctas < sm_count()) ? kp.max_ctas : sm_count();
   const int grid = static_cast<int>(tiles < cap ? tiles : cap);
-  S2T_LAUNCH(kern, grid, kGemmThreads, Cfg::kSmemBytes, stream, ta, tb, tc, kp);
+  S2T_LAUNCH(kern, grid, kGemmThreads, Cfg::kSmemBytes, stream, ta, tb, tc, tg, kp);
   return 0;
 }
 

@@ -112,6 +112,16 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const uint4* dyr = reinterpret_cast<const uint4*>(dy + static_cast<long long>(row) * C);
     float xh[NV][8], g[NV][8];
     float s1 = 0.f, s2 = 0.f;
+    // the residual gradient is only needed after the two row reductions: fetch it with the other operands so that its
+    // latency is not paid a second time behind them
+    const uint4* rr =
+        dx_res ? reinterpret_cast<const uint4*>(dx_res + static_cast<long long>(row) * C) : nullptr;
+    uint4 rpre[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vi = i * 32 + lane;
+      rpre[i] = (rr != nullptr && vi < nvec) ? rr[vi] : make_uint4(0u, 0u, 0u, 0u);
+    }
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int vi = i * 32 + lane;
@@ -133,8 +143,6 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     s1 = warp_sum(s1) / static_cast<float>(C);
     s2 = warp_sum(s2) / static_cast<float>(C);
     uint4* dxr = reinterpret_cast<uint4*>(dx + static_cast<long long>(row) * C);
-    const uint4* rr =
-        dx_res ? reinterpret_cast<const uint4*>(dx_res + static_cast<long long>(row) * C) : nullptr;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int vi = i * 32 + lane;
@@ -144,7 +152,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         for (int j = 0; j < 8; ++j) o[j] = rstd * (g[i][j] - s1 - xh[i][j] * s2);
         if (rr) {
           float r[8];
-          unpack8(rr[vi], r);
+          unpack8(rpre[i], r);
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += r[j];
         }

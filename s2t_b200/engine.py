@@ -942,12 +942,13 @@ class S2TEncoderEngine:
         embed_ln -> x * embed_scale (+ sinusoidal positions for abs attention) -> dropout (:1768-1794)."""
         c, S = self.cfg, self.store
         k, st, n = c.subsampling_kernel, c.subsampling_stride, c.subsampling_layers
+        with self._fork(0):          # integer length bookkeeping beside the feature kernels (joined before the last GLU)
+            ln = P.src_len
+            for i in range(n):
+                torch.div(ln + (2 * P.pad - k), st, rounding_mode="floor", out=P.sub_len[i])
+                P.sub_len[i] += 1
+                ln = P.sub_len[i]
         self._features(P, P.framed[0], P.pad)
-        ln = P.src_len
-        for i in range(n):
-            torch.div(ln + (2 * P.pad - k), st, rounding_mode="floor", out=P.sub_len[i])
-            P.sub_len[i] += 1
-            ln = P.sub_len[i]
         for i in range(n):
             xin = P.framed[i]
             cin, cout, t_out = xin.shape[2], self.sub_filters[i], P.t_sub[i + 1]
@@ -959,6 +960,7 @@ class S2TEncoderEngine:
                 nxt = P.framed[i + 1]
                 ops.glu_fwd(P.pre[i], out=nxt, T=t_out, ldy=cout // 2, y_bs=nxt.stride(0), y_off=P.pad * (cout // 2))
             else:
+                self._join()
                 ops.glu_fwd(P.pre[i], out=P.x0, lengths=P.sub_len[i], T=t_out)
         self._embed_block_fwd(P)
 

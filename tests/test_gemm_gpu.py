@@ -93,6 +93,41 @@ def test_epilogue_swish_and_gates(cuda_lib):
     _check(out, acc * (s * (1 + g * (1 - s))))
 
 
+@pytest.mark.parametrize("M,Nout,K", [(2000, 2048, 256), (333, 200, 136), (128, 64, 64), (700, 520, 72)])
+@pytest.mark.parametrize("tile_n", [0, 64, 128, 256])
+@pytest.mark.parametrize("max_ctas", [0, 5])
+def test_dgrad_relu_gate_staged_by_tma(cuda_lib, M, Nout, K, tile_n, max_ctas):
+    """FFN w_2 dgrad: dx[M, Nout] = alpha * (dy[M, K] @ w[K, Nout]) where gate > 0 — the compile-time gate epilogue of the
+    persistent kernel (gate tiles arrive by TMA).  Ragged rows/columns, several tiles per CTA (max_ctas=5) so that the
+    two gate buffers and their barriers wrap."""
+    from s2t_b200 import ops
+    dy, w, gt = _rand((M, K), 21), _rand((K, Nout), 22, 0.2), _rand((M, Nout), 23)
+    out = ops.linear_dgrad(dy.cuda(), w.cuda(), gate=gt.cuda(), gate_mode=ops.GATE_POSITIVE, ldg=Nout, alpha=1.25,
+                           tile_n=tile_n, max_ctas=max_ctas, split_k=-1)
+    torch.cuda.synchronize()
+    acc = 1.25 * (dy.float() @ w.float())
+    _check(out, torch.where(gt.float() > 0, acc, torch.zeros_like(acc)))
+
+
+def test_dgrad_relu_gate_batched_and_unaligned(cuda_lib):
+    """Batched gate (strides per batch) and a gate whose stride defeats 16-byte access (falls back to scalar loads)."""
+    from s2t_b200 import ops
+    Z, M, N, K = 3, 200, 128, 64
+    a, b, gt = _rand((Z, M, K), 31), _rand((Z, K, N), 32, 0.2), _rand((Z, M, N), 33)
+    out = torch.empty((Z, M, N), dtype=BF16, device="cuda")
+    ag, bg, gg = a.cuda(), b.cuda(), gt.cuda()
+    ops.gemm_raw(M=M, N=N, K=K, a=ag, lda=K, a_bs=(M * K, 0), b=bg, ldb=N, b_mn=True, b_bs=(K * N, 0), out=out, ldc=N,
+                 c_bs=(M * N, 0), batch=(Z, 1), gate=gg, gate_mode=ops.GATE_POSITIVE, ldg=N, g_bs=(M * N, 0))
+    torch.cuda.synchronize()
+    acc = torch.bmm(a.float(), b.float())
+    _check(out, torch.where(gt.float() > 0, acc, torch.zeros_like(acc)))
+    g_odd = torch.zeros((M, N + 4), dtype=BF16, device="cuda")
+    g_odd[:, :N] = gg[0]
+    out2 = ops.linear_dgrad(ag[0], bg[0], gate=g_odd, gate_mode=ops.GATE_POSITIVE, ldg=N + 4)
+    torch.cuda.synchronize()
+    _check(out2, torch.where(gt[0].float() > 0, acc[0], torch.zeros_like(acc[0])))
+
+
 def test_dropout_epilogue_is_regenerable_and_unbiased(cuda_lib):
     from s2t_b200 import ops
     M, N, K = 1024, 512, 64

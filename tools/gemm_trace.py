@@ -39,7 +39,7 @@ def run(tag, M, N, K, **epi):
             print(f"   {n:32s} {(best[i] - best[0]) / 1e3:8.2f} us")
 
 
-def run_raw(tag, **kw):
+def run_raw(tag, persistent=False, **kw):
     flush = torch.empty(64 << 20, device="cuda", dtype=torch.float32)
     best = None
     for _ in range(6):
@@ -54,8 +54,9 @@ def run_raw(tag, **kw):
             best = t
     print(f"== {tag}: CTA0 entry->exit {(best[11] - best[0]) / 1e3:.2f} us")
     names = dict(enumerate(NAMES))
-    names.update({5: "mma: all k-blocks committed", 6: "all partials visible (cluster sync)", 7: "slice: first group summed",
-                  9: "slice: epilogue stored"})
+    if not persistent:
+        names.update({5: "mma: all k-blocks committed", 6: "all partials visible (cluster sync)", 7: "slice: first group summed",
+                      9: "slice: epilogue stored"})
     for i in range(12):
         if best[i]:
             print(f"   {names[i]:40s} {(best[i] - best[0]) / 1e3:8.2f} us")
@@ -83,3 +84,14 @@ run("ffn1 relu+dropout", 2000, 2048, 256, act=ops.ACT_RELU, dropout=(0.1, 1234, 
 run("qkv", 2000, 768, 256)
 run("out-proj", 2000, 256, 256)
 run("ctc head", 2000, 10000, 256)
+
+go = torch.empty(R, 2048, device="cuda", dtype=torch.bfloat16)
+for cap in (0, 100):
+    run_raw(f"ffn2 dgrad + relu gate (N=2048, K=256, B mn-major, max_ctas={cap})", True, M=R, N=2048, K=256, a=dy, lda=256,
+            b=w2, ldb=2048, b_mn=True, out=go, ldc=2048, gate=f2048, gate_mode=ops.GATE_POSITIVE, ldg=2048, alpha=1.111,
+            max_ctas=cap)
+run_raw("ffn2 dgrad without gate", True, M=R, N=2048, K=256, a=dy, lda=256, b=w2, ldb=2048, b_mn=True, out=go, ldc=2048)
+wq = bf(768, 256)
+gq = bf(R, 768)
+run_raw("qkv dgrad (K=768, no split)", True, M=R, N=256, K=768, a=gq, lda=768, b=wq, ldb=256, b_mn=True, out=o, ldc=256,
+        split_k=-1)
