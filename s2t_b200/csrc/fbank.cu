@@ -30,9 +30,16 @@ fbank_kernel(const float* __restrict__ wave, long long wave_ld, const int* __res
              const float* __restrict__ window, int n_mels, void* __restrict__ out, int out_bf16,
              int max_frames, long long out_ld, long long out_bs, int* __restrict__ out_frames) {
   pdl_entry();
-  __shared__ float2 s_fft[kFbankWarps][kFft];
-  __shared__ float s_pow[kFbankWarps][kBins + 3];
-  __shared__ float2 s_tw[kFft / 2];  // exp(-2*pi*i*k/512)
+  // per warp: 512 complex values in the padded transpose layout (16 * L + (L >> 1) + r, see below); reused for the
+  // 257 power-spectrum bins once the FFT is back in registers
+  __shared__ float2 s_fft[kFbankWarps][kFft + 16];
+  // twiddles exp(-2*pi*i*k/512) laid out per FFT stage: entry (half - 1) + pos = k = pos << (8 - stage), so that the
+  // lanes of a stage read consecutive words (the strided k of a single table is a 16-way bank conflict mid-FFT)
+  __shared__ float2 s_tw[kFft];
+  // non-zero mel weights packed filter after filter (each FFT bin belongs to at most two triangular filters)
+  constexpr int kMelPacked = 2 * kBins + 32;
+  __shared__ float s_mw[kMelPacked];
+  __shared__ int s_moff[129], s_mlo[128], s_mhi[128];
 
   const int b = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -42,10 +49,48 @@ fbank_kernel(const float* __restrict__ wave, long long wave_ld, const int* __res
   if (blockIdx.x == 0 && threadIdx.x == 0 && out_frames != nullptr)
     out_frames[b] = nframes < max_frames ? nframes : max_frames;
 
-  for (int k = threadIdx.x; k < kFft / 2; k += blockDim.x) {
+  for (int e = threadIdx.x; e < kFft - 1; e += blockDim.x) {
+    const int st = 31 - __clz(e + 1);                 // stage: half = 1 << st
+    const int k = (e + 1 - (1 << st)) << (8 - st);
     float s, c;
     sincospif(-2.0f * static_cast<float>(k) / static_cast<float>(kFft), &s, &c);
-    s_tw[k] = make_float2(c, s);
+    s_tw[e] = make_float2(c, s);
+  }
+  if (threadIdx.x < 128) {
+    const int f = threadIdx.x;
+    const int lo = f < n_mels ? mel_range[2 * f] : 0, hi = f < n_mels ? mel_range[2 * f + 1] : 0;
+    s_mlo[f] = lo;
+    s_mhi[f] = hi > lo ? hi : lo;
+  }
+  __syncthreads();
+  if (warp == 0) {   // exclusive scan of the filter widths, four consecutive filters per lane
+    int cnt[4], tot = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      cnt[j] = s_mhi[lane * 4 + j] - s_mlo[lane * 4 + j];
+      tot += cnt[j];
+    }
+    int incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    int base = incl - tot;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      s_moff[lane * 4 + j] = base;
+      base += cnt[j];
+    }
+    if (lane == 31) s_moff[128] = incl;
+  }
+  __syncthreads();
+  const bool mel_packed = s_moff[128] <= kMelPacked;
+  if (mel_packed && threadIdx.x < n_mels) {
+    const int f = threadIdx.x, lo = s_mlo[f], n = s_mhi[f] - lo;
+    const float* wrow = mel_w + static_cast<long long>(f) * kBins + lo;
+    float* dst = s_mw + s_moff[f];
+    for (int k = 0; k < n; ++k) dst[k] = __ldg(wrow + k);
   }
   __syncthreads();
   if (frame >= max_frames) return;
@@ -72,8 +117,15 @@ fbank_kernel(const float* __restrict__ wave, long long wave_ld, const int* __res
     sum += x[i];
   }
   const float mean = warp_sum(sum) / static_cast<float>(kFrameLen);
-  // ---- pre-emphasis (replicate-padded first sample), povey window, bit-reversed scatter ---------
-  float2* fft = s_fft[warp];
+  // ---- pre-emphasis (replicate-padded first sample), povey window ------------------------------------------
+  // 512-point radix-2 DIT FFT held in registers.  Position p of the bit-reversed input order holds sample
+  // bitrev9(p); with p = 16 * L + r the samples of "virtual lane" L are 32 * rev4(r) + rev5(L): exactly the
+  // samples 32 * i + lane this lane has loaded, with L = rev5(lane), r = rev4(i).  Stages 0-3 (pairs inside one
+  // group of 16 positions) therefore need no data movement at all; one transpose through shared memory regroups
+  // to i = 256 * b8 + 16 * m + low4 (lane = 16 * b8 + low4, register m) for stages 4-7; stage 8 pairs lanes l, l ^ 16.
+  float2 y[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) y[i] = make_float2(0.f, 0.f);
 #pragma unroll
   for (int i = 0; i < 13; ++i) {
     const int idx = i * 32 + lane;
@@ -84,45 +136,92 @@ fbank_kernel(const float* __restrict__ wave, long long wave_ld, const int* __res
     if (lane == 0) prev = (i == 0) ? cur : prev_row;
     float v = 0.f;
     if (idx < kFrameLen) v = (cur - 0.97f * prev) * __ldg(window + idx);
-    fft[bitrev9(idx)] = make_float2(v, 0.f);
+    // rev4(i) as a compile-time constant after unrolling
+    y[((i & 1) << 3) | ((i & 2) << 1) | ((i & 4) >> 1) | ((i & 8) >> 3)].x = v;
   }
-  // zero padding 416..511 (indices 400..415 were written above as v = 0)
-  for (int idx = 13 * 32 + lane; idx < kFft; idx += 32) fft[bitrev9(idx)] = make_float2(0.f, 0.f);
-  __syncwarp();
-
-  // ---- 512-point radix-2 DIT FFT, 256 butterflies per stage, 8 per lane -------------------------
+  // ---- stages 0-3: registers only; twiddles are lane-uniform (broadcast reads) ------------------
 #pragma unroll
-  for (int st = 0; st < 9; ++st) {
+  for (int st = 0; st < 4; ++st) {
     const int half = 1 << st;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int t = j * 32 + lane;               // butterfly id 0..255
-      const int pos = t & (half - 1);
-      const int i0 = ((t >> st) << (st + 1)) + pos;
+      const int pos = j & (half - 1);
+      const int i0 = ((j >> st) << (st + 1)) + pos;
       const int i1 = i0 + half;
-      const float2 w = s_tw[pos << (8 - st)];
-      const float2 a = fft[i0], c = fft[i1];
+      const float2 w = s_tw[half - 1 + pos];
+      const float2 a = y[i0], c = y[i1];
       const float tr = c.x * w.x - c.y * w.y;
       const float ti = c.x * w.y + c.y * w.x;
-      fft[i0] = make_float2(a.x + tr, a.y + ti);
-      fft[i1] = make_float2(a.x - tr, a.y - ti);
+      y[i0] = make_float2(a.x + tr, a.y + ti);
+      y[i1] = make_float2(a.x - tr, a.y - ti);
     }
-    __syncwarp();
   }
-  // ---- power spectrum: torchaudio does rfft().abs().pow(2) ----------------------------------------
-  float* pw = s_pow[warp];
-  for (int k = lane; k < kBins; k += 32) {
-    const float2 v = fft[k];
-    const float a = sqrtf(v.x * v.x + v.y * v.y);
-    pw[k] = a * a;
+  // ---- transpose: position p = 16 * L + r lives at word p + (L >> 1) (conflict-free 64-bit accesses both ways) ----
+  float2* fft = s_fft[warp];
+  {
+    const int L = static_cast<int>(__brev(static_cast<unsigned>(lane)) >> 27);
+    float2* dst = fft + 16 * L + (L >> 1);
+#pragma unroll
+    for (int r = 0; r < 16; ++r) dst[r] = y[r];
+  }
+  __syncwarp();
+  const int b8 = lane >> 4, low4 = lane & 15;
+#pragma unroll
+  for (int m = 0; m < 16; ++m) {
+    const int Li = b8 * 16 + m;
+    y[m] = fft[16 * Li + (Li >> 1) + low4];
+  }
+  __syncwarp();   // the buffer is free again (power spectrum below)
+  // ---- stages 4-7: registers; the twiddle depends on low4 and the low bits of m ---------------------------
+#pragma unroll
+  for (int st = 4; st < 8; ++st) {
+    const int half = 1 << st, sub = 1 << (st - 4);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int mlow = j & (sub - 1);
+      const int m0 = ((j >> (st - 4)) << (st - 3)) + mlow;
+      const int m1 = m0 + sub;
+      const float2 w = s_tw[half - 1 + mlow * 16 + low4];
+      const float2 a = y[m0], c = y[m1];
+      const float tr = c.x * w.x - c.y * w.y;
+      const float ti = c.x * w.y + c.y * w.x;
+      y[m0] = make_float2(a.x + tr, a.y + ti);
+      y[m1] = make_float2(a.x - tr, a.y - ti);
+    }
+  }
+  // ---- stage 8 + power spectrum: bins 0..255 are the sums (lanes with b8 = 0), bin 256 the one difference at
+  // position 0; torchaudio does rfft().abs().pow(2) ---------------------------------------------------------
+  float* pw = reinterpret_cast<float*>(fft);
+#pragma unroll
+  for (int m = 0; m < 16; ++m) {
+    const float cx = __shfl_down_sync(0xffffffffu, y[m].x, 16);
+    const float cy = __shfl_down_sync(0xffffffffu, y[m].y, 16);
+    if (b8 == 0) {
+      const float2 w = s_tw[255 + m * 16 + low4];
+      const float tr = cx * w.x - cy * w.y;
+      const float ti = cx * w.y + cy * w.x;
+      const float vx = y[m].x + tr, vy = y[m].y + ti;
+      const float a = sqrtf(vx * vx + vy * vy);
+      pw[m * 16 + low4] = a * a;
+      if (m == 0 && lane == 0) {
+        const float ux = y[m].x - tr, uy = y[m].y - ti;
+        const float a2 = sqrtf(ux * ux + uy * uy);
+        pw[256] = a2 * a2;
+      }
+    }
   }
   __syncwarp();
   // ---- mel projection + log ---------------------------------------------------------------------
   for (int f = lane; f < n_mels; f += 32) {
-    const int lo = mel_range[2 * f], hi = mel_range[2 * f + 1];
-    const float* wrow = mel_w + static_cast<long long>(f) * kBins;
+    const int lo = s_mlo[f], hi = s_mhi[f];
     float acc = 0.f;
-    for (int k = lo; k < hi; ++k) acc = fmaf(pw[k], __ldg(wrow + k), acc);
+    if (mel_packed) {
+      const float* wp = s_mw + s_moff[f] - lo;
+      for (int k = lo; k < hi; ++k) acc = fmaf(pw[k], wp[k], acc);
+    } else {
+      const float* wrow = mel_w + static_cast<long long>(f) * kBins;
+      for (int k = lo; k < hi; ++k) acc = fmaf(pw[k], __ldg(wrow + k), acc);
+    }
     const float v = logf(fmaxf(acc, 1.1920928955078125e-07f));
     if (out_bf16) orow_h[f] = __float2bfloat16(v);
     else orow_f[f] = v;
