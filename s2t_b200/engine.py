@@ -825,13 +825,18 @@ class S2TEncoderEngine:
     def _features(self, P: Plan, dst: torch.Tensor, pad: int) -> None:
         """Features (or waveform -> fbank -> utterance CMVN) into a zero-framed bf16 conv input [B][T+2pad][D];
         frames >= src_len zero filled (collater padding, speech_to_text_dataset.py:267-285)."""
-        c = self.cfg
+        self._fbank(P)
+        self._cmvn(P, dst, pad)
+
+    def _fbank(self, P: Plan) -> None:
+        """Waveform input: log-mel features into P.fbank_raw; the kernel also writes the frame counts (P.src_len)."""
         if P.wave is not None:
-            mel_w, rng, win = frontend._tables(str(self.device), c.input_dim)
-            ops.fbank(P.wave, P.num_samples, mel_w, rng, win, P.T, out=P.fbank_raw)
-            src = P.fbank_raw
-        else:
-            src = P.feats_in
+            mel_w, rng, win = frontend._tables(str(self.device), self.cfg.input_dim)
+            ops.fbank(P.wave, P.num_samples, mel_w, rng, win, P.T, out=P.fbank_raw, frames=P.src_len)
+
+    def _cmvn(self, P: Plan, dst: torch.Tensor, pad: int) -> None:
+        c = self.cfg
+        src = P.fbank_raw if P.wave is not None else P.feats_in
         cm = 1 if P.wave is not None else 0
         ops._call("s2t_cmvn_utt", ops._p(src), src.stride(1), src.stride(0), ops._p(dst) + 2 * pad * c.input_dim, 1,
                   dst.stride(1), dst.stride(0), ops._p(P.src_len), P.B, P.T, c.input_dim, cm, cm,
@@ -942,13 +947,14 @@ class S2TEncoderEngine:
         embed_ln -> x * embed_scale (+ sinusoidal positions for abs attention) -> dropout (:1768-1794)."""
         c, S = self.cfg, self.store
         k, st, n = c.subsampling_kernel, c.subsampling_stride, c.subsampling_layers
+        self._fbank(P)
         with self._fork(0):          # integer length bookkeeping beside the feature kernels (joined before the last GLU)
             ln = P.src_len
             for i in range(n):
                 torch.div(ln + (2 * P.pad - k), st, rounding_mode="floor", out=P.sub_len[i])
                 P.sub_len[i] += 1
                 ln = P.sub_len[i]
-        self._features(P, P.framed[0], P.pad)
+        self._cmvn(P, P.framed[0], P.pad)
         for i in range(n):
             xin = P.framed[i]
             cin, cout, t_out = xin.shape[2], self.sub_filters[i], P.t_sub[i + 1]
@@ -1649,10 +1655,8 @@ class S2TEncoderEngine:
         if wave is not None:
             P.wave.copy_(wave, non_blocking=nb)
             P.num_samples.copy_(num_samples, non_blocking=nb)
-            # frames per utterance, snip_edges=True (torchaudio kaldi.fbank): 1 + (n - 400) // 160
-            torch.div(P.num_samples - frontend.FRAME_LEN, frontend.FRAME_SHIFT, rounding_mode="floor", out=P.src_len)
-            P.src_len += 1
-            P.src_len.clamp_(min=0)
+            # frames per utterance, snip_edges=True (torchaudio kaldi.fbank): 1 + (n - 400) // 160 — written into
+            # P.src_len by the fbank kernel at the start of the step (_fbank)
         else:
             P.feats_in.copy_(feats, non_blocking=nb)
             P.src_len.copy_(src_lengths, non_blocking=nb)

@@ -168,13 +168,16 @@ def fbank_num_frames(n: int) -> int:
 
 def fbank(wave: torch.Tensor, num_samples: torch.Tensor, mel_w: torch.Tensor, mel_range: torch.Tensor,
           window: torch.Tensor, max_frames: int, out: Optional[torch.Tensor] = None,
-          out_dtype: torch.dtype = torch.float32) -> Tuple[torch.Tensor, torch.Tensor]:
-    """wave fp32 [B, N] (int16 scale) -> log-mel [B, max_frames, n_mels], frames int32 [B]."""
+          out_dtype: torch.dtype = torch.float32, frames: Optional[torch.Tensor] = None
+          ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """wave fp32 [B, N] (int16 scale) -> log-mel [B, max_frames, n_mels], frames int32 [B]
+    (= min(1 + (n - 400) // 160, max_frames), 0 when n < 400)."""
     B = wave.shape[0]
     n_mels = mel_w.shape[0]
     if out is None:
         out = torch.empty((B, max_frames, n_mels), device=wave.device, dtype=out_dtype)
-    frames = torch.empty((B,), device=wave.device, dtype=torch.int32)
+    if frames is None:
+        frames = torch.empty((B,), device=wave.device, dtype=torch.int32)
     _call("s2t_fbank_fwd", _p(wave), wave.stride(0), _p(num_samples), B, _p(mel_w), _p(mel_range),
           _p(window), n_mels, _p(out), int(out.dtype == BF16), max_frames, out.stride(1), out.stride(0),
           _p(frames), _stream())
