@@ -280,7 +280,7 @@ def run_b200(a):
         eng = S2TEncoderEngine(cfg)
     if world > 1:
         dist.broadcast(eng.store.flat, src=0)                  # same weights on every rank (trainer.py:431)
-        eng.enable_data_parallel(n_buckets=4)
+        eng.enable_data_parallel(n_buckets=int(os.environ.get("S2T_DP_BUCKETS", "4")))
     n_samp = int(a.seconds * SAMPLE_RATE)
     from s2t_b200 import frontend
     T = frontend.num_frames(n_samp)

@@ -22,21 +22,33 @@ import torch
 import torch.distributed as dist
 
 
-def plan_buckets(total: int, cut_points: Sequence[int], n_buckets: int) -> List[Tuple[int, int]]:
+def plan_buckets(total: int, cut_points: Sequence[int], n_buckets: int,
+                 tail_fraction: float = 0.0) -> List[Tuple[int, int]]:
     """Split [0, total) into <= n_buckets contiguous ranges of roughly equal size whose boundaries are taken
     from ``cut_points`` (offsets at which the backward pass reports progress).  Returned in the order the
-    backward pass completes them: from the end of the buffer to the start."""
+    backward pass completes them: from the end of the buffer to the start.
+
+    ``tail_fraction`` > 0 asks for a small LAST bucket [0, c) with c the largest cut point <= tail_fraction * total:
+    that bucket's all-reduce is the only one no backward kernel is left to hide, so it should carry little."""
     cuts = sorted({int(c) for c in cut_points if 0 < int(c) < total})
     n_buckets = max(1, int(n_buckets))
-    target = total / n_buckets
+    lo = 0
+    if tail_fraction > 0.0 and n_buckets > 1:
+        small = [c for c in cuts if c <= tail_fraction * total]
+        if small:
+            lo = small[-1]
+            n_buckets -= 1
+    target = (total - lo) / n_buckets
     bounds = [total]
     hi = total
     for c in reversed(cuts):
-        if len(bounds) >= n_buckets:
+        if len(bounds) >= n_buckets or c <= lo:
             break
         if hi - c >= target:
             bounds.append(c)
             hi = c
+    if lo > 0:
+        bounds.append(lo)
     bounds.append(0)
     out = []
     for i in range(len(bounds) - 1):
@@ -47,11 +59,11 @@ def plan_buckets(total: int, cut_points: Sequence[int], n_buckets: int) -> List[
 
 class BucketedAllReduce:
     def __init__(self, flat_grad: torch.Tensor, cut_points: Sequence[int], n_buckets: int = 4,
-                 group: Optional[dist.ProcessGroup] = None):
+                 group: Optional[dist.ProcessGroup] = None, tail_fraction: float = 0.0):
         self.flat = flat_grad
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
-        self.buckets = plan_buckets(flat_grad.numel(), cut_points, n_buckets)
+        self.buckets = plan_buckets(flat_grad.numel(), cut_points, n_buckets, tail_fraction)
         self.next = 0
         self.works: list = []
         self.launched: List[Tuple[int, int]] = []

@@ -1682,7 +1682,7 @@ class S2TEncoderEngine:
         if self.dp is not None:
             self.dp.finish()
 
-    def enable_data_parallel(self, n_buckets: int = 4, group=None) -> None:
+    def enable_data_parallel(self, n_buckets: int = 4, group=None, tail_fraction: Optional[float] = None) -> None:
         """Bucketed gradient all-reduce overlapped with backward (dp.py); cut points = the offsets at which the
         backward pass reports progress (start of every layer / block in the flat gradient buffer)."""
         from .dp import BucketedAllReduce
@@ -1692,7 +1692,9 @@ class S2TEncoderEngine:
         cuts = [S.offset(n) for n in S.names()
                 if n in firsts or n in ("layer_norm.weight", "ctc.ctc_projection.weight", "embed_ln.weight")
                 or (n.startswith("subsample.") and n.endswith("weight")) or n.endswith("conv.0.weight")]
-        self.dp = BucketedAllReduce(S.grad, cuts, n_buckets, group)
+        if tail_fraction is None:
+            tail_fraction = float(os.environ.get("S2T_DP_TAIL", "0.12"))
+        self.dp = BucketedAllReduce(S.grad, cuts, n_buckets, group, tail_fraction)
         self.grad_ready_hook = self.dp.on_ready
 
     def capture(self, P: Plan, kind: str = "train") -> None:
