@@ -184,8 +184,13 @@ def gemm_roofline(torch, eng, P, peaks, replays: int = 20):
     calls = []
     orig = ops.gemm_raw
 
+    main_stream = torch.cuda.current_stream()
+
     def rec(**kw):
-        calls.append(kw)
+        kw = dict(kw)
+        if not kw.get("max_ctas"):
+            kw["max_ctas"] = ops._default_max_ctas      # the SM share in force at this point of the step
+        calls.append((kw, torch.cuda.current_stream() != main_stream))
         orig(**kw)
 
     ops.gemm_raw = rec
@@ -201,17 +206,30 @@ def gemm_roofline(torch, eng, P, peaks, replays: int = 20):
         eng.dp, eng.grad_ready_hook = dp, hook
     torch.cuda.synchronize()
     step_ms = e_all0.elapsed_time(e_all1)
-    fl = sum(2.0 * kw["M"] * kw["N"] * kw["K"] * kw.get("batch", (1, 1))[0] * kw.get("batch", (1, 1))[1] for kw in calls)
+    fl = sum(2.0 * kw["M"] * kw["N"] * kw["K"] * kw.get("batch", (1, 1))[0] * kw.get("batch", (1, 1))[1] for kw, _ in calls)
+    n_side = sum(1 for _, s_ in calls if s_)
     side = torch.cuda.Stream()
+    side2 = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
     g = torch.cuda.CUDAGraph()
+
+    def issue():
+        # chain launches on one stream, the launches the step puts on side streams (weight gradients, dV/dK) on a second
+        # one beside them — the configuration their SM shares (100 + 48 CTAs) are sized for
+        side2.wait_stream(side)
+        for kw, on_side in calls:
+            if on_side:
+                with torch.cuda.stream(side2):
+                    orig(**kw)
+            else:
+                orig(**kw)
+        side.wait_stream(side2)
+
     with torch.cuda.stream(side):
-        for kw in calls:
-            orig(**kw)
+        issue()
         torch.cuda.synchronize()
         with torch.cuda.graph(g, stream=side):
-            for kw in calls:
-                orig(**kw)
+            issue()
         for _ in range(3):
             g.replay()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -228,7 +246,7 @@ def gemm_roofline(torch, eng, P, peaks, replays: int = 20):
     # ncu measured for the same launches (profiles/gemm_traffic.json, committed with the launch list it was taken from)
     esz = lambda t: t.element_size() if t is not None else 2
     alg = 0.0
-    for kw in calls:
+    for kw, _ in calls:
         nb = kw.get("batch", (1, 1))
         z = nb[0] * nb[1]
         alg += z * (kw["M"] * kw["K"] * 2 + kw["N"] * kw["K"] * 2 + kw["M"] * kw["N"] * esz(kw.get("out")))
@@ -245,7 +263,10 @@ def gemm_roofline(torch, eng, P, peaks, replays: int = 20):
             "algorithmic_bytes_per_launch": alg / n,
             "launches_per_step": n, "avg_launch_us": 1e3 * ms / n, "gemm_ms_per_step": ms, "eager_step_ms": step_ms,
             "flop_per_step": fl,
-            "how": f"the step's {n} GEMM launches captured alone into one CUDA graph, {replays} replays between CUDA events",
+            "side_stream_launches": n_side,
+            "how": f"the step's {n} GEMM launches captured alone into one CUDA graph ({n - n_side} chain launches on one "
+                   f"stream, the {n_side} side-stream launches of the step on a second stream beside them, same SM shares "
+                   f"as in the step), {replays} replays between CUDA events",
             "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained"}
 
 
