@@ -574,6 +574,7 @@ class S2TEncoderEngine:
         # SM partition of the backward pass: (chain GEMM CTAs, weight-gradient GEMM CTAs, weight-gradient split-K policy);
         # measured on B200 (148 SMs): 100 + 48 without split-K, 2.14 -> 1.94 ms/step (ops.set_sm_shares)
         self.sm_shares = tuple(int(v) for v in os.environ.get("S2T_SM_SHARES", "100,48,-1").split(","))
+        self.fwd_share = 0       # SM bound of forward GEMMs (0 = whole GPU; MicroBatchEngine splits the GPU between groups)
         self._ln_stream = torch.cuda.Stream(device=self.device)   # LayerNorm dgamma/dbeta reductions (_ln_bwd)
         self._ln_pending = False
         self._forked: set = set()
@@ -1150,6 +1151,13 @@ class S2TEncoderEngine:
                          residual=res, ldr=C)
 
     def _forward(self, P: Plan) -> None:
+        prev = ops.set_sm_shares(self.fwd_share, 0, 0)
+        try:
+            self._forward_body(P)
+        finally:
+            ops.set_sm_shares(*prev)
+
+    def _forward_body(self, P: Plan) -> None:
         g = 0
         for i, St in enumerate(P.stages):
             if self.cfg.encoder_type == "s2t" and self.cfg.subsampling_type == "conv2d":

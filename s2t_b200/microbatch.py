@@ -53,6 +53,18 @@ class MicroBatchEngine:
         for i, e in enumerate(self.engines[1:], 1):
             e.store.flat = e0.store.flat           # ONE parameter buffer; gradients stay per engine until the join
             e.SEED = e0.SEED + 7919 * i            # independent dropout masks per group
+        if n_micro > 1:
+            # every group gets its share of the SMs (a GEMM CTA needs a whole SM: unbounded GEMMs of two groups would
+            # serialise): forward GEMMs, backward chain GEMMs, backward weight-gradient GEMMs
+            import os
+            sh = os.environ.get("S2T_MICRO_SHARES", "")
+            if sh:
+                f, c_, w = (int(v) for v in sh.split(","))
+            else:
+                f, c_, w = 148 // n_micro, 100 // n_micro, 48 // n_micro
+            for e in self.engines:
+                e.fwd_share = f
+                e.sm_shares = (c_, w, -1)
         self.device = e0.device
         self.store = e0.store
         self.streams = [torch.cuda.Stream(device=self.device) for _ in range(n_micro - 1)]
