@@ -235,6 +235,17 @@ int s2t_col2im2d(const void* dcol, void* dx, int batch, int T, int D, int Cin, i
  * batch statistics s2t_batchnorm_fwd consumes (BatchNorm2d over (B, D', T') == BatchNorm1d over the rows)   */
 int s2t_colstats_parts(long long rows);
 int s2t_colstats(const void* x, float* partials, long long rows, int C, void* stream);
+/* SpecAugment masks applied on device, in place, to a padded feature batch [batch][max_frames][ld] (fp32 or bf16).    *
+ * Replaces the apply half of fairseq/data/audio/feature_transforms/specaugment.py:80-131 (CPU numpy per utterance);   *
+ * the random draws stay on the host in the reference's numpy order (s2t_b200/specaugment.py).                         *
+ * freq_masks int32 [batch][n_freq_masks][2] = (f0, f): columns [f0, f0+f) of every frame < num_frames[b];            *
+ * time_masks int32 [batch][n_time_masks][2] = (t0, t): frames [t0, t0+t); width 0 = no mask.                          *
+ * Fill value = mask_value, or with use_mean the mean of the utterance's valid (frames x n_freqs) block computed on   *
+ * the device BEFORE masking (means = fp32 [batch * 32] scratch of partial sums; the reference's mask_value=None,     *
+ * :88-89).                                                                                                           */
+int s2t_specaugment(void* feats, int is_bf16, long long ld, long long bs, const int* num_frames, int batch,
+                    int max_frames, int n_freqs, const int* freq_masks, int n_freq_masks, const int* time_masks,
+                    int n_time_masks, float mask_value, int use_mean, float* means, void* stream);
 /* *counter += inc on the device (dropout seed counter of a captured step)                         */
 int s2t_counter_add(unsigned long long* counter, unsigned long long inc, void* stream);
 /* y += x, bf16 [n], n % 8 == 0                                                                    */

@@ -273,6 +273,8 @@ class Plan:
         self.num_samples = z(B, dt=torch.int32) if wave_len else None
         self.fbank_raw = e(B, T, c.input_dim, dt=F32) if wave_len else None
         self.cmvn_stats = e(B, 2, c.input_dim, dt=F32) if wave_len else None
+        self.sa_freq = self.sa_time = None      # SpecAugment masks of the current batch (set_inputs), int32 [B, N, 2]
+        self.sa_means = z(B * 32, dt=F32)       # s2t_specaugment scratch (partial sums of the utterance mean)
         self.src_len = z(B, dt=torch.int32)
         self.targets = z(B, max(smax, 1), dt=torch.int32)
         self.tgt_len = z(B, dt=torch.int32)
@@ -574,6 +576,7 @@ class S2TEncoderEngine:
         # SM partition of the backward pass: (chain GEMM CTAs, weight-gradient GEMM CTAs, weight-gradient split-K policy);
         # measured on B200 (148 SMs): 100 + 48 without split-K, 2.14 -> 1.94 ms/step (ops.set_sm_shares)
         self.sm_shares = tuple(int(v) for v in os.environ.get("S2T_SM_SHARES", "100,48,-1").split(","))
+        self.specaug = None      # specaugment.SpecAugmentConfig: masks given to set_inputs are applied after CMVN (training)
         self.fwd_share = 0       # SM bound of forward GEMMs (0 = whole GPU; MicroBatchEngine splits the GPU between groups)
         self._ln_stream = torch.cuda.Stream(device=self.device)   # LayerNorm dgamma/dbeta reductions (_ln_bwd)
         self._ln_pending = False
@@ -842,6 +845,10 @@ class S2TEncoderEngine:
         ops._call("s2t_cmvn_utt", ops._p(src), src.stride(1), src.stride(0), ops._p(dst) + 2 * pad * c.input_dim, 1,
                   dst.stride(1), dst.stride(0), ops._p(P.src_len), P.B, P.T, c.input_dim, cm, cm,
                   ops._p(P.cmvn_stats), ops._stream())
+        if self.specaug is not None and self.training and (P.sa_freq is not None or P.sa_time is not None):
+            # SpecAugment on the CMVN output (the reference's _train transform order: utterance_cmvn, specaugment)
+            ops.specaugment_(dst.view(P.B, -1, c.input_dim)[:, pad:pad + P.T], P.src_len, P.sa_freq, P.sa_time, self.specaug.mask_value,
+                             c.input_dim, P.sa_means)
 
     def _embed_block_fwd(self, P: Plan) -> None:
         """embed_ln -> x * embed_scale (+ sinusoidal positions for abs attention) -> dropout (s2t_transformer.py:1768-1794)."""
@@ -1656,10 +1663,18 @@ class S2TEncoderEngine:
     def set_inputs(self, P: Plan, *, feats: Optional[torch.Tensor] = None, src_lengths: Optional[torch.Tensor] = None,
                    wave: Optional[torch.Tensor] = None, num_samples: Optional[torch.Tensor] = None,
                    targets: Optional[torch.Tensor] = None, target_lengths: Optional[torch.Tensor] = None,
-                   xtargets: Optional[torch.Tensor] = None, xtarget_lengths: Optional[torch.Tensor] = None) -> None:
+                   xtargets: Optional[torch.Tensor] = None, xtarget_lengths: Optional[torch.Tensor] = None,
+                   sa_freq: Optional[torch.Tensor] = None, sa_time: Optional[torch.Tensor] = None) -> None:
         """Copy one batch into the plan's static input buffers (async on the current stream; host tensors
-        should be pinned).  feats fp32 [B, T, D] + src_lengths, or wave fp32 [B, N] (int16 scale) + num_samples."""
+        should be pinned).  feats fp32 [B, T, D] + src_lengths, or wave fp32 [B, N] (int16 scale) + num_samples.
+        sa_freq / sa_time: SpecAugment masks of this batch (specaugment.draw_masks), used when ``engine.specaug`` is set;
+        their shapes are fixed by the first call (static buffers of a captured step)."""
         nb = True
+        for name, m in (("sa_freq", sa_freq), ("sa_time", sa_time)):
+            if m is not None and m.shape[1] > 0:
+                if getattr(P, name) is None:
+                    setattr(P, name, torch.zeros(m.shape, dtype=torch.int32, device=self.device))
+                getattr(P, name).copy_(m, non_blocking=nb)
         if wave is not None:
             P.wave.copy_(wave, non_blocking=nb)
             P.num_samples.copy_(num_samples, non_blocking=nb)

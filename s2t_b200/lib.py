@@ -68,6 +68,7 @@ SIGNATURES = {
     "s2t_col2im2d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2t_colstats_parts": (_i, [_ll]),
     "s2t_colstats": (_i, [_vp, _vp, _ll, _i, _vp]),
+    "s2t_specaugment": (_i, [_vp, _i, _ll, _ll, _vp, _i, _i, _i, _vp, _i, _vp, _i, _f, _i, _vp, _vp]),
     "s2t_counter_add": (_i, [_vp, _ull, _vp]),
     "s2t_add_bf16": (_i, [_vp, _vp, _ll, _vp]),
     "s2t_f32_sum": (_i, [_vp, _i, _f, _vp, _vp]),

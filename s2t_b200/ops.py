@@ -623,3 +623,24 @@ def ctc_greedy(logits: torch.Tensor, input_lengths: torch.Tensor, V: int, blank:
     if with_scores:
         return tokens, lens, frame_ids, scores
     return tokens, lens, frame_ids
+
+
+# --------------------------------------------------------------------------------------------------
+# SpecAugment (apply half; the draws are host-side, s2t_b200/specaugment.py)
+# --------------------------------------------------------------------------------------------------
+def specaugment_(feats: torch.Tensor, num_frames: torch.Tensor, freq_masks: Optional[torch.Tensor],
+                 time_masks: Optional[torch.Tensor], mask_value: Optional[float] = 0.0, n_freqs: Optional[int] = None,
+                 means: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """In place on feats [B, T, ld] (fp32 or bf16, last dim contiguous): freq_masks int32 [B, Nf, 2] = (f0, f),
+    time_masks int32 [B, Nt, 2] = (t0, t); ``mask_value=None`` fills with the utterance mean (specaugment.py:88-89)."""
+    B, T, ld = feats.shape
+    assert feats.stride(2) == 1 and feats.dtype in (torch.float32, BF16)
+    nfm = 0 if freq_masks is None else freq_masks.shape[1]
+    ntm = 0 if time_masks is None else time_masks.shape[1]
+    use_mean = mask_value is None
+    if use_mean and means is None:
+        means = torch.empty((B * 32,), device=feats.device, dtype=torch.float32)      # partial sums (scratch)
+    _call("s2t_specaugment", _p(feats), int(feats.dtype == BF16), feats.stride(1), feats.stride(0), _p(num_frames), B, T,
+          n_freqs if n_freqs is not None else ld, _p(freq_masks), nfm, _p(time_masks), ntm,
+          0.0 if use_mean else float(mask_value), int(use_mean), _p(means), _stream())
+    return feats
