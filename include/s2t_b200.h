@@ -235,6 +235,17 @@ int s2t_col2im2d(const void* dcol, void* dx, int batch, int T, int D, int Cin, i
  * batch statistics s2t_batchnorm_fwd consumes (BatchNorm2d over (B, D', T') == BatchNorm1d over the rows)   */
 int s2t_colstats_parts(long long rows);
 int s2t_colstats(const void* x, float* partials, long long rows, int C, void* stream);
+/* CTC best alignment (Viterbi): replaces torch_imputer.best_alignment (fairseq/torch_imputer/best_alignment.cu:62-201  *
+ * + the host backtrack of imputer.py:245-259,282-325).  log_probs fp32, element (b, t, v) at b*lp_b_stride +           *
+ * t*lp_t_stride + v; targets int32 [batch][tgt_ld]; states int32 [batch][T]: the lattice state (0..2S) of every frame  *
+ * < input_lengths[b], -1 beyond; nll fp32 [batch] or NULL (-logsumexp of the two final states of the max-recursion, as  *
+ * the reference kernel returns).  workspace: s2t_ctc_viterbi_workspace_bytes() bytes (0 when the back-pointers fit in   *
+ * shared memory).                                                                                                     */
+long long s2t_ctc_viterbi_workspace_bytes(int batch, int T, int max_target_len);
+int s2t_ctc_viterbi(const float* log_probs, long long lp_t_stride, long long lp_b_stride, const int* targets,
+                    long long tgt_ld, const int* input_lengths, const int* target_lengths, int batch, int T, int V,
+                    int max_target_len, int blank, int* states, float* nll, void* workspace, long long workspace_bytes,
+                    void* stream);
 /* SpecAugment masks applied on device, in place, to a padded feature batch [batch][max_frames][ld] (fp32 or bf16).    *
  * Replaces the apply half of fairseq/data/audio/feature_transforms/specaugment.py:80-131 (CPU numpy per utterance);   *
  * the random draws stay on the host in the reference's numpy order (s2t_b200/specaugment.py).                         *

@@ -644,3 +644,29 @@ def specaugment_(feats: torch.Tensor, num_frames: torch.Tensor, freq_masks: Opti
           n_freqs if n_freqs is not None else ld, _p(freq_masks), nfm, _p(time_masks), ntm,
           0.0 if use_mean else float(mask_value), int(use_mean), _p(means), _stream())
     return feats
+
+
+# --------------------------------------------------------------------------------------------------
+# CTC best alignment (Viterbi)
+# --------------------------------------------------------------------------------------------------
+def ctc_viterbi(log_probs: torch.Tensor, targets: torch.Tensor, input_lengths: torch.Tensor,
+                target_lengths: torch.Tensor, blank: int = 0, batch_first: bool = True,
+                with_nll: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """torch_imputer.best_alignment on device, backtrack included: log_probs fp32 [B, T, V] (or [T, B, V] with
+    ``batch_first=False``, the reference's layout), targets int32 [B, S]; returns int32 states [B, T] (-1 beyond the
+    utterance) and the fp32 nll [B] of the max-recursion."""
+    assert log_probs.dtype == torch.float32 and log_probs.stride(2) == 1
+    if batch_first:
+        B, T, V = log_probs.shape
+        ts, bs = log_probs.stride(1), log_probs.stride(0)
+    else:
+        T, B, V = log_probs.shape
+        ts, bs = log_probs.stride(0), log_probs.stride(1)
+    smax = targets.shape[1]
+    states = torch.empty((B, T), device=log_probs.device, dtype=torch.int32)
+    nll = torch.empty((B,), device=log_probs.device, dtype=torch.float32) if with_nll else None
+    need = _lib.load().s2t_ctc_viterbi_workspace_bytes(B, T, smax)
+    ws = torch.empty((need,), device=log_probs.device, dtype=torch.uint8) if need else None
+    _call("s2t_ctc_viterbi", _p(log_probs), ts, bs, _p(targets), targets.stride(0), _p(input_lengths),
+          _p(target_lengths), B, T, V, smax, blank, _p(states), _p(nll), _p(ws), need, _stream())
+    return states, nll
