@@ -62,6 +62,29 @@ def test_plan_buckets_cover_the_buffer_in_backward_order():
     assert plan_buckets(10, [5], 1) == [(0, 10)]
 
 
+def test_plan_buckets_small_tail_and_would_ship():
+    """tail_fraction: the LAST bucket (lowest offsets, finished when no backward kernel is left to hide its all-reduce)
+    is the largest cut at or below the fraction; the rest is split evenly.  would_ship mirrors on_ready."""
+    import torch
+    from s2t_b200.dp import BucketedAllReduce, plan_buckets
+    cuts = list(range(50, 1000, 50))
+    b = plan_buckets(1000, cuts, 4, tail_fraction=0.12)
+    assert b[-1] == (0, 100) and len(b) == 4 and b[0][1] == 1000
+    assert sum(hi - lo for lo, hi in b) == 1000
+    sizes = [hi - lo for lo, hi in b[:-1]]
+    assert max(sizes) - min(sizes) <= 50
+    assert plan_buckets(1000, cuts, 4, tail_fraction=0.01) == plan_buckets(1000, cuts, 4)     # no cut that small
+    assert plan_buckets(1000, cuts, 1, tail_fraction=0.12) == [(0, 1000)]
+    dp = BucketedAllReduce(torch.zeros(1000), cuts, 4, None, 0.12)
+    assert not dp.would_ship(900)                       # first bucket starts below 900
+    first_lo = dp.buckets[0][0]
+    assert dp.would_ship(first_lo)
+    dp.on_ready(first_lo)
+    assert dp.launched == [dp.buckets[0]] and not dp.would_ship(first_lo)
+    dp.finish()
+    assert dp.launched == dp.buckets
+
+
 def test_param_store_layout_and_fused_views():
     from s2t_b200.params import ParamStore
     S = ParamStore(torch.device("cpu"))
