@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define S2T_ABI_VERSION 3
+#define S2T_ABI_VERSION 4
 
 /* status / introspection ---------------------------------------------------------------------- */
 const char* s2t_last_error(void);
@@ -373,7 +373,9 @@ int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, const float* ls
                  const int* targets, long long tgt_ld, const int* input_lengths,
                  const int* target_lengths, int batch, int T, int V, int max_target_len, int blank,
                  float* nll, void* dlogits /*same dtype and layout as logits, or NULL*/,
-                 float grad_scale, void* workspace, long long workspace_bytes, void* stream);
+                 float grad_scale, const float* grad_scale_dev /*optional device scalar multiplied into
+                 grad_scale (0 = zero-weight dummy batch, trainer.py:687-691), or NULL*/,
+                 void* workspace, long long workspace_bytes, void* stream);
 /*
  * Greedy CTC: argmax over V (lowest index on ties), padded frames -> blank, collapse repeats,
  * drop blank.  tokens int32 [B][T] (first out_lengths[b] valid, rest -1); frame_ids int32 [B][T]
@@ -384,6 +386,17 @@ int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, const float* ls
 int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, const int* input_lengths,
                    int batch, int T, int V, int blank, int* tokens, int* out_lengths,
                    int* frame_ids, float* scores, float* frame_lp, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
+/* Length-bucketed batching for the data-parallel path (host only, no device work).               */
+/* Replaces fairseq/data/data_utils_fast.pyx:20-103 batch_by_size_vec (behind                      */
+/* FairseqDataset.batch_by_size, --max-tokens / --required-batch-size-multiple).                   */
+/* num_tokens[i] = length of the i-th utterance of the ORDERED list (speech_to_text_dataset.py:    */
+/* 505-512); limits <= 0 are off.  Writes the exclusive end position of every batch to             */
+/* batch_ends (room for n + 1 entries) and returns the number of batches (-1 on error).            */
+/* --------------------------------------------------------------------------------------------- */
+long long s2t_batch_by_size(const long long* num_tokens, long long n, long long max_tokens,
+                            long long max_sentences, int bsz_mult, long long* batch_ends);
 
 #ifdef __cplusplus
 }

@@ -134,6 +134,44 @@ GRAD_KEYS = ["pae.embed_adapter.weight", "xctc_pae.embed_adapter.weight", "xctc.
              "layer_norm.weight", "ctc.ctc_projection.weight"]
 
 
+def build_reference_encoder(cfg, pds: bool = False):
+    """The reference's own encoder class (unmodified files through oracle/ref_shim.py) for an ``OracleConfig`` — the
+    inverse of ``oracle.encoder.config_from_args``.  Used by ``bench.py --impl reference`` when the reference tree is
+    available (``S2T_REFERENCE``: /root/reference here, baseline/_ref on the GPU box)."""
+    from oracle import ref_shim
+    ref = ref_shim.load()
+    us = lambda t: "_".join(str(int(v)) for v in t)
+    cs = lambda t: ",".join(str(int(v)) for v in t) if t else None
+    over = dict(
+        encoder_layers=cfg.layers, encoder_embed_dim=cfg.embed_dim, encoder_ffn_embed_dim=cfg.ffn_dim,
+        encoder_attention_heads=cfg.heads, subsampling_type=cfg.subsampling_type, subsampling_layers=cfg.subsampling_layers,
+        subsampling_filter=cfg.subsampling_filter, subsampling_kernel=cfg.subsampling_kernel,
+        subsampling_stride=cfg.subsampling_stride, subsampling_norm=cfg.subsampling_norm,
+        subsampling_activation=cfg.subsampling_activation, encoder_attention_type=cfg.attn_type,
+        macaron_style=cfg.macaron_style, use_cnn_module=cfg.use_cnn_module, cnn_module_kernel=cfg.cnn_module_kernel,
+        encoder_activation_fn=cfg.encoder_activation_fn, activation_fn=cfg.activation_fn,
+        layer_padding_mask=cfg.layer_padding_mask, dropout=cfg.dropout, vocab=cfg.vocab)
+    if cfg.tgt_vocab > 0 or cfg.inter_ctc_layers:
+        over.update(xctc_weight=0.1 if cfg.tgt_vocab > 0 else 0.0, inter_ctc_weight=0.1 if cfg.inter_ctc_layers else 0.0,
+                    inter_ctc_layers=cs(cfg.inter_ctc_layers), share_inter_ctc=cfg.share_inter_ctc,
+                    inter_xctc_weight=0.05 if cfg.inter_xctc_layers else 0.0, inter_xctc_layers=cs(cfg.inter_xctc_layers),
+                    ctc_pae=cfg.ctc_pae, xctc_pae=cfg.xctc_pae, pae_unnorm_input=cfg.pae_unnorm_input)
+    if pds:
+        n = len(cfg.pds_layers)
+        over.update(pds_stages=n, pds_layers=us(cfg.pds_layers), pds_ratios=us(cfg.pds_ratios), pds_fusion=False,
+                    pds_embed_dims=us(cfg.pds_dims), pds_kernel_sizes=us(cfg.pds_kernels),
+                    pds_ffn_ratios=us(cfg.pds_ffn_ratios), pds_attn_heads=us(cfg.pds_heads),
+                    pds_position_embed=us(cfg.pds_position_embed), pds_embed_norm=cfg.pds_embed_norm,
+                    pds_ds_method="conv", pds_attn_ds_ratios=us([1] * n), pds_dropout=cfg.pds_dropout)
+    args = reference_args(**over)
+    task = ref.FakeTask(cfg.vocab, cfg.tgt_vocab or cfg.vocab)
+    if pds:
+        ref.pds.pdss2t_transformer_s_8(args)
+        return ref.pds.PDSS2TTransformerEncoder(args, task, None)
+    ref.s2t.s2t_transformer_s(args)
+    return ref.s2t.S2TTransformerEncoder(args, task, None)
+
+
 def run_reference_encoder(case: str, seed: int = 0):
     from oracle import encoder as OE
     from oracle import ref_shim

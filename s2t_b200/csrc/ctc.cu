@@ -21,6 +21,8 @@
 //   ctc_occupancy      dlogits[b][t][l'_s] -= scale * gamma_t(s), duplicates of a label merged in smem
 //   argmax / collapse  greedy decode
 #include "common.cuh"
+
+#include <mutex>
 #include <stdlib.h>
 
 #include <math.h>
@@ -508,8 +510,9 @@ __global__ void __launch_bounds__(256)
 ctc_dense_grad_kernel(const void* __restrict__ logits, int is_bf16, long long ldv,
                       const float* __restrict__ lse, const int* __restrict__ in_len, int T, int V,
                       const float* __restrict__ nll_raw, float* __restrict__ nll_out,
-                      void* __restrict__ dlogits, float scale) {
+                      void* __restrict__ dlogits, float scale, const float* __restrict__ scale_mul) {
   pdl_entry();
+  if (scale_mul != nullptr) scale *= *scale_mul;   // device-side batch weight (0 for a data-parallel dummy batch)
   const long long row = blockIdx.x;
   const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
   // nll_raw == nullptr: launched beside the lattice kernel (s2t_ctc_loss); the occupancy kernel then publishes nll and
@@ -549,8 +552,9 @@ __global__ void ctc_occupancy_kernel(const int* __restrict__ targets, long long 
                                      const int* __restrict__ in_len, const int* __restrict__ tgt_len,
                                      int T, int Sp, int V, int blank, CtcWs ws, int is_bf16,
                                      long long ldv, void* __restrict__ dlogits, float scale,
-                                     float* __restrict__ nll_out) {
+                                     const float* __restrict__ scale_mul, float* __restrict__ nll_out) {
   pdl_entry();
+  if (scale_mul != nullptr) scale *= *scale_mul;
   extern __shared__ float s_occ[];  // [Sp]
   const int t = blockIdx.x, b = blockIdx.y;
   const float nr = ws.nll_raw[b];
@@ -589,12 +593,16 @@ __global__ void ctc_occupancy_kernel(const int* __restrict__ targets, long long 
     int l = ext_label(tgt, s, blank);
     l = min(max(l, 0), V - 1);
     const long long idx = row * ldv + l;
+    // lp_g of the leader state = logit - lse of this label: recompute softmax - occupancy in fp32 and round ONCE
+    // (a read-modify-write of the already rounded scale * softmax loses the difference where p and occ nearly cancel,
+    // i.e. on the label frames of a trained model)
+    const float pr = __expf(ws.lp_g[base + s]);
     if (is_bf16) {
       __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(dlogits);
-      o[idx] = __float2bfloat16(__bfloat162float(o[idx]) - scale * occ);
+      o[idx] = __float2bfloat16(scale * (pr - occ));
     } else {
       float* o = reinterpret_cast<float*>(dlogits);
-      o[idx] -= scale * occ;
+      o[idx] = scale * (pr - occ);
     }
   }
 }
@@ -736,8 +744,9 @@ extern "C" long long s2t_ctc_workspace_bytes(int batch, int T, int max_target_le
 extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, const float* lse,
                             const int* targets, long long tgt_ld, const int* input_lengths,
                             const int* target_lengths, int batch, int T, int V, int max_target_len,
-                            int blank, float* nll, void* dlogits, float grad_scale, void* workspace,
-                            long long workspace_bytes, void* stream) {
+                            int blank, float* nll, void* dlogits, float grad_scale,
+                            const float* grad_scale_dev, void* workspace, long long workspace_bytes,
+                            void* stream) {
   S2T_REQUIRE(logits && lse && targets && input_lengths && target_lengths && workspace,
               "s2t_ctc_loss: null pointer");
   S2T_REQUIRE(nll != nullptr, "s2t_ctc_loss: nll output required");
@@ -767,19 +776,31 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
   // With a gradient wanted, scale * softmax (one pass over the [B*T, V] logits, every SM) runs on an internal side
   // stream beside gather + lattice (a handful of warps, ~T dependent steps); the occupancy pass joins the two.
   // Event fork / join: also legal while `st` is being captured into a CUDA graph.
-  static cudaStream_t side = nullptr;
-  static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // (one side stream + event pair per device, created on first use under a lock)
+  struct Side { cudaStream_t side = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr; };
+  static Side sides[64];
+  static std::mutex side_mu;
   const bool overlap = dlogits != nullptr;
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   if (overlap) {
-    if (side == nullptr) {
-      S2T_CHECK_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
-      S2T_CHECK_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-      S2T_CHECK_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+    int dev = 0;
+    S2T_CHECK_CUDA(cudaGetDevice(&dev));
+    S2T_REQUIRE(dev >= 0 && dev < 64, "s2t_ctc_loss: device index %d out of range", dev);
+    {
+      std::lock_guard<std::mutex> lk(side_mu);
+      Side& sd = sides[dev];
+      if (sd.side == nullptr) {
+        S2T_CHECK_CUDA(cudaStreamCreateWithFlags(&sd.side, cudaStreamNonBlocking));
+        S2T_CHECK_CUDA(cudaEventCreateWithFlags(&sd.ev_fork, cudaEventDisableTiming));
+        S2T_CHECK_CUDA(cudaEventCreateWithFlags(&sd.ev_join, cudaEventDisableTiming));
+      }
+      side = sd.side; ev_fork = sd.ev_fork; ev_join = sd.ev_join;
     }
     S2T_CHECK_CUDA(cudaEventRecord(ev_fork, st));
     S2T_CHECK_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
     S2T_LAUNCH(ctc_dense_grad_kernel, batch * T, 256, 0, side, logits, is_bf16, ldv, lse, input_lengths, T, V,
-               static_cast<const float*>(nullptr), static_cast<float*>(nullptr), dlogits, grad_scale);
+               static_cast<const float*>(nullptr), static_cast<float*>(nullptr), dlogits, grad_scale, grad_scale_dev);
     S2T_LAUNCH_CHECK();
     S2T_CHECK_CUDA(cudaEventRecord(ev_join, side));
   }
@@ -823,13 +844,13 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
     S2T_LAUNCH_CHECK();
   }
   if (!overlap) {   // loss only: publish nll (zero_infinity applied)
-    S2T_LAUNCH(ctc_dense_grad_kernel, batch * T, 256, 0, st, logits, is_bf16, ldv, lse, input_lengths, T, V, ws.nll_raw, nll, dlogits, grad_scale);
+    S2T_LAUNCH(ctc_dense_grad_kernel, batch * T, 256, 0, st, logits, is_bf16, ldv, lse, input_lengths, T, V, ws.nll_raw, nll, dlogits, grad_scale, grad_scale_dev);
     S2T_LAUNCH_CHECK();
   } else {
     S2T_CHECK_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
     int othreads = ((Sp + 31) / 32) * 32;
     if (othreads > 256) othreads = 256;
-    S2T_LAUNCH(ctc_occupancy_kernel, dim3(T, batch), othreads, sizeof(float) * Sp, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, V, blank, ws, is_bf16, ldv, dlogits, grad_scale, nll);
+    S2T_LAUNCH(ctc_occupancy_kernel, dim3(T, batch), othreads, sizeof(float) * Sp, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, V, blank, ws, is_bf16, ldv, dlogits, grad_scale, grad_scale_dev, nll);
     S2T_LAUNCH_CHECK();
   }
   return 0;

@@ -276,6 +276,9 @@ class Plan:
         self.sa_freq = self.sa_time = None      # SpecAugment masks of the current batch (set_inputs), int32 [B, N, 2]
         self.sa_means = z(B * 32, dt=F32)       # s2t_specaugment scratch (partial sums of the utterance mean)
         self.src_len = z(B, dt=torch.int32)
+        # weight of this batch in the gradient (1 = real batch, 0 = the zero-weight dummy batch a data-parallel rank
+        # runs when it has no batch left, trainer.py:1045-1058,687-691); a device scalar so that one captured graph serves both
+        self.batch_weight = torch.ones(1, device=dev, dtype=F32)
         self.targets = z(B, max(smax, 1), dt=torch.int32)
         self.tgt_len = z(B, dt=torch.int32)
         drop = c.dropout > 0
@@ -455,6 +458,7 @@ class Plan:
                     I.xout = cur
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.graph_kind: Optional[str] = None
+        self.nbytes = 0
 
     @property
     def out_len(self) -> torch.Tensor:
@@ -565,7 +569,9 @@ class S2TEncoderEngine:
         self.embed_scale = 1.0 if (c.no_scale_embedding or c.encoder_type == "pds") else math.sqrt(C)  # quirk A17
         self.pos_tables: Dict[int, torch.Tensor] = {}
         self.step_counter = torch.zeros(1, device=self.device, dtype=torch.int64)
-        self.plans: Dict[Tuple[int, int, int, int], Plan] = {}
+        self.plans: Dict[Tuple[int, int, int, int], Plan] = {}      # insertion order = recency (plan())
+        self.plan_cache_bytes = int(float(os.environ.get("S2T_PLAN_CACHE_GB", "48")) * 2 ** 30)
+        self.plan_builds = self.plan_evictions = 0
         self.training = True
         self.grad_ready_hook = None  # callable(offset): store.grad[offset:] is final (dp.BucketedAllReduce.on_ready)
         # fork/join streams: leaf work of the backward pass (weight / bias gradients) and independent attention
@@ -811,10 +817,32 @@ class S2TEncoderEngine:
     # plans
     # ------------------------------------------------------------------------------------------
     def plan(self, B: int, T: int, smax: int = 0, wave_len: int = 0) -> Plan:
+        """The plan of one (batch, frames, max target length, samples) bucket, from an LRU cache bounded in bytes
+        (``plan_cache_bytes``, default 48 GiB or S2T_PLAN_CACHE_GB): under max-tokens batching every new (B, T) would
+        otherwise pin 0.5-2.3 GB of activations plus a captured graph for ever.  Callers quantise (B, T) with
+        ``batching.BucketSet`` so that the cache sees a small fixed set of keys."""
         key = (B, T, smax, wave_len)
-        if key not in self.plans:
-            self.plans[key] = Plan(self, B, T, smax, wave_len)
-        return self.plans[key]
+        P = self.plans.pop(key, None)
+        if P is None:
+            before = torch.cuda.memory_allocated(self.device)
+            P = Plan(self, B, T, smax, wave_len)
+            P.nbytes = max(0, torch.cuda.memory_allocated(self.device) - before)
+            self.plan_builds += 1
+            # make room: drop least-recently-used plans (their graphs and buffers) until the new one fits the cap
+            total = P.nbytes + sum(q.nbytes for q in self.plans.values())
+            while self.plans and total > self.plan_cache_bytes:
+                old_key = next(iter(self.plans))
+                old = self.plans.pop(old_key)
+                total -= old.nbytes
+                old.graph = None
+                self.plan_evictions += 1
+                del old
+        self.plans[key] = P          # most recently used last
+        return P
+
+    def plan_cache_stats(self) -> Dict[str, int]:
+        return {"plans": len(self.plans), "bytes": sum(q.nbytes for q in self.plans.values()),
+                "cap_bytes": self.plan_cache_bytes, "builds": self.plan_builds, "evictions": self.plan_evictions}
 
     def _drop(self, site: int, p: Optional[float] = None):
         """Dropout spec of call site ``site`` (unique stream id per site; mask regenerable in backward)."""
@@ -1197,7 +1225,7 @@ class S2TEncoderEngine:
                     ops.row_lse(logits, hs.V, out=lse)
                 w = P.loss_weights[idx]
                 ops.ctc_loss(logits.view(B, T, hs.ldv), P.tg[hs.tgt], P.out_len, P.tl[hs.tgt], hs.V, c.blank,
-                             need_grad=need_grad, grad_scale=w, lse=lse,
+                             need_grad=need_grad, grad_scale=w, grad_scale_dev=P.batch_weight, lse=lse,
                              dlogits=dlogits.view(B, T, hs.ldv) if need_grad else None, workspace=P.ctc_ws,
                              nll=P.nll_all[idx])
         ops.weighted_sum(P.nll_all, P.loss_w, P.loss)
@@ -1300,7 +1328,9 @@ class S2TEncoderEngine:
         ops.gemm_raw(M=P.R, N=C, K=hs.V, a=dlogits, lda=hs.ldv, b=S.p(wn), ldb=C, b_mn=True, out=out, ldc=C,
                      residual=residual, ldr=C if residual is not None else 0)
 
-    def _head_bwd(self, P: Plan):
+    def _head_bwd(self, P: Plan, extra: Optional[torch.Tensor] = None):
+        """Backward of _head_fwd.  ``extra``: an external gradient w.r.t. the encoder output (P.enc_out layout) added to
+        the heads' contribution — the AR decoder's gradient when the encoder is trained through ``backward_external``."""
         S = self.store
         St = P.stages[-1]
         self._touched = set()
@@ -1319,6 +1349,12 @@ class S2TEncoderEngine:
             else:
                 ops.add_(d, t0)
                 St.give(t0)
+        if extra is not None:
+            if d is None:
+                d = St.take()
+                d.copy_(extra)
+            else:
+                ops.add_(d, extra)
         dx, dd = self._ln_bwd(St, d, St.x[-1], "layer_norm", P.enc_st, nxt=self._next_branch(len(self.layer_specs)))
         self._ready("layer_norm.weight")
         St.give(d)
@@ -1607,19 +1643,19 @@ class S2TEncoderEngine:
         St.give(t)
         return out
 
-    def _backward(self, P: Plan) -> None:
+    def _backward(self, P: Plan, extra: Optional[torch.Tensor] = None) -> None:
         c = self.cfg
         for St in P.stages:
             St._ln_ev = [None] * len(St._ln_parts)      # events never cross a step (or a graph-capture) boundary
         prev = ops.set_sm_shares(*(self.sm_shares if self.multi_stream else (0, 0, 0)))
         try:
-            self._backward_body(P)
+            self._backward_body(P, extra)
         finally:
             ops.set_sm_shares(*prev)
 
-    def _backward_body(self, P: Plan) -> None:
+    def _backward_body(self, P: Plan, extra: Optional[torch.Tensor] = None) -> None:
         c = self.cfg
-        d, dd = self._head_bwd(P)
+        d, dd = self._head_bwd(P, extra)
         g = len(self.layer_specs)
         for i in reversed(range(len(P.stages))):
             n = c.layers if c.encoder_type == "s2t" else c.pds_layers[i]
@@ -1664,24 +1700,33 @@ class S2TEncoderEngine:
                    wave: Optional[torch.Tensor] = None, num_samples: Optional[torch.Tensor] = None,
                    targets: Optional[torch.Tensor] = None, target_lengths: Optional[torch.Tensor] = None,
                    xtargets: Optional[torch.Tensor] = None, xtarget_lengths: Optional[torch.Tensor] = None,
-                   sa_freq: Optional[torch.Tensor] = None, sa_time: Optional[torch.Tensor] = None) -> None:
+                   sa_freq: Optional[torch.Tensor] = None, sa_time: Optional[torch.Tensor] = None,
+                   weight: Optional[float] = None) -> None:
         """Copy one batch into the plan's static input buffers (async on the current stream; host tensors
         should be pinned).  feats fp32 [B, T, D] + src_lengths, or wave fp32 [B, N] (int16 scale) + num_samples.
         sa_freq / sa_time: SpecAugment masks of this batch (specaugment.draw_masks), used when ``engine.specaug`` is set;
         their shapes are fixed by the first call (static buffers of a captured step)."""
         nb = True
+        if weight is not None:          # 0.0 = dummy batch (gradient contribution exactly zero), 1.0 = real batch
+            P.batch_weight.fill_(float(weight))
         for name, m in (("sa_freq", sa_freq), ("sa_time", sa_time)):
             if m is not None and m.shape[1] > 0:
                 if getattr(P, name) is None:
                     setattr(P, name, torch.zeros(m.shape, dtype=torch.int32, device=self.device))
                 getattr(P, name).copy_(m, non_blocking=nb)
         if wave is not None:
-            P.wave.copy_(wave, non_blocking=nb)
+            if wave.shape[1] == P.wave.shape[1]:
+                P.wave.copy_(wave, non_blocking=nb)
+            else:       # shorter than the plan's sample bucket: samples >= num_samples are never read
+                P.wave[:, : wave.shape[1]].copy_(wave, non_blocking=nb)
             P.num_samples.copy_(num_samples, non_blocking=nb)
             # frames per utterance, snip_edges=True (torchaudio kaldi.fbank): 1 + (n - 400) // 160 — written into
             # P.src_len by the fbank kernel at the start of the step (_fbank)
         else:
-            P.feats_in.copy_(feats, non_blocking=nb)
+            if feats.shape[1] == P.T:
+                P.feats_in.copy_(feats, non_blocking=nb)
+            else:       # a batch shorter than the plan's frame bucket: frames >= src_len are never read (zero-filled by CMVN)
+                P.feats_in[:, : feats.shape[1]].copy_(feats, non_blocking=nb)
             P.src_len.copy_(src_lengths, non_blocking=nb)
         if targets is not None:
             P.targets[:, : targets.shape[1]].copy_(targets, non_blocking=nb)
@@ -1693,6 +1738,61 @@ class S2TEncoderEngine:
     def forward(self, P: Plan) -> None:
         """Encoder forward on the plan's inputs; results in P.enc_out [B*T', C], P.logits [B*T', ldv], P.out_len."""
         self._forward(P)
+
+    def out_frames(self, T: int) -> int:
+        """Frames of the encoder output the REFERENCE produces for a batch padded to ``T`` input frames (the stem's length
+        arithmetic on the padded length: subsampling.py:155,218; pdss2t_transformer.py:53-144 after quirk A7's padding).
+        A plan of a larger frame bucket holds more (masked) rows; the plugin slices its outputs to this count."""
+        c = self.cfg
+        if c.encoder_type == "s2t" and c.subsampling_type == "conv2d":
+            for _ in range(c.subsampling_layers):
+                T = (T - c.subsampling_kernel) // c.subsampling_stride + 1
+            return T
+        if c.encoder_type == "s2t":
+            pad = (c.subsampling_kernel - 1) // 2
+            for _ in range(c.subsampling_layers):
+                T = (T + 2 * pad - c.subsampling_kernel) // c.subsampling_stride + 1
+            return T
+        mult = 1
+        for r in c.pds_ratios:
+            mult *= max(1, r)
+        T = T + (mult - T % mult) if mult > 1 else T
+        for r, k in zip(c.pds_ratios, c.pds_kernels):
+            T = (T + 2 * ((k - 1) // 2) - k) // r + 1
+        return T
+
+    def forward_train(self, P: Plan) -> None:
+        """Training-mode forward only (fresh dropout streams): the first half of a step whose loss is computed OUTSIDE the
+        engine (an AR decoder + cross-entropy on encoder_out, s2t_transformer.py:868-880); ``backward_external`` is the
+        second half."""
+        ops.counter_add(self.step_counter, 1)
+        self._forward(P)
+
+    def backward_external(self, P: Plan, d_enc_out: Optional[torch.Tensor] = None,
+                          d_logits: Optional[Dict[tuple, torch.Tensor]] = None) -> None:
+        """Backward pass driven by external gradients: ``d_enc_out`` [B*T', C] w.r.t. P.enc_out and ``d_logits`` keyed
+        ("top", head) / ("inter", layer, head) w.r.t. the (unpadded, [B*T', V]) logits the forward pass produced.
+        Missing entries are zero.  Gradients land in store.grad exactly as in ``train_step`` (bucketed all-reduce
+        included)."""
+        d_logits = d_logits or {}
+        if self.dp is not None:
+            self.dp.reset()
+        for k, (hs, Hd) in enumerate(zip(self.heads, P.heads)):
+            bufs = [(("top", k), Hd.dlogits)] + [(("inter", l, k), P.inter[(l, k)].dlogits) for l in hs.inter_layers]
+            for key, buf in bufs:
+                buf.zero_()
+                g = d_logits.get(key)
+                if g is not None:
+                    buf[:, : hs.V].copy_(g.reshape(P.R, hs.V))
+        extra = None
+        if d_enc_out is not None:
+            if not hasattr(P, "ext_grad"):
+                P.ext_grad = torch.empty_like(P.enc_out)
+            P.ext_grad.copy_(d_enc_out.reshape(P.enc_out.shape))
+            extra = P.ext_grad
+        self._backward(P, extra)
+        if self.dp is not None:
+            self.dp.finish()
 
     def train_step(self, P: Plan) -> None:
         """One fwd+bwd pass: loss in P.loss, gradients in store.grad.  No host sync, no allocation."""
@@ -1725,10 +1825,17 @@ class S2TEncoderEngine:
         fn = self.train_step if kind == "train" else self.forward
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
+        # the warm-up launch must leave no trace: the batch in the plan is usually the live one and will be run again
+        # by the first replay, so the step counter (dropout streams) and the BatchNorm running statistics are restored
+        saved = {k: v.clone() for k, v in self.buffers.items()}
+        counter = self.step_counter.clone()
         with torch.cuda.stream(s):
             fn(P)                                # warm-up: function attributes, tensor-map cache
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
+        for k, v in saved.items():
+            self.buffers[k].copy_(v)
+        self.step_counter.copy_(counter)
         g = torch.cuda.CUDAGraph()
         # the dgrad chain is captured on a high-priority stream: when a chain GEMM and a side-stream weight-gradient
         # GEMM become ready together (both 1 CTA/SM), the chain's CTAs are placed first

@@ -102,10 +102,17 @@ def fbank_batch(wave: torch.Tensor, num_samples: torch.Tensor, n_mels: int = 80,
 
 
 def _get_torchaudio_fbank(waveform, sample_rate, n_bins: int = 80) -> Optional[np.ndarray]:
-    """Drop-in for audio_utils.py:59-79: (N,) or (1, N) samples in int16 scale -> (T, n_bins) fp32 numpy."""
+    """Drop-in for audio_utils.py:59-79: (N,) samples or the (channels, N) array ``get_waveform`` returns, int16 scale
+    -> (T, n_bins) fp32 numpy.  Several channels are merged to mono by averaging, as the reference's sox ``channels 1``
+    effect does (:67-72); the reference's own ``get_fbank`` hands the raw 2-D array to this hook."""
     if sample_rate != SAMPLE_RATE:
         raise ValueError("s2t_b200 fbank supports 16 kHz input (the path's sample rate)")
-    w = torch.as_tensor(np.asarray(waveform), dtype=torch.float32).reshape(1, -1).cuda()
+    arr = np.asarray(waveform.cpu() if isinstance(waveform, torch.Tensor) else waveform, dtype=np.float32)
+    if arr.ndim == 2:
+        arr = arr[0] if arr.shape[0] == 1 else arr.mean(axis=0)
+    elif arr.ndim != 1:
+        raise ValueError(f"s2t_b200 fbank: waveform must be (N,) or (channels, N), got shape {arr.shape}")
+    w = torch.as_tensor(arr, dtype=torch.float32).reshape(1, -1).cuda()
     n = torch.tensor([w.shape[1]], dtype=torch.int32, device=w.device)
     feats, _ = fbank_batch(w, n, n_bins)
     return feats[0].cpu().numpy()

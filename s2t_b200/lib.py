@@ -12,7 +12,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libs2t_b200.so"
 
 _vp, _i, _ll, _f, _ull, _u = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong, C.c_uint
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 ACT_NONE, ACT_RELU, ACT_SWISH = 0, 1, 2
 GATE_NONE, GATE_POSITIVE, GATE_SWISH_GRAD, GATE_MUL = 0, 1, 2, 3
 
@@ -94,7 +94,8 @@ SIGNATURES = {
     "s2t_softmax_rows_bwd": (_i, [_vp, _vp, _ll, _vp, _ll, _i, _i, _i, _vp]),
     "s2t_row_lse": (_i, [_vp, _i, _ll, _i, _i, _vp, _vp]),
     "s2t_ctc_workspace_bytes": (_ll, [_i, _i, _i]),
-    "s2t_ctc_loss": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _ll, _vp]),
+    "s2t_ctc_loss": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp, _ll, _vp]),
+    "s2t_batch_by_size": (_ll, [_vp, _ll, _ll, _ll, _i, _vp]),
     "s2t_ctc_greedy": (_i, [_vp, _i, _ll, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 

@@ -588,8 +588,9 @@ def ctc_loss(logits: torch.Tensor, targets: torch.Tensor, input_lengths: torch.T
              target_lengths: torch.Tensor, V: int, blank: int = 0, *, need_grad: bool = True,
              grad_scale: float = 1.0, lse: Optional[torch.Tensor] = None,
              dlogits: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None,
-             nll: Optional[torch.Tensor] = None):
-    """logits [B, T, ldv] utterance-major; targets int32 [B, Smax].  Returns (nll fp32 [B], dlogits|None)."""
+             nll: Optional[torch.Tensor] = None, grad_scale_dev: Optional[torch.Tensor] = None):
+    """logits [B, T, ldv] utterance-major; targets int32 [B, Smax].  Returns (nll fp32 [B], dlogits|None).
+    ``grad_scale_dev``: optional fp32 [1] device scalar multiplied into ``grad_scale`` on the device (batch weight)."""
     B, T, ldv = logits.shape
     smax = targets.shape[1]
     flat = logits.view(B * T, ldv)
@@ -604,7 +605,7 @@ def ctc_loss(logits: torch.Tensor, targets: torch.Tensor, input_lengths: torch.T
         dlogits = torch.empty_like(logits)
     _call("s2t_ctc_loss", _p(logits), int(logits.dtype == BF16), ldv, _p(lse), _p(targets),
           targets.stride(0), _p(input_lengths), _p(target_lengths), B, T, V, smax, blank, _p(nll),
-          _p(dlogits) if need_grad else None, grad_scale, _p(workspace),
+          _p(dlogits) if need_grad else None, grad_scale, _p(grad_scale_dev), _p(workspace),
           workspace.numel() * workspace.element_size(), _stream())
     return nll, (dlogits if need_grad else None)
 

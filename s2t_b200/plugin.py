@@ -34,6 +34,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
+from .batching import BucketSet
 from .engine import EncoderConfig, Plan, S2TEncoderEngine
 
 try:  # the reference package, when this runs inside a fairseq process
@@ -84,6 +85,34 @@ class _EngineStep(torch.autograd.Function):
         return g * grad_out.to(g.dtype), None, None
 
 
+class _EncoderForward(torch.autograd.Function):
+    """Differentiable encoder forward for losses computed OUTSIDE the engine — the AR decoder + (label-smoothed CE [+
+    CTC]) criterion of the ``s2t_transformer*`` / ``pdss2t_transformer*`` models (s2t_transformer.py:868-880).
+    Outputs: encoder_out [B*T', C] and every CTC logit set [B*T', V] (top heads, then inter blocks) as fresh tensors;
+    backward copies their gradients into the engine (``backward_external``) and returns the flat parameter gradient."""
+
+    @staticmethod
+    def forward(ctx, flat: torch.Tensor, encoder: "S2TTransformerEncoderB200", plan: Plan):
+        eng = encoder.engine
+        eng.forward_train(plan)
+        keys, outs = [], [plan.enc_out.clone()]
+        for k, hs in enumerate(eng.heads):
+            keys.append(("top", k))
+            outs.append(plan.heads[k].logits[:, : hs.V].clone())
+        for k, hs in enumerate(eng.heads):
+            for l in hs.inter_layers:
+                keys.append(("inter", l, k))
+                outs.append(plan.inter[(l, k)].logits[:, : hs.V].clone())
+        ctx.encoder, ctx.plan, ctx.keys = encoder, plan, keys
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, d_enc, *d_logits):
+        eng = ctx.encoder.engine
+        eng.backward_external(ctx.plan, d_enc, {k: g for k, g in zip(ctx.keys, d_logits) if g is not None})
+        return eng.store.grad.clone(), None, None
+
+
 class S2TTransformerEncoderB200(_EncoderBase):
     """Drop-in for ``S2TTransformerEncoder`` (fairseq/models/speech_to_text/s2t_transformer.py:883)."""
 
@@ -107,6 +136,10 @@ class S2TTransformerEncoderB200(_EncoderBase):
         self.ctc_infer_cfg = None
         self._last_plan: Optional[Plan] = None
         self.use_graph = bool(getattr(args, "b200_cuda_graph", True))
+        # frame buckets of the plan cache (batching.BucketSet).  BatchNorm statistics in training mode run over the padded
+        # frames of the batch (convolution.py:60, quirk A4), so models with BatchNorm keep the batch's exact frame count.
+        bn = self.cfg.use_cnn_module or (self.cfg.subsampling_type == "conv2d" and self.cfg.subsampling_norm == "batch2d")
+        self.buckets: Optional[BucketSet] = None if bn else BucketSet(max_frames=self.cfg.max_source_positions)
 
     # ---- reference state_dict names ---------------------------------------------------------------------
     def state_dict(self, destination=None, prefix="", keep_vars=False):
@@ -127,20 +160,28 @@ class S2TTransformerEncoderB200(_EncoderBase):
         B, T, D = src_tokens.shape
         if D != self.cfg.input_dim:
             raise ValueError(f"src_tokens has {D} features per frame, the encoder was built for {self.cfg.input_dim}")
-        return self.engine.plan(B, T, _bucket(smax))
+        Tq = self.buckets.frames(T) if self.buckets is not None else T
+        P = self.engine.plan(B, Tq, _bucket(smax))
+        P.batch_frames = T          # frames of THIS batch: outputs are sliced to what the reference would return for it
+        return P
 
-    def output_dict(self, P: Plan) -> Dict[str, list]:
-        """The encoder_out dict (s2t_transformer.py:2142-2154) as stride views of the plan's buffers."""
+    def output_dict(self, P: Plan, diff: Optional[tuple] = None) -> Dict[str, list]:
+        """The encoder_out dict (s2t_transformer.py:2142-2154) as stride views of the plan's buffers (or, with ``diff``,
+        of the autograd-tracked tensors ``_EncoderForward`` returned), cut to the output frames of the batch."""
         eng = self.engine
         B, T2, C = P.B, P.T2, eng.out_dim
-        tbc = lambda t, n: t.view(B, T2, -1)[..., :n].transpose(0, 1)
-        pad = torch.arange(T2, device=P.out_len.device)[None, :] >= P.out_len[:, None]
-        out = {"encoder_out": [tbc(P.enc_out, C)], "ctc_logit": [], "inter_ctc_logits": [], "xctc_logit": [],
+        Tv = min(T2, eng.out_frames(getattr(P, "batch_frames", P.T)))
+        tbc = lambda t, n: t.view(B, T2, -1)[:, :Tv, :n].transpose(0, 1)
+        pad = torch.arange(Tv, device=P.out_len.device)[None, :] >= P.out_len[:, None]
+        enc_src = diff[0] if diff is not None else P.enc_out
+        out = {"encoder_out": [tbc(enc_src, C)], "ctc_logit": [], "inter_ctc_logits": [], "xctc_logit": [],
                "inter_xctc_logits": [], "encoder_padding_mask": [pad], "mixup": None, "encoder_embedding": [],
                "encoder_states": [], "src_tokens": [], "src_lengths": []}
+        it = iter(diff[1:]) if diff is not None else None
+        tops = [next(it) if it is not None else P.heads[k].logits for k in range(len(eng.heads))]
         for k, hs in enumerate(eng.heads):
-            top = tbc(P.heads[k].logits, hs.V)
-            inter = [tbc(P.inter[(l, k)].logits, hs.V) for l in hs.inter_layers]
+            top = tbc(tops[k], hs.V)
+            inter = [tbc(next(it) if it is not None else P.inter[(l, k)].logits, hs.V) for l in hs.inter_layers]
             if hs.name == "ctc":
                 out["ctc_logit"] = [top]
                 out["inter_ctc_logits"] = [[lg, pad] for lg in inter]       # [logit, pad_mask] (quirk A13)
@@ -152,15 +193,20 @@ class S2TTransformerEncoderB200(_EncoderBase):
         return out
 
     def forward(self, src_tokens, src_lengths, **kwargs):
-        """src_tokens (B, T, 80*channels) float, src_lengths (B) -> encoder_out dict.  Inference / feature-extraction
-        entry: the tensors carry no autograd graph (training runs through CtcCriterionB200's fused step)."""
+        """src_tokens (B, T, 80*channels) float, src_lengths (B) -> encoder_out dict.
+        In training mode with autograd enabled the returned ``encoder_out`` / ``*ctc_logit*`` tensors carry an autograd
+        graph back to the flat parameter (``_EncoderForward``): a decoder + criterion stacked on top trains the encoder
+        exactly as decoder(encoder(.)) does in the reference (s2t_transformer.py:868-880).  Otherwise (eval / no_grad) the
+        tensors are plain views.  The pure-CTC models train through ``CtcCriterionB200``'s fused step instead."""
         if not src_tokens.is_cuda:
             raise ops._lib.S2TLibraryError("S2TTransformerEncoderB200.forward needs CUDA tensors (no CPU fallback)")
         P = self._plan_for(src_tokens, 0)
         self.engine.train(self.training)
         self.engine.set_inputs(P, feats=src_tokens.float(), src_lengths=src_lengths.to(torch.int32))
-        self.engine.forward(P)
         self._last_plan = P
+        if self.training and torch.is_grad_enabled():
+            return self.output_dict(P, diff=_EncoderForward.apply(self.flat, self, P))
+        self.engine.forward(P)
         return self.output_dict(P)
 
     def reorder_encoder_out(self, encoder_out, new_order):

@@ -49,10 +49,33 @@ def _reference_bf16_noise(pds, cfg_kw, sd, feats, lens, tokens, tgt_tokens=None)
     return {k: float((out[1][k] - out[0][k]).norm() / (out[0][k].norm() + 1e-12)) for k in out[0]}
 
 
+GTOL, GTOL_CAP = 5e-2, 0.15
+_WIDENED = {}      # test id -> [(parameter, rel-L2, tolerance used, reference bf16 noise)] where the tolerance exceeded GTOL
+
+
 def _gtol(noise, name):
     """Gradient tolerance: the stated 5e-2, or 1.25x the reference's own bf16-vs-fp32 deviation for
-    that parameter where that is larger."""
-    return max(5e-2, 1.25 * noise.get(name, 0.0))
+    that parameter where that is larger — never more than GTOL_CAP (0.15)."""
+    return min(GTOL_CAP, max(GTOL, 1.25 * noise.get(name, 0.0)))
+
+
+def _report_grads(case, rows):
+    """rows: (name, rel-L2, tolerance, noise).  Prints the worst row and every row whose tolerance was widened, and
+    appends them to gpurun_out/grad_tolerances.jsonl (copied to profiles/ per round)."""
+    import json
+    rows = sorted(rows, key=lambda r: -r[1])
+    worst = rows[0]
+    wide = [r for r in rows if r[2] > GTOL + 1e-12]
+    print(f"[{case}] worst gradient: {worst[0]} rel-L2 {worst[1]:.4f} (tolerance {worst[2]:.4f}, reference bf16 noise "
+          f"{worst[3]:.4f}); {len(wide)} of {len(rows)} parameters used a widened tolerance")
+    out = Path(__file__).resolve().parent.parent / "gpurun_out"
+    try:
+        out.mkdir(exist_ok=True)
+        with open(out / "grad_tolerances.jsonl", "a") as f:
+            f.write(json.dumps({"case": case, "n_params": len(rows), "worst": worst, "over_5e-2": [r for r in rows if r[1] > GTOL],
+                                "widened": wide}) + "\n")
+    except OSError:
+        pass
 
 
 def _engine_for(cfg_kw, sd):
@@ -74,11 +97,8 @@ def _run(eng, feats, lens, tokens, tgt_tokens=None):
     return P
 
 
-@pytest.mark.parametrize("case", ["c1_small", "c4_small", "c3_small", "c5_small", "conv2d_small"])
-def test_engine_matches_reference_golden(cuda_lib, case):
-    from oracle.make_golden import ENC_CASES, seeded_state_dict, state_checksum
-    fx = np.load(GOLDEN / f"enc_{case}.npz")
-    spec = ENC_CASES[case]
+def _cfg_from_spec(spec):
+    """EncoderConfig keywords of a golden case (oracle/make_golden.py ENC_CASES, reference arg names)."""
     ints = lambda k: tuple(int(v) for v in spec[k].split("_"))
     if spec.get("family") == "pds":
         cfg = dict(encoder_type="pds", vocab=spec["vocab"], dropout=0.0, pds_layers=ints("pds_layers"),
@@ -103,6 +123,15 @@ def test_engine_matches_reference_golden(cuda_lib, case):
                        inter_ctc_layers=csv("inter_ctc_layers"), inter_ctc_weight=spec["inter_ctc_weight"],
                        inter_xctc_layers=csv("inter_xctc_layers"), inter_xctc_weight=spec["inter_xctc_weight"],
                        ctc_pae=spec["ctc_pae"], xctc_pae=spec["xctc_pae"], pae_unnorm_input=spec["pae_unnorm_input"])
+    return cfg
+
+
+@pytest.mark.parametrize("case", ["c1_small", "c4_small", "c3_small", "c5_small", "conv2d_small"])
+def test_engine_matches_reference_golden(cuda_lib, case):
+    from oracle.make_golden import ENC_CASES, seeded_state_dict, state_checksum
+    fx = np.load(GOLDEN / f"enc_{case}.npz")
+    spec = ENC_CASES[case]
+    cfg = _cfg_from_spec(spec)
     shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
     sd = seeded_state_dict(shapes, int(fx["seed"]))
     assert state_checksum(sd) == str(fx["weights_sha256"]), "weight generator drifted from the fixture"
@@ -130,11 +159,15 @@ def test_engine_matches_reference_golden(cuda_lib, case):
         for mine, key in pairs:
             got = mine.float().view(B, T2, -1)[..., :V].transpose(0, 1).cpu()
             assert rel_l2(got[valid], torch.from_numpy(fx[key])[valid]) <= 3e-2, key
+    rows = []
     for key in fx.files:
         if key.startswith("grad::"):
             name = key[6:]
             r = rel_l2(grads[name], torch.from_numpy(fx[key]))
-            assert r <= _gtol(noise, name), (name, r, noise[name])
+            rows.append((name, r, _gtol(noise, name), noise[name]))
+    _report_grads(f"golden_{case}", rows)
+    for name, r, tol, nz in rows:
+        assert r <= tol, (name, r, tol, nz)
     # every parameter's gradient norm against the reference's
     norms = {str(n): float(v) for n, v in zip(fx["grad_names"], fx["grad_norms"])}
     for name, gn in norms.items():
@@ -181,6 +214,76 @@ def test_engine_matches_oracle_full_c1_shape(cuda_lib):
     grads = eng.grads()
     worst = max((rel_l2(grads[k], p.grad), k) for k, p in orc.named_parameters() if not k.endswith("k_proj.bias"))
     assert worst[0] <= 5e-2, worst
+
+
+@pytest.mark.parametrize("name", ["c3", "c4", "c5"])
+def test_engine_matches_oracle_full_size(cuda_lib, name):
+    """BASELINE.json configs[2..4] at their STATED size (s2t_b200/configs.py: C3 pdss2t_transformer_s_8 3_3_3_3 ffn x8;
+    C4 Conformer 12 layers d 256 macaron + conv k15 + rel_pos; C5 BiL-CTC 18 layers d 512 H 8, CTC + XCTC heads, inter-CTC
+    at 6,9,12,15 with inter_league adapters, V = 10000), 8 ragged utterances of up to 998 frames, dropout off, against
+    the CPU oracle (pinned to the reference by oracle/make_golden.py).  Output rel-L2 <= 2e-2, loss rel <= 1e-2,
+    per-parameter gradient rel-L2 <= 5e-2 for at least 90 % of the parameters and <= 0.15 for every one (deep bf16
+    stacks: the reference's own .to(bfloat16) mode deviates more than 5 % on some deep parameters, see
+    _reference_bf16_noise; at this size that second CPU pass in bf16 would take minutes, so the cap is used directly).
+    Every parameter above 5e-2 is printed and logged."""
+    from dataclasses import fields
+    from oracle import encoder as OE
+    from oracle.make_golden import seeded_state_dict
+    from s2t_b200.configs import encoder_kwargs
+    kw = encoder_kwargs(name, dropout=0.0)
+    okw = {k: v for k, v in kw.items() if k in {f.name for f in fields(OE.OracleConfig)}}
+    pds = kw.get("encoder_type") == "pds"
+    dual = kw.get("tgt_vocab", 0) > 0
+    torch.manual_seed(0)
+    orc = (OE.PDSS2TTransformerEncoder if pds else OE.S2TTransformerEncoder)(OE.OracleConfig(**okw))
+    shapes = {k: tuple(v.shape) for k, v in orc.state_dict().items()}
+    sd = seeded_state_dict(shapes, 11)
+    orc.load_state_dict(sd)
+    orc.train()
+    B, T, S, V = 8, 998, 60, 10000
+    g = torch.Generator().manual_seed(12)
+    feats = torch.randn((B, T, 80), generator=g)
+    lens = torch.tensor([998] + sorted([int(v) for v in torch.randint(500, 998, (B - 1,), generator=g)], reverse=True))
+    for b in range(B):
+        feats[b, lens[b]:] = 0
+
+    def toks(seed, smax):
+        gg = torch.Generator().manual_seed(seed)
+        t = torch.full((B, smax + 1), 1, dtype=torch.long)
+        for b in range(B):
+            n = smax - 3 * b
+            t[b, :n] = torch.randint(4, V, (n,), generator=gg)
+            t[b, n] = 2
+        return t
+
+    tokens, tgt_tokens = toks(13, S), (toks(14, S - 6) if dual else None)
+    out = orc(feats, lens)
+    if dual:
+        loss = OE.ctc_criterion_total(out, tokens, tgt_tokens, ctc_weight=kw["ctc_weight"], xctc_weight=kw["xctc_weight"],
+                                      inter_ctc_weight=kw["inter_ctc_weight"], inter_xctc_weight=kw["inter_xctc_weight"])
+    else:
+        loss = OE.ctc_criterion_loss(out["ctc_logit"][0], out["encoder_padding_mask"][0], tokens)
+    loss.backward()
+    eng = _engine_for(kw, sd)
+    P = _run(eng, feats, lens, tokens, tgt_tokens)
+    pad = out["encoder_padding_mask"][0]
+    assert P.out_len.cpu().tolist() == (~pad).sum(-1).tolist()
+    valid = ~pad.T
+    C = out["encoder_out"][0].shape[-1]
+    enc = P.enc_out.float().view(B, P.T2, C).transpose(0, 1).cpu()
+    e_rel = rel_l2(enc[valid], out["encoder_out"][0].detach()[valid])
+    l_rel = abs(P.loss.item() - loss.item()) / abs(loss.item())
+    print(f"[full_{name}] encoder_out rel-L2 {e_rel:.4f}, loss {P.loss.item():.4f} vs oracle {loss.item():.4f} (rel {l_rel:.2e})")
+    assert e_rel <= 2e-2, e_rel
+    assert l_rel <= 1e-2, (P.loss.item(), loss.item())
+    grads = eng.grads()
+    skip = ("k_proj.bias", "linear_k.bias")
+    rows = [(k, rel_l2(grads[k], p.grad), GTOL_CAP, 0.0) for k, p in orc.named_parameters()
+            if not k.endswith(skip) and p.grad is not None]
+    _report_grads(f"full_{name}", rows)
+    over = [r for r in rows if r[1] > GTOL]
+    assert all(r[1] <= GTOL_CAP for r in rows), sorted(rows, key=lambda r: -r[1])[:5]
+    assert len(over) <= 0.1 * len(rows), (len(over), len(rows), sorted(over, key=lambda r: -r[1])[:5])
 
 
 MID_CASES = {
@@ -238,10 +341,11 @@ def test_engine_matches_oracle_mid(cuda_lib, case):
     grads = eng.grads()
     skip = ("k_proj.bias", "linear_k.bias")
     noise = _reference_bf16_noise(pds, kw, sd, feats, lens, tokens)
-    for k, p in orc.named_parameters():
-        if not k.endswith(skip):
-            r = rel_l2(grads[k], p.grad)
-            assert r <= _gtol(noise, k), (k, r, noise[k])
+    rows = [(k, rel_l2(grads[k], p.grad), _gtol(noise, k), noise[k]) for k, p in orc.named_parameters()
+            if not k.endswith(skip)]
+    _report_grads(f"mid_{case}", rows)
+    for k, r, tol, nz in rows:
+        assert r <= tol, (k, r, tol, nz)
     if kw.get("use_cnn_module"):      # BatchNorm running statistics follow nn.BatchNorm1d's update
         sd2 = eng.state_dict()
         for k, v in orc.state_dict().items():
@@ -286,3 +390,101 @@ def test_engine_graph_replay_and_dropout(cuda_lib):
     eng2.run(P2); torch.cuda.synchronize(); a = P2.loss.item()
     eng2.run(P2); torch.cuda.synchronize(); b_ = P2.loss.item()
     assert np.isfinite(a) and np.isfinite(b_) and a != b_
+
+
+def _inject_engine_masks(orc, eng, P, p_drop):
+    """Make the oracle's nn.Dropout modules apply the ENGINE's Philox masks of the step that just ran (step counter
+    unchanged since): every site's mask is regenerated with the engine's own spec (``ops.dropout`` on ones — the same
+    (seed, site, counter, element-group) numbering the fused GEMM / LayerNorm epilogues use), the attention masks are read
+    off the saved probabilities (probs_d / probs).  Returns the number of hooked sites."""
+    import torch.nn as nn
+    from s2t_b200 import ops
+    from s2t_b200.params import BF16
+    B = P.B
+    keep_scale = 1.0 / (1.0 - p_drop)
+
+    def regen(site, rows, cols):
+        spec = eng._drop(site, p_drop)
+        ones = torch.ones((rows, cols), device="cuda", dtype=BF16)
+        m = ops.dropout(ones, spec, out=torch.empty_like(ones)).float().cpu()
+        assert set(torch.unique(m).tolist()) <= {0.0, float(torch.tensor(keep_scale).to(BF16))}
+        return (m != 0).float() * keep_scale
+
+    St = P.stages[0]
+    T2, C, R = St.T, St.C, St.R
+    tbc = lambda m: m.view(B, T2, -1).transpose(0, 1)
+    hooks = {"dropout_module": tbc(regen(1, R, C))}
+    for g, sp in enumerate(eng.layer_specs):
+        L = P.layers[g]
+        pre = f"layers.{g}."
+        pr, pd = L.probs.float().cpu(), L.probs_d.float().cpu()
+        am = torch.where(pr > 0, (pd != 0).float() * keep_scale, torch.full_like(pr, keep_scale))[:, :, :T2]
+        hooks[pre + "self_attn.dropout"] = am                                  # (B*H, T', T')
+        hooks[pre + "dropout_module"] = tbc(regen(sp.site + 1, R, C))
+        hooks[pre + "ffn.dropout1"] = tbc(regen(sp.site + 4, R, sp.F))
+        hooks[pre + "ffn.dropout2"] = tbc(regen(sp.site + 5, R, C))
+        if eng.cfg.macaron_style:
+            hooks[pre + "macaron_ffn.dropout1"] = tbc(regen(sp.site + 2, R, sp.F))
+            hooks[pre + "macaron_ffn.dropout2"] = tbc(regen(sp.site + 3, R, C))
+        if eng.cfg.use_cnn_module:
+            hooks[pre + "conv_module.dropout"] = regen(sp.site + 6, R, C).view(B, T2, C)
+    hooks["ctc.ctc_dropout_module"] = tbc(regen(eng.heads[0].site, R, C))
+    n = 0
+    for name, mod in orc.named_modules():
+        if isinstance(mod, nn.Dropout):
+            assert name in hooks, f"oracle dropout site {name} has no engine mask"
+            mask = hooks[name]
+
+            def hook(m, inp, out, mask=mask, name=name):
+                x = inp[0]
+                mm = mask.view(x.shape) if mask.numel() == x.numel() else None
+                assert mm is not None, (name, tuple(x.shape), tuple(mask.shape))
+                return x * mm.to(x.dtype)
+
+            mod.register_forward_hook(hook)
+            n += 1
+    return n
+
+
+@pytest.mark.parametrize("case", ["c1_small", "c4_small"])
+def test_engine_dropout_on_matches_oracle_with_injected_masks(cuda_lib, case):
+    """Numerical parity WITH dropout (the benchmarked configuration runs at p = 0.1): the engine's masks — regenerated
+    per site from its counter-based Philox streams — are injected into the oracle, then loss and every gradient must
+    agree at the dropout-free tolerances.  A site-id, scale (1/(1-p)), ReLU-gate-shortcut or LayerNorm ``out_drop``
+    mismatch between the forward and backward pass fails here."""
+    from dataclasses import fields
+    from oracle import encoder as OE
+    from oracle.make_golden import ENC_CASES, seeded_state_dict
+    fx = np.load(GOLDEN / f"enc_{case}.npz")
+    p_drop = 0.1
+    cfg = dict(_cfg_from_spec(ENC_CASES[case]), dropout=p_drop)
+    shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
+    sd = seeded_state_dict(shapes, int(fx["seed"]))
+    feats, lens, tokens = (torch.from_numpy(fx[k]) for k in ("feats", "lens", "tokens"))
+    eng = _engine_for(cfg, sd)
+    P = _run(eng, feats, lens, tokens)                    # one eager step: step counter = 1 from here on
+    okw = {k: v for k, v in cfg.items() if k in {f.name for f in fields(OE.OracleConfig)}}
+    orc = OE.S2TTransformerEncoder(OE.OracleConfig(**okw))
+    orc.load_state_dict(sd)
+    orc.train()
+    n = _inject_engine_masks(orc, eng, P, p_drop)
+    assert n >= 2 + 4 * eng.cfg.layers
+    out = orc(feats, lens)
+    loss = OE.ctc_criterion_loss(out["ctc_logit"][0], out["encoder_padding_mask"][0], tokens)
+    loss.backward()
+    # the masks really were on: the dropout-free loss of the fixture differs
+    assert abs(loss.item() - float(fx["loss"])) > 1e-3 * abs(float(fx["loss"]))
+    assert abs(P.loss.item() - loss.item()) <= 1e-2 * abs(loss.item()), (P.loss.item(), loss.item())
+    B, T2, C = P.B, P.T2, eng.cfg.embed_dim
+    valid = ~out["encoder_padding_mask"][0].T
+    enc = P.enc_out.float().view(B, T2, C).transpose(0, 1).cpu()
+    assert rel_l2(enc[valid], out["encoder_out"][0].detach()[valid]) <= 2e-2
+    grads = eng.grads()
+    # tolerance per parameter as in the dropout-free tests: 5e-2, widened (capped at 0.15) by the reference's own
+    # bf16-vs-fp32 deviation measured on the dropout-free model
+    noise = _reference_bf16_noise(False, dict(cfg, dropout=0.0), sd, feats, lens, tokens)
+    rows = [(k, rel_l2(grads[k], p.grad), _gtol(noise, k), noise[k])
+            for k, p in orc.named_parameters() if not k.endswith(("k_proj.bias", "linear_k.bias"))]
+    _report_grads(f"dropout_{case}", rows)
+    for k, r, tol, _ in rows:
+        assert r <= tol, (k, r, tol)

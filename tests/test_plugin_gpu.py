@@ -143,3 +143,103 @@ def test_ctc_decoder_generate_bit_exact(cuda_lib):
         assert h[0]["tokens"].dtype == torch.int64 and h[0]["tokens"].tolist() == [int(v) for v in want[b]]
         assert abs(float(h[0]["score"]) - scores[b]) <= 1e-3 * abs(scores[b]) + 1e-3
         assert len(h[0]["positional_scores"]) == len(want[b])
+
+
+@pytest.mark.parametrize("case", ["c1_small", "c5_small"])
+def test_encoder_trains_through_external_loss(cuda_lib, case):
+    """decoder(encoder(.)) training (s2t_transformer.py:868-880): in training mode ``forward`` returns encoder_out / logits
+    with an autograd graph; a loss computed OUTSIDE the engine (here a fixed linear 'decoder' read-out of encoder_out
+    plus a torch CTC loss on ctc_logit) must give the encoder the gradients the oracle gets for the same loss."""
+    from oracle import encoder as OE
+    from oracle.make_golden import seeded_state_dict
+    model, fx = _model(case)
+    args, spec = _args(case)
+    shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
+    sd = seeded_state_dict(shapes, int(fx["seed"]))
+    orc = OE.S2TTransformerEncoder(OE.config_from_args(args))
+    orc.load_state_dict(sd)
+    orc.train()
+    feats, lens, tokens = (torch.from_numpy(fx[k]) for k in ("feats", "lens", "tokens"))
+    g = torch.Generator().manual_seed(3)
+    C = args.encoder_embed_dim
+    readout = torch.randn((C,), generator=g) / C ** 0.5
+
+    def toy_loss(out, dev):
+        enc, pad = out["encoder_out"][0], out["encoder_padding_mask"][0]
+        keep = (~pad).T.unsqueeze(-1).to(enc.dtype)                      # T' x B x 1
+        dec = ((enc.float() * keep) @ readout.to(dev)).pow(2).sum()     # stands for the decoder's cross-entropy
+        ctc = OE.ctc_criterion_loss(out["ctc_logit"][0].float(), pad, tokens.to(dev))
+        extra = 0.0
+        if out["inter_ctc_logits"]:                                     # an inter-CTC term through the autograd path too
+            extra = 0.1 * OE.ctc_criterion_loss(out["inter_ctc_logits"][0][0].float(), pad, tokens.to(dev))
+        return dec + 0.3 * ctc + extra
+
+    ref_loss = toy_loss(orc(feats, lens), "cpu")
+    ref_loss.backward()
+    model.train()
+    out = model.encoder(feats.cuda(), lens.cuda())
+    assert out["encoder_out"][0].requires_grad and out["ctc_logit"][0].requires_grad
+    assert tuple(out["encoder_out"][0].shape) == tuple(fx["encoder_out"].shape)
+    loss = toy_loss(out, "cuda")
+    assert abs(loss.item() - ref_loss.item()) <= 2e-2 * abs(ref_loss.item()), (loss.item(), ref_loss.item())
+    loss.backward()
+    enc = model.encoder
+    assert enc.flat.grad is not None
+    grads = enc.engine.grads()
+    worst = max((float((grads[k].cpu() - p.grad).norm() / (p.grad.norm() + 1e-12)), k)
+                for k, p in orc.named_parameters()
+                if p.grad is not None and not k.endswith(("k_proj.bias", "linear_k.bias")) and float(p.grad.norm()) > 0)
+    assert worst[0] <= (5e-2 if case == "c1_small" else 0.15), worst
+    # eval / no_grad: plain tensors, no graph
+    model.eval()
+    with torch.no_grad():
+        out2 = model.encoder(feats.cuda(), lens.cuda())
+    assert not out2["encoder_out"][0].requires_grad
+
+
+def test_plan_cache_is_bounded_under_max_tokens_batching(cuda_lib):
+    """50 batches of random (B, T) as max-tokens batching produces them: the frame buckets keep the number of plans
+    small and the LRU byte cap holds (the cache used to grow by one plan + one graph per distinct (B, T))."""
+    from s2t_b200.batching import BucketSet
+    from s2t_b200.engine import EncoderConfig, S2TEncoderEngine
+    eng = S2TEncoderEngine(EncoderConfig(layers=2, ffn_dim=512, subsampling_filter=256, vocab=200, dropout=0.0))
+    cap = 1 << 30
+    eng.plan_cache_bytes = cap
+    bs = BucketSet()
+    rng = np.random.RandomState(0)
+    keys = set()
+    for i in range(50):
+        T = int(rng.randint(120, 1500))
+        B = max(8, (8000 // T) // 8 * 8)
+        Bq, Tq = bs.key(B, T)
+        keys.add((Bq, Tq))
+        P = eng.plan(Bq, Tq, 32)
+        feats = torch.randn((B, T, 80))
+        lens = torch.full((B,), T, dtype=torch.int32)
+        tg = torch.randint(4, 200, (B, 8)).to(torch.int32)
+        tl = torch.full((B,), 8, dtype=torch.int32)
+        eng.set_inputs(P, feats=feats, src_lengths=lens, targets=tg, target_lengths=tl)
+        eng.train_step(P)
+        st = eng.plan_cache_stats()
+        assert st["bytes"] <= cap, st
+    torch.cuda.synchronize()
+    st = eng.plan_cache_stats()
+    assert st["builds"] <= len(keys) + st["evictions"] and st["evictions"] > 0, st      # 1 GiB cap forces evictions here
+    assert np.isfinite(P.loss.item())
+    # an evicted bucket is rebuilt on demand and gives the same result as before
+    k0 = sorted(keys)[0]
+    assert eng.plan(k0[0], k0[1], 32) is eng.plan(k0[0], k0[1], 32)
+
+
+def test_multichannel_waveform_is_merged_to_mono(cuda_lib):
+    """audio_utils.py:67-72: the (channels, N) array get_waveform returns is merged to mono before the fbank."""
+    from s2t_b200 import frontend
+    g = np.random.RandomState(0)
+    stereo = (g.randn(2, 16000) * 3000).astype(np.float32)
+    a = frontend._get_torchaudio_fbank(stereo, 16000, 80)
+    b = frontend._get_torchaudio_fbank(stereo.mean(axis=0), 16000, 80)
+    c = frontend._get_torchaudio_fbank(stereo[:1], 16000, 80)
+    assert a.shape == b.shape == (98, 80) and np.array_equal(a, b)
+    assert c.shape == (98, 80) and np.array_equal(c, frontend._get_torchaudio_fbank(stereo[0], 16000, 80))
+    with pytest.raises(ValueError):
+        frontend._get_torchaudio_fbank(np.zeros((2, 2, 100), dtype=np.float32), 16000, 80)
