@@ -552,7 +552,7 @@ def run_bucketed(a, torch, dist, cfg, world, rank, local, peaks):
     steps_host = []
     for rb in sched:
         B, Tq = rb.key
-        wl = 400 + 160 * (Tq - 1)
+        wl = 400 + 160 * Tq                                 # any sample count that yields <= Tq frames fits
         ns = torch.tensor([int(samples[i]) for i in rb.indices], dtype=torch.int32)
         w = torch.zeros((B, int(ns.max())), dtype=torch.float32)
         for j, n in enumerate(ns.tolist()):

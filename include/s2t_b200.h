@@ -97,6 +97,10 @@ typedef struct s2t_gemm_args {
   /* side stream beside a latency-critical chain of kernels is given a small share so that the chain's CTAs always      */
   /* find free SMs; with a bound the split-K factor is also limited so that tiles * split_k <= max_ctas                 */
   int max_ctas;
+  /* optional, MN-major A only, no batch dims: colsum[m] (+)= sum_k A[m][k] (bf16 [M]) — for a weight gradient       */
+  /* dW = dY^T X this is the bias gradient of the same nn.Linear, summed from the dY tiles the kernel stages anyway   */
+  void* colsum;
+  int colsum_accumulate;
 } s2t_gemm_args;
 
 int s2t_gemm_bf16(const s2t_gemm_args* args, void* stream);
@@ -159,6 +163,17 @@ int s2t_layernorm_bwd(const void* dy, const void* x, const void* gamma, const fl
  * caller can run it beside the dgrad chain.                                                         */
 int s2t_layernorm_bwd_reduce(const float* partials, int rows, int C, void* dgamma, void* dbeta,
                              int accumulate, void* stream);
+/* The same reduction for a list of LayerNorm instances in one launch per 32 jobs (the step's 26-100 dgamma / dbeta
+ * reductions are only needed where a gradient bucket is shipped, so they are collected).  rows selects the number of
+ * partial rows exactly as s2t_layernorm_bwd_partials(rows, C).                                                      */
+typedef struct s2t_ln_reduce_job {
+  const float* partials;
+  int rows, C;
+  void* dgamma; /* bf16 [C] or NULL */
+  void* dbeta;  /* bf16 [C] or NULL */
+  int accumulate;
+} s2t_ln_reduce_job;
+int s2t_layernorm_bwd_reduce_batched(const s2t_ln_reduce_job* jobs, int n_jobs, void* stream);
 
 /* --------------------------------------------------------------------------------------------- */
 /* Elementwise / data-movement kernels of the path                                                */
@@ -216,11 +231,21 @@ int s2t_frame_rows(const void* x, const int* lengths, void* y, long long y_bs, i
 /* Fused self-attention forward (fairseq MultiheadAttention, modules/multihead_attention.py:246-265,372-416) for
  * d_k == 64 and T <= 256: per (utterance, head, 128-query tile) S = scale * Q K^T on tcgen05 into TMEM, key-padding mask,
  * fp32 softmax from TMEM, dropout, P V on tcgen05.  qkv bf16 [B*T][ldqkv] with q | k | v at columns 0 | C | 2C, head h at
- * h*64; outputs: probs / probs_drop bf16 [B*H][T][ld] (kept for the backward pass; probs_drop may be NULL when
- * dropout_p == 0), ctx bf16 [B*T][ldctx].  Same Philox numbering as s2t_attn_softmax_fwd.                    */
+ * h*64; outputs: probs / probs_drop bf16 [B*H][T][ld] (for the unfused backward pass; both may be NULL when lse is
+ * given), lse fp32 [B*H][T] = log-sum-exp of the scaled masked scores (for s2t_attn_fused_bwd; may be NULL when probs
+ * is given), ctx bf16 [B*T][ldctx].  Same Philox numbering as s2t_attn_softmax_fwd.                    */
 int s2t_attn_fused_fwd(const void* qkv, long long ldqkv, int C, void* probs, void* probs_drop, long long ld,
-                       void* ctx, long long ldctx, const int* klen, int batch, int heads, int T, int dk,
+                       float* lse, void* ctx, long long ldctx, const int* klen, int batch, int heads, int T, int dk,
                        float scale, float dropout_p, unsigned long long seed, unsigned int stream_id,
+                       const unsigned long long* seed_offset, void* stream);
+/* Fused self-attention backward (same shapes): one cluster of two CTAs per (utterance, head) recomputes
+ * P = exp(scale S - lse) from the row log-sum-exp the forward pass saved (probs == NULL there), regenerates the dropout
+ * mask, and produces dq | dk | dv (bf16 [B*T][ldg], columns 0 | C | 2C, head h at h*64) from o (forward context) and d_o
+ * (its gradient), both bf16 [B*T][ldo].  Replaces the dV / dP / softmax' / dK / dQ launches of the unfused path
+ * (multihead_attention.py:372-416 under autograd).                                                              */
+int s2t_attn_fused_bwd(const void* qkv, long long ldqkv, int C, const void* o, const void* d_o, long long ldo,
+                       const float* lse, void* dqkv, long long ldg, const int* klen, int batch, int heads, int T,
+                       int dk, float scale, float dropout_p, unsigned long long seed, unsigned int stream_id,
                        const unsigned long long* seed_offset, void* stream);
 /* Conv2dSubsampling (fairseq/modules/speech_to_text/subsampling.py:162-228): nn.Conv2d(k, stride, no padding) over a
  * channels-last activation x bf16 [B][T][D][Cin] as a GEMM over the patch matrix

@@ -33,8 +33,9 @@ constexpr int kSmRed = 2 * 4 * kTq * 4;          // row max / row sum partials [
 constexpr int kAttnSmem = kSmQ + kSmK + kSmV + kSmP + kSmRed + 1024 + 256;
 
 struct AttnParams {
-  __nv_bfloat16* probs;        // [B*H][T][ld]
-  __nv_bfloat16* probs_drop;   // same, after dropout (nullptr when dropout is off)
+  __nv_bfloat16* probs;        // [B*H][T][ld], or nullptr (the fused backward recomputes them from lse)
+  __nv_bfloat16* probs_drop;   // same, after dropout (nullptr when dropout is off or probs is nullptr)
+  float* lse;                  // [B*H][T] log-sum-exp of the scaled, masked scores (nullptr: not wanted)
   long long ld;
   __nv_bfloat16* ctx;          // [B*T][ldctx], head h at columns h*64
   long long ldctx;
@@ -168,8 +169,9 @@ attn_fused_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     named_bar_sync(1 + q, 128);
     sum = (s_red[4 * kTq + row] + s_red[5 * kTq + row]) + (s_red[6 * kTq + row] + s_red[7 * kTq + row]);
     const float inv = sum > 0.f ? 1.f / sum : 0.f;
-    // probabilities -> global (for backward), dropped probabilities -> global and the PV operand tile
-    __nv_bfloat16* prow = p.probs + grow * p.ld;
+    if (p.lse != nullptr && part == 0 && row_ok) p.lse[grow] = sum > 0.f ? m + __logf(sum) : 0.f;
+    // probabilities -> global (when the caller keeps them), dropped probabilities -> global and the PV operand tile
+    __nv_bfloat16* prow = p.probs ? p.probs + grow * p.ld : nullptr;
     __nv_bfloat16* drow = p.probs_drop ? p.probs_drop + grow * p.ld : nullptr;
     uint8_t* pdst = sP + part * 16384 + row * 128;
 #pragma unroll
@@ -181,7 +183,7 @@ attn_fused_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       uint4 pv;
       pv.x = pack_bf16(pr[0], pr[1]); pv.y = pack_bf16(pr[2], pr[3]);
       pv.z = pack_bf16(pr[4], pr[5]); pv.w = pack_bf16(pr[6], pr[7]);
-      if (row_ok && j0 < tk8) *reinterpret_cast<uint4*>(prow + j0) = pv;
+      if (prow != nullptr && row_ok && j0 < tk8) *reinterpret_cast<uint4*>(prow + j0) = pv;
       if (p.thresh16 != 0) {
         const uint32_t keep = dropout_keep8(seed, p.stream_id, grp_row + (j0 >> 3), p.thresh16);
 #pragma unroll
@@ -222,21 +224,301 @@ attn_fused_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Fused self-attention BACKWARD for one (utterance, head): a cluster of two CTAs, one per 128-query tile.
+//   S  = Q_i K^T, dP = dO_i V^T                      (tcgen05, 2 x 256 TMEM columns)
+//   P  = exp(scale * S - lse) (key mask), Pd = dropout(P)            } 16 softmax warps, straight out of TMEM;
+//   dS = P * (dropout'(dP) - delta), delta_i = dO_i . O_i            } no row reductions: lse and delta are per-row scalars
+//   dQ_i = scale * dS K ;  dK += scale * dS^T Q_i ;  dV += Pd^T dO_i  (tcgen05; Pd / dS tiles in shared memory, read as the
+//                                                    K-major A operand for dQ and as the MN-major A operand for dK / dV)
+// dK / dV are sums over the two query tiles: rank r owns keys [128 r, 128 r + 128) and receives the peer's fp32 partial of
+// that half over DSMEM (push, 64 KB each way into the retired Pd tile), adds its own from TMEM and stores bf16.
+// Replaces five launches (dV, dP, softmax', dK, dQ) and the round trips of P, dP and dS through HBM/L2; the probabilities are
+// recomputed from the saved row log-sum-exp, so the forward pass no longer writes them.
+// ---------------------------------------------------------------------------------------------
+constexpr int kSmDO = kTq * kDk * 2;                                   // 16 KB
+constexpr int kSmT = kTq * kTk * 2;                                    // 64 KB per [128][256] bf16 tile
+constexpr int kBwdSmem = kSmQ + kSmK + kSmV + kSmDO + 2 * kSmT + 1024 + 256;   // 225.25 KB of the 227 KB a CTA may own
+
+struct AttnBwdParams {
+  const __nv_bfloat16* o;      // forward context [B*T][ldo] (for delta)
+  const __nv_bfloat16* d_o;    // its gradient, same layout
+  long long ldo;
+  const float* lse;            // [B*H][T]
+  __nv_bfloat16* dqkv;         // [B*T][ldg]: dq | dk | dv at columns 0 | C | 2C, head h at h*64
+  long long ldg;
+  int C;
+  const int* klen;
+  int B, H, T;
+  float scale;
+  uint32_t thresh16;
+  float inv_keep;
+  unsigned long long seed;
+  const unsigned long long* seed_off;
+  uint32_t stream_id;
+};
+
+__global__ void __launch_bounds__(kAttnThreads, 1)
+attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
+                      const AttnBwdParams p) {
+  pdl_launch_dependents();
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + kSmQ;
+  uint8_t* sV = sK + kSmK;
+  uint8_t* sDO = sV + kSmV;
+  uint8_t* sPd = sDO + kSmDO;      // dropped probabilities; later the receive buffer of the dK / dV exchange
+  uint8_t* sDS = sPd + kSmT;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + kSmT);            // 0: operands landed, 1: S + dP ready, 2: tiles written, 3: MMAs done
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = static_cast<int>(cluster_ctarank());               // query tile of this CTA == key half it finalises
+  const int m0 = rank * kTq, h = blockIdx.y, b = blockIdx.z;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_init(&bars[2], 512);
+    mbar_init(&bars[3], 1);
+    fence_mbar_init();
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmDO);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);     // S: [0, 256), dP: [256, 512); then dQ [0, 64), dV halves [64, 192), dK halves [192, 320)
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  const int q = warp & 3;
+  const int part = warp >= 2 ? (warp - 2) >> 2 : 0;
+  const int row = q * 32 + lane;
+  const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(&bars[0], kSmQ + kSmK + kSmV + kSmDO);
+      tma_load_4d(sQ, &tmQ, &bars[0], 0, m0, h, b);
+      tma_load_4d(sDO, &tmDO, &bars[0], 0, m0, h, b);
+      tma_load_4d(sK, &tmK, &bars[0], 0, 0, h, b);
+      tma_load_4d(sV, &tmV, &bars[0], 0, 0, h, b);
+      mbar_wait(&bars[0], 0);
+      tc_fence_after();
+      const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK), va = smem_u32(sV), doa = smem_u32(sDO);
+      {
+        constexpr uint32_t idesc = umma_idesc_bf16(kTq, kTk, 0, 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)      // S = Q K^T
+          umma_bf16(tmem_base, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024), idesc,
+                    k != 0 ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)      // dP = dO V^T
+          umma_bf16(tmem_base + 256, umma_smem_desc(doa + k * 32, 16, 1024), umma_smem_desc(va + k * 32, 16, 1024), idesc,
+                    k != 0 ? 1u : 0u);
+        umma_commit(&bars[1]);
+      }
+      mbar_wait(&bars[2], 0);            // Pd and dS tiles are in shared memory, S / dP have been read out of TMEM
+      tc_fence_after();
+      const uint32_t pa = smem_u32(sPd), sa = smem_u32(sDS);
+      {
+        // dQ[i][d] = sum_j dS[i][j] K[j][d]: A = dS K-major (4 k-blocks of 64 keys), B = K MN-major
+        constexpr uint32_t idesc = umma_idesc_bf16(kTq, kDk, 0, 1);
+#pragma unroll
+        for (int kb = 0; kb < 4; ++kb)
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(tmem_base, umma_smem_desc(sa + kb * 16384 + k * 32, 16, 1024),
+                      umma_smem_desc(ka + kb * 8192 + k * 2048, 64 * 128, 1024), idesc, (kb | k) != 0 ? 1u : 0u);
+      }
+      {
+        // dV[j][d] = sum_i Pd[i][j] dO[i][d], dK[j][d] = sum_i dS[i][j] Q[i][d]: A = the tile read MN-major (M = 128 keys of
+        // half hj = two 64-key chunks 16 KB apart, K = 128 queries in steps of 16 rows = 2 KB), B = dO / Q MN-major
+        constexpr uint32_t idesc = umma_idesc_bf16(128, kDk, 1, 1);
+#pragma unroll
+        for (int hj = 0; hj < 2; ++hj) {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma_bf16(tmem_base + 64 + hj * 64, umma_smem_desc(pa + hj * 32768 + ks * 2048, 16384, 1024),
+                      umma_smem_desc(doa + ks * 2048, 64 * 128, 1024), idesc, ks != 0 ? 1u : 0u);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma_bf16(tmem_base + 192 + hj * 64, umma_smem_desc(sa + hj * 32768 + ks * 2048, 16384, 1024),
+                      umma_smem_desc(qa + ks * 2048, 64 * 128, 1024), idesc, ks != 0 ? 1u : 0u);
+        }
+      }
+      umma_commit(&bars[3]);
+    }
+  } else if (warp >= 2) {
+    const int i = m0 + row;
+    const bool row_ok = i < p.T;
+    int kl = p.klen ? p.klen[b] : p.T;
+    kl = kl < p.T ? kl : p.T;
+    unsigned long long seed = p.seed;
+    if (p.thresh16 != 0 && p.seed_off != nullptr) seed += *p.seed_off;
+    const long long grow = (static_cast<long long>(b) * p.H + h) * p.T + i;
+    const int tk8 = (p.T + 7) & ~7;
+    const unsigned long long grp_row = static_cast<unsigned long long>(grow) * (tk8 >> 3);
+    const int col0 = part * 64;
+    // delta_i = dO_i . O_i (64 products; every thread of the row computes it itself: 16 L2-resident 16-byte loads whose
+    // latency hides behind the operand loads and the first two MMAs — no shared-memory exchange, no barrier)
+    float delta = 0.f, lse = 0.f;
+    if (row_ok) {
+      const long long off = (static_cast<long long>(b) * p.T + i) * p.ldo + h * kDk;
+      const uint4* po = reinterpret_cast<const uint4*>(p.o + off);
+      const uint4* pg = reinterpret_cast<const uint4*>(p.d_o + off);
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const uint4 ov = po[c], gv = pg[c];
+        delta += bf16_lo(ov.x) * bf16_lo(gv.x) + bf16_hi(ov.x) * bf16_hi(gv.x) + bf16_lo(ov.y) * bf16_lo(gv.y) +
+                 bf16_hi(ov.y) * bf16_hi(gv.y) + bf16_lo(ov.z) * bf16_lo(gv.z) + bf16_hi(ov.z) * bf16_hi(gv.z) +
+                 bf16_lo(ov.w) * bf16_lo(gv.w) + bf16_hi(ov.w) * bf16_hi(gv.w);
+      }
+      lse = p.lse[grow];
+    }
+    mbar_wait(&bars[1], 0);
+    tc_fence_after();
+    uint8_t* pd_dst = sPd + part * 16384 + row * 128;
+    uint8_t* ds_dst = sDS + part * 16384 + row * 128;
+#pragma unroll 1
+    for (int hf = 0; hf < 2; ++hf) {
+      uint32_t rs[32], rp[32];
+      tmem_ld_32x32(t_addr + col0 + hf * 32, rs);
+      tmem_ld_32x32(t_addr + 256 + col0 + hf * 32, rp);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const int j0 = col0 + hf * 32 + g * 8;
+        uint32_t keep = 0xffu;
+        if (p.thresh16 != 0) keep = dropout_keep8(seed, p.stream_id, grp_row + (j0 >> 3), p.thresh16);
+        float pd[8], ds[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const bool live = row_ok && (j0 + e) < kl;
+          const float pr = live ? __expf(__uint_as_float(rs[g * 8 + e]) * p.scale - lse) : 0.f;
+          const float kf = ((keep >> e) & 1u) ? p.inv_keep : 0.f;
+          pd[e] = pr * kf;
+          ds[e] = pr * (kf * __uint_as_float(rp[g * 8 + e]) - delta);
+        }
+        uint4 v;
+        v.x = pack_bf16(pd[0], pd[1]); v.y = pack_bf16(pd[2], pd[3]);
+        v.z = pack_bf16(pd[4], pd[5]); v.w = pack_bf16(pd[6], pd[7]);
+        const int chunk = ((hf * 4 + g) ^ (row & 7)) << 4;
+        *reinterpret_cast<uint4*>(pd_dst + chunk) = v;
+        v.x = pack_bf16(ds[0], ds[1]); v.y = pack_bf16(ds[2], ds[3]);
+        v.z = pack_bf16(ds[4], ds[5]); v.w = pack_bf16(ds[6], ds[7]);
+        *reinterpret_cast<uint4*>(ds_dst + chunk) = v;
+      }
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    mbar_arrive(&bars[2]);
+    mbar_wait(&bars[3], 0);
+    tc_fence_after();
+    // dQ rows of this tile (parts 0 and 1: 32 columns each)
+    if (part < 2) {
+      uint32_t rg[32];
+      tmem_ld_32x32(t_addr + part * 32, rg);
+      tmem_ld_wait();
+      if (row_ok) {
+        __nv_bfloat16* o = p.dqkv + (static_cast<long long>(b) * p.T + i) * p.ldg + h * kDk + part * 32;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 ov;
+          ov.x = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 0]), p.scale * __uint_as_float(rg[g * 8 + 1]));
+          ov.y = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 2]), p.scale * __uint_as_float(rg[g * 8 + 3]));
+          ov.z = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 4]), p.scale * __uint_as_float(rg[g * 8 + 5]));
+          ov.w = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 6]), p.scale * __uint_as_float(rg[g * 8 + 7]));
+          *reinterpret_cast<uint4*>(o + g * 8) = ov;
+        }
+      }
+    }
+  }
+  // ---- dK / dV: exchange the key halves between the two query-tile CTAs ---------------------------------------------
+  // every MMA of this CTA has retired before it arrives here (bars[3]; warp 0 lane 0 issued the commit, the softmax warps
+  // waited for it), so after the first cluster barrier the peer's Pd tile may be overwritten
+  __syncwarp();
+  if (warp < 2) {            // the two control warps never waited for bars[3]: do it now so that "arrived" means "MMAs retired"
+    mbar_wait(&bars[3], 0);
+    tc_fence_after();
+  }
+  tc_fence_before();
+  __syncwarp();
+  cluster_sync_all();
+  // which accumulator a thread moves: parts 0 / 1 = dV columns [0, 32) / [32, 64), parts 2 / 3 = dK columns likewise
+  const int which_k = part >> 1;                  // 0 = dV, 1 = dK
+  const int chalf = part & 1;
+  const uint32_t recv_local = smem_u32(sPd);
+  if (warp >= 2) {
+    const int peer = rank ^ 1;
+    uint32_t rg[32];
+    tmem_ld_32x32(t_addr + 64 + which_k * 128 + peer * 64 + chalf * 32, rg);   // my partial of the PEER's key half
+    tmem_ld_wait();
+    const uint32_t dst = dsmem_addr(recv_local, static_cast<uint32_t>(peer));
+#pragma unroll
+    for (int g4 = 0; g4 < 8; ++g4) {
+      const uint32_t off = static_cast<uint32_t>(((part * 8 + g4) * 128 + row) << 4);
+      dsmem_st_f4(dst + off, make_float4(__uint_as_float(rg[g4 * 4]), __uint_as_float(rg[g4 * 4 + 1]),
+                                         __uint_as_float(rg[g4 * 4 + 2]), __uint_as_float(rg[g4 * 4 + 3])));
+    }
+  }
+  tc_fence_before();
+  __syncwarp();
+  cluster_sync_all();        // partials of my key half have landed in sPd
+  if (warp >= 2) {
+    tc_fence_after();
+    uint32_t rg[32];
+    tmem_ld_32x32(t_addr + 64 + which_k * 128 + rank * 64 + chalf * 32, rg);   // my own partial of my key half
+    tmem_ld_wait();
+    const int j = rank * 128 + row;                // key row this thread finalises
+    if (j < p.T) {
+      const float sc = which_k ? p.scale : 1.f;
+      const float4* recv = reinterpret_cast<const float4*>(sPd);
+      __nv_bfloat16* o = p.dqkv + (static_cast<long long>(b) * p.T + j) * p.ldg + (which_k ? p.C : 2 * p.C) + h * kDk + chalf * 32;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const float4 r0 = recv[(part * 8 + 2 * g) * 128 + row], r1 = recv[(part * 8 + 2 * g + 1) * 128 + row];
+        uint4 ov;
+        ov.x = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 0]) + r0.x), sc * (__uint_as_float(rg[g * 8 + 1]) + r0.y));
+        ov.y = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 2]) + r0.z), sc * (__uint_as_float(rg[g * 8 + 3]) + r0.w));
+        ov.z = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 4]) + r1.x), sc * (__uint_as_float(rg[g * 8 + 5]) + r1.y));
+        ov.w = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 6]) + r1.z), sc * (__uint_as_float(rg[g * 8 + 7]) + r1.w));
+        *reinterpret_cast<uint4*>(o + g * 8) = ov;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
 }  // namespace
 }  // namespace s2t
 
 using namespace s2t;
 
 extern "C" int s2t_attn_fused_fwd(const void* qkv, long long ldqkv, int C, void* probs, void* probs_drop, long long ld,
-                                  void* ctx, long long ldctx, const int* klen, int batch, int heads, int T, int dk,
+                                  float* lse, void* ctx, long long ldctx, const int* klen, int batch, int heads, int T, int dk,
                                   float scale, float dropout_p, unsigned long long seed, unsigned int stream_id,
                                   const unsigned long long* seed_offset, void* stream) {
-  S2T_REQUIRE(qkv && probs && ctx, "s2t_attn_fused_fwd: null pointer");
+  S2T_REQUIRE(qkv && ctx, "s2t_attn_fused_fwd: null pointer");
+  S2T_REQUIRE(probs != nullptr || lse != nullptr, "s2t_attn_fused_fwd: keep either the probabilities or the row log-sum-exp");
   S2T_REQUIRE(dk == kDk && T >= 1 && T <= kTk, "s2t_attn_fused_fwd: needs d_k == 64 and T <= 256 (got d_k=%d, T=%d)", dk, T);
   S2T_REQUIRE(heads * dk <= C && ldqkv >= 3ll * C && ldqkv % 8 == 0 && C % 8 == 0, "s2t_attn_fused_fwd: bad qkv layout");
-  S2T_REQUIRE(ld % 8 == 0 && ld >= ((T + 7) & ~7) && ldctx % 8 == 0, "s2t_attn_fused_fwd: ld / ldctx must be multiples of 8");
+  S2T_REQUIRE(ldctx % 8 == 0 && (probs == nullptr || (ld % 8 == 0 && ld >= ((T + 7) & ~7))),
+              "s2t_attn_fused_fwd: ld / ldctx must be multiples of 8");
   S2T_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "s2t_attn_fused_fwd: bad dropout_p");
-  S2T_REQUIRE(dropout_p == 0.f || probs_drop != nullptr, "s2t_attn_fused_fwd: dropout needs the probs_drop output");
+  S2T_REQUIRE(dropout_p == 0.f || probs == nullptr || probs_drop != nullptr,
+              "s2t_attn_fused_fwd: dropout with kept probabilities needs the probs_drop output");
   if (batch <= 0) return 0;
   const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(qkv);
   CUtensorMap tq, tk, tv;
@@ -249,7 +531,8 @@ extern "C" int s2t_attn_fused_fwd(const void* qkv, long long ldqkv, int C, void*
   AttnParams p;
   memset(&p, 0, sizeof(p));
   p.probs = reinterpret_cast<__nv_bfloat16*>(probs);
-  p.probs_drop = dropout_p > 0.f ? reinterpret_cast<__nv_bfloat16*>(probs_drop) : nullptr;
+  p.probs_drop = (dropout_p > 0.f && probs != nullptr) ? reinterpret_cast<__nv_bfloat16*>(probs_drop) : nullptr;
+  p.lse = lse;
   p.ld = ld;
   p.ctx = reinterpret_cast<__nv_bfloat16*>(ctx);
   p.ldctx = ldctx;
@@ -268,5 +551,70 @@ extern "C" int s2t_attn_fused_fwd(const void* qkv, long long ldqkv, int C, void*
   }
   S2T_LAUNCH(attn_fused_fwd_kernel, dim3((T + kTq - 1) / kTq, heads, batch), kAttnThreads, kAttnSmem,
              reinterpret_cast<cudaStream_t>(stream), tq, tk, tv, p);
+  return 0;
+}
+
+extern "C" int s2t_attn_fused_bwd(const void* qkv, long long ldqkv, int C, const void* o, const void* d_o, long long ldo,
+                                  const float* lse, void* dqkv, long long ldg, const int* klen, int batch, int heads,
+                                  int T, int dk, float scale, float dropout_p, unsigned long long seed,
+                                  unsigned int stream_id, const unsigned long long* seed_offset, void* stream) {
+  S2T_REQUIRE(qkv && o && d_o && lse && dqkv, "s2t_attn_fused_bwd: null pointer");
+  S2T_REQUIRE(dk == kDk && T >= 1 && T <= kTk, "s2t_attn_fused_bwd: needs d_k == 64 and T <= 256 (got d_k=%d, T=%d)", dk, T);
+  S2T_REQUIRE(heads * dk <= C && ldqkv >= 3ll * C && ldqkv % 8 == 0 && C % 8 == 0 && ldg >= 3ll * C && ldg % 8 == 0 &&
+                  ldo % 8 == 0 && ldo >= heads * dk,
+              "s2t_attn_fused_bwd: bad layout");
+  S2T_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "s2t_attn_fused_bwd: bad dropout_p");
+  S2T_REQUIRE((reinterpret_cast<uintptr_t>(o) & 15) == 0 && (reinterpret_cast<uintptr_t>(d_o) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(dqkv) & 15) == 0,
+              "s2t_attn_fused_bwd: o / d_o / dqkv must be 16-byte aligned");
+  if (batch <= 0) return 0;
+  const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(qkv);
+  CUtensorMap tq, tk, tv, tdo;
+  int rc = make_operand_map(&tq, base, kDk, T, ldqkv, heads, kDk, batch, 1ll * T * ldqkv, kTq);
+  if (rc) return rc;
+  rc = make_operand_map(&tk, base + C, kDk, T, ldqkv, heads, kDk, batch, 1ll * T * ldqkv, kTk);
+  if (rc) return rc;
+  rc = make_operand_map(&tv, base + 2 * C, kDk, T, ldqkv, heads, kDk, batch, 1ll * T * ldqkv, kTk);
+  if (rc) return rc;
+  rc = make_operand_map(&tdo, d_o, kDk, T, ldo, heads, kDk, batch, 1ll * T * ldo, kTq);
+  if (rc) return rc;
+  AttnBwdParams p;
+  memset(&p, 0, sizeof(p));
+  p.o = reinterpret_cast<const __nv_bfloat16*>(o);
+  p.d_o = reinterpret_cast<const __nv_bfloat16*>(d_o);
+  p.ldo = ldo;
+  p.lse = lse;
+  p.dqkv = reinterpret_cast<__nv_bfloat16*>(dqkv);
+  p.ldg = ldg;
+  p.C = C;
+  p.klen = klen;
+  p.B = batch; p.H = heads; p.T = T;
+  p.scale = scale;
+  p.thresh16 = dropout_p > 0.f ? static_cast<uint32_t>(dropout_p * 65536.f + 0.5f) : 0u;
+  p.inv_keep = 1.f / (1.f - dropout_p);
+  p.seed = seed;
+  p.seed_off = seed_offset;
+  p.stream_id = stream_id;
+  static bool configured = false;
+  if (!configured) {
+    S2T_CHECK_CUDA(cudaFuncSetAttribute(attn_fused_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(2, heads, batch);
+  cfg.blockDim = dim3(kAttnThreads, 1, 1);
+  cfg.dynamicSmemBytes = kBwdSmem;
+  cfg.stream = reinterpret_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  S2T_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_fused_bwd_kernel, tq, tk, tv, tdo, p));
   return 0;
 }

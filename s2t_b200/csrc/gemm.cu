@@ -27,8 +27,10 @@ namespace s2t {
 
 constexpr int kBM = 128;
 constexpr int kBK = 64;
-constexpr int kGemmThreads = 320;  // TMA warp, MMA warp, 8 epilogue warps
+constexpr int kGemmThreads = 320;    // split-K kernel: TMA warp, MMA warp, 8 epilogue warps
 constexpr int kEpiWarps = 8;
+constexpr int kColsumWarps = 4;      // persistent kernel only: column sums of the A operand (bias gradients), see below
+constexpr int kGemmThreadsP = kGemmThreads + 32 * kColsumWarps;
 
 struct GemmKernelParams {
   int M, N, K;
@@ -58,6 +60,10 @@ struct GemmKernelParams {
   long long ldc, c_bs1, c_bs2;
   int out_vec;          // out base 16B aligned, ldc and batch strides multiples of 8 (bf16) / 4 (fp32)
   unsigned long long* trace;  // debug: globaltimer stamps of CTA 0's phases (S2T_GEMM_TRACE=1), else nullptr
+  // persistent kernel, MN-major A (weight gradients dW = dY^T X): colsum[m] (+)= sum_k A[k][m] — the bias gradient of the
+  // same layer, summed from the dY tiles the main loop stages in shared memory anyway (no separate pass over dY)
+  __nv_bfloat16* colsum;
+  int colsum_accumulate;
 };
 
 // GATE = 1: the persistent kernel stages the epilogue's gate operand through shared memory by TMA (32 KB: 4 lane
@@ -205,7 +211,7 @@ __device__ __forceinline__ void epilogue8(float (&v)[8], const GemmKernelParams&
 //   warps 2-5 epilogue      : tcgen05.ld -> fused epilogue -> swizzled smem staging -> TMA store (coalesced,
 //                             edge-clipped by the tensor map); overlaps the next tile's loads and MMAs
 template <int BN, int A_MN, int B_MN, int EPI>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(kGemmThreadsP, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmG,
                  const GemmKernelParams p) {
@@ -234,9 +240,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int num_tiles = tiles_per_z * p.nbatch;
 
   if (threadIdx.x == 0) {
+    // with column sums a stage is free once the MMAs have retired AND the four column-sum warps have read it
+    const uint32_t empty_count = (A_MN && p.colsum != nullptr) ? 1u + kColsumWarps : 1u;
     for (int i = 0; i < Cfg::kStages; ++i) {
       mbar_init(&full_bar[i], 1);
-      mbar_init(&empty_bar[i], 1);
+      mbar_init(&empty_bar[i], empty_count);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
@@ -308,6 +316,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(&tempty_bar[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * BN;
+        // tiles of the first column block (n0 == 0) are the ones whose A stages the column-sum warps read; for every other
+        // tile this thread stands in for their arrivals
+        const bool colsum_standin = A_MN && p.colsum != nullptr && ((tile % tiles_per_z) / tiles_m) != 0;
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % Cfg::kStages;
           const uint32_t ph = (it / Cfg::kStages) & 1;
@@ -325,9 +336,53 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
           }
           umma_commit(&empty_bar[s]);  // frees this smem stage once the MMAs above retire
+          if (colsum_standin) {
+#pragma unroll
+            for (int w = 0; w < kColsumWarps; ++w) mbar_arrive(&empty_bar[s]);
+          }
         }
         umma_commit(&tfull_bar[buf]);  // accumulator of this tile complete
         if (lt == 0) trace_stamp(p, 5);
+      }
+    }
+  } else if (warp >= 2 + kEpiWarps) {
+    // ------------------------------ column sums of A (bias gradient) ----------
+    // 128 threads = the 128 M-columns of the tile.  A stage holds A as [64 k-rows][64 m] x 2 chunks, 128-byte rows with
+    // the 16-byte chunk index XORed by (k & 7); thread m adds its column of every stage of the tiles with n0 == 0.
+    if (A_MN && p.colsum != nullptr) {
+      const int cw = (warp - 2 - kEpiWarps) * 32 + lane;
+      const uint32_t coff = static_cast<uint32_t>((cw >> 6) * (kBK * 128) + (cw & 7) * 2);
+      const int cchunk = (cw & 63) >> 3;
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int r = tile % tiles_per_z;
+        if (r / tiles_m != 0) {
+          it += num_kb;
+          continue;
+        }
+        const int m0 = (r % tiles_m) * kBM;
+        float acc = 0.f;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % Cfg::kStages;
+          const uint32_t ph = (it / Cfg::kStages) & 1;
+          mbar_wait(&full_bar[s], ph);
+          const uint8_t* a_src = smem + s * Cfg::kStageBytes + coff;
+          float a0 = 0.f, a1 = 0.f;
+#pragma unroll 16
+          for (int k = 0; k < kBK; k += 2) {
+            const uint16_t v0 = *reinterpret_cast<const uint16_t*>(a_src + k * 128 + ((cchunk ^ (k & 7)) << 4));
+            const uint16_t v1 = *reinterpret_cast<const uint16_t*>(a_src + (k + 1) * 128 + ((cchunk ^ ((k + 1) & 7)) << 4));
+            a0 += __uint_as_float(static_cast<uint32_t>(v0) << 16);
+            a1 += __uint_as_float(static_cast<uint32_t>(v1) << 16);
+          }
+          acc += a0 + a1;
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&empty_bar[s]);
+        }
+        if (m0 + cw < p.M) {
+          if (p.colsum_accumulate) acc += __bfloat162float(p.colsum[m0 + cw]);
+          p.colsum[m0 + cw] = __float2bfloat16(acc);
+        }
       }
     }
   } else {
@@ -856,7 +911,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   const long long tiles = 1ll * ((kp.N + BN - 1) / BN) * ((kp.M + kBM - 1) / kBM) * nbatch;
   const int cap = (kp.max_ctas > 0 && kp.max_ctas < sm_count()) ? kp.max_ctas : sm_count();
   const int grid = static_cast<int>(tiles < cap ? tiles : cap);
-  S2T_LAUNCH(kern, grid, kGemmThreads, Cfg::kSmemBytes, stream, ta, tb, tc, tg, kp);
+  S2T_LAUNCH(kern, grid, kGemmThreadsP, Cfg::kSmemBytes, stream, ta, tb, tc, tg, kp);
   return 0;
 }
 
@@ -1011,6 +1066,10 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
     }
   }
 
+  if (g->colsum != nullptr) {
+    S2T_REQUIRE(g->a_mn_major && nb1 * nb2 == 1, "s2t_gemm_bf16: colsum needs an MN-major A operand and no batch dims");
+    split = 1;   // the column sums are taken by the persistent kernel
+  }
   CUtensorMap ta, tb, tc;
   int rc;
   if (g->a_mn_major)
@@ -1063,6 +1122,8 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
     vec = vec && (kp.ldg % 8 == 0) && (kp.g_bs1 % 8 == 0) && (kp.g_bs2 % 8 == 0) && al16(kp.gate);
   kp.aux_vec = vec ? 1 : 0;
   kp.trace = gemm_trace_buffer();
+  kp.colsum = reinterpret_cast<__nv_bfloat16*>(g->colsum);
+  kp.colsum_accumulate = g->colsum_accumulate;
   kp.out = g->out;
   kp.ldc = g->ldc; kp.c_bs1 = nb1 > 1 ? g->c_bs1 : 0; kp.c_bs2 = nb2 > 1 ? g->c_bs2 : 0;
   {

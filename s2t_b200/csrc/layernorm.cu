@@ -215,6 +215,46 @@ layernorm_bwd_reduce_kernel(const float* __restrict__ partials, int n_partials, 
   }
 }
 
+// The same reduction for up to kLnBatch LayerNorm instances in ONE launch (blockIdx.y = instance): the training step has
+// 26-100 LayerNorms whose dgamma / dbeta are only needed when a gradient bucket is shipped (or at the end of backward),
+// so their reductions are collected and run together instead of as one 5-10 us launch each.
+constexpr int kLnBatch = 32;
+struct LnReduceJob {
+  const float* partials;
+  __nv_bfloat16* dgamma;
+  __nv_bfloat16* dbeta;
+  int n_partials, C, accumulate;
+};
+struct LnReduceJobs {
+  LnReduceJob j[kLnBatch];
+};
+
+__global__ void __launch_bounds__(256)
+layernorm_bwd_reduce_batched_kernel(const __grid_constant__ LnReduceJobs jobs) {
+  pdl_entry();
+  const LnReduceJob& jb = jobs.j[blockIdx.y];
+  __shared__ float s_acc[8][33];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const int C = jb.C;
+  const int c = blockIdx.x * 32 + lane;
+  if (blockIdx.x * 32 >= 2 * C) return;      // whole block beyond this instance's [2][C] row (block-uniform)
+  float acc = 0.f;
+  if (c < 2 * C)
+    for (int p = slice; p < jb.n_partials; p += 8) acc += jb.partials[static_cast<long long>(p) * 2 * C + c];
+  s_acc[slice][lane] = acc;
+  __syncthreads();
+  if (slice == 0 && c < 2 * C) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) acc += s_acc[k][lane];
+    const int which = c / C, col = c % C;
+    __nv_bfloat16* dst = which == 0 ? jb.dgamma : jb.dbeta;
+    if (dst != nullptr) {
+      if (jb.accumulate) acc += __bfloat162float(dst[col]);
+      dst[col] = __float2bfloat16(acc);
+    }
+  }
+}
+
 static int ln_partials(int rows) {
   int n = (rows + kLnWarps - 1) / kLnWarps;            // one row per warp while the grid fits in one wave
   if (n > 296) n = 296;                                // 2 CTAs per SM on 148 SMs
@@ -296,5 +336,30 @@ extern "C" int s2t_layernorm_bwd_reduce(const float* partials, int rows, int C, 
   if (rows <= 0) return 0;
   S2T_LAUNCH(layernorm_bwd_reduce_kernel, (2 * C + 31) / 32, 256, 0, reinterpret_cast<cudaStream_t>(stream), partials, ln_partials(rows), C, reinterpret_cast<__nv_bfloat16*>(dgamma), reinterpret_cast<__nv_bfloat16*>(dbeta), accumulate);
   S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int s2t_layernorm_bwd_reduce_batched(const s2t_ln_reduce_job* jobs, int n_jobs, void* stream) {
+  S2T_REQUIRE(n_jobs >= 0 && (n_jobs == 0 || jobs != nullptr), "s2t_layernorm_bwd_reduce_batched: bad job list");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  for (int base = 0; base < n_jobs; base += kLnBatch) {
+    const int n = n_jobs - base < kLnBatch ? n_jobs - base : kLnBatch;
+    LnReduceJobs js;
+    memset(&js, 0, sizeof(js));
+    int cmax = 0;
+    for (int i = 0; i < n; ++i) {
+      const s2t_ln_reduce_job& in = jobs[base + i];
+      S2T_REQUIRE(in.partials != nullptr && in.rows > 0 && in.C > 0, "s2t_layernorm_bwd_reduce_batched: bad job %d", base + i);
+      js.j[i].partials = in.partials;
+      js.j[i].dgamma = reinterpret_cast<__nv_bfloat16*>(in.dgamma);
+      js.j[i].dbeta = reinterpret_cast<__nv_bfloat16*>(in.dbeta);
+      js.j[i].n_partials = ln_partials(in.rows);
+      js.j[i].C = in.C;
+      js.j[i].accumulate = in.accumulate;
+      if (in.C > cmax) cmax = in.C;
+    }
+    S2T_LAUNCH(layernorm_bwd_reduce_batched_kernel, dim3((2 * cmax + 31) / 32, n), 256, 0, st, js);
+    S2T_LAUNCH_CHECK();
+  }
   return 0;
 }

@@ -226,10 +226,9 @@ class _Stage(_Bufs):
         lib = ops._lib.load()
         cs = max(lib.s2t_colsum_workspace_floats(R, 3 * C), lib.s2t_colsum_workspace_floats(R, F))
         self.colsum_ws, self.colsum_ws2 = e(cs, dt=F32), e(cs, dt=F32)   # two: consecutive colsums overlap on a side stream
-        self.ln_part = e(lib.s2t_layernorm_bwd_partials(R, C), 2, C, dt=F32)
-        self._ln_parts = [self.ln_part] + [e(lib.s2t_layernorm_bwd_partials(R, C), 2, C, dt=F32) for _ in range(3)]
-        self._ln_i = 0
-        self._ln_ev: List[Optional[torch.cuda.Event]] = [None] * len(self._ln_parts)
+        # dgamma / dbeta partial sums: one buffer per LayerNorm instance (allocated on first use), reduced together by ONE
+        # batched launch where a gradient bucket is shipped or at the end of backward (engine._flush_ln)
+        self.ln_parts: Dict[str, torch.Tensor] = {}
         if c.attn_type == "rel_pos":
             n_rel = 2 * T - 1
             self.ldb = _round8(n_rel)
@@ -247,11 +246,12 @@ class _Stage(_Bufs):
     def take(self) -> torch.Tensor:
         return self.pool.pop()
 
-    def next_ln_part(self) -> torch.Tensor:
-        """Rotating LayerNorm-backward partial buffers (the dgamma/dbeta reduce of one LN runs on a side stream while
-        the next LN backward already writes its own partials)."""
-        self._ln_i = (self._ln_i + 1) % len(self._ln_parts)
-        return self._ln_parts[self._ln_i]
+    def ln_part(self, name: str, rows: int, C: int, dev) -> torch.Tensor:
+        t = self.ln_parts.get(name)
+        if t is None:
+            n = ops._lib.load().s2t_layernorm_bwd_partials(rows, C)
+            t = self.ln_parts[name] = torch.empty((n, 2, C), device=dev, dtype=F32)
+        return t
 
     def give(self, *bufs: torch.Tensor) -> None:
         for t in bufs:
@@ -326,6 +326,11 @@ class Plan:
             self.framed = [z(B, self.t_sub[i] + 2 * pad, chans[i]) for i in range(n)]
             self.pre = [e(B * self.t_sub[i + 1], eng.sub_filters[i]) for i in range(n)]
             self.sub_len = [z(B, dt=torch.int32) for _ in range(n)]
+            # frames the REFERENCE's intermediate conv outputs have for this batch (its padded length may be shorter than
+            # the plan's frame bucket): rows beyond are zero there (the next Conv1d's zero padding), so the intermediate
+            # GLUs cut at this count — set per batch by set_inputs
+            self.batch_sub = [torch.full((B,), self.t_sub[i + 1], device=dev, dtype=torch.int32) for i in range(n - 1)]
+            self.batch_T = T
             self.g_pre = [e(B * self.t_sub[i + 1], eng.sub_filters[i]) for i in range(n)]
             self.g_col = [e(B * self.t_sub[i + 1], k * chans[i]) for i in range(n)]
             self.xcol = [e(B * self.t_sub[i + 1], k * chans[i]) for i in range(n)]
@@ -380,8 +385,13 @@ class Plan:
                 L.xa = e(Rs, Cs)
             L.ln1, L.st1 = e(Rs, Cs), e(Rs, 2, dt=F32)
             L.qkv = e(Rs, 3 * Cs)
-            L.probs = z(B * Hs, St.T, St.ld)
-            L.probs_d = z(B * Hs, St.T, St.ld) if pdrop else L.probs
+            if eng.attn_is_fused(St):
+                # fused attention (attn.cu): the backward pass recomputes the probabilities from the row log-sum-exp
+                L.lse = e(B * Hs * St.T, dt=F32)
+                L.probs = L.probs_d = None
+            else:
+                L.probs = z(B * Hs, St.T, St.ld)
+                L.probs_d = z(B * Hs, St.T, St.ld) if pdrop else L.probs
             L.ctx = e(Rs, Cs)
             L.x1 = e(Rs, Cs)
             if c.attn_type == "rel_pos":
@@ -577,7 +587,9 @@ class S2TEncoderEngine:
         # fork/join streams: leaf work of the backward pass (weight / bias gradients) and independent attention
         # branches run beside the critical dgrad chain; captured into the CUDA graph as parallel branches
         self.multi_stream = True
-        self.fused_attention = os.environ.get("S2T_FUSED_ATTN", "0") == "1"   # attn.cu (selfattn, d_k 64, T' <= 256): parity with the 3-launch form at C2 (2.25 vs 2.23 ms/step), off by default
+        # attn.cu: one launch per layer and direction for selfattn with d_k 64 and T' <= 256 (S2T_FUSED_ATTN=0: the unfused
+        # GEMM / softmax / GEMM form, which also serves every other shape)
+        self.fused_attention = os.environ.get("S2T_FUSED_ATTN", "1") == "1"
         self._side = [torch.cuda.Stream(device=self.device) for _ in range(3)]
         # SM partition of the backward pass: (chain GEMM CTAs, weight-gradient GEMM CTAs, weight-gradient split-K policy);
         # measured on B200 (148 SMs): 100 + 48 without split-K, 2.14 -> 1.94 ms/step (ops.set_sm_shares)
@@ -586,9 +598,13 @@ class S2TEncoderEngine:
         self.fwd_share = 0       # SM bound of forward GEMMs (0 = whole GPU; MicroBatchEngine splits the GPU between groups)
         self._ln_stream = torch.cuda.Stream(device=self.device)   # LayerNorm dgamma/dbeta reductions (_ln_bwd)
         self._ln_pending = False
+        self._ln_jobs: list = []
         self._forked: set = set()
         self.dp = None               # dp.BucketedAllReduce when data parallel
         self.init_parameters()
+
+    def attn_is_fused(self, St: "_Stage") -> bool:
+        return self.fused_attention and self.cfg.attn_type == "selfattn" and St.dk == 64 and St.T <= 256
 
     def _pos_table(self, dim: int) -> torch.Tensor:
         if dim not in self.pos_tables:
@@ -940,18 +956,15 @@ class S2TEncoderEngine:
         St.give(dy)
         if c.encoder_embed_norm:
             o = St.take()
-            ops.layernorm_bwd(t, P.x0, S.p("embed_ln.weight"), P.e_st, S.g("embed_ln.weight"), S.g("embed_ln.bias"),
-                              out=o, partials=St.ln_part)
+            self._ln_bwd_plain(St, t, P.x0, "embed_ln", P.e_st, o)
             St.give(t)
             self._ready("embed_ln.weight")
             t = o
         ops.mask_rows_(t.view(P.B, St.T, C), St.lens)                   # padded frames were zeroed in forward
         L = P.c2[-1]
         y_last = (L.y if c.subsampling_norm == "batch2d" else L.pre).view(P.B * L.Tout, L.Dout * L.cout)
-        with self._fork(1):
-            ops.colsum(t, S.g("subsample.linear.bias"), workspace=P.stem_colsum_ws)
         with self._fork(0):
-            ops.linear_wgrad(t, y_last, out=S.g("subsample.linear.weight"))
+            ops.linear_wgrad(t, y_last, out=S.g("subsample.linear.weight"), colsum=S.g("subsample.linear.bias"))
         ops.linear_dgrad(t, S.p("subsample.linear.weight"), out=L.g_y.view(P.B * L.Tout, L.Dout * L.cout))
         self._ready("subsample.linear.weight")
         St.give(t)
@@ -966,10 +979,8 @@ class S2TEncoderEngine:
                 g = L.g_pre
             else:
                 g = L.g_y
-            with self._fork(1):
-                ops.colsum(g, S.g(n + "0.bias"), workspace=L.colsum_ws)
             with self._fork(0):
-                ops.linear_wgrad(g, L.col, out=S.g(n + "0.weight"))
+                ops.linear_wgrad(g, L.col, out=S.g(n + "0.weight"), colsum=S.g(n + "0.bias"))
             if i > 0:
                 ops.linear_dgrad(g, S.p(n + "0.weight"), out=L.g_col)
                 prev = P.c2[i - 1]
@@ -1000,7 +1011,8 @@ class S2TEncoderEngine:
                          bias=S.p(f"subsample.layers.{i}.0.bias"))
             if i < n - 1:
                 nxt = P.framed[i + 1]
-                ops.glu_fwd(P.pre[i], out=nxt, T=t_out, ldy=cout // 2, y_bs=nxt.stride(0), y_off=P.pad * (cout // 2))
+                ops.glu_fwd(P.pre[i], out=nxt, lengths=P.batch_sub[i], T=t_out, ldy=cout // 2, y_bs=nxt.stride(0),
+                            y_off=P.pad * (cout // 2))
             else:
                 self._join()
                 ops.glu_fwd(P.pre[i], out=P.x0, lengths=P.sub_len[i], T=t_out)
@@ -1072,10 +1084,9 @@ class S2TEncoderEngine:
         ops.linear(L.ln1, S.fused(a + q + ".weight", 3 * C, C), S.fused(a + q + ".bias", 3 * C, 0), out=L.qkv)
         bs_s = (T * ld, H * T * ld)
         dspec = self._drop(sp.site + 0, sp.p_drop)
-        if not rel and self.fused_attention and dk == 64 and T <= 256:
-            # one launch: S = q k^T (TMEM) -> masked fp32 softmax -> dropout -> P v  (attn.cu)
-            ops.attn_fused_fwd(L.qkv, C, St.lens, B, H, T, dk, probs=L.probs, probs_drop=L.probs_d if dspec else None,
-                               ctx=L.ctx, scale=dk ** -0.5, dropout=dspec)
+        if L.probs is None:
+            # one launch: S = q k^T (TMEM) -> masked fp32 softmax -> dropout -> P v; keeps the row log-sum-exp  (attn.cu)
+            ops.attn_fused_fwd(L.qkv, C, St.lens, B, H, T, dk, lse=L.lse, ctx=L.ctx, scale=dk ** -0.5, dropout=dspec)
             ops.linear(L.ctx, S.p(a + o + ".weight"), S.p(a + o + ".bias"), out=L.x1,
                        dropout=self._drop(sp.site + 1, sp.p_drop), residual=x, ldr=C)
             return
@@ -1262,6 +1273,7 @@ class S2TEncoderEngine:
         self.grad_ready_hook(off)
 
     def _join_ln(self) -> None:
+        self._flush_ln()
         if self._ln_pending:
             torch.cuda.current_stream().wait_stream(self._ln_stream)
             self._ln_pending = False
@@ -1272,30 +1284,36 @@ class S2TEncoderEngine:
         scale) of the residual branch whose backward consumes the result next: the kernel then also emits
         scale * dropout(dx) (second return value), so that branch needs no separate dropout pass."""
         S = self.store
-        part = St.next_ln_part()
+        part = St.ln_part(norm, x.shape[0], x.shape[1], self.device)
         dx, dd, spec, scale = St.take(), None, None, 1.0
         if nxt is not None and (nxt[0] is not None or nxt[1] != 1.0):
             dd, (spec, scale) = St.take(), nxt
-        idx = St._ln_i
-        main = torch.cuda.current_stream()
-        if self.multi_stream and St._ln_ev[idx] is not None:
-            main.wait_event(St._ln_ev[idx])          # the reduce that last read this partial buffer has finished
         ops.layernorm_bwd(dy, x, S.p(norm + ".weight"), stats, None, None, dx_residual=dx_residual, out=dx,
                           partials=part, out_drop=dd, drop=spec, drop_scale=scale, reduce=False)
+        self._ln_jobs.append((part, x.shape[0], x.shape[1], S.g(norm + ".weight"), S.g(norm + ".bias")))
+        return dx, dd
+
+    def _ln_bwd_plain(self, St: _Stage, dy: torch.Tensor, x: torch.Tensor, norm: str, stats: torch.Tensor,
+                      out: torch.Tensor) -> None:
+        """LayerNorm backward of a stem norm (embed_ln, downsampling norms) into ``out``; reduction deferred likewise."""
+        S = self.store
+        part = St.ln_part(norm, x.shape[0], x.shape[1], self.device)
+        ops.layernorm_bwd(dy, x, S.p(norm + ".weight"), stats, None, None, out=out, partials=part, reduce=False)
+        self._ln_jobs.append((part, x.shape[0], x.shape[1], S.g(norm + ".weight"), S.g(norm + ".bias")))
+
+    def _flush_ln(self) -> None:
+        """Run the collected dgamma / dbeta reductions as one batched launch, beside the dgrad chain."""
+        if not self._ln_jobs:
+            return
+        jobs, self._ln_jobs = self._ln_jobs, []
         if self.multi_stream:
-            # dgamma / dbeta reduction on its own stream, joined only where gradients are declared final (_ready):
-            # the ordinary _join() after every block must not put these 5 us on the dgrad chain
             ln = self._ln_stream
-            ln.wait_stream(main)
+            ln.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(ln):
-                ops.layernorm_bwd_reduce(part, x.shape[0], x.shape[1], S.g(norm + ".weight"), S.g(norm + ".bias"))
-                ev = torch.cuda.Event()
-                ev.record(ln)
-            St._ln_ev[idx] = ev
+                ops.layernorm_bwd_reduce_batched(jobs)
             self._ln_pending = True
         else:
-            ops.layernorm_bwd_reduce(part, x.shape[0], x.shape[1], S.g(norm + ".weight"), S.g(norm + ".bias"))
-        return dx, dd
+            ops.layernorm_bwd_reduce_batched(jobs)
 
     def _branch_grad(self, dy: torch.Tensor, spec, scale: float, out: torch.Tensor) -> torch.Tensor:
         """Gradient entering a residual branch y = x + scale * dropout(branch): scale * mask * dy / (1-p)."""
@@ -1316,15 +1334,14 @@ class S2TEncoderEngine:
         S = self.store
         wn, bn = hs.name + ".ctc_projection.weight", hs.name + ".ctc_projection.bias"
         C = out.shape[1]
-        with self._fork(1):
-            ops.colsum(dlogits, S.g(bn), accumulate=self._acc(bn), workspace=ws)
         gw = S.g(wn)
         dl = dlogits[:, : hs.V] if hs.V != hs.ldv else dlogits
-        with self._fork(0):
+        with self._fork(0):      # weight gradient; the bias gradient (column sums of dlogits) rides on its A tiles
+            acc_b = self._acc(bn)
             if self._acc(wn):
-                ops.linear_wgrad(dl, src, out=gw, residual=gw, ldr=C)
+                ops.linear_wgrad(dl, src, out=gw, residual=gw, ldr=C, colsum=S.g(bn), colsum_accumulate=acc_b)
             else:
-                ops.linear_wgrad(dl, src, out=gw)
+                ops.linear_wgrad(dl, src, out=gw, colsum=S.g(bn), colsum_accumulate=acc_b)
         ops.gemm_raw(M=P.R, N=C, K=hs.V, a=dlogits, lda=hs.ldv, b=S.p(wn), ldb=C, b_mn=True, out=out, ldc=C,
                      residual=residual, ldr=C if residual is not None else 0)
 
@@ -1407,9 +1424,7 @@ class S2TEncoderEngine:
         t0, t1 = St.take(), St.take()
         d2 = dyd if dyd is not None else self._branch_grad(dy, self._drop(site + 1), scale, t0)
         with self._fork(0):
-            ops.linear_wgrad(d2, f, out=S.g(ffn + ".w_2.weight"))
-        with self._fork(1):
-            ops.colsum(d2, S.g(ffn + ".w_2.bias"), workspace=St.colsum_ws)
+            ops.linear_wgrad(d2, f, out=S.g(ffn + ".w_2.weight"), colsum=S.g(ffn + ".w_2.bias"))
         if self.ffn_act == ops.ACT_RELU:
             # f = dropout(relu(h)) is positive exactly where h > 0 AND the element was kept, so the gate on f covers the
             # dropout mask too: no Philox regeneration in this epilogue, only the 1/(1-p) scale (folded into alpha)
@@ -1420,9 +1435,7 @@ class S2TEncoderEngine:
             ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=St.g_f, gate=h, gate_mode=ops.GATE_SWISH_GRAD, ldg=St.F,
                              dropout=self._drop(site))
         with self._fork(0):
-            ops.linear_wgrad(St.g_f, ln, out=S.g(ffn + ".w_1.weight"))
-        with self._fork(1):
-            ops.colsum(St.g_f, S.g(ffn + ".w_1.bias"), workspace=St.colsum_ws2)
+            ops.linear_wgrad(St.g_f, ln, out=S.g(ffn + ".w_1.weight"), colsum=S.g(ffn + ".w_1.bias"))
         ops.linear_dgrad(St.g_f, S.p(ffn + ".w_1.weight"), out=t1)
         dx, dd = self._ln_bwd(St, t1, x, norm, st, dx_residual=dy, nxt=nxt)
         self._join()
@@ -1466,14 +1479,17 @@ class S2TEncoderEngine:
         t0, t1, dctx = St.take(), St.take(), St.take()
         do = dyd if dyd is not None else self._branch_grad(dy, self._drop(sp.site + 1, sp.p_drop), 1.0, t0)
         with self._fork(0):
-            ops.linear_wgrad(do, L.ctx, out=S.g(a + o + ".weight"))
-        with self._fork(1):
-            ops.colsum(do, S.g(a + o + ".bias"), workspace=St.colsum_ws)
+            ops.linear_wgrad(do, L.ctx, out=S.g(a + o + ".weight"), colsum=S.g(a + o + ".bias"))
         ops.linear_dgrad(do, S.p(a + o + ".weight"), out=dctx)
         dspec = self._drop(sp.site + 0, sp.p_drop)
+        g_qkv = St.g_qkv
+        if L.probs is None:
+            # one launch: P recomputed from the saved log-sum-exp, dS, dQ / dK / dV  (attn.cu)
+            ops.attn_fused_bwd(L.qkv, C, L.ctx, dctx, L.lse, St.lens, B, H, T, dk, out=g_qkv, scale=dk ** -0.5,
+                               dropout=dspec)
+            return self._attn_bwd_tail(P, St, sp, L, dy, dyd, x, nxt, t0, t1, dctx)
         pd = L.probs_d if dspec else L.probs
         bs_x, bs_qkv, bs_s = (dk, T * C), (dk, T * 3 * C), (T * ld, H * T * ld)
-        g_qkv = St.g_qkv
         # dV = P_drop^T dctx (side) ; dP_drop = dctx V^T (main)
         with self._fork(2):
             ops.gemm_raw(M=T, N=dk, K=T, a=pd, lda=ld, a_mn=True, a_bs=bs_s, b=dctx, ldb=C, b_mn=True, b_bs=bs_x,
@@ -1510,11 +1526,19 @@ class S2TEncoderEngine:
             with self._fork(1):
                 ops.colsum(St.g_quv, S.fused(a + "pos_bias_u", 2 * C, 0, grad=True), workspace=St.colsum_ws)
             ops.relpos_qbias_bwd(St.g_quv, g_qkv, C)
+        return self._attn_bwd_tail(P, St, sp, L, dy, dyd, x, nxt, t0, t1, dctx)
+
+    def _attn_bwd_tail(self, P, St, sp, L, dy, dyd, x, nxt, t0, t1, dctx):
+        """Backward of the fused q/k/v projection and the attention LayerNorm (g_qkv holds dq | dk | dv)."""
+        c, S = self.cfg, self.store
+        C = St.C
+        a = sp.prefix + "self_attn."
+        q = "linear_q" if c.attn_type == "rel_pos" else "q_proj"
+        g_qkv = St.g_qkv
         self._join()                                      # g_qkv is complete (dV / dK came from side streams)
         with self._fork(0):
-            ops.linear_wgrad(g_qkv, L.ln1, out=S.fused(a + q + ".weight", 3 * C, C, grad=True))
-        with self._fork(1):
-            ops.colsum(g_qkv, S.fused(a + q + ".bias", 3 * C, 0, grad=True), workspace=St.colsum_ws)
+            ops.linear_wgrad(g_qkv, L.ln1, out=S.fused(a + q + ".weight", 3 * C, C, grad=True),
+                             colsum=S.fused(a + q + ".bias", 3 * C, 0, grad=True))
         ops.linear_dgrad(g_qkv, S.fused(a + q + ".weight", 3 * C, C), out=t1)
         dx, dd = self._ln_bwd(St, t1, x, sp.prefix + "self_attn_layer_norm", L.st1, dx_residual=dy, nxt=nxt)
         self._join()
@@ -1583,8 +1607,7 @@ class S2TEncoderEngine:
         St.give(dy)
         if c.encoder_embed_norm:
             o = St.take()
-            ops.layernorm_bwd(t, P.x0, S.p("embed_ln.weight"), P.e_st, S.g("embed_ln.weight"), S.g("embed_ln.bias"),
-                              out=o, partials=St.ln_part)
+            self._ln_bwd_plain(St, t, P.x0, "embed_ln", P.e_st, o)
             St.give(t)
             self._ready("embed_ln.weight")
             t = o
@@ -1596,12 +1619,11 @@ class S2TEncoderEngine:
             if i == n - 1:
                 ops.glu_bwd(P.pre[i], dy, out=P.g_pre[i], lengths=P.sub_len[i], T=t_out)
             else:
-                ops.glu_bwd(P.pre[i], dy, out=P.g_pre[i])
-            with self._fork(1):
-                ops.colsum(P.g_pre[i], S.g(f"subsample.layers.{i}.0.bias"), workspace=P.stem_colsum_ws)
+                ops.glu_bwd(P.pre[i], dy, out=P.g_pre[i], lengths=P.batch_sub[i], T=t_out)
             with self._fork(0):
                 ops.im2col1d(xin, xin.stride(0), P.B, t_out, cin, k, st, out=P.xcol[i])
-                ops.linear_wgrad(P.g_pre[i], P.xcol[i], out=S.g(f"subsample.layers.{i}.0.weight").view(cout, k * cin))
+                ops.linear_wgrad(P.g_pre[i], P.xcol[i], out=S.g(f"subsample.layers.{i}.0.weight").view(cout, k * cin),
+                                 colsum=S.g(f"subsample.layers.{i}.0.bias"))
             if i > 0:
                 ops.linear_dgrad(P.g_pre[i], S.p(f"subsample.layers.{i}.0.weight").view(cout, k * cin), out=P.g_col[i])
                 ops.col2im1d(P.g_col[i], P.B, P.t_sub[i], t_out, cin, k, st, P.pad, out=P.g_sub[i])
@@ -1621,16 +1643,14 @@ class S2TEncoderEngine:
         St.give(dy)
         if c.pds_embed_norm:
             o = St.take()
-            ops.layernorm_bwd(t, D.conv, S.p(n + "norm.weight"), D.st, S.g(n + "norm.weight"), S.g(n + "norm.bias"),
-                              out=o, partials=St.ln_part)
+            self._ln_bwd_plain(St, t, D.conv, n + "norm", D.st, o)
             St.give(t)
             t = o
-        with self._fork(1):
-            ops.colsum(t, S.g(n + "conv.0.bias"), workspace=D.colsum_ws)
         w = S.p(n + "conv.0.weight").view(D.cout, D.k * D.cin)
         with self._fork(0):
             ops.im2col1d(D.framed, D.framed.stride(0), P.B, D.t_out, D.cin, D.k, D.stride, out=D.xcol)
-            ops.linear_wgrad(t, D.xcol, out=S.g(n + "conv.0.weight").view(D.cout, D.k * D.cin))
+            ops.linear_wgrad(t, D.xcol, out=S.g(n + "conv.0.weight").view(D.cout, D.k * D.cin),
+                             colsum=S.g(n + "conv.0.bias"))
         out = None
         if i > 0:
             prev = P.stages[i - 1]
@@ -1645,8 +1665,7 @@ class S2TEncoderEngine:
 
     def _backward(self, P: Plan, extra: Optional[torch.Tensor] = None) -> None:
         c = self.cfg
-        for St in P.stages:
-            St._ln_ev = [None] * len(St._ln_parts)      # events never cross a step (or a graph-capture) boundary
+        self._ln_jobs = []
         prev = ops.set_sm_shares(*(self.sm_shares if self.multi_stream else (0, 0, 0)))
         try:
             self._backward_body(P, extra)
@@ -1672,6 +1691,7 @@ class S2TEncoderEngine:
                 d, dd = self._layer_bwd(P, g, d, dd)
             P.stages[i].give(dd)
             dd = None
+            self._flush_ln()             # the layers' LayerNorm reductions run beside the stem's backward
             if c.encoder_type == "s2t" and c.subsampling_type == "conv2d":
                 self._stem_conv2d_bwd(P, d)
             elif c.encoder_type == "s2t":
@@ -1707,6 +1727,15 @@ class S2TEncoderEngine:
         sa_freq / sa_time: SpecAugment masks of this batch (specaugment.draw_masks), used when ``engine.specaug`` is set;
         their shapes are fixed by the first call (static buffers of a captured step)."""
         nb = True
+        if hasattr(P, "batch_sub"):     # Conv1dSubsampling: intermediate frame counts of THIS batch's padded length
+            from .frontend import num_frames
+            t = feats.shape[1] if feats is not None else (num_frames(wave.shape[1]) if wave is not None else P.T)
+            if t != P.batch_T:
+                P.batch_T = t
+                c = self.cfg
+                for v in P.batch_sub:
+                    t = (t + 2 * P.pad - c.subsampling_kernel) // c.subsampling_stride + 1
+                    v.fill_(t)
         if weight is not None:          # 0.0 = dummy batch (gradient contribution exactly zero), 1.0 = real batch
             P.batch_weight.fill_(float(weight))
         for name, m in (("sa_freq", sa_freq), ("sa_time", sa_time)):

@@ -34,7 +34,14 @@ class GemmArgs(C.Structure):
         ("dropout_seed_offset", _vp),
         ("split_k", _i),
         ("max_ctas", _i),
+        ("colsum", _vp), ("colsum_accumulate", _i),
     ]
+
+
+class LnReduceJob(C.Structure):
+    """struct s2t_ln_reduce_job (include/s2t_b200.h)."""
+
+    _fields_ = [("partials", _vp), ("rows", _i), ("C", _i), ("dgamma", _vp), ("dbeta", _vp), ("accumulate", _i)]
 
 
 # name -> (restype, argtypes); every symbol declared in include/s2t_b200.h must appear here
@@ -53,6 +60,7 @@ SIGNATURES = {
     "s2t_layernorm_bwd_partials": (_i, [_i, _i]),
     "s2t_layernorm_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _f, _f, _ull, _u, _vp, _vp]),
     "s2t_layernorm_bwd_reduce": (_i, [_vp, _i, _i, _vp, _vp, _i, _vp]),
+    "s2t_layernorm_bwd_reduce_batched": (_i, [C.POINTER(LnReduceJob), _i, _vp]),
     "s2t_glu_fwd": (_i, [_vp, _vp, _ll, _ll, _i, _i, _vp, _i, _vp]),
     "s2t_glu_bwd": (_i, [_vp, _vp, _ll, _vp, _i, _i, _vp, _i, _vp]),
     "s2t_colsum": (_i, [_vp, _ll, _i, _i, _vp, _i, _vp, _ll, _vp]),
@@ -63,7 +71,8 @@ SIGNATURES = {
     "s2t_dropout": (_i, [_vp, _vp, _ll, _f, _f, _ull, _u, _vp, _vp]),
     "s2t_im2col1d": (_i, [_vp, _ll, _vp, _i, _i, _i, _i, _i, _vp]),
     "s2t_frame_rows": (_i, [_vp, _vp, _vp, _ll, _i, _i, _i, _i, _vp]),
-    "s2t_attn_fused_fwd": (_i, [_vp, _ll, _i, _vp, _vp, _ll, _vp, _ll, _vp, _i, _i, _i, _i, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_attn_fused_fwd": (_i, [_vp, _ll, _i, _vp, _vp, _ll, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _f, _f, _ull, _u, _vp, _vp]),
+    "s2t_attn_fused_bwd": (_i, [_vp, _ll, _i, _vp, _vp, _ll, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _f, _f, _ull, _u, _vp, _vp]),
     "s2t_im2col2d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2t_col2im2d": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "s2t_colstats_parts": (_i, [_ll]),

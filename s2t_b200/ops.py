@@ -24,7 +24,7 @@ _LAUNCHES = {
     "s2t_layernorm_fwd": 1, "s2t_layernorm_bwd": 1, "s2t_layernorm_bwd_reduce": 1, "s2t_glu_fwd": 1, "s2t_glu_bwd": 1,
     "s2t_colsum": 1, "s2t_col2im1d": 1, "s2t_embed_fwd": 1, "s2t_embed_bwd": 1, "s2t_mask_rows": 1,
     "s2t_permute_conv_weight": 1, "s2t_cast_f32_to_bf16": 1, "s2t_cast_bf16_to_f32": 1,
-    "s2t_attn_softmax_fwd": 1, "s2t_attn_fused_fwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4,
+    "s2t_attn_softmax_fwd": 1, "s2t_attn_fused_fwd": 1, "s2t_attn_fused_bwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4,
     "s2t_ctc_greedy": 2, "s2t_dwconv1d_fwd": 1, "s2t_dwconv1d_bwd": 3, "s2t_batchnorm_fwd": 1,
     "s2t_batchnorm_bwd": 2, "s2t_im2col2d": 1, "s2t_col2im2d": 1, "s2t_colstats": 1, "s2t_relpos_qbias_fwd": 1, "s2t_relpos_qbias_bwd": 1, "s2t_act_dropout": 1,
 }
@@ -86,6 +86,7 @@ def gemm_raw(
     g_bs: Tuple[int, int] = (0, 0), dropout: Optional[Tuple[float, int, int]] = None,
     out_scale: float = 1.0, residual: Optional[torch.Tensor] = None, ldr: int = 0,
     r_bs: Tuple[int, int] = (0, 0), tile_n: int = 0, split_k: int = 0, max_ctas: int = 0,
+    colsum: Optional[torch.Tensor] = None, colsum_accumulate: bool = False,
 ) -> None:
     """out[z] = residual + out_scale*dropout(gate(act(alpha * A[z] @ B[z]^T + bias))) — see s2t_b200.h.
 
@@ -119,6 +120,7 @@ def gemm_raw(
     g.tile_n = tile_n
     g.split_k = split_k
     g.max_ctas = max_ctas if max_ctas else _default_max_ctas
+    g.colsum, g.colsum_accumulate = _p(colsum), int(colsum_accumulate)
     _call("s2t_gemm_bf16", C.byref(g), _stream())
 
 
@@ -147,7 +149,8 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, *, out: Optional[torch.Tenso
 
 def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, *, out: Optional[torch.Tensor] = None,
                  out_dtype: torch.dtype = BF16, **epi) -> torch.Tensor:
-    """dw[N, K] = dy[R, N]^T @ x[R, K]  (both operands read MN-major)."""
+    """dw[N, K] = dy[R, N]^T @ x[R, K]  (both operands read MN-major).  ``colsum=`` (bf16 [N]) additionally receives the
+    column sums of dy — the bias gradient of the same layer — from the dy tiles the kernel stages anyway."""
     R, N = dy.shape
     K = x.shape[1]
     if out is None:
@@ -247,6 +250,21 @@ def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, stats:
 def layernorm_bwd_reduce(partials: torch.Tensor, rows: int, Cd: int, dgamma: Optional[torch.Tensor],
                          dbeta: Optional[torch.Tensor], accumulate: bool = False) -> None:
     _call("s2t_layernorm_bwd_reduce", _p(partials), rows, Cd, _p(dgamma), _p(dbeta), int(accumulate), _stream())
+
+
+def layernorm_bwd_reduce_batched(jobs) -> None:
+    """jobs: sequence of (partials, rows, C, dgamma, dbeta[, accumulate]) — all dgamma / dbeta reductions in one launch per
+    32 jobs."""
+    global launch_count
+    if not jobs:
+        return
+    arr = (_lib.LnReduceJob * len(jobs))()
+    for a, j in zip(arr, jobs):
+        a.partials, a.rows, a.C = _p(j[0]), int(j[1]), int(j[2])
+        a.dgamma, a.dbeta = _p(j[3]), _p(j[4])
+        a.accumulate = int(j[5]) if len(j) > 5 else 0
+    _lib.check(_lib.load().s2t_layernorm_bwd_reduce_batched(arr, len(jobs), _stream()))
+    launch_count += (len(jobs) + 31) // 32
 
 
 # --------------------------------------------------------------------------------------------------
@@ -443,12 +461,23 @@ def attn_softmax_fwd(scores: torch.Tensor, klen: Optional[torch.Tensor], heads: 
 
 
 def attn_fused_fwd(qkv: torch.Tensor, C: int, klen: Optional[torch.Tensor], B: int, H: int, T: int, dk: int, *,
-                   probs: torch.Tensor, probs_drop: Optional[torch.Tensor], ctx: torch.Tensor, scale: float,
-                   dropout=None) -> None:
-    """Fused self-attention forward (d_k == 64, T <= 256): qkv bf16 [B*T, >=3C] -> probs (+ probs_drop) [B*H, T, ld] and
-    ctx [B*T, C]."""
-    _call("s2t_attn_fused_fwd", _p(qkv), qkv.stride(0), C, _p(probs), _p(probs_drop), probs.stride(1), _p(ctx),
-          ctx.stride(0), _p(klen), B, H, T, dk, scale, *_drop(dropout), _stream())
+                   probs: Optional[torch.Tensor] = None, probs_drop: Optional[torch.Tensor] = None,
+                   lse: Optional[torch.Tensor] = None, ctx: torch.Tensor, scale: float, dropout=None) -> None:
+    """Fused self-attention forward (d_k == 64, T <= 256): qkv bf16 [B*T, >=3C] -> ctx [B*T, C] and either the
+    probabilities (+ probs_drop) [B*H, T, ld] or the row log-sum-exp ``lse`` fp32 [B*H*T] (for ``attn_fused_bwd``)."""
+    _call("s2t_attn_fused_fwd", _p(qkv), qkv.stride(0), C, _p(probs), _p(probs_drop),
+          probs.stride(1) if probs is not None else 0, _p(lse), _p(ctx), ctx.stride(0), _p(klen), B, H, T, dk, scale,
+          *_drop(dropout), _stream())
+
+
+def attn_fused_bwd(qkv: torch.Tensor, C: int, ctx: torch.Tensor, dctx: torch.Tensor, lse: torch.Tensor,
+                   klen: Optional[torch.Tensor], B: int, H: int, T: int, dk: int, *, out: torch.Tensor, scale: float,
+                   dropout=None) -> torch.Tensor:
+    """Fused self-attention backward: (qkv, ctx, dctx, lse) -> out = dq | dk | dv, bf16 [B*T, >=3C] (one launch)."""
+    assert ctx.stride(0) == dctx.stride(0)
+    _call("s2t_attn_fused_bwd", _p(qkv), qkv.stride(0), C, _p(ctx), _p(dctx), ctx.stride(0), _p(lse), _p(out),
+          out.stride(0), _p(klen), B, H, T, dk, scale, *_drop(dropout), _stream())
+    return out
 
 
 def attn_softmax_bwd(probs: torch.Tensor, dprobs_drop: torch.Tensor, klen: Optional[torch.Tensor],

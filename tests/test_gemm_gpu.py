@@ -223,3 +223,33 @@ def test_split_k_cluster_reduction(cuda_lib, M, N, K, kind, split_k, tile_n):
         ref = dy.float().T @ x.float()
     torch.cuda.synchronize()
     _check(out, ref)
+
+
+@pytest.mark.parametrize("R,N,K,max_ctas,tile_n", [(2000, 256, 2048, 0, 0), (2000, 2048, 256, 48, 128), (2000, 768, 256, 48, 64),
+                                                    (333, 200, 136, 0, 0), (2000, 10000, 256, 48, 0), (1999, 1024, 400, 7, 128),
+                                                    (64, 64, 64, 0, 0)])
+def test_wgrad_with_fused_bias_gradient(cuda_lib, R, N, K, max_ctas, tile_n):
+    """dw = dy^T x with colsum= : the bias gradient (column sums of dy) is taken from the dy tiles the weight-gradient
+    GEMM stages in shared memory (four extra warps of the persistent kernel), replacing the standalone column-sum launch.
+    Covers several tiles per CTA (max_ctas bound: tiles with and without column sums interleave on one CTA), M and K
+    tails, and accumulation into an existing gradient (shared CTC heads)."""
+    from s2t_b200 import ops
+    dy, x = _rand((R, N), 11, 0.5), _rand((R, K), 12)
+    ref_w = dy.float().T @ x.float()
+    ref_b = dy.float().sum(0)
+    db = torch.full((N,), 7.0, dtype=BF16).cuda()                   # must be overwritten, not accumulated
+    dw = ops.linear_wgrad(dy.cuda(), x.cuda(), colsum=db, max_ctas=max_ctas, tile_n=tile_n, split_k=-1)
+    torch.cuda.synchronize()
+    _check(dw, ref_w)
+    _check(db, ref_b)
+    # accumulate on top of a previous value (and a strided dy view: the padded logits of the CTC head)
+    wide = _rand((R, N + 8), 13, 0.5).cuda()
+    view = wide[:, :N]
+    prev = _rand((N,), 14).cuda()
+    db2 = prev.clone()
+    dw2 = ops.linear_wgrad(view, x.cuda(), colsum=db2, colsum_accumulate=True, max_ctas=max_ctas, split_k=-1)
+    torch.cuda.synchronize()
+    _check(dw2, view.float().cpu().T @ x.float())
+    _check(db2, view.float().cpu().sum(0) + prev.float().cpu())
+    # without colsum the plain kernel is unchanged
+    _check(ops.linear_wgrad(dy.cuda(), x.cuda(), max_ctas=max_ctas, split_k=-1), ref_w)

@@ -485,3 +485,93 @@ def test_attn_fused_fwd_matches_unfused(cuda_lib, T, p):
     for b in range(B):
         tail = probs.float().view(B, H, T, ld)[b, :, :, int(klen[b]):]
         assert tail.numel() == 0 or float(tail.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("T,p", [(250, 0.1), (256, 0.0), (100, 0.1), (129, 0.0), (37, 0.1)])
+def test_attn_fused_fwd_lse_and_fused_bwd_match_fp32_reference(cuda_lib, T, p):
+    """Fused attention forward (row log-sum-exp kept instead of the probabilities) and fused backward (one 2-CTA cluster
+    per (utterance, head): P recomputed from lse, dQ / dK / dV) against a plain PyTorch fp32 restatement of fairseq
+    MultiheadAttention's core (multihead_attention.py:372-416) using the SAME dropout mask (read off the kernel's own
+    probs / probs_drop outputs).  ctx / dq / dk / dv rel-L2 <= 2e-2 (bf16 operands), lse abs 2e-3."""
+    from s2t_b200 import ops
+    B, H, dk = 3, 4, 64
+    C = H * dk
+    g = torch.Generator().manual_seed(T)
+    qkv = (torch.randn((B * T, 3 * C), generator=g) * 0.7).to(BF16).cuda()
+    lens = torch.tensor([T, max(1, T - 17), max(1, T // 3)], dtype=torch.int32).cuda()
+    ld = (T + 7) // 8 * 8
+    spec = (p, 1234, 77, None) if p > 0 else None
+    probs = torch.zeros((B * H, T, ld), device="cuda", dtype=BF16)
+    probs_d = torch.zeros_like(probs)
+    lse = torch.zeros((B * H * T,), device="cuda", dtype=torch.float32)
+    ctx = torch.zeros((B * T, C), device="cuda", dtype=BF16)
+    scale = dk ** -0.5
+    ops.attn_fused_fwd(qkv, C, lens, B, H, T, dk, probs=probs, probs_drop=probs_d if p > 0 else None, lse=lse, ctx=ctx,
+                       scale=scale, dropout=spec)
+    # the production call: no probabilities written, same ctx and lse
+    ctx2, lse2 = torch.zeros_like(ctx), torch.zeros_like(lse)
+    ops.attn_fused_fwd(qkv, C, lens, B, H, T, dk, lse=lse2, ctx=ctx2, scale=scale, dropout=spec)
+    torch.cuda.synchronize()
+    assert torch.equal(ctx, ctx2) and torch.equal(lse, lse2)
+    # fp32 reference
+    x = qkv.float().view(B, T, 3, H, dk).permute(2, 0, 3, 1, 4)          # (3, B, H, T, dk)
+    q, k, v = x[0], x[1], x[2]
+    s = (q @ k.transpose(-1, -2)) * scale
+    kmask = torch.arange(T, device="cuda")[None, :] >= lens[:, None]      # (B, T) True = padded key
+    s = s.masked_fill(kmask[:, None, None, :], float("-inf"))
+    P = torch.softmax(s, dim=-1)
+    ref_lse = torch.logsumexp(s, dim=-1)
+    assert (lse.view(B, H, T) - ref_lse).abs().max() <= 2e-3
+    pr, pd = probs.float().view(B, H, T, ld)[..., :T], probs_d.float().view(B, H, T, ld)[..., :T]
+    if p > 0:
+        M = torch.where(pr > 0, (pd != 0).float() / (1 - p), torch.full_like(pr, 1 / (1 - p)))
+        keep = float((pd[pr > 0] != 0).float().mean())
+        assert abs(keep - (1 - p)) < 0.02
+    else:
+        M = torch.ones_like(pr)
+    Pd = P * M
+    ref_ctx = (Pd @ v).permute(0, 2, 1, 3).reshape(B * T, C)
+    rel = lambda a, b: float((a.float() - b).norm() / (b.norm() + 1e-12))
+    assert rel(ctx, ref_ctx) <= 2e-2
+    d_o = (torch.randn((B * T, C), generator=g) * 0.5).to(BF16).cuda()
+    go = d_o.float().view(B, T, H, dk).permute(0, 2, 1, 3)               # (B, H, T, dk)
+    dV = Pd.transpose(-1, -2) @ go
+    dP = (go @ v.transpose(-1, -2)) * M
+    dS = P * (dP - (dP * P).sum(-1, keepdim=True))
+    dQ = (dS @ k) * scale
+    dK = (dS.transpose(-1, -2) @ q) * scale
+    out = torch.full((B * T, 3 * C), float("nan"), device="cuda", dtype=BF16)
+    ops.attn_fused_bwd(qkv, C, ctx, d_o, lse, lens, B, H, T, dk, out=out, scale=scale, dropout=spec)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    got = out.float().view(B, T, 3, H, dk).permute(2, 0, 3, 1, 4)
+    for name, mine, ref in (("dq", got[0], dQ), ("dk", got[1], dK), ("dv", got[2], dV)):
+        assert rel(mine, ref) <= 2e-2, (name, rel(mine, ref))
+    # padded keys receive no gradient
+    assert float(got[1][2, :, int(lens[2]):].abs().max()) == 0.0 and float(got[2][2, :, int(lens[2]):].abs().max()) == 0.0
+
+
+def test_layernorm_bwd_reduce_batched(cuda_lib):
+    """One launch reduces the dgamma / dbeta partials of many LayerNorm instances (different widths, row counts,
+    accumulate flags) — equal to the per-instance reduction."""
+    from s2t_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    jobs, want = [], []
+    for i, (rows, C) in enumerate([(2000, 256), (998, 512), (7, 8), (4001, 256)] * 10):          # 40 jobs: two launches
+        x = torch.randn((rows, C), generator=g).to(BF16).cuda()
+        dy = torch.randn((rows, C), generator=g).to(BF16).cuda()
+        gamma = torch.rand(C, generator=g).to(BF16).cuda()
+        stats = torch.stack([x.float().mean(-1), 1.0 / torch.sqrt(x.float().var(-1, unbiased=False) + 1e-5)], dim=1).contiguous()
+        n = ops._lib.load().s2t_layernorm_bwd_partials(rows, C)
+        part = torch.empty((n, 2, C), device="cuda", dtype=torch.float32)
+        ops.layernorm_bwd(dy, x, gamma, stats, None, None, partials=part, reduce=False)
+        acc = i % 3 == 0
+        dg0, db0 = torch.randn(C, generator=g).to(BF16).cuda(), torch.randn(C, generator=g).to(BF16).cuda()
+        dg1, db1 = dg0.clone(), db0.clone()
+        ops.layernorm_bwd_reduce(part, rows, C, dg0, db0, accumulate=acc)
+        jobs.append((part, rows, C, dg1, db1, acc))
+        want.append((dg0, db0))
+    ops.layernorm_bwd_reduce_batched(jobs)
+    torch.cuda.synchronize()
+    for (_, _, _, dg1, db1, _), (dg0, db0) in zip(jobs, want):
+        assert torch.equal(dg1, dg0) and torch.equal(db1, db0)
