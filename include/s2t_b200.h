@@ -101,6 +101,10 @@ typedef struct s2t_gemm_args {
   /* dW = dY^T X this is the bias gradient of the same nn.Linear, summed from the dY tiles the kernel stages anyway   */
   void* colsum;
   int colsum_accumulate;
+  /* 1 = let the NEXT kernel of the stream start (programmatic dependent launch) only once every CTA has issued its last  */
+  /* operand load instead of at entry: for GEMMs on a side stream with an SM share, whose successor's waiting CTAs would  */
+  /* otherwise occupy SMs of the critical chain for the whole duration of this kernel                                    */
+  int late_trigger;
 } s2t_gemm_args;
 
 int s2t_gemm_bf16(const s2t_gemm_args* args, void* stream);

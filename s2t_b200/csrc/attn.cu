@@ -51,7 +51,8 @@ struct AttnParams {
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_fused_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                      const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
+                      const AttnParams p) {
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
@@ -76,6 +77,7 @@ attn_fused_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmO);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, 512);     // S: columns [0, 256), O: columns [256, 320)
@@ -198,24 +200,30 @@ attn_fused_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     fence_proxy_async();
     tc_fence_before();
     mbar_arrive(&bars[3]);
-    // epilogue: context rows (two 32-column chunks: parts 0 and 1)
+    // epilogue: context rows (parts 0 and 1: 32 columns each) -> bf16 tile in the retired Q buffer (swizzled 128-byte rows)
+    // -> ONE TMA store (coalesced, clipped at T by the tensor map) instead of 32 row-strided 16-byte stores per warp
     if (part < 2) {
       mbar_wait(&bars[4], 0);
       tc_fence_after();
       uint32_t rg[32];
       tmem_ld_32x32(t_addr + 256 + part * 32, rg);
       tmem_ld_wait();
-      if (row_ok) {
-        __nv_bfloat16* o = p.ctx + (static_cast<long long>(b) * p.T + i) * p.ldctx + h * kDk + part * 32;
+      uint8_t* orow = sQ + row * 128;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint4 ov;
-          ov.x = pack_bf16(__uint_as_float(rg[g * 8 + 0]), __uint_as_float(rg[g * 8 + 1]));
-          ov.y = pack_bf16(__uint_as_float(rg[g * 8 + 2]), __uint_as_float(rg[g * 8 + 3]));
-          ov.z = pack_bf16(__uint_as_float(rg[g * 8 + 4]), __uint_as_float(rg[g * 8 + 5]));
-          ov.w = pack_bf16(__uint_as_float(rg[g * 8 + 6]), __uint_as_float(rg[g * 8 + 7]));
-          *reinterpret_cast<uint4*>(o + g * 8) = ov;
-        }
+      for (int g = 0; g < 4; ++g) {
+        uint4 ov;
+        ov.x = pack_bf16(__uint_as_float(rg[g * 8 + 0]), __uint_as_float(rg[g * 8 + 1]));
+        ov.y = pack_bf16(__uint_as_float(rg[g * 8 + 2]), __uint_as_float(rg[g * 8 + 3]));
+        ov.z = pack_bf16(__uint_as_float(rg[g * 8 + 4]), __uint_as_float(rg[g * 8 + 5]));
+        ov.w = pack_bf16(__uint_as_float(rg[g * 8 + 6]), __uint_as_float(rg[g * 8 + 7]));
+        *reinterpret_cast<uint4*>(orow + (((part * 4 + g) ^ (row & 7)) << 4)) = ov;
+      }
+      fence_proxy_async();
+      named_bar_sync(5, 256);
+      if (warp == 2 && lane == 0) {
+        tma_store_4d(&tmO, sQ, 0, m0, h, b);
+        tma_store_commit();
+        tma_store_wait_read<0>();
       }
     }
   }
@@ -257,13 +265,24 @@ struct AttnBwdParams {
   unsigned long long seed;
   const unsigned long long* seed_off;
   uint32_t stream_id;
+  unsigned long long* trace;   // debug phase stamps of CTA (0,0,0) (S2T_GEMM_TRACE=1)
 };
+
+__device__ __forceinline__ void attn_stamp(unsigned long long* trace, int slot) {
+  if (trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    trace[slot] = t;
+  }
+}
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                       const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
-                      const AttnBwdParams p) {
+                      const __grid_constant__ CUtensorMap tmDQ, const __grid_constant__ CUtensorMap tmDK,
+                      const __grid_constant__ CUtensorMap tmDV, const AttnBwdParams p) {
   pdl_launch_dependents();
+  if (threadIdx.x == 0) attn_stamp(p.trace, 0);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* sQ = smem;
@@ -289,6 +308,9 @@ attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     tma_prefetch_desc(&tmDO);
+    tma_prefetch_desc(&tmDQ);
+    tma_prefetch_desc(&tmDK);
+    tma_prefetch_desc(&tmDV);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, 512);     // S: [0, 256), dP: [256, 512); then dQ [0, 64), dV halves [64, 192), dK halves [192, 320)
@@ -298,7 +320,9 @@ attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) attn_stamp(p.trace, 1);
   pdl_wait();
+  if (threadIdx.x == 0) attn_stamp(p.trace, 2);
 
   const int q = warp & 3;
   const int part = warp >= 2 ? (warp - 2) >> 2 : 0;
@@ -313,6 +337,7 @@ attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       tma_load_4d(sK, &tmK, &bars[0], 0, 0, h, b);
       tma_load_4d(sV, &tmV, &bars[0], 0, 0, h, b);
       mbar_wait(&bars[0], 0);
+      attn_stamp(p.trace, 3);
       tc_fence_after();
       const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK), va = smem_u32(sV), doa = smem_u32(sDO);
       {
@@ -328,6 +353,7 @@ attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         umma_commit(&bars[1]);
       }
       mbar_wait(&bars[2], 0);            // Pd and dS tiles are in shared memory, S / dP have been read out of TMEM
+      attn_stamp(p.trace, 5);
       tc_fence_after();
       const uint32_t pa = smem_u32(sPd), sa = smem_u32(sDS);
       {
@@ -369,23 +395,34 @@ attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     const int tk8 = (p.T + 7) & ~7;
     const unsigned long long grp_row = static_cast<unsigned long long>(grow) * (tk8 >> 3);
     const int col0 = part * 64;
-    // delta_i = dO_i . O_i (64 products; every thread of the row computes it itself: 16 L2-resident 16-byte loads whose
-    // latency hides behind the operand loads and the first two MMAs — no shared-memory exchange, no barrier)
+    // delta_i = dO_i . O_i for the 32 rows of this warp, with coalesced loads: one load instruction covers four whole
+    // 128-byte rows (8 lanes x 16 bytes each); the 8-lane partial dots are folded by shuffles and row L is handed to lane L
+    // (a thread-per-row walk costs 32 cache lines per load instruction: 4 us of LSU time per CTA)
     float delta = 0.f, lse = 0.f;
-    if (row_ok) {
-      const long long off = (static_cast<long long>(b) * p.T + i) * p.ldo + h * kDk;
-      const uint4* po = reinterpret_cast<const uint4*>(p.o + off);
-      const uint4* pg = reinterpret_cast<const uint4*>(p.d_o + off);
+    {
+      const int sub = lane >> 3, l8 = lane & 7;
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        const uint4 ov = po[c], gv = pg[c];
-        delta += bf16_lo(ov.x) * bf16_lo(gv.x) + bf16_hi(ov.x) * bf16_hi(gv.x) + bf16_lo(ov.y) * bf16_lo(gv.y) +
-                 bf16_hi(ov.y) * bf16_hi(gv.y) + bf16_lo(ov.z) * bf16_lo(gv.z) + bf16_hi(ov.z) * bf16_hi(gv.z) +
-                 bf16_lo(ov.w) * bf16_lo(gv.w) + bf16_hi(ov.w) * bf16_hi(gv.w);
+      for (int itr = 0; itr < 8; ++itr) {
+        const int gi = m0 + q * 32 + itr * 4 + sub;
+        float d = 0.f;
+        if (gi < p.T) {
+          const long long off = (static_cast<long long>(b) * p.T + gi) * p.ldo + h * kDk + l8 * 8;
+          const uint4 ov = *reinterpret_cast<const uint4*>(p.o + off);
+          const uint4 gv = *reinterpret_cast<const uint4*>(p.d_o + off);
+          d = bf16_lo(ov.x) * bf16_lo(gv.x) + bf16_hi(ov.x) * bf16_hi(gv.x) + bf16_lo(ov.y) * bf16_lo(gv.y) +
+              bf16_hi(ov.y) * bf16_hi(gv.y) + bf16_lo(ov.z) * bf16_lo(gv.z) + bf16_hi(ov.z) * bf16_hi(gv.z) +
+              bf16_lo(ov.w) * bf16_lo(gv.w) + bf16_hi(ov.w) * bf16_hi(gv.w);
+        }
+        d += __shfl_xor_sync(0xffffffffu, d, 1);
+        d += __shfl_xor_sync(0xffffffffu, d, 2);
+        d += __shfl_xor_sync(0xffffffffu, d, 4);
+        const float v = __shfl_sync(0xffffffffu, d, (lane & 3) * 8);     // row itr*4 + (lane & 3)
+        if ((lane >> 2) == itr) delta = v;
       }
-      lse = p.lse[grow];
+      if (row_ok) lse = p.lse[grow];
     }
     mbar_wait(&bars[1], 0);
+    if (threadIdx.x == 64) attn_stamp(p.trace, 4);
     tc_fence_after();
     uint8_t* pd_dst = sPd + part * 16384 + row * 128;
     uint8_t* ds_dst = sDS + part * 16384 + row * 128;
@@ -423,23 +460,28 @@ attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     tc_fence_before();
     mbar_arrive(&bars[2]);
     mbar_wait(&bars[3], 0);
+    if (threadIdx.x == 64) attn_stamp(p.trace, 6);
     tc_fence_after();
-    // dQ rows of this tile (parts 0 and 1: 32 columns each)
+    // dQ rows of this tile (parts 0 and 1: 32 columns each) -> bf16 tile in the retired Q buffer -> one TMA store
     if (part < 2) {
       uint32_t rg[32];
       tmem_ld_32x32(t_addr + part * 32, rg);
       tmem_ld_wait();
-      if (row_ok) {
-        __nv_bfloat16* o = p.dqkv + (static_cast<long long>(b) * p.T + i) * p.ldg + h * kDk + part * 32;
+      uint8_t* orow = sQ + row * 128;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint4 ov;
-          ov.x = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 0]), p.scale * __uint_as_float(rg[g * 8 + 1]));
-          ov.y = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 2]), p.scale * __uint_as_float(rg[g * 8 + 3]));
-          ov.z = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 4]), p.scale * __uint_as_float(rg[g * 8 + 5]));
-          ov.w = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 6]), p.scale * __uint_as_float(rg[g * 8 + 7]));
-          *reinterpret_cast<uint4*>(o + g * 8) = ov;
-        }
+      for (int g = 0; g < 4; ++g) {
+        uint4 ov;
+        ov.x = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 0]), p.scale * __uint_as_float(rg[g * 8 + 1]));
+        ov.y = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 2]), p.scale * __uint_as_float(rg[g * 8 + 3]));
+        ov.z = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 4]), p.scale * __uint_as_float(rg[g * 8 + 5]));
+        ov.w = pack_bf16(p.scale * __uint_as_float(rg[g * 8 + 6]), p.scale * __uint_as_float(rg[g * 8 + 7]));
+        *reinterpret_cast<uint4*>(orow + (((part * 4 + g) ^ (row & 7)) << 4)) = ov;
+      }
+      fence_proxy_async();
+      named_bar_sync(5, 256);
+      if (warp == 2 && lane == 0) {
+        tma_store_4d(&tmDQ, sQ, 0, m0, h, b);
+        tma_store_commit();
       }
     }
   }
@@ -453,7 +495,9 @@ attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   }
   tc_fence_before();
   __syncwarp();
+  if (threadIdx.x == 64) attn_stamp(p.trace, 7);
   cluster_sync_all();
+  if (threadIdx.x == 64) attn_stamp(p.trace, 8);
   // which accumulator a thread moves: parts 0 / 1 = dV columns [0, 32) / [32, 64), parts 2 / 3 = dK columns likewise
   const int which_k = part >> 1;                  // 0 = dV, 1 = dK
   const int chalf = part & 1;
@@ -473,32 +517,41 @@ attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   }
   tc_fence_before();
   __syncwarp();
+  if (threadIdx.x == 64) attn_stamp(p.trace, 9);
   cluster_sync_all();        // partials of my key half have landed in sPd
+  if (threadIdx.x == 64) attn_stamp(p.trace, 10);
   if (warp >= 2) {
     tc_fence_after();
     uint32_t rg[32];
     tmem_ld_32x32(t_addr + 64 + which_k * 128 + rank * 64 + chalf * 32, rg);   // my own partial of my key half
     tmem_ld_wait();
-    const int j = rank * 128 + row;                // key row this thread finalises
-    if (j < p.T) {
-      const float sc = which_k ? p.scale : 1.f;
-      const float4* recv = reinterpret_cast<const float4*>(sPd);
-      __nv_bfloat16* o = p.dqkv + (static_cast<long long>(b) * p.T + j) * p.ldg + (which_k ? p.C : 2 * p.C) + h * kDk + chalf * 32;
+    // my key half, summed, as a bf16 tile in the retired V (dV) / K (dK) buffer -> one TMA store each (clipped at T)
+    const float sc = which_k ? p.scale : 1.f;
+    const float4* recv = reinterpret_cast<const float4*>(sPd);
+    uint8_t* orow = (which_k ? sK : sV) + row * 128;
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const float4 r0 = recv[(part * 8 + 2 * g) * 128 + row], r1 = recv[(part * 8 + 2 * g + 1) * 128 + row];
-        uint4 ov;
-        ov.x = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 0]) + r0.x), sc * (__uint_as_float(rg[g * 8 + 1]) + r0.y));
-        ov.y = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 2]) + r0.z), sc * (__uint_as_float(rg[g * 8 + 3]) + r0.w));
-        ov.z = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 4]) + r1.x), sc * (__uint_as_float(rg[g * 8 + 5]) + r1.y));
-        ov.w = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 6]) + r1.z), sc * (__uint_as_float(rg[g * 8 + 7]) + r1.w));
-        *reinterpret_cast<uint4*>(o + g * 8) = ov;
-      }
+    for (int g = 0; g < 4; ++g) {
+      const float4 r0 = recv[(part * 8 + 2 * g) * 128 + row], r1 = recv[(part * 8 + 2 * g + 1) * 128 + row];
+      uint4 ov;
+      ov.x = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 0]) + r0.x), sc * (__uint_as_float(rg[g * 8 + 1]) + r0.y));
+      ov.y = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 2]) + r0.z), sc * (__uint_as_float(rg[g * 8 + 3]) + r0.w));
+      ov.z = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 4]) + r1.x), sc * (__uint_as_float(rg[g * 8 + 5]) + r1.y));
+      ov.w = pack_bf16(sc * (__uint_as_float(rg[g * 8 + 6]) + r1.z), sc * (__uint_as_float(rg[g * 8 + 7]) + r1.w));
+      *reinterpret_cast<uint4*>(orow + (((chalf * 4 + g) ^ (row & 7)) << 4)) = ov;
     }
+    fence_proxy_async();
+    named_bar_sync(6 + which_k, 256);
+    if ((warp == 2 || warp == 10) && lane == 0) {
+      tma_store_4d(which_k ? &tmDK : &tmDV, which_k ? sK : sV, 0, rank * 128, h, b);
+      tma_store_commit();
+    }
+    if (warp == 2 && lane == 0) tma_store_wait_read<0>();      // also covers the dQ store issued by this thread
+    if (warp == 10 && lane == 0) tma_store_wait_read<0>();
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, 512);
+  if (threadIdx.x == 0) attn_stamp(p.trace, 11);
 }
 
 }  // namespace
@@ -528,6 +581,9 @@ extern "C" int s2t_attn_fused_fwd(const void* qkv, long long ldqkv, int C, void*
   if (rc) return rc;
   rc = make_operand_map(&tv, base + 2 * C, kDk, T, ldqkv, heads, kDk, batch, 1ll * T * ldqkv, 64);
   if (rc) return rc;
+  CUtensorMap to;
+  rc = make_operand_map(&to, ctx, kDk, T, ldctx, heads, kDk, batch, 1ll * T * ldctx, kTq);
+  if (rc) return rc;
   AttnParams p;
   memset(&p, 0, sizeof(p));
   p.probs = reinterpret_cast<__nv_bfloat16*>(probs);
@@ -550,7 +606,7 @@ extern "C" int s2t_attn_fused_fwd(const void* qkv, long long ldqkv, int C, void*
     configured = true;
   }
   S2T_LAUNCH(attn_fused_fwd_kernel, dim3((T + kTq - 1) / kTq, heads, batch), kAttnThreads, kAttnSmem,
-             reinterpret_cast<cudaStream_t>(stream), tq, tk, tv, p);
+             reinterpret_cast<cudaStream_t>(stream), tq, tk, tv, to, p);
   return 0;
 }
 
@@ -578,6 +634,14 @@ extern "C" int s2t_attn_fused_bwd(const void* qkv, long long ldqkv, int C, const
   if (rc) return rc;
   rc = make_operand_map(&tdo, d_o, kDk, T, ldo, heads, kDk, batch, 1ll * T * ldo, kTq);
   if (rc) return rc;
+  CUtensorMap tdq, tdk, tdv;
+  const __nv_bfloat16* gbase = reinterpret_cast<const __nv_bfloat16*>(dqkv);
+  rc = make_operand_map(&tdq, gbase, kDk, T, ldg, heads, kDk, batch, 1ll * T * ldg, kTq);
+  if (rc) return rc;
+  rc = make_operand_map(&tdk, gbase + C, kDk, T, ldg, heads, kDk, batch, 1ll * T * ldg, 128);
+  if (rc) return rc;
+  rc = make_operand_map(&tdv, gbase + 2 * C, kDk, T, ldg, heads, kDk, batch, 1ll * T * ldg, 128);
+  if (rc) return rc;
   AttnBwdParams p;
   memset(&p, 0, sizeof(p));
   p.o = reinterpret_cast<const __nv_bfloat16*>(o);
@@ -595,6 +659,7 @@ extern "C" int s2t_attn_fused_bwd(const void* qkv, long long ldqkv, int C, const
   p.seed = seed;
   p.seed_off = seed_offset;
   p.stream_id = stream_id;
+  p.trace = trace_buffer();
   static bool configured = false;
   if (!configured) {
     S2T_CHECK_CUDA(cudaFuncSetAttribute(attn_fused_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
@@ -615,6 +680,6 @@ extern "C" int s2t_attn_fused_bwd(const void* qkv, long long ldqkv, int C, const
   attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
   cfg.numAttrs = 2;
-  S2T_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_fused_bwd_kernel, tq, tk, tv, tdo, p));
+  S2T_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_fused_bwd_kernel, tq, tk, tv, tdo, tdq, tdk, tdv, p));
   return 0;
 }

@@ -56,6 +56,7 @@ __device__ __forceinline__ void pdl_entry() {
 }
 
 bool pdl_enabled();   // capi.cu
+unsigned long long* trace_buffer();   // gemm.cu: 16 globaltimer slots (S2T_GEMM_TRACE=1), else nullptr
 
 // Build (or fetch from the cache) the 4-D SWIZZLE_128B tensor map of one bf16 (or fp32) matrix operand: `inner` contiguous
 // elements x `outer` rows of stride `ld`, two batch dimensions; TMA box = 64 (32 for fp32) x box_outer.  gemm.cu

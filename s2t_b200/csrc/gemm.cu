@@ -29,7 +29,8 @@ constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kGemmThreads = 320;    // split-K kernel: TMA warp, MMA warp, 8 epilogue warps
 constexpr int kEpiWarps = 8;
-constexpr int kColsumWarps = 4;      // persistent kernel only: column sums of the A operand (bias gradients), see below
+constexpr int kColsumWarps = 2;      // persistent kernel only: column sums of the A operand (bias gradients), see below;
+                                     // two warps keep the CTA at 384 threads = 170 registers per thread (no epilogue spills)
 constexpr int kGemmThreadsP = kGemmThreads + 32 * kColsumWarps;
 
 struct GemmKernelParams {
@@ -64,6 +65,7 @@ struct GemmKernelParams {
   // same layer, summed from the dY tiles the main loop stages in shared memory anyway (no separate pass over dY)
   __nv_bfloat16* colsum;
   int colsum_accumulate;
+  int late_trigger;   // release the dependent launch when this CTA has issued its last operand load, not at entry
 };
 
 // GATE = 1: the persistent kernel stages the epilogue's gate operand through shared memory by TMA (32 KB: 4 lane
@@ -217,7 +219,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const GemmKernelParams p) {
   constexpr int kGateTma = epi_gate_tma(EPI);
   using Cfg = GemmCfg<BN, kGateTma>;
-  pdl_launch_dependents();   // the next kernel's set-up may overlap this one (common.cuh, PDL)
+  // the next kernel's set-up may overlap this one (common.cuh, PDL) — except behind a side-stream GEMM that was given an
+  // SM share (late_trigger): its successor's CTAs would sit on SMs the latency-critical chain needs while they wait
+  if (!p.late_trigger) pdl_launch_dependents();
   if (threadIdx.x == 0) trace_stamp(p, 0);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -305,6 +309,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         if (tile == static_cast<int>(blockIdx.x)) trace_stamp(p, 3);
       }
+      // late trigger: every operand load of this CTA is in flight — what is left is the pipeline drain and the last
+      // epilogue (~2-3 us), about the launch latency of the dependent kernel, whose CTAs then wait only briefly
+      if (p.late_trigger) pdl_launch_dependents();
     }
   } else if (warp == 1) {
     // ------------------------------ MMA issuer --------------------------------
@@ -347,12 +354,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp >= 2 + kEpiWarps) {
     // ------------------------------ column sums of A (bias gradient) ----------
-    // 128 threads = the 128 M-columns of the tile.  A stage holds A as [64 k-rows][64 m] x 2 chunks, 128-byte rows with
-    // the 16-byte chunk index XORed by (k & 7); thread m adds its column of every stage of the tiles with n0 == 0.
+    // A stage = A as [64 k-rows][64 m] x 2 chunks, 128-byte rows, 16-byte chunk index XORed by (k & 7).  Warp w owns the
+    // 64-column chunk w: lane = cl * 8 + g reads the 16-byte pieces cl and cl + 4 of the rows k = 8 kk + g, so the eight
+    // lanes of a quarter-warp phase hit eight different piece positions (conflict-free) and the swizzle term is a per-lane
+    // constant; 16 LDS.128 + 128 adds per stage and lane, the 8 row groups are folded by shuffles at the tile end.
     if (A_MN && p.colsum != nullptr) {
-      const int cw = (warp - 2 - kEpiWarps) * 32 + lane;
-      const uint32_t coff = static_cast<uint32_t>((cw >> 6) * (kBK * 128) + (cw & 7) * 2);
-      const int cchunk = (cw & 63) >> 3;
+      const int cwarp = warp - 2 - kEpiWarps;
+      const int g = lane & 7, cl = lane >> 3;
+      const uint32_t cbase = static_cast<uint32_t>(cwarp * (kBK * 128) + g * 128);
+      const uint32_t off0 = cbase + ((cl ^ g) << 4), off1 = cbase + (((cl + 4) ^ g) << 4);
       uint32_t it = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int r = tile % tiles_per_z;
@@ -361,27 +371,45 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           continue;
         }
         const int m0 = (r % tiles_m) * kBM;
-        float acc = 0.f;
+        float acc[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc[j] = 0.f;
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % Cfg::kStages;
           const uint32_t ph = (it / Cfg::kStages) & 1;
           mbar_wait(&full_bar[s], ph);
-          const uint8_t* a_src = smem + s * Cfg::kStageBytes + coff;
-          float a0 = 0.f, a1 = 0.f;
-#pragma unroll 16
-          for (int k = 0; k < kBK; k += 2) {
-            const uint16_t v0 = *reinterpret_cast<const uint16_t*>(a_src + k * 128 + ((cchunk ^ (k & 7)) << 4));
-            const uint16_t v1 = *reinterpret_cast<const uint16_t*>(a_src + (k + 1) * 128 + ((cchunk ^ ((k + 1) & 7)) << 4));
-            a0 += __uint_as_float(static_cast<uint32_t>(v0) << 16);
-            a1 += __uint_as_float(static_cast<uint32_t>(v1) << 16);
+          const uint8_t* a_src = smem + s * Cfg::kStageBytes;
+#pragma unroll
+          for (int kk = 0; kk < kBK / 8; ++kk) {
+            const uint4 v = *reinterpret_cast<const uint4*>(a_src + off0 + kk * 1024);
+            const uint4 w = *reinterpret_cast<const uint4*>(a_src + off1 + kk * 1024);
+            acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
+            acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z); acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
+            acc[8] += bf16_lo(w.x); acc[9] += bf16_hi(w.x); acc[10] += bf16_lo(w.y); acc[11] += bf16_hi(w.y);
+            acc[12] += bf16_lo(w.z); acc[13] += bf16_hi(w.z); acc[14] += bf16_lo(w.w); acc[15] += bf16_hi(w.w);
           }
-          acc += a0 + a1;
           __syncwarp();
           if (lane == 0) mbar_arrive(&empty_bar[s]);
         }
-        if (m0 + cw < p.M) {
-          if (p.colsum_accumulate) acc += __bfloat162float(p.colsum[m0 + cw]);
-          p.colsum[m0 + cw] = __float2bfloat16(acc);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
+          acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 2);
+          acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 4);
+        }
+        if (g == 0) {
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const int col = m0 + cwarp * 64 + (cl + 4 * hh) * 8;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              if (col + j < p.M) {
+                float v = acc[hh * 8 + j];
+                if (p.colsum_accumulate) v += __bfloat162float(p.colsum[col + j]);
+                p.colsum[col + j] = __float2bfloat16(v);
+              }
+            }
+          }
         }
       }
     }
@@ -988,8 +1016,12 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUten
 
 using namespace s2t;
 
-// Debug phase trace (S2T_GEMM_TRACE=1): 16 globaltimer stamps written by CTA 0 of the last persistent-kernel launch.
-static unsigned long long* gemm_trace_buffer() {
+// Debug phase trace (S2T_GEMM_TRACE=1): 16 globaltimer stamps written by CTA 0 of the last traced launch.
+namespace s2t {
+unsigned long long* trace_buffer();
+}
+static unsigned long long* gemm_trace_buffer() { return s2t::trace_buffer(); }
+unsigned long long* s2t::trace_buffer() {
   static unsigned long long* buf = nullptr;
   static int init = 0;
   if (!init) {
@@ -1124,6 +1156,7 @@ extern "C" int s2t_gemm_bf16(const s2t_gemm_args* g, void* stream_) {
   kp.trace = gemm_trace_buffer();
   kp.colsum = reinterpret_cast<__nv_bfloat16*>(g->colsum);
   kp.colsum_accumulate = g->colsum_accumulate;
+  kp.late_trigger = g->late_trigger;
   kp.out = g->out;
   kp.ldc = g->ldc; kp.c_bs1 = nb1 > 1 ? g->c_bs1 : 0; kp.c_bs2 = nb2 > 1 ? g->c_bs2 : 0;
   {

@@ -219,9 +219,10 @@ class _Stage(_Bufs):
         self.x = [e(R, C) for _ in range(n_layers + 1)]     # x[j] = input of layer j, x[-1] = stage output
         self.scores = z(B * H, T, self.ld)
         self.g_p, self.g_s = z(B * H, T, self.ld), z(B * H, T, self.ld)
-        self.pool = [e(R, C) for _ in range(10)]
+        self.pool = [e(R, C) for _ in range(18)]      # incl. one block's worth in quarantine (engine._end_block)
         self._pool_ids = {id(t) for t in self.pool}
-        self.g_f = e(R, F)
+        self.g_fs = [e(R, F), e(R, F)]       # FFN hidden gradient: two buffers, alternated per FFN block (engine._end_block)
+        self._g_f_i = 0
         self.g_qkv = e(R, 3 * C)
         lib = ops._lib.load()
         cs = max(lib.s2t_colsum_workspace_floats(R, 3 * C), lib.s2t_colsum_workspace_floats(R, F))
@@ -600,6 +601,9 @@ class S2TEncoderEngine:
         self._ln_pending = False
         self._ln_jobs: list = []
         self._forked: set = set()
+        self.lag_join = os.environ.get("S2T_LAG_JOIN", "1") == "1"
+        self._lag_events: list = []
+        self._lag_stage, self._lag_bufs = None, ()
         self.dp = None               # dp.BucketedAllReduce when data parallel
         self.init_parameters()
 
@@ -1254,21 +1258,57 @@ class S2TEncoderEngine:
         self._forked.add(i)
         return torch.cuda.stream(side)
 
-    def _join(self) -> None:
-        """The main stream waits for all side-stream work forked since the last join."""
+    def _join(self, only: Optional[Tuple[int, ...]] = None) -> None:
+        """The main stream waits for the side-stream work forked since the last join (``only``: just those side streams —
+        a data dependency on one of them must not wait for the weight gradients on another)."""
         main = torch.cuda.current_stream()
         for i in sorted(self._forked):
-            main.wait_stream(self._side[i])
+            if only is None or i in only:
+                main.wait_stream(self._side[i])
+        self._forked = set() if only is None else {i for i in self._forked if i not in only}
+
+    def _end_block(self, St: _Stage, *bufs: torch.Tensor) -> None:
+        """End of a residual block's backward.  Its side-stream work (weight / bias gradients) only READS buffers of the
+        block, so the dgrad chain need not wait for it: the join is LAGGED by one block — here the chain waits for the side
+        work of the PREVIOUS block (normally long finished), and this block's pool buffers stay quarantined until the
+        next call.  Stage scratch read by side work (g_f, g_qkv, g_2c) is not rewritten before two blocks later (g_f
+        alternates between two buffers: macaron FFN blocks are adjacent).  S2T_LAG_JOIN=0: join at once."""
+        if not (self.multi_stream and self.lag_join):
+            self._join()
+            St.give(*bufs)
+            return
+        main = torch.cuda.current_stream()
+        for ev in self._lag_events:
+            main.wait_event(ev)
+        if self._lag_stage is not None:
+            self._lag_stage.give(*self._lag_bufs)
+        self._lag_events = []
+        for i in sorted(self._forked):
+            ev = torch.cuda.Event()
+            ev.record(self._side[i])
+            self._lag_events.append(ev)
         self._forked.clear()
+        self._lag_stage, self._lag_bufs = St, bufs
+
+    def _join_all(self) -> None:
+        """Immediate join of everything outstanding (lagged block joins included)."""
+        self._join()
+        main = torch.cuda.current_stream()
+        for ev in self._lag_events:
+            main.wait_event(ev)
+        self._lag_events = []
+        if self._lag_stage is not None:
+            self._lag_stage.give(*self._lag_bufs)
+        self._lag_stage, self._lag_bufs = None, ()
 
     def _ready(self, first_name: str) -> None:
         """Everything at or after ``first_name`` in the flat gradient buffer is final."""
-        self._join()
         if self.grad_ready_hook is None:
-            return                       # single GPU: the LayerNorm reductions are collected at the end of backward
+            return                       # single GPU: side work and the LayerNorm reductions are collected at the end of backward
         off = self.store.offset(first_name)
         if self.dp is not None and self.grad_ready_hook == self.dp.on_ready and not self.dp.would_ship(off):
             return                       # no bucket completes here: nothing has to be final yet
+        self._join_all()
         self._join_ln()
         self.grad_ready_hook(off)
 
@@ -1422,6 +1462,8 @@ class S2TEncoderEngine:
         Critical chain: dropout' -> dgrad w_2 -> dgrad w_1 -> LayerNorm'; weight / bias gradients on side streams."""
         S = self.store
         t0, t1 = St.take(), St.take()
+        St._g_f_i ^= 1
+        g_f = St.g_fs[St._g_f_i]
         d2 = dyd if dyd is not None else self._branch_grad(dy, self._drop(site + 1), scale, t0)
         with self._fork(0):
             ops.linear_wgrad(d2, f, out=S.g(ffn + ".w_2.weight"), colsum=S.g(ffn + ".w_2.bias"))
@@ -1429,17 +1471,16 @@ class S2TEncoderEngine:
             # f = dropout(relu(h)) is positive exactly where h > 0 AND the element was kept, so the gate on f covers the
             # dropout mask too: no Philox regeneration in this epilogue, only the 1/(1-p) scale (folded into alpha)
             spec = self._drop(site)
-            ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=St.g_f, gate=f, gate_mode=ops.GATE_POSITIVE, ldg=St.F,
+            ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=g_f, gate=f, gate_mode=ops.GATE_POSITIVE, ldg=St.F,
                              alpha=1.0 / (1.0 - spec[0]) if spec else 1.0)
         else:
-            ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=St.g_f, gate=h, gate_mode=ops.GATE_SWISH_GRAD, ldg=St.F,
+            ops.linear_dgrad(d2, S.p(ffn + ".w_2.weight"), out=g_f, gate=h, gate_mode=ops.GATE_SWISH_GRAD, ldg=St.F,
                              dropout=self._drop(site))
         with self._fork(0):
-            ops.linear_wgrad(St.g_f, ln, out=S.g(ffn + ".w_1.weight"), colsum=S.g(ffn + ".w_1.bias"))
-        ops.linear_dgrad(St.g_f, S.p(ffn + ".w_1.weight"), out=t1)
+            ops.linear_wgrad(g_f, ln, out=S.g(ffn + ".w_1.weight"), colsum=S.g(ffn + ".w_1.bias"))
+        ops.linear_dgrad(g_f, S.p(ffn + ".w_1.weight"), out=t1)
         dx, dd = self._ln_bwd(St, t1, x, norm, st, dx_residual=dy, nxt=nxt)
-        self._join()
-        St.give(t0, t1, dy, dyd)
+        self._end_block(St, t0, t1, dy, dyd)
         return dx, dd
 
     def _conv_bwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, dy: torch.Tensor, dyd: Optional[torch.Tensor],
@@ -1463,8 +1504,7 @@ class S2TEncoderEngine:
         ops.linear_dgrad(St.g_2c, S.p(m + "pointwise_conv1.weight"), out=t2)
         ops.mask_rows_(t2.view(B, T, C), St.lens)
         dx, dd = self._ln_bwd(St, t2, x, p + "conv_norm", L.c_st, dx_residual=dy, nxt=nxt)
-        self._join()
-        St.give(t0, t1, t2, dy, dyd)
+        self._end_block(St, t0, t1, t2, dy, dyd)
         return dx, dd
 
     def _attn_bwd(self, P: Plan, St: _Stage, sp: _LayerSpec, L: _Bufs, dy: torch.Tensor, dyd: Optional[torch.Tensor],
@@ -1535,14 +1575,13 @@ class S2TEncoderEngine:
         a = sp.prefix + "self_attn."
         q = "linear_q" if c.attn_type == "rel_pos" else "q_proj"
         g_qkv = St.g_qkv
-        self._join()                                      # g_qkv is complete (dV / dK came from side streams)
+        self._join(only=(1, 2))                           # g_qkv is complete (unfused path: dV / dK came from side stream 2)
         with self._fork(0):
             ops.linear_wgrad(g_qkv, L.ln1, out=S.fused(a + q + ".weight", 3 * C, C, grad=True),
                              colsum=S.fused(a + q + ".bias", 3 * C, 0, grad=True))
         ops.linear_dgrad(g_qkv, S.fused(a + q + ".weight", 3 * C, C), out=t1)
         dx, dd = self._ln_bwd(St, t1, x, sp.prefix + "self_attn_layer_norm", L.st1, dx_residual=dy, nxt=nxt)
-        self._join()
-        St.give(t0, t1, dctx, dy, dyd)
+        self._end_block(St, t0, t1, dctx, dy, dyd)
         return dx, dd
 
     def _branch_spec(self, g: int, block: str):
@@ -1666,6 +1705,7 @@ class S2TEncoderEngine:
     def _backward(self, P: Plan, extra: Optional[torch.Tensor] = None) -> None:
         c = self.cfg
         self._ln_jobs = []
+        self._lag_events, self._lag_stage, self._lag_bufs = [], None, ()
         prev = ops.set_sm_shares(*(self.sm_shares if self.multi_stream else (0, 0, 0)))
         try:
             self._backward_body(P, extra)
@@ -1698,7 +1738,7 @@ class S2TEncoderEngine:
                 self._stem_s2t_bwd(P, d)
             else:
                 d = self._stem_pds_bwd(P, i, d)
-        self._join()
+        self._join_all()
         self._join_ln()
 
     # ------------------------------------------------------------------------------------------

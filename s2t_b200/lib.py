@@ -34,7 +34,7 @@ class GemmArgs(C.Structure):
         ("dropout_seed_offset", _vp),
         ("split_k", _i),
         ("max_ctas", _i),
-        ("colsum", _vp), ("colsum_accumulate", _i),
+        ("colsum", _vp), ("colsum_accumulate", _i), ("late_trigger", _i),
     ]
 
 

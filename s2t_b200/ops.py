@@ -63,6 +63,7 @@ def _drop(d):
 # SM shares for the duration of the engine's multi-stream backward pass (0 = the whole GPU): GEMMs of the dgrad chain are
 # bounded to ``chain`` CTAs and weight-gradient GEMMs (side streams) to ``wgrad`` CTAs without split-K, chain + wgrad =
 # the SM count, so that neither ever waits for an SM held by the other (every GEMM CTA needs a whole SM's shared memory).
+_late_trigger_side = os.environ.get("S2T_LATE_TRIGGER", "1") == "1"
 _default_max_ctas = 0
 _wgrad_max_ctas = 0
 _wgrad_split_k = 0
@@ -86,7 +87,7 @@ def gemm_raw(
     g_bs: Tuple[int, int] = (0, 0), dropout: Optional[Tuple[float, int, int]] = None,
     out_scale: float = 1.0, residual: Optional[torch.Tensor] = None, ldr: int = 0,
     r_bs: Tuple[int, int] = (0, 0), tile_n: int = 0, split_k: int = 0, max_ctas: int = 0,
-    colsum: Optional[torch.Tensor] = None, colsum_accumulate: bool = False,
+    colsum: Optional[torch.Tensor] = None, colsum_accumulate: bool = False, late_trigger: Optional[bool] = None,
 ) -> None:
     """out[z] = residual + out_scale*dropout(gate(act(alpha * A[z] @ B[z]^T + bias))) — see s2t_b200.h.
 
@@ -121,6 +122,9 @@ def gemm_raw(
     g.split_k = split_k
     g.max_ctas = max_ctas if max_ctas else _default_max_ctas
     g.colsum, g.colsum_accumulate = _p(colsum), int(colsum_accumulate)
+    if late_trigger is None:     # default: late for GEMMs that run with the side-stream (weight-gradient) SM share
+        late_trigger = _late_trigger_side and _wgrad_max_ctas > 0 and g.max_ctas == _wgrad_max_ctas
+    g.late_trigger = int(bool(late_trigger))
     _call("s2t_gemm_bf16", C.byref(g), _stream())
 
 
