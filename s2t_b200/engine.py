@@ -587,7 +587,7 @@ class S2TEncoderEngine:
         self.grad_ready_hook = None  # callable(offset): store.grad[offset:] is final (dp.BucketedAllReduce.on_ready)
         # fork/join streams: leaf work of the backward pass (weight / bias gradients) and independent attention
         # branches run beside the critical dgrad chain; captured into the CUDA graph as parallel branches
-        self.multi_stream = True
+        self.multi_stream = os.environ.get("S2T_MULTI_STREAM", "1") == "1"
         # attn.cu: one launch per layer and direction for selfattn with d_k 64 and T' <= 256 (S2T_FUSED_ATTN=0: the unfused
         # GEMM / softmax / GEMM form, which also serves every other shape)
         self.fused_attention = os.environ.get("S2T_FUSED_ATTN", "1") == "1"

@@ -63,7 +63,7 @@ def _drop(d):
 # SM shares for the duration of the engine's multi-stream backward pass (0 = the whole GPU): GEMMs of the dgrad chain are
 # bounded to ``chain`` CTAs and weight-gradient GEMMs (side streams) to ``wgrad`` CTAs without split-K, chain + wgrad =
 # the SM count, so that neither ever waits for an SM held by the other (every GEMM CTA needs a whole SM's shared memory).
-_late_trigger_side = os.environ.get("S2T_LATE_TRIGGER", "1") == "1"
+_late_trigger_side = os.environ.get("S2T_LATE_TRIGGER", "0") == "1"   # measured: early release + lagged joins is faster (1.73 vs 2.03 ms at C2)
 _default_max_ctas = 0
 _wgrad_max_ctas = 0
 _wgrad_split_k = 0
