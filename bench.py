@@ -545,7 +545,8 @@ def run_bucketed(a, torch, dist, cfg, world, rank, local, peaks):
     samples = synth_durations(a.utterances, 0)
     n_frames = np.array([frontend.num_frames(int(n)) for n in samples], dtype=np.int64)
     bs = BucketSet(max_frames=cfg.max_source_positions)
-    sched = rank_schedule(n_frames, a.max_tokens, world, rank, bsz_mult=8, buckets=bs)
+    sched = rank_schedule(n_frames, a.max_tokens, world, rank, bsz_mult=8, buckets=bs, pad_batch=True)
+    eng.plan_cache_bytes = int(float(os.environ.get("S2T_PLAN_CACHE_GB", "120")) * 2 ** 30)     # one plan per frame bucket fits
     n_batches_total = len(sched) * world
     g = torch.Generator().manual_seed(1234 + rank)
     noise = (torch.randn(31 * SAMPLE_RATE, generator=g) * 3000.0)
@@ -553,16 +554,18 @@ def run_bucketed(a, torch, dist, cfg, world, rank, local, peaks):
     for rb in sched:
         B, Tq = rb.key
         wl = 400 + 160 * Tq                                 # any sample count that yields <= Tq frames fits
-        ns = torch.tensor([int(samples[i]) for i in rb.indices], dtype=torch.int32)
+        ns = torch.zeros(B, dtype=torch.int32)              # rows beyond the batch: empty utterances (0 samples, 0 targets)
+        ns[: len(rb.indices)] = torch.tensor([int(samples[i]) for i in rb.indices], dtype=torch.int32)
         w = torch.zeros((B, int(ns.max())), dtype=torch.float32)
         for j, n in enumerate(ns.tolist()):
-            off = int(torch.randint(0, noise.numel() - n, (1,), generator=g))
-            w[j, :n] = noise[off:off + n]
-        tl = torch.clamp((ns.float() / SAMPLE_RATE * 6).to(torch.int32), min=1)
+            if n > 0:
+                off = int(torch.randint(0, noise.numel() - n, (1,), generator=g))
+                w[j, :n] = noise[off:off + n]
+        tl = torch.where(ns > 0, torch.clamp((ns.float() / SAMPLE_RATE * 6).to(torch.int32), min=1), torch.zeros_like(ns))
         smax = (int(tl.max()) + 31) // 32 * 32
         tg = torch.randint(4, VOCAB, (B, smax), generator=g).to(torch.int32)
         steps_host.append(dict(key=(B, Tq, smax, wl), dummy=rb.dummy, audio_s=0.0 if rb.dummy else float(ns.sum()) / SAMPLE_RATE,
-                               frames=int(n_frames[rb.indices].sum()), padded=B * Tq,
+                               frames=int(n_frames[rb.indices].sum()), padded=B * Tq, real_b=len(rb.indices),
                                t=tuple(x.pin_memory() for x in (w, ns, tg, tl))))
 
     def run_step(i):

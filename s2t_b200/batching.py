@@ -96,10 +96,22 @@ class BucketSet:
             t = q + 1
         return out
 
-    def key(self, batch_size: int, max_frames: int) -> Tuple[int, int]:
-        """Plan key of a batch: the batch size as is (batch_by_size already makes it < M or a multiple of M) and the
-        quantised frame count."""
-        return int(batch_size), self.frames(int(max_frames))
+    def step_of(self, tq: int) -> int:
+        return self.fine if tq <= self.fine_until else (self.mid if tq <= self.mid_until else self.coarse)
+
+    def key(self, batch_size: int, max_frames: int, max_tokens: Optional[int] = None, bsz_mult: int = 8) -> Tuple[int, int]:
+        """Plan key (B_q, T_q) of a batch.  Without ``max_tokens`` the batch size is kept (batch_by_size already makes it
+        < M or a multiple of M).  With it, B_q is the LARGEST batch size max-tokens batching can produce for this frame
+        bucket (every batch with T in (T_q - step, T_q] has B <= max_tokens / T), rounded to the multiple — so one plan
+        (and one captured graph) serves the whole bucket; the caller pads the batch with EMPTY utterances (0 samples, 0
+        targets), which contribute exactly nothing: no valid frame, CTC nll 0 (criterions/ctc.py zero_infinity path)."""
+        tq = self.frames(int(max_frames))
+        if max_tokens is None:
+            return int(batch_size), tq
+        lower = max(tq - self.step_of(tq) + 1, 1)
+        cap = max(bsz_mult, (int(max_tokens) // lower) // bsz_mult * bsz_mult)
+        need = -(-int(batch_size) // 64) * 64          # very short utterances: do not size the plan for max_tokens / 1
+        return max(int(batch_size), min(cap, need)), tq
 
 
 @dataclass
@@ -111,9 +123,10 @@ class RankBatch:
 
 def rank_schedule(n_frames: Sequence[int], max_tokens: int, world: int, rank: int, *, bsz_mult: int = 8,
                   max_sentences: Optional[int] = None, buckets: Optional[BucketSet] = None,
-                  shuffle_perm: Optional[np.ndarray] = None) -> List[RankBatch]:
+                  shuffle_perm: Optional[np.ndarray] = None, pad_batch: bool = False) -> List[RankBatch]:
     """The sequence of batches rank ``rank`` of ``world`` runs for one epoch over utterances of ``n_frames`` frames:
-    order -> pack -> shard, short ranks padded with their first batch as a zero-weight dummy."""
+    order -> pack -> shard, short ranks padded with their first batch as a zero-weight dummy.  ``pad_batch``: plan keys
+    carry the bucket's full batch size (see BucketSet.key) — the caller pads with empty utterances."""
     buckets = buckets or BucketSet()
     nf = np.asarray(n_frames, dtype=np.int64)
     order = ordered_indices(nf, shuffle_perm)
@@ -125,5 +138,6 @@ def rank_schedule(n_frames: Sequence[int], max_tokens: int, world: int, rank: in
         src = b if b is not None else dummy
         if src is None:
             raise RuntimeError("rank_schedule: no batch at all (fewer batches than ranks and no dummy available)")
-        out.append(RankBatch(src, b is None, buckets.key(len(src), int(nf[src].max()))))
+        out.append(RankBatch(src, b is None, buckets.key(len(src), int(nf[src].max()), max_tokens if pad_batch else None,
+                                                          bsz_mult)))
     return out

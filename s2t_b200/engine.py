@@ -608,7 +608,11 @@ class S2TEncoderEngine:
         self.init_parameters()
 
     def attn_is_fused(self, St: "_Stage") -> bool:
-        return self.fused_attention and self.cfg.attn_type == "selfattn" and St.dk == 64 and St.T <= 256
+        """attn.cu serves selfattn with d_k 64 and T' <= 256.  One CTA (226 KB of shared memory: one per SM) per (utterance,
+        head, 128-query tile): beyond two waves of CTAs (B * H * 2 > 296; measured at B = 40: 5.95 vs 5.63 ms/step) the
+        batched GEMM form, which tiles over all (b, h) at once, is the faster one."""
+        return (self.fused_attention and self.cfg.attn_type == "selfattn" and St.dk == 64 and St.T <= 256
+                and St.B * St.H * 2 <= 296)
 
     def _pos_table(self, dim: int) -> torch.Tensor:
         if dim not in self.pos_tables:
@@ -1273,7 +1277,9 @@ class S2TEncoderEngine:
         work of the PREVIOUS block (normally long finished), and this block's pool buffers stay quarantined until the
         next call.  Stage scratch read by side work (g_f, g_qkv, g_2c) is not rewritten before two blocks later (g_f
         alternates between two buffers: macaron FFN blocks are adjacent).  S2T_LAG_JOIN=0: join at once."""
-        if not (self.multi_stream and self.lag_join):
+        # (large batches: the chain's kernels fill the GPU by themselves and overlapping more side work only adds
+        # contention — measured at R = 10000 rows: 5.95 vs 5.66 ms/step — so the lag applies up to 4096 rows)
+        if not (self.multi_stream and self.lag_join and St.R <= 4096):
             self._join()
             St.give(*bufs)
             return

@@ -49,6 +49,8 @@ def _reference_bf16_noise(pds, cfg_kw, sd, feats, lens, tokens, tgt_tokens=None)
         out.append({k: p.grad.double() for k, p in m.named_parameters() if p.grad is not None})
     noise = {k: float((out[1][k] - out[0][k]).norm() / (out[0][k].norm() + 1e-12)) for k in out[0]}
     noise["__encoder_out__"] = float((encs[1] - encs[0]).norm() / encs[0].norm())     # valid frames, bf16 mode vs fp32
+    f0, f1 = (torch.cat([o[k].reshape(-1) for k in sorted(out[0])]) for o in out)
+    noise["__flat__"] = float((f1 - f0).norm() / f0.norm())                             # the whole gradient as one vector
     return noise
 
 
@@ -310,8 +312,10 @@ def test_engine_matches_oracle_full_size(cuda_lib, name):
     ref = torch.cat([dict(orc.named_parameters())[k].grad.double().reshape(-1) for k in keys])
     flat_rel = float((mine - ref).norm() / ref.norm())
     median = sorted(r[1] for r in rows)[len(rows) // 2]
-    print(f"[full_{name}] flat gradient rel-L2 {flat_rel:.4f}, median per-parameter rel-L2 {median:.4f}")
-    assert flat_rel <= 0.1, flat_rel
+    flat_tol = max(GTOL, 1.25 * noise["__flat__"])
+    print(f"[full_{name}] flat gradient rel-L2 {flat_rel:.4f} (tolerance {flat_tol:.4f}; the reference's bf16 mode: "
+          f"{noise['__flat__']:.4f}), median per-parameter rel-L2 {median:.4f}")
+    assert flat_rel <= flat_tol, (flat_rel, flat_tol)
 
 
 MID_CASES = {
@@ -517,3 +521,39 @@ def test_engine_dropout_on_matches_oracle_with_injected_masks(cuda_lib, case):
     _report_grads(f"dropout_{case}", rows)
     for k, r, tol, _ in rows:
         assert r <= tol, (k, r, tol)
+
+
+@pytest.mark.parametrize("family", ["s2t", "pds"])
+def test_empty_utterances_pad_a_batch_without_changing_it(cuda_lib, family):
+    """Frame-bucket plans are padded to the bucket's batch size with EMPTY utterances (0 samples / 0 frames, 0 targets;
+    batching.BucketSet.key): loss and every gradient must equal those of the real utterances alone, bit for bit where the
+    kernels' reduction order does not depend on the batch size, else to bf16 round-off."""
+    from s2t_b200.engine import EncoderConfig, S2TEncoderEngine
+    kw = dict(layers=2, ffn_dim=512, subsampling_filter=256, vocab=200, dropout=0.0) if family == "s2t" else \
+        dict(encoder_type="pds", pds_layers=(1, 1, 1, 1), pds_ffn_ratios=(2, 2, 2, 2), vocab=200, dropout=0.0)
+    eng = S2TEncoderEngine(EncoderConfig(**kw))
+    g = torch.Generator().manual_seed(9)
+    n = 16000
+    T = 1 + (n - 400) // 160
+    wave3 = torch.randn((3, n), generator=g) * 3000.0
+    ns3 = torch.tensor([16000, 12000, 9000], dtype=torch.int32)
+    tg3 = torch.randint(4, 200, (3, 6), generator=g).to(torch.int32)
+    tl3 = torch.tensor([6, 4, 5], dtype=torch.int32)
+
+    def run(B):
+        wave, ns = torch.zeros((B, n)), torch.zeros(B, dtype=torch.int32)
+        tg, tl = torch.zeros((B, 6), dtype=torch.int32), torch.zeros(B, dtype=torch.int32)
+        wave[:3], ns[:3], tg[:3], tl[:3] = wave3, ns3, tg3, tl3
+        P = eng.plan(B, T, 6, wave_len=n)
+        eng.set_inputs(P, wave=wave, num_samples=ns, targets=tg, target_lengths=tl)
+        eng.train_step(P)
+        torch.cuda.synchronize()
+        assert P.out_len.cpu().tolist()[3:] == [0] * (B - 3)
+        return float(P.loss.item()), eng.store.grad.float().clone(), P.nll.clone()
+
+    l3, g3, _ = run(3)
+    l8, g8, nll8 = run(8)
+    assert np.isfinite(l8) and torch.isfinite(g8).all()
+    assert float(nll8[3:].abs().max()) == 0.0
+    assert abs(l8 - l3) <= 1e-4 * abs(l3), (l3, l8)
+    assert float((g8 - g3).norm() / g3.norm()) <= 2e-2
