@@ -542,6 +542,7 @@ def run_bucketed(a, torch, dist, cfg, world, rank, local, peaks):
     if world > 1:
         dist.broadcast(eng.store.flat, src=0)
         eng.enable_data_parallel(n_buckets=int(os.environ.get("S2T_DP_BUCKETS", "4")))
+        eng.collective_free_warmup = True       # ranks capture new plans at different steps (engine.capture)
     samples = synth_durations(a.utterances, 0)
     n_frames = np.array([frontend.num_frames(int(n)) for n in samples], dtype=np.int64)
     bs = BucketSet(max_frames=cfg.max_source_positions)

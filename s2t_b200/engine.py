@@ -605,6 +605,7 @@ class S2TEncoderEngine:
         self._lag_events: list = []
         self._lag_stage, self._lag_bufs = None, ()
         self.dp = None               # dp.BucketedAllReduce when data parallel
+        self.collective_free_warmup = False   # capture(): warm-up step without collectives (per-rank plans, see capture)
         self.init_parameters()
 
     def attn_is_fused(self, St: "_Stage") -> bool:
@@ -1904,8 +1905,17 @@ class S2TEncoderEngine:
         # by the first replay, so the step counter (dropout streams) and the BatchNorm running statistics are restored
         saved = {k: v.clone() for k, v in self.buffers.items()}
         counter = self.step_counter.clone()
-        with torch.cuda.stream(s):
-            fn(P)                                # warm-up: function attributes, tensor-map cache
+        # data parallel with per-rank plans (length-bucketed batches): ranks meet NEW plans at different steps, so the
+        # eager warm-up must not issue collectives (the step count of all-reduces has to match across ranks) — it runs
+        # without the gradient exchange; the captured graph contains it
+        dp, hook = self.dp, self.grad_ready_hook
+        if self.collective_free_warmup:
+            self.dp, self.grad_ready_hook = None, None
+        try:
+            with torch.cuda.stream(s):
+                fn(P)                                # warm-up: function attributes, tensor-map cache
+        finally:
+            self.dp, self.grad_ready_hook = dp, hook
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
         for k, v in saved.items():
