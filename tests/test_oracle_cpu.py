@@ -121,3 +121,25 @@ def test_encoder_oracle_matches_reference_golden(case):
         if key.startswith("grad::"):
             ref = torch.from_numpy(fx[key])
             assert (params[key[6:]].grad - ref).norm() <= 1e-3 * ref.norm() + 1e-9, key
+
+
+@pytest.mark.parametrize("name", ["c3", "c4", "c5"])
+def test_oracle_reproduces_reference_at_full_size(name):
+    """BASELINE configs[2..4] at their stated size: tests/golden/enc_full_<name>.npz holds summaries of the REFERENCE'S own
+    run (oracle/make_golden_full.py: the reference's unmodified encoder classes, 8 ragged utterances of up to 998 frames,
+    V = 10000; the restatement was asserted equal there, difference 0.0).  The restatement must reproduce them here."""
+    import numpy as np
+    from pathlib import Path
+    from oracle import full_size as FS
+    fx = np.load(Path(__file__).resolve().parent / "golden" / f"enc_full_{name}.npz")
+    c = FS.case(name)
+    out = c["oracle"](c["feats"], c["lens"])
+    loss = FS.loss_of(c, out)
+    loss.backward()
+    got = FS.summary(out, loss, {k: p.grad for k, p in c["oracle"].named_parameters() if p.grad is not None})
+    assert abs(got["loss"] - float(fx["loss"])) <= 1e-5 * abs(float(fx["loss"]))
+    assert got["out_len"].tolist() == fx["out_len"].tolist()
+    assert np.abs(got["enc_slice"] - fx["enc_slice"]).max() <= 1e-4
+    assert np.allclose(got["enc_abs_mean"], fx["enc_abs_mean"], rtol=1e-4)
+    assert got["grad_names"].tolist() == fx["grad_names"].tolist()
+    assert np.allclose(got["grad_norms"], fx["grad_norms"], rtol=1e-3, atol=1e-7)
