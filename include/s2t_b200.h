@@ -406,6 +406,18 @@ int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, const float* ls
                  grad_scale (0 = zero-weight dummy batch, trainer.py:687-691), or NULL*/,
                  void* workspace, long long workspace_bytes, void* stream);
 /*
+ * Masked ("imputer") CTC loss: torch_imputer.imputer_loss (fairseq/torch_imputer/imputer.cu:57-225,364-640), the loss
+ * CtcCriterion.get_ctc_loss switches to when ctc_masked_loss is set and the encoder supplies force_emit
+ * (criterions/ctc.py:455-465).  force_emit int32 [B][fe_ld]: index of the extended-label state (0 .. 2 S) that must be
+ * occupied at frame t, or -1 (free); every other state of a forced frame is removed from the lattice.  Everything
+ * else as s2t_ctc_loss (with all entries -1 the two agree).
+ */
+int s2t_ctc_loss_masked(const void* logits, int is_bf16, long long ldv, const float* lse,
+                        const int* targets, long long tgt_ld, const int* force_emit, long long fe_ld,
+                        const int* input_lengths, const int* target_lengths, int batch, int T, int V,
+                        int max_target_len, int blank, float* nll, void* dlogits, float grad_scale,
+                        const float* grad_scale_dev, void* workspace, long long workspace_bytes, void* stream);
+/*
  * Greedy CTC: argmax over V (lowest index on ties), padded frames -> blank, collapse repeats,
  * drop blank.  tokens int32 [B][T] (first out_lengths[b] valid, rest -1); frame_ids int32 [B][T]
  * (required) receives the per-frame argmax after pad->blank.  scores fp32 [B] (optional, with the

@@ -128,3 +128,108 @@ def greedy_scores(logits: np.ndarray, blank: int = 0) -> np.ndarray:
     idx = lp.argmax(axis=-1)
     real = np.where(idx == blank, float(blank), top)
     return -real.sum(axis=-1)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Masked ("imputer") CTC loss — fairseq/torch_imputer/imputer.cu:57-225 (log_alpha), :364-520 (log_beta), :535-640
+# (gradient), called from fairseq/criterions/ctc.py:455-465 when ``ctc_masked_loss`` is set.
+# force_emit[t] = index of the EXTENDED-label state (0 .. 2S) that must be occupied at frame t, or -1 (free): every other
+# state of that frame is removed from the lattice (alpha = beta = -inf).  With all entries -1 it is the plain CTC loss.
+# Parity status: the reference path exists only as a CUDA extension that cannot run in the CPU-only build container and
+# the reference holds no test vectors for it ("parity unpinned"); the restatement is checked against brute-force
+# enumeration of all alignments and against the plain CTC oracle (itself pinned to torch.nn.CTCLoss).
+# ---------------------------------------------------------------------------------------------------------------------
+def imputer_alpha_beta(lp: np.ndarray, target: np.ndarray, force_emit: np.ndarray, blank: int = 0):
+    """lp [T, V] log-probs (float64), target [S], force_emit [T] int.  Returns (nll, alpha, beta, ext)."""
+    T = lp.shape[0]
+    S = len(target)
+    ext = np.full(2 * S + 1, blank, dtype=np.int64)
+    ext[1::2] = target
+    Se = 2 * S + 1
+    alpha = np.full((T, Se), -np.inf)
+    beta = np.full((T, Se), -np.inf)
+    if T == 0:
+        return (0.0 if S == 0 else np.inf), alpha, beta, ext
+    allowed = lambda t, s: force_emit[t] < 0 or int(force_emit[t]) == s          # imputer.cu:117-119, 146-151
+    if allowed(0, 0):
+        alpha[0, 0] = lp[0, blank]
+    if Se > 1 and allowed(0, 1):
+        alpha[0, 1] = lp[0, ext[1]]
+    for t in range(1, T):
+        for s in range(Se):
+            if not allowed(t, s):
+                continue
+            a = alpha[t - 1, s]
+            b = alpha[t - 1, s - 1] if s >= 1 else -np.inf
+            c = alpha[t - 1, s - 2] if (s >= 2 and ext[s] != blank and ext[s] != ext[s - 2]) else -np.inf
+            alpha[t, s] = _logaddexp3(a, b, c) + lp[t, ext[s]]
+    if allowed(T - 1, Se - 1):
+        beta[T - 1, Se - 1] = lp[T - 1, blank]
+    if Se > 1 and allowed(T - 1, Se - 2):
+        beta[T - 1, Se - 2] = lp[T - 1, ext[Se - 2]]
+    for t in range(T - 2, -1, -1):
+        for s in range(Se):
+            if not allowed(t, s):
+                continue
+            a = beta[t + 1, s]
+            b = beta[t + 1, s + 1] if s + 1 < Se else -np.inf
+            c = beta[t + 1, s + 2] if (s + 2 < Se and ext[s] != blank and ext[s] != ext[s + 2]) else -np.inf
+            beta[t, s] = _logaddexp3(a, b, c) + lp[t, ext[s]]
+    tail = alpha[T - 1, Se - 2] if Se > 1 else -np.inf
+    ll = np.logaddexp(alpha[T - 1, Se - 1], tail)
+    return -ll, alpha, beta, ext
+
+
+def imputer_loss(logits: np.ndarray, targets: List[np.ndarray], force_emits, input_lengths, blank: int = 0,
+                 zero_infinity: bool = True) -> Tuple[np.ndarray, np.ndarray]:
+    """logits [B, T, V]; force_emits [B, T] (state indices or -1).  Returns (nll [B], d sum(nll) / d logits) in float64."""
+    logits = np.asarray(logits, dtype=np.float64)
+    B, T, V = logits.shape
+    nll = np.zeros(B)
+    grad = np.zeros_like(logits)
+    lp_all = log_softmax(logits)
+    for b in range(B):
+        Tb = int(input_lengths[b])
+        lp = lp_all[b, :Tb]
+        loss, alpha, beta, ext = imputer_alpha_beta(lp, np.asarray(targets[b], dtype=np.int64),
+                                                    np.asarray(force_emits[b][:Tb]), blank)
+        if not np.isfinite(loss):
+            nll[b] = 0.0 if zero_infinity else loss
+            continue
+        nll[b] = loss
+        occ = np.zeros((Tb, V))
+        g = alpha + beta + loss
+        for s in range(len(ext)):
+            col = g[:, s] - lp[:, ext[s]]
+            occ[:, ext[s]] += np.where(np.isfinite(col), np.exp(col), 0.0)
+        grad[b, :Tb] = np.exp(lp) - occ
+    return nll, grad
+
+
+def imputer_nll_bruteforce(lp: np.ndarray, target, force_emit, blank: int = 0) -> float:
+    """-log of the summed probability of every frame-level state path through the extended target (start in state 0 or
+    1, stay / advance by one / skip a blank between different labels, end in the last two states) that occupies the
+    forced states.  Exponential in T: tiny cases only."""
+    import itertools
+    T = lp.shape[0]
+    S = len(target)
+    ext = [blank] * (2 * S + 1)
+    ext[1::2] = list(target)
+    Se = len(ext)
+    total = 0.0
+    for path in itertools.product(range(Se), repeat=T):
+        if path[0] > 1 or path[-1] < Se - 2:
+            continue
+        ok = True
+        for t in range(T):
+            if force_emit[t] >= 0 and path[t] != force_emit[t]:
+                ok = False
+                break
+            if t > 0:
+                d = path[t] - path[t - 1]
+                if d < 0 or d > 2 or (d == 2 and (ext[path[t]] == blank or ext[path[t]] == ext[path[t - 1]])):
+                    ok = False
+                    break
+        if ok:
+            total += float(np.exp(sum(lp[t, ext[path[t]]] for t in range(T))))
+    return float(-np.log(total)) if total > 0 else float("inf")

@@ -211,9 +211,13 @@ __device__ __forceinline__ void vec_store(float* __restrict__ p, const float (&v
 
 constexpr int kCtcMaxPerThread = 4;  // Sp <= 4 * blockDim
 
+// MASKED: the "imputer" lattice (torch_imputer/imputer.cu:57-225, 364-520) — force_emit[b][t] = index of the extended-label
+// state that must be occupied at frame t, or -1; every other state of that frame is removed (alpha = beta = -inf).
+template <bool MASKED>
 __global__ void ctc_alpha_beta_kernel(const int* __restrict__ targets, long long tgt_ld,
                                       const int* __restrict__ in_len, const int* __restrict__ tgt_len,
-                                      int T, int Sp, int blank, CtcWs ws) {
+                                      int T, int Sp, int blank, CtcWs ws,
+                                      const int* __restrict__ force_emit, long long fe_ld) {
   pdl_entry();
   extern __shared__ float s_lat[];  // [2][Sp + 4]
   const int b = blockIdx.x;
@@ -261,6 +265,10 @@ __global__ void ctc_alpha_beta_kernel(const int* __restrict__ targets, long long
         } else {
           if (s >= Se - 2) v = lp[static_cast<long long>(t) * Sp + s];
         }
+        if (MASKED) {
+          const int fe = force_emit[b * fe_ld + t];
+          if (fe > -1 && fe != s) v = kNegInf;
+        }
         prev[s] = v;
         lat[static_cast<long long>(t) * Sp + s] = v;
       }
@@ -286,6 +294,8 @@ __global__ void ctc_alpha_beta_kernel(const int* __restrict__ targets, long long
       const int step = step0 + d;
       if (step < Tb) {  // block-uniform
         const int t = fwd ? step : Tb - 1 - step;
+        int fe = -1;
+        if (MASKED) fe = force_emit[b * fe_ld + t];
 #pragma unroll
         for (int k = 0; k < kCtcMaxPerThread; ++k) {
           const int s = threadIdx.x + k * blockDim.x;
@@ -300,7 +310,8 @@ __global__ void ctc_alpha_beta_kernel(const int* __restrict__ targets, long long
               bb = (s + 1 < Se) ? prev[s + 1] : kNegInf;
               c = skip[k] ? prev[s + 2] : kNegInf;
             }
-            const float v = lse3(a, bb, c) + pf[d][k];
+            float v = lse3(a, bb, c) + pf[d][k];
+            if (MASKED && fe > -1 && fe != s) v = kNegInf;
             cur[s] = v;
             lat[static_cast<long long>(t) * Sp + s] = v;
           }
@@ -741,12 +752,12 @@ extern "C" long long s2t_ctc_workspace_bytes(int batch, int T, int max_target_le
   return 4 * ctc_ws_floats(batch, T, Sp) + 256;
 }
 
-extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, const float* lse,
-                            const int* targets, long long tgt_ld, const int* input_lengths,
-                            const int* target_lengths, int batch, int T, int V, int max_target_len,
-                            int blank, float* nll, void* dlogits, float grad_scale,
-                            const float* grad_scale_dev, void* workspace, long long workspace_bytes,
-                            void* stream) {
+static int ctc_loss_impl(const void* logits, int is_bf16, long long ldv, const float* lse,
+                         const int* targets, long long tgt_ld, const int* input_lengths,
+                         const int* target_lengths, int batch, int T, int V, int max_target_len,
+                         int blank, float* nll, void* dlogits, float grad_scale,
+                         const float* grad_scale_dev, void* workspace, long long workspace_bytes,
+                         void* stream, const int* force_emit, long long fe_ld) {
   S2T_REQUIRE(logits && lse && targets && input_lengths && target_lengths && workspace,
               "s2t_ctc_loss: null pointer");
   S2T_REQUIRE(nll != nullptr, "s2t_ctc_loss: nll output required");
@@ -823,6 +834,11 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
       Tc = static_cast<int>((100 * 1024) / row_bytes);
       lat_smem = 2 * static_cast<size_t>(Tc) * row_bytes;
     }
+    if (force_emit != nullptr) {
+      // masked lattice: the block kernel (states in shared memory), every frame checks its forced state
+      S2T_LAUNCH(ctc_alpha_beta_kernel<true>, g, threads, smem, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws,
+                 force_emit, fe_ld);
+    } else
 #define S2T_CTC_WARP(NS)                                                                                          \
   do {                                                                                                            \
     S2T_CHECK_CUDA(cudaFuncSetAttribute(ctc_alpha_beta_warp_kernel<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
@@ -840,7 +856,8 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
       S2T_CTC_WARP(8);
 #undef S2T_CTC_WARP
     else
-      S2T_LAUNCH(ctc_alpha_beta_kernel, g, threads, smem, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws);
+      S2T_LAUNCH(ctc_alpha_beta_kernel<false>, g, threads, smem, st, targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank, ws,
+                 static_cast<const int*>(nullptr), 0ll);
     S2T_LAUNCH_CHECK();
   }
   if (!overlap) {   // loss only: publish nll (zero_infinity applied)
@@ -854,6 +871,29 @@ extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, cons
     S2T_LAUNCH_CHECK();
   }
   return 0;
+}
+
+extern "C" int s2t_ctc_loss(const void* logits, int is_bf16, long long ldv, const float* lse,
+                            const int* targets, long long tgt_ld, const int* input_lengths,
+                            const int* target_lengths, int batch, int T, int V, int max_target_len,
+                            int blank, float* nll, void* dlogits, float grad_scale,
+                            const float* grad_scale_dev, void* workspace, long long workspace_bytes,
+                            void* stream) {
+  return ctc_loss_impl(logits, is_bf16, ldv, lse, targets, tgt_ld, input_lengths, target_lengths, batch, T, V,
+                       max_target_len, blank, nll, dlogits, grad_scale, grad_scale_dev, workspace, workspace_bytes, stream,
+                       nullptr, 0);
+}
+
+extern "C" int s2t_ctc_loss_masked(const void* logits, int is_bf16, long long ldv, const float* lse,
+                                   const int* targets, long long tgt_ld, const int* force_emit, long long fe_ld,
+                                   const int* input_lengths, const int* target_lengths, int batch, int T, int V,
+                                   int max_target_len, int blank, float* nll, void* dlogits, float grad_scale,
+                                   const float* grad_scale_dev, void* workspace, long long workspace_bytes,
+                                   void* stream) {
+  S2T_REQUIRE(force_emit != nullptr && fe_ld >= T, "s2t_ctc_loss_masked: force_emit [B][fe_ld >= T] required");
+  return ctc_loss_impl(logits, is_bf16, ldv, lse, targets, tgt_ld, input_lengths, target_lengths, batch, T, V,
+                       max_target_len, blank, nll, dlogits, grad_scale, grad_scale_dev, workspace, workspace_bytes, stream,
+                       force_emit, fe_ld);
 }
 
 extern "C" int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, const int* input_lengths,

@@ -24,7 +24,7 @@ _LAUNCHES = {
     "s2t_layernorm_fwd": 1, "s2t_layernorm_bwd": 1, "s2t_layernorm_bwd_reduce": 1, "s2t_glu_fwd": 1, "s2t_glu_bwd": 1,
     "s2t_colsum": 1, "s2t_col2im1d": 1, "s2t_embed_fwd": 1, "s2t_embed_bwd": 1, "s2t_mask_rows": 1,
     "s2t_permute_conv_weight": 1, "s2t_cast_f32_to_bf16": 1, "s2t_cast_bf16_to_f32": 1,
-    "s2t_attn_softmax_fwd": 1, "s2t_attn_fused_fwd": 1, "s2t_attn_fused_bwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4,
+    "s2t_attn_softmax_fwd": 1, "s2t_attn_fused_fwd": 1, "s2t_attn_fused_bwd": 1, "s2t_attn_softmax_bwd": 1, "s2t_row_lse": 1, "s2t_ctc_loss": 4, "s2t_ctc_loss_masked": 4,
     "s2t_ctc_greedy": 2, "s2t_dwconv1d_fwd": 1, "s2t_dwconv1d_bwd": 3, "s2t_batchnorm_fwd": 1,
     "s2t_batchnorm_bwd": 2, "s2t_im2col2d": 1, "s2t_col2im2d": 1, "s2t_colstats": 1, "s2t_relpos_qbias_fwd": 1, "s2t_relpos_qbias_bwd": 1, "s2t_act_dropout": 1,
 }
@@ -621,7 +621,8 @@ def ctc_loss(logits: torch.Tensor, targets: torch.Tensor, input_lengths: torch.T
              target_lengths: torch.Tensor, V: int, blank: int = 0, *, need_grad: bool = True,
              grad_scale: float = 1.0, lse: Optional[torch.Tensor] = None,
              dlogits: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None,
-             nll: Optional[torch.Tensor] = None, grad_scale_dev: Optional[torch.Tensor] = None):
+             nll: Optional[torch.Tensor] = None, grad_scale_dev: Optional[torch.Tensor] = None,
+             force_emit: Optional[torch.Tensor] = None):
     """logits [B, T, ldv] utterance-major; targets int32 [B, Smax].  Returns (nll fp32 [B], dlogits|None).
     ``grad_scale_dev``: optional fp32 [1] device scalar multiplied into ``grad_scale`` on the device (batch weight)."""
     B, T, ldv = logits.shape
@@ -636,6 +637,15 @@ def ctc_loss(logits: torch.Tensor, targets: torch.Tensor, input_lengths: torch.T
         nll = torch.empty((B,), device=logits.device, dtype=torch.float32)
     if need_grad and dlogits is None:
         dlogits = torch.empty_like(logits)
+    if force_emit is not None:
+        # masked ("imputer") loss: force_emit int32 [B, T] = forced extended-label state per frame, -1 = free
+        if force_emit.dtype != torch.int32 or force_emit.shape[0] != B or force_emit.shape[1] < T:
+            raise ValueError("ctc_loss: force_emit must be int32 [B, >= T]")
+        _call("s2t_ctc_loss_masked", _p(logits), int(logits.dtype == BF16), ldv, _p(lse), _p(targets),
+              targets.stride(0), _p(force_emit), force_emit.stride(0), _p(input_lengths), _p(target_lengths), B, T, V,
+              smax, blank, _p(nll), _p(dlogits) if need_grad else None, grad_scale, _p(grad_scale_dev), _p(workspace),
+              workspace.numel() * workspace.element_size(), _stream())
+        return nll, (dlogits if need_grad else None)
     _call("s2t_ctc_loss", _p(logits), int(logits.dtype == BF16), ldv, _p(lse), _p(targets),
           targets.stride(0), _p(input_lengths), _p(target_lengths), B, T, V, smax, blank, _p(nll),
           _p(dlogits) if need_grad else None, grad_scale, _p(grad_scale_dev), _p(workspace),

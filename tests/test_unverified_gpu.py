@@ -1,0 +1,74 @@
+"""GPU checks of code written AFTER the round's GPU budget was spent (a deadlocked 8-GPU run consumed it):
+these kernels / paths have compiled for sm_100a but had never run on hardware when they were committed.  So that a defect
+in them cannot take the verified suite down, each check runs in its OWN python subprocess (a faulting kernel cannot poison
+this process's CUDA context; a hang is killed by the timeout) and is marked xfail(strict=False): the driver's GPU run
+reports it as XPASS (works on hardware) or XFAIL (does not) without failing the run.  None of this code is on the default
+training path (bench.py, the other tests): it is only reached through the options named in each test.
+"""
+import subprocess
+import sys
+import textwrap
+from pathlib import Path
+
+import pytest
+
+pytestmark = [pytest.mark.gpu, pytest.mark.xfail(strict=False, reason="first run on hardware: written after the round's GPU budget was spent")]
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def run_isolated(body: str, timeout: int = 300) -> None:
+    code = "import sys\nsys.path.insert(0, %r)\n" % str(ROOT) + textwrap.dedent(body)
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=timeout, cwd=str(ROOT))
+    sys.stdout.write(res.stdout[-4000:])
+    assert res.returncode == 0, res.stderr[-4000:]
+
+
+def test_unverified_masked_ctc_loss_matches_oracle(cuda_lib):
+    """s2t_ctc_loss_masked (torch_imputer.imputer_loss, criterions/ctc.py:455-465) against oracle/ctc.py imputer_loss
+    (brute-force checked, tests/test_imputer_cpu.py): loss rel 1e-3, gradient max-abs 1e-4 (fp32) / 2^-8 (bf16); states
+    forced along the Viterbi alignment, one utterance with an impossible forced state (-> zero_infinity), one unforced."""
+    run_isolated("""
+        import numpy as np, torch
+        from oracle import ctc as O
+        from oracle import viterbi as OV
+        from s2t_b200 import ops
+        rng = np.random.default_rng(0)
+        B, T, V = 5, 40, 56
+        tlens, ilens = [8, 0, 12, 5, 7], [40, 30, 39, 12, 25]
+        for dtype, tol in ((torch.float32, 1e-4), (torch.bfloat16, 2 ** -8)):
+            logits = torch.from_numpy(rng.normal(0, 1.5, size=(B, T, V)).astype(np.float32)).to(dtype)
+            smax = max(tlens)
+            tg = np.zeros((B, smax), dtype=np.int32)
+            tgts = []
+            for b, n in enumerate(tlens):
+                row = rng.integers(1, V, size=n)
+                if n >= 3:
+                    row[2] = row[1]
+                tg[b, :n] = row
+                tgts.append(row)
+            lp = O.log_softmax(logits.float().numpy())
+            paths, _ = OV.best_alignment(lp.astype(np.float32), tg.astype(np.int64), ilens, tlens)
+            fe = np.full((B, T), -1, dtype=np.int32)
+            for b in (0, 2, 3):
+                idx = rng.choice(ilens[b], size=ilens[b] // 3, replace=False)
+                fe[b, idx] = np.asarray(paths[b])[idx]
+            fe[3, 0] = 2 * tlens[3]                      # the last blank cannot be occupied at frame 0: infeasible
+            nll, dl = ops.ctc_loss(logits.cuda(), torch.from_numpy(tg).cuda(), torch.tensor(ilens, dtype=torch.int32).cuda(),
+                                   torch.tensor(tlens, dtype=torch.int32).cuda(), V, force_emit=torch.from_numpy(fe).cuda())
+            ref_nll, ref_grad = O.imputer_loss(logits.float().numpy(), tgts, fe, ilens)
+            nll = nll.cpu().numpy()
+            assert ref_nll[3] == 0 and nll[3] == 0, (ref_nll, nll)
+            assert np.allclose(nll, ref_nll, rtol=1e-3, atol=1e-3), (nll, ref_nll)
+            err = np.abs(dl.float().cpu().numpy() - ref_grad).max()
+            assert err < tol, (str(dtype), err)
+            # nothing forced == the plain loss (bit for bit: same gather / dense / occupancy kernels, other lattice kernel)
+            free = torch.full((B, T), -1, dtype=torch.int32).cuda()
+            nll_f, dl_f = ops.ctc_loss(logits.cuda(), torch.from_numpy(tg).cuda(), torch.tensor(ilens, dtype=torch.int32).cuda(),
+                                       torch.tensor(tlens, dtype=torch.int32).cuda(), V, force_emit=free)
+            nll_p, dl_p = ops.ctc_loss(logits.cuda(), torch.from_numpy(tg).cuda(), torch.tensor(ilens, dtype=torch.int32).cuda(),
+                                       torch.tensor(tlens, dtype=torch.int32).cuda(), V)
+            assert np.allclose(nll_f.cpu().numpy(), nll_p.cpu().numpy(), rtol=1e-4, atol=1e-4)
+            assert (dl_f.float() - dl_p.float()).abs().max().item() < tol
+        print("masked CTC loss ok")
+    """)
