@@ -379,6 +379,14 @@ int s2t_softmax_rows_fwd(const void* logits, long long ldv, const float* lse, vo
 int s2t_softmax_rows_bwd(const void* probs, const void* dprobs, long long ldp, void* dlogits,
                          long long ldv, int rows, int V, int accumulate, void* stream);
 
+/* Ground-truth mixing of the prediction-aware adapter (curriculum: s2t_transformer.py:1904-1946, 2061-2103;    */
+/* adapter.py:244-262): rows r with mask[r] != 0 get the one-hot distribution of truth_tok[r] (smooth != 0: 0.9 +  */
+/* 0.1 / V on the token, 0.1 / V elsewhere — pae-oracle-smooth) instead of the model's softmax; probs bf16 [rows][ldp].*/
+int s2t_rows_truth_mix(void* probs, long long ldp, const int* truth_tok, const int* mask, int rows, int V,
+                        int smooth, void* stream);
+/* x[r][0:ncols] = 0 where mask[r] != 0 (bf16 [rows][ld]): no gradient reaches the logits of a replaced frame         */
+int s2t_rows_zero_masked(void* x, long long ld, const int* mask, int rows, int ncols, void* stream);
+
 /* --------------------------------------------------------------------------------------------- */
 /* K7/K8/K9: CTC head softmax, CTC loss forward/backward, greedy decode.                          */
 /* Replaces utils.log_softmax (fairseq/utils.py:477-481) + torch.nn.CTCLoss(blank, 'none',        */

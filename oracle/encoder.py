@@ -56,6 +56,12 @@ class OracleConfig:
     ctc_pae: str = "none"                # none | inter_league
     xctc_pae: str = "none"
     pae_unnorm_input: bool = False
+    # ground-truth curriculum of the prediction-aware adapters (s2t_transformer.py:1050-1052, 1129-1148, 1232-1233)
+    ctc_pae_gt_ratio: float = 0.0        # --ctc-pae-ground-truth-ratio
+    xctc_pae_gt_ratio: float = 0.0       # --xctc-pae-ground-truth-ratio
+    pae_adaptive_gt: bool = False        # --xctc-pae-ground-truth-ratio-adaptive (applies to both heads, sic)
+    pae_gt_only_mistake: bool = False    # --xctc-pae-ground-truth-only-mistake (applies to both heads, sic)
+    pae_oracle_smooth: bool = False      # --pae-oracle-smooth (reaches the XCTC adapter only, sic :1066 vs :1233)
     # PDS (pdss2t_transformer.py:1361-1560)
     pds_layers: Tuple[int, ...] = (3, 3, 3, 3)
     pds_ratios: Tuple[int, ...] = (2, 2, 1, 2)
@@ -341,10 +347,17 @@ class Adapter(nn.Module):
         self.embed_adapter = nn.Linear(d, vocab, bias=False)              # used transposed as a (V, C) matrix
         nn.init.normal_(self.embed_adapter.weight, mean=0, std=d ** -0.5)
 
-    def forward(self, representation, logit):
+    def forward(self, representation, logit, oracle=None, oracle_mask=None, gt_ratio: float = 0.0, smooth: bool = False):
         T, B, _ = representation.shape
+        V = logit.size(-1)
         dist = F.softmax(logit, dim=-1)
-        soft = torch.mm(dist.contiguous().view(-1, logit.size(-1)), self.embed_adapter.weight).view(T, B, -1)
+        if gt_ratio > 0 and oracle is not None:                           # adapter.py:244-262 (oracle, mask: (B, T))
+            oracle_dis = (oracle.unsqueeze(-1) == torch.arange(V).unsqueeze(0)).to(dist.dtype).transpose(0, 1)
+            if smooth:
+                oracle_dis = torch.where(oracle_dis == 1, 0.9 + 0.1 / V, 0.1 / V).to(dist.dtype)
+            m = oracle_mask.transpose(0, 1).unsqueeze(-1).repeat(1, 1, V)
+            dist = m * oracle_dis + ~m * dist
+        soft = torch.mm(dist.contiguous().view(-1, V), self.embed_adapter.weight).view(T, B, -1)
         return representation + soft
 
 
@@ -385,8 +398,25 @@ class S2TTransformerEncoder(nn.Module):
         if cfg.inter_xctc_layers and cfg.xctc_pae != "none":
             self.xctc_pae = Adapter(d, cfg.tgt_vocab)
 
-    def forward(self, src_tokens: torch.Tensor, src_lengths: torch.Tensor) -> Dict[str, list]:
+    def _draw(self, entry, ratio: float, masks, key):
+        """(oracle tokens, mask, force_emit) of one head from a ``ctc_alignment_oracle`` entry (oracle, best_aligns_pad,
+        mistake_flag, mistake_ratio), s2t_transformer.py:1908-1936 / 2065-2092; ``masks[key]`` injects the mask instead of
+        drawing it (torch.rand) — the parity tests pass the same mask to the CUDA path."""
         cfg = self.cfg
+        oracle, best_aligns_pad, mistake_flag, mistake_ratio = entry
+        if masks is not None and key in masks:
+            mask = masks[key].bool().clone()
+        else:
+            prob = ratio * mistake_ratio.unsqueeze(-1) if cfg.pae_adaptive_gt else ratio
+            mask = (torch.rand(oracle.size()) < prob).bool()
+            if cfg.pae_gt_only_mistake:
+                mask.masked_fill_(~mistake_flag, False)
+        return oracle, mask, best_aligns_pad.masked_fill(~mask, -1)
+
+    def forward(self, src_tokens: torch.Tensor, src_lengths: torch.Tensor, ctc_alignment_oracle=None,
+                oracle_masks=None) -> Dict[str, list]:
+        cfg = self.cfg
+        ctc_or = xctc_or = None                                            # drawn at the first inter layer, then reused
         x = src_tokens.transpose(0, 1)                                     # :1728
         x, lens = self.subsample(x, src_lengths)                           # :1748
         pad = lengths_to_padding_mask(lens)                                # :1751
@@ -411,23 +441,40 @@ class S2TTransformerEncoder(nn.Module):
             if idx in cfg.inter_ctc_layers:                                # :1881-1946
                 norm_x = getattr(self, f"ctc_norm{idx}")(x)
                 logit = self.ctc(norm_x)
+                inter_logit = [logit, pad]
+                if cfg.ctc_pae_gt_ratio > 0 and ctc_alignment_oracle is not None and ctc_alignment_oracle.get("ctc") is not None:
+                    if ctc_or is None:
+                        ctc_or = self._draw(ctc_alignment_oracle["ctc"], cfg.ctc_pae_gt_ratio, oracle_masks, "ctc")
+                    inter_logit = [logit, None, ctc_or[2]]
                 if cfg.ctc_pae != "none":
-                    x = self.pae(x if cfg.pae_unnorm_input else norm_x, logit)
-                inter_ctc.append([logit, pad])
+                    o = ctc_or if ctc_or is not None else (None, None, None)
+                    x = self.pae(x if cfg.pae_unnorm_input else norm_x, logit, o[0], o[1], cfg.ctc_pae_gt_ratio, False)
+                inter_ctc.append(inter_logit)
             if idx in cfg.inter_xctc_layers:                               # :2043-2103
                 norm_x = getattr(self, f"xctc_norm{idx}")(x)
                 logit = self.xctc(norm_x)
+                inter_logit = logit
+                if cfg.xctc_pae_gt_ratio > 0 and ctc_alignment_oracle is not None and ctc_alignment_oracle.get("xctc") is not None:
+                    if xctc_or is None:
+                        xctc_or = self._draw(ctc_alignment_oracle["xctc"], cfg.xctc_pae_gt_ratio, oracle_masks, "xctc")
+                    inter_logit = [logit, None, xctc_or[2]]
                 if cfg.xctc_pae != "none":
-                    x = self.xctc_pae(x if cfg.pae_unnorm_input else norm_x, logit)
-                inter_xctc.append(logit)
+                    o = xctc_or if xctc_or is not None else (None, None, None)
+                    x = self.xctc_pae(x if cfg.pae_unnorm_input else norm_x, logit, o[0], o[1], cfg.xctc_pae_gt_ratio,
+                                      cfg.pae_oracle_smooth)
+                inter_xctc.append(inter_logit)
         x = self.layer_norm(x)                                             # :2112
         out = {"encoder_out": [x], "ctc_logit": [], "xctc_logit": [], "inter_ctc_logits": inter_ctc,
                "inter_xctc_logits": inter_xctc, "encoder_padding_mask": [pad], "mixup": None,
                "encoder_embedding": [], "encoder_states": [], "src_tokens": [], "src_lengths": []}
         if cfg.vocab > 0:
             out["ctc_logit"] = [self.ctc(x)]                               # :2126
+            if ctc_or is not None:
+                out["ctc_logit"] = [[out["ctc_logit"][0], None, ctc_or[2]]]          # :2136-2137
         if cfg.tgt_vocab > 0:
             out["xctc_logit"] = [self.xctc(x)]                             # :2130
+            if xctc_or is not None:
+                out["xctc_logit"] = [[out["xctc_logit"][0], None, xctc_or[2]]]       # :2139-2140
         return out
 
 
@@ -522,25 +569,89 @@ def ctc_criterion_loss(logit_tbv: torch.Tensor, padding_mask: torch.Tensor, toke
     return loss.sum()
 
 
+class _ImputerLoss(torch.autograd.Function):
+    """torch_imputer.imputer_loss (fairseq/torch_imputer/imputer.py:21-84 over imputer.cu) through the float64 numpy
+    restatement oracle/ctc.py imputer_loss: sum over utterances of the masked CTC nll, gradient w.r.t. the LOGITS."""
+
+    @staticmethod
+    def forward(ctx, logit_tbv, targets_list, force_emit, input_lengths, blank):
+        from oracle import ctc as OC
+        x = logit_tbv.detach().transpose(0, 1).double().numpy()                 # (B, T, V)
+        nll, grad = OC.imputer_loss(x, targets_list, force_emit.numpy(), input_lengths.tolist(), blank)
+        ctx.grad = torch.from_numpy(grad).transpose(0, 1).to(logit_tbv.dtype)
+        return torch.tensor(float(nll.sum()), dtype=torch.float32)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ctx.grad * g, None, None, None, None
+
+
+def imputer_criterion_loss(logit_tbv: torch.Tensor, padding_mask: torch.Tensor, tokens: torch.Tensor, force_emit: torch.Tensor,
+                           pad: int = 1, eos: int = 2, blank: int = 0) -> torch.Tensor:
+    """CtcCriterion.get_ctc_loss with ``ctc_masked_loss`` and a force_emit matrix (criterions/ctc.py:455-465): fp32
+    log_softmax + imputer_loss(..., reduction 'none', zero_infinity=True).sum()."""
+    input_lengths = (~padding_mask).long().sum(-1)
+    mask = (tokens != pad) & (tokens != eos)
+    targets_list = [tokens[b][mask[b]].numpy() for b in range(tokens.shape[0])]
+    return _ImputerLoss.apply(logit_tbv.float(), targets_list, force_emit, input_lengths, blank)
+
+
+def ground_truth_alignment(out: Dict[str, list], src_tokens: torch.Tensor, tgt_tokens: Optional[torch.Tensor],
+                           pad: int = 1, eos: int = 2, blank: int = 0) -> Dict[str, tuple]:
+    """CtcCriterion.get_ground_truth_alignment / get_ctc_align (criterions/ctc.py:283-433) on an encoder output dict:
+    per head (oracle tokens (B, T'), best_aligns_pad (B, T'), mistake_flag (B, T'), mistake_ratio (B)) from the best CTC
+    alignment (torch_imputer.best_alignment -> oracle/viterbi.py) of the TOP logits."""
+    from oracle import viterbi as OV
+    res = {}
+    pmask = out["encoder_padding_mask"][0]
+    input_lengths = (~pmask).long().sum(-1)
+    for key, logits, tokens in (("ctc", out["ctc_logit"], src_tokens), ("xctc", out["xctc_logit"], tgt_tokens)):
+        if not logits or tokens is None:
+            continue
+        top = logits[0][0] if isinstance(logits[0], list) else logits[0]
+        lp = F.log_softmax(top.detach(), dim=-1, dtype=torch.float32)              # (T, B, V)
+        tl = ((tokens != pad) & (tokens != eos)).sum(-1)
+        paths, _ = OV.best_alignment(lp.transpose(0, 1).numpy(), tokens.numpy(), input_lengths.tolist(), tl.tolist(), blank)
+        T = lp.size(0)
+        bap = torch.tensor([a + [0] * (T - len(a)) for a in paths], dtype=tokens.dtype)
+        pos = torch.div(bap, 2, rounding_mode="floor").clip(max=tokens.shape[1] - 1)
+        oracle = tokens.gather(-1, pos)
+        oracle.masked_fill_(bap % 2 == 0, blank)
+        mistake = lp.argmax(dim=-1).transpose(0, 1) != oracle
+        res[key] = (oracle, bap, mistake, mistake.sum(-1) / input_lengths)
+    return res
+
+
 def ctc_criterion_total(out: Dict[str, list], src_tokens: torch.Tensor, tgt_tokens: Optional[torch.Tensor], *,
                         ctc_weight: float, xctc_weight: float = 0.0, inter_ctc_weight: float = 0.0,
-                        inter_xctc_weight: float = 0.0) -> torch.Tensor:
+                        inter_xctc_weight: float = 0.0, masked_loss: bool = False) -> torch.Tensor:
     """CtcCriterion.compute_ctc_loss weighting (fairseq/criterions/ctc.py:542-682, 759-833, 1004-1015):
     ctc_w * ctc + xctc_w * xctc + inter_ctc_w * mean_l(inter) + inter_xctc_w * mean_l(inter_x); source-side losses use
     the transcript tokens, target-side (XCTC) losses the target tokens."""
     pad = out["encoder_padding_mask"][0]
     loss = src_tokens.new_zeros((), dtype=torch.float32)
+
+    def term(lg, tokens):
+        """one inter term: bare logit, [logit, pad_mask] or, under the curriculum, [logit, None, force_emit]
+        (criterions/ctc.py:586-627); the masked loss only with ``masked_loss`` (ctc_masked_loss)."""
+        if not isinstance(lg, list):
+            return ctc_criterion_loss(lg, pad, tokens)
+        pm = lg[1] if lg[1] is not None else pad
+        if len(lg) >= 3 and masked_loss:
+            return imputer_criterion_loss(lg[0], pm, tokens, lg[2])
+        return ctc_criterion_loss(lg[0], pm, tokens)
+
     if inter_ctc_weight > 0 and out["inter_ctc_logits"]:
-        it = [ctc_criterion_loss(lg[0], lg[1] if lg[1] is not None else pad, src_tokens) for lg in out["inter_ctc_logits"]]
+        it = [term(lg, src_tokens) for lg in out["inter_ctc_logits"]]
         loss = loss + inter_ctc_weight * sum(it) / len(it)
     if ctc_weight > 0 and out["ctc_logit"]:
-        loss = loss + ctc_weight * ctc_criterion_loss(out["ctc_logit"][0], pad, src_tokens)
+        loss = loss + ctc_weight * term(out["ctc_logit"][0], src_tokens)
     if tgt_tokens is not None:
         if inter_xctc_weight > 0 and out["inter_xctc_logits"]:
-            it = [ctc_criterion_loss(lg, pad, tgt_tokens) for lg in out["inter_xctc_logits"]]
+            it = [term(lg, tgt_tokens) for lg in out["inter_xctc_logits"]]
             loss = loss + inter_xctc_weight * sum(it) / len(it)
         if xctc_weight > 0 and out["xctc_logit"]:
-            loss = loss + xctc_weight * ctc_criterion_loss(out["xctc_logit"][0], pad, tgt_tokens)
+            loss = loss + xctc_weight * term(out["xctc_logit"][0], tgt_tokens)
     return loss
 
 
@@ -566,7 +677,11 @@ def config_from_args(args) -> OracleConfig:
         inter_ctc_layers=split(g("inter_ctc_layers")), inter_xctc_layers=split(g("inter_xctc_layers")),
         share_inter_ctc=g("share_inter_ctc", False), ctc_pae=g("ctc_pae", "none"),
         xctc_pae=g("xctc_pae", g("ctc_pae", "none")),
-        pae_unnorm_input=g("pae_unnorm_input", False), **_pds_from_args(args))
+        pae_unnorm_input=g("pae_unnorm_input", False), ctc_pae_gt_ratio=g("ctc_pae_ground_truth_ratio", 0.0),
+        xctc_pae_gt_ratio=g("xctc_pae_ground_truth_ratio", 0.0),
+        pae_adaptive_gt=g("xctc_pae_ground_truth_ratio_adaptive", False),
+        pae_gt_only_mistake=g("xctc_pae_ground_truth_only_mistake", False),
+        pae_oracle_smooth=g("pae_oracle_smooth", False), **_pds_from_args(args))
 
 
 def _pds_from_args(args) -> dict:

@@ -257,6 +257,103 @@ def run_reference_encoder(case: str, seed: int = 0):
     return fix
 
 
+CURR_CASE = dict(ENC_CASES["c5_small"], ctc_pae_ground_truth_ratio=0.3, xctc_pae_ground_truth_ratio=0.4,
+                 xctc_pae_ground_truth_only_mistake=True, pae_oracle_smooth=True)
+
+
+def run_reference_curriculum(seed: int = 0):
+    """The ground-truth curriculum of the prediction-aware adapters (reproduction_bil_ctc_synchronous.yaml:62-65) through
+    the REFERENCE encoder: first pass (no grad) -> alignment oracle (restated criterion arithmetic over the Viterbi
+    restatement: criterions/ctc.py and best_alignment.cu cannot run here) -> second pass with ``ctc_alignment_oracle``,
+    the masks drawn by the reference's own torch.rand under a fixed seed.  The restatement must reproduce that pass
+    bit-level with the same seed; the drawn masks, oracle tokens and forced states go into the fixture so that the CUDA
+    path can be given exactly the same ones."""
+    from oracle import encoder as OE
+    from oracle import ref_shim
+    ref = ref_shim.load()
+    spec = dict(CURR_CASE)
+    B, T, S, vocab = spec["B"], spec["T"], spec["S"], spec["vocab"]
+    args = reference_args(**spec)
+    task = ref.FakeTask(vocab, vocab)
+    torch.manual_seed(seed)
+    ref.s2t.s2t_transformer_s(args)
+    enc = ref.s2t.S2TTransformerEncoder(args, task, None)
+    shapes = {k: v.shape for k, v in enc.state_dict().items() if not k.endswith("_float_tensor")}
+    sd = seeded_state_dict(shapes, seed)
+    enc.load_state_dict(sd, strict=False)
+    enc.train()
+    feats, lens, tokens = synth_batch(B, T, S, vocab, seed + 1)
+    tgt_tokens = synth_batch(B, T, S + 2, vocab, seed + 2)[2]
+    wkw = dict(ctc_weight=args.ctc_weight, xctc_weight=args.xctc_weight, inter_ctc_weight=args.inter_ctc_weight,
+               inter_xctc_weight=args.inter_xctc_weight)
+    with torch.no_grad():
+        first = enc(feats, lens)
+    align = OE.ground_truth_alignment(first, tokens, tgt_tokens)
+    assert set(align) == {"ctc", "xctc"}
+    torch.manual_seed(1234)
+    out = enc(feats, lens, ctc_alignment_oracle=align)
+    fe_c, fe_x = out["inter_ctc_logits"][0][2], out["inter_xctc_logits"][0][2]
+    assert (fe_c >= 0).any() and (fe_x >= 0).any(), "the curriculum drew no forced frame: raise the ratios"
+    results = {}
+    for masked in (False, True):
+        enc.zero_grad(set_to_none=True)
+        o = out if not masked else None
+        if masked:
+            torch.manual_seed(1234)
+            o = enc(feats, lens, ctc_alignment_oracle=align)
+        loss = OE.ctc_criterion_total(o, tokens, tgt_tokens, masked_loss=masked, **wkw)
+        loss.backward()
+        results[masked] = (loss.item(), {k: p.grad.clone() for k, p in enc.named_parameters()})
+    # ---- the restatement, same seed -----------------------------------------------------------------
+    cfg = OE.config_from_args(args)
+    orc = OE.S2TTransformerEncoder(cfg)
+    orc.load_state_dict(sd)
+    orc.train()
+    for masked in (False, True):
+        orc.zero_grad(set_to_none=True)
+        torch.manual_seed(1234)
+        o_out = orc(feats, lens, ctc_alignment_oracle=align)
+        assert torch.equal(o_out["inter_ctc_logits"][0][2], fe_c) and torch.equal(o_out["inter_xctc_logits"][0][2], fe_x)
+        for a, b in zip(o_out["inter_xctc_logits"] + o_out["inter_ctc_logits"], out["inter_xctc_logits"] + out["inter_ctc_logits"]):
+            assert (a[0] - b[0]).abs().max().item() < 1e-4
+        assert (o_out["encoder_out"][0] - out["encoder_out"][0]).abs().max().item() < 1e-4
+        o_loss = OE.ctc_criterion_total(o_out, tokens, tgt_tokens, masked_loss=masked, **wkw)
+        o_loss.backward()
+        ref_loss, ref_grads = results[masked]
+        assert abs(o_loss.item() - ref_loss) < 1e-3 * abs(ref_loss)
+        for k, p in orc.named_parameters():
+            rel = (p.grad - ref_grads[k]).norm().item() / (ref_grads[k].norm().item() + 1e-8)
+            assert rel < 1e-3, (k, rel)
+    # the injected-mask interface reproduces the drawn pass
+    masks = {"ctc": fe_c >= 0, "xctc": fe_x >= 0}
+    inj = orc(feats, lens, ctc_alignment_oracle=align, oracle_masks=masks)
+    assert (inj["encoder_out"][0] - out["encoder_out"][0]).abs().max().item() < 1e-5
+    print(f"[c5_curr_small] oracle == reference under the curriculum: forced frames ctc {int((fe_c >= 0).sum())}, "
+          f"xctc {int((fe_x >= 0).sum())} of {fe_c.numel()}; loss {results[False][0]:.4f} (masked loss {results[True][0]:.4f})")
+    fix = dict(
+        seed=seed, weights_sha256=state_checksum(sd), param_names=np.array(sorted(shapes)),
+        param_shapes=np.array([str(tuple(shapes[k])) for k in sorted(shapes)]),
+        feats=feats.numpy(), lens=lens.numpy(), tokens=tokens.numpy(), tgt_tokens=tgt_tokens.numpy(),
+        oracle_ctc=align["ctc"][0].numpy(), oracle_xctc=align["xctc"][0].numpy(),
+        states_ctc=align["ctc"][1].numpy(), states_xctc=align["xctc"][1].numpy(),
+        mask_ctc=masks["ctc"].numpy(), mask_xctc=masks["xctc"].numpy(),
+        force_emit_ctc=fe_c.numpy(), force_emit_xctc=fe_x.numpy(),
+        encoder_out=out["encoder_out"][0].detach().numpy(), padding_mask=out["encoder_padding_mask"][0].numpy(),
+        loss=np.float64(results[False][0]), loss_masked=np.float64(results[True][0]),
+        torch_version=torch.__version__,
+    )
+    # a few whole gradients (the tensors the curriculum touches most directly) and the norm of every gradient
+    keep = ["xctc_pae.embed_adapter.weight", "pae.embed_adapter.weight", "xctc_norm3.weight", "ctc_norm2.weight",
+            "xctc.ctc_projection.weight", "layers.0.self_attn_layer_norm.bias", "embed_ln.weight"]
+    for masked, tag in ((False, "grad::"), (True, "gradm::")):
+        for k in keep:
+            fix[tag + k] = results[masked][1][k].numpy()
+        names = sorted(results[masked][1])
+        fix[tag[:-2] + "_norms"] = np.array([results[masked][1][k].norm().item() for k in names])
+    fix["grad_names"] = np.array(sorted(results[False][1]))
+    return fix
+
+
 def run_reference_fbank(seed: int = 0):
     import torchaudio
     import torchaudio.compliance.kaldi as K
@@ -286,6 +383,7 @@ def run_reference_fbank(seed: int = 0):
 def main():
     GOLDEN.mkdir(parents=True, exist_ok=True)
     np.savez_compressed(GOLDEN / "fbank_cmvn.npz", **run_reference_fbank())
+    np.savez_compressed(GOLDEN / "enc_c5_curr_small.npz", **run_reference_curriculum())
     for case in ENC_CASES:
         np.savez_compressed(GOLDEN / f"enc_{case}.npz", **run_reference_encoder(case))
     for f in sorted(GOLDEN.glob("*.npz")):

@@ -83,6 +83,34 @@ softmax_rows_bwd_kernel(const __nv_bfloat16* __restrict__ probs, const __nv_bflo
   }
 }
 
+
+// Prediction-aware encoding with ground-truth mixing (curriculum, s2t_transformer.py:1904-1946 / 2061-2103 and
+// adapter.py:244-262): rows whose mask is set take the (optionally smoothed) one-hot distribution of their aligned ground-truth token
+// instead of the model's softmax: smooth -> 0.9 + 0.1 / V on the token, 0.1 / V elsewhere (pae-oracle-smooth).
+__global__ void __launch_bounds__(256)
+rows_truth_mix_kernel(__nv_bfloat16* __restrict__ probs, long long ldp, const int* __restrict__ truth_tok,
+                       const int* __restrict__ mask, int V, int smooth) {
+  pdl_entry();
+  const long long row = blockIdx.x;
+  if (mask[row] == 0) return;
+  const int tok = truth_tok[row];
+  const float on = smooth ? 0.9f + 0.1f / static_cast<float>(V) : 1.f;
+  const float off = smooth ? 0.1f / static_cast<float>(V) : 0.f;
+  __nv_bfloat16* y = probs + row * ldp;
+  for (int v = threadIdx.x; v < static_cast<int>(ldp); v += 256)
+    y[v] = __float2bfloat16(v < V ? (v == tok ? on : off) : 0.f);
+}
+
+// x[r][:] = 0 for rows whose mask is set (no gradient reaches the logits of a frame whose distribution was replaced)
+__global__ void __launch_bounds__(256)
+rows_zero_masked_kernel(__nv_bfloat16* __restrict__ x, long long ld, const int* __restrict__ mask, int ncols) {
+  pdl_entry();
+  const long long row = blockIdx.x;
+  if (mask[row] == 0) return;
+  __nv_bfloat16* y = x + row * ld;
+  for (int v = threadIdx.x; v < ncols; v += 256) y[v] = __float2bfloat16(0.f);
+}
+
 }  // namespace s2t
 
 using namespace s2t;
@@ -105,6 +133,25 @@ extern "C" int s2t_softmax_rows_bwd(const void* probs, const void* dprobs, long 
               "s2t_softmax_rows_bwd: row strides must be multiples of 8 and cover round8(V)");
   if (rows <= 0) return 0;
   S2T_LAUNCH(softmax_rows_bwd_kernel, rows, 256, 0, reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<const __nv_bfloat16*>(probs), reinterpret_cast<const __nv_bfloat16*>(dprobs), ldp, reinterpret_cast<__nv_bfloat16*>(dlogits), ldv, V, accumulate);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int s2t_rows_truth_mix(void* probs, long long ldp, const int* truth_tok, const int* mask, int rows, int V,
+                                   int smooth, void* stream) {
+  S2T_REQUIRE(probs && truth_tok && mask, "s2t_rows_truth_mix: null pointer");
+  S2T_REQUIRE(V > 0 && ldp >= V, "s2t_rows_truth_mix: ldp must cover V");
+  if (rows <= 0) return 0;
+  S2T_LAUNCH(rows_truth_mix_kernel, rows, 256, 0, reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<__nv_bfloat16*>(probs), ldp, truth_tok, mask, V, smooth);
+  S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int s2t_rows_zero_masked(void* x, long long ld, const int* mask, int rows, int ncols, void* stream) {
+  S2T_REQUIRE(x && mask, "s2t_rows_zero_masked: null pointer");
+  S2T_REQUIRE(ncols >= 0 && ld >= ncols, "s2t_rows_zero_masked: ld must cover ncols");
+  if (rows <= 0 || ncols == 0) return 0;
+  S2T_LAUNCH(rows_zero_masked_kernel, rows, 256, 0, reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<__nv_bfloat16*>(x), ld, mask, ncols);
   S2T_LAUNCH_CHECK();
   return 0;
 }

@@ -83,6 +83,7 @@ class EncoderConfig:
     ctc_pae: str = "none"                  # none | inter_league
     xctc_pae: str = "none"
     pae_unnorm_input: bool = False
+    pae_gt_smooth: bool = False            # --pae-[o]racle-smooth: smoothed one-hot of the aligned ground-truth token (adapter.py:256-257)
     # --- PDS (pdss2t_transformer.py:1361-1560; defaults = pdss2t_transformer_s_8) -------------------------
     pds_layers: Tuple[int, ...] = (3, 3, 3, 3)
     pds_ratios: Tuple[int, ...] = (2, 2, 1, 2)
@@ -119,7 +120,8 @@ class EncoderConfig:
             inter_ctc_layers=csv(g("inter_ctc_layers")), inter_ctc_weight=g("inter_ctc_weight", 0.0),
             inter_xctc_layers=csv(g("inter_xctc_layers")), inter_xctc_weight=g("inter_xctc_weight", 0.0),
             share_inter_ctc=g("share_inter_ctc", False), ctc_pae=g("ctc_pae", "none"),
-            xctc_pae=g("xctc_pae", g("ctc_pae", "none")), pae_unnorm_input=g("pae_unnorm_input", False))
+            xctc_pae=g("xctc_pae", g("ctc_pae", "none")), pae_unnorm_input=g("pae_unnorm_input", False),
+            pae_gt_smooth=g("pae_oracle_smooth", False))
         if family == "pds":
             n = int(args.pds_stages)
             kw.update(encoder_type="pds", pds_layers=ints(args.pds_layers)[:n], pds_ratios=ints(args.pds_ratios)[:n],
@@ -467,6 +469,9 @@ class Plan:
                     cur = I.xout
                 else:
                     I.xout = cur
+        # ground-truth curriculum of the prediction-aware adapters (engine.set_ground_truth): per head (aligned token, mask,
+        # forced state) per frame, int32 [B*T']; None = off
+        self.gt: Dict[int, Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = {}
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.graph_kind: Optional[str] = None
         self.nbytes = 0
@@ -605,6 +610,7 @@ class S2TEncoderEngine:
         self._lag_events: list = []
         self._lag_stage, self._lag_bufs = None, ()
         self.dp = None               # dp.BucketedAllReduce when data parallel
+        self.ctc_masked_loss = False  # criterion option: imputer loss on the inter terms under the curriculum (_loss)
         self.collective_free_warmup = False   # capture(): warm-up step without collectives (per-rank plans, see capture)
         self.init_parameters()
 
@@ -1199,6 +1205,11 @@ class S2TEncoderEngine:
         ops.row_lse(I.logits, hs.V, out=I.lse)
         if hs.pae:
             ops.softmax_rows_fwd(I.logits, I.lse, hs.V, out=I.dist)
+            if k in P.gt and self.training:
+                # curriculum: masked frames feed the adapter the (smoothed) one-hot of their aligned ground-truth token
+                # instead of the model's prediction (adapter.py:244-262)
+                tok, msk, _ = P.gt[k]
+                ops.rows_truth_mix_(I.dist, tok, msk, hs.V, self.cfg.pae_gt_smooth and hs.name == "xctc")   # sic: only the XCTC adapter gets the smoothing option (s2t_transformer.py:1066 vs 1233)
             E = S.p(hs.pae + ".embed_adapter.weight")
             C = E.shape[1]
             res = I.xin if c.pae_unnorm_input else I.nx
@@ -1240,6 +1251,10 @@ class S2TEncoderEngine:
             terms = [(Hd.logits, Hd.dlogits, Hd.lse, Hd.loss_idx, True)]
             terms += [(P.inter[(l, k)].logits, P.inter[(l, k)].dlogits, P.inter[(l, k)].lse, P.inter[(l, k)].loss_idx, False)
                       for l in hs.inter_layers]
+            # masked ("imputer") loss when the criterion asked for it and the curriculum supplies the forced states: the
+            # encoder attaches force_emit to the inter logits AND to the top logits (s2t_transformer.py:1936, 2136-2140;
+            # criterions/ctc.py:455-465, 586-627, 646-666)
+            fe = P.gt[k][2].view(B, T) if (self.ctc_masked_loss and k in P.gt and self.training) else None
             for logits, dlogits, lse, idx, need_lse in terms:
                 if need_lse:
                     ops.row_lse(logits, hs.V, out=lse)
@@ -1247,7 +1262,7 @@ class S2TEncoderEngine:
                 ops.ctc_loss(logits.view(B, T, hs.ldv), P.tg[hs.tgt], P.out_len, P.tl[hs.tgt], hs.V, c.blank,
                              need_grad=need_grad, grad_scale=w, grad_scale_dev=P.batch_weight, lse=lse,
                              dlogits=dlogits.view(B, T, hs.ldv) if need_grad else None, workspace=P.ctc_ws,
-                             nll=P.nll_all[idx])
+                             nll=P.nll_all[idx], force_emit=fe)
         ops.weighted_sum(P.nll_all, P.loss_w, P.loss)
 
     # ------------------------------------------------------------------------------------------
@@ -1442,6 +1457,8 @@ class S2TEncoderEngine:
                     ops.linear_wgrad(dist, dy, out=gE, residual=gE, ldr=C)
                 else:
                     ops.linear_wgrad(dist, dy, out=gE)
+            if k in P.gt and self.training:
+                ops.rows_zero_masked_(Hd.ddist, P.gt[k][1], hs.V)       # replaced frames: no gradient to their logits
             ops.softmax_rows_bwd(I.dist, Hd.ddist, I.dlogits, hs.V, accumulate=True)
         spec = self._drop(hs.site + 1 + hs.inter_layers.index(l))
         t0 = St.take()
@@ -1810,6 +1827,24 @@ class S2TEncoderEngine:
         if xtargets is not None:        # target-text tokens for the XCTC losses (criterions/ctc.py:763-767)
             P.tg[1][:, : xtargets.shape[1]].copy_(xtargets, non_blocking=nb)
             P.tl[1].copy_(xtarget_lengths, non_blocking=nb)
+
+    def set_ground_truth(self, P: Plan, head: int, tokens: Optional[torch.Tensor], mask: Optional[torch.Tensor],
+                   force_emit: Optional[torch.Tensor]) -> None:
+        """Ground-truth curriculum inputs of head ``head`` (0 = CTC, 1 = XCTC) for this batch: per output frame the
+        aligned ground-truth token, the mixing mask and the forced lattice state (-1 = free), each [B, T'] or [B*T'] —
+        what the reference passes as ``ctc_alignment_oracle`` / builds at s2t_transformer.py:1904-1946, 2061-2103.
+        ``tokens=None`` switches the curriculum of that head off.  Static int32 buffers: a captured graph stays valid as
+        long as the set of heads with a curriculum does not change (re-capture otherwise)."""
+        if tokens is None:
+            P.gt.pop(head, None)
+            return
+        if head not in P.gt:
+            z = lambda: torch.zeros(P.R, dtype=torch.int32, device=self.device)
+            P.gt[head] = (z(), z(), torch.full((P.R,), -1, dtype=torch.int32, device=self.device))
+        tok, msk, fe = P.gt[head]
+        tok.copy_(tokens.reshape(-1).to(torch.int32), non_blocking=True)
+        msk.copy_(mask.reshape(-1).to(torch.int32), non_blocking=True)
+        fe.copy_(force_emit.reshape(-1).to(torch.int32), non_blocking=True)
 
     def forward(self, P: Plan) -> None:
         """Encoder forward on the plan's inputs; results in P.enc_out [B*T', C], P.logits [B*T', ldv], P.out_len."""

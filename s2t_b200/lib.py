@@ -101,6 +101,8 @@ SIGNATURES = {
     "s2t_act_dropout": (_i, [_vp, _vp, _ll, _i, _f, _ull, _u, _vp, _vp]),
     "s2t_softmax_rows_fwd": (_i, [_vp, _ll, _vp, _vp, _ll, _i, _i, _vp]),
     "s2t_softmax_rows_bwd": (_i, [_vp, _vp, _ll, _vp, _ll, _i, _i, _i, _vp]),
+    "s2t_rows_truth_mix": (_i, [_vp, _ll, _vp, _vp, _i, _i, _i, _vp]),
+    "s2t_rows_zero_masked": (_i, [_vp, _ll, _vp, _i, _i, _vp]),
     "s2t_row_lse": (_i, [_vp, _i, _ll, _i, _i, _vp, _vp]),
     "s2t_ctc_workspace_bytes": (_ll, [_i, _i, _i]),
     "s2t_ctc_loss": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp, _ll, _vp]),

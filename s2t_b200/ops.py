@@ -606,6 +606,16 @@ def softmax_rows_fwd(logits: torch.Tensor, lse: torch.Tensor, V: int, out: Optio
     return out
 
 
+def rows_truth_mix_(probs: torch.Tensor, truth_tok: torch.Tensor, mask: torch.Tensor, V: int, smooth: bool) -> None:
+    """In place: rows with mask != 0 become the (smoothed) one-hot distribution of their aligned ground-truth token (int32 [rows])."""
+    _call("s2t_rows_truth_mix", _p(probs), probs.stride(0), _p(truth_tok), _p(mask), probs.shape[0], V, int(smooth),
+          _stream())
+
+
+def rows_zero_masked_(x: torch.Tensor, mask: torch.Tensor, ncols: int) -> None:
+    _call("s2t_rows_zero_masked", _p(x), x.stride(0), _p(mask), x.shape[0], ncols, _stream())
+
+
 def softmax_rows_bwd(probs: torch.Tensor, dprobs: torch.Tensor, dlogits: torch.Tensor, V: int,
                      accumulate: bool = False) -> torch.Tensor:
     _call("s2t_softmax_rows_bwd", _p(probs), _p(dprobs), probs.stride(0), _p(dlogits), dlogits.stride(0),

@@ -131,7 +131,13 @@ class S2TTransformerEncoderB200(_EncoderBase):
         self.engine = S2TEncoderEngine(self.cfg)          # raises without a CUDA device (no CPU fallback)
         # the whole model is one flat bf16 parameter; .grad is the engine's flat gradient buffer
         self.flat = nn.Parameter(self.engine.store.flat, requires_grad=True)
-        self.pae_ground_truth_ratio = 0                   # criterions/ctc.py:262 (curriculum: SURVEY.md §8f rank 1)
+        # ground-truth curriculum of the prediction-aware adapters (s2t_transformer.py:947-949, 1050-1052, 1129-1148):
+        # the criterion reads the sum (criterions/ctc.py:262) and, when non-zero, aligns the batch first (_curriculum)
+        g = lambda k, d: getattr(args, k, d)
+        self.gt_ratio = {"ctc": float(g("ctc_pae_ground_truth_ratio", 0) or 0), "xctc": float(g("xctc_pae_ground_truth_ratio", 0) or 0)}
+        self.pae_adaptive_gt = bool(g("xctc_pae_ground_truth_ratio_adaptive", False))
+        self.pae_gt_only_mistake = bool(g("xctc_pae_ground_truth_only_mistake", False))
+        self.pae_ground_truth_ratio = self.gt_ratio["ctc"] + self.gt_ratio["xctc"]
         self.num_updates = 0
         self.ctc_infer_cfg = None
         self._last_plan: Optional[Plan] = None
@@ -319,6 +325,7 @@ class CtcCriterionB200(nn.Module):
         self.pad_idx = tgt.pad() if tgt is not None else 1
         self.eos_idx = tgt.eos() if tgt is not None else 2
         self.sentence_avg = bool(g("sentence_avg", False))
+        self.ctc_masked_loss = bool(g("ctc_masked_loss", False))          # criterions/ctc.py:92-95, 214
         self.post_process = g("post_process", "sentencepiece")
         self.ctc_weight = ctc_weight
 
@@ -329,6 +336,33 @@ class CtcCriterionB200(nn.Module):
     # criterions/ctc.py:516-540 — pad / eos stripped, left-packed int32 [B, S] + lengths
     def get_targets_for_ctc_loss(self, tokens: torch.Tensor):
         return S2TEncoderEngine.strip_targets(tokens, self.pad_idx, self.eos_idx)
+
+    def _curriculum(self, enc, eng, P) -> None:
+        """``get_ground_truth_alignment`` (criterions/ctc.py:262-265, 283-433) and the mask draw of the encoder
+        (s2t_transformer.py:1904-1936, 2061-2092), all on the device: a first forward pass without gradient, the best CTC
+        alignment of its TOP logits against the targets (``s2t_ctc_viterbi`` = torch_imputer.best_alignment + backtrack),
+        per frame the aligned ground-truth token, the mistake flags (argmax != aligned token) and the random mixing
+        mask; the forced states are the alignment where the mask is set, -1 elsewhere."""
+        eng.forward_train(P)
+        B, T2 = P.B, P.T2
+        for k, hs in enumerate(eng.heads):
+            ratio = enc.gt_ratio.get(hs.name, 0.0)
+            if ratio <= 0 or not hs.pae or not hs.inter_layers:
+                eng.set_ground_truth(P, k, None, None, None)
+                continue
+            lp = torch.log_softmax(P.heads[k].logits.view(B, T2, hs.ldv)[..., : hs.V], dim=-1, dtype=torch.float32)
+            states, _ = ops.ctc_viterbi(lp.contiguous(), P.tg[hs.tgt], P.out_len, P.tl[hs.tgt], self.blank_idx,
+                                        with_nll=False)
+            bap = states.clamp(min=0).long()                              # best_aligns_pad: 0 beyond the utterance
+            tgt = P.tg[hs.tgt].long()
+            pos = torch.div(bap, 2, rounding_mode="floor").clamp(max=tgt.shape[1] - 1)
+            tok = tgt.gather(1, pos).masked_fill(bap % 2 == 0, self.blank_idx)
+            mistake = lp.argmax(dim=-1) != tok
+            prob = ratio * (mistake.sum(-1) / P.out_len).unsqueeze(-1) if enc.pae_adaptive_gt else ratio
+            mask = torch.rand(tok.shape, device=tok.device) < prob
+            if enc.pae_gt_only_mistake:
+                mask = mask & mistake
+            eng.set_ground_truth(P, k, tok, mask, bap.masked_fill(~mask, -1))
 
     def forward(self, model, sample, reduce=True):
         enc: S2TTransformerEncoderB200 = getattr(model, "encoder", model)
@@ -347,6 +381,9 @@ class CtcCriterionB200(nn.Module):
         eng.set_inputs(P, feats=src_tokens.float(), src_lengths=src_lengths.to(torch.int32), targets=tg,
                        target_lengths=tl, xtargets=xt, xtarget_lengths=xl)
         if model.training and torch.is_grad_enabled():
+            if getattr(enc, "pae_ground_truth_ratio", 0) != 0:
+                eng.ctc_masked_loss = self.ctc_masked_loss
+                self._curriculum(enc, eng, P)
             if enc.use_graph and P.graph is None:
                 eng.capture(P, "train")
             loss = _EngineStep.apply(enc.flat, enc, P)

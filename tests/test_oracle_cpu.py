@@ -143,3 +143,45 @@ def test_oracle_reproduces_reference_at_full_size(name):
     assert np.allclose(got["enc_abs_mean"], fx["enc_abs_mean"], rtol=1e-4)
     assert got["grad_names"].tolist() == fx["grad_names"].tolist()
     assert np.allclose(got["grad_norms"], fx["grad_norms"], rtol=1e-3, atol=1e-7)
+
+
+@pytest.mark.parametrize("masked", [False, True])
+def test_oracle_curriculum_reproduces_reference_fixture(masked):
+    """Ground-truth curriculum of the prediction-aware adapters: tests/golden/enc_c5_curr_small.npz holds what the
+    REFERENCE encoder produced with the masks its own torch.rand drew (oracle/make_golden.py run_reference_curriculum,
+    restatement asserted equal there).  Given the same aligned tokens / masks through the injection interface, the
+    restatement must reproduce loss (plain and imputer) and gradient norms."""
+    import numpy as np
+    from pathlib import Path
+    from oracle import encoder as OE
+    from oracle.make_golden import CURR_CASE, reference_args, seeded_state_dict, state_checksum
+    fx = np.load(Path(__file__).resolve().parent / "golden" / "enc_c5_curr_small.npz")
+    args = reference_args(**dict(CURR_CASE))
+    for k, v in dict(encoder_embed_dim=256, encoder_attention_heads=4, subsampling_layers=2, subsampling_kernel=5,
+                     subsampling_stride=2).items():
+        if not hasattr(args, k):
+            setattr(args, k, v)
+    cfg = OE.config_from_args(args)
+    orc = OE.S2TTransformerEncoder(cfg)
+    shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
+    sd = seeded_state_dict(shapes, int(fx["seed"]))
+    assert state_checksum(sd) == str(fx["weights_sha256"])
+    orc.load_state_dict(sd)
+    orc.train()
+    t = lambda k: torch.from_numpy(fx[k])
+    align = {h: (t(f"oracle_{h}"), t(f"states_{h}"), None, None) for h in ("ctc", "xctc")}
+    masks = {h: t(f"mask_{h}") for h in ("ctc", "xctc")}
+    out = orc(t("feats"), t("lens"), ctc_alignment_oracle=align, oracle_masks=masks)
+    assert torch.equal(out["inter_xctc_logits"][0][2], t("force_emit_xctc"))
+    assert (out["encoder_out"][0].detach() - t("encoder_out")).abs().max().item() < 1e-4
+    loss = OE.ctc_criterion_total(out, t("tokens"), t("tgt_tokens"), ctc_weight=args.ctc_weight, xctc_weight=args.xctc_weight,
+                                  inter_ctc_weight=args.inter_ctc_weight, inter_xctc_weight=args.inter_xctc_weight,
+                                  masked_loss=masked)
+    ref = float(fx["loss_masked" if masked else "loss"])
+    assert abs(loss.item() - ref) <= 1e-4 * abs(ref), (loss.item(), ref)
+    loss.backward()
+    names = [str(n) for n in fx["grad_names"]]
+    norms = dict(zip(names, fx[("gradm" if masked else "grad") + "_norms"]))
+    grads = {k: p.grad for k, p in orc.named_parameters()}
+    for n, gn in norms.items():
+        assert abs(float(grads[n].norm()) - gn) <= 1e-3 * gn + 1e-7, (n, float(grads[n].norm()), gn)

@@ -72,3 +72,67 @@ def test_unverified_masked_ctc_loss_matches_oracle(cuda_lib):
             assert (dl_f.float() - dl_p.float()).abs().max().item() < tol
         print("masked CTC loss ok")
     """)
+
+
+def test_unverified_ground_truth_curriculum_matches_reference_fixture(cuda_lib):
+    """The ground-truth curriculum of the prediction-aware adapters (reproduction_bil_ctc_synchronous.yaml:62-65): with the
+    aligned tokens, masks and forced states the REFERENCE drew (tests/golden/enc_c5_curr_small.npz, oracle/make_golden.py
+    run_reference_curriculum: restatement == reference) given to the engine (set_ground_truth), loss and gradients must
+    match the reference's — plain CTC loss and, with ctc_masked_loss, the imputer loss on every term."""
+    run_isolated("""
+        import numpy as np, torch
+        from pathlib import Path
+        from oracle.make_golden import CURR_CASE, seeded_state_dict, state_checksum
+        from s2t_b200.engine import EncoderConfig, S2TEncoderEngine
+        fx = np.load(Path("tests/golden/enc_c5_curr_small.npz"))
+        sp = CURR_CASE
+        csv = lambda k: tuple(int(v) for v in sp[k].split(","))
+        cfg = dict(layers=sp["encoder_layers"], embed_dim=sp["encoder_embed_dim"], ffn_dim=sp["encoder_ffn_embed_dim"],
+                   heads=sp["encoder_attention_heads"], subsampling_filter=sp["subsampling_filter"], vocab=sp["vocab"],
+                   tgt_vocab=sp["vocab"], dropout=0.0, macaron_style=True, use_cnn_module=True, cnn_module_kernel=15,
+                   attn_type="rel_pos", encoder_activation_fn="swish", ctc_weight=sp["ctc_weight"], xctc_weight=sp["xctc_weight"],
+                   inter_ctc_layers=csv("inter_ctc_layers"), inter_ctc_weight=sp["inter_ctc_weight"],
+                   inter_xctc_layers=csv("inter_xctc_layers"), inter_xctc_weight=sp["inter_xctc_weight"],
+                   ctc_pae=sp["ctc_pae"], xctc_pae=sp["xctc_pae"], pae_unnorm_input=sp["pae_unnorm_input"], pae_gt_smooth=True)
+        shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
+        sd = seeded_state_dict(shapes, int(fx["seed"]))
+        assert state_checksum(sd) == str(fx["weights_sha256"])
+        feats, lens = torch.from_numpy(fx["feats"]), torch.from_numpy(fx["lens"])
+        names = [str(n) for n in fx["grad_names"]]
+        for masked, lkey, tag in ((False, "loss", "grad"), (True, "loss_masked", "gradm")):
+            eng = S2TEncoderEngine(EncoderConfig(**cfg))
+            eng.load_state_dict(sd)
+            eng.ctc_masked_loss = masked
+            tg, tl = eng.strip_targets(torch.from_numpy(fx["tokens"]))
+            xt, xl = eng.strip_targets(torch.from_numpy(fx["tgt_tokens"]))
+            B, T, _ = feats.shape
+            P = eng.plan(B, T, max(tg.shape[1], xt.shape[1]))
+            eng.set_inputs(P, feats=feats, src_lengths=lens.to(torch.int32), targets=tg, target_lengths=tl, xtargets=xt,
+                           xtarget_lengths=xl)
+            for k, h in enumerate(("ctc", "xctc")):
+                eng.set_ground_truth(P, k, torch.from_numpy(fx[f"oracle_{h}"]).cuda(), torch.from_numpy(fx[f"mask_{h}"]).cuda(),
+                                     torch.from_numpy(fx[f"force_emit_{h}"]).cuda())
+            eng.train_step(P)
+            torch.cuda.synchronize()
+            ref_loss = float(fx[lkey])
+            assert abs(P.loss.item() - ref_loss) <= 1e-2 * abs(ref_loss), (masked, P.loss.item(), ref_loss)
+            valid = ~torch.from_numpy(fx["padding_mask"]).T
+            enc = P.enc_out.float().view(B, P.T2, -1).transpose(0, 1).cpu()
+            ref_enc = torch.from_numpy(fx["encoder_out"])
+            assert float((enc[valid] - ref_enc[valid]).norm() / ref_enc[valid].norm()) <= 3e-2
+            grads = eng.grads()
+            for key in fx.files:
+                if key.startswith(tag + "::"):
+                    n = key.split("::", 1)[1]
+                    ref = torch.from_numpy(fx[key])
+                    rel = float((grads[n].cpu() - ref).norm() / (ref.norm() + 1e-12))
+                    assert rel <= 0.15, (masked, n, rel)
+            norms = dict(zip(names, fx[tag + "_norms"]))
+            for n, gn in norms.items():
+                if n.endswith(("linear_k.bias", "k_proj.bias")) or gn < 1e-6:
+                    continue
+                mine = float(grads[n].norm())
+                assert abs(mine - gn) <= 0.2 * gn + 1e-6, (masked, n, mine, gn)
+            # without the curriculum inputs the same engine gives a different loss (the mixing really happened)
+        print("curriculum ok")
+    """)
