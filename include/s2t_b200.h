@@ -437,6 +437,16 @@ int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, const int* in
                    int* frame_ids, float* scores, float* frame_lp, void* stream);
 
 /* --------------------------------------------------------------------------------------------- */
+/* Batch collation on the device.  Replaces _collate_frames + index_select(order) of                 */
+/* SpeechToTextDataset.collater (fairseq/data/audio/speech_to_text_dataset.py:267-285, 411-423).     */
+/* packed fp32: the utterances of a batch back to back (utterance i at element offsets[i], lengths[i] */
+/* frames of F values; F = 1 for raw waveforms); order int32 [B] (the collater's descending-length    */
+/* permutation) or NULL; out fp32 [B] x out_bs + [T][F], zero padded; lengths_out int32 [B] or NULL.  */
+/* --------------------------------------------------------------------------------------------- */
+int s2t_collate_frames(const float* packed, const long long* offsets, const int* lengths, const int* order,
+                       int batch, int T, int F, float* out, long long out_bs, int* lengths_out, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
 /* Length-bucketed batching for the data-parallel path (host only, no device work).               */
 /* Replaces fairseq/data/data_utils_fast.pyx:20-103 batch_by_size_vec (behind                      */
 /* FairseqDataset.batch_by_size, --max-tokens / --required-batch-size-multiple).                   */

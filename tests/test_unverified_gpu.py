@@ -136,3 +136,34 @@ def test_unverified_ground_truth_curriculum_matches_reference_fixture(cuda_lib):
             # without the curriculum inputs the same engine gives a different loss (the mixing really happened)
         print("curriculum ok")
     """)
+
+
+def test_unverified_device_collate_is_bit_exact(cuda_lib):
+    """s2t_collate_frames (speech_to_text_dataset.py:267-285, 411-423 on the device) against the reference's own outputs
+    (tests/golden/collate.npz): packed utterances -> zero-padded, length-sorted batch, bit-exact; also into a larger plan
+    buffer (row stride > T * F) and with T larger than the longest utterance (frame bucket)."""
+    run_isolated("""
+        import numpy as np, torch
+        from s2t_b200 import collate as PC
+        fx = np.load("tests/golden/collate.npz")
+        for name in ("feat80", "feat83", "wave", "single"):
+            F = int(fx[f"{name}::F"])
+            lens = fx[f"{name}::lengths"].tolist()
+            packed = torch.from_numpy(fx[f"{name}::packed"])
+            frames, o = [], 0
+            for n in lens:
+                frames.append(packed[o:o + n * F].view(n, F) if F > 1 else packed[o:o + n])
+                o += n * F
+            pk, offsets, lengths, order = PC.pack_frames(frames)
+            want = torch.from_numpy(fx[f"{name}::collated"])
+            B, T = want.shape[0], want.shape[1]
+            out, lo = PC.collate_frames(pk.cuda(), offsets.cuda(), lengths.cuda(), order.cuda(), T, F)
+            assert torch.equal(out.cpu().view(want.shape), want), name
+            assert lo.cpu().tolist() == sorted(lens, reverse=True), name
+            big = torch.full((B, (T + 5) * F + 4), 7.0, device="cuda")
+            PC.collate_frames(pk.cuda(), offsets.cuda(), lengths.cuda(), order.cuda(), T + 5, F, out=big)
+            got = big.cpu()[:, : (T + 5) * F].view(B, T + 5, F)
+            assert torch.equal(got[:, :T].reshape(want.shape), want) and float(got[:, T:].abs().max()) == 0.0, name
+            assert float((big.cpu()[:, (T + 5) * F:] - 7.0).abs().max()) == 0.0      # beyond the row: untouched
+        print("device collate ok")
+    """)
