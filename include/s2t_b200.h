@@ -437,6 +437,25 @@ int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, const int* in
                    int* frame_ids, float* scores, float* frame_lp, void* stream);
 
 /* --------------------------------------------------------------------------------------------- */
+/* Fused update over the flat bf16 parameter / gradient buffers.  Replaces, per update, the trainer's */
+/* optimizer.multiply_grads -> clip_grad_norm -> Adam.step -> copy to the low-precision parameters    */
+/* (fairseq/trainer.py:729-759, fairseq/utils.py:328-369, fairseq/optim/adam.py:145-231,              */
+/* fairseq/optim/fp16_optimizer.py).                                                                  */
+/* s2t_grad_norm: total_norm[0] = mult * ||grad||_2 (fp32 accumulation, fixed summation order);       */
+/* partials: fp32 scratch of s2t_grad_norm_partials(n) elements.                                      */
+/* s2t_fused_adam: g = grad * grad_mult * clip_coef, clip_coef = min(1, max_norm / (total_norm[0] +   */
+/* 1e-6)) when total_norm != NULL and max_norm > 0; m, v, master fp32 [n]; param = bf16(master);      */
+/* step counts from 1; lr_dev / step_dev: optional device scalars that override lr / step (a captured */
+/* graph replays with fresh values).                                                                  */
+/* --------------------------------------------------------------------------------------------- */
+int s2t_grad_norm_partials(long long n);
+int s2t_grad_norm(const void* grad, long long n, float mult, float* partials, float* total_norm, void* stream);
+int s2t_fused_adam(void* param, float* master, const void* grad, float* exp_avg, float* exp_avg_sq, long long n,
+                   float lr, float beta1, float beta2, float eps, float weight_decay, long long step,
+                   float grad_mult, const float* total_norm, float max_norm, const float* lr_dev,
+                   const long long* step_dev, void* stream);
+
+/* --------------------------------------------------------------------------------------------- */
 /* Batch collation on the device.  Replaces _collate_frames + index_select(order) of                 */
 /* SpeechToTextDataset.collater (fairseq/data/audio/speech_to_text_dataset.py:267-285, 411-423).     */
 /* packed fp32: the utterances of a batch back to back (utterance i at element offsets[i], lengths[i] */

@@ -107,6 +107,9 @@ SIGNATURES = {
     "s2t_ctc_workspace_bytes": (_ll, [_i, _i, _i]),
     "s2t_ctc_loss": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp, _ll, _vp]),
     "s2t_ctc_loss_masked": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp, _ll, _vp]),
+    "s2t_grad_norm_partials": (_i, [_ll]),
+    "s2t_grad_norm": (_i, [_vp, _ll, _f, _vp, _vp, _vp]),
+    "s2t_fused_adam": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _f, _ll, _f, _vp, _f, _vp, _vp, _vp]),
     "s2t_collate_frames": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _ll, _vp, _vp]),
     "s2t_batch_by_size": (_ll, [_vp, _ll, _ll, _ll, _i, _vp]),
     "s2t_ctc_greedy": (_i, [_vp, _i, _ll, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

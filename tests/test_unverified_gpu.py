@@ -167,3 +167,40 @@ def test_unverified_device_collate_is_bit_exact(cuda_lib):
             assert float((big.cpu()[:, (T + 5) * F:] - 7.0).abs().max()) == 0.0      # beyond the row: untouched
         print("device collate ok")
     """)
+
+
+def test_unverified_fused_adam_matches_reference_golden(cuda_lib):
+    """s2t_grad_norm + s2t_fused_adam (FusedAdamB200) against three updates of the reference's own Adam + clip_grad_norm_
+    (tests/golden/fused_adam.npz): gradient norm rel 1e-5, fp32 master weights rel 1e-5, moments rel 1e-5, bf16 parameters
+    = bf16(master); with clipping, weight decay and the gradient multiplier."""
+    run_isolated("""
+        import numpy as np, torch
+        from s2t_b200.optim import FusedAdamB200
+        fx = np.load("tests/golden/fused_adam.npz")
+        for name in ("recipe", "clipped_wd", "no_clip"):
+            lr, b1, b2, eps, wd, mult, max_norm = (float(v) for v in fx[f"{name}::hyper"])
+            p = torch.from_numpy(fx[f"{name}::p0"]).to(torch.bfloat16).cuda()
+            g = torch.zeros_like(p)
+            opt = FusedAdamB200(p, g, lr=lr, betas=(b1, b2), eps=eps, weight_decay=wd)
+            for step in (1, 2, 3):
+                g.copy_(torch.from_numpy(fx[f"{name}::grads"][step - 1]).to(torch.bfloat16))
+                tn = opt.step(grad_mult=mult, max_norm=max_norm)
+                torch.cuda.synchronize()
+                want = fx[f"{name}::norms"][step - 1]
+                assert abs(float(tn.item()) - want) <= 1e-5 * want, (name, step, float(tn.item()), want)
+                ref = torch.from_numpy(fx[f"{name}::master{step}"])
+                err = float((opt.master.cpu() - ref).abs().max() / ref.abs().max())
+                assert err <= 1e-5, (name, step, err)
+                assert torch.equal(p.cpu(), opt.master.cpu().to(torch.bfloat16))
+            assert np.allclose(opt.exp_avg.cpu().numpy(), fx[f"{name}::exp_avg"], rtol=1e-5, atol=1e-10)
+            assert np.allclose(opt.exp_avg_sq.cpu().numpy(), fx[f"{name}::exp_avg_sq"], rtol=1e-5, atol=1e-12)
+        # device-side lr / step scalars give the same update as host scalars
+        p1 = torch.from_numpy(fx["no_clip::p0"]).to(torch.bfloat16).cuda(); p2 = p1.clone()
+        g = torch.from_numpy(fx["no_clip::grads"][0]).to(torch.bfloat16).cuda()
+        o1, o2 = FusedAdamB200(p1, g, lr=5e-4), FusedAdamB200(p2, g, lr=123.0)
+        o1.step()
+        o2.step(lr_dev=torch.tensor([5e-4], device="cuda"), step_dev=torch.tensor([1], device="cuda", dtype=torch.int64))
+        torch.cuda.synchronize()
+        assert float((o1.master - o2.master).abs().max()) <= 1e-7
+        print("fused adam ok")
+    """)
