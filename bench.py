@@ -30,7 +30,7 @@ UNIT = "audio-s/s"
 SAMPLE_RATE = 16000
 VOCAB = 10000
 TARGET_LEN = 60           # ~6 tokens / s
-MICRO_DEFAULT = 1          # utterance groups run side by side (s2t_b200/microbatch.py)
+MICRO_DEFAULT = 1          # utterance groups run side by side (s2t_b200/experimental/microbatch.py)
 
 
 def parse():
@@ -348,7 +348,7 @@ def run_b200(a):
     if a.bucketed:
         return run_bucketed(a, torch, dist, cfg, world, rank, local, peaks)
     if a.micro > 1:
-        from s2t_b200.microbatch import MicroBatchEngine
+        from s2t_b200.experimental.microbatch import MicroBatchEngine
         eng = MicroBatchEngine(cfg, n_micro=a.micro)
     else:
         eng = S2TEncoderEngine(cfg)

@@ -21,8 +21,8 @@ from typing import Dict, List, Optional
 
 import torch
 
-from . import ops
-from .engine import EncoderConfig, Plan, S2TEncoderEngine
+from .. import ops
+from ..engine import EncoderConfig, Plan, S2TEncoderEngine
 
 
 class MicroPlan:

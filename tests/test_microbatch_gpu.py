@@ -1,4 +1,4 @@
-"""Concurrent micro-batches (s2t_b200/microbatch.py) must give the loss and gradients of the one-batch engine:
+"""Concurrent micro-batches (s2t_b200/experimental/microbatch.py) must give the loss and gradients of the one-batch engine:
 gradient accumulation over utterance groups is exact up to bf16 summation order (trainer.py:716-734 semantics)."""
 import pytest
 import torch
@@ -15,7 +15,7 @@ def rel_l2(a, b):
 @pytest.mark.parametrize("graph", [False, True])
 def test_microbatch_matches_single_batch(cuda_lib, n_micro, graph):
     from s2t_b200.engine import EncoderConfig, S2TEncoderEngine
-    from s2t_b200.microbatch import MicroBatchEngine
+    from s2t_b200.experimental.microbatch import MicroBatchEngine
     kw = dict(layers=3, ffn_dim=512, subsampling_filter=256, vocab=120, dropout=0.0)
     ref = S2TEncoderEngine(EncoderConfig(**kw))
     mb = MicroBatchEngine(EncoderConfig(**kw), n_micro=n_micro)
@@ -48,7 +48,7 @@ def test_microbatch_matches_single_batch(cuda_lib, n_micro, graph):
 
 def test_microbatch_rejects_batchnorm_models(cuda_lib):
     from s2t_b200.engine import EncoderConfig
-    from s2t_b200.microbatch import MicroBatchEngine
+    from s2t_b200.experimental.microbatch import MicroBatchEngine
     with pytest.raises(ValueError):
         MicroBatchEngine(EncoderConfig(layers=1, vocab=50, use_cnn_module=True, macaron_style=True, attn_type="rel_pos"),
                          n_micro=2)
