@@ -240,10 +240,16 @@ def test_unverified_criterion_curriculum_end_to_end(cuda_lib):
         eng, P = enc.engine, enc._last_plan
         assert np.isfinite(loss.item()) and torch.isfinite(enc.flat.grad.float()).all()
         assert set(P.gt) == {0, 1}
+        drawn = {k: tuple(t.view(P.B, P.T2).cpu().clone() for t in P.gt[k]) for k in (0, 1)}
+        # the alignment was taken on the FIRST pass (no mixing yet): reproduce that pass (dropout 0, batch statistics)
+        for k in (0, 1):
+            eng.set_ground_truth(P, k, None, None, None)
+        eng.forward(P)
+        torch.cuda.synchronize()
         for k, (tokens_key, h) in enumerate((("tokens", "ctc"), ("tgt_tokens", "xctc"))):
-            tok, msk, fe = (t.view(P.B, P.T2).cpu() for t in P.gt[k])
+            tok, msk, fe = drawn[k]
             assert int(msk.sum()) > 0 and bool(((fe >= 0) == (msk != 0)).all())
-            # the forced states lie on the best alignment of the first pass's top logits (dropout 0: same logits as now)
+            # the forced states lie on the best alignment of the first pass's top logits
             hs = eng.heads[k]
             lp = torch.log_softmax(P.heads[k].logits.float().view(P.B, P.T2, hs.ldv)[..., : hs.V], -1).cpu().numpy()
             tg, tl = eng.strip_targets(torch.from_numpy(fx[tokens_key]))
@@ -254,8 +260,6 @@ def test_unverified_criterion_curriculum_end_to_end(cuda_lib):
                 assert np.array_equal(fe[b, :n][forced].numpy(), np.asarray(paths[b])[forced.numpy()]), (h, b)
         # ratio 0: the plain criterion
         enc.pae_ground_truth_ratio = 0
-        for k in (0, 1):
-            eng.set_ground_truth(P, k, None, None, None)
         plain, _, _ = crit(model, sample)
         assert abs(plain.item() - float(np.load("tests/golden/enc_c5_small.npz")["loss"])) <= 1e-2 * abs(plain.item())
         print("criterion curriculum ok", loss.item(), plain.item())
