@@ -154,3 +154,29 @@ def test_bucketed_schedule_world2_gloo():
     n_frames = np.clip(rng.lognormal(np.log(550), 0.6, size=333), 50, 3000).astype(np.int64)
     assert f0 + f1 == float(n_frames.sum())
     assert abs(sum(s0) * 2 - float(n_frames.sum())) <= 1e-3 * float(n_frames.sum())
+
+
+def test_out_frames_matches_the_reference_length_arithmetic():
+    """engine.out_frames(T) — the number of output frames the REFERENCE returns for a batch padded to T frames (used to
+    slice the outputs of a larger frame-bucket plan) — against the oracle encoders (pinned to the reference) run on CPU
+    for the three stems: Conv1d x2, Conv2d x2 and the PDS stages with their padding quirk (A7)."""
+    from types import SimpleNamespace
+    import torch
+    from oracle import encoder as OE
+    from s2t_b200.engine import EncoderConfig, S2TEncoderEngine
+    cases = [
+        (dict(layers=1, ffn_dim=64, embed_dim=64, heads=1, subsampling_filter=64, vocab=0), False),
+        (dict(layers=1, ffn_dim=64, embed_dim=64, heads=1, subsampling_type="conv2d", subsampling_filter=16,
+              subsampling_kernel=3, subsampling_norm="batch2d", subsampling_activation="swish", vocab=0), False),
+        (dict(encoder_type="pds", pds_layers=(1, 1, 1, 1), pds_dims=(64, 64, 64, 64), pds_heads=(1, 1, 1, 1),
+              pds_ffn_ratios=(1, 1, 1, 1), vocab=0), True),
+    ]
+    from dataclasses import fields
+    for kw, pds in cases:
+        okw = {k: v for k, v in kw.items() if k in {f.name for f in fields(OE.OracleConfig)}}
+        orc = (OE.PDSS2TTransformerEncoder if pds else OE.S2TTransformerEncoder)(OE.OracleConfig(dropout=0.0, **okw)).eval()
+        fake = SimpleNamespace(cfg=EncoderConfig(dropout=0.0, **kw))
+        for T in (9, 16, 63, 64, 83, 128, 250, 998):
+            with torch.no_grad():
+                out = orc(torch.randn(2, T, 80), torch.tensor([T, max(T - 3, 8)]))
+            assert S2TEncoderEngine.out_frames(fake, T) == out["encoder_out"][0].shape[0], (kw.get("encoder_type", kw.get("subsampling_type", "conv1d")), T)
