@@ -330,13 +330,16 @@ def run_b200(a):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     import faulthandler
     # a wedged collective must not hang the box: dump every thread's stack and exit instead
-    faulthandler.dump_traceback_later(float(os.environ.get("S2T_BENCH_WATCHDOG_S", "900")), exit=True)
+    faulthandler.dump_traceback_later(float(os.environ.get("S2T_BENCH_WATCHDOG_S", "600")), exit=True)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py (impl b200) needs a CUDA device: s2t_b200 has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        # a mismatched collective must fail within minutes, not hold an 8-GPU box for the default 10-minute NCCL timeout
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local),
+                                timeout=datetime.timedelta(seconds=int(os.environ.get("S2T_NCCL_TIMEOUT_S", "180"))))
     peaks = {}
     pk = ROOT / "MEASURED_PEAKS.json"
     if pk.exists():
