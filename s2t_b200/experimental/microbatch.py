@@ -148,7 +148,7 @@ class MicroBatchEngine:
     def enable_data_parallel(self, n_buckets: int = 4, group=None) -> None:
         """Gradient all-reduce after the groups' gradients have been summed (bucketed so that NCCL pipelines the
         buckets; there is no backward left to overlap with once the sum exists)."""
-        from .dp import BucketedAllReduce
+        from ..dp import BucketedAllReduce
         S = self.store
         total = S.grad.numel()
         cuts = [total * k // n_buckets // 64 * 64 for k in range(1, n_buckets)]

@@ -194,3 +194,17 @@ def test_plugin_host_logic_and_registration(monkeypatch):
     assert sorted(done["models"]) == ["pdss2t_transformer_s_8", "s2t_ctc", "s2t_transformer_s"] and done["criterions"] == ["ctc"]
     assert crits.CRITERION_REGISTRY["ctc"] is plugin.CtcCriterionB200 and crits.CRITERION_REGISTRY["cross_entropy"] is object
     assert models.ARCH_MODEL_REGISTRY["transformer"].build_encoder(None) == "reference encoder"   # untouched
+
+
+def test_experimental_microbatch_enable_data_parallel_resolves_dp_module():
+    """MicroBatchEngine.enable_data_parallel imports BucketedAllReduce lazily; after the move to s2t_b200/experimental/
+    the relative import pointed at a module that does not exist.  Driven here with a stand-in engine (a flat CPU gradient
+    buffer, world size 1) so the import and the bucket planning run without a GPU."""
+    from types import SimpleNamespace
+
+    from s2t_b200.dp import BucketedAllReduce
+    from s2t_b200.experimental.microbatch import MicroBatchEngine
+    stub = SimpleNamespace(store=SimpleNamespace(grad=torch.zeros(64 * 40, dtype=torch.bfloat16)), dp=None)
+    MicroBatchEngine.enable_data_parallel(stub, n_buckets=4)
+    assert isinstance(stub.dp, BucketedAllReduce)
+    assert [hi - lo for lo, hi in stub.dp.buckets] == [640] * 4 and stub.dp.buckets[0][1] == 64 * 40
