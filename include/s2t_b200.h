@@ -286,6 +286,23 @@ int s2t_ctc_viterbi(const float* log_probs, long long lp_t_stride, long long lp_
 int s2t_specaugment(void* feats, int is_bf16, long long ld, long long bs, const int* num_frames, int batch,
                     int max_frames, int n_freqs, const int* freq_masks, int n_freq_masks, const int* time_masks,
                     int n_time_masks, float mask_value, int use_mean, float* means, void* stream);
+/* s2t_specaugment for callers that cannot allocate device memory.  No counterpart in the reference: it exists for hosts *
+ * of this library that are given the feature batch but may not call cudaMalloc (or torch's allocator) themselves — a   *
+ * data-loader worker or plugin running inside another component's memory pool or capture region, or under a            *
+ * "nothing is allocated after start-up" rule — and so have nowhere to put the `means` scratch of the mean fill.         *
+ * Same arguments and results as s2t_specaugment without `means`: the partial sums go to a fixed 128 KiB array that is   *
+ * part of the library image (each GPU that loads the library holds it until the process exits).                         *
+ *   - batch <= S2T_SPECAUGMENT_STATIC_MAX_BATCH, otherwise -1 and a message (split the batch, or use s2t_specaugment); *
+ *   - the first call on each device looks up the array's device address (one cudaGetSymbolAddress, with that device     *
+ *     current) and caches it: make that first call outside any stream capture;                                          *
+ *   - the call itself never calls cudaMalloc / cudaFree or any allocating routine;                                      *
+ *   - all calls on a device share the one array.  Each call overwrites the part it reads before reading it, so stale    *
+ *     contents are harmless and nothing needs clearing — but two calls whose kernels can run at the same time on the    *
+ *     same GPU (different streams, different host threads) race on it: keep them ordered on one stream or by events.     */
+#define S2T_SPECAUGMENT_STATIC_MAX_BATCH 1024
+int s2t_specaugment_static(void* feats, int is_bf16, long long ld, long long bs, const int* num_frames, int batch,
+                           int max_frames, int n_freqs, const int* freq_masks, int n_freq_masks, const int* time_masks,
+                           int n_time_masks, float mask_value, int use_mean, void* stream);
 /* *counter += inc on the device (dropout seed counter of a captured step)                         */
 int s2t_counter_add(unsigned long long* counter, unsigned long long inc, void* stream);
 /* y += x, bf16 [n], n % 8 == 0                                                                    */

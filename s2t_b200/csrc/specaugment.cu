@@ -8,6 +8,8 @@
 // utterance, fp32, fixed reduction order), then 8 CTAs per mask rectangle.
 #include "common.cuh"
 
+#include <mutex>
+
 #include "../../include/s2t_b200.h"
 
 namespace s2t {
@@ -114,6 +116,75 @@ extern "C" int s2t_specaugment(void* feats, int is_bf16, long long ld, long long
   S2T_LAUNCH(specaug_apply_kernel, dim3(n_freq_masks + n_time_masks, batch, kRowSlices), 256, 0, st, feats, is_bf16, ld, bs,
              num_frames, max_frames, n_freqs, freq_masks, n_freq_masks, time_masks, n_time_masks, mask_value,
              static_cast<const float*>(use_mean ? means : nullptr));
+  S2T_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// s2t_specaugment_static: the same two kernels for callers that have no way to obtain device memory for the partial
+// sums of the mean fill — a data-loader worker or a plugin that is handed the feature batch but runs where cudaMalloc is
+// off limits (inside someone else's memory pool or capture region, in a process whose allocator it does not own, under a
+// "no allocation after start-up" policy).  The partial sums live in a fixed array inside the library image instead.
+//
+// The array below is device memory that every GPU loading this library keeps until the process exits (128 KiB each).
+// On the host its NAME is only a handle for the runtime: passing `g_specaug_static_partials` itself to a kernel would
+// hand the kernel a host address.  The device address has to be asked for, per device, with cudaGetSymbolAddress —
+// static_partials_ptr() does that the first time each device is used and remembers the answer.
+// ---------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_specaug_static_partials[S2T_SPECAUGMENT_STATIC_MAX_BATCH * s2t::kMeanChunks];
+
+namespace {
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+float* g_static_ptr[kStaticMaxDevices] = {};   // device address of the array on each device, nullptr = not asked yet
+
+// Device address of the scratch array on the CURRENT device (looked up once per device, then cached).
+int static_partials_ptr(float** out) {
+  int dev = -1;
+  S2T_CHECK_CUDA(cudaGetDevice(&dev));
+  S2T_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "s2t_specaugment_static: device ordinal %d not supported (max %d)", dev,
+              kStaticMaxDevices - 1);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (g_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    S2T_CHECK_CUDA(cudaGetSymbolAddress(&p, g_specaug_static_partials));
+    S2T_REQUIRE(p != nullptr, "s2t_specaugment_static: cudaGetSymbolAddress returned a null address");
+    g_static_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_static_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int s2t_specaugment_static(void* feats, int is_bf16, long long ld, long long bs, const int* num_frames,
+                                      int batch, int max_frames, int n_freqs, const int* freq_masks, int n_freq_masks,
+                                      const int* time_masks, int n_time_masks, float mask_value, int use_mean,
+                                      void* stream) {
+  S2T_REQUIRE(feats && num_frames, "s2t_specaugment_static: null pointer");
+  S2T_REQUIRE(n_freq_masks >= 0 && n_time_masks >= 0, "s2t_specaugment_static: negative mask count");
+  S2T_REQUIRE(n_freq_masks == 0 || freq_masks != nullptr, "s2t_specaugment_static: freq_masks missing");
+  S2T_REQUIRE(n_time_masks == 0 || time_masks != nullptr, "s2t_specaugment_static: time_masks missing");
+  S2T_REQUIRE(ld >= n_freqs && n_freqs > 0, "s2t_specaugment_static: ld must be >= n_freqs");
+  S2T_REQUIRE(batch <= S2T_SPECAUGMENT_STATIC_MAX_BATCH,
+              "s2t_specaugment_static: batch %d exceeds the built-in scratch (at most %d utterances per call); split the "
+              "batch or use s2t_specaugment with your own buffer", batch, S2T_SPECAUGMENT_STATIC_MAX_BATCH);
+  if (batch <= 0 || max_frames <= 0 || n_freq_masks + n_time_masks == 0) return 0;
+  // Looked up even when use_mean == 0, so that ANY first call on a device completes the one-time set-up.
+  float* partials = nullptr;
+  if (int rc = static_partials_ptr(&partials)) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (use_mean) {
+    // Every partial the apply kernel reads (batch * kMeanChunks of them) is written by this launch first, so nothing
+    // left over from an earlier call is ever read and nothing has to be zeroed.
+    S2T_LAUNCH(specaug_mean_kernel, dim3(kMeanChunks, batch), 256, 0, st, static_cast<const void*>(feats), is_bf16, ld, bs,
+               num_frames, max_frames, n_freqs, partials);
+    S2T_LAUNCH_CHECK();
+  }
+  S2T_LAUNCH(specaug_apply_kernel, dim3(n_freq_masks + n_time_masks, batch, kRowSlices), 256, 0, st, feats, is_bf16, ld, bs,
+             num_frames, max_frames, n_freqs, freq_masks, n_freq_masks, time_masks, n_time_masks, mask_value,
+             static_cast<const float*>(use_mean ? partials : nullptr));
   S2T_LAUNCH_CHECK();
   return 0;
 }

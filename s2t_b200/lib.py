@@ -80,6 +80,7 @@ SIGNATURES = {
     "s2t_ctc_viterbi_workspace_bytes": (_ll, [_i, _i, _i]),
     "s2t_ctc_viterbi": (_i, [_vp, _ll, _ll, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _ll, _vp]),
     "s2t_specaugment": (_i, [_vp, _i, _ll, _ll, _vp, _i, _i, _i, _vp, _i, _vp, _i, _f, _i, _vp, _vp]),
+    "s2t_specaugment_static": (_i, [_vp, _i, _ll, _ll, _vp, _i, _i, _i, _vp, _i, _vp, _i, _f, _i, _vp]),
     "s2t_counter_add": (_i, [_vp, _ull, _vp]),
     "s2t_add_bf16": (_i, [_vp, _vp, _ll, _vp]),
     "s2t_f32_sum": (_i, [_vp, _i, _f, _vp, _vp]),
