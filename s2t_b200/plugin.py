@@ -32,6 +32,7 @@ from typing import Dict, List, Optional
 
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from . import ops
 from .batching import BucketSet
@@ -337,20 +338,25 @@ class CtcCriterionB200(nn.Module):
     def get_targets_for_ctc_loss(self, tokens: torch.Tensor):
         return S2TEncoderEngine.strip_targets(tokens, self.pad_idx, self.eos_idx)
 
-    def _curriculum(self, enc, eng, P) -> None:
+    def _curriculum(self, enc, eng, P, Tv: Optional[int] = None) -> None:
         """``get_ground_truth_alignment`` (criterions/ctc.py:262-265, 283-433) and the mask draw of the encoder
         (s2t_transformer.py:1904-1936, 2061-2092), all on the device: a first forward pass without gradient, the best CTC
         alignment of its TOP logits against the targets (``s2t_ctc_viterbi`` = torch_imputer.best_alignment + backtrack),
         per frame the aligned ground-truth token, the mistake flags (argmax != aligned token) and the random mixing
-        mask; the forced states are the alignment where the mask is set, -1 elsewhere."""
+        mask; the forced states are the alignment where the mask is set, -1 elsewhere.
+
+        ``Tv``: output frames of THIS batch (``eng.out_frames(batch frames)``).  A plan of a larger frame bucket has more
+        (masked) rows; they are not part of the reference's tensors, so mistake counts, the adaptive ratio and the shape
+        of the random draw are taken over the first Tv frames only and the rest is filled with token 0 / mask 0 / free."""
         eng.forward_train(P)
         B, T2 = P.B, P.T2
+        Tv = T2 if Tv is None else min(int(Tv), T2)
         for k, hs in enumerate(eng.heads):
             ratio = enc.gt_ratio.get(hs.name, 0.0)
             if ratio <= 0 or not hs.pae or not hs.inter_layers:
                 eng.set_ground_truth(P, k, None, None, None)
                 continue
-            lp = torch.log_softmax(P.heads[k].logits.view(B, T2, hs.ldv)[..., : hs.V], dim=-1, dtype=torch.float32)
+            lp = torch.log_softmax(P.heads[k].logits.view(B, T2, hs.ldv)[:, :Tv, : hs.V], dim=-1, dtype=torch.float32)
             states, _ = ops.ctc_viterbi(lp.contiguous(), P.tg[hs.tgt], P.out_len, P.tl[hs.tgt], self.blank_idx,
                                         with_nll=False)
             bap = states.clamp(min=0).long()                              # best_aligns_pad: 0 beyond the utterance
@@ -362,7 +368,11 @@ class CtcCriterionB200(nn.Module):
             mask = torch.rand(tok.shape, device=tok.device) < prob
             if enc.pae_gt_only_mistake:
                 mask = mask & mistake
-            eng.set_ground_truth(P, k, tok, mask, bap.masked_fill(~mask, -1))
+            fe = bap.masked_fill(~mask, -1)
+            if Tv < T2:
+                padc = (0, T2 - Tv)
+                tok, mask, fe = F.pad(tok, padc, value=0), F.pad(mask, padc, value=False), F.pad(fe, padc, value=-1)
+            eng.set_ground_truth(P, k, tok, mask, fe)
 
     def forward(self, model, sample, reduce=True):
         enc: S2TTransformerEncoderB200 = getattr(model, "encoder", model)
@@ -383,7 +393,7 @@ class CtcCriterionB200(nn.Module):
         if model.training and torch.is_grad_enabled():
             if getattr(enc, "pae_ground_truth_ratio", 0) != 0:
                 eng.ctc_masked_loss = self.ctc_masked_loss
-                self._curriculum(enc, eng, P)
+                self._curriculum(enc, eng, P, eng.out_frames(src_tokens.shape[1]))
             if enc.use_graph and P.graph is None:
                 eng.capture(P, "train")
             loss = _EngineStep.apply(enc.flat, enc, P)

@@ -57,3 +57,48 @@ def test_criterion_curriculum_host_arithmetic_matches_the_restatement(monkeypatc
     rec.clear()
     crit._curriculum(enc, eng, P)
     assert rec[0] == (None, None, None) and rec[1][0] is not None
+
+
+def test_criterion_curriculum_ignores_the_rows_of_a_larger_frame_bucket(monkeypatch):
+    """With frame buckets the plan holds more output rows than the batch has (their logits are the head's bias: argmax is
+    not blank).  The reference never sees those rows: mistake counts, the adaptive ratio
+    (--xctc-pae-ground-truth-ratio-adaptive, criterions/ctc.py:283-330) and the shape of the random draw must be those of
+    the batch's own T' frames.  Same seed, same logits: the padded plan gives the unpadded plan's tokens / masks / forced
+    states on the first T' columns and 0 / 0 / -1 beyond."""
+    from oracle import viterbi as OV
+    from s2t_b200 import plugin
+    B, Tv, extra, V, ldv = 3, 17, 6, 30, 32
+    g = torch.Generator().manual_seed(1)
+    lens = torch.tensor([17, 12, 9], dtype=torch.int32)
+    tg = torch.tensor([[5, 6, 6, 9], [7, 8, 0, 0], [4, 4, 4, 11]], dtype=torch.int32)
+    tl = torch.tensor([4, 2, 4], dtype=torch.int32)
+    small = torch.randn((B, Tv, ldv), generator=g) * 2
+    big = torch.zeros((B, Tv + extra, ldv))
+    big[:, :Tv] = small
+    big[:, Tv:, 7] = 9.0                                                   # padded rows: a confident non-blank argmax
+
+    def fake_viterbi(lp, targets, input_lengths, target_lengths, blank=0, batch_first=True, with_nll=True):
+        paths, _ = OV.best_alignment(lp.numpy(), targets.numpy().astype(np.int64), input_lengths.tolist(), target_lengths.tolist(), blank)
+        out = torch.full((lp.shape[0], lp.shape[1]), -1, dtype=torch.int32)
+        for b, p in enumerate(paths):
+            out[b, : len(p)] = torch.tensor(p, dtype=torch.int32)
+        return out, None
+
+    monkeypatch.setattr(plugin.ops, "ctc_viterbi", fake_viterbi)
+    heads = [SimpleNamespace(name="ctc", V=V, ldv=ldv, tgt=0, pae="pae", inter_layers=(2,))]
+    enc = SimpleNamespace(gt_ratio={"ctc": 0.9}, pae_adaptive_gt=True, pae_gt_only_mistake=False)
+    crit = plugin.CtcCriterionB200(None, None)
+    got = {}
+    for tag, logits, T2, tv in (("small", small, Tv, None), ("big", big, Tv + extra, Tv)):
+        rec = {}
+        eng = SimpleNamespace(heads=heads, forward_train=lambda P: None,
+                              set_ground_truth=lambda P, k, tok, msk, fe: rec.__setitem__(k, (tok, msk, fe)))
+        P = SimpleNamespace(B=B, T2=T2, out_len=lens, tg=[tg], tl=[tl], heads=[SimpleNamespace(logits=logits.reshape(B * T2, ldv))])
+        torch.manual_seed(5)
+        crit._curriculum(enc, eng, P, tv)
+        got[tag] = rec[0]
+    for a, b, fill in zip(got["small"], got["big"], (0, False, -1)):
+        assert b.shape == (B, Tv + extra)
+        assert torch.equal(b[:, :Tv], a)
+        assert bool((b[:, Tv:] == fill).all())
+    assert bool(got["small"][1].any())
