@@ -64,6 +64,19 @@ def workload_name(a) -> str:
             f"fbank+CMVN on device, dropout {CONFIGS[a.config]['dropout']:g}, fwd+bwd")
 
 
+def workload_config(a, world: int) -> dict:
+    """The ``config`` object of the fixed-shape bench line.  Built from the command line alone so that the reference arm
+    prints the SAME object for the same flags (the driver compares the two arms' configs); figures that need the engine
+    (parameter count, activation footprint) are top-level keys of our line instead."""
+    from s2t_b200 import frontend
+    n_samp = int(a.seconds * SAMPLE_RATE)
+    return {"workload": workload_name(a), "global_batch_utts": world * a.batch,
+            "audio_s_per_step": world * a.batch * n_samp / SAMPLE_RATE, "name": a.config,
+            "frames": frontend.num_frames(n_samp), "vocab": VOCAB, "parallelism": f"dp{world}",
+            "cuda_graph": not a.no_graph, "micro_batches": a.micro,
+            "l2": "no flush: per-step working set (activations+logits+grads, > 400 MB) exceeds the 126 MB L2"}
+
+
 def synth_batch(batch: int, seconds: float, seed: int):
     """Synthetic int16-scale waveform: randn * 3000 + a 440 Hz tone; random targets."""
     import torch
@@ -209,7 +222,8 @@ def run_reference(a):
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": r["steps_done"],
         "steps_requested": a.steps, "warmup": max(1, a.warmup), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a)},
+        "config": ({"workload": workload_name(a)} if getattr(a, "bucketed", False) else workload_config(a, max(1, a.gpus))),
+        "config_note": "the config of the arm this line is compared with; the reference itself ran on rank 0's host cores",
         "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
                          "value_1thread": r1["value"], "wall_clock_cap_s": budget, "capped": r["capped"]},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -491,10 +505,7 @@ def run_b200(a):
             "metric": METRIC, "value": world * audio_s_step * a.steps / (ms_total * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_total / a.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": workload_name(a), "global_batch_utts": world * a.batch, "audio_s_per_step": world * audio_s_step,
-                       "name": a.config, "frames": T, "vocab": VOCAB, "params": eng.num_params(), "parallelism": f"dp{world}",
-                       "cuda_graph": not a.no_graph, "micro_batches": a.micro,
-                       "l2": "no flush: per-step working set (activations+logits+grads, > 400 MB) exceeds the 126 MB L2"},
+            "config": workload_config(a, world), "params": eng.num_params(),
             "e2e": {"value": world * audio_s_step * a.steps / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / a.steps,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "how": "pinned host batch -> InputFeeder (H2D of batch i+1 overlaps step i) -> CUDA-graph step -> loss "
