@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define S2T_ABI_VERSION 4
+#define S2T_ABI_VERSION 5
 
 /* status / introspection ---------------------------------------------------------------------- */
 const char* s2t_last_error(void);
@@ -463,12 +463,16 @@ int s2t_ctc_greedy(const void* logits, int is_bf16, long long ldv, const int* in
 /* s2t_fused_adam: g = grad * grad_mult * clip_coef, clip_coef = min(1, max_norm / (total_norm[0] +   */
 /* 1e-6)) when total_norm != NULL and max_norm > 0; m, v, master fp32 [n]; param = bf16(master);      */
 /* step counts from 1; lr_dev / step_dev: optional device scalars that override lr / step (a captured */
-/* graph replays with fresh values).                                                                  */
+/* graph replays with fresh values).  beta1 / beta2 are doubles (ABI 5): the reference forms 1 - beta in  */
+/* double before rounding to fp32, and 1.f - 0.999f is 1.3e-5 away from that.  The update is skipped on the device (nothing is written) when   */
+/* total_norm is given and total_norm[0] is NaN or Inf (overflowed gradients: the reference trainer   */
+/* raises FloatingPointError before optimizer.step, fairseq/trainer.py:751-753; the host can read the */
+/* same scalar), and when step_dev[0] < 1.  Without total_norm there is no overflow guard.            */
 /* --------------------------------------------------------------------------------------------- */
 int s2t_grad_norm_partials(long long n);
 int s2t_grad_norm(const void* grad, long long n, float mult, float* partials, float* total_norm, void* stream);
 int s2t_fused_adam(void* param, float* master, const void* grad, float* exp_avg, float* exp_avg_sq, long long n,
-                   float lr, float beta1, float beta2, float eps, float weight_decay, long long step,
+                   float lr, double beta1, double beta2, float eps, float weight_decay, long long step,
                    float grad_mult, const float* total_norm, float max_norm, const float* lr_dev,
                    const long long* step_dev, void* stream);
 

@@ -61,6 +61,9 @@ __global__ void grad_norm_finish_kernel(const float* __restrict__ partials, int 
 
 struct AdamParams {
   float lr, beta1, beta2, eps, weight_decay, grad_mult, max_norm;
+  float one_minus_beta1, one_minus_beta2;     // float(1 - beta) with the subtraction in DOUBLE, as the reference's
+                                              // Python scalars `1 - beta1`, `1 - beta2` (adam.py:207-208): 1.f - 0.999f is
+                                              // 1.3e-5 away from 0.001f, which showed up in exp_avg_sq on hardware
   float bias_correction1, bias_correction2;   // used when step_dev == nullptr
   const float* lr_dev;                         // optional device scalars (a captured graph replays with fresh values)
   const long long* step_dev;
@@ -74,19 +77,28 @@ fused_adam_kernel(__nv_bfloat16* __restrict__ param, float* __restrict__ master,
   float lr = a.lr_dev != nullptr ? *a.lr_dev : a.lr;
   float bc1 = a.bias_correction1, bc2 = a.bias_correction2;
   if (a.step_dev != nullptr) {
-    const float t = static_cast<float>(*a.step_dev);
+    const long long step = *a.step_dev;
+    if (step < 1) return;          // steps count from 1: step 0 would make the bias correction 0 and the step size infinite
+    const float t = static_cast<float>(step);
     bc1 = 1.f - powf(a.beta1, t);
     bc2 = 1.f - powf(a.beta2, t);
   }
   float coef = a.grad_mult;
-  if (a.total_norm != nullptr && a.max_norm > 0.f) coef *= fminf(1.f, a.max_norm / (*a.total_norm + 1e-6f));
+  if (a.total_norm != nullptr) {
+    // Overflowed gradients (NaN / Inf norm): the whole update is skipped — master weights, moments and bf16 parameters
+    // stay as they were — as the reference trainer skips it by raising FloatingPointError before optimizer.step
+    // (fairseq/trainer.py:751-753).  The host sees the same condition in total_norm[0].
+    const float tn = *a.total_norm;
+    if (!isfinite(tn)) return;
+    if (a.max_norm > 0.f) coef *= fminf(1.f, a.max_norm / (tn + 1e-6f));
+  }
   const float step_size = lr * sqrtf(bc2) / bc1;
   const float decay = a.weight_decay * lr;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
     const float g = __bfloat162float(grad[i]) * coef;
-    const float m = a.beta1 * exp_avg[i] + (1.f - a.beta1) * g;
-    const float v = a.beta2 * exp_avg_sq[i] + (1.f - a.beta2) * g * g;
+    const float m = a.beta1 * exp_avg[i] + a.one_minus_beta1 * g;
+    const float v = a.beta2 * exp_avg_sq[i] + a.one_minus_beta2 * g * g;
     float p = master[i];
     if (a.weight_decay != 0.f) p -= decay * p;
     p -= step_size * (m / (sqrtf(v) + a.eps));
@@ -121,18 +133,19 @@ extern "C" int s2t_grad_norm(const void* grad, long long n, float mult, float* p
 }
 
 extern "C" int s2t_fused_adam(void* param, float* master, const void* grad, float* exp_avg, float* exp_avg_sq,
-                              long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
+                              long long n, float lr, double beta1, double beta2, float eps, float weight_decay,
                               long long step, float grad_mult, const float* total_norm, float max_norm,
                               const float* lr_dev, const long long* step_dev, void* stream) {
   S2T_REQUIRE(param && master && grad && exp_avg && exp_avg_sq, "s2t_fused_adam: null pointer");
   S2T_REQUIRE(step >= 1 || step_dev != nullptr, "s2t_fused_adam: step counts from 1");
-  S2T_REQUIRE(beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f, "s2t_fused_adam: betas must be in [0, 1)");
+  S2T_REQUIRE(beta1 >= 0.0 && beta1 < 1.0 && beta2 >= 0.0 && beta2 < 1.0, "s2t_fused_adam: betas must be in [0, 1)");
   if (n <= 0) return 0;
   AdamParams a;
-  a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
+  a.lr = lr; a.beta1 = static_cast<float>(beta1); a.beta2 = static_cast<float>(beta2); a.eps = eps;
+  a.one_minus_beta1 = static_cast<float>(1.0 - beta1); a.one_minus_beta2 = static_cast<float>(1.0 - beta2); a.weight_decay = weight_decay;
   a.grad_mult = grad_mult; a.max_norm = max_norm;
-  a.bias_correction1 = static_cast<float>(1.0 - pow(static_cast<double>(beta1), static_cast<double>(step)));
-  a.bias_correction2 = static_cast<float>(1.0 - pow(static_cast<double>(beta2), static_cast<double>(step)));
+  a.bias_correction1 = static_cast<float>(1.0 - pow(beta1, static_cast<double>(step)));
+  a.bias_correction2 = static_cast<float>(1.0 - pow(beta2, static_cast<double>(step)));
   a.lr_dev = lr_dev; a.step_dev = step_dev; a.total_norm = total_norm;
   long long g = (n + 255) / 256;
   if (g > 148 * 8) g = 148 * 8;

@@ -282,6 +282,7 @@ class Plan:
         # weight of this batch in the gradient (1 = real batch, 0 = the zero-weight dummy batch a data-parallel rank
         # runs when it has no batch left, trainer.py:1045-1058,687-691); a device scalar so that one captured graph serves both
         self.batch_weight = torch.ones(1, device=dev, dtype=F32)
+        self.batch_w_host = 1.0                 # host copy of batch_weight: set_inputs refills the device scalar only on change
         self.targets = z(B, max(smax, 1), dt=torch.int32)
         self.tgt_len = z(B, dt=torch.int32)
         drop = c.dropout > 0
@@ -445,6 +446,7 @@ class Plan:
         if eng.heads:
             self.nll_all = z(len(weights), B, dt=F32)
             self.loss_w = torch.tensor(weights, dtype=F32, device=dev)
+            self.loss_w0 = self.loss_w.clone()       # loss_w = loss_w0 * batch weight (a dummy batch logs loss 0, trainer.py:687-691)
             self.loss_weights = weights
             self.loss = z(1, dt=F32)
             self.ctc_ws = e((ops.ctc_workspace_bytes(B, T2, max(smax, 1)) + 3) // 4, dt=F32)
@@ -786,35 +788,45 @@ class S2TEncoderEngine:
                 t = (torch.rand(shape, generator=g) * 2 - 1) * bound
             S.p(name).copy_(t.to(BF16))
 
+    def _ref_to_store(self, name: str, t: torch.Tensor) -> torch.Tensor:
+        """One reference-layout tensor (fp32, CPU) in the layout and shape of its slot in the flat buffers."""
+        S = self.store
+        t = self._to_internal(name, t)
+        if name in self.conv_names:
+            t = t.permute(0, 2, 1).contiguous()               # [Cout][Cin][k] -> [Cout][k][Cin]
+        if name in self.ref_shapes:
+            if tuple(t.shape) != self.ref_shapes[name]:
+                raise ValueError(f"{name}: shape {tuple(t.shape)} != {self.ref_shapes[name]}")
+            t = t.reshape(S.shape(name))
+        if name in self.padded_bias:
+            full = torch.zeros(S.shape(name))
+            full[: t.numel()] = t
+            t = full
+        if tuple(t.shape) != S.shape(name):
+            raise ValueError(f"{name}: shape {tuple(t.shape)} != {S.shape(name)}")
+        return t
+
     def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
         """Load a reference-layout state_dict (names of SURVEY.md §8b)."""
         S = self.store
         for name in S.names():
             if name not in sd:
                 raise KeyError(f"state_dict is missing {name}")
-            t = self._to_internal(name, sd[name].detach().to(F32).cpu())
-            if name in self.conv_names:
-                t = t.permute(0, 2, 1).contiguous()               # [Cout][Cin][k] -> [Cout][k][Cin]
-            if name in self.ref_shapes:
-                if tuple(t.shape) != self.ref_shapes[name]:
-                    raise ValueError(f"{name}: shape {tuple(t.shape)} != {self.ref_shapes[name]}")
-                t = t.reshape(S.shape(name))
-            if name in self.padded_bias:
-                full = torch.zeros(S.shape(name))
-                full[: t.numel()] = t
-                t = full
-            if tuple(t.shape) != S.shape(name):
-                raise ValueError(f"{name}: shape {tuple(t.shape)} != {S.shape(name)}")
-            S.p(name).copy_(t.to(BF16))
+            S.p(name).copy_(self._ref_to_store(name, sd[name].detach().to(F32).cpu()).to(BF16))
         for name, buf in self.buffers.items():
             if name in sd:
                 buf.copy_(sd[name].to(buf.dtype))
 
-    def _export(self, grad: bool) -> Dict[str, torch.Tensor]:
+    def export_flat(self, flat: torch.Tensor) -> Dict[str, torch.Tensor]:
+        """Any buffer laid out like the flat parameter buffer (gradients, fp32 master weights, optimizer moments) cut into
+        the reference's named tensors, in the reference's shapes and layouts (fp32 copies)."""
         S = self.store
+        if flat.numel() != S.total:
+            raise ValueError(f"buffer of {flat.numel()} elements does not match the parameter layout ({S.total})")
         out = {}
         for name in S.names():
-            t = (S.g(name) if grad else S.p(name)).detach().float()
+            off = S.offset(name)
+            t = flat[off:off + S.numel(name)].view(S.shape(name)).detach().float()
             if name in self.conv_names:
                 t = t.permute(0, 2, 1).contiguous()
             if name in self.ref_shapes:
@@ -823,6 +835,22 @@ class S2TEncoderEngine:
                 t = t[: self.padded_bias[name]]
             out[name] = self._to_reference(name, t)
         return out
+
+    def import_flat(self, tensors: Dict[str, torch.Tensor], flat: torch.Tensor) -> None:
+        """Inverse of export_flat: reference-layout tensors written into their slots of ``flat`` (alignment gaps and
+        padding untouched)."""
+        S = self.store
+        if flat.numel() != S.total:
+            raise ValueError(f"buffer of {flat.numel()} elements does not match the parameter layout ({S.total})")
+        for name in S.names():
+            if name not in tensors:
+                raise KeyError(f"missing {name}")
+            off = S.offset(name)
+            t = self._ref_to_store(name, tensors[name].detach().to(F32).cpu())
+            flat[off:off + S.numel(name)].view(S.shape(name)).copy_(t.to(flat.dtype))
+
+    def _export(self, grad: bool) -> Dict[str, torch.Tensor]:
+        return self.export_flat(self.store.grad if grad else self.store.flat)
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
         sd = self._export(False)
@@ -1800,8 +1828,14 @@ class S2TEncoderEngine:
                 for v in P.batch_sub:
                     t = (t + 2 * P.pad - c.subsampling_kernel) // c.subsampling_stride + 1
                     v.fill_(t)
-        if weight is not None:          # 0.0 = dummy batch (gradient contribution exactly zero), 1.0 = real batch
-            P.batch_weight.fill_(float(weight))
+        # 0.0 = dummy batch (gradient contribution and logged loss exactly zero), 1.0 = real batch.  Set on EVERY call: a
+        # plan that ran a dummy batch and is reused by a caller that does not pass ``weight`` is a real batch again.
+        w = 1.0 if weight is None else float(weight)
+        if w != P.batch_w_host:
+            P.batch_weight.fill_(w)
+            if hasattr(P, "loss_w0"):
+                torch.mul(P.loss_w0, w, out=P.loss_w)
+            P.batch_w_host = w
         for name, m in (("sa_freq", sa_freq), ("sa_time", sa_time)):
             if m is not None and m.shape[1] > 0:
                 if getattr(P, name) is None:

@@ -12,7 +12,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libs2t_b200.so"
 
 _vp, _i, _ll, _f, _ull, _u = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong, C.c_uint
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 ACT_NONE, ACT_RELU, ACT_SWISH = 0, 1, 2
 GATE_NONE, GATE_POSITIVE, GATE_SWISH_GRAD, GATE_MUL = 0, 1, 2, 3
 
@@ -110,7 +110,7 @@ SIGNATURES = {
     "s2t_ctc_loss_masked": (_i, [_vp, _i, _ll, _vp, _vp, _ll, _vp, _ll, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp, _ll, _vp]),
     "s2t_grad_norm_partials": (_i, [_ll]),
     "s2t_grad_norm": (_i, [_vp, _ll, _f, _vp, _vp, _vp]),
-    "s2t_fused_adam": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _f, _ll, _f, _vp, _f, _vp, _vp, _vp]),
+    "s2t_fused_adam": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _f, C.c_double, C.c_double, _f, _f, _ll, _f, _vp, _f, _vp, _vp, _vp]),
     "s2t_collate_frames": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _ll, _vp, _vp]),
     "s2t_batch_by_size": (_ll, [_vp, _ll, _ll, _ll, _i, _vp]),
     "s2t_ctc_greedy": (_i, [_vp, _i, _ll, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

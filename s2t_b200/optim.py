@@ -55,7 +55,20 @@ class FusedAdamB200:
                   float(max_norm), ops._p(lr_dev), ops._p(step_dev), ops._stream())
         return self.total_norm
 
+    def check_finite(self) -> float:
+        """Host-side half of the overflow guard (one device->host read of the norm): the kernel has already skipped the
+        update if the gradient norm was NaN / Inf; this undoes the host step count and raises FloatingPointError like
+        the reference trainer (fairseq/trainer.py:751-753).  Returns the norm otherwise."""
+        tn = float(self.total_norm.item())
+        if not (tn == tn and abs(tn) != float("inf")):
+            self.step_count -= 1
+            raise FloatingPointError("gradients are Nan/Inf")
+        return tn
+
+    # ---- state --------------------------------------------------------------------------------------------------------
     def state_dict(self):
+        """Flat state (the layout of the engine's parameter buffer): the cheapest form to save and restore between runs of
+        THIS library.  ``reference_state_dict`` gives the reference's optimizer format instead."""
         return {"step": self.step_count, "master": self.master, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq}
 
     def load_state_dict(self, sd) -> None:
@@ -63,3 +76,54 @@ class FusedAdamB200:
         for k in ("master", "exp_avg", "exp_avg_sq"):
             getattr(self, k).copy_(sd[k])
         self.param.copy_(self.master.to(torch.bfloat16))
+
+    def reference_state_dict(self, engine, names=None):
+        """The optimizer state in the reference's checkpoint format: torch's ``Optimizer.state_dict()`` of its Adam
+        (fairseq/optim/adam.py:145-231: per parameter ``step`` / ``exp_avg`` / ``exp_avg_sq`` in fp32, the parameter's own
+        shape) as ``FairseqOptimizer.state_dict`` returns it (last_optimizer_state of a checkpoint saved WITHOUT --fp16
+        flattening, i.e. one state entry per parameter).  ``names``: the reference model's parameter order
+        (``[n for n, _ in model.named_parameters()]``); default = the engine's own order."""
+        return pack_reference_state(engine.export_flat(self.exp_avg), engine.export_flat(self.exp_avg_sq), self.step_count,
+                                    names or engine.store.names(), lr=self.lr, betas=self.betas, eps=self.eps,
+                                    weight_decay=self.weight_decay)
+
+    def load_reference_state_dict(self, engine, sd, names=None) -> None:
+        """Inverse of ``reference_state_dict``: moments and step count from a reference optimizer state; the fp32 master
+        weights restart from the engine's current bf16 parameters (the reference keeps no separate master copy in this
+        format; under --fp16 it rebuilds it from the model the same way, fp16_optimizer.py)."""
+        ea, es, step = unpack_reference_state(sd, names or engine.store.names())
+        engine.import_flat(ea, self.exp_avg)
+        engine.import_flat(es, self.exp_avg_sq)
+        self.step_count = step
+        self.master.copy_(self.param.float())
+
+
+def pack_reference_state(exp_avg, exp_avg_sq, step, names, *, lr, betas, eps, weight_decay):
+    """name -> tensor dicts of the two moments -> torch ``Optimizer.state_dict()`` layout (state keyed by the position of
+    the parameter in ``names``, one param group carrying the reference Adam's hyper-parameters)."""
+    names = list(names)
+    missing = [n for n in names if n not in exp_avg]
+    if missing:
+        raise KeyError(f"no optimizer state for {missing[:3]}")
+    state = {i: {"step": int(step), "exp_avg": exp_avg[n].float().cpu(), "exp_avg_sq": exp_avg_sq[n].float().cpu()}
+             for i, n in enumerate(names)}
+    group = {"lr": float(lr), "betas": (float(betas[0]), float(betas[1])), "eps": float(eps),
+             "weight_decay": float(weight_decay), "amsgrad": False, "params": list(range(len(names)))}
+    return {"state": state, "param_groups": [group]}
+
+
+def unpack_reference_state(sd, names):
+    """torch ``Optimizer.state_dict()`` layout -> (exp_avg by name, exp_avg_sq by name, step).  Every parameter must carry
+    the same step count (one flat update has one)."""
+    names = list(names)
+    order = [i for g in sd["param_groups"] for i in g["params"]]
+    if len(order) != len(names):
+        raise ValueError(f"optimizer state holds {len(order)} parameters, the model has {len(names)}")
+    ea, es, steps = {}, {}, set()
+    for n, i in zip(names, order):
+        st = sd["state"][i]
+        ea[n], es[n] = st["exp_avg"], st["exp_avg_sq"]
+        steps.add(int(st["step"]))
+    if len(steps) != 1:
+        raise ValueError(f"parameters disagree on the step count: {sorted(steps)}")
+    return ea, es, steps.pop()

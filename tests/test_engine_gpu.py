@@ -534,3 +534,96 @@ def test_empty_utterances_pad_a_batch_without_changing_it(cuda_lib, family):
     assert float(nll8[3:].abs().max()) == 0.0
     assert abs(l8 - l3) <= 1e-4 * abs(l3), (l3, l8)
     assert float((g8 - g3).norm() / g3.norm()) <= 2e-2
+
+
+def test_ground_truth_curriculum_matches_reference_fixture(cuda_lib):
+    """The ground-truth curriculum of the prediction-aware adapters (reproduction_bil_ctc_synchronous.yaml:62-65): with the
+    aligned tokens, masks and forced states the REFERENCE drew (tests/golden/enc_c5_curr_small.npz, oracle/make_golden.py
+    run_reference_curriculum: restatement == reference) given to the engine (set_ground_truth), loss and gradients must
+    match the reference's — plain CTC loss and, with ctc_masked_loss, the imputer loss on every term."""
+    from pathlib import Path
+    _GOLDEN = Path(__file__).resolve().parent / "golden"
+    from pathlib import Path
+    from oracle.make_golden import CURR_CASE, seeded_state_dict, state_checksum
+    from s2t_b200.engine import EncoderConfig, S2TEncoderEngine
+    fx = np.load(_GOLDEN / "enc_c5_curr_small.npz")
+    sp = CURR_CASE
+    csv = lambda k: tuple(int(v) for v in sp[k].split(","))
+    cfg = dict(layers=sp["encoder_layers"], embed_dim=sp["encoder_embed_dim"], ffn_dim=sp["encoder_ffn_embed_dim"],
+               heads=sp["encoder_attention_heads"], subsampling_filter=sp["subsampling_filter"], vocab=sp["vocab"],
+               tgt_vocab=sp["vocab"], dropout=0.0, macaron_style=True, use_cnn_module=True, cnn_module_kernel=15,
+               attn_type="rel_pos", encoder_activation_fn="swish", ctc_weight=sp["ctc_weight"], xctc_weight=sp["xctc_weight"],
+               inter_ctc_layers=csv("inter_ctc_layers"), inter_ctc_weight=sp["inter_ctc_weight"],
+               inter_xctc_layers=csv("inter_xctc_layers"), inter_xctc_weight=sp["inter_xctc_weight"],
+               ctc_pae=sp["ctc_pae"], xctc_pae=sp["xctc_pae"], pae_unnorm_input=sp["pae_unnorm_input"], pae_gt_smooth=True)
+    shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
+    sd = seeded_state_dict(shapes, int(fx["seed"]))
+    assert state_checksum(sd) == str(fx["weights_sha256"])
+    feats, lens = torch.from_numpy(fx["feats"]), torch.from_numpy(fx["lens"])
+    names = [str(n) for n in fx["grad_names"]]
+    for masked, lkey, tag in ((False, "loss", "grad"), (True, "loss_masked", "gradm")):
+        eng = S2TEncoderEngine(EncoderConfig(**cfg))
+        eng.load_state_dict(sd)
+        eng.ctc_masked_loss = masked
+        tg, tl = eng.strip_targets(torch.from_numpy(fx["tokens"]))
+        xt, xl = eng.strip_targets(torch.from_numpy(fx["tgt_tokens"]))
+        B, T, _ = feats.shape
+        P = eng.plan(B, T, max(tg.shape[1], xt.shape[1]))
+        eng.set_inputs(P, feats=feats, src_lengths=lens.to(torch.int32), targets=tg, target_lengths=tl, xtargets=xt,
+                       xtarget_lengths=xl)
+        for k, h in enumerate(("ctc", "xctc")):
+            eng.set_ground_truth(P, k, torch.from_numpy(fx[f"oracle_{h}"]).cuda(), torch.from_numpy(fx[f"mask_{h}"]).cuda(),
+                                 torch.from_numpy(fx[f"force_emit_{h}"]).cuda())
+        eng.train_step(P)
+        torch.cuda.synchronize()
+        ref_loss = float(fx[lkey])
+        assert abs(P.loss.item() - ref_loss) <= 1e-2 * abs(ref_loss), (masked, P.loss.item(), ref_loss)
+        valid = ~torch.from_numpy(fx["padding_mask"]).T
+        enc = P.enc_out.float().view(B, P.T2, -1).transpose(0, 1).cpu()
+        ref_enc = torch.from_numpy(fx["encoder_out"])
+        assert float((enc[valid] - ref_enc[valid]).norm() / ref_enc[valid].norm()) <= 3e-2
+        grads = eng.grads()
+        for key in fx.files:
+            if key.startswith(tag + "::"):
+                n = key.split("::", 1)[1]
+                ref = torch.from_numpy(fx[key])
+                rel = float((grads[n].cpu() - ref).norm() / (ref.norm() + 1e-12))
+                assert rel <= 0.15, (masked, n, rel)
+        norms = dict(zip(names, fx[tag + "_norms"]))
+        for n, gn in norms.items():
+            if n.endswith(("linear_k.bias", "k_proj.bias")) or gn < 1e-6:
+                continue
+            mine = float(grads[n].norm())
+            assert abs(mine - gn) <= 0.2 * gn + 1e-6, (masked, n, mine, gn)
+        # without the curriculum inputs the same engine gives a different loss (the mixing really happened)
+
+
+def test_dummy_batch_weight_is_per_call_and_zeroes_the_logged_loss(cuda_lib):
+    """The zero-weight dummy batch of a rank that ran out of data (fairseq/trainer.py:1045-1058: gradients multiplied by 0,
+    :687-691: its loss is not logged): on ONE captured plan, weight=0.0 gives a zero gradient and a zero loss, and the next
+    set_inputs WITHOUT a weight (what the plugin and the criterion call) is a real batch again — same loss and gradients
+    as before the dummy batch, bit for bit."""
+    from s2t_b200.engine import EncoderConfig, S2TEncoderEngine
+    eng = S2TEncoderEngine(EncoderConfig(layers=2, ffn_dim=512, subsampling_filter=256, vocab=120, dropout=0.0))
+    B, T, S = 3, 211, 7
+    g = torch.Generator().manual_seed(8)
+    feats = torch.randn((B, T, 80), generator=g)
+    lens = torch.tensor([211, 180, 64], dtype=torch.int32)
+    tg = torch.randint(4, 120, (B, S), generator=g).to(torch.int32)
+    tl = torch.tensor([7, 5, 2], dtype=torch.int32)
+    P = eng.plan(B, T, S)
+    kw = dict(feats=feats, src_lengths=lens, targets=tg, target_lengths=tl)
+    eng.set_inputs(P, **kw)
+    eng.capture(P)
+    eng.run(P)
+    torch.cuda.synchronize()
+    loss0, g0 = P.loss.clone(), eng.store.grad.clone()
+    assert float(loss0) > 0 and float(g0.float().abs().max()) > 0
+    eng.set_inputs(P, weight=0.0, **kw)
+    eng.run(P)
+    torch.cuda.synchronize()
+    assert float(P.loss) == 0.0 and float(eng.store.grad.float().abs().max()) == 0.0
+    eng.set_inputs(P, **kw)                 # no weight given: a real batch
+    eng.run(P)
+    torch.cuda.synchronize()
+    assert torch.equal(P.loss, loss0) and torch.equal(eng.store.grad, g0)

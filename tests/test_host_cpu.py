@@ -30,7 +30,7 @@ def test_library_exports_every_header_symbol():
         assert hasattr(handle, s), f"{s} declared in include/s2t_b200.h but not exported"
         assert s in lib.SIGNATURES, f"{s} has no ctypes signature in s2t_b200/lib.py"
     assert set(lib.SIGNATURES) == set(syms), set(lib.SIGNATURES) ^ set(syms)
-    assert handle.s2t_abi_version() == lib.ABI_VERSION == 4
+    assert handle.s2t_abi_version() == lib.ABI_VERSION == 5
     assert handle.s2t_fbank_num_frames(160000) == 998 and handle.s2t_fbank_num_frames(399) == 0
     assert handle.s2t_ctc_workspace_bytes(8, 250, 60) > 0            # pure host queries only: no compute without a GPU
 

@@ -245,3 +245,61 @@ def test_multichannel_waveform_is_merged_to_mono(cuda_lib):
     assert c.shape == (98, 80) and np.array_equal(c, frontend._get_torchaudio_fbank(stereo[0], 16000, 80))
     with pytest.raises(ValueError):
         frontend._get_torchaudio_fbank(np.zeros((2, 2, 100), dtype=np.float32), 16000, 80)
+
+
+def test_criterion_curriculum_end_to_end(cuda_lib):
+    """CtcCriterionB200 with the curriculum options of reproduction_bil_ctc_synchronous.yaml:62-65 switched on
+    (xctc/ctc-pae-ground-truth-ratio, only-mistake, oracle-smooth, ctc_masked_loss): the alignment the criterion computes
+    on the device equals the Viterbi restatement on the same logits, the drawn masks respect the mistake flags, the loss
+    and the flat gradient are finite, and with ratio 0 the criterion gives the curriculum-free loss."""
+    from pathlib import Path
+    _GOLDEN = Path(__file__).resolve().parent / "golden"
+    from argparse import Namespace
+    from oracle import viterbi as OV
+    from oracle.make_golden import CURR_CASE, reference_args, seeded_state_dict
+    from s2t_b200 import plugin
+    fx = np.load(_GOLDEN / "enc_c5_curr_small.npz")
+    args = reference_args(**dict(CURR_CASE))
+    for k, v in dict(encoder_embed_dim=256, encoder_ffn_embed_dim=2048, encoder_layers=12, encoder_attention_heads=4,
+                     subsampling_layers=2, subsampling_filter=1024, subsampling_kernel=5, subsampling_stride=2).items():
+        if not hasattr(args, k):
+            setattr(args, k, v)
+    args.b200_cuda_graph = False
+    model = plugin.S2TCTCModelB200.build_model(args, None)
+    shapes = {n: eval(s) for n, s in zip(fx["param_names"], fx["param_shapes"])}
+    model.encoder.load_state_dict(seeded_state_dict(shapes, int(fx["seed"])))
+    enc = model.encoder
+    assert enc.pae_ground_truth_ratio > 0 and enc.pae_gt_only_mistake
+    crit = plugin.CtcCriterionB200(Namespace(ctc_masked_loss=True), None)
+    sample = {"net_input": {"src_tokens": torch.from_numpy(fx["feats"]).cuda(), "src_lengths": torch.from_numpy(fx["lens"]).cuda(),
+                            "prev_output_tokens": None},
+              "transcript": {"tokens": torch.from_numpy(fx["tokens"])}, "target": torch.from_numpy(fx["tgt_tokens"])}
+    model.train()
+    torch.manual_seed(0)
+    loss, _, log = crit(model, sample)
+    loss.backward()
+    eng, P = enc.engine, enc._last_plan
+    assert np.isfinite(loss.item()) and torch.isfinite(enc.flat.grad.float()).all()
+    assert set(P.gt) == {0, 1}
+    drawn = {k: tuple(t.view(P.B, P.T2).cpu().clone() for t in P.gt[k]) for k in (0, 1)}
+    # the alignment was taken on the FIRST pass (no mixing yet): reproduce that pass (dropout 0, batch statistics)
+    for k in (0, 1):
+        eng.set_ground_truth(P, k, None, None, None)
+    eng.forward(P)
+    torch.cuda.synchronize()
+    for k, (tokens_key, h) in enumerate((("tokens", "ctc"), ("tgt_tokens", "xctc"))):
+        tok, msk, fe = drawn[k]
+        assert int(msk.sum()) > 0 and bool(((fe >= 0) == (msk != 0)).all())
+        # the forced states lie on the best alignment of the first pass's top logits
+        hs = eng.heads[k]
+        lp = torch.log_softmax(P.heads[k].logits.float().view(P.B, P.T2, hs.ldv)[..., : hs.V], -1).cpu().numpy()
+        tg, tl = eng.strip_targets(torch.from_numpy(fx[tokens_key]))
+        paths, _ = OV.best_alignment(lp, tg.numpy().astype(np.int64), P.out_len.cpu().tolist(), tl.tolist())
+        for b in range(P.B):
+            n = int(P.out_len[b])
+            forced = fe[b, :n] >= 0
+            assert np.array_equal(fe[b, :n][forced].numpy(), np.asarray(paths[b])[forced.numpy()]), (h, b)
+    # ratio 0: the plain criterion
+    enc.pae_ground_truth_ratio = 0
+    plain, _, _ = crit(model, sample)
+    assert abs(plain.item() - float(np.load(_GOLDEN / "enc_c5_small.npz")["loss"])) <= 1e-2 * abs(plain.item())
