@@ -600,11 +600,8 @@ extern "C" int s2t_attn_fused_fwd(const void* qkv, long long ldqkv, int C, void*
   p.seed = seed;
   p.seed_off = seed_offset;
   p.stream_id = stream_id;
-  static bool configured = false;
-  if (!configured) {
-    S2T_CHECK_CUDA(cudaFuncSetAttribute(attn_fused_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
-    configured = true;
-  }
+  static std::atomic<unsigned long long> configured{0};   // per device, see once_per_device
+  S2T_CHECK_CUDA(once_per_device(configured, [&] { return cudaFuncSetAttribute(attn_fused_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem); }));
   S2T_LAUNCH(attn_fused_fwd_kernel, dim3((T + kTq - 1) / kTq, heads, batch), kAttnThreads, kAttnSmem,
              reinterpret_cast<cudaStream_t>(stream), tq, tk, tv, to, p);
   return 0;
@@ -660,11 +657,8 @@ extern "C" int s2t_attn_fused_bwd(const void* qkv, long long ldqkv, int C, const
   p.seed_off = seed_offset;
   p.stream_id = stream_id;
   p.trace = trace_buffer();
-  static bool configured = false;
-  if (!configured) {
-    S2T_CHECK_CUDA(cudaFuncSetAttribute(attn_fused_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
-    configured = true;
-  }
+  static std::atomic<unsigned long long> configured{0};   // per device, see once_per_device
+  S2T_CHECK_CUDA(once_per_device(configured, [&] { return cudaFuncSetAttribute(attn_fused_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem); }));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(2, heads, batch);

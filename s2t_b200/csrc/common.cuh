@@ -8,6 +8,8 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <atomic>
+
 namespace s2t {
 
 // ---------------------------------------------------------------------------------------------
@@ -34,6 +36,21 @@ void set_last_error(const char* fmt, ...);
   } while (0)
 
 #define S2T_LAUNCH_CHECK() S2T_CHECK_CUDA(cudaGetLastError())
+
+// cudaFuncSetAttribute applies to the CURRENT device only: a call site that raises a kernel's dynamic shared memory limit
+// must do so once on every device it launches on (a process-wide `static bool` configures the first device and leaves the
+// others at the 48 KB default, so their launches fail).  `done` = one bit per device ordinal, owned by the call site.
+template <class SetFn>
+inline cudaError_t once_per_device(std::atomic<unsigned long long>& done, SetFn&& set) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (done.load(std::memory_order_acquire) & bit) return cudaSuccess;
+  e = set();
+  if (e == cudaSuccess) done.fetch_or(bit, std::memory_order_release);
+  return e;
+}
 
 // ---------------------------------------------------------------------------------------------
 // Programmatic dependent launch (PDL).  The training step is a chain of several hundred kernels of a few

@@ -244,7 +244,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int num_tiles = tiles_per_z * p.nbatch;
 
   if (threadIdx.x == 0) {
-    // with column sums a stage is free once the MMAs have retired AND the four column-sum warps have read it
+    // with column sums a stage is free once the MMAs have retired AND the kColsumWarps column-sum warps have read it
     const uint32_t empty_count = (A_MN && p.colsum != nullptr) ? 1u + kColsumWarps : 1u;
     for (int i = 0; i < Cfg::kStages; ++i) {
       mbar_init(&full_bar[i], 1);
@@ -929,13 +929,9 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     if (rc) return rc;
     kp.gate_tma = 1;
   }
-  static bool configured = false;
+  static std::atomic<unsigned long long> configured{0};   // per device, see once_per_device
   auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI>;
-  if (!configured) {
-    S2T_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        Cfg::kSmemBytes));
-    configured = true;
-  }
+  S2T_CHECK_CUDA(once_per_device(configured, [&] { return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes); }));
   const long long tiles = 1ll * ((kp.N + BN - 1) / BN) * ((kp.M + kBM - 1) / kBM) * nbatch;
   const int cap = (kp.max_ctas > 0 && kp.max_ctas < sm_count()) ? kp.max_ctas : sm_count();
   const int grid = static_cast<int>(tiles < cap ? tiles : cap);
@@ -947,13 +943,9 @@ template <int BN, int A_MN, int B_MN, int EPI>
 static int launch_gemm_splitk(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
                               const GemmKernelParams& kp, int nbatch, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
-  static bool configured = false;
+  static std::atomic<unsigned long long> configured{0};   // per device, see once_per_device
   auto kern = gemm_bf16_splitk_kernel<BN, A_MN, B_MN, EPI>;
-  if (!configured) {
-    S2T_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        Cfg::kSmemBytes));
-    configured = true;
-  }
+  S2T_CHECK_CUDA(once_per_device(configured, [&] { return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes); }));
   const long long tiles = 1ll * ((kp.N + BN - 1) / BN) * ((kp.M + kBM - 1) / kBM) * nbatch;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));

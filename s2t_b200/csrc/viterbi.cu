@@ -127,11 +127,8 @@ extern "C" int s2t_ctc_viterbi(const float* log_probs, long long lp_t_stride, lo
   const long long need = s2t_ctc_viterbi_workspace_bytes(batch, T, max_target_len);
   S2T_REQUIRE(need == 0 || (workspace != nullptr && workspace_bytes >= need), "s2t_ctc_viterbi: workspace too small");
   size_t smem = static_cast<size_t>(2) * Sp * 4 + (need == 0 ? static_cast<size_t>(T) * Sp : 0);
-  static bool configured = false;
-  if (!configured) {
-    S2T_CHECK_CUDA(cudaFuncSetAttribute(ctc_viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 210 * 1024));
-    configured = true;
-  }
+  static std::atomic<unsigned long long> configured{0};   // per device, see once_per_device
+  S2T_CHECK_CUDA(once_per_device(configured, [&] { return cudaFuncSetAttribute(ctc_viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 210 * 1024); }));
   S2T_LAUNCH(ctc_viterbi_kernel, batch, Sp, smem, reinterpret_cast<cudaStream_t>(stream), log_probs, lp_t_stride,
              lp_b_stride, targets, tgt_ld, input_lengths, target_lengths, T, Sp, blank,
              need == 0 ? static_cast<uint8_t*>(nullptr) : reinterpret_cast<uint8_t*>(workspace), states, nll);
