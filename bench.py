@@ -520,17 +520,42 @@ def run_b200(a):
         }
         print(json.dumps(line), flush=True)
     if world > 1:
-        # The captured step graph holds NCCL kernels of the process group's communicator; tearing the communicator down
-        # under it (destroy_process_group) can block forever.  Drain, meet at a barrier, drop the graphs and leave
-        # without running the communicator's destructor.
-        torch.cuda.synchronize()
-        dist.barrier()
-        for plan in list(eng.plans.values()):
-            plan.graph = None
-        torch.cuda.synchronize()
-        sys.stdout.flush()
+        teardown(torch, dist, eng)
+
+
+def teardown(torch, dist, eng) -> None:
+    """Leave a multi-rank run the way a host program has to be able to: the captured step graphs hold NCCL kernels of the
+    process group's communicator, and destroying the communicator under them can block for ever — so drain, meet at a
+    barrier, destroy the GRAPHS first (drop every reference, collect), then call destroy_process_group.  A 30 s timer is
+    the safety net (os._exit if the clean path has not finished by then; an 8-GPU box must not be held by a teardown);
+    stderr says which path was taken."""
+    import gc
+    import threading
+    import time
+    torch.cuda.synchronize()
+    dist.barrier()
+    for plan in list(eng.plans.values()):
+        plan.graph = None
+    eng.plans.clear()
+    gc.collect()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    if os.environ.get("S2T_CLEAN_EXIT", "1") != "1":
+        os._exit(0)
+
+    def bail():
+        sys.stderr.write("teardown: clean exit did not finish within 30 s, leaving through os._exit(0)\n")
         sys.stderr.flush()
         os._exit(0)
+
+    timer = threading.Timer(30.0, bail)
+    timer.daemon = True
+    timer.start()
+    t0 = time.time()
+    dist.destroy_process_group()
+    sys.stderr.write(f"teardown: graphs dropped, destroy_process_group returned after {time.time() - t0:.2f} s\n")
+    sys.stderr.flush()
 
 
 def synth_durations(n: int, seed: int = 0):
@@ -614,7 +639,7 @@ def run_bucketed(a, torch, dist, cfg, world, rank, local, peaks):
         clocks.start()
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    audio = frames = padded = h2d = 0.0
+    audio = frames = padded = h2d = dummies = 0.0
     launches = 0
     barrier()
     e0.record()
@@ -622,12 +647,13 @@ def run_bucketed(a, torch, dist, cfg, world, rank, local, peaks):
         h, P = run_step(i)                                     # H2D of the batch + step: the public call with HOST buffers
         loss_host.copy_(P.loss, non_blocking=True)
         audio += h["audio_s"]; frames += 0 if h["dummy"] else h["frames"]; padded += h["padded"]
+        dummies += 1.0 if h["dummy"] else 0.0
         h2d += sum(t.numel() * t.element_size() for t in h["t"])
         launches += getattr(P, "launches", 0)
     e1.record()
     barrier()
     ms_local = e0.elapsed_time(e1)
-    stats = torch.tensor([ms_local, -ms_local, audio, frames, padded], device="cuda", dtype=torch.float64)
+    stats = torch.tensor([ms_local, -ms_local, audio, frames, padded, dummies], device="cuda", dtype=torch.float64)
     if world > 1:
         mx = stats.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = stats.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
@@ -651,18 +677,13 @@ def run_bucketed(a, torch, dist, cfg, world, rank, local, peaks):
             "bucketing": {"real_frames": float(sm[3]), "padded_frames": float(sm[4]),
                           "padding_efficiency": float(sm[3]) / max(float(sm[4]), 1.0),
                           "rank_time_ms_min": ms_min, "rank_time_ms_max": ms_total,
+                          "dummy_batches_in_timed_steps": int(sm[5]),
                           "rank0_plan_cache": eng.plan_cache_stats(), "bucket_frames": bs.all_frames()[:8] + ["..."]},
             "gpu_launches": launches, "clocks": clk, "roofline": None, "cpu_baseline": None,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
-        torch.cuda.synchronize()
-        dist.barrier()
-        for plan in list(eng.plans.values()):
-            plan.graph = None
-        torch.cuda.synchronize()
-        sys.stdout.flush()
-        os._exit(0)
+        teardown(torch, dist, eng)
 
 
 def data_parallel_check(torch, dist, eng, P, host0, dual, world, rank):
